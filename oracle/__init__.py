@@ -1,0 +1,6 @@
+"""CPU oracle for the association hot path -- TEST INFRASTRUCTURE ONLY.
+
+Nothing under ``boxmot_b200/`` may import this package.  Only ``tests/``,
+``__graft_entry__.smoke()`` and the ``cpu_baseline`` / ``--impl reference`` legs of
+``bench.py`` use it, and only as the checker / reported CPU baseline.
+"""
