@@ -39,6 +39,8 @@ typedef struct {
     int nr, nc, n, extended;
     cost_t pad;
     long scans; /* instrumentation: number of full row/column sweeps */
+    int skip_mode;      /* 1: model of the GPU shortcut (see scan_cols) */
+    int hm_set; cost_t hmax;
 } mat_t;
 
 static inline cost_t at(const mat_t *m, int i, int j)
@@ -154,6 +156,14 @@ static int scan_cols(mat_t *m, int *plo, int *phi, cost_t *d, int *cols, int *pr
         const int i = y[j];
         const cost_t mind = d[j];
         const cost_t h = at(m, i, j) - v[j] - mind;
+        if (m->skip_mode && m->extended && i >= m->nr) {
+            /* All dummy rows hold the same entries, so a sweep from a dummy row with
+             * h <= an earlier dummy sweep's h (same path) cannot lower any d[j]:
+             * (c - v[j]) - h is monotone in h.  The CUDA solver skips such sweeps;
+             * this branch is its CPU model (results must equal the plain algorithm). */
+            if (m->hm_set && h <= m->hmax) continue;
+            m->hmax = h; m->hm_set = 1;
+        }
         m->scans++;
         for (int k = hi; k < n; k++) {
             j = cols[k];
@@ -179,6 +189,7 @@ static int find_path(mat_t *m, int start, const int *y, cost_t *v, int *pred,
 {
     const int n = m->n;
     int lo = 0, hi = 0, final_j = -1, n_ready = 0;
+    m->hm_set = 0;
     for (int j = 0; j < n; j++) {
         cols[j] = j; pred[j] = start; d[j] = at(m, start, j) - v[j];
     }
@@ -248,10 +259,11 @@ static void solve_square(mat_t *m, int *x, int *y)
  * Returns 0, or -1 for a non-square matrix without extension.  *scans (optional)
  * receives the number of row sweeps performed (used to size the GPU work estimate).
  */
-int oracle_lapjv(const double *cost, int nr, int nc, int extend, double cost_limit,
-                 int *x, int *y, long *scans)
+static int lapjv_impl(const double *cost, int nr, int nc, int extend, double cost_limit,
+                      int *x, int *y, long *scans, int skip_mode)
 {
     mat_t m;
+    m.skip_mode = skip_mode; m.hm_set = 0; m.hmax = 0.0;
     const int limited = cost_limit < DBL_MAX;
     m.c = cost; m.nr = nr; m.nc = nc; m.scans = 0;
     if (scans) *scans = 0;
@@ -280,4 +292,17 @@ int oracle_lapjv(const double *cost, int nr, int nc, int extend, double cost_lim
     if (scans) *scans = m.scans;
     free(xe); free(ye);
     return 0;
+}
+
+int oracle_lapjv(const double *cost, int nr, int nc, int extend, double cost_limit,
+                 int *x, int *y, long *scans)
+{
+    return lapjv_impl(cost, nr, nc, extend, cost_limit, x, y, scans, 0);
+}
+
+/* CPU model of the CUDA solver's exact shortcut (tests assert it equals oracle_lapjv). */
+int oracle_lapjv_skip(const double *cost, int nr, int nc, int extend, double cost_limit,
+                      int *x, int *y, long *scans)
+{
+    return lapjv_impl(cost, nr, nc, extend, cost_limit, x, y, scans, 1);
 }
