@@ -1,0 +1,63 @@
+"""ctypes loader for libboxmot_b200.so (the C ABI declared in include/boxmot_b200.h).
+
+There is no CPU fallback: if the library is missing or a call fails, this raises."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libboxmot_b200.so")
+_lib = None
+
+c_void_p, c_int, c_double = ctypes.c_void_p, ctypes.c_int, ctypes.c_double
+
+
+class OcsortConfig(ctypes.Structure):
+    _fields_ = [(n, c_double) for n in ("det_thresh", "min_conf", "asso_threshold", "inertia",
+                                         "q_xy_scaling", "q_s_scaling")] + \
+               [(n, c_int) for n in ("max_age", "min_hits", "delta_t", "asso_func", "use_byte",
+                                      "img_w", "img_h")]
+
+
+ASSO_FUNCS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hmiou": 4, "centroid": 5}
+
+_SIGS = {
+    "bm_last_error": (ctypes.c_char_p, []),
+    "bm_version": (c_int, []),
+    "bm_ocsort_create": (c_int, [ctypes.POINTER(OcsortConfig), c_int, c_int, c_int, c_int,
+                                 ctypes.POINTER(c_void_p)]),
+    "bm_ocsort_destroy": (c_int, [c_void_p]),
+    "bm_ocsort_reset": (c_int, [c_void_p, c_void_p]),
+    "bm_ocsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_ocsort_status": (c_int, [c_void_p, ctypes.POINTER(c_int),
+                                 ctypes.POINTER(ctypes.c_ulonglong),
+                                 ctypes.POINTER(ctypes.c_ulonglong), c_void_p]),
+    "bm_ocsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p,
+                               c_void_p, c_void_p]),
+    "bm_lap_solve_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
+                                   c_void_p, c_void_p, c_void_p]),
+    "bm_iou_matrix": (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_double, c_double,
+                              c_void_p, c_void_p]),
+    "bm_xysr_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
+    "bm_xysr_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+}
+EXPORTS = tuple(_SIGS)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libboxmot_b200.so is not built (run `python -m boxmot_b200.build`); "
+                "there is no CPU fallback for the association path")
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        raise RuntimeError("%s failed (%d): %s" % (what, rc, lib().bm_last_error().decode()))

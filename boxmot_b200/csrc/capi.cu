@@ -1,0 +1,173 @@
+// extern "C" surface of libboxmot_b200.so (declarations: include/boxmot_b200.h).
+#include "../../include/boxmot_b200.h"
+#include "ocsort_engine.cuh"
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <vector>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    if (e != cudaSuccess) snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(g_err, sizeof(g_err), "%s", what);
+    return code;
+}
+
+#define BM_CUDA(call)                                         \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) return fail(-2, #call, e_);    \
+    } while (0)
+
+struct OcsEngine {
+    bm::OcsState st;
+    bm::OcsParams pr;
+    std::vector<void*> allocs;
+    size_t smem;
+};
+
+template <typename T>
+cudaError_t dev_alloc(OcsEngine* e, T** p, size_t n) {
+    cudaError_t r = cudaMalloc(reinterpret_cast<void**>(p), n * sizeof(T));
+    if (r == cudaSuccess) e->allocs.push_back(*p);
+    return r;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* bm_last_error(void) { return g_err; }
+int bm_version(void) { return 100; }
+
+int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, int det_cap,
+                     int smem_cost_bytes, void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
+        return fail(-1, "bm_ocsort_create: bad argument");
+    if (cfg->delta_t < 1 || cfg->delta_t > 16) return fail(-1, "bm_ocsort_create: delta_t out of range");
+    OcsEngine* e = new (std::nothrow) OcsEngine();
+    if (!e) return fail(-3, "out of host memory");
+    bm::OcsState& st = e->st;
+    st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap; st.R = cfg->delta_t;
+    st.scratch_elems = (size_t)track_cap * det_cap;
+    st.smem_cost_elems = smem_cost_bytes / 8;
+    bm::OcsParams& pr = e->pr;
+    pr.det_thresh = cfg->det_thresh; pr.min_conf = cfg->min_conf; pr.iou_thr = cfg->asso_threshold;
+    pr.inertia = cfg->inertia; pr.q_xy = cfg->q_xy_scaling; pr.q_s = cfg->q_s_scaling;
+    pr.diag = sqrt((double)cfg->img_w * cfg->img_w + (double)cfg->img_h * cfg->img_h);
+    pr.max_age = cfg->max_age; pr.min_hits = cfg->min_hits; pr.delta_t = cfg->delta_t;
+    pr.asso_func = cfg->asso_func; pr.use_byte = cfg->use_byte ? 1 : 0;
+    const size_t S = n_streams, T = track_cap;
+    cudaError_t r = cudaSuccess;
+    if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * 56 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.sxP, S * 56 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.lastz, S * 4 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.lastobs, S * 5 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.vel, S * 2 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.confcls, S * 2 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.ring, S * st.R * 4 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.ring_age, S * st.R * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.ints, S * bm::OI_COUNT * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.order, S * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.hdr, S * bm::OH_COUNT);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.n_updates, S);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.scratch, S * st.scratch_elems);
+    e->smem = bm::ocsort_step_smem(st, pr);
+    if (r == cudaSuccess) r = bm::ocsort_step_configure(e->smem);
+    if (r != cudaSuccess) {
+        for (void* p : e->allocs) cudaFree(p);
+        delete e;
+        return fail(-2, "bm_ocsort_create", r);
+    }
+    *handle = e;
+    return bm_ocsort_reset(e, nullptr);
+}
+
+int bm_ocsort_destroy(void* handle) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return 0;
+    for (void* p : e->allocs) cudaFree(p);
+    delete e;
+    return 0;
+}
+
+int bm_ocsort_reset(void* handle, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::OcsState& st = e->st;
+    const size_t S = st.S, T = st.Tcap;
+    BM_CUDA(cudaMemsetAsync(st.hdr, 0, S * bm::OH_COUNT * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.n_updates, 0, S * sizeof(unsigned long long), s));
+    BM_CUDA(cudaMemsetAsync(st.order, 0, S * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::OI_COUNT * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.xP, 0, S * 56 * T * sizeof(double), s));
+    BM_CUDA(cudaMemsetAsync(st.sxP, 0, S * 56 * T * sizeof(double), s));
+    return 0;
+}
+
+int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out, int* d_nout,
+                   void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_ocsort_step: null argument");
+    BM_CUDA(bm::ocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
+                                   static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_updates,
+                     unsigned long long* lap_solves, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int S = e->st.S;
+    std::vector<int> hdr((size_t)S * bm::OH_COUNT);
+    std::vector<unsigned long long> nu(S);
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), e->st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(nu.data(), e->st.n_updates, nu.size() * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    int err = 0;
+    unsigned long long tot = 0, laps = 0;
+    for (int i = 0; i < S; i++) {
+        err |= hdr[(size_t)i * bm::OH_COUNT + bm::OH_ERR];
+        laps += (unsigned long long)hdr[(size_t)i * bm::OH_COUNT + bm::OH_LAPS];
+        tot += nu[i];
+    }
+    if (err_bits) *err_bits = err;
+    if (track_updates) *track_updates = tot;
+    if (lap_solves) *lap_solves = laps;
+    return 0;
+}
+
+int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P, int* h_ids, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || si < 0 || si >= e->st.S) return fail(-1, "bm_ocsort_peek: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::OcsState& st = e->st;
+    const size_t T = st.Tcap;
+    std::vector<double> xp(56 * T);
+    std::vector<int> order(T), ints(bm::OI_COUNT * T), hdr(bm::OH_COUNT);
+    BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * 56 * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(order.data(), st.order + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::OI_COUNT * T, ints.size() * 4,
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), st.hdr + (size_t)si * bm::OH_COUNT, hdr.size() * 4,
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    const int n = hdr[bm::OH_NLIST];
+    if (n_tracks) *n_tracks = n;
+    for (int p = 0; p < n; p++) {
+        const int slot = order[p];
+        if (h_x) for (int c = 0; c < 7; c++) h_x[p * 7 + c] = xp[c * T + slot];
+        if (h_P) for (int c = 0; c < 49; c++) h_P[p * 49 + c] = xp[(7 + c) * T + slot];
+        if (h_ids) h_ids[p] = ints[bm::OI_ID * T + slot];
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <math_constants.h>
 
 #define BM_WARP 32
 #define BM_FULL 0xffffffffu

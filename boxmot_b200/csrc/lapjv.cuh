@@ -69,7 +69,7 @@ __device__ __forceinline__ double warp_min_d(double v) {
 }
 
 // Phase 1: column reduction + reduction transfer.  Returns the number of free rows.
-__device__ int lap_ccrrt(const LapMat& m, LapWork& w) {
+static __device__ int lap_ccrrt(const LapMat& m, LapWork& w) {
     const int n = m.n, lane = lane_id();
     for (int j = lane; j < n; j += 32) {
         double vm = BM_LAP_LARGE;
@@ -129,7 +129,7 @@ __device__ int lap_ccrrt(const LapMat& m, LapWork& w) {
 }
 
 // Phase 2: augmenting row reduction.
-__device__ int lap_carr(const LapMat& m, LapWork& w, int n_free) {
+static __device__ int lap_carr(const LapMat& m, LapWork& w, int n_free) {
     const int n = m.n, lane = lane_id();
     int current = 0, new_free = 0;
     long long rr_cnt = 0;
@@ -180,7 +180,7 @@ __device__ int lap_carr(const LapMat& m, LapWork& w, int n_free) {
 // Phase 3 helper: one shortest augmenting path from free row `start` (modified
 // Dijkstra over the TODO/SCAN/READY partition of `cols`).  Returns the free column
 // that ends the path, or -1 when the iteration guard trips (non-finite costs).
-__device__ int lap_find_path(const LapMat& m, LapWork& w, int start) {
+static __device__ int lap_find_path(const LapMat& m, LapWork& w, int start) {
     const int n = m.n, lane = lane_id();
     for (int j = lane; j < n; j += 32) {
         w.cols[j] = j;
@@ -287,7 +287,7 @@ __device__ int lap_find_path(const LapMat& m, LapWork& w, int start) {
 
 // Solve the assignment problem; on return w.x[i] (i < n) / w.y[j] (j < n) hold the
 // extended assignment.  Returns 0, or 1 when a guard tripped (non-finite costs).
-__device__ int lap_solve_warp(const LapMat& m, LapWork& w) {
+static __device__ int lap_solve_warp(const LapMat& m, LapWork& w) {
     const int lane = lane_id();
     int n_free = lap_ccrrt(m, w);
     for (int it = 0; n_free > 0 && it < 2; it++) n_free = lap_carr(m, w, n_free);

@@ -1,0 +1,217 @@
+// Device-resident, stream-batched OC-SORT engine: state layout and per-track helpers.
+//
+// One engine holds S independent streams (one reference `OcSort` instance each,
+// boxmot/trackers/ocsort/ocsort.py:195-439).  Track state is SoA in HBM,
+// [stream][field][slot] with `slot` fastest, so a warp that walks consecutive slots
+// issues fully coalesced 8-byte loads.  Slots are stable for the life of a track; the
+// reference's ordered `active_tracks` list is the per-stream `order` array
+// (list position -> slot), which is what keeps cost-matrix column order -- and with it
+// lapjv's tie-breaking -- identical to the reference.
+#pragma once
+#include "common.cuh"
+#include "kf_xysr.cuh"
+#include "iou.cuh"
+#include "lapjv.cuh"
+
+namespace bm {
+
+enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
+enum { OF_OBSERVED = 1, OF_SAVED = 2 };
+enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_COUNT = 8 };
+
+struct OcsParams {
+    double det_thresh, min_conf, iou_thr, inertia, q_xy, q_s, diag;
+    int max_age, min_hits, delta_t, asso_func, use_byte;
+};
+
+struct OcsState {
+    int S, Tcap, Dcap, R;
+    size_t scratch_elems;          // doubles of global cost scratch per stream
+    int smem_cost_elems;           // doubles of shared-memory cost region per CTA
+    double* xP;                    // [S][56][Tcap]   x(7) then P(49) row-major
+    double* sxP;                   // [S][56][Tcap]   state frozen at the first miss (ORU)
+    double* lastz;                 // [S][4][Tcap]    last real measurement (xc,yc,s,r)
+    double* lastobs;               // [S][5][Tcap]    last observation x1,y1,x2,y2,conf (-1 = none)
+    double* vel;                   // [S][2][Tcap]    (dy, dx) unit direction
+    double* confcls;               // [S][2][Tcap]
+    double* ring;                  // [S][R][4][Tcap] observations of the last delta_t ages
+    int* ring_age;                 // [S][R][Tcap]
+    int* ints;                     // [S][OI_COUNT][Tcap]
+    int* order;                    // [S][Tcap]
+    int* hdr;                      // [S][OH_COUNT]
+    unsigned long long* n_updates; // [S] live tracks that entered predict (bench unit)
+    double* scratch;               // [S][scratch_elems]
+};
+
+struct OcsView {   // per-stream base pointers
+    double *xP, *sxP, *lastz, *lastobs, *vel, *confcls, *ring;
+    int *ring_age, *ints, *order, *hdr;
+    int Tcap, R;
+    __device__ OcsView(const OcsState& st, int s) : Tcap(st.Tcap), R(st.R) {
+        const size_t T = st.Tcap;
+        xP = st.xP + (size_t)s * 56 * T;
+        sxP = st.sxP + (size_t)s * 56 * T;
+        lastz = st.lastz + (size_t)s * 4 * T;
+        lastobs = st.lastobs + (size_t)s * 5 * T;
+        vel = st.vel + (size_t)s * 2 * T;
+        confcls = st.confcls + (size_t)s * 2 * T;
+        ring = st.ring + (size_t)s * st.R * 4 * T;
+        ring_age = st.ring_age + (size_t)s * st.R * T;
+        ints = st.ints + (size_t)s * OI_COUNT * T;
+        order = st.order + (size_t)s * T;
+        hdr = st.hdr + (size_t)s * OH_COUNT;
+    }
+    __device__ __forceinline__ int& I(int f, int slot) const { return ints[f * Tcap + slot]; }
+};
+
+__device__ __forceinline__ void load_xP(const double* base, int Tcap, int slot, double* x, double* P) {
+#pragma unroll
+    for (int c = 0; c < 7; c++) x[c] = base[c * Tcap + slot];
+#pragma unroll
+    for (int c = 0; c < 49; c++) P[c] = base[(7 + c) * Tcap + slot];
+}
+__device__ __forceinline__ void store_xP(double* base, int Tcap, int slot, const double* x, const double* P) {
+#pragma unroll
+    for (int c = 0; c < 7; c++) base[c * Tcap + slot] = x[c];
+#pragma unroll
+    for (int c = 0; c < 49; c++) base[(7 + c) * Tcap + slot] = P[c];
+}
+
+// Observation `delta_t` steps back (ocsort.py:17-28 / :146-152): the stored box of age
+// cur_age-dt for dt = delta_t..1, else the last observation.  Returns false when the
+// track has never been observed.
+__device__ __forceinline__ bool ocs_lookback(const OcsView& v, int slot, int cur_age, int delta_t,
+                                             double* box) {
+    if (v.I(OI_HITS, slot) == 0) return false;
+    for (int dt = delta_t; dt >= 1; dt--) {
+        const int a = cur_age - dt;
+        if (a < 0) continue;
+        const int r = a % v.R;
+        if (v.ring_age[r * v.Tcap + slot] == a) {
+#pragma unroll
+            for (int c = 0; c < 4; c++) box[c] = v.ring[(r * 4 + c) * v.Tcap + slot];
+            return true;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) box[c] = v.lastobs[c * v.Tcap + slot];
+    return true;
+}
+
+// KalmanBoxTracker.update(bbox, cls, det_ind) with a real detection (ocsort.py:136-169)
+// followed by KalmanFilterXYSR.update (xysr_kf.py:211-291, ORU at :249-254).
+__device__ inline void ocs_track_update(const OcsView& v, int slot, const double* det /*x1,y1,x2,y2,conf*/,
+                                        double cls, int det_ind, int delta_t, const XysrConst& kc) {
+    const int T = v.Tcap;
+    v.I(OI_DETIND, slot) = det_ind;
+    v.confcls[0 * T + slot] = det[4];
+    v.confcls[1 * T + slot] = cls;
+    const int age = v.I(OI_AGE, slot);
+    // `if self.last_observation.sum() >= 0` -- numpy sums 5 values left to right
+    double lo[5];
+#pragma unroll
+    for (int c = 0; c < 5; c++) lo[c] = v.lastobs[c * T + slot];
+    const double lsum = (((lo[0] + lo[1]) + lo[2]) + lo[3]) + lo[4];
+    if (lsum >= 0) {
+        double pb[4];
+        bool found = false;
+        for (int dt = delta_t; dt >= 1 && !found; dt--) {
+            const int a = age - dt;
+            if (a < 0) continue;
+            const int r = a % v.R;
+            if (v.ring_age[r * T + slot] == a) {
+#pragma unroll
+                for (int c = 0; c < 4; c++) pb[c] = v.ring[(r * 4 + c) * T + slot];
+                found = true;
+            }
+        }
+        if (!found) {
+#pragma unroll
+            for (int c = 0; c < 4; c++) pb[c] = lo[c];
+        }
+        // speed_direction(previous_box, bbox)  (ocsort.py:48-53)
+        const double cx1 = (pb[0] + pb[2]) / 2.0, cy1 = (pb[1] + pb[3]) / 2.0;
+        const double cx2 = (det[0] + det[2]) / 2.0, cy2 = (det[1] + det[3]) / 2.0;
+        const double dy = cy2 - cy1, dx = cx2 - cx1;
+        const double norm = sqrt(dy * dy + dx * dx) + 1e-6;
+        v.vel[0 * T + slot] = dy / norm;
+        v.vel[1 * T + slot] = dx / norm;
+    }
+#pragma unroll
+    for (int c = 0; c < 5; c++) v.lastobs[c * T + slot] = det[c];
+    {
+        const int r = age % v.R;
+        v.ring_age[r * T + slot] = age;
+#pragma unroll
+        for (int c = 0; c < 4; c++) v.ring[(r * 4 + c) * T + slot] = det[c];
+    }
+    v.I(OI_TSU, slot) = 0;
+    v.I(OI_HITS, slot) += 1;
+    v.I(OI_STREAK, slot) += 1;
+
+    double z[4];
+    xyxy_to_z(det, z);
+    double x[7], P[49];
+    int flags = v.I(OI_FLAGS, slot);
+    if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
+        load_xP(v.sxP, T, slot, x, P);
+        double z1[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) z1[c] = v.lastz[c * T + slot];
+        xysr_oru_replay(x, P, z1, z, v.I(OI_NNONE, slot) + 1, kc);
+    } else {
+        load_xP(v.xP, T, slot, x, P);
+    }
+    xysr_update(x, P, z);
+    store_xP(v.xP, T, slot, x, P);
+#pragma unroll
+    for (int c = 0; c < 4; c++) v.lastz[c * T + slot] = z[c];
+    v.I(OI_FLAGS, slot) = flags | OF_OBSERVED;
+    v.I(OI_NNONE, slot) = 0;
+}
+
+// KalmanBoxTracker.update(None, ...) (ocsort.py:170-171 -> xysr_kf.py:233-246)
+__device__ inline void ocs_track_miss(const OcsView& v, int slot) {
+    const int T = v.Tcap;
+    int flags = v.I(OI_FLAGS, slot);
+    if (flags & OF_OBSERVED) {
+        for (int c = 0; c < 56; c++) v.sxP[c * T + slot] = v.xP[c * T + slot];
+        flags |= OF_SAVED;
+    }
+    v.I(OI_FLAGS, slot) = flags & ~OF_OBSERVED;
+    v.I(OI_NNONE, slot) += 1;
+}
+
+// KalmanBoxTracker.__init__ (ocsort.py:63-134)
+__device__ inline void ocs_track_init(const OcsView& v, int slot, const double* det, double cls,
+                                      int det_ind, int id) {
+    const int T = v.Tcap;
+    double z[4], x[7], P[49];
+    xyxy_to_z(det, z);
+    xysr_init(x, P, z);
+    store_xP(v.xP, T, slot, x, P);
+    v.I(OI_ID, slot) = id;
+    v.I(OI_TSU, slot) = 0;
+    v.I(OI_HITS, slot) = 0;
+    v.I(OI_STREAK, slot) = 0;
+    v.I(OI_AGE, slot) = 0;
+    v.I(OI_DETIND, slot) = det_ind;
+    v.I(OI_FLAGS, slot) = 0;
+    v.I(OI_NNONE, slot) = 0;
+    v.confcls[0 * T + slot] = det[4];
+    v.confcls[1 * T + slot] = cls;
+#pragma unroll
+    for (int c = 0; c < 5; c++) v.lastobs[c * T + slot] = -1.0;
+    v.vel[0 * T + slot] = 0.0;
+    v.vel[1 * T + slot] = 0.0;
+    for (int r = 0; r < v.R; r++) v.ring_age[r * T + slot] = -1;
+}
+
+}  // namespace bm
+
+namespace bm {
+size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr);
+cudaError_t ocsort_step_configure(size_t smem);
+cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
+                               double* out, int* nout, cudaStream_t stream);
+}  // namespace bm

@@ -1,0 +1,136 @@
+// Stand-alone kernels behind the unit-testable C-ABI entry points (function-level
+// parity tests call the same device code the fused engines use).
+#include "../../include/boxmot_b200.h"
+#include "iou.cuh"
+#include "kf_xysr.cuh"
+#include "lapjv.cuh"
+#include <cstdio>
+#include <limits>
+
+namespace bm {
+
+// One warp per problem, LAP_WPB problems per CTA.  The cost block is read in place
+// from global memory (L2-resident at these sizes).
+constexpr int LAP_WPB = 4;
+
+__global__ void __launch_bounds__(LAP_WPB * 32)
+lap_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, int nc_max,
+                 const int* __restrict__ nr_, const int* __restrict__ nc_, double cost_limit,
+                 int limited, int* __restrict__ x_out, int* __restrict__ y_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int wid = warp_id(), lane = lane_id();
+    const int b = blockIdx.x * LAP_WPB + wid;
+    if (b >= n_problems) return;
+    const int nr = nr_[b], nc = nc_[b];
+    int* x = x_out + (size_t)b * nr_max;
+    int* y = y_out + (size_t)b * nc_max;
+    if (nr <= 0 || nc <= 0) {
+        for (int i = lane; i < nr_max; i += 32) x[i] = -1;
+        for (int j = lane; j < nc_max; j += 32) y[j] = -1;
+        return;
+    }
+    const double* c = cost + (size_t)b * nr_max * nc_max;
+    double pad;
+    if (limited) pad = cost_limit / 2.0;
+    else {
+        double mx = -CUDART_INF;
+        for (int e = lane; e < nr * nc; e += 32) mx = fmax(mx, c[(size_t)(e / nc) * nc_max + (e % nc)]);
+        for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, shfl_xor_d(mx, o));
+        pad = mx + 1.0;
+    }
+    const size_t wbytes = (lap_work_bytes(nr_max + nc_max) + 15) / 16 * 16;
+    LapWork w = lap_carve(smem_raw + (size_t)wid * wbytes, nr + nc);
+    LapMat m = {c, nc_max, nr, nc, nr + nc, 1, pad};
+    lap_solve_warp(m, w);
+    for (int i = lane; i < nr_max; i += 32) x[i] = (i < nr && w.x[i] < nc) ? w.x[i] : -1;
+    for (int j = lane; j < nc_max; j += 32) y[j] = (j < nc && w.y[j] < nr) ? w.y[j] : -1;
+}
+
+__global__ void iou_matrix_kernel(int func, const double* __restrict__ a, int na,
+                                  const double* __restrict__ b, int nb, double diag,
+                                  double* __restrict__ out) {
+    const size_t total = (size_t)na * nb;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total;
+         e += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(e / nb), j = (int)(e % nb);
+        Box A = {a[i * 4 + 0], a[i * 4 + 1], a[i * 4 + 2], a[i * 4 + 3]};
+        Box B = {b[j * 4 + 0], b[j * 4 + 1], b[j * 4 + 2], b[j * 4 + 3]};
+        out[e] = asso_pair(func, A, B, diag);
+    }
+}
+
+__global__ void xysr_predict_kernel(double* x, double* P, int n, XysrConst kc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double xs[7], Ps[49];
+    for (int c = 0; c < 7; c++) xs[c] = x[(size_t)i * 7 + c];
+    for (int c = 0; c < 49; c++) Ps[c] = P[(size_t)i * 49 + c];
+    xysr_predict(xs, Ps, kc);
+    for (int c = 0; c < 7; c++) x[(size_t)i * 7 + c] = xs[c];
+    for (int c = 0; c < 49; c++) P[(size_t)i * 49 + c] = Ps[c];
+}
+
+__global__ void xysr_update_kernel(double* x, double* P, const double* z, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double xs[7], Ps[49], zs[4];
+    for (int c = 0; c < 7; c++) xs[c] = x[(size_t)i * 7 + c];
+    for (int c = 0; c < 49; c++) Ps[c] = P[(size_t)i * 49 + c];
+    for (int c = 0; c < 4; c++) zs[c] = z[(size_t)i * 4 + c];
+    xysr_update(xs, Ps, zs);
+    for (int c = 0; c < 7; c++) x[(size_t)i * 7 + c] = xs[c];
+    for (int c = 0; c < 49; c++) P[(size_t)i * 49 + c] = Ps[c];
+}
+
+}  // namespace bm
+
+static int unit_fail(const char* what, cudaError_t e) {
+    fprintf(stderr, "boxmot_b200: %s: %s\n", what, cudaGetErrorString(e));
+    return -2;
+}
+
+extern "C" {
+
+int bm_lap_solve_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                       const int* d_nc, double cost_limit, int* d_x, int* d_y, void* stream) {
+    if (n_problems <= 0) return 0;
+    const int limited = cost_limit < std::numeric_limits<double>::max();
+    const size_t wbytes = (bm::lap_work_bytes(nr_max + nc_max) + 15) / 16 * 16;
+    const size_t smem = wbytes * bm::LAP_WPB;
+    cudaError_t e = cudaFuncSetAttribute(bm::lap_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return unit_fail("lap smem", e);
+    const int grid = (n_problems + bm::LAP_WPB - 1) / bm::LAP_WPB;
+    bm::lap_batch_kernel<<<grid, bm::LAP_WPB * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, cost_limit, limited, d_x, d_y);
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("lap_batch_kernel", e);
+}
+
+int bm_iou_matrix(int asso_func, const double* d_a, int na, const double* d_b, int nb, double img_w,
+                  double img_h, double* d_out, void* stream) {
+    if (na <= 0 || nb <= 0) return 0;
+    const size_t total = (size_t)na * nb;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    bm::iou_matrix_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        asso_func, d_a, na, d_b, nb, sqrt(img_w * img_w + img_h * img_h), d_out);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("iou_matrix_kernel", e);
+}
+
+int bm_xysr_predict(double* d_x, double* d_P, int n, double q_xy, double q_s, void* stream) {
+    if (n <= 0) return 0;
+    bm::XysrConst kc = {q_xy, q_s};
+    bm::xysr_predict_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_P, n, kc);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("xysr_predict_kernel", e);
+}
+
+int bm_xysr_update(double* d_x, double* d_P, const double* d_z, int n, void* stream) {
+    if (n <= 0) return 0;
+    bm::xysr_update_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_P, d_z, n);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("xysr_update_kernel", e);
+}
+
+}  // extern "C"

@@ -1,0 +1,81 @@
+/*
+ * boxmot_b200.h -- C ABI of the B200-native association engine (libboxmot_b200.so).
+ *
+ * The reference (muntherr/boxmot) is pure Python and has no FFI; the entry points
+ * below are what a ctypes binding for its per-frame association path binds.  Each
+ * declaration cites the reference interface it replaces (paths under the reference
+ * tree).  Conventions: every function returns 0 on success and a negative code on
+ * failure (message via bm_last_error()); all pointers named d_* are DEVICE pointers
+ * owned by the caller; `stream` is a cudaStream_t passed as void*; the library
+ * allocates only the opaque engine state at create.  There is no CPU fallback.
+ */
+#ifndef BOXMOT_B200_H
+#define BOXMOT_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* bm_last_error(void);
+int bm_version(void);
+
+/* Association functions: boxmot/utils/iou.py:320-346 (AssociationFunction selector). */
+enum { BM_ASSO_IOU = 0, BM_ASSO_GIOU = 1, BM_ASSO_DIOU = 2, BM_ASSO_CIOU = 3, BM_ASSO_HMIOU = 4, BM_ASSO_CENTROID = 5 };
+
+/* ---- OC-SORT engine: S independent streams, one reference OcSort instance each.
+ * Replaces OcSort.__init__/update (boxmot/trackers/ocsort/ocsort.py:213-244, :246-439),
+ * KalmanBoxTracker (:56-192), KalmanFilterXYSR (boxmot/motion/kalman_filters/aabb/
+ * xysr_kf.py:137-291) and associate (boxmot/utils/association.py:377-556). */
+typedef struct bm_ocsort_config {
+    double det_thresh, min_conf, asso_threshold, inertia, q_xy_scaling, q_s_scaling;
+    int max_age, min_hits, delta_t, asso_func, use_byte;
+    int img_w, img_h;              /* only used by the centroid association function */
+} bm_ocsort_config;
+
+/* track_cap / det_cap: per-stream capacities (exceeding them sets an error bit, never
+ * truncates silently).  smem_cost_bytes: shared memory reserved per CTA for the cost
+ * matrix (larger matrices go to an L2-resident global scratch). */
+int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, int det_cap,
+                     int smem_cost_bytes, void** handle);
+int bm_ocsort_destroy(void* handle);
+int bm_ocsort_reset(void* handle, void* stream);
+/* One frame for all streams.  d_dets [S][det_cap][6] float32 (x1,y1,x2,y2,conf,cls):
+ * float32 is the reference's own input precision (basetracker.py:122-128 converts every
+ * ndarray).  d_ndets [S] int32.  d_out [S][track_cap][8] float64 rows
+ * (x1,y1,x2,y2,id,conf,cls,det_ind) in the reference's row order, d_nout [S] int32. */
+int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
+                   int* d_nout, void* stream);
+/* Synchronises `stream`; returns the OR of all per-stream error bits in *err_bits, the
+ * number of live tracks that entered predict since create/reset in *track_updates and
+ * the number of lapjv solves in *lap_solves. */
+int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_updates,
+                     unsigned long long* lap_solves, void* stream);
+/* Debug / test access: copy one stream's list length and per-track Kalman state
+ * (list order) to host buffers x[track_cap*7], P[track_cap*49], ids[track_cap]. */
+int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
+                   int* h_ids, void* stream);
+
+/* ---- unit-testable kernels ---------------------------------------------------- */
+
+/* lap.lapjv(cost, extend_cost=True, cost_limit) for a batch of problems (call sites:
+ * boxmot/utils/matching.py:54-55, association.py:50-51,109, boosttrack/assoc.py:113).
+ * d_cost [B][nr_max][nc_max] float64, per-problem sizes d_nr/d_nc, cost_limit = +inf
+ * for "no limit".  d_x [B][nr_max], d_y [B][nc_max] (-1 = unassigned). */
+int bm_lap_solve_batch(const double* d_cost, int n_problems, int nr_max, int nc_max,
+                       const int* d_nr, const int* d_nc, double cost_limit, int* d_x, int* d_y,
+                       void* stream);
+
+/* AssociationFunction.*_batch (boxmot/utils/iou.py:50-307): d_a [A][4], d_b [B][4]
+ * xyxy float64 -> d_out [A][B] float64. */
+int bm_iou_matrix(int asso_func, const double* d_a, int na, const double* d_b, int nb,
+                  double img_w, double img_h, double* d_out, void* stream);
+
+/* KalmanFilterXYSR.predict / update with OC-SORT constants (xysr_kf.py:137-175,
+ * :256-291; ocsort.py:83-113): d_x [N][7], d_P [N][49] updated in place, d_z [N][4]. */
+int bm_xysr_predict(double* d_x, double* d_P, int n, double q_xy, double q_s, void* stream);
+int bm_xysr_update(double* d_x, double* d_P, const double* d_z, int n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

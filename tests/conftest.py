@@ -1,0 +1,68 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def mot17_frames(seq):
+    """Per-frame (N,6) detection arrays of a MOT17-mini sequence (fixture copy of
+    assets/MOT17-mini/train/<seq>/det/det.txt, see oracle/gen_golden.py)."""
+    rows = np.load(os.path.join(GOLD, "mot17_mini_dets.npz"))[seq].astype(np.float64)
+    n = int(rows[:, 0].max())
+    return [np.c_[rows[rows[:, 0] == f][:, 1:], np.zeros(int((rows[:, 0] == f).sum()))]
+            for f in range(1, n + 1)]
+
+
+def golden_rows(tracker, case):
+    z = np.load(os.path.join(GOLD, "ref_%s_%s.npz" % (tracker, case)))
+    rows = z["rows"]
+    kw = eval(str(z["kw"])) if "kw" in z.files else {}
+    return rows, kw
+
+
+def split_by_frame(rows, n_frames):
+    return [rows[rows[:, 0] == f][:, 1:] for f in range(n_frames)]
+
+
+SYNTH_CASES = {
+    "synth_k100": (0, 100, 80),
+    "synth_k30_byte": (1, 30, 120),
+    "synth_k30_giou": (2, 30, 80),
+    "synth_k50_dt1": (3, 50, 80),
+    "synth_k40_ciou": (4, 40, 60),
+}
+OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_threshold=0.3,
+                   delta_t=3, asso_func="iou", inertia=0.1, use_byte=False, Q_xy_scaling=0.01,
+                   Q_s_scaling=0.0001)
+
+
+def case_frames(case):
+    from boxmot_b200.synth import make_stream
+    if case.startswith("MOT17"):
+        return mot17_frames(case)
+    sid, k, f = SYNTH_CASES[case]
+    return make_stream(sid, k, f)
+
+
+def assert_rows_match(got, want, frame, box_rtol=1e-6):
+    """ids / conf / cls / det_ind exact and in the reference's row order; boxes 1e-6 rel."""
+    got = np.asarray(got, dtype=float).reshape(-1, 8) if np.size(got) else np.empty((0, 8))
+    want = np.asarray(want, dtype=float).reshape(-1, 8) if np.size(want) else np.empty((0, 8))
+    assert got.shape == want.shape, "frame %d: %s vs %s rows" % (frame, got.shape, want.shape)
+    if got.size == 0:
+        return
+    assert np.array_equal(got[:, 4], want[:, 4]), "frame %d: track ids differ" % frame
+    assert np.array_equal(got[:, 7], want[:, 7]), "frame %d: det_ind differ" % frame
+    assert np.array_equal(got[:, 5:7], want[:, 5:7]), "frame %d: conf/cls differ" % frame
+    np.testing.assert_allclose(got[:, :4], want[:, :4], rtol=box_rtol, atol=1e-6,
+                               err_msg="frame %d boxes" % frame)

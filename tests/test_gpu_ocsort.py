@@ -1,0 +1,83 @@
+"""End-to-end GPU parity of the OC-SORT engine against the reference-generated golden
+fixtures and the oracle, through the reference-facing API and the batched engine."""
+import numpy as np
+import pytest
+
+from conftest import (OCSORT_YAML, SYNTH_CASES, assert_rows_match, case_frames, golden_rows,
+                      split_by_frame)
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+IMG = np.zeros((1080, 1920, 3), np.uint8)
+
+
+@pytest.mark.parametrize("case", list(SYNTH_CASES) + ["MOT17_02_FRCNN", "MOT17_04_FRCNN"])
+def test_ocsort_tracker_matches_reference_golden(case):
+    """create_tracker(...).update(dets, img) row-for-row against the reference's output."""
+    import boxmot_b200
+    want, kw = golden_rows("ocsort", case)
+    frames = case_frames(case)
+    trk = boxmot_b200.create_tracker("ocsort", boxmot_b200.get_tracker_config("ocsort"),
+                                     evolve_param_dict={**OCSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = trk.update(d, IMG)
+        assert_rows_match(got, want_f[f], f)
+
+
+def test_ocsort_engine_batched_streams_match_oracle():
+    """64 different streams stepped by one launch per frame; every stream must equal a
+    private oracle instance (ids are per stream)."""
+    from boxmot_b200.engine import OcSortEngine
+    from boxmot_b200.synth import make_batch
+    from oracle.ocsort import OcSortOracle
+    S, K, F, D = 64, 40, 50, 64
+    dets, nd = make_batch(S, K, F, D, first_stream=100)
+    eng = OcSortEngine(S, track_cap=128, det_cap=D, **OCSORT_YAML)
+    oracles = [OcSortOracle(**OCSORT_YAML) for _ in range(S)]
+    d_dets = torch.as_tensor(dets.astype(np.float32)).cuda()
+    d_nd = torch.as_tensor(nd).cuda()
+    for f in range(F):
+        out, nout = eng.step(d_dets[f], d_nd[f])
+        out, nout = out.cpu().numpy(), nout.cpu().numpy()
+        for s in range(S):
+            want = oracles[s].update(dets[f, s, : nd[f, s]])
+            assert_rows_match(out[s, : nout[s]], want, f)
+    st = eng.status()
+    assert st["track_updates"] == sum(o.n_updates for o in oracles)
+
+
+def test_ocsort_empty_frames_and_capacity_error():
+    from boxmot_b200.engine import OcSortEngine
+    from oracle.ocsort import OcSortOracle
+    eng = OcSortEngine(1, track_cap=32, det_cap=64, **OCSORT_YAML)
+    ora = OcSortOracle(**OCSORT_YAML)
+    rng = np.random.default_rng(0)
+    base = rng.random((10, 2)) * [1500, 800] + 100
+    for f in range(12):
+        if f in (3, 4, 9):
+            d = np.empty((0, 6))
+        else:
+            c = base + 2 * f
+            d = np.c_[c, c + [50, 110], rng.uniform(0.65, 0.95, 10), np.zeros(10)]
+        got = eng.step_host([d])[0]
+        assert_rows_match(got, ora.update(d), f)
+    eng.status()
+    # 40 far-apart detections into a 32-track engine must raise, not truncate
+    c = np.stack([np.arange(40) * 45.0 + 10, np.full(40, 100.0)], 1)
+    d = np.c_[c, c + [30, 60], np.full(40, 0.9), np.zeros(40)]
+    eng2 = OcSortEngine(1, track_cap=32, det_cap=64, **OCSORT_YAML)
+    eng2.step_host([d])
+    with pytest.raises(RuntimeError):
+        eng2.status()
+
+
+def test_input_validation_matches_reference_asserts():
+    import boxmot_b200
+    trk = boxmot_b200.create_tracker("ocsort", boxmot_b200.get_tracker_config("ocsort"))
+    with pytest.raises(AssertionError):
+        trk.update(np.zeros((3, 5)), IMG)
+    with pytest.raises(AssertionError):
+        trk.update([[0, 0, 1, 1, 0.9, 0]], IMG)
+    out = trk.update(np.empty((0, 6)), IMG)
+    assert out.size == 0

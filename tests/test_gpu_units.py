@@ -1,0 +1,146 @@
+"""Function-level GPU parity: unit kernels called through the C ABI vs the oracle."""
+import ctypes
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a, dtype=None):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).cuda()
+
+
+def _lap_batch(costs, limit=np.inf):
+    from boxmot_b200 import _lib
+    B = len(costs)
+    nr = np.array([c.shape[0] for c in costs], np.int32)
+    nc = np.array([c.shape[1] for c in costs], np.int32)
+    R, C = max(int(nr.max()), 1), max(int(nc.max()), 1)
+    buf = np.zeros((B, R, C))
+    for b, c in enumerate(costs):
+        buf[b, : c.shape[0], : c.shape[1]] = c
+    d_c, d_nr, d_nc = _dev(buf), _dev(nr), _dev(nc)
+    d_x = torch.full((B, R), -7, dtype=torch.int32, device="cuda")
+    d_y = torch.full((B, C), -7, dtype=torch.int32, device="cuda")
+    lim = float(limit) if limit < np.inf else float("inf")
+    _lib.check(_lib.lib().bm_lap_solve_batch(
+        ctypes.c_void_p(d_c.data_ptr()), B, R, C, ctypes.c_void_p(d_nr.data_ptr()),
+        ctypes.c_void_p(d_nc.data_ptr()), lim, ctypes.c_void_p(d_x.data_ptr()),
+        ctypes.c_void_p(d_y.data_ptr()), None), "bm_lap_solve_batch")
+    torch.cuda.synchronize()
+    return d_x.cpu().numpy(), d_y.cpu().numpy()
+
+
+def _random_costs(rng, n, kind):
+    out = []
+    for it in range(n):
+        nr, nc = rng.integers(1, 90, 2)
+        c = rng.random((nr, nc))
+        k = kind if kind >= 0 else it % 5
+        if k == 1:
+            c = np.round(c * 4) / 4                      # heavy exact ties
+        elif k == 2:
+            c = -np.where(rng.random((nr, nc)) < 0.9, 0.0, c)   # IoU-like: mostly exact zeros
+        elif k == 3:
+            c = -(np.where(rng.random((nr, nc)) < 0.85, 0.0, c) + 0.02 * np.round(rng.normal(size=(nr, nc))))
+        elif k == 4:
+            c = np.zeros((nr, nc))                       # fully degenerate
+        out.append(c)
+    return out
+
+
+@pytest.mark.parametrize("limit", [np.inf, 0.9, 0.3])
+def test_lap_batch_equals_lapjv_restatement_including_ties(limit):
+    from oracle import lap
+    rng = np.random.default_rng(5)
+    costs = _random_costs(rng, 400, -1)
+    x, y = _lap_batch(costs, limit)
+    for b, c in enumerate(costs):
+        _, xo, yo = lap.lapjv(c, extend_cost=True, cost_limit=limit)
+        assert np.array_equal(x[b, : c.shape[0]], xo), "problem %d rows" % b
+        assert np.array_equal(y[b, : c.shape[1]], yo), "problem %d cols" % b
+        assert (x[b, c.shape[0]:] == -1).all() and (y[b, c.shape[1]:] == -1).all()
+
+
+def test_lap_batch_large_tracking_shaped():
+    """C2/C5-shaped problems: D x T IoU-like costs, n_ext up to ~700."""
+    from oracle import lap
+    rng = np.random.default_rng(9)
+    costs = []
+    for nr, nc in [(41, 145), (100, 100), (200, 260), (300, 400), (1, 300), (300, 1)]:
+        c = -np.where(rng.random((nr, nc)) < 0.95, 0.0, rng.random((nr, nc)))
+        c += -0.05 * (rng.random((nr, nc)) - 0.5) * (rng.random((1, nc)) < 0.6)
+        costs.append(c)
+    x, y = _lap_batch(costs)
+    for b, c in enumerate(costs):
+        _, xo, yo = lap.lapjv(c, extend_cost=True)
+        assert np.array_equal(x[b, : c.shape[0]], xo)
+        assert np.array_equal(y[b, : c.shape[1]], yo)
+
+
+def test_lap_batch_empty_problem():
+    x, y = _lap_batch([np.zeros((0, 0)), np.ones((2, 2))])
+    assert (x[0] == -1).all() and (y[0] == -1).all()
+
+
+@pytest.mark.parametrize("name", ["iou", "giou", "diou", "ciou", "hmiou", "centroid"])
+def test_iou_family_bit_exact(name):
+    from boxmot_b200 import _lib
+    from oracle import assoc
+    rng = np.random.default_rng(3)
+
+    def boxes(n):
+        c = rng.random((n, 2)) * [1800, 900]
+        wh = rng.uniform(20, 300, (n, 2))
+        return np.c_[c, c + wh]
+
+    a, b = boxes(257), boxes(131)
+    a[:5] = b[:5]                               # identical boxes -> IoU exactly 1
+    d_a, d_b = _dev(a), _dev(b)
+    out = torch.zeros((len(a), len(b)), dtype=torch.float64, device="cuda")
+    _lib.check(_lib.lib().bm_iou_matrix(_lib.ASSO_FUNCS[name], ctypes.c_void_p(d_a.data_ptr()), len(a),
+                                        ctypes.c_void_p(d_b.data_ptr()), len(b), 1920.0, 1080.0,
+                                        ctypes.c_void_p(out.data_ptr()), None), "bm_iou_matrix")
+    torch.cuda.synchronize()
+    want = assoc.asso_func(name, 1920, 1080)(a, b)
+    got = out.cpu().numpy()
+    if name == "ciou":                           # arctan differs from libm by <= 1 ulp
+        np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-14)
+    else:
+        assert np.array_equal(got, want)
+
+
+def test_xysr_predict_update_vs_oracle():
+    from boxmot_b200 import _lib
+    from oracle import kalman
+    rng = np.random.default_rng(4)
+    n = 300
+    P0, Q, R = kalman.xysr_constants(0.01, 0.0001)
+    xs = np.zeros((n, 7))
+    Ps = np.zeros((n, 7, 7))
+    zs = np.zeros((n, 4))
+    for i in range(n):
+        A = rng.normal(size=(7, 7))
+        Ps[i] = A @ A.T + P0 * rng.uniform(0.1, 2)
+        xs[i] = np.r_[rng.uniform(100, 1500, 2), rng.uniform(2000, 40000), rng.uniform(0.3, 0.8),
+                      rng.normal(0, 3, 3)]
+        zs[i] = xs[i, :4] + rng.normal(0, 2, 4) * [1, 1, 50, 0.01]
+    d_x, d_P, d_z = _dev(xs), _dev(Ps.reshape(n, 49)), _dev(zs)
+    L = _lib.lib()
+    _lib.check(L.bm_xysr_predict(ctypes.c_void_p(d_x.data_ptr()), ctypes.c_void_p(d_P.data_ptr()), n,
+                                 0.01, 0.0001, None), "predict")
+    torch.cuda.synchronize()
+    px, pP = d_x.cpu().numpy(), d_P.cpu().numpy().reshape(n, 7, 7)
+    for i in range(n):
+        wx, wP = kalman.xysr_predict(xs[i], Ps[i], Q)
+        assert np.array_equal(px[i], wx) and np.array_equal(pP[i], wP)   # 0/1 matrices: bit exact
+    _lib.check(L.bm_xysr_update(ctypes.c_void_p(d_x.data_ptr()), ctypes.c_void_p(d_P.data_ptr()),
+                                ctypes.c_void_p(d_z.data_ptr()), n, None), "update")
+    torch.cuda.synchronize()
+    ux, uP = d_x.cpu().numpy(), d_P.cpu().numpy().reshape(n, 7, 7)
+    for i in range(n):
+        wx, wP = kalman.xysr_update(px[i], pP[i], zs[i], R)
+        np.testing.assert_allclose(ux[i], wx, rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(uP[i], wP, rtol=1e-9, atol=1e-9)

@@ -1,0 +1,86 @@
+"""CPU suite: the oracle against the reference-generated golden fixtures, the lapjv
+restatement against scipy, and the C-ABI library's exports (no compute without a GPU)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+from scipy.optimize import linear_sum_assignment
+
+from conftest import (OCSORT_YAML, ROOT, assert_rows_match, case_frames, golden_rows,
+                      split_by_frame)
+from oracle import lap
+from oracle.ocsort import OcSortOracle
+
+
+def test_lapjv_optimum_matches_scipy():
+    rng = np.random.default_rng(0)
+    for it in range(200):
+        nr, nc = rng.integers(1, 40, 2)
+        c = rng.random((nr, nc))
+        opt, x, y = lap.lapjv(c, extend_cost=True)
+        r, cc = linear_sum_assignment(c)
+        assert abs(opt - c[r, cc].sum()) < 1e-9
+        assert (x >= 0).sum() == min(nr, nc)
+        L = 0.5
+        _, x, y = lap.lapjv(c, extend_cost=True, cost_limit=L)
+        n = nr + nc
+        e = np.full((n, n), L / 2)
+        e[nr:, nc:] = 0
+        e[:nr, :nc] = c
+        r, cc = linear_sum_assignment(e)
+        mine = sum(c[i, x[i]] for i in range(nr) if x[i] >= 0) + L / 2 * ((x < 0).sum() + (y < 0).sum())
+        assert abs(e[r, cc].sum() - mine) < 1e-9
+        for i in range(nr):
+            if x[i] >= 0:
+                assert y[x[i]] == i and c[i, x[i]] <= L
+
+
+def test_lapjv_skip_rule_is_result_neutral():
+    """oracle_lapjv_skip models the CUDA solver's one shortcut; it must equal the plain
+    algorithm on tie-heavy inputs."""
+    lib = lap._lib()
+    lib.oracle_lapjv_skip.restype = ctypes.c_int
+    lib.oracle_lapjv_skip.argtypes = lib.oracle_lapjv.argtypes
+    rng = np.random.default_rng(1)
+    for it in range(600):
+        nr, nc = rng.integers(1, 70, 2)
+        c = rng.random((nr, nc))
+        if it % 3 == 1:
+            c = np.round(c * 4) / 4
+        if it % 3 == 2:
+            c = -np.where(rng.random((nr, nc)) < 0.9, 0.0, c)
+        lim = 1.7976931348623157e308 if it % 2 else 0.4
+        c = np.ascontiguousarray(c)
+        res = []
+        for fn in (lib.oracle_lapjv, lib.oracle_lapjv_skip):
+            x = np.empty(nr, np.int32)
+            y = np.empty(nc, np.int32)
+            fn(c.ctypes.data, nr, nc, 1, lim, x.ctypes.data, y.ctypes.data, None)
+            res.append((x, y))
+        assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])
+
+
+@pytest.mark.parametrize("case", ["synth_k100", "synth_k30_byte", "synth_k30_giou",
+                                  "synth_k50_dt1", "synth_k40_ciou", "MOT17_02_FRCNN"])
+def test_ocsort_oracle_matches_reference_golden(case):
+    want, kw = golden_rows("ocsort", case)
+    frames = case_frames(case)
+    ora = OcSortOracle(**{**OCSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = ora.update(d)
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
+
+
+def test_library_exports_every_declared_symbol():
+    from boxmot_b200 import _lib, build
+    path = build.build()
+    L = ctypes.CDLL(path)
+    header = open(os.path.join(ROOT, "include", "boxmot_b200.h")).read()
+    import re
+    declared = set(re.findall(r"\b(bm_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations found"
+    for name in declared:
+        assert hasattr(L, name), "missing export " + name
+    assert set(_lib.EXPORTS) == declared
