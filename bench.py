@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""Headline benchmark: OC-SORT association hot path on 1024 concurrent synthetic streams
+(BASELINE.json configs[1]: 100 objects/frame, 300 frames, IoU + OCM velocity cost, lapjv).
+
+    python bench.py --gpus N --steps K --warmup W            # B200 engine (default arm)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port of
+                                                             # the reference path on host cores
+
+A "step" is ONE frame advanced for every stream of the batch (one launch of the fused
+frame-step kernel).  `value` = track-updates/s (live tracks entering predict, summed over
+streams and frames) with inputs resident in HBM; `e2e` = the same metric
+through the host-buffer API with H2D/D2H inside the timed region.  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_threshold=0.3,
+                   delta_t=3, asso_func="iou", inertia=0.1, use_byte=False, Q_xy_scaling=0.01,
+                   Q_s_scaling=0.0001)     # boxmot/configs/trackers/ocsort.yaml defaults
+METRIC = "track-updates/sec"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=290)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
+    ap.add_argument("--objects", type=int, default=100)
+    ap.add_argument("--det-cap", type=int, default=128)
+    ap.add_argument("--track-cap", type=int, default=256)
+    ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between steps")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-streams", type=int, default=4, help="cpu_baseline sample size")
+    ap.add_argument("--ref-streams-per-core", type=int, default=1)
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- inputs
+def _gen_one(a):
+    from boxmot_b200.synth import make_stream
+    sid, k, f, dcap = a
+    fr = make_stream(sid, k, f)
+    d = np.zeros((f, dcap, 6), np.float32)
+    n = np.zeros((f,), np.int32)
+    for i, x in enumerate(fr):
+        if len(x) > dcap:
+            raise ValueError("frame with %d detections > det_cap %d" % (len(x), dcap))
+        d[i, : len(x)] = x
+        n[i] = len(x)
+    return d, n
+
+
+def gen_inputs(first_stream, n_streams, k, n_frames, dcap, workers):
+    """dets [F,S,dcap,6] float32, ndets [F,S] int32; generated before CUDA is touched."""
+    import multiprocessing as mp
+    dets = np.zeros((n_frames, n_streams, dcap, 6), np.float32)
+    nd = np.zeros((n_frames, n_streams), np.int32)
+    jobs = [(first_stream + s, k, n_frames, dcap) for s in range(n_streams)]
+    if workers > 1:
+        with mp.get_context("fork").Pool(workers) as pool:
+            for s, (d, n) in enumerate(pool.imap(_gen_one, jobs, chunksize=8)):
+                dets[:, s], nd[:, s] = d, n
+    else:
+        for s, j in enumerate(jobs):
+            dets[:, s], nd[:, s] = _gen_one(j)
+    return dets, nd
+
+
+# --------------------------------------------------------------------------- CPU arms
+def _cpu_worker(a):
+    """Runs whole streams through the oracle port; returns (timed seconds, timed updates)."""
+    os.environ["OMP_NUM_THREADS"] = "1"
+    from boxmot_b200.synth import make_stream
+    from oracle.ocsort import OcSortOracle
+    sids, k, warm, steps = a
+    tot_t, tot_u = 0.0, 0
+    for sid in sids:
+        fr = make_stream(sid, k, warm + steps)
+        o = OcSortOracle(**OCSORT_YAML)
+        for f in range(warm):
+            o.update(fr[f])
+        u0 = o.n_updates
+        t0 = time.perf_counter()
+        for f in range(warm, warm + steps):
+            o.update(fr[f])
+        tot_t += time.perf_counter() - t0
+        tot_u += o.n_updates - u0
+    return tot_t, tot_u
+
+
+def cpu_single_core(k, warm, steps, n_streams):
+    t, u = _cpu_worker((list(range(n_streams)), k, warm, steps))
+    return u / t, "%d streams x %d frames (after %d warm-up), K=%d, 1 core" % (n_streams, steps, warm, k)
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU path (the oracle port: the reference is pure
+    Python and /root/reference does not travel to the GPU box) on all host cores, one
+    stream per worker process at a time, mirroring boxmot/engine/val.py:389-392."""
+    import multiprocessing as mp
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import lap as olap
+    olap.build()
+    cores = os.cpu_count() or 1
+    workers = max(1, cores - 1) if cores > 2 else cores
+    per = max(1, args.ref_streams_per_core)
+    steps = min(args.steps, 300)
+    jobs = [([w * per + i for i in range(per)], args.objects, args.warmup, steps) for w in range(workers)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(workers) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    tmax = max(r[0] for r in res)
+    upd = sum(r[1] for r in res)
+    value = upd / tmax
+    sample = "%d streams (%d per worker x %d workers) x %d frames after %d warm-up, K=%d" % (
+        workers * per, per, workers, steps, args.warmup, args.objects)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "track-updates/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * tmax / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "OC-SORT ocsort.yaml, synthetic streams x %d dets/frame (SURVEY 8(d) C2), "
+                               "CPU sample of the 1024-stream job" % args.objects,
+                   "streams": workers * per, "objects": args.objects},
+        "cpu_baseline": {"value": value, "unit": "track-updates/s", "cores": workers, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "track-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": wall, "host_cores": cores,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons every 100 ms during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz, self.ok = None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as ex:  # no NVML: report it, never invent numbers
+            self.err = repr(ex)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [],
+                    "note": "NVML unavailable or region shorter than one sample"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------- GPU arm
+def alg_bytes(track_updates, matches, births, dets_in, rows_out):
+    """Algorithmic bytes moved by the fused frame-step kernel (SURVEY.md 8(d) per-unit
+    figures, XYSR state = 7+49 fp64 = 448 B): predict 2*448*T, update (2*448+32)*M,
+    detections in 24*D (float32 x 6; the IoU operands), LAP result 4*(T+D), lifecycle
+    scalars 64*T, output rows 64*M_out, birth state write 448*B.  Cost matrix and LAP
+    input count 0 bytes: they are fused on chip."""
+    return (2 * 448 * track_updates + (2 * 448 + 32) * matches + 24 * dets_in
+            + 4 * (track_updates + dets_in) + 64 * track_updates + 64 * rows_out + 448 * births)
+
+
+def run_gpu_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    S, K, W = args.streams, args.steps, args.warmup
+    F = W + K
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    dets, nd = gen_inputs(rank * S, S, args.objects, F, args.det_cap, max(1, min(32, cores // world)))
+    gen_s = time.perf_counter() - t0
+
+    import torch
+    import torch.distributed as dist
+    from boxmot_b200.engine import OcSortEngine
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
+    h_dets = torch.from_numpy(dets).pin_memory()
+    h_nd = torch.from_numpy(nd).pin_memory()
+    d_dets = h_dets.to(dev, non_blocking=True)
+    d_nd = h_nd.to(dev, non_blocking=True)
+    flush_buf = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(step_fn):
+        """W untimed steps, then exactly K steps, each bracketed by its own CUDA-event pair
+        on the launching stream so the (optional) L2 flush between steps is not billed."""
+        eng.reset()
+        for f in range(W):
+            step_fn(f)
+        c0 = eng.counters()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        w0 = time.perf_counter()
+        for i in range(K):
+            if not args.no_flush:
+                flush_buf.zero_()
+            ev[i][0].record()
+            step_fn(W + i)
+            ev[i][1].record()
+        barrier()
+        wall = time.perf_counter() - w0
+        sampler.stop_flag = True
+        sampler.join()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        c1 = eng.counters()
+        eng.status()   # raises on any capacity / solver error bit
+        return ms, wall, {k: c1[k] - c0[k] for k in c1}, sampler.summary()
+
+    # (1) inputs resident in HBM
+    def step_dev(f):
+        eng.step(d_dets[f], d_nd[f])
+
+    ms_dev, wall_dev, cnt, clocks = timed(step_dev)
+
+    # (2) end to end through the host-buffer API: H2D of the frame's detections from pinned
+    # memory, the step, D2H of the result rows, host sync
+    h_out = torch.empty((S, args.track_cap, 8), dtype=torch.float64).pin_memory()
+    h_nout = torch.empty((S,), dtype=torch.int32).pin_memory()
+    s_dets = torch.empty((S, args.det_cap, 6), dtype=torch.float32, device=dev)
+    s_nd = torch.empty((S,), dtype=torch.int32, device=dev)
+    e2e = None
+    if not args.no_e2e:
+        def step_e2e(f):
+            s_dets.copy_(h_dets[f], non_blocking=True)
+            s_nd.copy_(h_nd[f], non_blocking=True)
+            out, nout = eng.step(s_dets, s_nd)
+            h_out.copy_(out, non_blocking=True)
+            h_nout.copy_(nout, non_blocking=True)
+            torch.cuda.current_stream(dev).synchronize()
+
+        ms_e2e, wall_e2e, cnt_e, _ = timed(step_e2e)
+        e2e = (ms_e2e, cnt_e["track_updates"])
+
+    # aggregate over ranks: max time, summed units
+    def agg(ms, units):
+        if world == 1:
+            return ms, units
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        u = torch.tensor([units], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(u, op=dist.ReduceOp.SUM)
+        return float(t.item()), float(u.item())
+
+    ms_all, upd_all = agg(ms_dev, cnt["track_updates"])
+    line = None
+    if e2e is not None:
+        ms_e_all, upd_e_all = agg(*e2e)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import lap as olap
+        olap.build()
+        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), args.cpu_streams)
+        cpu = {"value": v, "unit": "track-updates/s", "cores": 1, "kind": "port", "sample": sample}
+    if rank == 0:
+        peaks = {}
+        pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(pk):
+            peaks = json.load(open(pk))
+        peak = peaks.get("hbm_gbs", 6650.0)
+        dets_in = int(nd[W:W + K].sum())
+        # output rows <= matched tracks (rows are emitted only for tracks updated this frame)
+        nbytes = alg_bytes(cnt["track_updates"], cnt["matches"], cnt["births"], dets_in, cnt["matches"])
+        achieved = nbytes / (ms_dev * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": upd_all / (ms_all * 1e-3), "unit": "track-updates/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_all / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                   "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])" % (S, args.objects, F),
+                       "streams_per_gpu": S, "objects": args.objects, "frames": F, "det_cap": args.det_cap,
+                       "track_cap": args.track_cap, "partition": "streams sharded by rank, no data-path collective",
+                       "l2": "no flush" if args.no_flush else "L2 flushed (252 MB memset) between timed steps, outside the event pairs"},
+            "stream_frames_per_s": world * S * K / (ms_all * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
+                         "kernel": "ocsort_step_kernel", "alg_bytes_per_launch": nbytes / K,
+                         "avg_launch_ms": ms_dev / K},
+            "gpu_launches": K * (2 if not args.no_e2e else 1),
+            "clocks": clocks,
+            "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
+        }
+        if e2e is not None:
+            line["e2e"] = {"value": upd_e_all / (ms_e_all * 1e-3), "unit": "track-updates/s",
+                           "h2d_bytes_per_step": int(s_dets.numel() * 4 + s_nd.numel() * 4),
+                           "d2h_bytes_per_step": int(h_out.numel() * 8 + h_nout.numel() * 4),
+                           "ms_per_step": ms_e_all / K}
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -144,6 +144,27 @@ int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_upda
     return 0;
 }
 
+int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !out4) return fail(-1, "bm_ocsort_counters: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int S = e->st.S;
+    std::vector<int> hdr((size_t)S * bm::OH_COUNT);
+    std::vector<unsigned long long> nu(S);
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), e->st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(nu.data(), e->st.n_updates, nu.size() * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    out4[0] = out4[1] = out4[2] = out4[3] = 0;
+    for (int i = 0; i < S; i++) {
+        out4[0] += nu[i];
+        out4[1] += (unsigned long long)hdr[(size_t)i * bm::OH_COUNT + bm::OH_LAPS];
+        out4[2] += (unsigned long long)hdr[(size_t)i * bm::OH_COUNT + bm::OH_MATCH];
+        out4[3] += (unsigned long long)hdr[(size_t)i * bm::OH_COUNT + bm::OH_BIRTHS];
+    }
+    return 0;
+}
+
 int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P, int* h_ids, void* stream) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e || si < 0 || si >= e->st.S) return fail(-1, "bm_ocsort_peek: bad argument");

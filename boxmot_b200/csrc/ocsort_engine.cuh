@@ -17,7 +17,7 @@ namespace bm {
 
 enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
 enum { OF_OBSERVED = 1, OF_SAVED = 2 };
-enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_COUNT = 8 };
+enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_COUNT = 8 };
 
 struct OcsParams {
     double det_thresh, min_conf, iou_thr, inertia, q_xy, q_s, diag;

@@ -22,7 +22,7 @@ struct OcsSmem {
     double* cost;
 };
 
-enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_OCR_RAN, M_NREJ, M_LAPBAD, M_COUNT = 16 };
+enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_OCR_RAN, M_NREJ, M_LAPBAD, M_NMATCH, M_COUNT = 16 };
 
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
     size_t d = (size_t)Dcap, t = (size_t)Tcap;
@@ -485,6 +485,7 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
         const int tsu = v.I(OI_TSU, slot);
         const bool emit = tsu < 1 && (v.I(OI_STREAK, slot) >= pr.min_hits || frame <= pr.min_hits);
         sm.kvalid[p] = (emit ? 1 : 0) | (tsu > pr.max_age ? 2 : 0);
+        if (p < nT && tsu == 0) atomicAdd(&sm.misc[M_NMATCH], 1);   // matched this frame (bench counter)
     }
     __syncthreads();
     if (tid == 0) {
@@ -528,6 +529,8 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
         v.hdr[OH_NLIST] = keep;
         v.hdr[OH_NEXT_ID] = id0 + born;
         v.hdr[OH_FRAME] = frame;
+        v.hdr[OH_MATCH] += sm.misc[M_NMATCH];
+        v.hdr[OH_BIRTHS] += born;
         if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
     }
 }

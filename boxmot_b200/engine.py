@@ -91,6 +91,14 @@ class OcSortEngine:
             raise RuntimeError("OC-SORT engine error: " + "; ".join(msgs))
         return {"err": err.value, "track_updates": upd.value, "lap_solves": laps.value}
 
+    def counters(self):
+        """Cumulative {track_updates, lap_solves, matches, births} over all streams."""
+        buf = (ctypes.c_ulonglong * 4)()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_ocsort_counters(self._h, ctypes.byref(buf),
+                                                     _stream_ptr(self.device)), "bm_ocsort_counters")
+        return dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
+
     def peek(self, stream_index):
         n = ctypes.c_int(0)
         x = np.zeros((self.Tcap, 7))

@@ -50,6 +50,10 @@ int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double
  * the number of lapjv solves in *lap_solves. */
 int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_updates,
                      unsigned long long* lap_solves, void* stream);
+/* Cumulative work counters since create/reset, summed over streams (synchronises
+ * `stream`): out4 = {track_updates, lap_solves, matches (Kalman updates with a
+ * detection), births}.  Used by bench.py for the algorithmic-bytes figure. */
+int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream);
 /* Debug / test access: copy one stream's list length and per-track Kalman state
  * (list order) to host buffers x[track_cap*7], P[track_cap*49], ids[track_cap]. */
 int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
