@@ -36,6 +36,8 @@ _SIGS = {
                                c_void_p, c_void_p]),
     "bm_lap_solve_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
                                    c_void_p, c_void_p, c_void_p]),
+    "bm_lap_rect_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
+                                  c_void_p, c_void_p, c_void_p]),
     "bm_iou_matrix": (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_double, c_double,
                               c_void_p, c_void_p]),
     "bm_xysr_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),

@@ -1,0 +1,185 @@
+// Warp-cooperative exact solver for the rectangular assignment problem with a "null"
+// option -- the engine's fast path for every assignment the reference sends to
+// lap.lapjv(cost, extend_cost=True[, cost_limit]) (boxmot/utils/association.py:50-51,109,
+// boxmot/utils/matching.py:54-55, boxmot/trackers/boosttrack/assoc.py:113).
+//
+// lapjv's (nr+nc)^2 extension (real block = cost, off-diagonal blocks = pad, dummy block
+// = 0) is equivalent to: every real row either takes a real column at c[i][j] or stays
+// unmatched, and each matched pair saves 2*pad.  So the optimum of the extended problem
+// restricted to the real block is the optimum of
+//        min  sum_{matched (i,j)} (c[i][j] - null_cost),      null_cost = 2*pad
+// (= cost_limit when a limit is given, 2*(max(c)+1) otherwise).  That problem is solved
+// here directly by successive shortest augmenting paths over the REAL rows only
+// (Crouse-style row/column duals, all columns start free with v = 0), with the null
+// option as an always-free sink of reduced cost null_cost - u[i].  No dummy rows are
+// ever augmented, which is what makes it ~100x shorter than emulating lapjv on the
+// extension (csrc/lapjv.cuh keeps that step-for-step emulation for the cases where
+// lapjv's internal tie-breaking is observable, see ocsort_step.cu).
+//
+// Exactness: the result is an optimal assignment in fp64.  When the optimum is unique
+// it equals lapjv's x/y (tests/test_gpu_units.py); when it is not, any optimal solution
+// may be returned.
+#pragma once
+#include "common.cuh"
+#include <math_constants.h>
+
+namespace bm {
+
+struct RectWork {     // shared memory, carved by rect_carve
+    double *u, *v, *spc, *scd;   // [nr] [nc] [nc] [nc]
+    int *x, *y, *path, *sc, *fr; // [nr] [nc] [nc] [nc] [nr]
+};
+
+__host__ __device__ inline size_t rect_work_bytes(int nr, int nc) {
+    return (size_t)nr * 8 + (size_t)nc * 24 + ((size_t)nr * 2 + (size_t)nc * 3) * 4 + 8;
+}
+
+__device__ inline RectWork rect_carve(void* smem, int nr, int nc) {
+    RectWork w;
+    w.u = reinterpret_cast<double*>(smem);
+    w.v = w.u + nr;
+    w.spc = w.v + nc;
+    w.scd = w.spc + nc;
+    w.x = reinterpret_cast<int*>(w.scd + nc);
+    w.y = w.x + nr;
+    w.path = w.y + nc;
+    w.sc = w.path + nc;
+    w.fr = w.sc + nc;
+    return w;
+}
+
+// (value, index) arg-min over the warp; ties go to the lower index.
+__device__ __forceinline__ void warp_argmin(double& s, int& j) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double so = shfl_xor_d(s, o);
+        const int jo = __shfl_xor_sync(BM_FULL, j, o);
+        if (so < s || (so == s && jo < j)) { s = so; j = jo; }
+    }
+}
+
+// Solve with one warp.  c: nr x nc row-major (leading dimension ld), any address space.
+// rowmin/rowarg: optional per-row minimum and its column (computed by the caller while
+// the costs were generated); pass nullptr to have the warp compute them.
+// On return w.x[i] = column of row i or -1, w.y[j] = row of column j or -1.
+// Returns 0, or 1 when a guard tripped (NaN costs).
+static __device__ int rect_solve_warp(const double* c, int ld, int nr, int nc, double null_cost,
+                                      RectWork& w, const double* rowmin, const int* rowarg) {
+    const int lane = lane_id();
+    for (int j = lane; j < nc; j += 32) { w.v[j] = 0.0; w.y[j] = 0x7fffffff; }
+    __syncwarp();
+    // ---- row reduction: u[i] = min_j c[i][j] (capped by the null option), greedy claim
+    if (rowmin) {
+        for (int i = lane; i < nr; i += 32) {
+            double m = rowmin[i];
+            int a = rowarg[i];
+            if (!(m <= null_cost)) { m = null_cost; a = -1; }
+            w.u[i] = m;
+            w.x[i] = a;
+        }
+    } else {
+        for (int i = 0; i < nr; i++) {
+            double m = CUDART_INF;
+            int a = 0x7fffffff;
+            for (int j = lane; j < nc; j += 32) {
+                const double cc = c[(size_t)i * ld + j];
+                if (cc < m) { m = cc; a = j; }
+            }
+            warp_argmin(m, a);
+            if (!(m <= null_cost)) { m = null_cost; a = -1; }
+            if (lane == 0) { w.u[i] = m; w.x[i] = a; }
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < nr; i += 32) { const int a = w.x[i]; if (a >= 0) atomicMin(&w.y[a], i); }
+    __syncwarp();
+    int n_free = 0;
+    for (int base = 0; base < nr; base += 32) {
+        const int i = base + lane;
+        bool fr = false;
+        if (i < nr) {
+            const int a = w.x[i];
+            if (a < 0 || w.y[a] != i) { fr = true; w.x[i] = -1; }
+        }
+        const unsigned b = __ballot_sync(BM_FULL, fr);
+        if (fr) w.fr[n_free + __popc(b & ((1u << lane) - 1))] = i;
+        n_free += __popc(b);
+    }
+    for (int j = lane; j < nc; j += 32) if (w.y[j] == 0x7fffffff) w.y[j] = -1;
+    __syncwarp();
+
+    // ---- one shortest augmenting path per free row
+    int bad = 0;
+    for (int f = 0; f < n_free && !bad; f++) {
+        const int r0 = w.fr[f];
+        for (int j = lane; j < nc; j += 32) w.spc[j] = CUDART_INF;
+        __syncwarp();
+        double minval = 0.0, best_null = CUDART_INF;
+        int i = r0, null_row = -1, nsc = 0, sink = -2;
+        int guard = nc + 2;
+        while (sink == -2) {
+            if (--guard < 0) { bad = 1; break; }
+            const double ui = w.u[i];
+            const double cn = minval + (null_cost - ui);
+            if (cn < best_null) { best_null = cn; null_row = i; }
+            double lowest = CUDART_INF;
+            int jl = 0x7fffffff;
+            const double* ci = c + (size_t)i * ld;
+            for (int j = lane; j < nc; j += 32) {
+                double s = w.spc[j];
+                if (s == -CUDART_INF) continue;          // already scanned
+                const double r = minval + ((ci[j] - ui) - w.v[j]);
+                if (r < s) { s = r; w.spc[j] = r; w.path[j] = i; }
+                if (s < lowest) { lowest = s; jl = j; }
+            }
+            warp_argmin(lowest, jl);
+            if (!(lowest < best_null)) { sink = -1; break; }      // null option ends the path
+            minval = lowest;
+            const int yj = w.y[jl];
+            __syncwarp();
+            if (lane == 0) { w.sc[nsc] = jl; w.scd[nsc] = lowest; w.spc[jl] = -CUDART_INF; }
+            nsc++;
+            __syncwarp();
+            if (yj < 0) sink = jl; else i = yj;
+        }
+        if (bad) break;
+        const double fin = sink == -1 ? best_null : minval;
+        // dual updates (rows first: they read y[] before the path is flipped)
+        for (int k = lane; k < nsc; k += 32) {
+            const int j = w.sc[k];
+            const double dk = fin - w.scd[k];
+            const int yi = w.y[j];
+            if (yi >= 0) w.u[yi] += dk;
+            w.v[j] -= dk;
+        }
+        if (lane == 0) w.u[r0] += fin;
+        __syncwarp();
+        if (lane == 0) {
+            int hops = 0;
+            if (sink == -1) {
+                int ii = null_row, j = w.x[ii];
+                w.x[ii] = -1;
+                while (ii != r0 && hops++ <= nr) {
+                    ii = w.path[j];
+                    w.y[j] = ii;
+                    const int t = w.x[ii];
+                    w.x[ii] = j;
+                    j = t;
+                }
+            } else {
+                int j = sink, ii;
+                do {
+                    ii = w.path[j];
+                    w.y[j] = ii;
+                    const int t = w.x[ii];
+                    w.x[ii] = j;
+                    j = t;
+                } while (ii != r0 && hops++ <= nr);
+            }
+        }
+        __syncwarp();
+    }
+    return bad;
+}
+
+}  // namespace bm

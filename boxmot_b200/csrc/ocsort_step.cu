@@ -10,14 +10,15 @@
 //   E  optional BYTE round (ocsort.py:330-356) and OCR round (ocsort.py:358-386)
 //   F  misses, births, output rows and dead-track removal (ocsort.py:388-439)
 #include "ocsort_engine.cuh"
+#include "lap_rect.cuh"
 
 namespace bm {
 
 constexpr int OCS_NT = 128;
 
 struct OcsSmem {
-    double *dbox, *dconf, *dcls, *sbox, *sconf, *scls, *tbox, *kcx, *kcy, *vy, *vx, *wred;
-    int *dind, *sind, *slot_of, *kvalid, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc;
+    double *dbox, *dconf, *dcls, *sbox, *sconf, *scls, *tbox, *kcx, *kcy, *vy, *vx, *wred, *rmin;
+    int *dind, *sind, *slot_of, *kvalid, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg;
     void* lapw;
     double* cost;
 };
@@ -26,8 +27,8 @@ enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_OCR_RAN, M_NREJ, 
 
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
     size_t d = (size_t)Dcap, t = (size_t)Tcap;
-    size_t dbl = 6 * d + (use_byte ? 6 * d : 0) + 8 * t + 8;
-    size_t ints = d + (use_byte ? d : 0) + 2 * t + d + t + d + t + d + t + d + M_COUNT;
+    size_t dbl = 7 * d + (use_byte ? 6 * d : 0) + 8 * t + 8;
+    size_t ints = 2 * d + (use_byte ? d : 0) + 2 * t + d + t + d + t + d + t + d + M_COUNT;
     size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
     b += (lap_work_bytes((int)(d + t)) + 7) / 8 * 8;
     b += (size_t)cost_elems * 8;
@@ -48,6 +49,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.vy = p; p += Tcap;
     m.vx = p; p += Tcap;
     m.wred = p; p += 8;
+    m.rmin = p; p += Dcap;
     int* q = reinterpret_cast<int*>(p);
     int* q0 = q;
     m.dind = q; q += Dcap;
@@ -62,6 +64,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.colcnt = q; q += Tcap;
     m.hit_t = q; q += Dcap;
     m.misc = q; q += M_COUNT;
+    m.rarg = q; q += Dcap;
     size_t ib = ((size_t)(q - q0) * 4 + 7) / 8 * 8;
     unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
     m.lapw = r;
@@ -132,13 +135,13 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
         return false;
     }
     if (wid == 0) {
-        LapMat m = {cost, nB, nA, nB, nA + nB, 1, cmx + 1.0};
-        LapWork w = lap_carve(sm.lapw, nA + nB);
-        const int bad = lap_solve_warp(m, w);
+        // Only pairs with iou >= thr survive, and the caller re-sorts what is left: any
+        // optimal solution gives the same result, so the fast exact solver is used.
+        RectWork w = rect_carve(sm.lapw, nA, nB);
+        const int bad = rect_solve_warp(cost, nB, nA, nB, 2.0 * (cmx + 1.0), w, nullptr, nullptr);
         if (bad && lane == 0) sm.misc[M_LAPBAD] = 1;
         for (int r = lane; r < nA; r += 32) {
             int c = w.x[r];
-            if (c >= nB) c = -1;
             // `if iou_left[m0, m1] < thr: continue`
             if (c >= 0 && -cost[(size_t)r * nB + c] < pr.iou_thr) c = -1;
             pair_b[r] = c;
@@ -282,28 +285,34 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
     }
     if (nD > 0 && nT > 0 && assoc_ok) {
         double cmx = -CUDART_INF;
-        for (size_t e = tid; e < need; e += OCS_NT) {
-            const int d = (int)(e / nT), t = (int)(e % nT);
-            Box a = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d], sm.dbox[3 * Dcap + d]};
-            Box b = {sm.tbox[0 * Tcap + t], sm.tbox[1 * Tcap + t], sm.tbox[2 * Tcap + t], sm.tbox[3 * Tcap + t]};
-            const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
-            // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
+        for (int d = wid; d < nD; d += OCS_NT / 32) {      // one warp per detection row
+            const Box a = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d], sm.dbox[3 * Dcap + d]};
             const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
-            double dx = cxd - sm.kcx[t], dy = cyd - sm.kcy[t];
-            const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
-            dx = dx / norm; dy = dy / norm;
-            double cs = sm.vx[t] * dx + sm.vy[t] * dy;
-            cs = fmin(1.0, fmax(-1.0, cs));
-            const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
-            const double motion = ((sm.kvalid[t] ? 1.0 : 0.0) * ang) * pr.inertia;
-            const double cc = -(iou + motion);
-            cost[e] = cc;
-            cmx = fmax(cmx, cc);
-            if (iou > pr.iou_thr) {
-                atomicAdd(&sm.rowcnt[d], 1);
-                atomicAdd(&sm.colcnt[t], 1);
-                sm.hit_t[d] = t;
+            double rm = CUDART_INF;
+            int ra = 0x7fffffff, nhit = 0, lasthit = -1;
+            for (int t = lane; t < nT; t += 32) {
+                const Box b = {sm.tbox[0 * Tcap + t], sm.tbox[1 * Tcap + t], sm.tbox[2 * Tcap + t], sm.tbox[3 * Tcap + t]};
+                const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
+                // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
+                double dx = cxd - sm.kcx[t], dy = cyd - sm.kcy[t];
+                const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
+                dx = dx / norm; dy = dy / norm;
+                double cs = sm.vx[t] * dx + sm.vy[t] * dy;
+                cs = fmin(1.0, fmax(-1.0, cs));
+                const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
+                const double motion = ((sm.kvalid[t] ? 1.0 : 0.0) * ang) * pr.inertia;
+                const double cc = -(iou + motion);
+                cost[(size_t)d * nT + t] = cc;
+                cmx = fmax(cmx, cc);
+                if (cc < rm) { rm = cc; ra = t; }
+                if (iou > pr.iou_thr) { nhit++; lasthit = t; atomicAdd(&sm.colcnt[t], 1); }
             }
+            warp_argmin(rm, ra);
+            for (int o = 16; o > 0; o >>= 1) {
+                nhit += __shfl_xor_sync(BM_FULL, nhit, o);
+                lasthit = max(lasthit, __shfl_xor_sync(BM_FULL, lasthit, o));
+            }
+            if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
         }
         for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
         if (lane == 0) sm.wred[wid] = cmx;
@@ -328,12 +337,26 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
             } else {
                 double pad = sm.wred[0];
                 for (int i = 1; i < OCS_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
-                LapMat m = {cost, nT, nD, nT, nD + nT, 1, pad + 1.0};
-                LapWork w = lap_carve(sm.lapw, nD + nT);
-                const int bad = lap_solve_warp(m, w);
+                // With nD <= nT every detection is assigned in every optimal solution, so the
+                // reference's unmatched-detection ORDER (never-assigned first, then rejected,
+                // ocsort ids follow it) does not depend on lapjv's tie-breaking and the fast
+                // exact solver applies.  With nD > nT WHICH zero-gain detections stay
+                // unassigned is decided by lapjv's scan order: emulate it step for step.
+                int bad;
+                int* xsol;
+                if (nD <= nT) {
+                    RectWork w = rect_carve(sm.lapw, nD, nT);
+                    bad = rect_solve_warp(cost, nT, nD, nT, 2.0 * (pad + 1.0), w, sm.rmin, sm.rarg);
+                    xsol = w.x;
+                } else {
+                    LapMat m = {cost, nT, nD, nT, nD + nT, 1, pad + 1.0};
+                    LapWork w = lap_carve(sm.lapw, nD + nT);
+                    bad = lap_solve_warp(m, w);
+                    xsol = w.x;
+                }
                 if (bad && lane == 0) sm.misc[M_LAPBAD] = 1;
                 for (int d = lane; d < nD; d += 32) {
-                    int t = w.x[d];
+                    int t = xsol[d];
                     if (t >= nT) t = -1;
                     int stt = 0;                              // 0 never assigned
                     if (t >= 0) {

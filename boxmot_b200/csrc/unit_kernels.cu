@@ -4,6 +4,7 @@
 #include "iou.cuh"
 #include "kf_xysr.cuh"
 #include "lapjv.cuh"
+#include "lap_rect.cuh"
 #include <cstdio>
 #include <limits>
 
@@ -13,6 +14,7 @@ namespace bm {
 // from global memory (L2-resident at these sizes).
 constexpr int LAP_WPB = 4;
 
+template <int RECT>
 __global__ void __launch_bounds__(LAP_WPB * 32)
 lap_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, int nc_max,
                  const int* __restrict__ nr_, const int* __restrict__ nc_, double cost_limit,
@@ -39,6 +41,13 @@ lap_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, in
         pad = mx + 1.0;
     }
     const size_t wbytes = (lap_work_bytes(nr_max + nc_max) + 15) / 16 * 16;
+    if (RECT) {   // fast exact solver on the real rows (csrc/lap_rect.cuh)
+        RectWork rw = rect_carve(smem_raw + (size_t)wid * wbytes, nr, nc);
+        rect_solve_warp(c, nc_max, nr, nc, 2.0 * pad, rw, nullptr, nullptr);
+        for (int i = lane; i < nr_max; i += 32) x[i] = i < nr ? rw.x[i] : -1;
+        for (int j = lane; j < nc_max; j += 32) y[j] = j < nc ? rw.y[j] : -1;
+        return;
+    }
     LapWork w = lap_carve(smem_raw + (size_t)wid * wbytes, nr + nc);
     LapMat m = {c, nc_max, nr, nc, nr + nc, 1, pad};
     lap_solve_warp(m, w);
@@ -91,19 +100,31 @@ static int unit_fail(const char* what, cudaError_t e) {
 
 extern "C" {
 
-int bm_lap_solve_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
-                       const int* d_nc, double cost_limit, int* d_x, int* d_y, void* stream) {
+static int lap_batch_launch(int rect, const double* d_cost, int n_problems, int nr_max, int nc_max,
+                            const int* d_nr, const int* d_nc, double cost_limit, int* d_x, int* d_y,
+                            void* stream) {
     if (n_problems <= 0) return 0;
     const int limited = cost_limit < std::numeric_limits<double>::max();
     const size_t wbytes = (bm::lap_work_bytes(nr_max + nc_max) + 15) / 16 * 16;
     const size_t smem = wbytes * bm::LAP_WPB;
-    cudaError_t e = cudaFuncSetAttribute(bm::lap_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    auto kern = rect ? bm::lap_batch_kernel<1> : bm::lap_batch_kernel<0>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return unit_fail("lap smem", e);
     const int grid = (n_problems + bm::LAP_WPB - 1) / bm::LAP_WPB;
-    bm::lap_batch_kernel<<<grid, bm::LAP_WPB * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+    kern<<<grid, bm::LAP_WPB * 32, smem, static_cast<cudaStream_t>(stream)>>>(
         d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, cost_limit, limited, d_x, d_y);
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("lap_batch_kernel", e);
+}
+
+int bm_lap_solve_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                       const int* d_nc, double cost_limit, int* d_x, int* d_y, void* stream) {
+    return lap_batch_launch(0, d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, cost_limit, d_x, d_y, stream);
+}
+
+int bm_lap_rect_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                      const int* d_nc, double cost_limit, int* d_x, int* d_y, void* stream) {
+    return lap_batch_launch(1, d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, cost_limit, d_x, d_y, stream);
 }
 
 int bm_iou_matrix(int asso_func, const double* d_a, int na, const double* d_b, int nb, double img_w,

@@ -69,6 +69,13 @@ int bm_lap_solve_batch(const double* d_cost, int n_problems, int nr_max, int nc_
                        const int* d_nr, const int* d_nc, double cost_limit, int* d_x, int* d_y,
                        void* stream);
 
+/* Same contract and arguments, solved by the engine's fast exact solver (real rows only,
+ * implicit null option; csrc/lap_rect.cuh).  Equal to bm_lap_solve_batch whenever the
+ * optimum is unique; under exact cost ties it may return a different optimal solution. */
+int bm_lap_rect_batch(const double* d_cost, int n_problems, int nr_max, int nc_max,
+                      const int* d_nr, const int* d_nc, double cost_limit, int* d_x, int* d_y,
+                      void* stream);
+
 /* AssociationFunction.*_batch (boxmot/utils/iou.py:50-307): d_a [A][4], d_b [B][4]
  * xyxy float64 -> d_out [A][B] float64. */
 int bm_iou_matrix(int asso_func, const double* d_a, int na, const double* d_b, int nb,

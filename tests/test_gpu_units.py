@@ -12,7 +12,7 @@ def _dev(a, dtype=None):
     return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).cuda()
 
 
-def _lap_batch(costs, limit=np.inf):
+def _lap_batch(costs, limit=np.inf, entry="bm_lap_solve_batch"):
     from boxmot_b200 import _lib
     B = len(costs)
     nr = np.array([c.shape[0] for c in costs], np.int32)
@@ -25,7 +25,7 @@ def _lap_batch(costs, limit=np.inf):
     d_x = torch.full((B, R), -7, dtype=torch.int32, device="cuda")
     d_y = torch.full((B, C), -7, dtype=torch.int32, device="cuda")
     lim = float(limit) if limit < np.inf else float("inf")
-    _lib.check(_lib.lib().bm_lap_solve_batch(
+    _lib.check(getattr(_lib.lib(), entry)(
         ctypes.c_void_p(d_c.data_ptr()), B, R, C, ctypes.c_void_p(d_nr.data_ptr()),
         ctypes.c_void_p(d_nc.data_ptr()), lim, ctypes.c_void_p(d_x.data_ptr()),
         ctypes.c_void_p(d_y.data_ptr()), None), "bm_lap_solve_batch")
@@ -78,6 +78,53 @@ def test_lap_batch_large_tracking_shaped():
         _, xo, yo = lap.lapjv(c, extend_cost=True)
         assert np.array_equal(x[b, : c.shape[0]], xo)
         assert np.array_equal(y[b, : c.shape[1]], yo)
+
+
+@pytest.mark.parametrize("limit", [np.inf, 0.9, 0.3, -0.2])
+def test_lap_rect_equals_lapjv_on_unique_optima(limit):
+    """The engine's fast solver (real rows + implicit null option) returns lapjv's x / y
+    whenever the optimum is unique (continuous random costs), for every cost_limit mode."""
+    from oracle import lap
+    rng = np.random.default_rng(11)
+    costs = []
+    for it in range(300):
+        nr, nc = rng.integers(1, 120, 2)
+        c = rng.random((nr, nc)) * 2.0 - 1.2
+        if it % 3 == 0:      # tracking-shaped: few strong pairs on a weak dense background
+            c = -0.05 * rng.random((nr, nc))
+            k = min(nr, nc)
+            c[rng.permutation(nr)[:k], rng.permutation(nc)[:k]] -= rng.uniform(0.3, 1.0, k)
+        costs.append(c)
+    x, y = _lap_batch(costs, limit, entry="bm_lap_rect_batch")
+    for b, c in enumerate(costs):
+        _, xo, yo = lap.lapjv(c, extend_cost=True, cost_limit=limit)
+        assert np.array_equal(x[b, : c.shape[0]], xo), "problem %d rows" % b
+        assert np.array_equal(y[b, : c.shape[1]], yo), "problem %d cols" % b
+        assert (x[b, c.shape[0]:] == -1).all() and (y[b, c.shape[1]:] == -1).all()
+
+
+def test_lap_rect_is_optimal_under_ties():
+    """With exact ties any optimal solution may come back: the extended objective must
+    equal lapjv's (sum of matched costs + cost_limit/2 per unmatched row and column)."""
+    from oracle import lap
+    rng = np.random.default_rng(12)
+    costs = _random_costs(rng, 300, -1)
+    for limit in (0.4, np.inf):
+        x, y = _lap_batch(costs, limit, entry="bm_lap_rect_batch")
+        for b, c in enumerate(costs):
+            nr, nc = c.shape
+            _, xo, _ = lap.lapjv(c, extend_cost=True, cost_limit=limit)
+            pad = limit / 2 if limit < np.inf else c.max() + 1
+
+            def obj(xx):
+                m = xx >= 0
+                return c[np.nonzero(m)[0], xx[m]].sum() + pad * ((nr - m.sum()) + (nc - m.sum()))
+            xb = x[b, :nr]
+            assert len(set(xb[xb >= 0])) == (xb >= 0).sum()
+            for i in range(nr):
+                if xb[i] >= 0:
+                    assert y[b, xb[i]] == i
+            assert abs(obj(xb) - obj(xo)) < 1e-9, "problem %d: %r vs %r" % (b, obj(xb), obj(xo))
 
 
 def test_lap_batch_empty_problem():
