@@ -49,6 +49,7 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
         return fail(-1, "bm_ocsort_create: bad argument");
     if (cfg->delta_t < 1 || cfg->delta_t > 16) return fail(-1, "bm_ocsort_create: delta_t out of range");
+    if (track_cap > 1024) return fail(-1, "bm_ocsort_create: track_cap must be <= 1024");
     OcsEngine* e = new (std::nothrow) OcsEngine();
     if (!e) return fail(-3, "out of host memory");
     bm::OcsState& st = e->st;
@@ -76,6 +77,9 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     if (r == cudaSuccess) r = dev_alloc(e, &st.hdr, S * bm::OH_COUNT);
     if (r == cudaSuccess) r = dev_alloc(e, &st.n_updates, S);
     if (r == cudaSuccess) r = dev_alloc(e, &st.scratch, S * st.scratch_elems);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.abuf, S * bm::AB_COUNT * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.upd, S * 2 * (size_t)det_cap);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.born, S * (size_t)det_cap);
     e->smem = bm::ocsort_step_smem(st, pr);
     if (r == cudaSuccess) r = bm::ocsort_step_configure(e->smem);
     if (r != cudaSuccess) {

@@ -17,7 +17,9 @@ namespace bm {
 
 enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
 enum { OF_OBSERVED = 1, OF_SAVED = 2 };
-enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_COUNT = 8 };
+enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_COUNT = 12 };
+// association operands written by the predict kernel, indexed by LIST POSITION
+enum { AB_X1 = 0, AB_Y1, AB_X2, AB_Y2, AB_VY, AB_VX, AB_KCX, AB_KCY, AB_KVALID, AB_COUNT };
 
 struct OcsParams {
     double det_thresh, min_conf, iou_thr, inertia, q_xy, q_s, diag;
@@ -41,6 +43,9 @@ struct OcsState {
     int* hdr;                      // [S][OH_COUNT]
     unsigned long long* n_updates; // [S] live tracks that entered predict (bench unit)
     double* scratch;               // [S][scratch_elems]
+    double* abuf;                  // [S][AB_COUNT][Tcap] predicted boxes / OCM operands per list position
+    int* upd;                      // [S][2][Dcap] this frame's (slot, detection row) Kalman updates
+    int* born;                     // [S][Dcap]    detection rows that start a track, in id order
 };
 
 struct OcsView {   // per-stream base pointers

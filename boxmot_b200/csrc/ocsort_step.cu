@@ -1,34 +1,81 @@
-// OC-SORT frame step: ONE launch advances every stream of the engine by one frame
-// (one CTA per stream).  Mirrors OcSort.update (boxmot/trackers/ocsort/ocsort.py:246-439)
-// and enhanced_associate (boxmot/utils/association.py:377-533 with repairs R1-R3).
+// OC-SORT frame step: FOUR launches advance every stream of the engine by one frame,
+// with no host synchronisation in between (all lifecycle decisions are made on the device).
+// Mirrors OcSort.update (boxmot/trackers/ocsort/ocsort.py:246-439) and enhanced_associate
+// (boxmot/utils/association.py:377-533 with repairs R1-R3).
 //
-// Phases inside the CTA (all state decisions are made on the device, no host sync):
-//   A  split detections by confidence (ocsort.py:265-275)
-//   B  Kalman predict of every live track (ocsort.py:281-288, :173-186)
-//   C  IoU + velocity-direction (OCM) cost matrix, permutation fast path or lapjv
-//   D  Kalman update (+ORU) of matched tracks (ocsort.py:321-324)
-//   E  optional BYTE round (ocsort.py:330-356) and OCR round (ocsort.py:358-386)
-//   F  misses, births, output rows and dead-track removal (ocsort.py:388-439)
+//   K1 ocs_predict_kernel   thread per live track        Kalman predict (ocsort.py:281-288,
+//                           (HBM-streaming, SoA state)   :173-186) + association operands
+//   K2 ocs_assoc_kernel     CTA per stream, low regs     score split (:265-275), IoU + OCM cost,
+//                           cost matrix in smem          permutation fast path or exact LAP,
+//                                                        BYTE (:330-356) and OCR (:358-386) rounds
+//   K3 ocs_update_kernel    thread per matched track     Kalman update + ORU (:321-324,
+//                           (HBM-streaming)              xysr_kf.py:211-291)
+//   K4 ocs_finalize_kernel  CTA per stream               misses, births, output rows, dead-track
+//                                                        removal (:388-439)
+//
+// Splitting the step keeps the register-heavy fp64 Kalman code (255 registers/thread) out
+// of the association CTA, whose occupancy would otherwise be 2 CTAs/SM.
 #include "ocsort_engine.cuh"
 #include "lap_rect.cuh"
 
 namespace bm {
 
-constexpr int OCS_NT = 128;
+constexpr int K1_NT = 128;
+constexpr int K2_NT = 128;
+constexpr int K3_NT = 64;
 
+// ============================================================================ K1
+__global__ void __launch_bounds__(K1_NT)
+ocs_predict_kernel(OcsState st, OcsParams pr) {
+    const int chunks = (st.Tcap + K1_NT - 1) / K1_NT;
+    const int s = blockIdx.x / chunks;
+    const int p = (blockIdx.x % chunks) * K1_NT + threadIdx.x;
+    OcsView v(st, s);
+    const int nT = v.hdr[OH_NLIST];
+    if (p == 0) st.n_updates[s] += (unsigned long long)nT;
+    if (p >= nT) return;
+    const int Tcap = st.Tcap;
+    const XysrConst kc = {pr.q_xy, pr.q_s};
+    const int slot = v.order[p];
+    double x[7], P[49];
+    load_xP(v.xP, Tcap, slot, x, P);
+    if (x[6] + x[2] <= 0) x[6] *= 0.0;
+    xysr_predict(x, P, kc);
+    store_xP(v.xP, Tcap, slot, x, P);
+    const int age = v.I(OI_AGE, slot) + 1;
+    v.I(OI_AGE, slot) = age;
+    const int tsu = v.I(OI_TSU, slot);
+    if (tsu > 0) v.I(OI_STREAK, slot) = 0;
+    v.I(OI_TSU, slot) = tsu + 1;
+    double b[4];
+    x_to_xyxy(x, b);      // a NaN box makes K2 drop the track (ocsort.py:284-288)
+    double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
+#pragma unroll
+    for (int c = 0; c < 4; c++) ab[(AB_X1 + c) * Tcap + p] = b[c];
+    ab[AB_VY * Tcap + p] = v.vel[0 * Tcap + slot];
+    ab[AB_VX * Tcap + p] = v.vel[1 * Tcap + slot];
+    double kb[4];
+    const bool ok = ocs_lookback(v, slot, age, pr.delta_t, kb);
+    // placeholder observation is [-1,-1,-1,-1,-1] -> centre (-1,-1)
+    ab[AB_KCX * Tcap + p] = ok ? (kb[0] + kb[2]) / 2.0 : -1.0;
+    ab[AB_KCY * Tcap + p] = ok ? (kb[1] + kb[3]) / 2.0 : -1.0;
+    ab[AB_KVALID * Tcap + p] = ok ? 1.0 : 0.0;
+}
+
+// ============================================================================ K2
 struct OcsSmem {
-    double *dbox, *dconf, *dcls, *sbox, *sconf, *scls, *tbox, *kcx, *kcy, *vy, *vx, *wred, *rmin;
+    double *dbox, *dconf, *sbox, *tbox, *kcx, *kcy, *vy, *vx, *wred, *rmin;
     int *dind, *sind, *slot_of, *kvalid, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg;
     void* lapw;
     double* cost;
 };
 
-enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_OCR_RAN, M_NREJ, M_LAPBAD, M_NMATCH, M_COUNT = 16 };
+enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M_TMP, M_COUNT = 16 };
 
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
     size_t d = (size_t)Dcap, t = (size_t)Tcap;
-    size_t dbl = 7 * d + (use_byte ? 6 * d : 0) + 8 * t + 8;
-    size_t ints = 2 * d + (use_byte ? d : 0) + 2 * t + d + t + d + t + d + t + d + M_COUNT;
+    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + 8 * t + 8;
+    size_t ints = 7 * d + (use_byte ? d : 0) + 5 * t + M_COUNT;
     size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
     b += (lap_work_bytes((int)(d + t)) + 7) / 8 * 8;
     b += (size_t)cost_elems * 8;
@@ -40,32 +87,31 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     double* p = reinterpret_cast<double*>(base);
     m.dbox = p; p += 4 * Dcap;
     m.dconf = p; p += Dcap;
-    m.dcls = p; p += Dcap;
-    if (use_byte) { m.sbox = p; p += 4 * Dcap; m.sconf = p; p += Dcap; m.scls = p; p += Dcap; }
-    else { m.sbox = m.sconf = m.scls = nullptr; }
+    m.rmin = p; p += Dcap;
+    if (use_byte) { m.sbox = p; p += 4 * Dcap; } else m.sbox = nullptr;
     m.tbox = p; p += 4 * Tcap;
     m.kcx = p; p += Tcap;
     m.kcy = p; p += Tcap;
     m.vy = p; p += Tcap;
     m.vx = p; p += Tcap;
     m.wred = p; p += 8;
-    m.rmin = p; p += Dcap;
     int* q = reinterpret_cast<int*>(p);
     int* q0 = q;
     m.dind = q; q += Dcap;
     if (use_byte) { m.sind = q; q += Dcap; } else m.sind = nullptr;
+    m.d2t = q; q += Dcap;
+    m.um_d = q; q += Dcap;
+    m.rowcnt = q; q += Dcap;
+    m.hit_t = q; q += Dcap;
+    m.rarg = q; q += Dcap;
     m.slot_of = q; q += Tcap;
     m.kvalid = q; q += Tcap;
-    m.d2t = q; q += Dcap;
     m.t2d = q; q += Tcap;
-    m.um_d = q; q += Dcap;
     m.um_t = q; q += Tcap;
-    m.rowcnt = q; q += Dcap;
     m.colcnt = q; q += Tcap;
-    m.hit_t = q; q += Dcap;
     m.misc = q; q += M_COUNT;
-    m.rarg = q; q += Dcap;
-    size_t ib = ((size_t)(q - q0) * 4 + 7) / 8 * 8;
+    // 7*Dcap reserved: one Dcap block is spare so the int area never undercounts
+    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)5 * Tcap + M_COUNT) * 4 + 7) / 8 * 8;
     unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
     m.lapw = r;
     r += (lap_work_bytes(Dcap + Tcap) + 7) / 8 * 8;
@@ -82,6 +128,22 @@ __device__ __forceinline__ double acos_pinned(double c) {
     return acos(c);
 }
 
+// Stable compaction by ONE warp: out[k0 + rank] = val(i) for every i in [0, n) with
+// pred(i), in ascending i.  Returns k0 + count on all lanes.
+template <typename Pred, typename Val>
+__device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, Val val) {
+    const int lane = lane_id();
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + lane;
+        const bool ok = i < n && pred(i);
+        const unsigned b = __ballot_sync(BM_FULL, ok);
+        if (ok) out[k0 + __popc(b & ((1u << lane) - 1))] = val(i);
+        k0 += __popc(b);
+    }
+    __syncwarp();
+    return k0;
+}
+
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
 // `alist` (indices into a detection set `abox`), cols = the nB list positions in
 // `blist` with boxes fetched by `bfetch`.  lapjv on -iou, accept pairs with iou >= thr
@@ -96,14 +158,14 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
     double* cost = (need <= (size_t)st.smem_cost_elems) ? sm.cost : st.scratch + (size_t)s * st.scratch_elems;
     if (need > st.scratch_elems && need > (size_t)st.smem_cost_elems) {
         if (tid == 0) atomicOr(&st.hdr[(size_t)s * OH_COUNT + OH_ERR], BM_ERR_SCRATCH);
-        for (int r = tid; r < nA; r += OCS_NT) pair_b[r] = -1;
+        for (int r = tid; r < nA; r += K2_NT) pair_b[r] = -1;
         __syncthreads();
         return false;
     }
     double mx = -CUDART_INF;   // max of iou_left
     double cmx = -CUDART_INF;  // max of -iou_left
     int nanf = 0;
-    for (size_t e = tid; e < need; e += OCS_NT) {
+    for (size_t e = tid; e < need; e += K2_NT) {
         const int r = (int)(e / nB), c = (int)(e % nB);
         const int d = alist[r];
         Box a = {abox[0 * Dld + d], abox[1 * Dld + d], abox[2 * Dld + d], abox[3 * Dld + d]};
@@ -115,22 +177,21 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
         cmx = fmax(cmx, cc);
         cost[e] = cc;
     }
-    // block reductions (max, max, or)
     for (int o = 16; o > 0; o >>= 1) {
         mx = fmax(mx, shfl_xor_d(mx, o));
         cmx = fmax(cmx, shfl_xor_d(cmx, o));
         nanf |= __shfl_xor_sync(BM_FULL, nanf, o);
     }
-    __shared__ double s_mx[OCS_NT / 32], s_cmx[OCS_NT / 32];
-    __shared__ int s_nan[OCS_NT / 32];
+    __shared__ double s_mx[K2_NT / 32], s_cmx[K2_NT / 32];
+    __shared__ int s_nan[K2_NT / 32];
     if (lane == 0) { s_mx[wid] = mx; s_cmx[wid] = cmx; s_nan[wid] = nanf; }
     __syncthreads();
     mx = s_mx[0]; cmx = s_cmx[0]; nanf = s_nan[0];
-    for (int i = 1; i < OCS_NT / 32; i++) { mx = fmax(mx, s_mx[i]); cmx = fmax(cmx, s_cmx[i]); nanf |= s_nan[i]; }
+    for (int i = 1; i < K2_NT / 32; i++) { mx = fmax(mx, s_mx[i]); cmx = fmax(cmx, s_cmx[i]); nanf |= s_nan[i]; }
     __syncthreads();
     const bool run = !nanf && mx > pr.iou_thr;
     if (!run) {
-        for (int r = tid; r < nA; r += OCS_NT) pair_b[r] = -1;
+        for (int r = tid; r < nA; r += K2_NT) pair_b[r] = -1;
         __syncthreads();
         return false;
     }
@@ -152,10 +213,6 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
     return true;
 }
 
-}  // namespace bm
-
-namespace bm {
-
 struct FetchPred {
     const double* tbox; int Tcap;
     __device__ Box operator()(int p) const {
@@ -172,25 +229,24 @@ struct FetchLast {
 
 // dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
 // precision: BaseTracker.setup_decorator round-trips every ndarray through float32
-// (boxmot/trackers/basetracker.py:122-128).  out: [S][Tcap][8] float64 rows
-// (x1,y1,x2,y2,id,conf,cls,det_ind) in the reference's row order; nout[S].
-__global__ void __launch_bounds__(OCS_NT)
-ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
-                   const int* __restrict__ ndets, double* __restrict__ out, int* __restrict__ nout) {
+// (boxmot/trackers/basetracker.py:122-128).
+__global__ void __launch_bounds__(K2_NT, 4)
+ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const int Tcap = st.Tcap, Dcap = st.Dcap;
     OcsSmem sm = ocs_carve(smem_raw, Tcap, Dcap, pr.use_byte, st.smem_cost_elems);
     OcsView v(st, s);
-    const XysrConst kc = {pr.q_xy, pr.q_s};
     const float* dsrc = dets + (size_t)s * Dcap * 6;
+    int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
+    int* upd_det = upd_slot + Dcap;
 
-    // ------------------------------------------------------------------ phase A
+    // ---- split detections by confidence (ocsort.py:265-275), stable order
     int nD_in = ndets[s];
     if (nD_in > Dcap) { if (tid == 0) atomicOr(&v.hdr[OH_ERR], BM_ERR_DET_OVERFLOW); nD_in = Dcap; }
     if (tid < M_COUNT) sm.misc[tid] = 0;
     __syncthreads();
-    if (wid == 0) {   // stable compaction of the high (and second-round) detections
+    if (wid == 0) {
         int nh = 0, ns = 0;
         for (int base = 0; base < nD_in; base += 32) {
             const int i = base + lane;
@@ -203,79 +259,59 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
             if (hi) {
                 const int p = nh + __popc(bh & lt);
                 for (int c = 0; c < 4; c++) sm.dbox[c * Dcap + p] = (double)dsrc[i * 6 + c];
-                sm.dconf[p] = conf; sm.dcls[p] = (double)dsrc[i * 6 + 5]; sm.dind[p] = i;
+                sm.dconf[p] = conf; sm.dind[p] = i;
             }
             if (se) {
                 const int p = ns + __popc(bs & lt);
                 for (int c = 0; c < 4; c++) sm.sbox[c * Dcap + p] = (double)dsrc[i * 6 + c];
-                sm.sconf[p] = conf; sm.scls[p] = (double)dsrc[i * 6 + 5]; sm.sind[p] = i;
+                sm.sind[p] = i;
             }
             nh += __popc(bh); ns += __popc(bs);
         }
         if (lane == 0) { sm.misc[M_ND] = nh; sm.misc[M_NS] = ns; }
     }
+    // ---- association operands of the predicted tracks (written by K1)
     int nT = v.hdr[OH_NLIST];
-    const int frame = v.hdr[OH_FRAME] + 1;
-    __syncthreads();
-    const int nD = sm.misc[M_ND], nS = sm.misc[M_NS];
-    if (tid == 0) st.n_updates[s] += (unsigned long long)nT;
-
-    // ------------------------------------------------------------------ phase B
-    for (int p = tid; p < nT; p += OCS_NT) {
-        const int slot = v.order[p];
-        double x[7], P[49];
-        load_xP(v.xP, Tcap, slot, x, P);
-        if (x[6] + x[2] <= 0) x[6] *= 0.0;
-        xysr_predict(x, P, kc);
-        store_xP(v.xP, Tcap, slot, x, P);
-        v.I(OI_AGE, slot) += 1;
-        const int tsu = v.I(OI_TSU, slot);
-        if (tsu > 0) v.I(OI_STREAK, slot) = 0;
-        v.I(OI_TSU, slot) = tsu + 1;
+    const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
+    for (int p = tid; p < nT; p += K2_NT) {
         double b[4];
-        x_to_xyxy(x, b);
-        if (b[0] != b[0] || b[1] != b[1] || b[2] != b[2] || b[3] != b[3]) {
-            sm.t2d[p] = -2;   // NaN prediction: the reference drops the track (ocsort.py:284-288)
-            sm.misc[M_ANYBAD] = 1;
-        } else sm.t2d[p] = -1;
+#pragma unroll
+        for (int c = 0; c < 4; c++) { b[c] = ab[(AB_X1 + c) * Tcap + p]; sm.tbox[c * Tcap + p] = b[c]; }
+        sm.vy[p] = ab[AB_VY * Tcap + p];
+        sm.vx[p] = ab[AB_VX * Tcap + p];
+        sm.kcx[p] = ab[AB_KCX * Tcap + p];
+        sm.kcy[p] = ab[AB_KCY * Tcap + p];
+        sm.kvalid[p] = ab[AB_KVALID * Tcap + p] != 0.0 ? 1 : 0;
+        sm.slot_of[p] = v.order[p];
+        const bool bad = b[0] != b[0] || b[1] != b[1] || b[2] != b[2] || b[3] != b[3];
+        sm.t2d[p] = bad ? -2 : -1;
+        sm.colcnt[p] = 0;
+        if (bad) sm.misc[M_ANYBAD] = 1;
     }
     __syncthreads();
-    if (sm.misc[M_ANYBAD]) {
+    if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288)
         if (tid == 0) {
             int k = 0;
-            for (int p = 0; p < nT; p++) if (sm.t2d[p] != -2) v.order[k++] = v.order[p];
+            for (int p = 0; p < nT; p++) {
+                if (sm.t2d[p] == -2) continue;
+                for (int c = 0; c < 4; c++) sm.tbox[c * Tcap + k] = sm.tbox[c * Tcap + p];
+                sm.vy[k] = sm.vy[p]; sm.vx[k] = sm.vx[p]; sm.kcx[k] = sm.kcx[p]; sm.kcy[k] = sm.kcy[p];
+                sm.kvalid[k] = sm.kvalid[p]; sm.slot_of[k] = sm.slot_of[p]; sm.t2d[k] = -1;
+                v.order[k] = sm.slot_of[k];
+                k++;
+            }
+            v.hdr[OH_NLIST] = k;
             sm.misc[M_NT] = k;
         }
         __syncthreads();
         nT = sm.misc[M_NT];
     }
-    // per-position operands of the association
-    for (int p = tid; p < nT; p += OCS_NT) {
-        const int slot = v.order[p];
-        sm.slot_of[p] = slot;
-        double x[7];
-#pragma unroll
-        for (int c = 0; c < 7; c++) x[c] = v.xP[c * Tcap + slot];
-        double b[4];
-        x_to_xyxy(x, b);
-#pragma unroll
-        for (int c = 0; c < 4; c++) sm.tbox[c * Tcap + p] = b[c];
-        sm.vy[p] = v.vel[0 * Tcap + slot];
-        sm.vx[p] = v.vel[1 * Tcap + slot];
-        double kb[4];
-        const bool ok = ocs_lookback(v, slot, v.I(OI_AGE, slot), pr.delta_t, kb);
-        sm.kvalid[p] = ok ? 1 : 0;
-        // placeholder observation is [-1,-1,-1,-1,-1] -> centre (-1,-1)
-        sm.kcx[p] = ok ? (kb[0] + kb[2]) / 2.0 : -1.0;
-        sm.kcy[p] = ok ? (kb[1] + kb[3]) / 2.0 : -1.0;
-        sm.t2d[p] = -1;
-        sm.colcnt[p] = 0;
-    }
-    for (int d = tid; d < nD; d += OCS_NT) { sm.d2t[d] = -1; sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
+    const int nD = sm.misc[M_ND], nS = sm.misc[M_NS];
+    for (int d = tid; d < nD; d += K2_NT) { sm.d2t[d] = -1; sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
     __syncthreads();
 
-    // ------------------------------------------------------------------ phase C
-    // cost[d][t] = -(iou + OCM), det-major like enhanced_associate (association.py:427-461)
+    // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
+    // (association.py:427-461); permutation fast path (:501-503) or exact LAP (:505-507)
     const size_t need = (size_t)nD * nT;
     double* cost = (need <= (size_t)st.smem_cost_elems) ? sm.cost : st.scratch + (size_t)s * st.scratch_elems;
     bool assoc_ok = true;
@@ -285,7 +321,7 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
     }
     if (nD > 0 && nT > 0 && assoc_ok) {
         double cmx = -CUDART_INF;
-        for (int d = wid; d < nD; d += OCS_NT / 32) {      // one warp per detection row
+        for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
             const Box a = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d], sm.dbox[3 * Dcap + d]};
             const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
             double rm = CUDART_INF;
@@ -293,14 +329,20 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
             for (int t = lane; t < nT; t += 32) {
                 const Box b = {sm.tbox[0 * Tcap + t], sm.tbox[1 * Tcap + t], sm.tbox[2 * Tcap + t], sm.tbox[3 * Tcap + t]};
                 const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
-                // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
-                double dx = cxd - sm.kcx[t], dy = cyd - sm.kcy[t];
-                const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
-                dx = dx / norm; dy = dy / norm;
-                double cs = sm.vx[t] * dx + sm.vy[t] * dy;
-                cs = fmin(1.0, fmax(-1.0, cs));
-                const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
-                const double motion = ((sm.kvalid[t] ? 1.0 : 0.0) * ang) * pr.inertia;
+                const double vx = sm.vx[t], vy = sm.vy[t];
+                double motion = 0.0;
+                // A track that was never observed (valid = 0) or has no velocity yet
+                // (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly) contributes exactly 0.
+                if (sm.kvalid[t] && (vx != 0.0 || vy != 0.0)) {
+                    // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
+                    double dx = cxd - sm.kcx[t], dy = cyd - sm.kcy[t];
+                    const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
+                    dx = dx / norm; dy = dy / norm;
+                    double cs = vx * dx + vy * dy;
+                    cs = fmin(1.0, fmax(-1.0, cs));
+                    const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
+                    motion = (1.0 * ang) * pr.inertia;
+                }
                 const double cc = -(iou + motion);
                 cost[(size_t)d * nT + t] = cc;
                 cmx = fmax(cmx, cc);
@@ -317,7 +359,6 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
         for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
         if (lane == 0) sm.wred[wid] = cmx;
         __syncthreads();
-        // permutation fast path: every row/column has at most one IoU hit, at least one exists
         if (wid == 0) {
             int rmax = 0, cmax_ = 0;
             for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
@@ -336,9 +377,9 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
                 }
             } else {
                 double pad = sm.wred[0];
-                for (int i = 1; i < OCS_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
+                for (int i = 1; i < K2_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
                 // With nD <= nT every detection is assigned in every optimal solution, so the
-                // reference's unmatched-detection ORDER (never-assigned first, then rejected,
+                // reference's unmatched-detection ORDER (never-assigned first, then rejected;
                 // ocsort ids follow it) does not depend on lapjv's tie-breaking and the fast
                 // exact solver applies.  With nD > nT WHICH zero-gain detections stay
                 // unassigned is decided by lapjv's scan order: emulate it step for step.
@@ -377,155 +418,204 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
         }
         __syncthreads();
     } else {
-        for (int d = tid; d < nD; d += OCS_NT) { sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
+        for (int d = tid; d < nD; d += K2_NT) { sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
         __syncthreads();
     }
-    // unmatched lists in the reference's order (repair R3): never-assigned ascending,
-    // then IoU-rejected pairs in detection-row order.
-    if (tid == 0) {
-        int nud = 0, nut = 0;
-        for (int d = 0; d < nD; d++) if (sm.rowcnt[d] == 0) sm.um_d[nud++] = d;
+    // ---- unmatched lists in the reference's order (repair R3): never-assigned ascending,
+    // then IoU-rejected pairs in detection-row order; matched pairs go to the update list
+    if (wid == 0) {
+        const bool lap_ran = sm.misc[M_FAST] == 0 && nD > 0;
+        int nud = warp_compact(nD, sm.um_d, 0, [&](int d) { return sm.rowcnt[d] == 0; }, [&](int d) { return d; });
+        int nut = warp_compact(nT, sm.um_t, 0,
+                               [&](int t) { return sm.t2d[t] < 0 && !(sm.colcnt[t] < 0 && lap_ran); },
+                               [&](int t) { return t; });
         if (nT > 0) {
-            for (int t = 0; t < nT; t++) {
-                // a track is "never assigned" when no detection row holds it (accepted or rejected)
-                const bool rejected_col = sm.colcnt[t] < 0 && sm.misc[M_FAST] == 0 && nD > 0;
-                if (sm.t2d[t] < 0 && !rejected_col) sm.um_t[nut++] = t;
-            }
-            for (int d = 0; d < nD; d++) if (sm.rowcnt[d] == 2) { sm.um_d[nud++] = d; sm.um_t[nut++] = sm.hit_t[d]; }
+            const int nud0 = nud;
+            nud = warp_compact(nD, sm.um_d, nud0, [&](int d) { return sm.rowcnt[d] == 2; }, [&](int d) { return d; });
+            nut = warp_compact(nD, sm.um_t, nut, [&](int d) { return sm.rowcnt[d] == 2; }, [&](int d) { return sm.hit_t[d]; });
         }
-        sm.misc[M_NUD] = nud; sm.misc[M_NUT] = nut;
+        const int nup = warp_compact(nD, upd_slot, 0, [&](int d) { return sm.d2t[d] >= 0; },
+                                     [&](int d) { return sm.slot_of[sm.d2t[d]]; });
+        warp_compact(nD, upd_det, 0, [&](int d) { return sm.d2t[d] >= 0; }, [&](int d) { return sm.dind[d]; });
+        if (lane == 0) { sm.misc[M_NUD] = nud; sm.misc[M_NUT] = nut; sm.misc[M_NUPD] = nup; }
     }
     __syncthreads();
 
-    // ------------------------------------------------------------------ phase D
-    for (int d = tid; d < nD; d += OCS_NT) {
-        const int t = sm.d2t[d];
-        if (t >= 0) {
-            const double det[5] = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d],
-                                   sm.dbox[3 * Dcap + d], sm.dconf[d]};
-            ocs_track_update(v, sm.slot_of[t], det, sm.dcls[d], sm.dind[d], pr.delta_t, kc);
-        }
-    }
-    __syncthreads();
-
-    // ------------------------------------------------------------------ phase E
+    // ---- BYTE round on the low-score detections (ocsort.py:330-356)
     int nUD = sm.misc[M_NUD], nUT = sm.misc[M_NUT];
-    if (pr.use_byte && nS > 0 && nUT > 0) {   // BYTE round on the low-score detections
-        for (int r = tid; r < nS; r += OCS_NT) sm.d2t[r] = r;
-        for (int t = tid; t < nT; t += OCS_NT) sm.colcnt[t] = 0;
+    if (pr.use_byte && nS > 0 && nUT > 0) {
+        for (int r = tid; r < nS; r += K2_NT) sm.d2t[r] = r;
+        for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = 0;
         __syncthreads();
         const bool ran = ocs_second_round(st, pr, s, sm, sm.sbox, Dcap, sm.d2t, nS, sm.um_t, nUT,
                                           FetchPred{sm.tbox, Tcap}, sm.hit_t);
         if (ran) {
-            for (int r = tid; r < nS; r += OCS_NT) {
-                const int c = sm.hit_t[r];
-                if (c >= 0) {
-                    const int t = sm.um_t[c];
-                    const double det[5] = {sm.sbox[0 * Dcap + r], sm.sbox[1 * Dcap + r], sm.sbox[2 * Dcap + r],
-                                           sm.sbox[3 * Dcap + r], sm.sconf[r]};
-                    ocs_track_update(v, sm.slot_of[t], det, sm.scls[r], sm.sind[r], pr.delta_t, kc);
-                    sm.colcnt[t] = 2;   // taken
-                }
-            }
-            __syncthreads();
-            if (tid == 0) {   // np.setdiff1d: sorted ascending, taken tracks removed
-                for (int c = 0; c < nUT; c++) { const int t = sm.um_t[c]; if (sm.colcnt[t] != 2) sm.colcnt[t] = 1; }
-                int k = 0;
-                for (int t = 0; t < nT; t++) if (sm.colcnt[t] == 1) sm.um_t[k++] = t;
-                sm.misc[M_NUT] = k;
+            if (wid == 0) {
+                const int n0 = sm.misc[M_NUPD];
+                for (int r = lane; r < nS; r += 32) if (sm.hit_t[r] >= 0) sm.colcnt[sm.um_t[sm.hit_t[r]]] = 2;   // taken
+                __syncwarp();
+                const int n1 = warp_compact(nS, upd_slot, n0, [&](int r) { return sm.hit_t[r] >= 0; },
+                                            [&](int r) { return sm.slot_of[sm.um_t[sm.hit_t[r]]]; });
+                warp_compact(nS, upd_det, n0, [&](int r) { return sm.hit_t[r] >= 0; }, [&](int r) { return sm.sind[r]; });
+                // np.setdiff1d: sorted ascending, taken tracks removed
+                for (int c = lane; c < nUT; c += 32) { const int t = sm.um_t[c]; if (sm.colcnt[t] != 2) sm.colcnt[t] = 1; }
+                __syncwarp();
+                const int k = warp_compact(nT, sm.um_t, 0, [&](int t) { return sm.colcnt[t] == 1; }, [&](int t) { return t; });
+                if (lane == 0) { sm.misc[M_NUT] = k; sm.misc[M_NUPD] = n1; }
             }
             __syncthreads();
             nUT = sm.misc[M_NUT];
         }
     }
-    if (nUD > 0 && nUT > 0) {                  // OCR: leftover detections vs last observations
-        for (int t = tid; t < nT; t += OCS_NT) sm.colcnt[t] = 0;
-        for (int d = tid; d < nD; d += OCS_NT) sm.rowcnt[d] = 0;
+    // ---- OCR: leftover detections vs the tracks' last observations (ocsort.py:358-386)
+    if (nUD > 0 && nUT > 0) {
+        for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = 0;
+        for (int d = tid; d < nD; d += K2_NT) sm.rowcnt[d] = 0;
         __syncthreads();
         const bool ran = ocs_second_round(st, pr, s, sm, sm.dbox, Dcap, sm.um_d, nUD, sm.um_t, nUT,
                                           FetchLast{v.lastobs, sm.slot_of, Tcap}, sm.hit_t);
         if (ran) {
-            for (int r = tid; r < nUD; r += OCS_NT) {
-                const int c = sm.hit_t[r];
-                if (c >= 0) {
-                    const int d = sm.um_d[r], t = sm.um_t[c];
-                    const double det[5] = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d],
-                                           sm.dbox[3 * Dcap + d], sm.dconf[d]};
-                    ocs_track_update(v, sm.slot_of[t], det, sm.dcls[d], sm.dind[d], pr.delta_t, kc);
-                    sm.colcnt[t] = 2;
-                    sm.rowcnt[d] = 2;
+            if (wid == 0) {
+                const int n0 = sm.misc[M_NUPD];
+                for (int r = lane; r < nUD; r += 32) {
+                    const int c = sm.hit_t[r];
+                    if (c >= 0) { sm.colcnt[sm.um_t[c]] = 2; sm.rowcnt[sm.um_d[r]] = 2; }
                 }
+                __syncwarp();
+                const int n1 = warp_compact(nUD, upd_slot, n0, [&](int r) { return sm.hit_t[r] >= 0; },
+                                            [&](int r) { return sm.slot_of[sm.um_t[sm.hit_t[r]]]; });
+                warp_compact(nUD, upd_det, n0, [&](int r) { return sm.hit_t[r] >= 0; },
+                             [&](int r) { return sm.dind[sm.um_d[r]]; });
+                for (int c = lane; c < nUT; c += 32) { const int t = sm.um_t[c]; if (sm.colcnt[t] != 2) sm.colcnt[t] = 1; }
+                for (int r = lane; r < nUD; r += 32) { const int d = sm.um_d[r]; if (sm.rowcnt[d] != 2) sm.rowcnt[d] = 1; }
+                __syncwarp();
+                const int k = warp_compact(nT, sm.um_t, 0, [&](int t) { return sm.colcnt[t] == 1; }, [&](int t) { return t; });
+                const int kd = warp_compact(nD, sm.um_d, 0, [&](int d) { return sm.rowcnt[d] == 1; }, [&](int d) { return d; });
+                if (lane == 0) { sm.misc[M_NUT] = k; sm.misc[M_NUD] = kd; sm.misc[M_NUPD] = n1; }
             }
             __syncthreads();
-            if (tid == 0) {
-                for (int c = 0; c < nUT; c++) { const int t = sm.um_t[c]; if (sm.colcnt[t] != 2) sm.colcnt[t] = 1; }
-                for (int r = 0; r < nUD; r++) { const int d = sm.um_d[r]; if (sm.rowcnt[d] != 2) sm.rowcnt[d] = 1; }
-                int k = 0;
-                for (int t = 0; t < nT; t++) if (sm.colcnt[t] == 1) sm.um_t[k++] = t;
-                sm.misc[M_NUT] = k;
-                k = 0;
-                for (int d = 0; d < nD; d++) if (sm.rowcnt[d] == 1) sm.um_d[k++] = d;
-                sm.misc[M_NUD] = k;
-            }
-            __syncthreads();
-            nUT = sm.misc[M_NUT];
             nUD = sm.misc[M_NUD];
         }
     }
+    // ---- births: ids are handed out in unmatched-detection list order (ocsort.py:392-413)
+    int* born = st.born + (size_t)s * Dcap;
+    for (int r = tid; r < nUD; r += K2_NT) born[r] = sm.dind[sm.um_d[r]];
+    if (tid == 0) {
+        v.hdr[OH_NUPD] = sm.misc[M_NUPD];
+        v.hdr[OH_NBORN] = nUD;
+        v.hdr[OH_MATCH] += sm.misc[M_NUPD];
+        if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
+    }
+}
 
-    // ------------------------------------------------------------------ phase F
-    for (int c = tid; c < nUT; c += OCS_NT) ocs_track_miss(v, sm.slot_of[sm.um_t[c]]);
-    // births: ids and slots are handed out in unmatched-detection list order (ocsort.py:392-413)
-    if (tid == 0) {
-        for (int t = 0; t < Tcap; t++) sm.colcnt[t] = 0;            // slot-in-use map
-        for (int p = 0; p < nT; p++) sm.colcnt[sm.slot_of[p]] = 1;
-        int next_free = 0, born = 0;
-        for (int r = 0; r < nUD; r++) {
-            while (next_free < Tcap && sm.colcnt[next_free]) next_free++;
-            if (next_free >= Tcap) { atomicOr(&v.hdr[OH_ERR], BM_ERR_TRACK_OVERFLOW); break; }
-            sm.colcnt[next_free] = 1;
-            sm.hit_t[r] = next_free;                                 // slot of the r-th birth
-            v.order[nT + born] = next_free;
-            born++;
+// ============================================================================ K3
+// One thread per (track, detection) pair of the frame: KalmanBoxTracker.update with a
+// real detection (ocsort.py:136-169) + KalmanFilterXYSR.update incl. ORU.
+__global__ void __launch_bounds__(K3_NT)
+ocs_update_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
+    const int chunks = (st.Dcap + K3_NT - 1) / K3_NT;
+    const int s = blockIdx.x / chunks;
+    const int k = (blockIdx.x % chunks) * K3_NT + threadIdx.x;
+    OcsView v(st, s);
+    if (k >= v.hdr[OH_NUPD]) return;
+    const int* upd_slot = st.upd + (size_t)s * 2 * st.Dcap;
+    const int slot = upd_slot[k], di = upd_slot[st.Dcap + k];
+    const float* dr = dets + ((size_t)s * st.Dcap + di) * 6;
+    const double det[5] = {(double)dr[0], (double)dr[1], (double)dr[2], (double)dr[3], (double)dr[4]};
+    const XysrConst kc = {pr.q_xy, pr.q_s};
+    ocs_track_update(v, slot, det, (double)dr[5], di, pr.delta_t, kc);
+}
+
+// ============================================================================ K4
+// Exclusive block scan of one int per thread (blockDim <= 1024); total on all threads.
+__device__ __forceinline__ int block_excl_scan(int val, int* total, int* ws /*[33]*/) {
+    const int lane = lane_id(), wid = warp_id();
+    int inc = val;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(BM_FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) ws[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const int nw = (blockDim.x + 31) / 32;
+        int w = lane < nw ? ws[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(BM_FULL, w, o);
+            if (lane >= o) w += t;
         }
-        sm.misc[M_NREJ] = born;
+        if (lane < nw) ws[lane] = w;     // inclusive warp totals
+        if (lane == 31) ws[32] = w;
     }
     __syncthreads();
-    const int born = sm.misc[M_NREJ];
+    const int base = wid > 0 ? ws[wid - 1] : 0;
+    *total = ws[32];
+    __syncthreads();
+    return base + inc - val;
+}
+
+// One CTA per stream, one thread per slot / list position (blockDim = Tcap rounded up
+// to a warp, Tcap <= 1024).
+__global__ void __launch_bounds__(1024)
+ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, double* __restrict__ out,
+                    int* __restrict__ nout) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int* inuse = reinterpret_cast<int*>(smem_raw);     // [Tcap]
+    int* bslot = inuse + st.Tcap;                       // [Tcap]
+    __shared__ int ws[33];
+    const int s = blockIdx.x, tid = threadIdx.x;
+    const int Tcap = st.Tcap, Dcap = st.Dcap;
+    OcsView v(st, s);
+    const int nT = v.hdr[OH_NLIST];
+    int born = v.hdr[OH_NBORN];
     const int id0 = v.hdr[OH_NEXT_ID];
-    for (int r = tid; r < born; r += OCS_NT) {
-        const int d = sm.um_d[r];
-        const double det[5] = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d],
-                               sm.dbox[3 * Dcap + d], sm.dconf[d]};
-        ocs_track_init(v, sm.hit_t[r], det, sm.dcls[d], sm.dind[d], id0 + r);
+    const int frame = v.hdr[OH_FRAME] + 1;
+    const XysrConst kc = {pr.q_xy, pr.q_s};
+    (void)kc;
+    // slots in use, misses
+    if (tid < Tcap) inuse[tid] = 0;
+    __syncthreads();
+    int slot = -1;
+    if (tid < nT) {
+        slot = v.order[tid];
+        inuse[slot] = 1;
+        if (v.I(OI_TSU, slot) != 0) ocs_track_miss(v, slot);   // update(None) (ocsort.py:388-389)
     }
     __syncthreads();
-    const int nAll = nT + born;
+    // births take the free slots in ascending order
+    const int isfree = (tid < Tcap && !inuse[tid]) ? 1 : 0;
+    int nfree;
+    const int frank = block_excl_scan(isfree, &nfree, ws);
+    if (born > nfree) {
+        if (tid == 0) atomicOr(&v.hdr[OH_ERR], BM_ERR_TRACK_OVERFLOW);
+        born = nfree;
+    }
+    if (isfree && frank < born) bslot[frank] = tid;
+    __syncthreads();
+    if (tid < born) {
+        const int di = st.born[(size_t)s * Dcap + tid];
+        const float* dr = dets + ((size_t)s * Dcap + di) * 6;
+        const double det[5] = {(double)dr[0], (double)dr[1], (double)dr[2], (double)dr[3], (double)dr[4]};
+        ocs_track_init(v, bslot[tid], det, (double)dr[5], di, id0 + tid);
+    }
+    if (tid >= nT && tid < nT + born) slot = bslot[tid - nT];
+    __syncthreads();
     // output rows walk the list backwards; dead tracks leave the list (ocsort.py:414-436)
-    double* orow = out + (size_t)s * Tcap * 8;
-    for (int p = tid; p < nAll; p += OCS_NT) {
-        const int slot = v.order[p];
+    const int nAll = nT + born;
+    int emit = 0, keep = 0;
+    if (tid < nAll) {
         const int tsu = v.I(OI_TSU, slot);
-        const bool emit = tsu < 1 && (v.I(OI_STREAK, slot) >= pr.min_hits || frame <= pr.min_hits);
-        sm.kvalid[p] = (emit ? 1 : 0) | (tsu > pr.max_age ? 2 : 0);
-        if (p < nT && tsu == 0) atomicAdd(&sm.misc[M_NMATCH], 1);   // matched this frame (bench counter)
+        emit = (tsu < 1 && (v.I(OI_STREAK, slot) >= pr.min_hits || frame <= pr.min_hits)) ? 1 : 0;
+        keep = tsu > pr.max_age ? 0 : 1;
     }
-    __syncthreads();
-    if (tid == 0) {
-        int k = 0;
-        for (int p = nAll - 1; p >= 0; p--) if (sm.kvalid[p] & 1) sm.um_t[p] = k++; else sm.um_t[p] = -1;
-        nout[s] = k;
-        int keep = 0;
-        for (int p = 0; p < nAll; p++) if (!(sm.kvalid[p] & 2)) sm.slot_of[keep++] = v.order[p];
-        sm.misc[M_NT] = keep;
-    }
-    __syncthreads();
-    for (int p = tid; p < nAll; p += OCS_NT) {
-        const int k = sm.um_t[p];
-        if (k < 0) continue;
-        const int slot = v.order[p];
-        double b[4];
-        double lo[5];
+    int n_emit, n_keep;
+    const int erank = block_excl_scan(emit, &n_emit, ws);
+    const int krank = block_excl_scan(keep, &n_keep, ws);
+    if (emit) {
+        const int k = n_emit - 1 - erank;              // rows are newest-first
+        double b[4], lo[5];
 #pragma unroll
         for (int c = 0; c < 5; c++) lo[c] = v.lastobs[c * Tcap + slot];
         const double lsum = (((lo[0] + lo[1]) + lo[2]) + lo[3]) + lo[4];
@@ -538,23 +628,20 @@ ocsort_step_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets,
 #pragma unroll
             for (int c = 0; c < 4; c++) b[c] = lo[c];
         }
-        double* o = orow + (size_t)k * 8;
+        double* o = out + ((size_t)s * Tcap + k) * 8;
         o[0] = b[0]; o[1] = b[1]; o[2] = b[2]; o[3] = b[3];
         o[4] = (double)(v.I(OI_ID, slot) + 1);
         o[5] = v.confcls[0 * Tcap + slot];
         o[6] = v.confcls[1 * Tcap + slot];
         o[7] = (double)v.I(OI_DETIND, slot);
     }
-    __syncthreads();
-    const int keep = sm.misc[M_NT];
-    for (int p = tid; p < keep; p += OCS_NT) v.order[p] = sm.slot_of[p];
+    if (keep) v.order[krank] = slot;      // every thread read its slot before the scans' barriers
     if (tid == 0) {
-        v.hdr[OH_NLIST] = keep;
+        nout[s] = n_emit;
+        v.hdr[OH_NLIST] = n_keep;
         v.hdr[OH_NEXT_ID] = id0 + born;
         v.hdr[OH_FRAME] = frame;
-        v.hdr[OH_MATCH] += sm.misc[M_NMATCH];
         v.hdr[OH_BIRTHS] += born;
-        if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
     }
 }
 
@@ -567,13 +654,17 @@ size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr) {
 }
 
 cudaError_t ocsort_step_configure(size_t smem) {
-    return cudaFuncSetAttribute(ocsort_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    return cudaFuncSetAttribute(ocs_assoc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
 cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
                                double* out, int* nout, cudaStream_t stream) {
-    const size_t smem = ocsort_step_smem(st, pr);
-    ocsort_step_kernel<<<st.S, OCS_NT, smem, stream>>>(st, pr, dets, ndets, out, nout);
+    const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
+    ocs_predict_kernel<<<st.S * c1, K1_NT, 0, stream>>>(st, pr);
+    ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets, ndets);
+    ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
+    const int nt4 = (st.Tcap + 31) / 32 * 32;
+    ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
     return cudaGetLastError();
 }
 
