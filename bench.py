@@ -199,13 +199,14 @@ class ClockSampler(threading.Thread):
 
 # --------------------------------------------------------------------------- GPU arm
 def alg_bytes(track_updates, matches, births, dets_in, rows_out):
-    """Algorithmic bytes moved by the fused frame-step kernel (SURVEY.md 8(d) per-unit
-    figures, XYSR state = 7+49 fp64 = 448 B): predict 2*448*T, update (2*448+32)*M,
-    detections in 24*D (float32 x 6; the IoU operands), LAP result 4*(T+D), lifecycle
-    scalars 64*T, output rows 64*M_out, birth state write 448*B.  Cost matrix and LAP
-    input count 0 bytes: they are fused on chip."""
-    return (2 * 448 * track_updates + (2 * 448 + 32) * matches + 24 * dets_in
-            + 4 * (track_updates + dets_in) + 64 * track_updates + 64 * rows_out + 448 * births)
+    """Algorithmic bytes of one frame step (the SURVEY.md 8(d) terms, with the engine's
+    block-form XYSR state of 7 + 13 fp64 = 160 B per track instead of the dense 7 + 49 =
+    448 B the survey assumed): predict 2*160*T, update (2*160+32)*M, detections in 24*D
+    (float32 x 6; the IoU operands), LAP result 4*(T+D), lifecycle scalars 64*T, output rows
+    64*M_out, birth state write 160*B.  Cost matrix and LAP input count 0 bytes: they
+    never leave the SM."""
+    return (2 * 160 * track_updates + (2 * 160 + 32) * matches + 24 * dets_in
+            + 4 * (track_updates + dets_in) + 64 * track_updates + 64 * rows_out + 160 * births)
 
 
 def run_gpu_arm(args):
@@ -335,9 +336,9 @@ def run_gpu_arm(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "ocsort_step_kernel", "alg_bytes_per_launch": nbytes / K,
+                         "kernel": "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize", "alg_bytes_per_launch": nbytes / K,
                          "avg_launch_ms": ms_dev / K},
-            "gpu_launches": K * (2 if not args.no_e2e else 1),
+            "gpu_launches": 4 * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }

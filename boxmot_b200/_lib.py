@@ -42,6 +42,8 @@ _SIGS = {
                               c_void_p, c_void_p]),
     "bm_xysr_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysr_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "bm_xysrb_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
+    "bm_xysrb_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
 }
 EXPORTS = tuple(_SIGS)
 

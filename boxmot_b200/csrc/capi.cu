@@ -64,8 +64,8 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     pr.asso_func = cfg->asso_func; pr.use_byte = cfg->use_byte ? 1 : 0;
     const size_t S = n_streams, T = track_cap;
     cudaError_t r = cudaSuccess;
-    if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * 56 * T);
-    if (r == cudaSuccess) r = dev_alloc(e, &st.sxP, S * 56 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::XB_N * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.sxP, S * bm::XB_N * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.lastz, S * 4 * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.lastobs, S * 5 * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.vel, S * 2 * T);
@@ -109,8 +109,8 @@ int bm_ocsort_reset(void* handle, void* stream) {
     BM_CUDA(cudaMemsetAsync(st.n_updates, 0, S * sizeof(unsigned long long), s));
     BM_CUDA(cudaMemsetAsync(st.order, 0, S * T * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::OI_COUNT * T * sizeof(int), s));
-    BM_CUDA(cudaMemsetAsync(st.xP, 0, S * 56 * T * sizeof(double), s));
-    BM_CUDA(cudaMemsetAsync(st.sxP, 0, S * 56 * T * sizeof(double), s));
+    BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::XB_N * T * sizeof(double), s));
+    BM_CUDA(cudaMemsetAsync(st.sxP, 0, S * bm::XB_N * T * sizeof(double), s));
     return 0;
 }
 
@@ -175,9 +175,9 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const bm::OcsState& st = e->st;
     const size_t T = st.Tcap;
-    std::vector<double> xp(56 * T);
+    std::vector<double> xp(bm::XB_N * T);
     std::vector<int> order(T), ints(bm::OI_COUNT * T), hdr(bm::OH_COUNT);
-    BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * 56 * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * bm::XB_N * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(order.data(), st.order + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::OI_COUNT * T, ints.size() * 4,
                             cudaMemcpyDeviceToHost, s));
@@ -189,7 +189,11 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
     for (int p = 0; p < n; p++) {
         const int slot = order[p];
         if (h_x) for (int c = 0; c < 7; c++) h_x[p * 7 + c] = xp[c * T + slot];
-        if (h_P) for (int c = 0; c < 49; c++) h_P[p * 49 + c] = xp[(7 + c) * T + slot];
+        if (h_P) {
+            double pb[13];
+            for (int c = 0; c < 13; c++) pb[c] = xp[(7 + c) * T + slot];
+            bm::xysrb_expand(pb, h_P + (size_t)p * 49);
+        }
         if (h_ids) h_ids[p] = ints[bm::OI_ID * T + slot];
     }
     return 0;

@@ -218,4 +218,95 @@ __device__ inline void xysr_oru_replay(double* x, double* P, const double* z1, c
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Block form used by the engine.  With F = I + shift, H = [I4 0] and DIAGONAL Q, R, P0 the
+// covariance only ever couples (x,vx), (y,vy), (s,vs); r stands alone.  Every entry outside
+// those blocks is an exact zero in the reference's own arithmetic (a product with an exact
+// zero factor), and adding an exact zero never changes a sum, so evaluating only the
+// non-zero terms IN THE SAME ORDER is bit-identical to the dense 7x7 code above (checked
+// on the GPU by tests/test_gpu_units.py::test_xysr_block_form_is_bit_identical).  State per
+// track: x[7] and Pb[13] = {P[b][b], P[b][b+4], P[b+4][b], P[b+4][b+4]} for b = 0,1,2, then
+// P[3][3]: 20 doubles instead of 56, ~60 flops per update instead of ~3000.
+constexpr int XB_N = 20;   // doubles of Kalman state per track (x[7] + Pb[13])
+
+__device__ __forceinline__ void xysrb_init(double* x, double* Pb, const double* z) {
+#pragma unroll
+    for (int i = 0; i < 7; i++) x[i] = i < 4 ? z[i] : 0.0;
+#pragma unroll
+    for (int b = 0; b < 3; b++) { Pb[4 * b] = 10.0; Pb[4 * b + 1] = 0.0; Pb[4 * b + 2] = 0.0; Pb[4 * b + 3] = 10000.0; }
+    Pb[12] = 10.0;
+}
+
+__device__ __forceinline__ void xysrb_predict(double* x, double* Pb, const XysrConst& kc) {
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+        x[b] = x[b] + x[b + 4];
+        const double a = Pb[4 * b], bb = Pb[4 * b + 1], c = Pb[4 * b + 2], d = Pb[4 * b + 3];
+        const double a1 = a + c, b1 = bb + d;
+        Pb[4 * b] = (a1 + b1) + 1.0;
+        Pb[4 * b + 1] = b1;
+        Pb[4 * b + 2] = c + d;
+        Pb[4 * b + 3] = d + (b < 2 ? kc.q_xy : kc.q_s);
+    }
+    Pb[12] = Pb[12] + 1.0;
+}
+
+__device__ __forceinline__ void xysrb_update(double* x, double* Pb, const double* z) {
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+        const double r = b < 2 ? 1.0 : 10.0;
+        const double a = Pb[4 * b], bb = Pb[4 * b + 1], c = Pb[4 * b + 2], d = Pb[4 * b + 3];
+        const double y = z[b] - x[b];
+        const double si = 1.0 / (a + r);
+        const double Kp = a * si, Kq = c * si;
+        x[b] = x[b] + Kp * y;
+        x[b + 4] = x[b + 4] + Kq * y;
+        const double Ap = 1.0 - Kp, Aq = 0.0 - Kq;
+        const double APpp = Ap * a, APpq = Ap * bb, APqp = Aq * a + c, APqq = Aq * bb + d;
+        Pb[4 * b] = APpp * Ap + (Kp * r) * Kp;
+        Pb[4 * b + 1] = (APpp * Aq + APpq) + (Kp * r) * Kq;
+        Pb[4 * b + 2] = APqp * Ap + (Kq * r) * Kp;
+        Pb[4 * b + 3] = (APqp * Aq + APqq) + (Kq * r) * Kq;
+    }
+    const double P33 = Pb[12];
+    const double y = z[3] - x[3];
+    const double si = 1.0 / (P33 + 10.0);
+    const double K = P33 * si;
+    x[3] = x[3] + K * y;
+    const double A = 1.0 - K;
+    Pb[12] = (A * P33) * A + (K * 10.0) * K;
+}
+
+// ORU in block form (same schedule as xysr_oru_replay).
+__device__ inline void xysrb_oru_replay(double* x, double* Pb, const double* z1, const double* z2,
+                                        int gap, const XysrConst& kc) {
+    const double x1 = z1[0], y1 = z1[1];
+    const double w1 = sqrt(z1[2] * z1[3]), h1 = sqrt(z1[2] / z1[3]);
+    const double x2 = z2[0], y2 = z2[1];
+    const double w2 = sqrt(z2[2] * z2[3]), h2 = sqrt(z2[2] / z2[3]);
+    const double g = (double)gap;
+    const double dx = (x2 - x1) / g, dy = (y2 - y1) / g;
+    const double dw = (w2 - w1) / g, dh = (h2 - h1) / g;
+    for (int i = 0; i < gap; i++) {
+        const double f = (double)(i + 1);
+        const double xx = x1 + f * dx, yy = y1 + f * dy;
+        const double ww = w1 + f * dw, hh = h1 + f * dh;
+        double zi[4] = {xx, yy, ww * hh, ww / hh};
+        xysrb_update(x, Pb, zi);
+        if (i != gap - 1) xysrb_predict(x, Pb, kc);
+    }
+}
+
+// expand the block form to the dense row-major 7x7 (debug / unit ABI)
+__host__ __device__ inline void xysrb_expand(const double* Pb, double* P) {
+    for (int i = 0; i < 49; i++) P[i] = 0.0;
+    for (int b = 0; b < 3; b++) {
+        P[b * 7 + b] = Pb[4 * b];
+        P[b * 7 + b + 4] = Pb[4 * b + 1];
+        P[(b + 4) * 7 + b] = Pb[4 * b + 2];
+        P[(b + 4) * 7 + b + 4] = Pb[4 * b + 3];
+    }
+    P[3 * 7 + 3] = Pb[12];
+}
+
 }  // namespace bm

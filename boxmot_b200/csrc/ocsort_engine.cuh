@@ -30,8 +30,8 @@ struct OcsState {
     int S, Tcap, Dcap, R;
     size_t scratch_elems;          // doubles of global cost scratch per stream
     int smem_cost_elems;           // doubles of shared-memory cost region per CTA
-    double* xP;                    // [S][56][Tcap]   x(7) then P(49) row-major
-    double* sxP;                   // [S][56][Tcap]   state frozen at the first miss (ORU)
+    double* xP;                    // [S][20][Tcap]   x(7) then the 13 non-zero covariance entries (kf_xysr.cuh block form)
+    double* sxP;                   // [S][20][Tcap]   state frozen at the first miss (ORU)
     double* lastz;                 // [S][4][Tcap]    last real measurement (xc,yc,s,r)
     double* lastobs;               // [S][5][Tcap]    last observation x1,y1,x2,y2,conf (-1 = none)
     double* vel;                   // [S][2][Tcap]    (dy, dx) unit direction
@@ -54,8 +54,8 @@ struct OcsView {   // per-stream base pointers
     int Tcap, R;
     __device__ OcsView(const OcsState& st, int s) : Tcap(st.Tcap), R(st.R) {
         const size_t T = st.Tcap;
-        xP = st.xP + (size_t)s * 56 * T;
-        sxP = st.sxP + (size_t)s * 56 * T;
+        xP = st.xP + (size_t)s * XB_N * T;
+        sxP = st.sxP + (size_t)s * XB_N * T;
         lastz = st.lastz + (size_t)s * 4 * T;
         lastobs = st.lastobs + (size_t)s * 5 * T;
         vel = st.vel + (size_t)s * 2 * T;
@@ -69,17 +69,17 @@ struct OcsView {   // per-stream base pointers
     __device__ __forceinline__ int& I(int f, int slot) const { return ints[f * Tcap + slot]; }
 };
 
-__device__ __forceinline__ void load_xP(const double* base, int Tcap, int slot, double* x, double* P) {
+__device__ __forceinline__ void load_xP(const double* base, int Tcap, int slot, double* x, double* Pb) {
 #pragma unroll
     for (int c = 0; c < 7; c++) x[c] = base[c * Tcap + slot];
 #pragma unroll
-    for (int c = 0; c < 49; c++) P[c] = base[(7 + c) * Tcap + slot];
+    for (int c = 0; c < 13; c++) Pb[c] = base[(7 + c) * Tcap + slot];
 }
-__device__ __forceinline__ void store_xP(double* base, int Tcap, int slot, const double* x, const double* P) {
+__device__ __forceinline__ void store_xP(double* base, int Tcap, int slot, const double* x, const double* Pb) {
 #pragma unroll
     for (int c = 0; c < 7; c++) base[c * Tcap + slot] = x[c];
 #pragma unroll
-    for (int c = 0; c < 49; c++) base[(7 + c) * Tcap + slot] = P[c];
+    for (int c = 0; c < 13; c++) base[(7 + c) * Tcap + slot] = Pb[c];
 }
 
 // Observation `delta_t` steps back (ocsort.py:17-28 / :146-152): the stored box of age
@@ -156,18 +156,18 @@ __device__ inline void ocs_track_update(const OcsView& v, int slot, const double
 
     double z[4];
     xyxy_to_z(det, z);
-    double x[7], P[49];
+    double x[7], P[13];
     int flags = v.I(OI_FLAGS, slot);
     if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
         load_xP(v.sxP, T, slot, x, P);
         double z1[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) z1[c] = v.lastz[c * T + slot];
-        xysr_oru_replay(x, P, z1, z, v.I(OI_NNONE, slot) + 1, kc);
+        xysrb_oru_replay(x, P, z1, z, v.I(OI_NNONE, slot) + 1, kc);
     } else {
         load_xP(v.xP, T, slot, x, P);
     }
-    xysr_update(x, P, z);
+    xysrb_update(x, P, z);
     store_xP(v.xP, T, slot, x, P);
 #pragma unroll
     for (int c = 0; c < 4; c++) v.lastz[c * T + slot] = z[c];
@@ -180,7 +180,7 @@ __device__ inline void ocs_track_miss(const OcsView& v, int slot) {
     const int T = v.Tcap;
     int flags = v.I(OI_FLAGS, slot);
     if (flags & OF_OBSERVED) {
-        for (int c = 0; c < 56; c++) v.sxP[c * T + slot] = v.xP[c * T + slot];
+        for (int c = 0; c < XB_N; c++) v.sxP[c * T + slot] = v.xP[c * T + slot];
         flags |= OF_SAVED;
     }
     v.I(OI_FLAGS, slot) = flags & ~OF_OBSERVED;
@@ -191,9 +191,9 @@ __device__ inline void ocs_track_miss(const OcsView& v, int slot) {
 __device__ inline void ocs_track_init(const OcsView& v, int slot, const double* det, double cls,
                                       int det_ind, int id) {
     const int T = v.Tcap;
-    double z[4], x[7], P[49];
+    double z[4], x[7], P[13];
     xyxy_to_z(det, z);
-    xysr_init(x, P, z);
+    xysrb_init(x, P, z);
     store_xP(v.xP, T, slot, x, P);
     v.I(OI_ID, slot) = id;
     v.I(OI_TSU, slot) = 0;

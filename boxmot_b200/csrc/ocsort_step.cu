@@ -37,10 +37,10 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
     const int Tcap = st.Tcap;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
-    double x[7], P[49];
+    double x[7], P[13];
     load_xP(v.xP, Tcap, slot, x, P);
     if (x[6] + x[2] <= 0) x[6] *= 0.0;
-    xysr_predict(x, P, kc);
+    xysrb_predict(x, P, kc);
     store_xP(v.xP, Tcap, slot, x, P);
     const int age = v.I(OI_AGE, slot) + 1;
     v.I(OI_AGE, slot) = age;

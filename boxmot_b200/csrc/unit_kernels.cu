@@ -91,6 +91,29 @@ __global__ void xysr_update_kernel(double* x, double* P, const double* z, int n)
     for (int c = 0; c < 49; c++) P[(size_t)i * 49 + c] = Ps[c];
 }
 
+__global__ void xysrb_predict_kernel(double* x, double* Pb, int n, XysrConst kc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double xs[7], Ps[13];
+    for (int c = 0; c < 7; c++) xs[c] = x[(size_t)i * 7 + c];
+    for (int c = 0; c < 13; c++) Ps[c] = Pb[(size_t)i * 13 + c];
+    xysrb_predict(xs, Ps, kc);
+    for (int c = 0; c < 7; c++) x[(size_t)i * 7 + c] = xs[c];
+    for (int c = 0; c < 13; c++) Pb[(size_t)i * 13 + c] = Ps[c];
+}
+
+__global__ void xysrb_update_kernel(double* x, double* Pb, const double* z, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double xs[7], Ps[13], zs[4];
+    for (int c = 0; c < 7; c++) xs[c] = x[(size_t)i * 7 + c];
+    for (int c = 0; c < 13; c++) Ps[c] = Pb[(size_t)i * 13 + c];
+    for (int c = 0; c < 4; c++) zs[c] = z[(size_t)i * 4 + c];
+    xysrb_update(xs, Ps, zs);
+    for (int c = 0; c < 7; c++) x[(size_t)i * 7 + c] = xs[c];
+    for (int c = 0; c < 13; c++) Pb[(size_t)i * 13 + c] = Ps[c];
+}
+
 }  // namespace bm
 
 static int unit_fail(const char* what, cudaError_t e) {
@@ -152,6 +175,21 @@ int bm_xysr_update(double* d_x, double* d_P, const double* d_z, int n, void* str
     bm::xysr_update_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_P, d_z, n);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("xysr_update_kernel", e);
+}
+
+int bm_xysrb_predict(double* d_x, double* d_Pb, int n, double q_xy, double q_s, void* stream) {
+    if (n <= 0) return 0;
+    bm::XysrConst kc = {q_xy, q_s};
+    bm::xysrb_predict_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_Pb, n, kc);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("xysrb_predict_kernel", e);
+}
+
+int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* stream) {
+    if (n <= 0) return 0;
+    bm::xysrb_update_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_Pb, d_z, n);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("xysrb_update_kernel", e);
 }
 
 }  // extern "C"

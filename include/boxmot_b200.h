@@ -86,6 +86,13 @@ int bm_iou_matrix(int asso_func, const double* d_a, int na, const double* d_b, i
 int bm_xysr_predict(double* d_x, double* d_P, int n, double q_xy, double q_s, void* stream);
 int bm_xysr_update(double* d_x, double* d_P, const double* d_z, int n, void* stream);
 
+/* The same filter in the engine's block form (csrc/kf_xysr.cuh): d_Pb [N][13] holds, for
+ * b = 0,1,2, P[b][b], P[b][b+4], P[b+4][b], P[b+4][b+4] and then P[3][3] -- the only
+ * entries that are ever non-zero with the OC-SORT constants.  Bit-identical to
+ * bm_xysr_predict / bm_xysr_update on such covariances. */
+int bm_xysrb_predict(double* d_x, double* d_Pb, int n, double q_xy, double q_s, void* stream);
+int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

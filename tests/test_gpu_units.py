@@ -191,3 +191,39 @@ def test_xysr_predict_update_vs_oracle():
         wx, wP = kalman.xysr_update(px[i], pP[i], zs[i], R)
         np.testing.assert_allclose(ux[i], wx, rtol=1e-9, atol=1e-9)
         np.testing.assert_allclose(uP[i], wP, rtol=1e-9, atol=1e-9)
+
+
+def test_xysr_block_form_is_bit_identical():
+    """The engine keeps only the 13 covariance entries that can be non-zero; its predict /
+    update must reproduce the dense 7x7 kernels bit for bit over a long random schedule."""
+    from boxmot_b200 import _lib
+    rng = np.random.default_rng(6)
+    n = 512
+    z0 = np.c_[rng.uniform(100, 1500, (n, 2)), rng.uniform(2000, 40000, n), rng.uniform(0.3, 0.8, n)]
+    x = np.c_[z0, np.zeros((n, 3))]
+    Pb = np.tile(np.array([10.0, 0, 0, 1e4] * 3 + [10.0]), (n, 1))
+    P = np.zeros((n, 7, 7))
+    for b in range(3):
+        P[:, b, b], P[:, b + 4, b + 4] = 10.0, 1e4
+    P[:, 3, 3] = 10.0
+    d_x, d_P = _dev(x), _dev(P.reshape(n, 49))
+    d_xb, d_Pb = _dev(x), _dev(Pb)
+    L = _lib.lib()
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    for step in range(40):
+        _lib.check(L.bm_xysr_predict(p(d_x), p(d_P), n, 0.01, 0.0001, None), "predict")
+        _lib.check(L.bm_xysrb_predict(p(d_xb), p(d_Pb), n, 0.01, 0.0001, None), "predict_b")
+        if step % 3 != 2:
+            z = d_x.cpu().numpy()[:, :4] + rng.normal(0, 2, (n, 4)) * [1, 1, 50, 0.01]
+            d_z = _dev(z)
+            _lib.check(L.bm_xysr_update(p(d_x), p(d_P), p(d_z), n, None), "update")
+            _lib.check(L.bm_xysrb_update(p(d_xb), p(d_Pb), p(d_z), n, None), "update_b")
+        torch.cuda.synchronize()
+        full, blk = d_P.cpu().numpy().reshape(n, 7, 7), d_Pb.cpu().numpy()
+        assert np.array_equal(d_x.cpu().numpy(), d_xb.cpu().numpy()), "step %d x" % step
+        exp = np.zeros_like(full)
+        for b in range(3):
+            exp[:, b, b], exp[:, b, b + 4] = blk[:, 4 * b], blk[:, 4 * b + 1]
+            exp[:, b + 4, b], exp[:, b + 4, b + 4] = blk[:, 4 * b + 2], blk[:, 4 * b + 3]
+        exp[:, 3, 3] = blk[:, 12]
+        assert np.array_equal(full, exp), "step %d P" % step
