@@ -46,6 +46,9 @@ struct OcsState {
     double* abuf;                  // [S][AB_COUNT][Tcap] predicted boxes / OCM operands per list position
     int* upd;                      // [S][2][Dcap] this frame's (slot, detection row) Kalman updates
     int* born;                     // [S][Dcap]    detection rows that start a track, in id order
+    double* rowd;                  // [S][2][Dcap] per cost row: minimum, maximum (written by the cost kernel)
+    int* rowi;                     // [S][3][Dcap] per cost row: argmin column, #IoU hits, last hit column
+    int* colhit;                   // [S][Tcap]    per cost column: #IoU hits (zeroed by the predict kernel)
 };
 
 struct OcsView {   // per-stream base pointers

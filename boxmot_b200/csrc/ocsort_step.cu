@@ -1,13 +1,16 @@
-// OC-SORT frame step: FOUR launches advance every stream of the engine by one frame,
+// OC-SORT frame step: FIVE launches advance every stream of the engine by one frame,
 // with no host synchronisation in between (all lifecycle decisions are made on the device).
 // Mirrors OcSort.update (boxmot/trackers/ocsort/ocsort.py:246-439) and enhanced_associate
 // (boxmot/utils/association.py:377-533 with repairs R1-R3).
 //
 //   K1 ocs_predict_kernel   thread per live track        Kalman predict (ocsort.py:281-288,
 //                           (HBM-streaming, SoA state)   :173-186) + association operands
-//   K2 ocs_assoc_kernel     CTA per stream, low regs     score split (:265-275), IoU + OCM cost,
-//                           cost matrix in smem          permutation fast path or exact LAP,
-//                                                        BYTE (:330-356) and OCR (:358-386) rounds
+//   K2a ocs_cost_kernel     warp per cost-matrix row     score split (:265-275), IoU + OCM velocity
+//                           (fp64-pipe bound)            cost (association.py:427-461) -> L2-resident
+//                                                        matrix + per-row / per-column summaries
+//   K2b ocs_assoc_kernel    CTA per stream, small smem   permutation fast path or exact LAP,
+//                           (latency bound, all CTAs     BYTE (:330-356) and OCR (:358-386) rounds
+//                           co-resident)
 //   K3 ocs_update_kernel    thread per matched track     Kalman update + ORU (:321-324,
 //                           (HBM-streaming)              xysr_kf.py:211-291)
 //   K4 ocs_finalize_kernel  CTA per stream               misses, births, output rows, dead-track
@@ -23,6 +26,7 @@ namespace bm {
 constexpr int K1_NT = 128;
 constexpr int K2_NT = 128;
 constexpr int K3_NT = 64;
+constexpr int KC_NT = 256;   // cost kernel: 8 warps = 8 matrix rows per CTA
 
 // ============================================================================ K1
 __global__ void __launch_bounds__(K1_NT)
@@ -33,8 +37,9 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
     OcsView v(st, s);
     const int nT = v.hdr[OH_NLIST];
     if (p == 0) st.n_updates[s] += (unsigned long long)nT;
-    if (p >= nT) return;
     const int Tcap = st.Tcap;
+    if (p < Tcap) st.colhit[(size_t)s * Tcap + p] = 0;
+    if (p >= nT) return;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
     double x[7], P[13];
@@ -64,8 +69,8 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
 
 // ============================================================================ K2
 struct OcsSmem {
-    double *dbox, *dconf, *sbox, *tbox, *kcx, *kcy, *vy, *vx, *wred, *rmin;
-    int *dind, *sind, *slot_of, *kvalid, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg;
+    double *dbox, *dconf, *sbox, *tbox, *wred, *rmin;
+    int *dind, *sind, *slot_of, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg;
     void* lapw;
     double* cost;
 };
@@ -74,8 +79,8 @@ enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M
 
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
     size_t d = (size_t)Dcap, t = (size_t)Tcap;
-    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + 8 * t + 8;
-    size_t ints = 7 * d + (use_byte ? d : 0) + 5 * t + M_COUNT;
+    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + 4 * t + 8;
+    size_t ints = 7 * d + (use_byte ? d : 0) + 4 * t + M_COUNT;
     size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
     b += (lap_work_bytes((int)(d + t)) + 7) / 8 * 8;
     b += (size_t)cost_elems * 8;
@@ -90,10 +95,6 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.rmin = p; p += Dcap;
     if (use_byte) { m.sbox = p; p += 4 * Dcap; } else m.sbox = nullptr;
     m.tbox = p; p += 4 * Tcap;
-    m.kcx = p; p += Tcap;
-    m.kcy = p; p += Tcap;
-    m.vy = p; p += Tcap;
-    m.vx = p; p += Tcap;
     m.wred = p; p += 8;
     int* q = reinterpret_cast<int*>(p);
     int* q0 = q;
@@ -105,13 +106,12 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.hit_t = q; q += Dcap;
     m.rarg = q; q += Dcap;
     m.slot_of = q; q += Tcap;
-    m.kvalid = q; q += Tcap;
     m.t2d = q; q += Tcap;
     m.um_t = q; q += Tcap;
     m.colcnt = q; q += Tcap;
     m.misc = q; q += M_COUNT;
     // 7*Dcap reserved: one Dcap block is spare so the int area never undercounts
-    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)5 * Tcap + M_COUNT) * 4 + 7) / 8 * 8;
+    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)4 * Tcap + M_COUNT) * 4 + 7) / 8 * 8;
     unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
     m.lapw = r;
     r += (lap_work_bytes(Dcap + Tcap) + 7) / 8 * 8;
@@ -142,6 +142,106 @@ __device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, 
     }
     __syncwarp();
     return k0;
+}
+
+// ============================================================================ K2a
+// First-round cost matrix, one warp per detection row (8 rows per CTA), written det-major
+// to the per-stream scratch (stays in L2 until ocs_assoc_kernel reads the rows it needs).
+// dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
+// precision: BaseTracker.setup_decorator round-trips every ndarray through float32
+// (boxmot/trackers/basetracker.py:122-128).
+__global__ void __launch_bounds__(KC_NT)
+ocs_cost_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
+    extern __shared__ __align__(16) double cs_sm[];      // [AB_COUNT][Tcap] operands by column
+    __shared__ int s_nt;
+    constexpr int ROWS = KC_NT / 32;
+    const int Tcap = st.Tcap, Dcap = st.Dcap;
+    const int chunks = (Dcap + ROWS - 1) / ROWS;
+    const int s = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
+    const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
+    const int d = chunk * ROWS + wid;
+    int nT = st.hdr[(size_t)s * OH_COUNT + OH_NLIST];
+    const int nD_in = min(ndets[s], Dcap);
+    const float* dsrc = dets + (size_t)s * Dcap * 6;
+    // rank of this warp's row among the high-score detections (ocsort.py:268-275)
+    int nh = 0, mydet = -1;
+    for (int base = 0; base < nD_in; base += 32) {
+        const int i = base + lane;
+        const bool hi = i < nD_in && (double)dsrc[i * 6 + 4] > pr.det_thresh;
+        const unsigned bh = __ballot_sync(BM_FULL, hi);
+        const int c = __popc(bh);
+        if (d >= nh && d < nh + c) mydet = base + __fns(bh, 0, d - nh + 1);
+        nh += c;
+    }
+    const int nD = nh;
+    if (chunk * ROWS >= nD || nT == 0) return;            // uniform over the CTA
+    const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
+    int bad = 0;
+    for (int e = tid; e < AB_COUNT * nT; e += KC_NT) {
+        const int f = e / nT, p = e - f * nT;
+        const double val = ab[f * Tcap + p];
+        cs_sm[f * Tcap + p] = val;
+        if (f < 4 && val != val) bad = 1;
+    }
+    if (__syncthreads_or(bad)) {   // NaN prediction: drop the column, as ocs_assoc_kernel does
+        if (tid == 0) {
+            int k = 0;
+            for (int p = 0; p < nT; p++) {
+                bool nan = false;
+                for (int f = 0; f < 4; f++) nan |= cs_sm[f * Tcap + p] != cs_sm[f * Tcap + p];
+                if (nan) continue;
+                for (int f = 0; f < AB_COUNT; f++) cs_sm[f * Tcap + k] = cs_sm[f * Tcap + p];
+                k++;
+            }
+            s_nt = k;
+        }
+        __syncthreads();
+        nT = s_nt;
+        if (nT == 0) return;
+    }
+    if (d >= nD) return;
+    const double* tb = cs_sm;
+    const Box a = {(double)dsrc[mydet * 6 + 0], (double)dsrc[mydet * 6 + 1], (double)dsrc[mydet * 6 + 2],
+                   (double)dsrc[mydet * 6 + 3]};
+    const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
+    double* cost = st.scratch + (size_t)s * st.scratch_elems + (size_t)d * nT;
+    double rm = CUDART_INF, cmx = -CUDART_INF;
+    int ra = 0x7fffffff, nhit = 0, lasthit = -1;
+    for (int t = lane; t < nT; t += 32) {
+        const Box b = {tb[AB_X1 * Tcap + t], tb[AB_Y1 * Tcap + t], tb[AB_X2 * Tcap + t], tb[AB_Y2 * Tcap + t]};
+        const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
+        const double vx = tb[AB_VX * Tcap + t], vy = tb[AB_VY * Tcap + t];
+        double motion = 0.0;
+        // A track that was never observed (valid = 0) or has no velocity yet
+        // (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly) contributes exactly 0.
+        if (tb[AB_KVALID * Tcap + t] != 0.0 && (vx != 0.0 || vy != 0.0)) {
+            // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
+            double dx = cxd - tb[AB_KCX * Tcap + t], dy = cyd - tb[AB_KCY * Tcap + t];
+            const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
+            dx = dx / norm; dy = dy / norm;
+            double cs = vx * dx + vy * dy;
+            cs = fmin(1.0, fmax(-1.0, cs));
+            const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
+            motion = (1.0 * ang) * pr.inertia;
+        }
+        const double cc = -(iou + motion);
+        cost[t] = cc;
+        cmx = fmax(cmx, cc);
+        if (cc < rm) { rm = cc; ra = t; }
+        if (iou > pr.iou_thr) { nhit++; lasthit = t; atomicAdd(&st.colhit[(size_t)s * Tcap + t], 1); }
+    }
+    warp_argmin(rm, ra);
+    for (int o = 16; o > 0; o >>= 1) {
+        cmx = fmax(cmx, shfl_xor_d(cmx, o));
+        nhit += __shfl_xor_sync(BM_FULL, nhit, o);
+        lasthit = max(lasthit, __shfl_xor_sync(BM_FULL, lasthit, o));
+    }
+    if (lane == 0) {
+        double* rd = st.rowd + (size_t)s * 2 * Dcap;
+        int* ri = st.rowi + (size_t)s * 3 * Dcap;
+        rd[d] = rm; rd[Dcap + d] = cmx;
+        ri[d] = ra; ri[Dcap + d] = nhit; ri[2 * Dcap + d] = lasthit;
+    }
 }
 
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
@@ -270,33 +370,26 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         }
         if (lane == 0) { sm.misc[M_ND] = nh; sm.misc[M_NS] = ns; }
     }
-    // ---- association operands of the predicted tracks (written by K1)
+    // ---- predicted boxes of the live tracks (written by K1)
     int nT = v.hdr[OH_NLIST];
     const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
     for (int p = tid; p < nT; p += K2_NT) {
         double b[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) { b[c] = ab[(AB_X1 + c) * Tcap + p]; sm.tbox[c * Tcap + p] = b[c]; }
-        sm.vy[p] = ab[AB_VY * Tcap + p];
-        sm.vx[p] = ab[AB_VX * Tcap + p];
-        sm.kcx[p] = ab[AB_KCX * Tcap + p];
-        sm.kcy[p] = ab[AB_KCY * Tcap + p];
-        sm.kvalid[p] = ab[AB_KVALID * Tcap + p] != 0.0 ? 1 : 0;
         sm.slot_of[p] = v.order[p];
         const bool bad = b[0] != b[0] || b[1] != b[1] || b[2] != b[2] || b[3] != b[3];
         sm.t2d[p] = bad ? -2 : -1;
-        sm.colcnt[p] = 0;
         if (bad) sm.misc[M_ANYBAD] = 1;
     }
     __syncthreads();
-    if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288)
-        if (tid == 0) {
+    if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288);
+        if (tid == 0) {        // the cost kernel compacted its columns the same way
             int k = 0;
             for (int p = 0; p < nT; p++) {
                 if (sm.t2d[p] == -2) continue;
                 for (int c = 0; c < 4; c++) sm.tbox[c * Tcap + k] = sm.tbox[c * Tcap + p];
-                sm.vy[k] = sm.vy[p]; sm.vx[k] = sm.vx[p]; sm.kcx[k] = sm.kcx[p]; sm.kcy[k] = sm.kcy[p];
-                sm.kvalid[k] = sm.kvalid[p]; sm.slot_of[k] = sm.slot_of[p]; sm.t2d[k] = -1;
+                sm.slot_of[k] = sm.slot_of[p]; sm.t2d[k] = -1;
                 v.order[k] = sm.slot_of[k];
                 k++;
             }
@@ -307,58 +400,31 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         nT = sm.misc[M_NT];
     }
     const int nD = sm.misc[M_ND], nS = sm.misc[M_NS];
-    for (int d = tid; d < nD; d += K2_NT) { sm.d2t[d] = -1; sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
-    __syncthreads();
-
-    // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
-    // (association.py:427-461); permutation fast path (:501-503) or exact LAP (:505-507)
+    // ---- first round: cost[d][t] = -(iou + OCM) was written det-major to the L2-resident
+    // scratch by ocs_cost_kernel together with the row / column summaries;
+    // permutation fast path (association.py:501-503) or exact LAP (:505-507)
     const size_t need = (size_t)nD * nT;
-    double* cost = (need <= (size_t)st.smem_cost_elems) ? sm.cost : st.scratch + (size_t)s * st.scratch_elems;
-    bool assoc_ok = true;
-    if (need > (size_t)st.smem_cost_elems && need > st.scratch_elems) {
-        if (tid == 0) atomicOr(&v.hdr[OH_ERR], BM_ERR_SCRATCH);
-        assoc_ok = false;
-    }
-    if (nD > 0 && nT > 0 && assoc_ok) {
+    double* cost = st.scratch + (size_t)s * st.scratch_elems;
+    const bool assoc_ok = true;
+    {
+        const double* rd = st.rowd + (size_t)s * 2 * Dcap;
+        const int* ri = st.rowi + (size_t)s * 3 * Dcap;
+        const bool have = nD > 0 && nT > 0;
         double cmx = -CUDART_INF;
-        for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
-            const Box a = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d], sm.dbox[3 * Dcap + d]};
-            const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
-            double rm = CUDART_INF;
-            int ra = 0x7fffffff, nhit = 0, lasthit = -1;
-            for (int t = lane; t < nT; t += 32) {
-                const Box b = {sm.tbox[0 * Tcap + t], sm.tbox[1 * Tcap + t], sm.tbox[2 * Tcap + t], sm.tbox[3 * Tcap + t]};
-                const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
-                const double vx = sm.vx[t], vy = sm.vy[t];
-                double motion = 0.0;
-                // A track that was never observed (valid = 0) or has no velocity yet
-                // (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly) contributes exactly 0.
-                if (sm.kvalid[t] && (vx != 0.0 || vy != 0.0)) {
-                    // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
-                    double dx = cxd - sm.kcx[t], dy = cyd - sm.kcy[t];
-                    const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
-                    dx = dx / norm; dy = dy / norm;
-                    double cs = vx * dx + vy * dy;
-                    cs = fmin(1.0, fmax(-1.0, cs));
-                    const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
-                    motion = (1.0 * ang) * pr.inertia;
-                }
-                const double cc = -(iou + motion);
-                cost[(size_t)d * nT + t] = cc;
-                cmx = fmax(cmx, cc);
-                if (cc < rm) { rm = cc; ra = t; }
-                if (iou > pr.iou_thr) { nhit++; lasthit = t; atomicAdd(&sm.colcnt[t], 1); }
-            }
-            warp_argmin(rm, ra);
-            for (int o = 16; o > 0; o >>= 1) {
-                nhit += __shfl_xor_sync(BM_FULL, nhit, o);
-                lasthit = max(lasthit, __shfl_xor_sync(BM_FULL, lasthit, o));
-            }
-            if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
+        for (int d = tid; d < nD; d += K2_NT) {
+            sm.d2t[d] = -1;
+            sm.rmin[d] = have ? rd[d] : 0.0;
+            if (have) cmx = fmax(cmx, rd[Dcap + d]);
+            sm.rarg[d] = have ? ri[d] : -1;
+            sm.rowcnt[d] = have ? ri[Dcap + d] : 0;
+            sm.hit_t[d] = have ? ri[2 * Dcap + d] : -1;
         }
+        for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = nD > 0 ? st.colhit[(size_t)s * Tcap + t] : 0;
         for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
         if (lane == 0) sm.wred[wid] = cmx;
-        __syncthreads();
+    }
+    __syncthreads();
+    if (nD > 0 && nT > 0 && assoc_ok) {
         if (wid == 0) {
             int rmax = 0, cmax_ = 0;
             for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
@@ -661,6 +727,8 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
                                double* out, int* nout, cudaStream_t stream) {
     const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
     ocs_predict_kernel<<<st.S * c1, K1_NT, 0, stream>>>(st, pr);
+    const int cc = (st.Dcap + KC_NT / 32 - 1) / (KC_NT / 32);
+    ocs_cost_kernel<<<st.S * cc, KC_NT, (size_t)AB_COUNT * st.Tcap * sizeof(double), stream>>>(st, pr, dets, ndets);
     ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets, ndets);
     ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
     const int nt4 = (st.Tcap + 31) / 32 * 32;
