@@ -336,9 +336,9 @@ def run_gpu_arm(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "frame step = ocs_predict + ocs_cost + ocs_assoc + ocs_update + ocs_finalize", "alg_bytes_per_launch": nbytes / K,
+                         "kernel": "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize", "alg_bytes_per_launch": nbytes / K,
                          "avg_launch_ms": ms_dev / K},
-            "gpu_launches": 5 * K * (2 if not args.no_e2e else 1),
+            "gpu_launches": 4 * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }

@@ -58,12 +58,20 @@ __device__ __forceinline__ void warp_argmin(double& s, int& j) {
     }
 }
 
-// Solve with one warp.  c: nr x nc row-major (leading dimension ld), any address space.
+// Cost accessor over a stored row-major matrix.
+struct DenseCost {
+    const double* c; int ld;
+    __device__ __forceinline__ double operator()(int i, int j) const { return c[(size_t)i * ld + j]; }
+};
+
+// Solve with one warp.  cost(i, j): entry accessor (a stored matrix, or a functor that
+// evaluates the entry on demand -- the solver only touches the rows it sweeps).
 // rowmin/rowarg: optional per-row minimum and its column (computed by the caller while
 // the costs were generated); pass nullptr to have the warp compute them.
 // On return w.x[i] = column of row i or -1, w.y[j] = row of column j or -1.
 // Returns 0, or 1 when a guard tripped (NaN costs).
-static __device__ int rect_solve_warp(const double* c, int ld, int nr, int nc, double null_cost,
+template <typename CostFn>
+static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double null_cost,
                                       RectWork& w, const double* rowmin, const int* rowarg) {
     const int lane = lane_id();
     for (int j = lane; j < nc; j += 32) { w.v[j] = 0.0; w.y[j] = 0x7fffffff; }
@@ -82,7 +90,7 @@ static __device__ int rect_solve_warp(const double* c, int ld, int nr, int nc, d
             double m = CUDART_INF;
             int a = 0x7fffffff;
             for (int j = lane; j < nc; j += 32) {
-                const double cc = c[(size_t)i * ld + j];
+                const double cc = cost(i, j);
                 if (cc < m) { m = cc; a = j; }
             }
             warp_argmin(m, a);
@@ -124,11 +132,10 @@ static __device__ int rect_solve_warp(const double* c, int ld, int nr, int nc, d
             if (cn < best_null) { best_null = cn; null_row = i; }
             double lowest = CUDART_INF;
             int jl = 0x7fffffff;
-            const double* ci = c + (size_t)i * ld;
             for (int j = lane; j < nc; j += 32) {
                 double s = w.spc[j];
                 if (s == -CUDART_INF) continue;          // already scanned
-                const double r = minval + ((ci[j] - ui) - w.v[j]);
+                const double r = minval + ((cost(i, j) - ui) - w.v[j]);
                 if (r < s) { s = r; w.spc[j] = r; w.path[j] = i; }
                 if (s < lowest) { lowest = s; jl = j; }
             }

@@ -26,7 +26,6 @@ namespace bm {
 constexpr int K1_NT = 128;
 constexpr int K2_NT = 128;
 constexpr int K3_NT = 64;
-constexpr int KC_NT = 256;   // cost kernel: 8 warps = 8 matrix rows per CTA
 
 // ============================================================================ K1
 __global__ void __launch_bounds__(K1_NT)
@@ -38,7 +37,6 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
     const int nT = v.hdr[OH_NLIST];
     if (p == 0) st.n_updates[s] += (unsigned long long)nT;
     const int Tcap = st.Tcap;
-    if (p < Tcap) st.colhit[(size_t)s * Tcap + p] = 0;
     if (p >= nT) return;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
@@ -70,7 +68,7 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
 // ============================================================================ K2
 struct OcsSmem {
     double *dbox, *dconf, *sbox, *tbox, *wred, *rmin;
-    int *dind, *sind, *slot_of, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg;
+    int *dind, *sind, *slot_of, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg, *cand;
     void* lapw;
     double* cost;
 };
@@ -79,8 +77,8 @@ enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M
 
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
     size_t d = (size_t)Dcap, t = (size_t)Tcap;
-    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + 4 * t + 8;
-    size_t ints = 7 * d + (use_byte ? d : 0) + 4 * t + M_COUNT;
+    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + AB_COUNT * t + 8;
+    size_t ints = 7 * d + (use_byte ? d : 0) + 4 * t + M_COUNT + 64 * (K2_NT / 32);
     size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
     b += (lap_work_bytes((int)(d + t)) + 7) / 8 * 8;
     b += (size_t)cost_elems * 8;
@@ -94,7 +92,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.dconf = p; p += Dcap;
     m.rmin = p; p += Dcap;
     if (use_byte) { m.sbox = p; p += 4 * Dcap; } else m.sbox = nullptr;
-    m.tbox = p; p += 4 * Tcap;
+    m.tbox = p; p += AB_COUNT * Tcap;     // all association operands; rows 0-3 are the box
     m.wred = p; p += 8;
     int* q = reinterpret_cast<int*>(p);
     int* q0 = q;
@@ -110,8 +108,9 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.um_t = q; q += Tcap;
     m.colcnt = q; q += Tcap;
     m.misc = q; q += M_COUNT;
+    m.cand = q; q += 64 * (K2_NT / 32);
     // 7*Dcap reserved: one Dcap block is spare so the int area never undercounts
-    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)4 * Tcap + M_COUNT) * 4 + 7) / 8 * 8;
+    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)4 * Tcap + M_COUNT + 64 * (K2_NT / 32)) * 4 + 7) / 8 * 8;
     unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
     m.lapw = r;
     r += (lap_work_bytes(Dcap + Tcap) + 7) / 8 * 8;
@@ -144,104 +143,134 @@ __device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, 
     return k0;
 }
 
-// ============================================================================ K2a
-// First-round cost matrix, one warp per detection row (8 rows per CTA), written det-major
-// to the per-stream scratch (stays in L2 until ocs_assoc_kernel reads the rows it needs).
-// dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
-// precision: BaseTracker.setup_decorator round-trips every ndarray through float32
-// (boxmot/trackers/basetracker.py:122-128).
-__global__ void __launch_bounds__(KC_NT)
-ocs_cost_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
-    extern __shared__ __align__(16) double cs_sm[];      // [AB_COUNT][Tcap] operands by column
-    __shared__ int s_nt;
-    constexpr int ROWS = KC_NT / 32;
-    const int Tcap = st.Tcap, Dcap = st.Dcap;
-    const int chunks = (Dcap + ROWS - 1) / ROWS;
-    const int s = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
-    const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
-    const int d = chunk * ROWS + wid;
-    int nT = st.hdr[(size_t)s * OH_COUNT + OH_NLIST];
-    const int nD_in = min(ndets[s], Dcap);
-    const float* dsrc = dets + (size_t)s * Dcap * 6;
-    // rank of this warp's row among the high-score detections (ocsort.py:268-275)
-    int nh = 0, mydet = -1;
-    for (int base = 0; base < nD_in; base += 32) {
-        const int i = base + lane;
-        const bool hi = i < nD_in && (double)dsrc[i * 6 + 4] > pr.det_thresh;
-        const unsigned bh = __ballot_sync(BM_FULL, hi);
-        const int c = __popc(bh);
-        if (d >= nh && d < nh + c) mydet = base + __fns(bh, 0, d - nh + 1);
-        nh += c;
-    }
-    const int nD = nh;
-    if (chunk * ROWS >= nD || nT == 0) return;            // uniform over the CTA
-    const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
-    int bad = 0;
-    for (int e = tid; e < AB_COUNT * nT; e += KC_NT) {
-        const int f = e / nT, p = e - f * nT;
-        const double val = ab[f * Tcap + p];
-        cs_sm[f * Tcap + p] = val;
-        if (f < 4 && val != val) bad = 1;
-    }
-    if (__syncthreads_or(bad)) {   // NaN prediction: drop the column, as ocs_assoc_kernel does
-        if (tid == 0) {
-            int k = 0;
-            for (int p = 0; p < nT; p++) {
-                bool nan = false;
-                for (int f = 0; f < 4; f++) nan |= cs_sm[f * Tcap + p] != cs_sm[f * Tcap + p];
-                if (nan) continue;
-                for (int f = 0; f < AB_COUNT; f++) cs_sm[f * Tcap + k] = cs_sm[f * Tcap + p];
-                k++;
-            }
-            s_nt = k;
-        }
-        __syncthreads();
-        nT = s_nt;
-        if (nT == 0) return;
-    }
-    if (d >= nD) return;
-    const double* tb = cs_sm;
-    const Box a = {(double)dsrc[mydet * 6 + 0], (double)dsrc[mydet * 6 + 1], (double)dsrc[mydet * 6 + 2],
-                   (double)dsrc[mydet * 6 + 3]};
-    const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
-    double* cost = st.scratch + (size_t)s * st.scratch_elems + (size_t)d * nT;
-    double rm = CUDART_INF, cmx = -CUDART_INF;
-    int ra = 0x7fffffff, nhit = 0, lasthit = -1;
-    for (int t = lane; t < nT; t += 32) {
-        const Box b = {tb[AB_X1 * Tcap + t], tb[AB_Y1 * Tcap + t], tb[AB_X2 * Tcap + t], tb[AB_Y2 * Tcap + t]};
-        const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
+// ---------------------------------------------------------------------------------------
+// First-round cost, evaluated ON DEMAND.  cost(d, t) = -(iou + OCM) exactly as
+// enhanced_associate builds it (association.py:427-461), det-major.  The assignment solver
+// needs (a) every row's minimum and (b) the full rows it sweeps while augmenting -- on
+// tracking data that is ~2 rows per frame -- so the matrix is never materialised.
+struct OcmCost {
+    const double* dbox; int Dcap;      // high-score detections [4][Dcap] (shared memory)
+    const double* tb; int Tcap;        // operands per track column [AB_COUNT][Tcap] (shared memory)
+    int func; double diag, inertia;
+
+    // velocity-direction term; exactly 0 for a track that was never observed (valid = 0)
+    // or has no velocity yet (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly)
+    __device__ __forceinline__ double motion(double cxd, double cyd, int t) const {
         const double vx = tb[AB_VX * Tcap + t], vy = tb[AB_VY * Tcap + t];
-        double motion = 0.0;
-        // A track that was never observed (valid = 0) or has no velocity yet
-        // (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly) contributes exactly 0.
-        if (tb[AB_KVALID * Tcap + t] != 0.0 && (vx != 0.0 || vy != 0.0)) {
-            // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
-            double dx = cxd - tb[AB_KCX * Tcap + t], dy = cyd - tb[AB_KCY * Tcap + t];
-            const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
-            dx = dx / norm; dy = dy / norm;
-            double cs = vx * dx + vy * dy;
-            cs = fmin(1.0, fmax(-1.0, cs));
-            const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
-            motion = (1.0 * ang) * pr.inertia;
-        }
-        const double cc = -(iou + motion);
-        cost[t] = cc;
-        cmx = fmax(cmx, cc);
-        if (cc < rm) { rm = cc; ra = t; }
-        if (iou > pr.iou_thr) { nhit++; lasthit = t; atomicAdd(&st.colhit[(size_t)s * Tcap + t], 1); }
+        if (tb[AB_KVALID * Tcap + t] == 0.0 || (vx == 0.0 && vy == 0.0)) return 0.0;
+        // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
+        double dx = cxd - tb[AB_KCX * Tcap + t], dy = cyd - tb[AB_KCY * Tcap + t];
+        const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
+        dx = dx / norm; dy = dy / norm;
+        double cs = vx * dx + vy * dy;
+        cs = fmin(1.0, fmax(-1.0, cs));
+        const double ang = (CUDART_PI / 2.0 - fabs(acos_pinned(cs))) / CUDART_PI;
+        return (1.0 * ang) * inertia;
     }
+    __device__ __forceinline__ Box det(int d) const {
+        return Box{dbox[0 * Dcap + d], dbox[1 * Dcap + d], dbox[2 * Dcap + d], dbox[3 * Dcap + d]};
+    }
+    __device__ __forceinline__ Box trk(int t) const {
+        return Box{tb[AB_X1 * Tcap + t], tb[AB_Y1 * Tcap + t], tb[AB_X2 * Tcap + t], tb[AB_Y2 * Tcap + t]};
+    }
+    __device__ __forceinline__ double entry(const Box& a, double cxd, double cyd, int t, double* iou_out) const {
+        const double iou = asso_pair(func, a, trk(t), diag);
+        *iou_out = iou;
+        return -(iou + motion(cxd, cyd, t));
+    }
+    __device__ __forceinline__ double operator()(int d, int t) const {
+        const Box a = det(d);
+        double iou;
+        return entry(a, (a.x1 + a.x2) / 2.0, (a.y1 + a.y2) / 2.0, t, &iou);
+    }
+};
+
+// fp32 screening value of the OCM cosine (monotone proxy of the motion term); only used
+// to pick which zero-IoU entries of a row are evaluated exactly.
+__device__ __forceinline__ float ocm_cos32(const OcmCost& c, double cxd, double cyd, int t) {
+    const float dx = (float)(cxd - c.tb[AB_KCX * c.Tcap + t]), dy = (float)(cyd - c.tb[AB_KCY * c.Tcap + t]);
+    const float vx = (float)c.tb[AB_VX * c.Tcap + t], vy = (float)c.tb[AB_VY * c.Tcap + t];
+    return (vx * dx + vy * dy) / (sqrtf(dx * dx + dy * dy) + 1e-6f);
+}
+constexpr float OCM_BAND = 5e-5f;   // >> fp32 error of ocm_cos32 (~1e-6), << spacing of candidates
+
+// Row summaries for the solver and the permutation fast path, one warp per row:
+// exact minimum / argmin of the row, number of IoU hits (> thr) and the last hit column.
+// With asso_func = iou an entry whose boxes do not overlap is exactly -(0 + motion), and
+// motion is a monotone function of the OCM cosine, so only (i) overlapping entries and
+// (ii) the zero-IoU entries whose fp32 cosine is within OCM_BAND of the row's best are
+// evaluated in fp64 (the rest provably cannot be the minimum); entries whose motion
+// is exactly 0 compete as -0.0.  Other association functions evaluate every entry.
+__device__ inline void ocm_row_summary(const OcmCost& c, int d, int nT, double iou_thr, int* cand /*[64] per warp*/,
+                                       int* colcnt, double* rm_out, int* ra_out, int* nhit_out, int* last_out) {
+    const int lane = lane_id();
+    const bool sparse = c.func == ASSO_IOU;
+    const Box a = c.det(d);
+    const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
+    const double area_a = (a.x2 - a.x1) * (a.y2 - a.y1);
+    double rm = CUDART_INF;
+    int ra = 0x7fffffff, nhit = 0, lasthit = -1, ncand = 0, zero_t = 0x7fffffff;
+    float m32 = -CUDART_INF_F;
+    auto flush = [&]() {
+        __syncwarp();
+        for (int k = lane; k < ncand; k += 32) {
+            const int t = cand[k];
+            double iou;
+            const double cc = c.entry(a, cxd, cyd, t, &iou);
+            if (cc < rm || (cc == rm && t < ra)) { rm = cc; ra = t; }
+            if (iou > iou_thr) { nhit++; lasthit = max(lasthit, t); atomicAdd(&colcnt[t], 1); }
+        }
+        ncand = 0;
+        __syncwarp();
+    };
+    auto push = [&](bool pred, int t) {
+        const unsigned b = __ballot_sync(BM_FULL, pred);
+        if (pred) cand[ncand + __popc(b & ((1u << lane) - 1))] = t;
+        ncand += __popc(b);
+        if (ncand > 32) flush();
+    };
+    auto overlaps = [&](int t) {
+        const Box b = c.trk(t);
+        const double w = fmin(a.x2, b.x2) - fmax(a.x1, b.x1), h = fmin(a.y2, b.y2) - fmax(a.y1, b.y1);
+        // iou is exactly 0 iff the clipped overlap is 0 and the union is a positive number
+        const double den = area_a + (b.x2 - b.x1) * (b.y2 - b.y1);
+        return !((w <= 0.0 || h <= 0.0) && den > 0.0);
+    };
+    auto moving = [&](int t) {
+        return c.tb[AB_KVALID * c.Tcap + t] != 0.0 && (c.tb[AB_VX * c.Tcap + t] != 0.0 || c.tb[AB_VY * c.Tcap + t] != 0.0);
+    };
+    for (int base = 0; base < nT; base += 32) {
+        const int t = base + lane;
+        bool ex = false;
+        if (t < nT) {
+            ex = !sparse || overlaps(t);
+            if (!ex) {
+                if (moving(t)) m32 = fmaxf(m32, ocm_cos32(c, cxd, cyd, t));
+                else zero_t = min(zero_t, t);
+            }
+        }
+        push(ex, t);
+    }
+    if (sparse) {
+        for (int o = 16; o > 0; o >>= 1) {
+            m32 = fmaxf(m32, __shfl_xor_sync(BM_FULL, m32, o));
+            zero_t = min(zero_t, __shfl_xor_sync(BM_FULL, zero_t, o));
+        }
+        for (int base = 0; base < nT; base += 32) {
+            const int t = base + lane;
+            const bool ex = t < nT && !overlaps(t) && moving(t) && ocm_cos32(c, cxd, cyd, t) >= m32 - OCM_BAND;
+            push(ex, t);
+        }
+    }
+    flush();
     warp_argmin(rm, ra);
     for (int o = 16; o > 0; o >>= 1) {
-        cmx = fmax(cmx, shfl_xor_d(cmx, o));
         nhit += __shfl_xor_sync(BM_FULL, nhit, o);
         lasthit = max(lasthit, __shfl_xor_sync(BM_FULL, lasthit, o));
     }
-    if (lane == 0) {
-        double* rd = st.rowd + (size_t)s * 2 * Dcap;
-        int* ri = st.rowi + (size_t)s * 3 * Dcap;
-        rd[d] = rm; rd[Dcap + d] = cmx;
-        ri[d] = ra; ri[Dcap + d] = nhit; ri[2 * Dcap + d] = lasthit;
-    }
+    // zero-motion, zero-IoU entries hold -(0.0 + 0.0) = -0.0
+    if (zero_t != 0x7fffffff && (-0.0 < rm || (-0.0 == rm && zero_t < ra))) { rm = -0.0; ra = zero_t; }
+    *rm_out = rm; *ra_out = ra; *nhit_out = nhit; *last_out = lasthit;
 }
 
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
@@ -299,7 +328,7 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
         // Only pairs with iou >= thr survive, and the caller re-sorts what is left: any
         // optimal solution gives the same result, so the fast exact solver is used.
         RectWork w = rect_carve(sm.lapw, nA, nB);
-        const int bad = rect_solve_warp(cost, nB, nA, nB, 2.0 * (cmx + 1.0), w, nullptr, nullptr);
+        const int bad = rect_solve_warp(DenseCost{cost, nB}, nA, nB, 2.0 * (cmx + 1.0), w, nullptr, nullptr);
         if (bad && lane == 0) sm.misc[M_LAPBAD] = 1;
         for (int r = lane; r < nA; r += 32) {
             int c = w.x[r];
@@ -370,26 +399,26 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         }
         if (lane == 0) { sm.misc[M_ND] = nh; sm.misc[M_NS] = ns; }
     }
-    // ---- predicted boxes of the live tracks (written by K1)
+    // ---- association operands of the predicted tracks (written by K1)
     int nT = v.hdr[OH_NLIST];
     const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
-    for (int p = tid; p < nT; p += K2_NT) {
-        double b[4];
-#pragma unroll
-        for (int c = 0; c < 4; c++) { b[c] = ab[(AB_X1 + c) * Tcap + p]; sm.tbox[c * Tcap + p] = b[c]; }
-        sm.slot_of[p] = v.order[p];
-        const bool bad = b[0] != b[0] || b[1] != b[1] || b[2] != b[2] || b[3] != b[3];
-        sm.t2d[p] = bad ? -2 : -1;
-        if (bad) sm.misc[M_ANYBAD] = 1;
+    for (int e = tid; e < AB_COUNT * nT; e += K2_NT) {
+        const int f = e / nT, p = e - f * nT;
+        const double val = ab[f * Tcap + p];
+        sm.tbox[f * Tcap + p] = val;
+        if (f < 4 && val != val) sm.misc[M_ANYBAD] = 1;
     }
+    for (int p = tid; p < nT; p += K2_NT) { sm.slot_of[p] = v.order[p]; sm.t2d[p] = -1; sm.colcnt[p] = 0; }
     __syncthreads();
-    if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288);
-        if (tid == 0) {        // the cost kernel compacted its columns the same way
+    if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288)
+        if (tid == 0) {
             int k = 0;
             for (int p = 0; p < nT; p++) {
-                if (sm.t2d[p] == -2) continue;
-                for (int c = 0; c < 4; c++) sm.tbox[c * Tcap + k] = sm.tbox[c * Tcap + p];
-                sm.slot_of[k] = sm.slot_of[p]; sm.t2d[k] = -1;
+                bool nan = false;
+                for (int f = 0; f < 4; f++) nan |= sm.tbox[f * Tcap + p] != sm.tbox[f * Tcap + p];
+                if (nan) continue;
+                for (int f = 0; f < AB_COUNT; f++) sm.tbox[f * Tcap + k] = sm.tbox[f * Tcap + p];
+                sm.slot_of[k] = sm.slot_of[p];
                 v.order[k] = sm.slot_of[k];
                 k++;
             }
@@ -400,40 +429,47 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         nT = sm.misc[M_NT];
     }
     const int nD = sm.misc[M_ND], nS = sm.misc[M_NS];
-    // ---- first round: cost[d][t] = -(iou + OCM) was written det-major to the L2-resident
-    // scratch by ocs_cost_kernel together with the row / column summaries;
-    // permutation fast path (association.py:501-503) or exact LAP (:505-507)
-    const size_t need = (size_t)nD * nT;
-    double* cost = st.scratch + (size_t)s * st.scratch_elems;
-    const bool assoc_ok = true;
-    {
-        const double* rd = st.rowd + (size_t)s * 2 * Dcap;
-        const int* ri = st.rowi + (size_t)s * 3 * Dcap;
-        const bool have = nD > 0 && nT > 0;
-        double cmx = -CUDART_INF;
-        for (int d = tid; d < nD; d += K2_NT) {
-            sm.d2t[d] = -1;
-            sm.rmin[d] = have ? rd[d] : 0.0;
-            if (have) cmx = fmax(cmx, rd[Dcap + d]);
-            sm.rarg[d] = have ? ri[d] : -1;
-            sm.rowcnt[d] = have ? ri[Dcap + d] : 0;
-            sm.hit_t[d] = have ? ri[2 * Dcap + d] : -1;
-        }
-        for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = nD > 0 ? st.colhit[(size_t)s * Tcap + t] : 0;
-        for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
-        if (lane == 0) sm.wred[wid] = cmx;
-    }
+    for (int d = tid; d < nD; d += K2_NT) { sm.d2t[d] = -1; sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
     __syncthreads();
-    if (nD > 0 && nT > 0 && assoc_ok) {
+
+    // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
+    // (association.py:427-461), evaluated on demand; permutation fast path (:501-503) or
+    // exact LAP (:505-507)
+    const OcmCost ocm = {sm.dbox, Dcap, sm.tbox, Tcap, pr.asso_func, pr.diag, pr.inertia};
+    if (nD > 0 && nT > 0) {
+        for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
+            double rm; int ra, nhit, lasthit;
+            ocm_row_summary(ocm, d, nT, pr.iou_thr, sm.cand + 64 * wid, sm.colcnt, &rm, &ra, &nhit, &lasthit);
+            if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
+        }
+        __syncthreads();
+        // permutation fast path: every row/column has at most one IoU hit, at least one exists
+        int rmax = 0, cmax_ = 0;
+        for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
+        for (int t = lane; t < nT; t += 32) cmax_ = max(cmax_, sm.colcnt[t]);
+        for (int o = 16; o > 0; o >>= 1) {
+            rmax = max(rmax, __shfl_xor_sync(BM_FULL, rmax, o));
+            cmax_ = max(cmax_, __shfl_xor_sync(BM_FULL, cmax_, o));
+        }
+        const bool fast = rmax == 1 && cmax_ == 1;           // uniform over the CTA
+        double* cost = st.scratch + (size_t)s * st.scratch_elems;
+        if (!fast && nD > nT) {
+            // WHICH zero-gain detections stay unassigned when there are more detections than
+            // tracks is decided by lapjv's scan order (the reference's unmatched-detection ORDER,
+            // and with it the new ids, depends on it): materialise the matrix for the
+            // step-for-step lapjv emulation.
+            double cmx = -CUDART_INF;
+            for (int d = wid; d < nD; d += K2_NT / 32)
+                for (int t = lane; t < nT; t += 32) {
+                    const double cc = ocm(d, t);
+                    cost[(size_t)d * nT + t] = cc;
+                    cmx = fmax(cmx, cc);
+                }
+            for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
+            if (lane == 0) sm.wred[wid] = cmx;
+            __syncthreads();
+        }
         if (wid == 0) {
-            int rmax = 0, cmax_ = 0;
-            for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
-            for (int t = lane; t < nT; t += 32) cmax_ = max(cmax_, sm.colcnt[t]);
-            for (int o = 16; o > 0; o >>= 1) {
-                rmax = max(rmax, __shfl_xor_sync(BM_FULL, rmax, o));
-                cmax_ = max(cmax_, __shfl_xor_sync(BM_FULL, cmax_, o));
-            }
-            const bool fast = rmax == 1 && cmax_ == 1;
             if (fast) {
                 for (int d = lane; d < nD; d += 32) {
                     const int t = sm.rowcnt[d] == 1 ? sm.hit_t[d] : -1;
@@ -442,20 +478,18 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
                     if (t >= 0) sm.t2d[t] = d;
                 }
             } else {
-                double pad = sm.wred[0];
-                for (int i = 1; i < K2_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
-                // With nD <= nT every detection is assigned in every optimal solution, so the
-                // reference's unmatched-detection ORDER (never-assigned first, then rejected;
-                // ocsort ids follow it) does not depend on lapjv's tie-breaking and the fast
-                // exact solver applies.  With nD > nT WHICH zero-gain detections stay
-                // unassigned is decided by lapjv's scan order: emulate it step for step.
                 int bad;
                 int* xsol;
                 if (nD <= nT) {
+                    // Every detection is assigned in every optimal solution (any real entry beats
+                    // the padding), so the outcome does not depend on lapjv's tie-breaking and the
+                    // fast exact solver applies; the null option is never taken (cost +inf).
                     RectWork w = rect_carve(sm.lapw, nD, nT);
-                    bad = rect_solve_warp(cost, nT, nD, nT, 2.0 * (pad + 1.0), w, sm.rmin, sm.rarg);
+                    bad = rect_solve_warp(ocm, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
                     xsol = w.x;
                 } else {
+                    double pad = sm.wred[0];
+                    for (int i = 1; i < K2_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
                     LapMat m = {cost, nT, nD, nT, nD + nT, 1, pad + 1.0};
                     LapWork w = lap_carve(sm.lapw, nD + nT);
                     bad = lap_solve_warp(m, w);
@@ -468,9 +502,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
                     int stt = 0;                              // 0 never assigned
                     if (t >= 0) {
                         // iou re-evaluated for the assigned pair only (same arithmetic, same value)
-                        Box a = {sm.dbox[0 * Dcap + d], sm.dbox[1 * Dcap + d], sm.dbox[2 * Dcap + d], sm.dbox[3 * Dcap + d]};
-                        Box b = {sm.tbox[0 * Tcap + t], sm.tbox[1 * Tcap + t], sm.tbox[2 * Tcap + t], sm.tbox[3 * Tcap + t]};
-                        const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
+                        const double iou = asso_pair(pr.asso_func, ocm.det(d), ocm.trk(t), pr.diag);
                         if (iou < pr.iou_thr) { stt = 2; sm.colcnt[t] = -1 - d; }   // rejected (remember the row)
                         else { stt = 1; sm.t2d[t] = d; }
                     }
@@ -727,8 +759,6 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
                                double* out, int* nout, cudaStream_t stream) {
     const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
     ocs_predict_kernel<<<st.S * c1, K1_NT, 0, stream>>>(st, pr);
-    const int cc = (st.Dcap + KC_NT / 32 - 1) / (KC_NT / 32);
-    ocs_cost_kernel<<<st.S * cc, KC_NT, (size_t)AB_COUNT * st.Tcap * sizeof(double), stream>>>(st, pr, dets, ndets);
     ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets, ndets);
     ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
     const int nt4 = (st.Tcap + 31) / 32 * 32;

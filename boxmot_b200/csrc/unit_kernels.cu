@@ -43,7 +43,7 @@ lap_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, in
     const size_t wbytes = (lap_work_bytes(nr_max + nc_max) + 15) / 16 * 16;
     if (RECT) {   // fast exact solver on the real rows (csrc/lap_rect.cuh)
         RectWork rw = rect_carve(smem_raw + (size_t)wid * wbytes, nr, nc);
-        rect_solve_warp(c, nc_max, nr, nc, 2.0 * pad, rw, nullptr, nullptr);
+        rect_solve_warp(DenseCost{c, nc_max}, nr, nc, 2.0 * pad, rw, nullptr, nullptr);
         for (int i = lane; i < nr_max; i += 32) x[i] = i < nr ? rw.x[i] : -1;
         for (int j = lane; j < nc_max; j += 32) y[j] = j < nc ? rw.y[j] : -1;
         return;
