@@ -66,6 +66,11 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
 }
 
 // ============================================================================ K2
+// bytes of the fp32 screening tables (OcmScreen below)
+__host__ __device__ inline size_t ocm_screen_bytes(int Tcap, int warps) {
+    return (size_t)Tcap * (sizeof(float4) + sizeof(float2)) + (size_t)warps * Tcap * sizeof(float);
+}
+
 struct OcsSmem {
     double *dbox, *dconf, *sbox, *tbox, *wred, *rmin;
     int *dind, *sind, *slot_of, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg, *cand;
@@ -80,7 +85,8 @@ __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byt
     size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + AB_COUNT * t + 8;
     size_t ints = 7 * d + (use_byte ? d : 0) + 4 * t + M_COUNT + 64 * (K2_NT / 32);
     size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
-    b += (lap_work_bytes((int)(d + t)) + 7) / 8 * 8;
+    size_t lw = (lap_work_bytes((int)(d + t)) + 15) / 16 * 16, sw = (ocm_screen_bytes((int)t, K2_NT / 32) + 15) / 16 * 16;
+    b = (b + 15) / 16 * 16 + (lw > sw ? lw : sw);
     b += (size_t)cost_elems * 8;
     return b;
 }
@@ -112,8 +118,12 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     // 7*Dcap reserved: one Dcap block is spare so the int area never undercounts
     size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)4 * Tcap + M_COUNT + 64 * (K2_NT / 32)) * 4 + 7) / 8 * 8;
     unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
+    r = base + ((size_t)(r - base) + 15) / 16 * 16;
     m.lapw = r;
-    r += (lap_work_bytes(Dcap + Tcap) + 7) / 8 * 8;
+    {
+        size_t lw = (lap_work_bytes(Dcap + Tcap) + 15) / 16 * 16, sw = (ocm_screen_bytes(Tcap, K2_NT / 32) + 15) / 16 * 16;
+        r += lw > sw ? lw : sw;
+    }
     m.cost = cost_elems > 0 ? reinterpret_cast<double*>(r) : nullptr;
     return m;
 }
@@ -185,29 +195,50 @@ struct OcmCost {
     }
 };
 
-// fp32 screening value of the OCM cosine (monotone proxy of the motion term); only used
-// to pick which zero-IoU entries of a row are evaluated exactly.
-__device__ __forceinline__ float ocm_cos32(const OcmCost& c, double cxd, double cyd, int t) {
-    const float dx = (float)(cxd - c.tb[AB_KCX * c.Tcap + t]), dy = (float)(cyd - c.tb[AB_KCY * c.Tcap + t]);
-    const float vx = (float)c.tb[AB_VX * c.Tcap + t], vy = (float)c.tb[AB_VY * c.Tcap + t];
-    return (vx * dx + vy * dy) / (sqrtf(dx * dx + dy * dy) + 1e-6f);
+// fp32 screening tables, built once per stream-frame (they alias the solver's work area,
+// which is idle while the row summaries are computed).
+//   boxf[t]  the track box rounded OUTWARDS to float (x1,y1 down; x2,y2 up): if the float
+//            boxes do not overlap, the fp64 boxes do not either.  A degenerate / non-finite
+//            box is stored as (-inf,-inf,+inf,+inf) so it is always evaluated exactly.
+//   mvf[t]   (vx, vy) as floats, (0,0) when the OCM term is exactly 0 for this track.
+struct OcmScreen {
+    float4* boxf;
+    float2* mvf;
+    float* cs;          // [warps][Tcap] per-row screening cosines
+};
+__device__ inline void ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, int t) {
+    const Box b = c.trk(t);
+    const bool ok = (b.x2 - b.x1) * (b.y2 - b.y1) > 0.0 && b.x2 > b.x1;
+    sc.boxf[t] = ok ? make_float4(__double2float_rd(b.x1), __double2float_rd(b.y1),
+                                  __double2float_ru(b.x2), __double2float_ru(b.y2))
+                    : make_float4(-CUDART_INF_F, -CUDART_INF_F, CUDART_INF_F, CUDART_INF_F);
+    const double vx = c.tb[AB_VX * c.Tcap + t], vy = c.tb[AB_VY * c.Tcap + t];
+    const bool mv = c.tb[AB_KVALID * c.Tcap + t] != 0.0 && (vx != 0.0 || vy != 0.0);
+    float fx = mv ? (float)vx : 0.f, fy = mv ? (float)vy : 0.f;
+    if (mv && fx == 0.f && fy == 0.f) fx = 1e-30f;      // keep "moving" distinguishable
+    sc.mvf[t] = make_float2(fx, fy);
 }
-constexpr float OCM_BAND = 5e-5f;   // >> fp32 error of ocm_cos32 (~1e-6), << spacing of candidates
+constexpr float OCM_BAND = 1e-4f;   // >> error of the fp32 cosine (~1e-6), << spacing of candidates
+constexpr float OCM_NOCAND = -4.f;
 
 // Row summaries for the solver and the permutation fast path, one warp per row:
 // exact minimum / argmin of the row, number of IoU hits (> thr) and the last hit column.
 // With asso_func = iou an entry whose boxes do not overlap is exactly -(0 + motion), and
-// motion is a monotone function of the OCM cosine, so only (i) overlapping entries and
-// (ii) the zero-IoU entries whose fp32 cosine is within OCM_BAND of the row's best are
-// evaluated in fp64 (the rest provably cannot be the minimum); entries whose motion
-// is exactly 0 compete as -0.0.  Other association functions evaluate every entry.
-__device__ inline void ocm_row_summary(const OcmCost& c, int d, int nT, double iou_thr, int* cand /*[64] per warp*/,
-                                       int* colcnt, double* rm_out, int* ra_out, int* nhit_out, int* last_out) {
+// motion is a monotone function of the OCM cosine, so only (i) entries whose outward-rounded
+// float boxes overlap and (ii) the remaining entries whose fp32 cosine is within OCM_BAND of
+// the row's best are evaluated in fp64 (the rest provably cannot be the minimum); entries
+// whose motion is exactly 0 compete as -0.0.  Other association functions, and detections
+// with a degenerate box, evaluate every entry.
+__device__ inline void ocm_row_summary(const OcmCost& c, const OcmScreen& sc, int d, int nT, double iou_thr,
+                                       int* cand /*[64] per warp*/, int* colcnt, double* rm_out, int* ra_out,
+                                       int* nhit_out, int* last_out) {
     const int lane = lane_id();
-    const bool sparse = c.func == ASSO_IOU;
     const Box a = c.det(d);
     const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
-    const double area_a = (a.x2 - a.x1) * (a.y2 - a.y1);
+    const bool sparse = c.func == ASSO_IOU && (a.x2 - a.x1) * (a.y2 - a.y1) > 0.0 && a.x2 > a.x1;
+    // detections arrive as float32, so these casts are exact
+    const float ax1 = (float)a.x1, ay1 = (float)a.y1, ax2 = (float)a.x2, ay2 = (float)a.y2;
+    float* csrow = sc.cs + (size_t)warp_id() * c.Tcap;
     double rm = CUDART_INF;
     int ra = 0x7fffffff, nhit = 0, lasthit = -1, ncand = 0, zero_t = 0x7fffffff;
     float m32 = -CUDART_INF_F;
@@ -229,25 +260,29 @@ __device__ inline void ocm_row_summary(const OcmCost& c, int d, int nT, double i
         ncand += __popc(b);
         if (ncand > 32) flush();
     };
-    auto overlaps = [&](int t) {
-        const Box b = c.trk(t);
-        const double w = fmin(a.x2, b.x2) - fmax(a.x1, b.x1), h = fmin(a.y2, b.y2) - fmax(a.y1, b.y1);
-        // iou is exactly 0 iff the clipped overlap is 0 and the union is a positive number
-        const double den = area_a + (b.x2 - b.x1) * (b.y2 - b.y1);
-        return !((w <= 0.0 || h <= 0.0) && den > 0.0);
-    };
-    auto moving = [&](int t) {
-        return c.tb[AB_KVALID * c.Tcap + t] != 0.0 && (c.tb[AB_VX * c.Tcap + t] != 0.0 || c.tb[AB_VY * c.Tcap + t] != 0.0);
-    };
     for (int base = 0; base < nT; base += 32) {
         const int t = base + lane;
         bool ex = false;
         if (t < nT) {
-            ex = !sparse || overlaps(t);
-            if (!ex) {
-                if (moving(t)) m32 = fmaxf(m32, ocm_cos32(c, cxd, cyd, t));
-                else zero_t = min(zero_t, t);
+            float csv = OCM_NOCAND;
+            ex = true;
+            if (sparse) {
+                const float4 b = sc.boxf[t];
+                ex = ax1 < b.z && b.x < ax2 && ay1 < b.w && b.y < ay2;
+                if (!ex) {
+                    const float2 mv = sc.mvf[t];
+                    if (mv.x == 0.f && mv.y == 0.f) zero_t = min(zero_t, t);
+                    else {
+                        const float dx = (float)(cxd - c.tb[AB_KCX * c.Tcap + t]);
+                        const float dy = (float)(cyd - c.tb[AB_KCY * c.Tcap + t]);
+                        const float n2 = dx * dx + dy * dy;
+                        const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
+                        csv = __fdividef(mv.x * dx + mv.y * dy, nrm + 1e-6f);
+                        m32 = fmaxf(m32, csv);
+                    }
+                }
             }
+            csrow[t] = csv;
         }
         push(ex, t);
     }
@@ -256,10 +291,10 @@ __device__ inline void ocm_row_summary(const OcmCost& c, int d, int nT, double i
             m32 = fmaxf(m32, __shfl_xor_sync(BM_FULL, m32, o));
             zero_t = min(zero_t, __shfl_xor_sync(BM_FULL, zero_t, o));
         }
+        const float lim = m32 - OCM_BAND;
         for (int base = 0; base < nT; base += 32) {
             const int t = base + lane;
-            const bool ex = t < nT && !overlaps(t) && moving(t) && ocm_cos32(c, cxd, cyd, t) >= m32 - OCM_BAND;
-            push(ex, t);
+            push(t < nT && csrow[t] >= lim && csrow[t] != OCM_NOCAND, t);
         }
     }
     flush();
@@ -437,9 +472,15 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
     // exact LAP (:505-507)
     const OcmCost ocm = {sm.dbox, Dcap, sm.tbox, Tcap, pr.asso_func, pr.diag, pr.inertia};
     if (nD > 0 && nT > 0) {
+        OcmScreen scr;      // aliases the solver work area (idle until the summaries are done)
+        scr.boxf = reinterpret_cast<float4*>(sm.lapw);
+        scr.mvf = reinterpret_cast<float2*>(scr.boxf + Tcap);
+        scr.cs = reinterpret_cast<float*>(scr.mvf + Tcap);
+        for (int t = tid; t < nT; t += K2_NT) ocm_screen_fill(ocm, scr, t);
+        __syncthreads();
         for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
             double rm; int ra, nhit, lasthit;
-            ocm_row_summary(ocm, d, nT, pr.iou_thr, sm.cand + 64 * wid, sm.colcnt, &rm, &ra, &nhit, &lasthit);
+            ocm_row_summary(ocm, scr, d, nT, pr.iou_thr, sm.cand + 64 * wid, sm.colcnt, &rm, &ra, &nhit, &lasthit);
             if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
         }
         __syncthreads();

@@ -35,7 +35,7 @@ class OcSortEngine:
         self.device = torch.device(device)
         self.S, self.Tcap, self.Dcap = int(n_streams), int(track_cap), int(det_cap)
         if smem_cost_bytes is None:
-            smem_cost_bytes = min(8 * self.Tcap * self.Dcap, 8 * 1024)
+            smem_cost_bytes = 0     # second-round matrices live in the L2-resident scratch
         cfg = _lib.OcsortConfig(det_thresh, min_conf, asso_threshold, inertia, Q_xy_scaling,
                                 Q_s_scaling, int(max_age), int(min_hits), int(delta_t),
                                 _lib.ASSO_FUNCS[asso_func], int(bool(use_byte)),
