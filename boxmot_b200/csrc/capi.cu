@@ -80,9 +80,7 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     if (r == cudaSuccess) r = dev_alloc(e, &st.abuf, S * bm::AB_COUNT * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.upd, S * 2 * (size_t)det_cap);
     if (r == cudaSuccess) r = dev_alloc(e, &st.born, S * (size_t)det_cap);
-    if (r == cudaSuccess) r = dev_alloc(e, &st.rowd, S * 2 * (size_t)det_cap);
-    if (r == cudaSuccess) r = dev_alloc(e, &st.rowi, S * 3 * (size_t)det_cap);
-    if (r == cudaSuccess) r = dev_alloc(e, &st.colhit, S * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.hsel, S * 2 * (size_t)det_cap);
     e->smem = bm::ocsort_step_smem(st, pr);
     if (r == cudaSuccess) r = bm::ocsort_step_configure(e->smem);
     if (r != cudaSuccess) {
@@ -111,7 +109,6 @@ int bm_ocsort_reset(void* handle, void* stream) {
     BM_CUDA(cudaMemsetAsync(st.hdr, 0, S * bm::OH_COUNT * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.n_updates, 0, S * sizeof(unsigned long long), s));
     BM_CUDA(cudaMemsetAsync(st.order, 0, S * T * sizeof(int), s));
-    BM_CUDA(cudaMemsetAsync(st.colhit, 0, S * T * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::OI_COUNT * T * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::XB_N * T * sizeof(double), s));
     BM_CUDA(cudaMemsetAsync(st.sxP, 0, S * bm::XB_N * T * sizeof(double), s));

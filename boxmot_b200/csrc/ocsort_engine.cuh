@@ -17,7 +17,7 @@ namespace bm {
 
 enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
 enum { OF_OBSERVED = 1, OF_SAVED = 2 };
-enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_COUNT = 12 };
+enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_ND, OH_NS, OH_COUNT = 12 };
 // association operands written by the predict kernel, indexed by LIST POSITION
 enum { AB_X1 = 0, AB_Y1, AB_X2, AB_Y2, AB_VY, AB_VX, AB_KCX, AB_KCY, AB_KVALID, AB_COUNT };
 
@@ -46,9 +46,7 @@ struct OcsState {
     double* abuf;                  // [S][AB_COUNT][Tcap] predicted boxes / OCM operands per list position
     int* upd;                      // [S][2][Dcap] this frame's (slot, detection row) Kalman updates
     int* born;                     // [S][Dcap]    detection rows that start a track, in id order
-    double* rowd;                  // [S][2][Dcap] per cost row: minimum, maximum (written by the cost kernel)
-    int* rowi;                     // [S][3][Dcap] per cost row: argmin column, #IoU hits, last hit column
-    int* colhit;                   // [S][Tcap]    per cost column: #IoU hits (zeroed by the predict kernel)
+    int* hsel;                     // [S][2][Dcap] detection rows of the high-score set, then of the BYTE set
 };
 
 struct OcsView {   // per-stream base pointers

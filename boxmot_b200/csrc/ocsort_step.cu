@@ -5,12 +5,13 @@
 //
 //   K1 ocs_predict_kernel   thread per live track        Kalman predict (ocsort.py:281-288,
 //                           (HBM-streaming, SoA state)   :173-186) + association operands
-//   K2a ocs_cost_kernel     warp per cost-matrix row     score split (:265-275), IoU + OCM velocity
-//                           (fp64-pipe bound)            cost (association.py:427-461) -> L2-resident
-//                                                        matrix + per-row / per-column summaries
-//   K2b ocs_assoc_kernel    CTA per stream, small smem   permutation fast path or exact LAP,
-//                           (latency bound, all CTAs     BYTE (:330-356) and OCR (:358-386) rounds
-//                           co-resident)
+//                                                        and the confidence split (:265-275)
+//   K2a ocs_rowsum_kernel   warp per cost-matrix row     exact row minima / IoU-hit counts of the
+//                           (throughput kernel)          IoU + OCM cost (association.py:427-461),
+//                                                        fp32-screened, matrix never materialised
+//   K2b ocs_assoc_kernel    CTA per stream               permutation fast path or exact LAP with
+//                           (latency bound)              on-demand cost rows, BYTE (:330-356) and
+//                                                        OCR (:358-386) rounds
 //   K3 ocs_update_kernel    thread per matched track     Kalman update + ORU (:321-324,
 //                           (HBM-streaming)              xysr_kf.py:211-291)
 //   K4 ocs_finalize_kernel  CTA per stream               misses, births, output rows, dead-track
@@ -20,23 +21,60 @@
 // of the association CTA, whose occupancy would otherwise be 2 CTAs/SM.
 #include "ocsort_engine.cuh"
 #include "lap_rect.cuh"
+#include <cstdio>
+#include <cstdlib>
 
 namespace bm {
 
 constexpr int K1_NT = 128;
-constexpr int K2_NT = 128;
+constexpr int K2_NT = 64;
 constexpr int K3_NT = 64;
 
 // ============================================================================ K1
+// Blocks [0, S*chunks) predict; the trailing ceil(S/4) blocks split each stream's detections
+// by confidence (ocsort.py:265-275; one warp per stream, stable order) for the kernels that
+// follow.  dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
+// precision: BaseTracker.setup_decorator round-trips every ndarray through float32
+// (boxmot/trackers/basetracker.py:122-128).
 __global__ void __launch_bounds__(K1_NT)
-ocs_predict_kernel(OcsState st, OcsParams pr) {
+ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
     const int chunks = (st.Tcap + K1_NT - 1) / K1_NT;
+    const int Tcap = st.Tcap;
+    if ((int)blockIdx.x >= st.S * chunks) {
+        const int s = ((int)blockIdx.x - st.S * chunks) * (K1_NT / 32) + warp_id();
+        if (s >= st.S) return;
+        const int lane = lane_id(), Dcap = st.Dcap;
+        int* hdr = st.hdr + (size_t)s * OH_COUNT;
+        int nD_in = ndets[s];
+        if (nD_in > Dcap) { if (lane == 0) atomicOr(&hdr[OH_ERR], BM_ERR_DET_OVERFLOW); nD_in = Dcap; }
+        const float* dsrc = dets + (size_t)s * Dcap * 6;
+        int* hs = st.hsel + (size_t)s * 2 * Dcap;
+        int nh = 0, ns = 0;
+        for (int base = 0; base < nD_in; base += 128) {          // 4 independent loads in flight
+            float cf[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) { const int i = base + 32 * k + lane; cf[k] = i < nD_in ? dsrc[i * 6 + 4] : -1.f; }
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int i = base + 32 * k + lane;
+                const double conf = (double)cf[k];
+                const bool hi = i < nD_in && conf > pr.det_thresh;
+                const bool se = pr.use_byte && i < nD_in && conf > pr.min_conf && conf < pr.det_thresh;
+                const unsigned bh = __ballot_sync(BM_FULL, hi), bs = __ballot_sync(BM_FULL, se);
+                const unsigned lt = (1u << lane) - 1;
+                if (hi) hs[nh + __popc(bh & lt)] = i;
+                if (se) hs[Dcap + ns + __popc(bs & lt)] = i;
+                nh += __popc(bh); ns += __popc(bs);
+            }
+        }
+        if (lane == 0) { hdr[OH_ND] = nh; hdr[OH_NS] = ns; }
+        return;
+    }
     const int s = blockIdx.x / chunks;
     const int p = (blockIdx.x % chunks) * K1_NT + threadIdx.x;
     OcsView v(st, s);
     const int nT = v.hdr[OH_NLIST];
     if (p == 0) st.n_updates[s] += (unsigned long long)nT;
-    const int Tcap = st.Tcap;
     if (p >= nT) return;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
@@ -66,42 +104,58 @@ ocs_predict_kernel(OcsState st, OcsParams pr) {
 }
 
 // ============================================================================ K2
-// bytes of the fp32 screening tables (OcmScreen below)
-__host__ __device__ inline size_t ocm_screen_bytes(int Tcap, int warps) {
-    return (size_t)Tcap * (sizeof(float4) + sizeof(float2)) + (size_t)warps * Tcap * sizeof(float);
-}
-
+// One CTA of two warps per stream; ~23 KB of shared memory and <= 128 registers keep eight
+// CTAs resident per SM, i.e. ALL streams of the headline workload in a single wave: the
+// kernel is a chain of short dependent phases, so throughput comes from co-residency.
 struct OcsSmem {
-    double *dbox, *dconf, *sbox, *tbox, *wred, *rmin;
-    int *dind, *sind, *slot_of, *d2t, *t2d, *um_d, *um_t, *rowcnt, *colcnt, *hit_t, *misc, *rarg, *cand;
-    void* lapw;
-    double* cost;
+    float4 *dbox, *sbox;                 // [Dcap] high-score / BYTE detections (inputs are float32: exact)
+    double* rmin;                        // [Dcap]
+    void* work;                          // screening tables, later the solver's work area
+    int *dind, *sind, *d2t, *um_d, *rowcnt, *hit_t, *rarg;   // [Dcap]
+    int *slot_of, *t2d, *um_t, *colcnt;                     // [Tcap]
+    int *misc, *cand;
 };
 
-enum { M_NT = 0, M_ND, M_NS, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M_TMP, M_COUNT = 16 };
+enum { M_NT = 0, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M_COUNT = 8 };
 
-__host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte, int cost_elems) {
-    size_t d = (size_t)Dcap, t = (size_t)Tcap;
-    size_t dbl = 6 * d + (use_byte ? 4 * d : 0) + AB_COUNT * t + 8;
-    size_t ints = 7 * d + (use_byte ? d : 0) + 4 * t + M_COUNT + 64 * (K2_NT / 32);
-    size_t b = dbl * 8 + ((ints * 4 + 7) / 8) * 8;
-    size_t lw = (lap_work_bytes((int)(d + t)) + 15) / 16 * 16, sw = (ocm_screen_bytes((int)t, K2_NT / 32) + 15) / 16 * 16;
-    b = (b + 15) / 16 * 16 + (lw > sw ? lw : sw);
-    b += (size_t)cost_elems * 8;
-    return b;
+// fp32 screening tables, built once per stream-frame (they alias the solver's work area,
+// which is idle while the row summaries are computed).
+//   boxf[t]  the track box rounded OUTWARDS to float (x1,y1 down; x2,y2 up): if the float
+//            boxes do not overlap, the fp64 boxes do not either.  A degenerate / non-finite
+//            box is stored as (-inf,-inf,+inf,+inf) so it is always evaluated exactly.
+//   kc[t]    centre of the observation delta_t frames back (fp64, exact differences)
+//   mvf[t]   (vx, vy) as floats, (0,0) when the OCM term is exactly 0 for this track
+//   cs       [warps][Tcap] per-row screening cosines
+struct OcmScreen {
+    float4* boxf;
+    double2* kc;
+    float2* mvf;
+    float* cs;
+};
+__host__ __device__ inline size_t ocm_screen_bytes(int Tcap, int warps) {
+    return (size_t)Tcap * (sizeof(float4) + sizeof(double2) + sizeof(float2)) + (size_t)warps * Tcap * sizeof(float);
+}
+__host__ __device__ inline size_t ocs_work_bytes(int Tcap, int Dcap) {
+    // the lapjv emulation only runs with more detections than tracks: n = nD + nT < 2 * Dcap
+    const size_t a = ocm_screen_bytes(Tcap, K2_NT / 32), b = rect_work_bytes(Dcap, Tcap), c = lap_work_bytes(2 * Dcap);
+    const size_t m = a > b ? (a > c ? a : c) : (b > c ? b : c);
+    return (m + 15) / 16 * 16;
 }
 
-__device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int use_byte, int cost_elems) {
+__host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte) {
+    const size_t d = (size_t)Dcap, t = (size_t)Tcap;
+    size_t b = 16 * d * (use_byte ? 2 : 1) + 8 * d + ocs_work_bytes(Tcap, Dcap);
+    b += 4 * ((use_byte ? 7 : 6) * d + 4 * t + M_COUNT + 64 * (K2_NT / 32));
+    return (b + 15) / 16 * 16;
+}
+
+__device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int use_byte) {
     OcsSmem m;
-    double* p = reinterpret_cast<double*>(base);
-    m.dbox = p; p += 4 * Dcap;
-    m.dconf = p; p += Dcap;
-    m.rmin = p; p += Dcap;
-    if (use_byte) { m.sbox = p; p += 4 * Dcap; } else m.sbox = nullptr;
-    m.tbox = p; p += AB_COUNT * Tcap;     // all association operands; rows 0-3 are the box
-    m.wred = p; p += 8;
-    int* q = reinterpret_cast<int*>(p);
-    int* q0 = q;
+    m.dbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap;
+    if (use_byte) { m.sbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap; } else m.sbox = nullptr;
+    m.work = base; base += ocs_work_bytes(Tcap, Dcap);
+    m.rmin = reinterpret_cast<double*>(base); base += 8 * (size_t)Dcap;
+    int* q = reinterpret_cast<int*>(base);
     m.dind = q; q += Dcap;
     if (use_byte) { m.sind = q; q += Dcap; } else m.sind = nullptr;
     m.d2t = q; q += Dcap;
@@ -114,17 +168,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.um_t = q; q += Tcap;
     m.colcnt = q; q += Tcap;
     m.misc = q; q += M_COUNT;
-    m.cand = q; q += 64 * (K2_NT / 32);
-    // 7*Dcap reserved: one Dcap block is spare so the int area never undercounts
-    size_t ib = (((size_t)7 * Dcap + (use_byte ? Dcap : 0) + (size_t)4 * Tcap + M_COUNT + 64 * (K2_NT / 32)) * 4 + 7) / 8 * 8;
-    unsigned char* r = reinterpret_cast<unsigned char*>(q0) + ib;
-    r = base + ((size_t)(r - base) + 15) / 16 * 16;
-    m.lapw = r;
-    {
-        size_t lw = (lap_work_bytes(Dcap + Tcap) + 15) / 16 * 16, sw = (ocm_screen_bytes(Tcap, K2_NT / 32) + 15) / 16 * 16;
-        r += lw > sw ? lw : sw;
-    }
-    m.cost = cost_elems > 0 ? reinterpret_cast<double*>(r) : nullptr;
+    m.cand = q;
     return m;
 }
 
@@ -157,10 +201,12 @@ __device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, 
 // First-round cost, evaluated ON DEMAND.  cost(d, t) = -(iou + OCM) exactly as
 // enhanced_associate builds it (association.py:427-461), det-major.  The assignment solver
 // needs (a) every row's minimum and (b) the full rows it sweeps while augmenting -- on
-// tracking data that is ~2 rows per frame -- so the matrix is never materialised.
+// tracking data that is ~2 rows per frame -- so the matrix is never materialised.  The
+// fp64 operands stay where the predict kernel wrote them (L2-resident global memory); only
+// the fp32 screening tables live in shared memory.
 struct OcmCost {
-    const double* dbox; int Dcap;      // high-score detections [4][Dcap] (shared memory)
-    const double* tb; int Tcap;        // operands per track column [AB_COUNT][Tcap] (shared memory)
+    const float4* dbox;                // high-score detections (shared memory)
+    const double* tb; int Tcap;        // operands per track column [AB_COUNT][Tcap] (global, L2)
     int func; double diag, inertia;
 
     // velocity-direction term; exactly 0 for a track that was never observed (valid = 0)
@@ -178,7 +224,8 @@ struct OcmCost {
         return (1.0 * ang) * inertia;
     }
     __device__ __forceinline__ Box det(int d) const {
-        return Box{dbox[0 * Dcap + d], dbox[1 * Dcap + d], dbox[2 * Dcap + d], dbox[3 * Dcap + d]};
+        const float4 v = dbox[d];
+        return Box{(double)v.x, (double)v.y, (double)v.z, (double)v.w};
     }
     __device__ __forceinline__ Box trk(int t) const {
         return Box{tb[AB_X1 * Tcap + t], tb[AB_Y1 * Tcap + t], tb[AB_X2 * Tcap + t], tb[AB_Y2 * Tcap + t]};
@@ -195,18 +242,8 @@ struct OcmCost {
     }
 };
 
-// fp32 screening tables, built once per stream-frame (they alias the solver's work area,
-// which is idle while the row summaries are computed).
-//   boxf[t]  the track box rounded OUTWARDS to float (x1,y1 down; x2,y2 up): if the float
-//            boxes do not overlap, the fp64 boxes do not either.  A degenerate / non-finite
-//            box is stored as (-inf,-inf,+inf,+inf) so it is always evaluated exactly.
-//   mvf[t]   (vx, vy) as floats, (0,0) when the OCM term is exactly 0 for this track.
-struct OcmScreen {
-    float4* boxf;
-    float2* mvf;
-    float* cs;          // [warps][Tcap] per-row screening cosines
-};
-__device__ inline void ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, int t) {
+// Returns true when the predicted box is NaN (the reference drops such a track).
+__device__ inline bool ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, int t) {
     const Box b = c.trk(t);
     const bool ok = (b.x2 - b.x1) * (b.y2 - b.y1) > 0.0 && b.x2 > b.x1;
     sc.boxf[t] = ok ? make_float4(__double2float_rd(b.x1), __double2float_rd(b.y1),
@@ -217,6 +254,8 @@ __device__ inline void ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, in
     float fx = mv ? (float)vx : 0.f, fy = mv ? (float)vy : 0.f;
     if (mv && fx == 0.f && fy == 0.f) fx = 1e-30f;      // keep "moving" distinguishable
     sc.mvf[t] = make_float2(fx, fy);
+    sc.kc[t] = make_double2(c.tb[AB_KCX * c.Tcap + t], c.tb[AB_KCY * c.Tcap + t]);
+    return b.x1 != b.x1 || b.y1 != b.y1 || b.x2 != b.x2 || b.y2 != b.y2;
 }
 constexpr float OCM_BAND = 1e-4f;   // >> error of the fp32 cosine (~1e-6), << spacing of candidates
 constexpr float OCM_NOCAND = -4.f;
@@ -236,8 +275,7 @@ __device__ inline void ocm_row_summary(const OcmCost& c, const OcmScreen& sc, in
     const Box a = c.det(d);
     const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
     const bool sparse = c.func == ASSO_IOU && (a.x2 - a.x1) * (a.y2 - a.y1) > 0.0 && a.x2 > a.x1;
-    // detections arrive as float32, so these casts are exact
-    const float ax1 = (float)a.x1, ay1 = (float)a.y1, ax2 = (float)a.x2, ay2 = (float)a.y2;
+    const float4 af = c.dbox[d];
     float* csrow = sc.cs + (size_t)warp_id() * c.Tcap;
     double rm = CUDART_INF;
     int ra = 0x7fffffff, nhit = 0, lasthit = -1, ncand = 0, zero_t = 0x7fffffff;
@@ -268,13 +306,13 @@ __device__ inline void ocm_row_summary(const OcmCost& c, const OcmScreen& sc, in
             ex = true;
             if (sparse) {
                 const float4 b = sc.boxf[t];
-                ex = ax1 < b.z && b.x < ax2 && ay1 < b.w && b.y < ay2;
+                ex = af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w;
                 if (!ex) {
                     const float2 mv = sc.mvf[t];
                     if (mv.x == 0.f && mv.y == 0.f) zero_t = min(zero_t, t);
                     else {
-                        const float dx = (float)(cxd - c.tb[AB_KCX * c.Tcap + t]);
-                        const float dy = (float)(cyd - c.tb[AB_KCY * c.Tcap + t]);
+                        const double2 k = sc.kc[t];
+                        const float dx = (float)(cxd - k.x), dy = (float)(cyd - k.y);
                         const float n2 = dx * dx + dy * dy;
                         const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
                         csv = __fdividef(mv.x * dx + mv.y * dy, nrm + 1e-6f);
@@ -312,15 +350,16 @@ __device__ inline void ocm_row_summary(const OcmCost& c, const OcmScreen& sc, in
 // `alist` (indices into a detection set `abox`), cols = the nB list positions in
 // `blist` with boxes fetched by `bfetch`.  lapjv on -iou, accept pairs with iou >= thr
 // (ocsort.py:336-353, :363-380).  Writes pair_b[r] = column index or -1.  Returns
-// whether the block ran (max iou > thr and no NaN).
+// whether the block ran (max iou > thr and no NaN).  The matrix lives in the stream's
+// L2-resident scratch.
 template <typename BFetch>
-__device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s, OcsSmem& sm,
-                                 const double* abox, int Dld, const int* alist, int nA,
+__device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s, OcsSmem& sm, int Tcap, int Dcap,
+                                 const float4* abox, const int* alist, int nA,
                                  const int* blist, int nB, BFetch bfetch, int* pair_b) {
     const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const size_t need = (size_t)nA * nB;
-    double* cost = (need <= (size_t)st.smem_cost_elems) ? sm.cost : st.scratch + (size_t)s * st.scratch_elems;
-    if (need > st.scratch_elems && need > (size_t)st.smem_cost_elems) {
+    double* cost = st.scratch + (size_t)s * st.scratch_elems;
+    if (need > st.scratch_elems) {
         if (tid == 0) atomicOr(&st.hdr[(size_t)s * OH_COUNT + OH_ERR], BM_ERR_SCRATCH);
         for (int r = tid; r < nA; r += K2_NT) pair_b[r] = -1;
         __syncthreads();
@@ -331,9 +370,9 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
     int nanf = 0;
     for (size_t e = tid; e < need; e += K2_NT) {
         const int r = (int)(e / nB), c = (int)(e % nB);
-        const int d = alist[r];
-        Box a = {abox[0 * Dld + d], abox[1 * Dld + d], abox[2 * Dld + d], abox[3 * Dld + d]};
-        Box b = bfetch(blist[c]);
+        const float4 av = abox[alist[r]];
+        const Box a = {(double)av.x, (double)av.y, (double)av.z, (double)av.w};
+        const Box b = bfetch(blist[c]);
         const double iou = asso_pair(pr.asso_func, a, b, pr.diag);
         if (iou != iou) nanf = 1;
         mx = fmax(mx, iou);
@@ -362,7 +401,7 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
     if (wid == 0) {
         // Only pairs with iou >= thr survive, and the caller re-sorts what is left: any
         // optimal solution gives the same result, so the fast exact solver is used.
-        RectWork w = rect_carve(sm.lapw, nA, nB);
+        RectWork w = rect_carve(sm.work, nA, nB);
         const int bad = rect_solve_warp(DenseCost{cost, nB}, nA, nB, 2.0 * (cmx + 1.0), w, nullptr, nullptr);
         if (bad && lane == 0) sm.misc[M_LAPBAD] = 1;
         for (int r = lane; r < nA; r += 32) {
@@ -377,13 +416,13 @@ __device__ bool ocs_second_round(const OcsState& st, const OcsParams& pr, int s,
     return true;
 }
 
-struct FetchPred {
-    const double* tbox; int Tcap;
+struct FetchPred {     // predicted boxes (global, written by the predict kernel)
+    const double* tb; int Tcap;
     __device__ Box operator()(int p) const {
-        return Box{tbox[0 * Tcap + p], tbox[1 * Tcap + p], tbox[2 * Tcap + p], tbox[3 * Tcap + p]};
+        return Box{tb[AB_X1 * Tcap + p], tb[AB_Y1 * Tcap + p], tb[AB_X2 * Tcap + p], tb[AB_Y2 * Tcap + p]};
     }
 };
-struct FetchLast {
+struct FetchLast {     // last observations (global state)
     const double* lastobs; const int* slot_of; int Tcap;
     __device__ Box operator()(int p) const {
         const int sl = slot_of[p];
@@ -391,68 +430,59 @@ struct FetchLast {
     }
 };
 
-// dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
-// precision: BaseTracker.setup_decorator round-trips every ndarray through float32
-// (boxmot/trackers/basetracker.py:122-128).
-__global__ void __launch_bounds__(K2_NT, 4)
-ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
+__global__ void __launch_bounds__(K2_NT, 8)
+ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const int Tcap = st.Tcap, Dcap = st.Dcap;
-    OcsSmem sm = ocs_carve(smem_raw, Tcap, Dcap, pr.use_byte, st.smem_cost_elems);
+    OcsSmem sm = ocs_carve(smem_raw, Tcap, Dcap, pr.use_byte);
     OcsView v(st, s);
     const float* dsrc = dets + (size_t)s * Dcap * 6;
     int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
     int* upd_det = upd_slot + Dcap;
+    double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;     // operands written by the predict kernel
 
-    // ---- split detections by confidence (ocsort.py:265-275), stable order
-    int nD_in = ndets[s];
-    if (nD_in > Dcap) { if (tid == 0) atomicOr(&v.hdr[OH_ERR], BM_ERR_DET_OVERFLOW); nD_in = Dcap; }
     if (tid < M_COUNT) sm.misc[tid] = 0;
     __syncthreads();
-    if (wid == 0) {
-        int nh = 0, ns = 0;
-        for (int base = 0; base < nD_in; base += 32) {
-            const int i = base + lane;
-            double conf = -1.0;
-            if (i < nD_in) conf = (double)dsrc[i * 6 + 4];
-            const bool hi = i < nD_in && conf > pr.det_thresh;
-            const bool se = pr.use_byte && i < nD_in && conf > pr.min_conf && conf < pr.det_thresh;
-            const unsigned bh = __ballot_sync(BM_FULL, hi), bs = __ballot_sync(BM_FULL, se);
-            const unsigned lt = (1u << lane) - 1;
-            if (hi) {
-                const int p = nh + __popc(bh & lt);
-                for (int c = 0; c < 4; c++) sm.dbox[c * Dcap + p] = (double)dsrc[i * 6 + c];
-                sm.dconf[p] = conf; sm.dind[p] = i;
-            }
-            if (se) {
-                const int p = ns + __popc(bs & lt);
-                for (int c = 0; c < 4; c++) sm.sbox[c * Dcap + p] = (double)dsrc[i * 6 + c];
-                sm.sind[p] = i;
-            }
-            nh += __popc(bh); ns += __popc(bs);
-        }
-        if (lane == 0) { sm.misc[M_ND] = nh; sm.misc[M_NS] = ns; }
-    }
-    // ---- association operands of the predicted tracks (written by K1)
+    // ---- the confidence split (ocsort.py:265-275) was done by the predict launch
+    const int nD = v.hdr[OH_ND], nS = pr.use_byte ? v.hdr[OH_NS] : 0;
     int nT = v.hdr[OH_NLIST];
-    const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
-    for (int e = tid; e < AB_COUNT * nT; e += K2_NT) {
-        const int f = e / nT, p = e - f * nT;
-        const double val = ab[f * Tcap + p];
-        sm.tbox[f * Tcap + p] = val;
-        if (f < 4 && val != val) sm.misc[M_ANYBAD] = 1;
+    {
+        const int* hs = st.hsel + (size_t)s * 2 * Dcap;
+        for (int d = tid; d < nD; d += K2_NT) {
+            const int i = hs[d];
+            sm.dbox[d] = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
+            sm.dind[d] = i;
+            sm.d2t[d] = -1;
+        }
+        for (int r = tid; r < nS; r += K2_NT) {
+            const int i = hs[Dcap + r];
+            sm.sbox[r] = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
+            sm.sind[r] = i;
+        }
     }
-    for (int p = tid; p < nT; p += K2_NT) { sm.slot_of[p] = v.order[p]; sm.t2d[p] = -1; sm.colcnt[p] = 0; }
+    // ---- screening tables of the predicted tracks
+    const OcmCost ocm = {sm.dbox, ab, Tcap, pr.asso_func, pr.diag, pr.inertia};
+    OcmScreen scr;
+    scr.boxf = reinterpret_cast<float4*>(sm.work);
+    scr.kc = reinterpret_cast<double2*>(scr.boxf + Tcap);
+    scr.mvf = reinterpret_cast<float2*>(scr.kc + Tcap);
+    scr.cs = reinterpret_cast<float*>(scr.mvf + Tcap);
+    for (int p = tid; p < nT; p += K2_NT) {
+        sm.slot_of[p] = v.order[p];
+        sm.t2d[p] = -1;
+        sm.colcnt[p] = 0;
+        if (ocm_screen_fill(ocm, scr, p)) sm.misc[M_ANYBAD] = 1;
+    }
     __syncthreads();
     if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288)
         if (tid == 0) {
             int k = 0;
             for (int p = 0; p < nT; p++) {
                 bool nan = false;
-                for (int f = 0; f < 4; f++) nan |= sm.tbox[f * Tcap + p] != sm.tbox[f * Tcap + p];
+                for (int f = 0; f < 4; f++) nan |= ab[f * Tcap + p] != ab[f * Tcap + p];
                 if (nan) continue;
-                for (int f = 0; f < AB_COUNT; f++) sm.tbox[f * Tcap + k] = sm.tbox[f * Tcap + p];
+                for (int f = 0; f < AB_COUNT; f++) ab[f * Tcap + k] = ab[f * Tcap + p];
                 sm.slot_of[k] = sm.slot_of[p];
                 v.order[k] = sm.slot_of[k];
                 k++;
@@ -462,28 +492,20 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         }
         __syncthreads();
         nT = sm.misc[M_NT];
+        for (int p = tid; p < nT; p += K2_NT) ocm_screen_fill(ocm, scr, p);
+        __syncthreads();
     }
-    const int nD = sm.misc[M_ND], nS = sm.misc[M_NS];
-    for (int d = tid; d < nD; d += K2_NT) { sm.d2t[d] = -1; sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
-    __syncthreads();
 
     // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
     // (association.py:427-461), evaluated on demand; permutation fast path (:501-503) or
     // exact LAP (:505-507)
-    const OcmCost ocm = {sm.dbox, Dcap, sm.tbox, Tcap, pr.asso_func, pr.diag, pr.inertia};
     if (nD > 0 && nT > 0) {
-        OcmScreen scr;      // aliases the solver work area (idle until the summaries are done)
-        scr.boxf = reinterpret_cast<float4*>(sm.lapw);
-        scr.mvf = reinterpret_cast<float2*>(scr.boxf + Tcap);
-        scr.cs = reinterpret_cast<float*>(scr.mvf + Tcap);
-        for (int t = tid; t < nT; t += K2_NT) ocm_screen_fill(ocm, scr, t);
-        __syncthreads();
         for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
             double rm; int ra, nhit, lasthit;
             ocm_row_summary(ocm, scr, d, nT, pr.iou_thr, sm.cand + 64 * wid, sm.colcnt, &rm, &ra, &nhit, &lasthit);
             if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
         }
-        __syncthreads();
+        __syncthreads();       // the screening tables are dead from here on (sm.work is reused)
         // permutation fast path: every row/column has at most one IoU hit, at least one exists
         int rmax = 0, cmax_ = 0;
         for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
@@ -494,6 +516,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         }
         const bool fast = rmax == 1 && cmax_ == 1;           // uniform over the CTA
         double* cost = st.scratch + (size_t)s * st.scratch_elems;
+        __shared__ double s_cmx[K2_NT / 32];
         if (!fast && nD > nT) {
             // WHICH zero-gain detections stay unassigned when there are more detections than
             // tracks is decided by lapjv's scan order (the reference's unmatched-detection ORDER,
@@ -507,7 +530,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
                     cmx = fmax(cmx, cc);
                 }
             for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
-            if (lane == 0) sm.wred[wid] = cmx;
+            if (lane == 0) s_cmx[wid] = cmx;
             __syncthreads();
         }
         if (wid == 0) {
@@ -525,14 +548,14 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
                     // Every detection is assigned in every optimal solution (any real entry beats
                     // the padding), so the outcome does not depend on lapjv's tie-breaking and the
                     // fast exact solver applies; the null option is never taken (cost +inf).
-                    RectWork w = rect_carve(sm.lapw, nD, nT);
+                    RectWork w = rect_carve(sm.work, nD, nT);
                     bad = rect_solve_warp(ocm, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
                     xsol = w.x;
                 } else {
-                    double pad = sm.wred[0];
-                    for (int i = 1; i < K2_NT / 32; i++) pad = fmax(pad, sm.wred[i]);
+                    double pad = s_cmx[0];
+                    for (int i = 1; i < K2_NT / 32; i++) pad = fmax(pad, s_cmx[i]);
                     LapMat m = {cost, nT, nD, nT, nD + nT, 1, pad + 1.0};
-                    LapWork w = lap_carve(sm.lapw, nD + nT);
+                    LapWork w = lap_carve(sm.work, nD + nT);
                     bad = lap_solve_warp(m, w);
                     xsol = w.x;
                 }
@@ -586,8 +609,8 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         for (int r = tid; r < nS; r += K2_NT) sm.d2t[r] = r;
         for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = 0;
         __syncthreads();
-        const bool ran = ocs_second_round(st, pr, s, sm, sm.sbox, Dcap, sm.d2t, nS, sm.um_t, nUT,
-                                          FetchPred{sm.tbox, Tcap}, sm.hit_t);
+        const bool ran = ocs_second_round(st, pr, s, sm, Tcap, Dcap, sm.sbox, sm.d2t, nS, sm.um_t, nUT,
+                                          FetchPred{ab, Tcap}, sm.hit_t);
         if (ran) {
             if (wid == 0) {
                 const int n0 = sm.misc[M_NUPD];
@@ -611,7 +634,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, cons
         for (int t = tid; t < nT; t += K2_NT) sm.colcnt[t] = 0;
         for (int d = tid; d < nD; d += K2_NT) sm.rowcnt[d] = 0;
         __syncthreads();
-        const bool ran = ocs_second_round(st, pr, s, sm, sm.dbox, Dcap, sm.um_d, nUD, sm.um_t, nUT,
+        const bool ran = ocs_second_round(st, pr, s, sm, Tcap, Dcap, sm.dbox, sm.um_d, nUD, sm.um_t, nUT,
                                           FetchLast{v.lastobs, sm.slot_of, Tcap}, sm.hit_t);
         if (ran) {
             if (wid == 0) {
@@ -789,21 +812,37 @@ ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, d
 namespace bm {
 
 size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr) {
-    return ocs_smem_bytes(st.Tcap, st.Dcap, pr.use_byte, st.smem_cost_elems);
+    return ocs_smem_bytes(st.Tcap, st.Dcap, pr.use_byte);
 }
 
 cudaError_t ocsort_step_configure(size_t smem) {
     return cudaFuncSetAttribute(ocs_assoc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
+// BM_DEBUG_SYNC=1 in the environment synchronises after every kernel and names the one that
+// faulted (compute-sanitizer is not available on every pool).
+static cudaError_t dbg_check(const char* name, cudaStream_t stream) {
+    static const bool on = [] { const char* e = getenv("BM_DEBUG_SYNC"); return e && e[0] == '1'; }();
+    if (!on) return cudaSuccess;
+    cudaError_t e = cudaStreamSynchronize(stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) fprintf(stderr, "boxmot_b200: kernel %s failed: %s\n", name, cudaGetErrorString(e));
+    return e;
+}
+
 cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
                                double* out, int* nout, cudaStream_t stream) {
     const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
-    ocs_predict_kernel<<<st.S * c1, K1_NT, 0, stream>>>(st, pr);
-    ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets, ndets);
+    cudaError_t e;
+    ocs_predict_kernel<<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets);
+    if ((e = dbg_check("ocs_predict_kernel", stream)) != cudaSuccess) return e;
+    ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
+    if ((e = dbg_check("ocs_assoc_kernel", stream)) != cudaSuccess) return e;
     ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
+    if ((e = dbg_check("ocs_update_kernel", stream)) != cudaSuccess) return e;
     const int nt4 = (st.Tcap + 31) / 32 * 32;
     ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
+    if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
