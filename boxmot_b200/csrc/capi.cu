@@ -53,6 +53,7 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     OcsEngine* e = new (std::nothrow) OcsEngine();
     if (!e) return fail(-3, "out of host memory");
     bm::OcsState& st = e->st;
+    st.prof = nullptr;
     st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap; st.R = cfg->delta_t;
     st.scratch_elems = (size_t)track_cap * det_cap;
     st.smem_cost_elems = smem_cost_bytes / 8;
@@ -146,6 +147,13 @@ int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_upda
     if (err_bits) *err_bits = err;
     if (track_updates) *track_updates = tot;
     if (lap_solves) *lap_solves = laps;
+    return 0;
+}
+
+int bm_ocsort_debug_profile(void* handle, long long* d_stamps) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    e->st.prof = d_stamps;
     return 0;
 }
 

@@ -58,10 +58,18 @@ __device__ __forceinline__ void warp_argmin(double& s, int& j) {
     }
 }
 
+__device__ __forceinline__ double warp_min_rect(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, shfl_xor_d(v, o));
+    return v;
+}
+
 // Cost accessor over a stored row-major matrix.
 struct DenseCost {
+    static constexpr bool kBounded = false;
     const double* c; int ld;
     __device__ __forceinline__ double operator()(int i, int j) const { return c[(size_t)i * ld + j]; }
+    __device__ __forceinline__ double lower(int i, int j, bool* exact) const { *exact = true; return (*this)(i, j); }
 };
 
 // Solve with one warp.  cost(i, j): entry accessor (a stored matrix, or a functor that
@@ -122,7 +130,7 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
         const int r0 = w.fr[f];
         for (int j = lane; j < nc; j += 32) w.spc[j] = CUDART_INF;
         __syncwarp();
-        double minval = 0.0, best_null = CUDART_INF;
+        double minval = 0.0, best_null = CUDART_INF, bfree = CUDART_INF;
         int i = r0, null_row = -1, nsc = 0, sink = -2;
         int guard = nc + 2;
         while (sink == -2) {
@@ -132,6 +140,44 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
             if (cn < best_null) { best_null = cn; null_row = i; }
             double lowest = CUDART_INF;
             int jl = 0x7fffffff;
+            if (CostFn::kBounded) {
+                // Expensive entries: cost.lower(i, j) is a cheap rigorous lower bound.  `bfree` is the
+                // exact distance of the best free column (or the null option) found so far, an upper
+                // bound of the final path length; an entry whose bound cannot beat min(spc[j], bfree)
+                // can neither lie on the shortest path nor be selected before the search ends, and
+                // the duals only read the distances of SCANNED columns, so it is never evaluated.
+                double lbf = CUDART_INF;
+                int jf = 0x7fffffff;
+                for (int j = lane; j < nc; j += 32) {          // pass A: most promising free column
+                    if (w.spc[j] == -CUDART_INF || w.y[j] >= 0) continue;
+                    bool ex;
+                    const double r = minval + ((cost.lower(i, j, &ex) - ui) - w.v[j]);
+                    if (r < lbf) { lbf = r; jf = j; }
+                }
+                warp_argmin(lbf, jf);
+                if (jf != 0x7fffffff && lane == (jf & 31)) {
+                    const double r = minval + ((cost(i, jf) - ui) - w.v[jf]);
+                    if (r < w.spc[jf]) { w.spc[jf] = r; w.path[jf] = i; }
+                }
+                __syncwarp();
+                if (jf != 0x7fffffff) bfree = fmin(bfree, w.spc[jf]);
+                bfree = fmin(bfree, best_null);
+                double nb = CUDART_INF;                         // best free distance after this sweep
+                for (int j = lane; j < nc; j += 32) {          // pass B
+                    double s = w.spc[j];
+                    if (s == -CUDART_INF) continue;
+                    bool ex;
+                    double r = minval + ((cost.lower(i, j, &ex) - ui) - w.v[j]);
+                    if (r < fmin(s, bfree) || (ex && r < s)) {
+                        if (!ex) r = minval + ((cost(i, j) - ui) - w.v[j]);
+                        if (r < s) { s = r; w.spc[j] = r; w.path[j] = i; }
+                    }
+                    if (s < lowest) { lowest = s; jl = j; }
+                    if (w.y[j] < 0) nb = fmin(nb, s);
+                }
+                nb = warp_min_rect(nb);
+                bfree = fmin(bfree, nb);
+            } else
             for (int j = lane; j < nc; j += 32) {
                 double s = w.spc[j];
                 if (s == -CUDART_INF) continue;          // already scanned

@@ -46,6 +46,7 @@ struct OcsState {
     double* abuf;                  // [S][AB_COUNT][Tcap] predicted boxes / OCM operands per list position
     int* upd;                      // [S][2][Dcap] this frame's (slot, detection row) Kalman updates
     int* born;                     // [S][Dcap]    detection rows that start a track, in id order
+    long long* prof;               // optional [S][8] clock64 phase stamps of the association kernel (debug)
     int* hsel;                     // [S][2][Dcap] detection rows of the high-score set, then of the BYTE set
 };
 

@@ -145,7 +145,7 @@ __host__ __device__ inline size_t ocs_work_bytes(int Tcap, int Dcap) {
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte) {
     const size_t d = (size_t)Dcap, t = (size_t)Tcap;
     size_t b = 16 * d * (use_byte ? 2 : 1) + 8 * d + ocs_work_bytes(Tcap, Dcap);
-    b += 4 * ((use_byte ? 7 : 6) * d + 4 * t + M_COUNT + 64 * (K2_NT / 32));
+    b += 4 * ((use_byte ? 7 : 6) * d + 4 * t + M_COUNT + (t + 64) * (K2_NT / 32));
     return (b + 15) / 16 * 16;
 }
 
@@ -205,6 +205,9 @@ __device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, 
 // fp64 operands stay where the predict kernel wrote them (L2-resident global memory); only
 // the fp32 screening tables live in shared memory.
 struct OcmCost {
+    // bounded sweeps (lower()) measured slower than plain exact sweeps on B200: two extra
+    // passes of L2 loads per sweep cost more than the ~140 exact entries they avoid
+    static constexpr bool kBounded = false;
     const float4* dbox;                // high-score detections (shared memory)
     const double* tb; int Tcap;        // operands per track column [AB_COUNT][Tcap] (global, L2)
     int func; double diag, inertia;
@@ -212,10 +215,12 @@ struct OcmCost {
     // velocity-direction term; exactly 0 for a track that was never observed (valid = 0)
     // or has no velocity yet (vx = vy = 0 -> cos = 0 -> arccos = pi/2 exactly)
     __device__ __forceinline__ double motion(double cxd, double cyd, int t) const {
-        const double vx = tb[AB_VX * Tcap + t], vy = tb[AB_VY * Tcap + t];
-        if (tb[AB_KVALID * Tcap + t] == 0.0 || (vx == 0.0 && vy == 0.0)) return 0.0;
+        // all operands are fetched up front (one L2 round trip instead of three dependent ones)
+        const double vx = tb[AB_VX * Tcap + t], vy = tb[AB_VY * Tcap + t], valid = tb[AB_KVALID * Tcap + t];
+        const double kx = tb[AB_KCX * Tcap + t], ky = tb[AB_KCY * Tcap + t];
+        if (valid == 0.0 || (vx == 0.0 && vy == 0.0)) return 0.0;
         // speed_direction_batch(dets, previous_obs)  (association.py:10-20)
-        double dx = cxd - tb[AB_KCX * Tcap + t], dy = cyd - tb[AB_KCY * Tcap + t];
+        double dx = cxd - kx, dy = cyd - ky;
         const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
         dx = dx / norm; dy = dy / norm;
         double cs = vx * dx + vy * dy;
@@ -231,14 +236,40 @@ struct OcmCost {
         return Box{tb[AB_X1 * Tcap + t], tb[AB_Y1 * Tcap + t], tb[AB_X2 * Tcap + t], tb[AB_Y2 * Tcap + t]};
     }
     __device__ __forceinline__ double entry(const Box& a, double cxd, double cyd, int t, double* iou_out) const {
-        const double iou = asso_pair(func, a, trk(t), diag);
+        const Box b = trk(t);
+        const double m = motion(cxd, cyd, t);        // issues its loads before the IoU arithmetic
+        const double iou = asso_pair(func, a, b, diag);
         *iou_out = iou;
-        return -(iou + motion(cxd, cyd, t));
+        return -(iou + m);
     }
     __device__ __forceinline__ double operator()(int d, int t) const {
         const Box a = det(d);
         double iou;
         return entry(a, (a.x1 + a.x2) / 2.0, (a.y1 + a.y2) / 2.0, t, &iou);
+    }
+    // Cheap rigorous lower bound of cost(d, t) for the solver's sweeps (*exact = true when the
+    // returned value IS the entry).  asso_func = iou only: boxes that do not overlap give
+    // cost = -motion exactly, and motion <= inertia * asin(cos + eps) / pi with cos taken in
+    // fp32 (error << eps); everything else is evaluated exactly.
+    __device__ __forceinline__ double lower(int d, int t, bool* exact) const {
+        const Box a = det(d), b = trk(t);
+        const double w = fmin(a.x2, b.x2) - fmax(a.x1, b.x1), h = fmin(a.y2, b.y2) - fmax(a.y1, b.y1);
+        const double den = (a.x2 - a.x1) * (a.y2 - a.y1) + (b.x2 - b.x1) * (b.y2 - b.y1);
+        const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
+        if (func != ASSO_IOU || !((w <= 0.0 || h <= 0.0) && den > 0.0)) {
+            double iou;
+            *exact = true;
+            return entry(a, cxd, cyd, t, &iou);
+        }
+        const double vx = tb[AB_VX * Tcap + t], vy = tb[AB_VY * Tcap + t];
+        if (tb[AB_KVALID * Tcap + t] == 0.0 || (vx == 0.0 && vy == 0.0)) { *exact = true; return -0.0; }
+        *exact = false;
+        const float dx = (float)(cxd - tb[AB_KCX * Tcap + t]), dy = (float)(cyd - tb[AB_KCY * Tcap + t]);
+        const float n2 = dx * dx + dy * dy;
+        const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
+        const float cs = __fdividef((float)vx * dx + (float)vy * dy, nrm + 1e-6f);
+        const double ub = (double)asinf(fminf(1.f, cs + 2e-5f)) + 4e-6;  // >= asin(true cos)
+        return -(ub * (1.0 / CUDART_PI) * inertia + 1e-12);
     }
 };
 
@@ -260,90 +291,127 @@ __device__ inline bool ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, in
 constexpr float OCM_BAND = 1e-4f;   // >> error of the fp32 cosine (~1e-6), << spacing of candidates
 constexpr float OCM_NOCAND = -4.f;
 
-// Row summaries for the solver and the permutation fast path, one warp per row:
-// exact minimum / argmin of the row, number of IoU hits (> thr) and the last hit column.
+// Row summaries for the solver and the permutation fast path: exact minimum / argmin of
+// every row, number of IoU hits (> thr) and the last hit column.  Each warp scans its rows
+// (d = warp, warp + W, ...) one after the other.
 // With asso_func = iou an entry whose boxes do not overlap is exactly -(0 + motion), and
 // motion is a monotone function of the OCM cosine, so only (i) entries whose outward-rounded
 // float boxes overlap and (ii) the remaining entries whose fp32 cosine is within OCM_BAND of
 // the row's best are evaluated in fp64 (the rest provably cannot be the minimum); entries
 // whose motion is exactly 0 compete as -0.0.  Other association functions, and detections
-// with a degenerate box, evaluate every entry.
-__device__ inline void ocm_row_summary(const OcmCost& c, const OcmScreen& sc, int d, int nT, double iou_thr,
-                                       int* cand /*[64] per warp*/, int* colcnt, double* rm_out, int* ra_out,
-                                       int* nhit_out, int* last_out) {
-    const int lane = lane_id();
-    const Box a = c.det(d);
-    const double cxd = (a.x1 + a.x2) / 2.0, cyd = (a.y1 + a.y2) / 2.0;
-    const bool sparse = c.func == ASSO_IOU && (a.x2 - a.x1) * (a.y2 - a.y1) > 0.0 && a.x2 > a.x1;
-    const float4 af = c.dbox[d];
-    float* csrow = sc.cs + (size_t)warp_id() * c.Tcap;
-    double rm = CUDART_INF;
-    int ra = 0x7fffffff, nhit = 0, lasthit = -1, ncand = 0, zero_t = 0x7fffffff;
-    float m32 = -CUDART_INF_F;
+// with a degenerate box, evaluate every entry.  The exact evaluations are batched ACROSS rows
+// (one lane per candidate, segmented arg-min per row), flushed at row boundaries.
+// Outputs (shared memory, pre-set by the caller to +inf / INT_MAX / 0 / -1): rmin, rarg,
+// rowcnt, hit_t; colcnt accumulates the per-column hits; zero_t is scratch [nD].
+__device__ inline void ocm_scan_rows(const OcmCost& c, const OcmScreen& sc, int nD, int nT, double iou_thr,
+                                     int* cand /*[Tcap + 64] per warp*/, int* colcnt, double* rmin, int* rarg,
+                                     int* rowcnt, int* hit_t, int* zero_ts) {
+    const int lane = lane_id(), wid = warp_id(), NW = blockDim.x >> 5;
+    float* csrow = sc.cs + (size_t)wid * c.Tcap;
+    int ncand = 0;
     auto flush = [&]() {
         __syncwarp();
-        for (int k = lane; k < ncand; k += 32) {
-            const int t = cand[k];
-            double iou;
-            const double cc = c.entry(a, cxd, cyd, t, &iou);
-            if (cc < rm || (cc == rm && t < ra)) { rm = cc; ra = t; }
-            if (iou > iou_thr) { nhit++; lasthit = max(lasthit, t); atomicAdd(&colcnt[t], 1); }
+        for (int k0 = 0; k0 < ncand; k0 += 32) {
+            const int k = k0 + lane;
+            const bool valid = k < ncand;
+            const int pk = valid ? cand[k] : 0;
+            const int d = pk >> 16;
+            int t = pk & 0xffff;
+            double cc = CUDART_INF;
+            if (valid) {
+                const Box a = c.det(d);
+                double iou;
+                cc = c.entry(a, (a.x1 + a.x2) / 2.0, (a.y1 + a.y2) / 2.0, t, &iou);
+                if (iou > iou_thr) { atomicAdd(&rowcnt[d], 1); atomicMax(&hit_t[d], t); atomicAdd(&colcnt[t], 1); }
+            }
+            const int row = valid ? d : -1 - lane;           // rows are contiguous in the buffer
+            const int prev = __shfl_up_sync(BM_FULL, row, 1);
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const double occ = __shfl_down_sync(BM_FULL, cc, o);
+                const int ot = __shfl_down_sync(BM_FULL, t, o), orow = __shfl_down_sync(BM_FULL, row, o);
+                if (lane + o < 32 && orow == row && (occ < cc || (occ == cc && ot < t))) { cc = occ; t = ot; }
+            }
+            if (valid && (lane == 0 || prev != row)) {       // segment head merges into the row state
+                const double cur = rmin[d];
+                if (cc < cur || (cc == cur && t < rarg[d])) { rmin[d] = cc; rarg[d] = t; }
+            }
+            __syncwarp();
         }
         ncand = 0;
-        __syncwarp();
     };
-    auto push = [&](bool pred, int t) {
+    auto push = [&](bool pred, int d, int t) {
         const unsigned b = __ballot_sync(BM_FULL, pred);
-        if (pred) cand[ncand + __popc(b & ((1u << lane) - 1))] = t;
+        if (pred) cand[ncand + __popc(b & ((1u << lane) - 1))] = (d << 16) | t;
         ncand += __popc(b);
-        if (ncand > 32) flush();
     };
-    for (int base = 0; base < nT; base += 32) {
-        const int t = base + lane;
-        bool ex = false;
-        if (t < nT) {
-            float csv = OCM_NOCAND;
-            ex = true;
-            if (sparse) {
-                const float4 b = sc.boxf[t];
-                ex = af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w;
-                if (!ex) {
-                    const float2 mv = sc.mvf[t];
-                    if (mv.x == 0.f && mv.y == 0.f) zero_t = min(zero_t, t);
-                    else {
-                        const double2 k = sc.kc[t];
-                        const float dx = (float)(cxd - k.x), dy = (float)(cyd - k.y);
-                        const float n2 = dx * dx + dy * dy;
-                        const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
-                        csv = __fdividef(mv.x * dx + mv.y * dy, nrm + 1e-6f);
-                        m32 = fmaxf(m32, csv);
+    for (int d = wid; d < nD; d += NW) {
+        const float4 af = c.dbox[d];
+        const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
+        const bool sparse = c.func == ASSO_IOU &&
+                            ((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x;
+        int zero_t = 0x7fffffff;
+        float m32 = -CUDART_INF_F;
+        for (int base = 0; base < nT; base += 128) {         // 4 independent chunks in flight
+            bool ex[4];
+            float csv[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int t = base + 32 * u + lane;
+                ex[u] = false;
+                csv[u] = OCM_NOCAND;
+                if (t < nT) {
+                    ex[u] = true;
+                    if (sparse) {
+                        const float4 b = sc.boxf[t];
+                        ex[u] = af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w;
+                        if (!ex[u]) {
+                            const float2 mv = sc.mvf[t];
+                            if (mv.x == 0.f && mv.y == 0.f) zero_t = min(zero_t, t);
+                            else {
+                                const double2 kc = sc.kc[t];
+                                const float dx = (float)(cxd - kc.x), dy = (float)(cyd - kc.y);
+                                const float n2 = dx * dx + dy * dy;
+                                const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
+                                csv[u] = __fdividef(mv.x * dx + mv.y * dy, nrm + 1e-6f);
+                                m32 = fmaxf(m32, csv[u]);
+                            }
+                        }
                     }
                 }
             }
-            csrow[t] = csv;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int t = base + 32 * u + lane;
+                if (base + 32 * u < nT) {                    // warp-uniform
+                    if (t < nT) csrow[t] = csv[u];
+                    push(ex[u], d, t);
+                }
+            }
         }
-        push(ex, t);
-    }
-    if (sparse) {
-        for (int o = 16; o > 0; o >>= 1) {
-            m32 = fmaxf(m32, __shfl_xor_sync(BM_FULL, m32, o));
-            zero_t = min(zero_t, __shfl_xor_sync(BM_FULL, zero_t, o));
+        if (sparse) {
+            for (int o = 16; o > 0; o >>= 1) {
+                m32 = fmaxf(m32, __shfl_xor_sync(BM_FULL, m32, o));
+                zero_t = min(zero_t, __shfl_xor_sync(BM_FULL, zero_t, o));
+            }
+            const float lim = m32 - OCM_BAND;
+            __syncwarp();
+            for (int base = 0; base < nT; base += 32) {
+                const int t = base + lane;
+                const float v = t < nT ? csrow[t] : OCM_NOCAND;
+                push(v >= lim && v != OCM_NOCAND, d, t);
+            }
         }
-        const float lim = m32 - OCM_BAND;
-        for (int base = 0; base < nT; base += 32) {
-            const int t = base + lane;
-            push(t < nT && csrow[t] >= lim && csrow[t] != OCM_NOCAND, t);
-        }
+        if (lane == 0) zero_ts[d] = zero_t;
+        if (ncand >= 32) flush();
     }
     flush();
-    warp_argmin(rm, ra);
-    for (int o = 16; o > 0; o >>= 1) {
-        nhit += __shfl_xor_sync(BM_FULL, nhit, o);
-        lasthit = max(lasthit, __shfl_xor_sync(BM_FULL, lasthit, o));
-    }
     // zero-motion, zero-IoU entries hold -(0.0 + 0.0) = -0.0
-    if (zero_t != 0x7fffffff && (-0.0 < rm || (-0.0 == rm && zero_t < ra))) { rm = -0.0; ra = zero_t; }
-    *rm_out = rm; *ra_out = ra; *nhit_out = nhit; *last_out = lasthit;
+    for (int d = wid + lane * NW; d < nD; d += 32 * NW) {
+        const int zt = zero_ts[d];
+        const double rm = rmin[d];
+        if (zt != 0x7fffffff && (-0.0 < rm || (-0.0 == rm && zt < rarg[d]))) { rmin[d] = -0.0; rarg[d] = zt; }
+    }
 }
 
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
@@ -442,6 +510,9 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     int* upd_det = upd_slot + Dcap;
     double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;     // operands written by the predict kernel
 
+    long long* prof = st.prof ? st.prof + (size_t)s * 8 : nullptr;
+#define BM_STAMP(k) do { if (prof && tid == 0) prof[k] = clock64(); } while (0)
+    BM_STAMP(0);
     if (tid < M_COUNT) sm.misc[tid] = 0;
     __syncthreads();
     // ---- the confidence split (ocsort.py:265-275) was done by the predict launch
@@ -454,6 +525,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
             sm.dbox[d] = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
             sm.dind[d] = i;
             sm.d2t[d] = -1;
+            sm.rmin[d] = CUDART_INF; sm.rarg[d] = 0x7fffffff; sm.rowcnt[d] = 0; sm.hit_t[d] = -1;
         }
         for (int r = tid; r < nS; r += K2_NT) {
             const int i = hs[Dcap + r];
@@ -496,16 +568,15 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
         __syncthreads();
     }
 
+    BM_STAMP(1);
     // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
     // (association.py:427-461), evaluated on demand; permutation fast path (:501-503) or
     // exact LAP (:505-507)
     if (nD > 0 && nT > 0) {
-        for (int d = wid; d < nD; d += K2_NT / 32) {      // one warp per detection row
-            double rm; int ra, nhit, lasthit;
-            ocm_row_summary(ocm, scr, d, nT, pr.iou_thr, sm.cand + 64 * wid, sm.colcnt, &rm, &ra, &nhit, &lasthit);
-            if (lane == 0) { sm.rmin[d] = rm; sm.rarg[d] = ra; sm.rowcnt[d] = nhit; sm.hit_t[d] = lasthit; }
-        }
+        ocm_scan_rows(ocm, scr, nD, nT, pr.iou_thr, sm.cand + (Tcap + 64) * wid, sm.colcnt, sm.rmin, sm.rarg,
+                      sm.rowcnt, sm.hit_t, sm.um_d);
         __syncthreads();       // the screening tables are dead from here on (sm.work is reused)
+        BM_STAMP(2);
         // permutation fast path: every row/column has at most one IoU hit, at least one exists
         int rmax = 0, cmax_ = 0;
         for (int d = lane; d < nD; d += 32) rmax = max(rmax, sm.rowcnt[d]);
@@ -583,6 +654,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
         for (int d = tid; d < nD; d += K2_NT) { sm.rowcnt[d] = 0; sm.hit_t[d] = -1; }
         __syncthreads();
     }
+    BM_STAMP(3);
     // ---- unmatched lists in the reference's order (repair R3): never-assigned ascending,
     // then IoU-rejected pairs in detection-row order; matched pairs go to the update list
     if (wid == 0) {
@@ -603,6 +675,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     }
     __syncthreads();
 
+    BM_STAMP(4);
     // ---- BYTE round on the low-score detections (ocsort.py:330-356)
     int nUD = sm.misc[M_NUD], nUT = sm.misc[M_NUT];
     if (pr.use_byte && nS > 0 && nUT > 0) {
@@ -659,6 +732,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
             nUD = sm.misc[M_NUD];
         }
     }
+    BM_STAMP(5);
     // ---- births: ids are handed out in unmatched-detection list order (ocsort.py:392-413)
     int* born = st.born + (size_t)s * Dcap;
     for (int r = tid; r < nUD; r += K2_NT) born[r] = sm.dind[sm.um_d[r]];
@@ -667,7 +741,9 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
         v.hdr[OH_NBORN] = nUD;
         v.hdr[OH_MATCH] += sm.misc[M_NUPD];
         if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
-    }
+        BM_STAMP(6);
+#undef BM_STAMP
+}
 }
 
 // ============================================================================ K3

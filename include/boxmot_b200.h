@@ -54,6 +54,9 @@ int bm_ocsort_status(void* handle, int* err_bits, unsigned long long* track_upda
  * `stream`): out4 = {track_updates, lap_solves, matches (Kalman updates with a
  * detection), births}.  Used by bench.py for the algorithmic-bytes figure. */
 int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream);
+/* Debug: when d_stamps (device, [S][8] int64) is non-null the association kernel records
+ * clock64() at its phase boundaries for every stream; pass NULL to switch it off. */
+int bm_ocsort_debug_profile(void* handle, long long* d_stamps);
 /* Debug / test access: copy one stream's list length and per-track Kalman state
  * (list order) to host buffers x[track_cap*7], P[track_cap*49], ids[track_cap]. */
 int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
