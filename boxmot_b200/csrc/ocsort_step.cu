@@ -1,4 +1,4 @@
-// OC-SORT frame step: FIVE launches advance every stream of the engine by one frame,
+// OC-SORT frame step: FOUR launches advance every stream of the engine by one frame,
 // with no host synchronisation in between (all lifecycle decisions are made on the device).
 // Mirrors OcSort.update (boxmot/trackers/ocsort/ocsort.py:246-439) and enhanced_associate
 // (boxmot/utils/association.py:377-533 with repairs R1-R3).
@@ -6,19 +6,18 @@
 //   K1 ocs_predict_kernel   thread per live track        Kalman predict (ocsort.py:281-288,
 //                           (HBM-streaming, SoA state)   :173-186) + association operands
 //                                                        and the confidence split (:265-275)
-//   K2a ocs_rowsum_kernel   warp per cost-matrix row     exact row minima / IoU-hit counts of the
-//                           (throughput kernel)          IoU + OCM cost (association.py:427-461),
-//                                                        fp32-screened, matrix never materialised
-//   K2b ocs_assoc_kernel    CTA per stream               permutation fast path or exact LAP with
-//                           (latency bound)              on-demand cost rows, BYTE (:330-356) and
-//                                                        OCR (:358-386) rounds
+//   K2 ocs_assoc_kernel     CTA (2 warps) per stream     exact row minima of the IoU + OCM cost
+//                           (latency bound)              (association.py:427-461; fp32-screened,
+//                                                        matrix never materialised), permutation
+//                                                        fast path or exact LAP with on-demand
+//                                                        cost rows, BYTE (:330-356), OCR (:358-386)
 //   K3 ocs_update_kernel    thread per matched track     Kalman update + ORU (:321-324,
 //                           (HBM-streaming)              xysr_kf.py:211-291)
 //   K4 ocs_finalize_kernel  CTA per stream               misses, births, output rows, dead-track
 //                                                        removal (:388-439)
 //
-// Splitting the step keeps the register-heavy fp64 Kalman code (255 registers/thread) out
-// of the association CTA, whose occupancy would otherwise be 2 CTAs/SM.
+// Splitting the step keeps the register-heavy fp64 Kalman code out of the association CTA,
+// whose occupancy would otherwise be 2 CTAs/SM.
 #include "ocsort_engine.cuh"
 #include "lap_rect.cuh"
 #include <cstdio>
@@ -866,7 +865,9 @@ ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, d
 #pragma unroll
             for (int c = 0; c < 4; c++) b[c] = lo[c];
         }
-        double* o = out + ((size_t)s * Tcap + k) * 8;
+        // every emitted row belongs to a track that received a detection this frame (or was born
+        // from one), so min(Tcap, Dcap) rows per stream always suffice
+        double* o = out + ((size_t)s * min(Tcap, Dcap) + k) * 8;
         o[0] = b[0]; o[1] = b[1]; o[2] = b[2]; o[3] = b[3];
         o[4] = (double)(v.I(OI_ID, slot) + 1);
         o[5] = v.confcls[0 * Tcap + slot];

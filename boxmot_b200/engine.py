@@ -46,7 +46,8 @@ class OcSortEngine:
                                                    int(smem_cost_bytes), ctypes.byref(self._h)),
                        "bm_ocsort_create")
             torch.cuda.synchronize(self.device)
-        self.out = torch.zeros((self.S, self.Tcap, 8), dtype=torch.float64, device=self.device)
+        self.out_rows = min(self.Tcap, self.Dcap)
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
         self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
         self.launches = 0
 
@@ -65,18 +66,22 @@ class OcSortEngine:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().bm_ocsort_reset(self._h, _stream_ptr(self.device)), "bm_ocsort_reset")
 
-    def step(self, dets, ndets):
+    def step(self, dets, ndets, out=None, nout=None):
         """dets: float32 cuda tensor [S, det_cap, 6]; ndets: int32 cuda tensor [S].
-        Asynchronous; returns the engine-owned (out [S,track_cap,8] f64, nout [S] i32)."""
+        Asynchronous; returns (out [S,out_rows,8] f64, nout [S] i32) -- the engine-owned
+        buffers unless the caller passes its own (e.g. to double-buffer the D2H copy)."""
         assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
         assert tuple(dets.shape) == (self.S, self.Dcap, 6)
         assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().bm_ocsort_step(self._h, _ptr(dets), _ptr(ndets), _ptr(self.out),
-                                                 _ptr(self.nout), _stream_ptr(self.device)),
+            _lib.check(_lib.lib().bm_ocsort_step(self._h, _ptr(dets), _ptr(ndets), _ptr(out),
+                                                 _ptr(nout), _stream_ptr(self.device)),
                        "bm_ocsort_step")
-        self.launches += 1
-        return self.out, self.nout
+        self.launches += 4      # predict, assoc, update, finalize
+        return out, nout
 
     def status(self, raise_on_error=True):
         err = ctypes.c_int(0)
@@ -119,7 +124,7 @@ class OcSortEngine:
             self._h_nd = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
             self._d_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32, device=self.device)
             self._d_nd = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
-            self._h_out = torch.zeros((self.S, self.Tcap, 8), dtype=torch.float64).pin_memory()
+            self._h_out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64).pin_memory()
             self._h_nout = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
         hd = self._h_dets.numpy()
         hn = self._h_nd.numpy()
@@ -138,3 +143,57 @@ class OcSortEngine:
         torch.cuda.current_stream(self.device).synchronize()
         ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
         return [ho[s, : hn2[s]].copy() for s in range(self.S)]
+
+
+class HostPipeline:
+    """Double-buffered host <-> device pipeline around ``OcSortEngine.step``: while frame f
+    is being associated, the detections of frame f+1 upload on a copy stream and the rows
+    of frame f-1 download on another.  ``submit`` returns the finished result of the
+    PREVIOUS frame (numpy views of pinned buffers, valid until the next ``submit``)."""
+
+    def __init__(self, engine):
+        e = self.eng = engine
+        dev = e.device
+        self.s_in, self.s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        mk = lambda shape, dt: [torch.zeros(shape, dtype=dt, device=dev) for _ in range(2)]
+        pin = lambda shape, dt: [torch.zeros(shape, dtype=dt).pin_memory() for _ in range(2)]
+        self.d_dets, self.d_nd = mk((e.S, e.Dcap, 6), torch.float32), mk((e.S,), torch.int32)
+        self.d_out, self.d_nout = mk((e.S, e.out_rows, 8), torch.float64), mk((e.S,), torch.int32)
+        self.h_out, self.h_nout = pin((e.S, e.out_rows, 8), torch.float64), pin((e.S,), torch.int32)
+        self.ev_in = [torch.cuda.Event() for _ in range(2)]
+        self.ev_comp = [torch.cuda.Event() for _ in range(2)]
+        self.ev_out = [torch.cuda.Event() for _ in range(2)]
+        self.n = 0
+        self.h2d_bytes = e.S * e.Dcap * 6 * 4 + e.S * 4
+        self.d2h_bytes = e.S * e.out_rows * 8 * 8 + e.S * 4
+
+    def submit(self, h_dets, h_nd):
+        """h_dets [S,det_cap,6] float32 / h_nd [S] int32 pinned host tensors of the next frame."""
+        b = self.n & 1
+        cur = torch.cuda.current_stream(self.eng.device)
+        if self.n >= 2:
+            self.s_in.wait_event(self.ev_comp[b])      # frame n-2 has consumed d_dets[b]
+        with torch.cuda.stream(self.s_in):
+            self.d_dets[b].copy_(h_dets, non_blocking=True)
+            self.d_nd[b].copy_(h_nd, non_blocking=True)
+            self.ev_in[b].record(self.s_in)
+        cur.wait_event(self.ev_in[b])
+        if self.n >= 2:
+            cur.wait_event(self.ev_out[b])             # rows of frame n-2 have left d_out[b]
+        self.eng.step(self.d_dets[b], self.d_nd[b], out=self.d_out[b], nout=self.d_nout[b])
+        self.ev_comp[b].record(cur)
+        self.s_out.wait_event(self.ev_comp[b])
+        with torch.cuda.stream(self.s_out):
+            self.h_out[b].copy_(self.d_out[b], non_blocking=True)
+            self.h_nout[b].copy_(self.d_nout[b], non_blocking=True)
+            self.ev_out[b].record(self.s_out)
+        self.n += 1
+        return self._result(1 - b) if self.n >= 2 else None
+
+    def _result(self, b):
+        self.ev_out[b].synchronize()
+        return self.h_out[b].numpy(), self.h_nout[b].numpy()
+
+    def drain(self):
+        """Result of the last submitted frame."""
+        return self._result((self.n - 1) & 1) if self.n else None

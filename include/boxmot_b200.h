@@ -41,8 +41,10 @@ int bm_ocsort_destroy(void* handle);
 int bm_ocsort_reset(void* handle, void* stream);
 /* One frame for all streams.  d_dets [S][det_cap][6] float32 (x1,y1,x2,y2,conf,cls):
  * float32 is the reference's own input precision (basetracker.py:122-128 converts every
- * ndarray).  d_ndets [S] int32.  d_out [S][track_cap][8] float64 rows
- * (x1,y1,x2,y2,id,conf,cls,det_ind) in the reference's row order, d_nout [S] int32. */
+ * ndarray).  d_ndets [S] int32.  d_out [S][out_rows][8] float64 rows
+ * (x1,y1,x2,y2,id,conf,cls,det_ind) in the reference's row order, out_rows =
+ * min(track_cap, det_cap) (a row is only emitted for a track that received a detection
+ * this frame), d_nout [S] int32. */
 int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
                    int* d_nout, void* stream);
 /* Synchronises `stream`; returns the OR of all per-stream error bits in *err_bits, the

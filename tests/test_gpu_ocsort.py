@@ -81,3 +81,35 @@ def test_input_validation_matches_reference_asserts():
         trk.update([[0, 0, 1, 1, 0.9, 0]], IMG)
     out = trk.update(np.empty((0, 6)), IMG)
     assert out.size == 0
+
+
+def test_host_pipeline_matches_direct_stepping():
+    """The double-buffered H2D / step / D2H pipeline returns, one frame late, exactly the
+    rows a synchronous step returns."""
+    from boxmot_b200.engine import HostPipeline, OcSortEngine
+    from boxmot_b200.synth import make_batch
+    S, K, F, D = 16, 30, 20, 64
+    dets, nd = make_batch(S, K, F, D, first_stream=300)
+    h_dets = torch.as_tensor(dets.astype(np.float32)).pin_memory()
+    h_nd = torch.as_tensor(nd).pin_memory()
+    ref = OcSortEngine(S, track_cap=128, det_cap=D, **OCSORT_YAML)
+    want = []
+    for f in range(F):
+        out, nout = ref.step(h_dets[f].cuda(), h_nd[f].cuda())
+        want.append((out.cpu().numpy().copy(), nout.cpu().numpy().copy()))
+    eng = OcSortEngine(S, track_cap=128, det_cap=D, **OCSORT_YAML)
+    pipe = HostPipeline(eng)
+    got = []
+    for f in range(F):
+        r = pipe.submit(h_dets[f], h_nd[f])
+        if r is not None:
+            got.append((r[0].copy(), r[1].copy()))
+    r = pipe.drain()
+    got.append((r[0].copy(), r[1].copy()))
+    eng.status()
+    assert len(got) == F
+    for f in range(F):
+        assert np.array_equal(got[f][1], want[f][1])
+        for s in range(S):
+            n = want[f][1][s]
+            assert np.array_equal(got[f][0][s, :n], want[f][0][s, :n])
