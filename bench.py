@@ -209,6 +209,23 @@ def alg_bytes(track_updates, matches, births, dets_in, rows_out):
             + 4 * (track_updates + dets_in) + 64 * track_updates + 64 * rows_out + 160 * births)
 
 
+def per_kernel(ksum_ms, steps, cnt, dets_in):
+    """Live CUDA-event time of each of the four launches (averaged over `steps` L2-flushed
+    steps) next to its share of the algorithmic bytes (the terms of alg_bytes)."""
+    T, M, B = cnt["track_updates"], cnt["matches"], cnt["births"]
+    nbytes = {"ocs_predict_kernel": 2 * 160 * T,
+              "ocs_assoc_kernel": 24 * dets_in + 4 * (T + dets_in),
+              "ocs_update_kernel": (2 * 160 + 32) * M,
+              "ocs_finalize_kernel": 64 * T + 64 * M + 160 * B}
+    tot = float(sum(ksum_ms)) or 1.0
+    out = []
+    for (name, nb), ms in zip(nbytes.items(), ksum_ms):
+        out.append({"kernel": name, "avg_ms": float(ms) / steps, "share": float(ms) / tot,
+                    "alg_bytes_per_launch": nb / steps,
+                    "achieved_gbs": nb / (float(ms) * 1e-3) / 1e9 if ms > 0 else None})
+    return out
+
+
 def run_gpu_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -272,6 +289,25 @@ def run_gpu_arm(args):
         eng.step(d_dets[f], d_nd[f])
 
     ms_dev, wall_dev, cnt, clocks = timed(step_dev)
+
+    # (1b) per-kernel breakdown of the same steps: the library brackets its four launches with
+    # CUDA events on the launching stream (bm_ocsort_time_kernels); separate short pass so the
+    # extra event records never sit inside the headline timing.
+    KB = min(K, 100)
+    eng.reset()
+    for f in range(W):
+        step_dev(f)
+    eng.time_kernels(True)
+    ksum = np.zeros(4)
+    ck0 = eng.counters()
+    for i in range(KB):
+        if not args.no_flush:
+            flush_buf.zero_()
+        step_dev(W + i)
+        ksum += eng.kernel_times()
+    ck1 = eng.counters()
+    eng.time_kernels(False)
+    kcnt = {k: ck1[k] - ck0[k] for k in ck1}
 
     # (2) end to end through the public host-buffer API (boxmot_b200.engine.HostPipeline):
     # every step uploads that frame's detections from pinned host memory and downloads its
@@ -349,7 +385,9 @@ def run_gpu_arm(args):
                          "frac": achieved / peak, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "kernel": "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize", "alg_bytes_per_launch": nbytes / K,
-                         "avg_launch_ms": ms_dev / K},
+                         "avg_launch_ms": ms_dev / K,
+                         "per_kernel": per_kernel(ksum, KB, kcnt, int(nd[W:W + KB].sum())),
+                         "dominant_kernel": "ocs_assoc_kernel"},
             "gpu_launches": 4 * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,

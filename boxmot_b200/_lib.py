@@ -33,6 +33,8 @@ _SIGS = {
                                  ctypes.POINTER(ctypes.c_ulonglong), c_void_p]),
     "bm_ocsort_counters": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_ulonglong * 4), c_void_p]),
     "bm_ocsort_debug_profile": (c_int, [c_void_p, c_void_p]),
+    "bm_ocsort_time_kernels": (c_int, [c_void_p, c_int]),
+    "bm_ocsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 4)]),
     "bm_ocsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p,
                                c_void_p, c_void_p]),
     "bm_lap_solve_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,

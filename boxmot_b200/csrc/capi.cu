@@ -28,6 +28,8 @@ struct OcsEngine {
     bm::OcsParams pr;
     std::vector<void*> allocs;
     size_t smem;
+    cudaEvent_t ev[5];
+    bool timing = false, timed = false;
 };
 
 template <typename T>
@@ -96,6 +98,7 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
 int bm_ocsort_destroy(void* handle) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e) return 0;
+    if (e->timing) for (int i = 0; i < 5; i++) cudaEventDestroy(e->ev[i]);
     for (void* p : e->allocs) cudaFree(p);
     delete e;
     return 0;
@@ -121,7 +124,30 @@ int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_ocsort_step: null argument");
     BM_CUDA(bm::ocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
-                                   static_cast<cudaStream_t>(stream)));
+                                   static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    e->timed = e->timing;
+    return 0;
+}
+
+int bm_ocsort_time_kernels(void* handle, int enable) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    if (enable && !e->timing) {
+        for (int i = 0; i < 5; i++) BM_CUDA(cudaEventCreate(&e->ev[i]));
+        e->timing = true;
+    } else if (!enable && e->timing) {
+        for (int i = 0; i < 5; i++) cudaEventDestroy(e->ev[i]);
+        e->timing = e->timed = false;
+    }
+    return 0;
+}
+
+int bm_ocsort_kernel_times(void* handle, float* ms4) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !ms4) return fail(-1, "bm_ocsort_kernel_times: bad argument");
+    if (!e->timed) return fail(-1, "bm_ocsort_kernel_times: no timed step (call bm_ocsort_time_kernels first)");
+    BM_CUDA(cudaEventSynchronize(e->ev[4]));
+    for (int i = 0; i < 4; i++) BM_CUDA(cudaEventElapsedTime(&ms4[i], e->ev[i], e->ev[i + 1]));
     return 0;
 }
 

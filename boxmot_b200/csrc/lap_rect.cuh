@@ -66,7 +66,7 @@ __device__ __forceinline__ double warp_min_rect(double v) {
 
 // Cost accessor over a stored row-major matrix.
 struct DenseCost {
-    static constexpr bool kBounded = false;
+    static constexpr bool kBounded = false, kStaged = false;
     const double* c; int ld;
     __device__ __forceinline__ double operator()(int i, int j) const { return c[(size_t)i * ld + j]; }
     __device__ __forceinline__ double lower(int i, int j, bool* exact) const { *exact = true; return (*this)(i, j); }
@@ -74,6 +74,9 @@ struct DenseCost {
 
 // Solve with one warp.  cost(i, j): entry accessor (a stored matrix, or a functor that
 // evaluates the entry on demand -- the solver only touches the rows it sweeps).
+// A cost functor with kStaged = true gets cost.stage(i, spc) called (by the whole warp,
+// converged) before every sweep of row i -- it may evaluate the row into a buffer with the
+// help of other warps, skipping columns with spc[j] == -inf -- and must be given rowmin.
 // rowmin/rowarg: optional per-row minimum and its column (computed by the caller while
 // the costs were generated); pass nullptr to have the warp compute them.
 // On return w.x[i] = column of row i or -1, w.y[j] = row of column j or -1.
@@ -94,6 +97,7 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
             w.x[i] = a;
         }
     } else {
+        if (CostFn::kStaged) return 1;
         for (int i = 0; i < nr; i++) {
             double m = CUDART_INF;
             int a = 0x7fffffff;
@@ -140,7 +144,8 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
             if (cn < best_null) { best_null = cn; null_row = i; }
             double lowest = CUDART_INF;
             int jl = 0x7fffffff;
-            if (CostFn::kBounded) {
+            if constexpr (CostFn::kStaged) cost.stage(i, w.spc);
+            if constexpr (CostFn::kBounded) {
                 // Expensive entries: cost.lower(i, j) is a cheap rigorous lower bound.  `bfree` is the
                 // exact distance of the best free column (or the null option) found so far, an upper
                 // bound of the final path length; an entry whose bound cannot beat min(spc[j], bfree)

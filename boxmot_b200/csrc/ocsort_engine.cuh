@@ -220,5 +220,5 @@ namespace bm {
 size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr);
 cudaError_t ocsort_step_configure(size_t smem);
 cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
-                               double* out, int* nout, cudaStream_t stream);
+                               double* out, int* nout, cudaStream_t stream, cudaEvent_t* ev = nullptr);
 }  // namespace bm

@@ -28,6 +28,7 @@ namespace bm {
 constexpr int K1_NT = 128;
 constexpr int K2_NT = 64;
 constexpr int K3_NT = 64;
+static_assert(K2_NT == 64, "OcmCostStaged's named barrier and the helper warp assume two warps per association CTA");
 
 // ============================================================================ K1
 // Blocks [0, S*chunks) predict; the trailing ceil(S/4) blocks split each stream's detections
@@ -115,24 +116,25 @@ struct OcsSmem {
     int *misc, *cand;
 };
 
-enum { M_NT = 0, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M_COUNT = 8 };
+enum { M_NT = 0, M_NUD, M_NUT, M_FAST, M_ANYBAD, M_NUPD, M_LAPBAD, M_ROW, M_COUNT = 8 };
 
 // fp32 screening tables, built once per stream-frame (they alias the solver's work area,
 // which is idle while the row summaries are computed).
 //   boxf[t]  the track box rounded OUTWARDS to float (x1,y1 down; x2,y2 up): if the float
 //            boxes do not overlap, the fp64 boxes do not either.  A degenerate / non-finite
 //            box is stored as (-inf,-inf,+inf,+inf) so it is always evaluated exactly.
-//   kc[t]    centre of the observation delta_t frames back (fp64, exact differences)
+//   kc[t]    centre of the observation delta_t frames back as (x_hi, x_lo, y_hi, y_lo) float
+//            pairs: (cx_hi - x_hi) + (cx_lo - x_lo) is the fp64 difference to ~1e-7 relative
 //   mvf[t]   (vx, vy) as floats, (0,0) when the OCM term is exactly 0 for this track
 //   cs       [warps][Tcap] per-row screening cosines
 struct OcmScreen {
     float4* boxf;
-    double2* kc;
+    float4* kc;
     float2* mvf;
     float* cs;
 };
 __host__ __device__ inline size_t ocm_screen_bytes(int Tcap, int warps) {
-    return (size_t)Tcap * (sizeof(float4) + sizeof(double2) + sizeof(float2)) + (size_t)warps * Tcap * sizeof(float);
+    return (size_t)Tcap * (sizeof(float4) + sizeof(float4) + sizeof(float2)) + (size_t)warps * Tcap * sizeof(float);
 }
 __host__ __device__ inline size_t ocs_work_bytes(int Tcap, int Dcap) {
     // the lapjv emulation only runs with more detections than tracks: n = nD + nT < 2 * Dcap
@@ -141,10 +143,17 @@ __host__ __device__ inline size_t ocs_work_bytes(int Tcap, int Dcap) {
     return (m + 15) / 16 * 16;
 }
 
+// per-warp candidate scratch: [Tcap + 64] packed candidates (ocm_scan_rows) or
+// LANE_CAND results (8 B) + packed candidates (4 B) (ocm_scan_rows_lane)
+constexpr int LANE_CAND = 128;
+__host__ __device__ inline size_t ocs_cand_ints(int Tcap) {
+    const size_t a = (size_t)Tcap + 64, b = 3 * LANE_CAND;
+    return ((a > b ? a : b) + 3) / 4 * 4;
+}
 __host__ __device__ inline size_t ocs_smem_bytes(int Tcap, int Dcap, int use_byte) {
     const size_t d = (size_t)Dcap, t = (size_t)Tcap;
     size_t b = 16 * d * (use_byte ? 2 : 1) + 8 * d + ocs_work_bytes(Tcap, Dcap);
-    b += 4 * ((use_byte ? 7 : 6) * d + 4 * t + M_COUNT + (t + 64) * (K2_NT / 32));
+    b += 4 * ((use_byte ? 7 : 6) * d + 4 * t + M_COUNT + ocs_cand_ints(Tcap) * (K2_NT / 32));
     return (b + 15) / 16 * 16;
 }
 
@@ -153,6 +162,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.dbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap;
     if (use_byte) { m.sbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap; } else m.sbox = nullptr;
     m.work = base; base += ocs_work_bytes(Tcap, Dcap);
+    m.cand = reinterpret_cast<int*>(base); base += 4 * ocs_cand_ints(Tcap) * (K2_NT / 32);
     m.rmin = reinterpret_cast<double*>(base); base += 8 * (size_t)Dcap;
     int* q = reinterpret_cast<int*>(base);
     m.dind = q; q += Dcap;
@@ -166,8 +176,7 @@ __device__ inline OcsSmem ocs_carve(unsigned char* base, int Tcap, int Dcap, int
     m.t2d = q; q += Tcap;
     m.um_t = q; q += Tcap;
     m.colcnt = q; q += Tcap;
-    m.misc = q; q += M_COUNT;
-    m.cand = q;
+    m.misc = q;
     return m;
 }
 
@@ -206,7 +215,7 @@ __device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, 
 struct OcmCost {
     // bounded sweeps (lower()) measured slower than plain exact sweeps on B200: two extra
     // passes of L2 loads per sweep cost more than the ~140 exact entries they avoid
-    static constexpr bool kBounded = false;
+    static constexpr bool kBounded = false, kStaged = false;
     const float4* dbox;                // high-score detections (shared memory)
     const double* tb; int Tcap;        // operands per track column [AB_COUNT][Tcap] (global, L2)
     int func; double diag, inertia;
@@ -272,6 +281,52 @@ struct OcmCost {
     }
 };
 
+// The same cost for the solver's sweeps with BOTH warps of the CTA evaluating the swept row
+// into a shared-memory buffer (the fp64 entry is a long dependent chain, so a sweep's time is
+// its chunk count): warp 0 runs the solver and calls stage(); warp 1 sits in helper() until
+// release().  Named barrier 1 (64 threads) separates "row published" / "row evaluated".
+struct OcmCostStaged {
+    static constexpr bool kBounded = false, kStaged = true;
+    OcmCost base;
+    double* rowc;          // [nc]
+    int* cur;              // row being swept, -1 = solver finished
+    const double* spc;     // solver's distance array (column scanned <=> -inf)
+    int nc;
+    static __device__ __forceinline__ void bar() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
+    __device__ __forceinline__ void fill(int i, int w) const {
+        const Box a = base.det(i);
+        const double cx = (a.x1 + a.x2) / 2.0, cy = (a.y1 + a.y2) / 2.0;
+        for (int j = 32 * w + lane_id(); j < nc; j += 64) {
+            if (spc[j] == -CUDART_INF) continue;
+            double iou;
+            rowc[j] = base.entry(a, cx, cy, j, &iou);
+        }
+    }
+    __device__ __forceinline__ void stage(int i, const double*) const {
+        __syncwarp();
+        if (lane_id() == 0) *cur = i;
+        bar();
+        fill(i, 0);
+        bar();
+    }
+    __device__ __forceinline__ void release() const {
+        __syncwarp();
+        if (lane_id() == 0) *cur = -1;
+        bar();
+    }
+    __device__ __forceinline__ void helper() const {
+        for (;;) {
+            bar();
+            const int i = *(volatile int*)cur;
+            if (i < 0) break;
+            fill(i, 1);
+            bar();
+        }
+    }
+    __device__ __forceinline__ double operator()(int, int j) const { return rowc[j]; }
+    __device__ __forceinline__ double lower(int i, int j, bool* exact) const { *exact = true; return rowc[j]; }
+};
+
 // Returns true when the predicted box is NaN (the reference drops such a track).
 __device__ inline bool ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, int t) {
     const Box b = c.trk(t);
@@ -284,8 +339,19 @@ __device__ inline bool ocm_screen_fill(const OcmCost& c, const OcmScreen& sc, in
     float fx = mv ? (float)vx : 0.f, fy = mv ? (float)vy : 0.f;
     if (mv && fx == 0.f && fy == 0.f) fx = 1e-30f;      // keep "moving" distinguishable
     sc.mvf[t] = make_float2(fx, fy);
-    sc.kc[t] = make_double2(c.tb[AB_KCX * c.Tcap + t], c.tb[AB_KCY * c.Tcap + t]);
+    const double kx = c.tb[AB_KCX * c.Tcap + t], ky = c.tb[AB_KCY * c.Tcap + t];
+    const float kxh = (float)kx, kyh = (float)ky;
+    sc.kc[t] = make_float4(kxh, (float)(kx - (double)kxh), kyh, (float)(ky - (double)kyh));
     return b.x1 != b.x1 || b.y1 != b.y1 || b.x2 != b.x2 || b.y2 != b.y2;
+}
+// fp32 cosine between the track's velocity (mv) and the direction from its look-back
+// centre (kc, hi/lo split) to the detection centre (association.py:10-20, :437-438).
+__device__ __forceinline__ float ocm_screen_cos(const float4 kc, const float2 mv, float cxh, float cxl,
+                                                float cyh, float cyl) {
+    const float dx = (cxh - kc.x) + (cxl - kc.y), dy = (cyh - kc.z) + (cyl - kc.w);
+    const float n2 = fmaf(dy, dy, dx * dx);
+    const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
+    return __fdividef(fmaf(mv.y, dy, mv.x * dx), nrm + 1e-6f);
 }
 constexpr float OCM_BAND = 1e-4f;   // >> error of the fp32 cosine (~1e-6), << spacing of candidates
 constexpr float OCM_NOCAND = -4.f;
@@ -347,6 +413,8 @@ __device__ inline void ocm_scan_rows(const OcmCost& c, const OcmScreen& sc, int 
     for (int d = wid; d < nD; d += NW) {
         const float4 af = c.dbox[d];
         const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
+        const float cxh = (float)cxd, cyh = (float)cyd;
+        const float cxl = (float)(cxd - (double)cxh), cyl = (float)(cyd - (double)cyh);
         const bool sparse = c.func == ASSO_IOU &&
                             ((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x;
         int zero_t = 0x7fffffff;
@@ -368,11 +436,7 @@ __device__ inline void ocm_scan_rows(const OcmCost& c, const OcmScreen& sc, int 
                             const float2 mv = sc.mvf[t];
                             if (mv.x == 0.f && mv.y == 0.f) zero_t = min(zero_t, t);
                             else {
-                                const double2 kc = sc.kc[t];
-                                const float dx = (float)(cxd - kc.x), dy = (float)(cyd - kc.y);
-                                const float n2 = dx * dx + dy * dy;
-                                const float nrm = n2 * rsqrtf(fmaxf(n2, 1e-30f));
-                                csv[u] = __fdividef(mv.x * dx + mv.y * dy, nrm + 1e-6f);
+                                csv[u] = ocm_screen_cos(sc.kc[t], mv, cxh, cxl, cyh, cyl);
                                 m32 = fmaxf(m32, csv[u]);
                             }
                         }
@@ -410,6 +474,151 @@ __device__ inline void ocm_scan_rows(const OcmCost& c, const OcmScreen& sc, int 
         const int zt = zero_ts[d];
         const double rm = rmin[d];
         if (zt != 0x7fffffff && (-0.0 < rm || (-0.0 == rm && zt < rarg[d]))) { rmin[d] = -0.0; rarg[d] = zt; }
+    }
+}
+
+// asso_func = iou: the same row summaries with ONE LANE PER ROW.  A lane walks all tracks of
+// its detection (the screening tables are read as shared-memory broadcasts, so the walk has
+// no shuffles, ballots or list traffic and pipelines freely) and keeps in registers
+//   * the tracks whose outward-rounded float box overlaps the detection (up to OVL_CAP
+//     10-bit columns packed in two 64-bit words),
+//   * a 6-deep shift register of the columns whose fp32 cosine came within OCM_BAND of the
+//     RUNNING maximum (a superset of those within the band of the final maximum; the fp32
+//     value is recomputed for the survivors),
+//   * the first column whose entry is exactly -0.0.
+// Afterwards every lane evaluates its few candidates in fp64 with the reference's operation
+// order.  Rows that overflow a register list, lose a possibly-in-band column out of the shift
+// register, or have a degenerate detection box are redone by the whole warp with every entry
+// evaluated exactly.  Results are identical to ocm_scan_rows (exact minima, lowest column on
+// ties).
+constexpr int OVL_CAP = 12;
+__device__ inline void ocm_scan_rows_lane(const OcmCost& c, const OcmScreen& sc, int nD, int nT, double iou_thr,
+                                          int* colcnt, double* rmin, int* rarg, int* rowcnt, int* hit_t,
+                                          int* scratch /*[3 * LANE_CAND] per warp, 8-byte aligned*/) {
+    const int lane = lane_id(), wid = warp_id(), NW = blockDim.x >> 5;
+    double* cres = reinterpret_cast<double*>(scratch);
+    int* clist = scratch + 2 * LANE_CAND;
+    for (int r0 = 32 * wid; r0 < nD; r0 += 32 * NW) {
+        const int d = r0 + lane;
+        const bool live = d < nD;
+        const float4 af = c.dbox[live ? d : r0];
+        const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
+        const float cxh = (float)cxd, cyh = (float)cyd;
+        const float cxl = (float)(cxd - (double)cxh), cyl = (float)(cyd - (double)cyh);
+        bool dense = !(((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x);
+        unsigned long long ov0 = 0, ov1 = 0, bl = 0;
+        int nov = 0, nb = 0, zero_t = 0x7fffffff;
+        float runmax = -CUDART_INF_F;
+#pragma unroll 4
+        for (int t = 0; t < nT; t++) {
+            const float4 b = sc.boxf[t];
+            const float2 mv = sc.mvf[t];
+            const float4 kc = sc.kc[t];
+            if (af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w) {
+                if (nov < 6) ov0 |= (unsigned long long)t << (10 * nov);
+                else if (nov < OVL_CAP) ov1 |= (unsigned long long)t << (10 * (nov - 6));
+                nov++;
+            } else if (mv.x == 0.f && mv.y == 0.f) {
+                zero_t = min(zero_t, t);
+            } else {
+                const float cs = ocm_screen_cos(kc, mv, cxh, cxl, cyh, cyl);
+                if (cs >= runmax - OCM_BAND) {
+                    bl = (bl << 10) | (unsigned long long)t;
+                    nb++;
+                    runmax = fmaxf(runmax, cs);
+                }
+            }
+        }
+        if (nov > OVL_CAP) dense = true;
+        const float lim = runmax - OCM_BAND;
+        const int nbk = min(nb, 6);
+        if (nb > 6) {
+            // the oldest retained column bounds (within one band) everything shifted out before it
+            const int t5 = (int)((bl >> 50) & 1023u);
+            if (ocm_screen_cos(sc.kc[t5], sc.mvf[t5], cxh, cxl, cyh, cyl) >= lim - OCM_BAND) dense = true;
+        }
+        // survivors of the band filter (fp32 value against the FINAL maximum)
+        unsigned long long bf = 0;
+        int nbf = 0;
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            if (k < nbk) {
+                const int t = (int)((bl >> (10 * k)) & 1023u);
+                if (ocm_screen_cos(sc.kc[t], sc.mvf[t], cxh, cxl, cyh, cyl) >= lim) {
+                    bf |= (unsigned long long)t << (10 * nbf);
+                    nbf++;
+                }
+            }
+        }
+        // ---- exact evaluation: the warp's candidates are pooled in shared memory so that all
+        // 32 lanes evaluate (the fp64 entry is a long dependent chain), then every lane folds
+        // the results of its own row; LANE_CAND candidates per round
+        const int ntot = (live && !dense) ? nov + nbf : 0;
+        double best = CUDART_INF;
+        int bt = 0x7fffffff, cnt = 0, ht = -1, done = 0;
+        for (;;) {
+            const int rem = ntot - done;
+            int incl = rem;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int up = __shfl_up_sync(BM_FULL, incl, o);
+                if (lane >= o) incl += up;
+            }
+            const int total = __shfl_sync(BM_FULL, incl, 31);
+            if (total == 0) break;
+            const int excl = incl - rem;
+            const int take = max(0, min(rem, LANE_CAND - excl));
+            for (int j = 0; j < take; j++) {
+                const int q = done + j;
+                const unsigned long long w = q < 6 ? ov0 >> (10 * q) : q < nov ? ov1 >> (10 * (q - 6)) : 0;
+                const int t = q < nov ? (int)(w & 1023u) : (int)((bf >> (10 * (q - nov))) & 1023u);
+                clist[excl + j] = (lane << 10) | t;
+            }
+            __syncwarp();
+            const int nsub = min(total, LANE_CAND);
+            for (int k = lane; k < nsub; k += 32) {
+                const int pk = clist[k], t = pk & 1023;
+                const Box a = c.det(r0 + (pk >> 10));
+                double iou;
+                cres[k] = c.entry(a, (a.x1 + a.x2) / 2.0, (a.y1 + a.y2) / 2.0, t, &iou);
+                if (iou > iou_thr) { atomicAdd(&colcnt[t], 1); clist[k] = pk | (1 << 20); }
+            }
+            __syncwarp();
+            for (int j = 0; j < take; j++) {
+                const int pk = clist[excl + j], t = pk & 1023;
+                const double cc = cres[excl + j];
+                if (pk & (1 << 20)) { cnt++; ht = max(ht, t); }
+                if (cc < best || (cc == best && t < bt)) { best = cc; bt = t; }
+            }
+            done += take;
+            __syncwarp();
+        }
+        // zero-motion, zero-IoU entries hold -(0.0 + 0.0) = -0.0
+        if (zero_t != 0x7fffffff && (-0.0 < best || (-0.0 == best && zero_t < bt))) { best = -0.0; bt = zero_t; }
+        if (live && !dense) { rmin[d] = best; rarg[d] = bt; rowcnt[d] = cnt; hit_t[d] = ht; }
+        // ---- rare rows: every entry exactly, by the whole warp
+        unsigned dm = __ballot_sync(BM_FULL, live && dense);
+        while (dm) {
+            const int src = __ffs(dm) - 1;
+            dm &= dm - 1;
+            const int dd = r0 + src;
+            const Box a = c.det(dd);
+            const double ax = (a.x1 + a.x2) / 2.0, ay = (a.y1 + a.y2) / 2.0;
+            double m = CUDART_INF;
+            int mt = 0x7fffffff, hc = 0, hmax = -1;
+            for (int t = lane; t < nT; t += 32) {
+                double iou;
+                const double cc = c.entry(a, ax, ay, t, &iou);
+                if (iou > iou_thr) { hc++; hmax = max(hmax, t); atomicAdd(&colcnt[t], 1); }
+                if (cc < m) { m = cc; mt = t; }
+            }
+            warp_argmin(m, mt);
+            for (int o = 16; o > 0; o >>= 1) {
+                hc += __shfl_xor_sync(BM_FULL, hc, o);
+                hmax = max(hmax, __shfl_xor_sync(BM_FULL, hmax, o));
+            }
+            if (lane == 0) { rmin[dd] = m; rarg[dd] = mt; rowcnt[dd] = hc; hit_t[dd] = hmax; }
+        }
     }
 }
 
@@ -536,7 +745,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     const OcmCost ocm = {sm.dbox, ab, Tcap, pr.asso_func, pr.diag, pr.inertia};
     OcmScreen scr;
     scr.boxf = reinterpret_cast<float4*>(sm.work);
-    scr.kc = reinterpret_cast<double2*>(scr.boxf + Tcap);
+    scr.kc = scr.boxf + Tcap;
     scr.mvf = reinterpret_cast<float2*>(scr.kc + Tcap);
     scr.cs = reinterpret_cast<float*>(scr.mvf + Tcap);
     for (int p = tid; p < nT; p += K2_NT) {
@@ -572,8 +781,12 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     // (association.py:427-461), evaluated on demand; permutation fast path (:501-503) or
     // exact LAP (:505-507)
     if (nD > 0 && nT > 0) {
-        ocm_scan_rows(ocm, scr, nD, nT, pr.iou_thr, sm.cand + (Tcap + 64) * wid, sm.colcnt, sm.rmin, sm.rarg,
-                      sm.rowcnt, sm.hit_t, sm.um_d);
+        if (pr.asso_func == ASSO_IOU)
+            ocm_scan_rows_lane(ocm, scr, nD, nT, pr.iou_thr, sm.colcnt, sm.rmin, sm.rarg, sm.rowcnt, sm.hit_t,
+                               sm.cand + ocs_cand_ints(Tcap) * wid);
+        else
+            ocm_scan_rows(ocm, scr, nD, nT, pr.iou_thr, sm.cand + ocs_cand_ints(Tcap) * wid, sm.colcnt, sm.rmin, sm.rarg,
+                          sm.rowcnt, sm.hit_t, sm.um_d);
         __syncthreads();       // the screening tables are dead from here on (sm.work is reused)
         BM_STAMP(2);
         // permutation fast path: every row/column has at most one IoU hit, at least one exists
@@ -619,7 +832,9 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
                     // the padding), so the outcome does not depend on lapjv's tie-breaking and the
                     // fast exact solver applies; the null option is never taken (cost +inf).
                     RectWork w = rect_carve(sm.work, nD, nT);
-                    bad = rect_solve_warp(ocm, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
+                    const OcmCostStaged oc2 = {ocm, reinterpret_cast<double*>(sm.cand), &sm.misc[M_ROW], w.spc, nT};
+                    bad = rect_solve_warp(oc2, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
+                    oc2.release();
                     xsol = w.x;
                 } else {
                     double pad = s_cmx[0];
@@ -647,6 +862,10 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
                 if (lane == 0) atomicAdd(&v.hdr[OH_LAPS], 1);
             }
             if (lane == 0) sm.misc[M_FAST] = fast ? 1 : 0;
+        } else if (wid == 1 && !fast && nD <= nT) {
+            RectWork w = rect_carve(sm.work, nD, nT);
+            const OcmCostStaged oc2 = {ocm, reinterpret_cast<double*>(sm.cand), &sm.misc[M_ROW], w.spc, nT};
+            oc2.helper();
         }
         __syncthreads();
     } else {
@@ -908,18 +1127,26 @@ static cudaError_t dbg_check(const char* name, cudaStream_t stream) {
 }
 
 cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
-                               double* out, int* nout, cudaStream_t stream) {
+                               double* out, int* nout, cudaStream_t stream, cudaEvent_t* ev) {
     const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
     cudaError_t e;
+    // optional per-kernel timing: five events bracket the four launches (bm_ocsort_kernel_times)
+#define BM_EV(k) do { if (ev && (e = cudaEventRecord(ev[k], stream)) != cudaSuccess) return e; } while (0)
+    BM_EV(0);
     ocs_predict_kernel<<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets);
     if ((e = dbg_check("ocs_predict_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(1);
     ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(2);
     ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_update_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(3);
     const int nt4 = (st.Tcap + 31) / 32 * 32;
     ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
     if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(4);
+#undef BM_EV
     return cudaGetLastError();
 }
 

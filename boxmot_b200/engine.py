@@ -104,6 +104,16 @@ class OcSortEngine:
                                                      _stream_ptr(self.device)), "bm_ocsort_counters")
         return dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
 
+    def time_kernels(self, enable=True):
+        """Bracket the four launches of every following step with CUDA events."""
+        _lib.check(_lib.lib().bm_ocsort_time_kernels(self._h, int(bool(enable))), "bm_ocsort_time_kernels")
+
+    def kernel_times(self):
+        """(predict, assoc, update, finalize) milliseconds of the last timed step (synchronises)."""
+        buf = (ctypes.c_float * 4)()
+        _lib.check(_lib.lib().bm_ocsort_kernel_times(self._h, ctypes.byref(buf)), "bm_ocsort_kernel_times")
+        return tuple(float(v) for v in buf)
+
     def peek(self, stream_index):
         n = ctypes.c_int(0)
         x = np.zeros((self.Tcap, 7))

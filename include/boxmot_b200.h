@@ -59,6 +59,13 @@ int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream);
 /* Debug: when d_stamps (device, [S][8] int64) is non-null the association kernel records
  * clock64() at its phase boundaries for every stream; pass NULL to switch it off. */
 int bm_ocsort_debug_profile(void* handle, long long* d_stamps);
+/* Per-kernel timing of the frame step (measurement aid for bench.py's roofline): when
+ * enabled, bm_ocsort_step brackets its four launches (predict, assoc, update, finalize) with
+ * CUDA events on the caller's stream; bm_ocsort_kernel_times waits for the last timed step and
+ * returns the four durations in milliseconds. */
+int bm_ocsort_time_kernels(void* handle, int enable);
+int bm_ocsort_kernel_times(void* handle, float* ms4);
+
 /* Debug / test access: copy one stream's list length and per-track Kalman state
  * (list order) to host buffers x[track_cap*7], P[track_cap*49], ids[track_cap]. */
 int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
