@@ -46,6 +46,9 @@ OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_th
                    Q_s_scaling=0.0001)
 
 
+BYTETRACK_YAML = dict(min_conf=0.1, track_thresh=0.6, match_thresh=0.9, track_buffer=30, frame_rate=30)
+
+
 def case_frames(case):
     from boxmot_b200.synth import make_stream
     if case.startswith("MOT17"):

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 from scipy.optimize import linear_sum_assignment
 
-from conftest import (OCSORT_YAML, ROOT, assert_rows_match, case_frames, golden_rows,
+from conftest import (BYTETRACK_YAML, OCSORT_YAML, ROOT, assert_rows_match, case_frames, golden_rows,
                       split_by_frame)
 from oracle import lap
 from oracle.ocsort import OcSortOracle
@@ -67,6 +67,20 @@ def test_ocsort_oracle_matches_reference_golden(case):
     want, kw = golden_rows("ocsort", case)
     frames = case_frames(case)
     ora = OcSortOracle(**{**OCSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = ora.update(d)
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
+
+
+@pytest.mark.parametrize("case", ["synth_k100", "synth_k30_byte", "synth_k30_giou", "synth_k50_dt1",
+                                  "synth_k40_ciou", "MOT17_02_FRCNN", "MOT17_04_FRCNN"])
+def test_bytetrack_oracle_matches_reference_golden(case):
+    """BASELINE configs[0] (MOT17-mini, bytetrack.yaml) and the synthetic streams."""
+    from oracle.bytetrack import ByteTrackOracle
+    want, _ = golden_rows("bytetrack", case)
+    frames = case_frames(case)
+    ora = ByteTrackOracle(**BYTETRACK_YAML)
     want_f = split_by_frame(want, len(frames))
     for f, d in enumerate(frames):
         got = ora.update(d)
