@@ -18,6 +18,11 @@ class OcsortConfig(ctypes.Structure):
                                       "img_w", "img_h")]
 
 
+class BytetrackConfig(ctypes.Structure):
+    _fields_ = [(n, c_double) for n in ("min_conf", "track_thresh", "match_thresh")] + \
+               [(n, c_int) for n in ("track_buffer", "frame_rate")]
+
+
 ASSO_FUNCS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hmiou": 4, "centroid": 5}
 
 _SIGS = {
@@ -37,6 +42,15 @@ _SIGS = {
     "bm_ocsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 4)]),
     "bm_ocsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p,
                                c_void_p, c_void_p]),
+    "bm_bytetrack_create": (c_int, [ctypes.POINTER(BytetrackConfig), c_int, c_int, c_int,
+                                    ctypes.POINTER(c_void_p)]),
+    "bm_bytetrack_destroy": (c_int, [c_void_p]),
+    "bm_bytetrack_reset": (c_int, [c_void_p, c_void_p]),
+    "bm_bytetrack_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_bytetrack_counters": (c_int, [c_void_p, ctypes.POINTER(c_int),
+                                      ctypes.POINTER(ctypes.c_ulonglong * 4), c_void_p]),
+    "bm_bytetrack_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_lap_solve_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
                                    c_void_p, c_void_p, c_void_p]),
     "bm_lap_rect_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,

@@ -1,6 +1,7 @@
 // extern "C" surface of libboxmot_b200.so (declarations: include/boxmot_b200.h).
 #include "../../include/boxmot_b200.h"
 #include "ocsort_engine.cuh"
+#include "bytetrack_engine.cuh"
 #include <cstdio>
 #include <cstring>
 #include <limits>
@@ -32,8 +33,14 @@ struct OcsEngine {
     bool timing = false, timed = false;
 };
 
-template <typename T>
-cudaError_t dev_alloc(OcsEngine* e, T** p, size_t n) {
+struct ByteEngine {
+    bm::ByteState st;
+    bm::ByteParams pr;
+    std::vector<void*> allocs;
+};
+
+template <typename E, typename T>
+cudaError_t dev_alloc(E* e, T** p, size_t n) {
     cudaError_t r = cudaMalloc(reinterpret_cast<void**>(p), n * sizeof(T));
     if (r == cudaSuccess) e->allocs.push_back(*p);
     return r;
@@ -230,6 +237,131 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
             bm::xysrb_expand(pb, h_P + (size_t)p * 49);
         }
         if (h_ids) h_ids[p] = ints[bm::OI_ID * T + slot];
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- ByteTrack
+
+int bm_bytetrack_create(const bm_bytetrack_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
+        return fail(-1, "bm_bytetrack_create: bad argument");
+    if (track_cap > 1024) return fail(-1, "bm_bytetrack_create: track_cap must be <= 1024");
+    ByteEngine* e = new (std::nothrow) ByteEngine();
+    if (!e) return fail(-3, "out of host memory");
+    bm::ByteState& st = e->st;
+    st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap;
+    bm::ByteParams& pr = e->pr;
+    pr.track_thresh = cfg->track_thresh; pr.min_conf = cfg->min_conf; pr.match_thresh = cfg->match_thresh;
+    pr.det_thresh = cfg->track_thresh;                                   // bytetrack.py:152
+    pr.max_time_lost = (int)(cfg->frame_rate / 30.0 * cfg->track_buffer);   // bytetrack.py:153-154
+    const size_t S = n_streams, T = track_cap;
+    cudaError_t r = cudaSuccess;
+    if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::XA_N * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.confcls, S * 2 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.tbox, S * 4 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.ints, S * bm::BI_COUNT * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.act, S * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.lost, S * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.hdr, S * bm::BH_COUNT);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.n_updates, S);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.scratch, S * T * (size_t)det_cap);
+    if (r == cudaSuccess) r = bm::bytetrack_step_configure(bm::bytetrack_step_smem(st));
+    if (r != cudaSuccess) {
+        for (void* p : e->allocs) cudaFree(p);
+        delete e;
+        return fail(-2, "bm_bytetrack_create", r);
+    }
+    *handle = e;
+    return bm_bytetrack_reset(e, nullptr);
+}
+
+int bm_bytetrack_destroy(void* handle) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e) return 0;
+    for (void* p : e->allocs) cudaFree(p);
+    delete e;
+    return 0;
+}
+
+int bm_bytetrack_reset(void* handle, void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::ByteState& st = e->st;
+    const size_t S = st.S, T = st.Tcap;
+    BM_CUDA(cudaMemsetAsync(st.hdr, 0, S * bm::BH_COUNT * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.n_updates, 0, S * sizeof(unsigned long long), s));
+    BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::BI_COUNT * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.act, 0, S * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.lost, 0, S * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::XA_N * T * sizeof(double), s));
+    BM_CUDA(cudaMemsetAsync(st.tbox, 0, S * 4 * T * sizeof(double), s));
+    return 0;
+}
+
+int bm_bytetrack_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out, int* d_nout,
+                      void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_bytetrack_step: null argument");
+    BM_CUDA(bm::bytetrack_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
+                                      static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int bm_bytetrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || !out4) return fail(-1, "bm_bytetrack_counters: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int S = e->st.S;
+    std::vector<int> hdr((size_t)S * bm::BH_COUNT);
+    std::vector<unsigned long long> nu(S);
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), e->st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(nu.data(), e->st.n_updates, nu.size() * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    int err = 0;
+    out4[0] = out4[1] = out4[2] = out4[3] = 0;
+    for (int i = 0; i < S; i++) {
+        const int* h = &hdr[(size_t)i * bm::BH_COUNT];
+        err |= h[bm::BH_ERR];
+        out4[0] += nu[i];
+        out4[1] += (unsigned long long)h[bm::BH_LAPS];
+        out4[2] += (unsigned long long)h[bm::BH_MATCH];
+        out4[3] += (unsigned long long)h[bm::BH_BIRTHS];
+    }
+    if (err_bits) *err_bits = err;
+    return 0;
+}
+
+int bm_bytetrack_peek(void* handle, int si, int* n_active, int* n_lost, double* h_mean, double* h_cov,
+                      int* h_ids, void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || si < 0 || si >= e->st.S) return fail(-1, "bm_bytetrack_peek: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::ByteState& st = e->st;
+    const size_t T = st.Tcap;
+    std::vector<double> xp(bm::XA_N * T);
+    std::vector<int> act(T), lost(T), ints(bm::BI_COUNT * T), hdr(bm::BH_COUNT);
+    BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * bm::XA_N * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(act.data(), st.act + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(lost.data(), st.lost + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::BI_COUNT * T, ints.size() * 4,
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), st.hdr + (size_t)si * bm::BH_COUNT, hdr.size() * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    const int na = hdr[bm::BH_NACT], nl = hdr[bm::BH_NLOST];
+    if (n_active) *n_active = na;
+    if (n_lost) *n_lost = nl;
+    for (int p = 0; p < na + nl; p++) {
+        const int slot = p < na ? act[p] : lost[p - na];
+        if (h_mean) for (int c = 0; c < 8; c++) h_mean[p * 8 + c] = xp[c * T + slot];
+        if (h_cov) {
+            double pb[12];
+            for (int c = 0; c < 12; c++) pb[c] = xp[(8 + c) * T + slot];
+            bm::xyah_expand(pb, h_cov + (size_t)p * 64);
+        }
+        if (h_ids) h_ids[p] = ints[bm::BI_ID * T + slot];
     }
     return 0;
 }

@@ -24,6 +24,22 @@ __device__ __forceinline__ double shfl_xor_d(double v, int m) {
     return __shfl_xor_sync(BM_FULL, v, m);
 }
 
+// Stable compaction by ONE warp: out[k0 + rank] = val(i) for every i in [0, n) with
+// pred(i), in ascending i.  Returns k0 + count on all lanes.
+template <typename Pred, typename Val>
+__device__ __forceinline__ int warp_compact(int n, int* out, int k0, Pred pred, Val val) {
+    const int lane = lane_id();
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + lane;
+        const bool ok = i < n && pred(i);
+        const unsigned b = __ballot_sync(BM_FULL, ok);
+        if (ok) out[k0 + __popc(b & ((1u << lane) - 1))] = val(i);
+        k0 += __popc(b);
+    }
+    __syncwarp();
+    return k0;
+}
+
 // Error bits recorded per stream in the engine header (never silently ignored: the
 // host wrapper raises when any bit is set).
 enum : int {

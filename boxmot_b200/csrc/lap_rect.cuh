@@ -96,8 +96,9 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
             w.u[i] = m;
             w.x[i] = a;
         }
+    } else if constexpr (CostFn::kStaged) {
+        return 1;            // staged cost functors must come with row minima
     } else {
-        if (CostFn::kStaged) return 1;
         for (int i = 0; i < nr; i++) {
             double m = CUDART_INF;
             int a = 0x7fffffff;

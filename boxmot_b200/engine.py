@@ -19,7 +19,37 @@ def _stream_ptr(device):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
-class OcSortEngine:
+class _HostStepMixin:
+    # -- host-buffer convenience (the reference-facing path: H2D, step, D2H) -------------
+    def step_host(self, dets_per_stream):
+        """dets_per_stream: list of S arrays (N_s, 6).  Returns list of (M_s, 8) arrays."""
+        if not hasattr(self, "_h_dets"):
+            self._h_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32).pin_memory()
+            self._h_nd = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+            self._d_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32, device=self.device)
+            self._d_nd = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+            self._h_out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64).pin_memory()
+            self._h_nout = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+        hd = self._h_dets.numpy()
+        hn = self._h_nd.numpy()
+        for s, d in enumerate(dets_per_stream):
+            n = 0 if d is None else len(d)
+            if n > self.Dcap:
+                raise RuntimeError("stream %d: %d detections exceed det_cap=%d" % (s, n, self.Dcap))
+            if n:
+                hd[s, :n] = d
+            hn[s] = n
+        self._d_dets.copy_(self._h_dets, non_blocking=True)
+        self._d_nd.copy_(self._h_nd, non_blocking=True)
+        out, nout = self.step(self._d_dets, self._d_nd)
+        self._h_out.copy_(out, non_blocking=True)
+        self._h_nout.copy_(nout, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
+        return [ho[s, : hn2[s]].copy() for s in range(self.S)]
+
+
+class OcSortEngine(_HostStepMixin):
     """S independent OC-SORT trackers advanced by one kernel launch per frame.
 
     Parameters are those of the reference ``OcSort.__init__``
@@ -126,33 +156,6 @@ class OcSortEngine:
         k = n.value
         return x[:k], P[:k].reshape(k, 7, 7), ids[:k]
 
-    # -- host-buffer convenience (the reference-facing path: H2D, step, D2H) -------------
-    def step_host(self, dets_per_stream):
-        """dets_per_stream: list of S arrays (N_s, 6).  Returns list of (M_s, 8) arrays."""
-        if not hasattr(self, "_h_dets"):
-            self._h_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32).pin_memory()
-            self._h_nd = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
-            self._d_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32, device=self.device)
-            self._d_nd = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
-            self._h_out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64).pin_memory()
-            self._h_nout = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
-        hd = self._h_dets.numpy()
-        hn = self._h_nd.numpy()
-        for s, d in enumerate(dets_per_stream):
-            n = 0 if d is None else len(d)
-            if n > self.Dcap:
-                raise RuntimeError("stream %d: %d detections exceed det_cap=%d" % (s, n, self.Dcap))
-            if n:
-                hd[s, :n] = d
-            hn[s] = n
-        self._d_dets.copy_(self._h_dets, non_blocking=True)
-        self._d_nd.copy_(self._h_nd, non_blocking=True)
-        out, nout = self.step(self._d_dets, self._d_nd)
-        self._h_out.copy_(out, non_blocking=True)
-        self._h_nout.copy_(nout, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
-        return [ho[s, : hn2[s]].copy() for s in range(self.S)]
 
 
 class HostPipeline:
@@ -207,3 +210,85 @@ class HostPipeline:
     def drain(self):
         """Result of the last submitted frame."""
         return self._result((self.n - 1) & 1) if self.n else None
+
+
+class ByteTrackEngine(_HostStepMixin):
+    """S independent ByteTrack trackers advanced by ONE kernel launch per frame.
+
+    Parameters are those of the reference ``ByteTrack.__init__``
+    (boxmot/trackers/bytetrack/bytetrack.py:132-156).  Same buffer interface as
+    ``OcSortEngine`` (``step`` / ``step_host`` / ``HostPipeline``)."""
+
+    def __init__(self, n_streams, track_cap=256, det_cap=128, device="cuda:0", min_conf=0.1,
+                 track_thresh=0.45, match_thresh=0.8, track_buffer=25, frame_rate=30):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ByteTrackEngine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.S, self.Tcap, self.Dcap = int(n_streams), int(track_cap), int(det_cap)
+        cfg = _lib.BytetrackConfig(min_conf, track_thresh, match_thresh, int(track_buffer), int(frame_rate))
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_create(ctypes.byref(cfg), self.S, self.Tcap, self.Dcap,
+                                                      ctypes.byref(self._h)), "bm_bytetrack_create")
+            torch.cuda.synchronize(self.device)
+        self.out_rows = min(self.Tcap, self.Dcap)
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+        self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+        self.launches = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            _lib.lib().bm_bytetrack_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_reset(self._h, _stream_ptr(self.device)), "bm_bytetrack_reset")
+
+    def step(self, dets, ndets, out=None, nout=None):
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (self.S, self.Dcap, 6)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_step(self._h, _ptr(dets), _ptr(ndets), _ptr(out), _ptr(nout),
+                                                    _stream_ptr(self.device)), "bm_bytetrack_step")
+        self.launches += 1
+        return out, nout
+
+    def counters(self, raise_on_error=True):
+        """Cumulative {track_updates, lap_solves, matches, births}; raises on device error bits."""
+        buf = (ctypes.c_ulonglong * 4)()
+        err = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_counters(self._h, ctypes.byref(err), ctypes.byref(buf),
+                                                        _stream_ptr(self.device)), "bm_bytetrack_counters")
+        if raise_on_error and err.value:
+            raise RuntimeError("ByteTrack engine error: " + "; ".join(m for b, m in ERR_BITS.items() if err.value & b))
+        d = dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
+        d["err"] = err.value
+        return d
+
+    def status(self, raise_on_error=True):
+        return self.counters(raise_on_error)
+
+    def peek(self, stream_index):
+        """(means [n,8], covariances [n,8,8], ids [n], n_active) -- active then lost tracks."""
+        na, nl = ctypes.c_int(0), ctypes.c_int(0)
+        m = np.zeros((self.Tcap, 8))
+        P = np.zeros((self.Tcap, 64))
+        ids = np.zeros((self.Tcap,), dtype=np.int32)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_peek(self._h, int(stream_index), ctypes.byref(na), ctypes.byref(nl),
+                                                    m.ctypes.data, P.ctypes.data, ids.ctypes.data,
+                                                    _stream_ptr(self.device)), "bm_bytetrack_peek")
+        k = na.value + nl.value
+        return m[:k], P[:k].reshape(k, 8, 8), ids[:k], na.value

@@ -59,6 +59,32 @@ int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream);
 /* Debug: when d_stamps (device, [S][8] int64) is non-null the association kernel records
  * clock64() at its phase boundaries for every stream; pass NULL to switch it off. */
 int bm_ocsort_debug_profile(void* handle, long long* d_stamps);
+/* ---- ByteTrack engine -------------------------------------------------------------
+ * Replaces ByteTrack.__init__/update (boxmot/trackers/bytetrack/bytetrack.py:132-156,
+ * :158-302), STrack (:14-116), joint/sub/remove_duplicate_stracks (:308-346),
+ * KalmanFilterXYAH (boxmot/motion/kalman_filters/aabb/xyah_kf.py, base_kalman_filter.py:
+ * 43-155), iou_distance / fuse_score / linear_assignment (boxmot/utils/matching.py:184-227,
+ * :488-560, :30-108).  Same buffer conventions as bm_ocsort_step: d_dets [S][det_cap][6]
+ * float32, d_ndets [S], d_out [S][min(track_cap,det_cap)][8] float64 rows
+ * (x1,y1,x2,y2,id,conf,cls,det_ind) in active_tracks order, d_nout [S]. */
+typedef struct bm_bytetrack_config {
+    double min_conf, track_thresh, match_thresh;
+    int track_buffer, frame_rate;
+} bm_bytetrack_config;
+int bm_bytetrack_create(const bm_bytetrack_config* cfg, int n_streams, int track_cap, int det_cap,
+                        void** handle);
+int bm_bytetrack_destroy(void* handle);
+int bm_bytetrack_reset(void* handle, void* stream);
+int bm_bytetrack_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
+                      int* d_nout, void* stream);
+/* out4 = {pool tracks predicted, assignments solved, matches, births}, summed over streams;
+ * err_bits = OR of the per-stream error bits.  Synchronises the stream. */
+int bm_bytetrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
+/* Host copy of one stream: active tracks then lost tracks in list order; h_mean [n][8],
+ * h_cov [n][64] (dense), h_ids [n]; any pointer may be NULL. */
+int bm_bytetrack_peek(void* handle, int stream_index, int* n_active, int* n_lost, double* h_mean,
+                      double* h_cov, int* h_ids, void* stream);
+
 /* Per-kernel timing of the frame step (measurement aid for bench.py's roofline): when
  * enabled, bm_ocsort_step brackets its four launches (predict, assoc, update, finalize) with
  * CUDA events on the caller's stream; bm_ocsort_kernel_times waits for the last timed step and
