@@ -27,6 +27,8 @@ if ROOT not in sys.path:
 OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_threshold=0.3,
                    delta_t=3, asso_func="iou", inertia=0.1, use_byte=False, Q_xy_scaling=0.01,
                    Q_s_scaling=0.0001)     # boxmot/configs/trackers/ocsort.yaml defaults
+BYTETRACK_YAML = dict(min_conf=0.1, track_thresh=0.6, match_thresh=0.9, track_buffer=30,
+                      frame_rate=30)   # boxmot/configs/trackers/bytetrack.yaml defaults
 METRIC = "track-updates/sec"
 L2_BYTES = 126 * 1024 * 1024
 
@@ -37,6 +39,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=290)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack"],
+                    help="ocsort = the headline workload (BASELINE configs[1]); bytetrack = the same "
+                         "synthetic streams through the ByteTrack engine (the tracker of configs[0])")
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
     ap.add_argument("--objects", type=int, default=100)
     ap.add_argument("--det-cap", type=int, default=128)
@@ -85,12 +90,17 @@ def _cpu_worker(a):
     """Runs whole streams through the oracle port; returns (timed seconds, timed updates)."""
     os.environ["OMP_NUM_THREADS"] = "1"
     from boxmot_b200.synth import make_stream
-    from oracle.ocsort import OcSortOracle
-    sids, k, warm, steps = a
+    sids, k, warm, steps, tracker = a
+    if tracker == "bytetrack":
+        from oracle.bytetrack import ByteTrackOracle
+        make = lambda: ByteTrackOracle(**BYTETRACK_YAML)
+    else:
+        from oracle.ocsort import OcSortOracle
+        make = lambda: OcSortOracle(**OCSORT_YAML)
     tot_t, tot_u = 0.0, 0
     for sid in sids:
         fr = make_stream(sid, k, warm + steps)
-        o = OcSortOracle(**OCSORT_YAML)
+        o = make()
         for f in range(warm):
             o.update(fr[f])
         u0 = o.n_updates
@@ -102,8 +112,8 @@ def _cpu_worker(a):
     return tot_t, tot_u
 
 
-def cpu_single_core(k, warm, steps, n_streams):
-    t, u = _cpu_worker((list(range(n_streams)), k, warm, steps))
+def cpu_single_core(k, warm, steps, n_streams, tracker):
+    t, u = _cpu_worker((list(range(n_streams)), k, warm, steps, tracker))
     return u / t, "%d streams x %d frames (after %d warm-up), K=%d, 1 core" % (n_streams, steps, warm, k)
 
 
@@ -121,7 +131,8 @@ def run_reference_arm(args):
     workers = max(1, cores - 1) if cores > 2 else cores
     per = max(1, args.ref_streams_per_core)
     steps = min(args.steps, 300)
-    jobs = [([w * per + i for i in range(per)], args.objects, args.warmup, steps) for w in range(workers)]
+    jobs = [([w * per + i for i in range(per)], args.objects, args.warmup, steps, args.tracker)
+            for w in range(workers)]
     t0 = time.perf_counter()
     with mp.get_context("fork").Pool(workers) as pool:
         res = pool.map(_cpu_worker, jobs)
@@ -136,8 +147,8 @@ def run_reference_arm(args):
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * tmax / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "OC-SORT ocsort.yaml, synthetic streams x %d dets/frame (SURVEY 8(d) C2), "
-                               "CPU sample of the 1024-stream job" % args.objects,
+        "config": {"workload": "%s, synthetic streams x %d dets/frame (SURVEY 8(d) C2 streams), "
+                               "CPU sample of the 1024-stream job" % (TRACKER_NAMES[args.tracker], args.objects),
                    "streams": workers * per, "objects": args.objects},
         "cpu_baseline": {"value": value, "unit": "track-updates/s", "cores": workers, "kind": "port",
                          "sample": sample},
@@ -198,6 +209,15 @@ class ClockSampler(threading.Thread):
 
 
 # --------------------------------------------------------------------------- GPU arm
+# DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) of ONE frame step at the default
+# workload, from the ncu captures committed under profiles/ (cold caches: ncu flushes L2 before
+# every kernel, so this is an upper bound of what a live step moves):
+#   profiles/r1_launches_lane_scan_traffic.csv   predict 55.2 + assoc 19.3 + update 72.0 + finalize 39.7 MB
+#   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
+NCU_TRAFFIC = {"ocsort": 186.1e6, "bytetrack": 41.1e6}
+TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)"}
+
+
 def alg_bytes(track_updates, matches, births, dets_in, rows_out):
     """Algorithmic bytes of one frame step (the SURVEY.md 8(d) terms, with the engine's
     block-form XYSR state of 7 + 13 fp64 = 160 B per track instead of the dense 7 + 49 =
@@ -239,12 +259,17 @@ def run_gpu_arm(args):
 
     import torch
     import torch.distributed as dist
-    from boxmot_b200.engine import OcSortEngine
+    from boxmot_b200.engine import ByteTrackEngine, OcSortEngine
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
+    byte = args.tracker == "bytetrack"
+    if byte:
+        eng = ByteTrackEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **BYTETRACK_YAML)
+    else:
+        eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
+    n_kernels = 1 if byte else 4
     h_dets = torch.from_numpy(dets).pin_memory()
     h_nd = torch.from_numpy(nd).pin_memory()
     d_dets = h_dets.to(dev, non_blocking=True)
@@ -294,20 +319,22 @@ def run_gpu_arm(args):
     # CUDA events on the launching stream (bm_ocsort_time_kernels); separate short pass so the
     # extra event records never sit inside the headline timing.
     KB = min(K, 100)
-    eng.reset()
-    for f in range(W):
-        step_dev(f)
-    eng.time_kernels(True)
-    ksum = np.zeros(4)
-    ck0 = eng.counters()
-    for i in range(KB):
-        if not args.no_flush:
-            flush_buf.zero_()
-        step_dev(W + i)
-        ksum += eng.kernel_times()
-    ck1 = eng.counters()
-    eng.time_kernels(False)
-    kcnt = {k: ck1[k] - ck0[k] for k in ck1}
+    ksum, kcnt = None, None
+    if not byte:                       # the ByteTrack step is a single kernel: nothing to break down
+        eng.reset()
+        for f in range(W):
+            step_dev(f)
+        eng.time_kernels(True)
+        ksum = np.zeros(4)
+        ck0 = eng.counters()
+        for i in range(KB):
+            if not args.no_flush:
+                flush_buf.zero_()
+            step_dev(W + i)
+            ksum += eng.kernel_times()
+        ck1 = eng.counters()
+        eng.time_kernels(False)
+        kcnt = {k: ck1[k] - ck0[k] for k in ck1}
 
     # (2) end to end through the public host-buffer API (boxmot_b200.engine.HostPipeline):
     # every step uploads that frame's detections from pinned host memory and downloads its
@@ -358,7 +385,7 @@ def run_gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import lap as olap
         olap.build()
-        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), args.cpu_streams)
+        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), args.cpu_streams, args.tracker)
         cpu = {"value": v, "unit": "track-updates/s", "cores": 1, "kind": "port", "sample": sample}
     if rank == 0:
         peaks = {}
@@ -375,23 +402,32 @@ def run_gpu_arm(args):
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_all / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
-                                   "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])" % (S, args.objects, F),
+            "config": {"workload": ("ByteTrack (bytetrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                    "IoU + fuse_score cost, three thresholded lapjv-exact assignments per frame "
+                                    "(tracker of BASELINE configs[0] on the configs[1] streams)" if byte else
+                                    "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                    "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])") % (S, args.objects, F),
+                       "tracker": args.tracker,
                        "streams_per_gpu": S, "objects": args.objects, "frames": F, "det_cap": args.det_cap,
                        "track_cap": args.track_cap, "partition": "streams sharded by rank, no data-path collective",
                        "l2": "no flush" if args.no_flush else "L2 flushed (252 MB memset) between timed steps, outside the event pairs"},
             "stream_frames_per_s": world * S * K / (ms_all * 1e-3),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak,
+                         "traffic": NCU_TRAFFIC[args.tracker] if (S, args.objects, args.det_cap, args.track_cap) ==
+                         (1024, 100, 128, 256) else None,
+                         "traffic_source": "ncu dram__bytes_read+write per frame step, cold caches (profiles/r1_launches_*_traffic.csv)",
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize", "alg_bytes_per_launch": nbytes / K,
-                         "avg_launch_ms": ms_dev / K,
-                         "per_kernel": per_kernel(ksum, KB, kcnt, int(nd[W:W + KB].sum())),
-                         "dominant_kernel": "ocs_assoc_kernel"},
-            "gpu_launches": 4 * K * (2 if not args.no_e2e else 1),
+                         "kernel": "byte_step_kernel" if byte else
+                                   "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize",
+                         "alg_bytes_per_launch": nbytes / K, "avg_launch_ms": ms_dev / K},
+            "gpu_launches": n_kernels * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }
+        if ksum is not None:
+            line["roofline"]["per_kernel"] = per_kernel(ksum, KB, kcnt, int(nd[W:W + KB].sum()))
+            line["roofline"]["dominant_kernel"] = "ocs_assoc_kernel"
         if e2e is not None:
             line["e2e"] = {"value": upd_e_all / (ms_e_all * 1e-3), "unit": "track-updates/s",
                            "h2d_bytes_per_step": int(pipe.h2d_bytes), "d2h_bytes_per_step": int(pipe.d2h_bytes),

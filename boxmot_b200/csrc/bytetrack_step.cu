@@ -135,7 +135,8 @@ __device__ inline void byte_assign(const double* cost, int nr, int nc, double th
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(BT_NT)
+// <= 146 registers: seven CTAs per SM keep all 1024 streams of the bench in one wave on 148 SMs
+__global__ void __launch_bounds__(BT_NT, 7)
 byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, const int* __restrict__ ndets,
                  double* __restrict__ out, int* __restrict__ nout) {
     extern __shared__ __align__(16) unsigned char smem_raw[];

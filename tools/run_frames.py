@@ -1,17 +1,22 @@
-"""Advance S synthetic streams by F frames through the engine (driver for ncu captures).
-usage: run_frames.py [S=1024] [F=45] [K=100]"""
+"""Advance S synthetic streams by F frames through an engine (driver for ncu captures).
+usage: run_frames.py [S=1024] [F=45] [K=100] [tracker=ocsort]"""
 import os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from boxmot_b200.engine import OcSortEngine
+from boxmot_b200.engine import ByteTrackEngine, OcSortEngine
 from boxmot_b200.synth import make_batch
-kw = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_threshold=0.3, delta_t=3, asso_func="iou",
-          inertia=0.1, use_byte=False, Q_xy_scaling=0.01, Q_s_scaling=0.0001)
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 F = int(sys.argv[2]) if len(sys.argv) > 2 else 45
 K = int(sys.argv[3]) if len(sys.argv) > 3 else 100
+tracker = sys.argv[4] if len(sys.argv) > 4 else "ocsort"
 dets, nd = make_batch(S, K, F, 128)
-eng = OcSortEngine(S, track_cap=256, det_cap=128, **kw)
+if tracker == "bytetrack":
+    eng = ByteTrackEngine(S, track_cap=256, det_cap=128, min_conf=0.1, track_thresh=0.6, match_thresh=0.9,
+                          track_buffer=30, frame_rate=30)
+else:
+    eng = OcSortEngine(S, track_cap=256, det_cap=128, min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3,
+                       asso_threshold=0.3, delta_t=3, asso_func="iou", inertia=0.1, use_byte=False,
+                       Q_xy_scaling=0.01, Q_s_scaling=0.0001)
 dd = torch.as_tensor(dets.astype(np.float32)).cuda(); dn = torch.as_tensor(nd).cuda()
 for f in range(F):
     eng.step(dd[f], dn[f])
