@@ -33,6 +33,18 @@ METRIC = "track-updates/sec"
 L2_BYTES = 126 * 1024 * 1024
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -155,7 +167,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": "track-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": wall, "host_cores": cores,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # --------------------------------------------------------------------------- clocks
@@ -435,7 +447,7 @@ def run_gpu_arm(args):
                            "ms_per_step": ms_e_all / K}
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -443,6 +455,12 @@ def run_gpu_arm(args):
 
 def main():
     args = parse()
+    # stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version
+    # banner, for one) is diverted to stderr by pointing fd 1 at fd 2 while the run lasts.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
     else:
