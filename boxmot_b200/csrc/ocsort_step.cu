@@ -17,7 +17,10 @@
 //                                                        removal (:388-439)
 //
 // Splitting the step keeps the register-heavy fp64 Kalman code out of the association CTA,
-// whose occupancy would otherwise be 2 CTAs/SM.
+// whose occupancy would otherwise be 2 CTAs/SM, and lets the state-streaming phases run with
+// a thread per track over the whole GPU.  (A single fused launch with one 64-thread CTA per
+// stream was measured 10-20 % slower at every stream count from 1 to 1024: 64 threads per
+// stream cannot keep enough loads in flight for the predict / update / finalize phases.)
 #include "ocsort_engine.cuh"
 #include "lap_rect.cuh"
 #include <cstdio>
@@ -36,46 +39,40 @@ static_assert(K2_NT == 64, "OcmCostStaged's named barrier and the helper warp as
 // follow.  dets: [S][Dcap][6] float32 (x1,y1,x2,y2,conf,cls) -- float32 IS the reference's
 // precision: BaseTracker.setup_decorator round-trips every ndarray through float32
 // (boxmot/trackers/basetracker.py:122-128).
-__global__ void __launch_bounds__(K1_NT)
-ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
-    const int chunks = (st.Tcap + K1_NT - 1) / K1_NT;
-    const int Tcap = st.Tcap;
-    if ((int)blockIdx.x >= st.S * chunks) {
-        const int s = ((int)blockIdx.x - st.S * chunks) * (K1_NT / 32) + warp_id();
-        if (s >= st.S) return;
-        const int lane = lane_id(), Dcap = st.Dcap;
-        int* hdr = st.hdr + (size_t)s * OH_COUNT;
-        int nD_in = ndets[s];
-        if (nD_in > Dcap) { if (lane == 0) atomicOr(&hdr[OH_ERR], BM_ERR_DET_OVERFLOW); nD_in = Dcap; }
-        const float* dsrc = dets + (size_t)s * Dcap * 6;
-        int* hs = st.hsel + (size_t)s * 2 * Dcap;
-        int nh = 0, ns = 0;
-        for (int base = 0; base < nD_in; base += 128) {          // 4 independent loads in flight
-            float cf[4];
+// Confidence split of one stream by ONE warp (ocsort.py:265-275; stable order).
+__device__ __forceinline__ void ocs_split_warp(const OcsState& st, const OcsParams& pr, int s,
+                                               const float* __restrict__ dets, const int* __restrict__ ndets) {
+    const int lane = lane_id(), Dcap = st.Dcap;
+    int* hdr = st.hdr + (size_t)s * OH_COUNT;
+    int nD_in = ndets[s];
+    if (nD_in > Dcap) { if (lane == 0) atomicOr(&hdr[OH_ERR], BM_ERR_DET_OVERFLOW); nD_in = Dcap; }
+    const float* dsrc = dets + (size_t)s * Dcap * 6;
+    int* hs = st.hsel + (size_t)s * 2 * Dcap;
+    int nh = 0, ns = 0;
+    for (int base = 0; base < nD_in; base += 128) {          // 4 independent loads in flight
+        float cf[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) { const int i = base + 32 * k + lane; cf[k] = i < nD_in ? dsrc[i * 6 + 4] : -1.f; }
+        for (int k = 0; k < 4; k++) { const int i = base + 32 * k + lane; cf[k] = i < nD_in ? dsrc[i * 6 + 4] : -1.f; }
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const int i = base + 32 * k + lane;
-                const double conf = (double)cf[k];
-                const bool hi = i < nD_in && conf > pr.det_thresh;
-                const bool se = pr.use_byte && i < nD_in && conf > pr.min_conf && conf < pr.det_thresh;
-                const unsigned bh = __ballot_sync(BM_FULL, hi), bs = __ballot_sync(BM_FULL, se);
-                const unsigned lt = (1u << lane) - 1;
-                if (hi) hs[nh + __popc(bh & lt)] = i;
-                if (se) hs[Dcap + ns + __popc(bs & lt)] = i;
-                nh += __popc(bh); ns += __popc(bs);
-            }
+        for (int k = 0; k < 4; k++) {
+            const int i = base + 32 * k + lane;
+            const double conf = (double)cf[k];
+            const bool hi = i < nD_in && conf > pr.det_thresh;
+            const bool se = pr.use_byte && i < nD_in && conf > pr.min_conf && conf < pr.det_thresh;
+            const unsigned bh = __ballot_sync(BM_FULL, hi), bs = __ballot_sync(BM_FULL, se);
+            const unsigned lt = (1u << lane) - 1;
+            if (hi) hs[nh + __popc(bh & lt)] = i;
+            if (se) hs[Dcap + ns + __popc(bs & lt)] = i;
+            nh += __popc(bh); ns += __popc(bs);
         }
-        if (lane == 0) { hdr[OH_ND] = nh; hdr[OH_NS] = ns; }
-        return;
     }
-    const int s = blockIdx.x / chunks;
-    const int p = (blockIdx.x % chunks) * K1_NT + threadIdx.x;
-    OcsView v(st, s);
-    const int nT = v.hdr[OH_NLIST];
-    if (p == 0) st.n_updates[s] += (unsigned long long)nT;
-    if (p >= nT) return;
+    if (lane == 0) { hdr[OH_ND] = nh; hdr[OH_NS] = ns; }
+}
+
+// Predict of the track at list position p (ocsort.py:173-186, xysr_kf.py:137-175) and its
+// association operands.
+__device__ __forceinline__ void ocs_predict_track(const OcsState& st, const OcsParams& pr, const OcsView& v, int s, int p) {
+    const int Tcap = st.Tcap;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
     double x[7], P[13];
@@ -101,6 +98,22 @@ ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, co
     ab[AB_KCX * Tcap + p] = ok ? (kb[0] + kb[2]) / 2.0 : -1.0;
     ab[AB_KCY * Tcap + p] = ok ? (kb[1] + kb[3]) / 2.0 : -1.0;
     ab[AB_KVALID * Tcap + p] = ok ? 1.0 : 0.0;
+}
+
+__global__ void __launch_bounds__(K1_NT)
+ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
+    const int chunks = (st.Tcap + K1_NT - 1) / K1_NT;
+    if ((int)blockIdx.x >= st.S * chunks) {
+        const int s = ((int)blockIdx.x - st.S * chunks) * (K1_NT / 32) + warp_id();
+        if (s < st.S) ocs_split_warp(st, pr, s, dets, ndets);
+        return;
+    }
+    const int s = blockIdx.x / chunks;
+    const int p = (blockIdx.x % chunks) * K1_NT + threadIdx.x;
+    OcsView v(st, s);
+    const int nT = v.hdr[OH_NLIST];
+    if (p == 0) st.n_updates[s] += (unsigned long long)nT;
+    if (p < nT) ocs_predict_track(st, pr, v, s, p);
 }
 
 // ============================================================================ K2
@@ -690,12 +703,12 @@ struct FetchLast {     // last observations (global state)
     }
 };
 
-__global__ void __launch_bounds__(K2_NT, 8)
-ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
+__device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParams& pr, const float* __restrict__ dets,
+                                              int s, unsigned char* smem_raw, OcsSmem& sm_out) {
+    const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const int Tcap = st.Tcap, Dcap = st.Dcap;
     OcsSmem sm = ocs_carve(smem_raw, Tcap, Dcap, pr.use_byte);
+    sm_out = sm;
     OcsView v(st, s);
     const float* dsrc = dets + (size_t)s * Dcap * 6;
     int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
@@ -945,7 +958,14 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
         if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
         BM_STAMP(6);
 #undef BM_STAMP
+    }
 }
+
+__global__ void __launch_bounds__(K2_NT, 8)
+ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    OcsSmem sm;
+    ocs_assoc_cta(st, pr, dets, blockIdx.x, smem_raw, sm);
 }
 
 // ============================================================================ K3
