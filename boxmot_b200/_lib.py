@@ -40,6 +40,7 @@ _SIGS = {
     "bm_ocsort_debug_profile": (c_int, [c_void_p, c_void_p]),
     "bm_ocsort_time_kernels": (c_int, [c_void_p, c_int]),
     "bm_ocsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 4)]),
+    "bm_ocsort_stream_info": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_ocsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p,
                                c_void_p, c_void_p]),
     "bm_bytetrack_create": (c_int, [ctypes.POINTER(BytetrackConfig), c_int, c_int, c_int,
@@ -59,6 +60,9 @@ _SIGS = {
                               c_void_p, c_void_p]),
     "bm_xysr_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysr_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "bm_kf_cv8": (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "bm_kf_cv8_gating": (c_int, [c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
+                                 c_void_p]),
     "bm_xysrb_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysrb_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
 }

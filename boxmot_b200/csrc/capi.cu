@@ -211,6 +211,21 @@ int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream) {
     return 0;
 }
 
+int bm_ocsort_stream_info(void* handle, int* h_n_tracks, int* h_next_id, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int S = e->st.S;
+    std::vector<int> hdr((size_t)S * bm::OH_COUNT);
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), e->st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    for (int i = 0; i < S; i++) {
+        if (h_n_tracks) h_n_tracks[i] = hdr[(size_t)i * bm::OH_COUNT + bm::OH_NLIST];
+        if (h_next_id) h_next_id[i] = hdr[(size_t)i * bm::OH_COUNT + bm::OH_NEXT_ID];
+    }
+    return 0;
+}
+
 int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P, int* h_ids, void* stream) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e || si < 0 || si >= e->st.S) return fail(-1, "bm_ocsort_peek: bad argument");

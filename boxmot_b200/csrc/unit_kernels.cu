@@ -3,6 +3,7 @@
 #include "../../include/boxmot_b200.h"
 #include "iou.cuh"
 #include "kf_xysr.cuh"
+#include "kf_xyah.cuh"
 #include "lapjv.cuh"
 #include "lap_rect.cuh"
 #include <cstdio>
@@ -114,6 +115,48 @@ __global__ void xysrb_update_kernel(double* x, double* Pb, const double* z, int 
     for (int c = 0; c < 13; c++) Pb[(size_t)i * 13 + c] = Ps[c];
 }
 
+
+// ---- constant-velocity box filters (XYAH / XYWH), dense [n][8][8] covariance at the ABI
+__device__ __forceinline__ void cv8_load(const double* mean, const double* cov, int i, double* x, double* P) {
+    for (int c = 0; c < 8; c++) x[c] = mean[(size_t)i * 8 + c];
+    const double* C = cov + (size_t)i * 64;
+    for (int c = 0; c < 4; c++) { P[c] = C[c * 8 + c]; P[4 + c] = C[c * 8 + 4 + c]; P[8 + c] = C[(4 + c) * 8 + 4 + c]; }
+}
+__device__ __forceinline__ void cv8_store(double* mean, double* cov, int i, const double* x, const double* P) {
+    for (int c = 0; c < 8; c++) mean[(size_t)i * 8 + c] = x[c];
+    xyah_expand(P, cov + (size_t)i * 64);
+}
+
+// op: 0 initiate (z -> mean, cov), 1 predict, 2 update (z, conf)
+template <int KIND>
+__global__ void cv8_kernel(int op, double* mean, double* cov, const double* z, const double* conf, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double x[8], P[12], zs[4];
+    if (z) for (int c = 0; c < 4; c++) zs[c] = z[(size_t)i * 4 + c];
+    if (op == 0) {
+        cv8_initiate<KIND>(zs, x, P);
+    } else {
+        cv8_load(mean, cov, i, x, P);
+        if (op == 1) cv8_predict<KIND>(x, P);
+        else cv8_update<KIND>(x, P, zs, conf ? conf[i] : 0.0);
+    }
+    cv8_store(mean, cov, i, x, P);
+}
+
+// out[t][d] = gating_distance(track t, measurement d)
+template <int KIND>
+__global__ void cv8_gating_kernel(const double* mean, const double* cov, int nt, const double* meas, int nd,
+                                  int only_position, int gaussian, double* out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nt * nd) return;
+    const int t = e / nd, d = e % nd;
+    double x[8], P[12], zs[4];
+    cv8_load(mean, cov, t, x, P);
+    for (int c = 0; c < 4; c++) zs[c] = meas[(size_t)d * 4 + c];
+    out[e] = cv8_gating<KIND>(x, P, zs, only_position != 0, gaussian != 0);
+}
+
 }  // namespace bm
 
 static int unit_fail(const char* what, cudaError_t e) {
@@ -190,6 +233,33 @@ int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* s
     bm::xysrb_update_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_x, d_Pb, d_z, n);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("xysrb_update_kernel", e);
+}
+
+int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z, const double* d_conf, int n,
+              void* stream) {
+    if (n <= 0) return 0;
+    if ((kind != 0 && kind != 1) || op < 0 || op > 2 || !d_mean || !d_cov || (op != 1 && !d_z)) return -1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (kind == 0) bm::cv8_kernel<bm::CV8_XYAH><<<(n + 127) / 128, 128, 0, st>>>(op, d_mean, d_cov, d_z, d_conf, n);
+    else bm::cv8_kernel<bm::CV8_XYWH><<<(n + 127) / 128, 128, 0, st>>>(op, d_mean, d_cov, d_z, d_conf, n);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("cv8_kernel", e);
+}
+
+int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_tracks, const double* d_meas,
+                     int n_meas, int only_position, int gaussian, double* d_out, void* stream) {
+    if (n_tracks <= 0 || n_meas <= 0) return 0;
+    if ((kind != 0 && kind != 1) || !d_mean || !d_cov || !d_meas || !d_out) return -1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int n = n_tracks * n_meas;
+    if (kind == 0)
+        bm::cv8_gating_kernel<bm::CV8_XYAH><<<(n + 127) / 128, 128, 0, st>>>(d_mean, d_cov, n_tracks, d_meas, n_meas,
+                                                                            only_position, gaussian, d_out);
+    else
+        bm::cv8_gating_kernel<bm::CV8_XYWH><<<(n + 127) / 128, 128, 0, st>>>(d_mean, d_cov, n_tracks, d_meas, n_meas,
+                                                                            only_position, gaussian, d_out);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("cv8_gating_kernel", e);
 }
 
 }  // extern "C"

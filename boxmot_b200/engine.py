@@ -134,6 +134,15 @@ class OcSortEngine(_HostStepMixin):
                                                      _stream_ptr(self.device)), "bm_ocsort_counters")
         return dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
 
+    def stream_info(self):
+        """(live tracks [S], tracks created so far [S]) as int32 arrays (synchronises)."""
+        n = np.zeros((self.S,), dtype=np.int32)
+        nid = np.zeros((self.S,), dtype=np.int32)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_ocsort_stream_info(self._h, n.ctypes.data, nid.ctypes.data,
+                                                        _stream_ptr(self.device)), "bm_ocsort_stream_info")
+        return n, nid
+
     def time_kernels(self, enable=True):
         """Bracket the four launches of every following step with CUDA events."""
         _lib.check(_lib.lib().bm_ocsort_time_kernels(self._h, int(bool(enable))), "bm_ocsort_time_kernels")

@@ -29,9 +29,11 @@ class OcSort(BaseTracker):
         self._engine = None
 
     def _make_engine(self):
+        # per_class (basetracker.py:154-201): one engine stream per class id, same frame count
         n = self.nr_classes if self.per_class else 1
-        if self.per_class:
-            raise NotImplementedError("per_class OC-SORT is not wired to the engine yet")
+        self._created = np.zeros((n,), dtype=np.int64)      # tracks created so far, per class
+        self._global_ids = [[] for _ in range(n)]           # class-local id -> tracker-wide id
+        self._count = 0                                      # KalmanBoxTracker.count
         self._engine = OcSortEngine(
             n, track_cap=self._caps[0], det_cap=self._caps[1], device=self._device,
             min_conf=self.min_conf, det_thresh=self.det_thresh, max_age=self.max_age,
@@ -46,11 +48,35 @@ class OcSort(BaseTracker):
         if self._engine is None:
             self._make_engine()
         self.frame_count += 1
-        rows = self._engine.step_host([dets])[0]
+        if not self.per_class:
+            rows = self._engine.step_host([dets])[0]
+            self._engine.status()
+            return rows if len(rows) else np.array([])
+        # get_class_dets_n_embs (basetracker.py:83-106): rows of class c, in input order;
+        # det_ind is then the index WITHIN the class subset (ocsort.py:265 runs per class)
+        per_cls = [dets[dets[:, 5] == c] if dets.size else dets[:0] for c in range(self.nr_classes)]
+        rows = self._engine.step_host(per_cls)
         self._engine.status()
-        return rows if len(rows) else np.array([])
+        # ids: the reference draws every new track's id from ONE counter while it walks the
+        # classes in order (KalmanBoxTracker.count, ocsort.py:79-80), emitted or not
+        _, created = self._engine.stream_info()
+        for c in range(self.nr_classes):
+            for _ in range(int(created[c] - self._created[c])):
+                self._global_ids[c].append(self._count)
+                self._count += 1
+        self._created[:] = created
+        out = []
+        for c, r in enumerate(rows):
+            if len(r):
+                r = r.copy()
+                r[:, 4] = [self._global_ids[c][int(i) - 1] + 1 for i in r[:, 4]]
+                out.append(r)
+        return np.vstack(out) if out else np.empty((0, 8))
 
     def reset(self):
         if self._engine is not None:
             self._engine.reset()
+            self._created[:] = 0
+            self._global_ids = [[] for _ in self._global_ids]
+            self._count = 0
         self.frame_count = 0

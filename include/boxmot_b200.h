@@ -92,6 +92,12 @@ int bm_bytetrack_peek(void* handle, int stream_index, int* n_active, int* n_lost
 int bm_ocsort_time_kernels(void* handle, int enable);
 int bm_ocsort_kernel_times(void* handle, float* ms4);
 
+/* Per-stream live-track count and number of tracks created so far (h_* [S], either may be
+ * NULL).  KalmanBoxTracker.count (ocsort.py:60,79-80) is ONE counter per tracker object in the
+ * reference: the per_class adapter (basetracker.py:154-201) renumbers the per-class ids with
+ * the creation counts of every class.  Synchronises the stream. */
+int bm_ocsort_stream_info(void* handle, int* h_n_tracks, int* h_next_id, void* stream);
+
 /* Debug / test access: copy one stream's list length and per-track Kalman state
  * (list order) to host buffers x[track_cap*7], P[track_cap*49], ids[track_cap]. */
 int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
@@ -130,6 +136,20 @@ int bm_xysr_update(double* d_x, double* d_P, const double* d_z, int n, void* str
  * bm_xysr_predict / bm_xysr_update on such covariances. */
 int bm_xysrb_predict(double* d_x, double* d_Pb, int n, double q_xy, double q_s, void* stream);
 int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* stream);
+
+/* Constant-velocity box Kalman filters, batched (unit-testable form of what the ByteTrack
+ * engine runs per track).  kind 0 = KalmanFilterXYAH (boxmot/motion/kalman_filters/aabb/
+ * xyah_kf.py), 1 = KalmanFilterXYWH (xywh_kf.py); op 0 = initiate (base_kalman_filter.py:43-53;
+ * reads d_z, writes mean/cov), 1 = predict (:62-77, multi_predict :111-127), 2 = update
+ * (:129-155 with project :86-109; d_conf [n] is the NSA confidence, NULL = 0).
+ * d_mean [n][8], d_cov [n][8][8] dense, d_z [n][4].  Covariances must have the filter's own
+ * sparsity (only (pos_i, vel_i) coupled), which initiate/predict/update preserve. */
+int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z, const double* d_conf,
+              int n, void* stream);
+/* gating_distance (base_kalman_filter.py:166-194) of every (track, measurement) pair:
+ * d_out [n_tracks][n_meas]; gaussian = 0 -> squared Mahalanobis ("maha"), 1 -> "gaussian". */
+int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_tracks, const double* d_meas,
+                     int n_meas, int only_position, int gaussian, double* d_out, void* stream);
 
 #ifdef __cplusplus
 }

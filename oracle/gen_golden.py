@@ -57,6 +57,61 @@ def synth_cases():
     ]
 
 
+def per_class_frames():
+    """Three classes by image column (class = floor(xc / 640)): objects that cross a boundary
+    change class, so tracks die and are born in another class's list."""
+    out = []
+    for d in make_stream(5, 40, 60):
+        d = d.copy()
+        d[:, 5] = np.floor((d[:, 0] + d[:, 2]) / 2.0 / 640.0).clip(0, 2)
+        out.append(d)
+    return out
+
+
+def main_per_class():
+    out = run_ref("ocsort", per_class_frames(), per_class=True)
+    np.savez_compressed(os.path.join(GOLD, "ref_ocsort_synth_k40_perclass.npz"), rows=out,
+                        kw=np.array(repr({"per_class": True})))
+    print("ocsort per_class", out.shape, "ids", int(out[:, 5].max()))
+
+
+def main_kf():
+    """Known-answer vectors of the reference's KalmanFilterXYAH / XYWH (rows a1-a5): a chain
+    initiate -> (predict -> update(conf))* on random boxes, and gating distances."""
+    ref_shim.load()
+    from boxmot.motion.kalman_filters.aabb.xyah_kf import KalmanFilterXYAH
+    from boxmot.motion.kalman_filters.aabb.xywh_kf import KalmanFilterXYWH
+    rng = np.random.default_rng(11)
+    out = {}
+    for kind, kf in (("xyah", KalmanFilterXYAH()), ("xywh", KalmanFilterXYWH())):
+        n, steps = 64, 6
+        c = rng.random((n, 2)) * [1800, 1000]
+        wh = rng.uniform(20, 300, (n, 2))
+        z0 = np.c_[c, wh[:, 0] / wh[:, 1] if kind == "xyah" else wh[:, 0], wh[:, 1]]
+        zs = z0[None] + np.cumsum(rng.normal(0, 1.5, (steps, n, 4)) * [1, 1, 0.01 if kind == "xyah" else 1, 1], axis=0)
+        conf = rng.uniform(0, 0.95, (steps, n))
+        means, covs = [], []
+        cur = [kf.initiate(z) for z in z0]
+        means.append(np.array([m for m, _ in cur])); covs.append(np.array([c_ for _, c_ in cur]))
+        for k in range(steps):
+            cur = [kf.predict(m, c_) for m, c_ in cur]
+            means.append(np.array([m for m, _ in cur])); covs.append(np.array([c_ for _, c_ in cur]))
+            cur = [kf.update(m, c_, zs[k, i], conf[k, i] if k % 2 else 0.0) for i, (m, c_) in enumerate(cur)]
+            means.append(np.array([m for m, _ in cur])); covs.append(np.array([c_ for _, c_ in cur]))
+        mm, cc = kf.multi_predict(means[-1].copy(), covs[-1].copy())
+        meas = zs[-1][:20]
+        gate = {}
+        for op in (False, True):
+            for metric in ("maha", "gaussian"):
+                gate["%s_%d" % (metric, op)] = np.array([kf.gating_distance(m, c_, meas, op, metric)
+                                                         for m, c_ in cur])
+        out.update({kind + "_z0": z0, kind + "_zs": zs, kind + "_conf": conf, kind + "_means": np.array(means),
+                    kind + "_covs": np.array(covs), kind + "_mp_mean": mm, kind + "_mp_cov": cc,
+                    kind + "_meas": meas, **{kind + "_gate_" + k: v for k, v in gate.items()}})
+    np.savez_compressed(os.path.join(GOLD, "ref_kf_cv8.npz"), **out)
+    print("kf cv8 vectors", {k: v.shape for k, v in out.items() if k.startswith("xyah")})
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -80,4 +135,9 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--per-class" in sys.argv:
+        main_per_class()
+    elif "--kf" in sys.argv:
+        main_kf()
+    else:
+        main()

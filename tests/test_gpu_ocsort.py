@@ -5,6 +5,7 @@ import pytest
 
 from conftest import (OCSORT_YAML, SYNTH_CASES, assert_rows_match, case_frames, golden_rows,
                       split_by_frame)
+from boxmot_b200.synth import make_stream as case_frames_raw
 
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
@@ -113,3 +114,24 @@ def test_host_pipeline_matches_direct_stepping():
         for s in range(S):
             n = want[f][1][s]
             assert np.array_equal(got[f][0][s, :n], want[f][0][s, :n])
+
+
+def test_ocsort_per_class_matches_reference_golden():
+    """per_class=True (basetracker.py:154-201): one list of tracks per class id, ONE id counter
+    for the whole tracker, det_ind relative to the class subset, rows stacked in class order."""
+    import boxmot_b200
+    want, _ = golden_rows("ocsort", "synth_k40_perclass")
+    frames = []
+    for d in case_frames_raw(5, 40, 60):
+        d = d.copy()
+        d[:, 5] = np.floor((d[:, 0] + d[:, 2]) / 2.0 / 640.0).clip(0, 2)
+        frames.append(d)
+    trk = boxmot_b200.create_tracker("ocsort", boxmot_b200.get_tracker_config("ocsort"), per_class=True)
+    want_f = split_by_frame(want, len(frames))
+    seen = 0
+    for f, d in enumerate(frames):
+        got = trk.update(d, IMG)
+        assert got.shape[1:] == (8,) or got.size == 0
+        assert_rows_match(got, want_f[f], f)
+        seen += len(got)
+    assert seen == len(want) and len(np.unique(want[:, 7])) == 3     # rows of three classes

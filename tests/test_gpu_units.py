@@ -227,3 +227,47 @@ def test_xysr_block_form_is_bit_identical():
             exp[:, b + 4, b], exp[:, b + 4, b + 4] = blk[:, 4 * b + 2], blk[:, 4 * b + 3]
         exp[:, 3, 3] = blk[:, 12]
         assert np.array_equal(full, exp), "step %d P" % step
+
+
+@pytest.mark.parametrize("kind", ["xyah", "xywh"])
+def test_cv8_kalman_kernels_match_reference_vectors(kind):
+    """bm_kf_cv8 / bm_kf_cv8_gating (block-form XYAH / XYWH filters) against the reference's own
+    KalmanFilterXYAH / XYWH outputs (tests/golden/ref_kf_cv8.npz): initiate, predict, update with
+    NSA confidence, gating distances (rows a1-a5).  Tolerance 1e-9 relative (the reference goes
+    through LAPACK/OpenBLAS; the block form differs at the rounding level only)."""
+    import os
+    from boxmot_b200 import _lib
+    from conftest import GOLD
+    z = np.load(os.path.join(GOLD, "ref_kf_cv8.npz"))
+    k = {"xyah": 0, "xywh": 1}[kind]
+    means, covs, zs, conf = z[kind + "_means"], z[kind + "_covs"], z[kind + "_zs"], z[kind + "_conf"]
+    n = means.shape[1]
+    L = _lib.lib()
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    d_mean = torch.zeros((n, 8), dtype=torch.float64, device="cuda")
+    d_cov = torch.zeros((n, 8, 8), dtype=torch.float64, device="cuda")
+    _lib.check(L.bm_kf_cv8(k, 0, p(d_mean), p(d_cov), p(_dev(z[kind + "_z0"])), None, n, None), "initiate")
+    step = 0
+
+    def check():
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(d_mean.cpu().numpy(), means[step], rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(d_cov.cpu().numpy(), covs[step], rtol=1e-9, atol=1e-12)
+
+    check()
+    for i in range(zs.shape[0]):
+        _lib.check(L.bm_kf_cv8(k, 1, p(d_mean), p(d_cov), None, None, n, None), "predict")
+        step += 1
+        check()
+        cf = _dev(conf[i]) if i % 2 else None
+        _lib.check(L.bm_kf_cv8(k, 2, p(d_mean), p(d_cov), p(_dev(zs[i])), p(cf), n, None), "update")
+        step += 1
+        check()
+    meas = _dev(z[kind + "_meas"])
+    out = torch.zeros((n, meas.shape[0]), dtype=torch.float64, device="cuda")
+    for op in (0, 1):
+        for gi, metric in enumerate(("maha", "gaussian")):
+            _lib.check(L.bm_kf_cv8_gating(k, p(d_mean), p(d_cov), n, p(meas), meas.shape[0], op, gi, p(out), None),
+                       "gating")
+            torch.cuda.synchronize()
+            np.testing.assert_allclose(out.cpu().numpy(), z["%s_gate_%s_%d" % (kind, metric, op)], rtol=1e-8)

@@ -87,6 +87,40 @@ def test_bytetrack_oracle_matches_reference_golden(case):
         assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
 
 
+@pytest.mark.parametrize("kind", ["xyah", "xywh"])
+def test_cv8_kalman_oracle_matches_reference_vectors(kind):
+    """oracle/kalman.py cv8_* against known-answer vectors generated from the reference's
+    KalmanFilterXYAH / KalmanFilterXYWH (oracle/gen_golden.py --kf): SURVEY rows a1-a5."""
+    from conftest import GOLD
+    from oracle import kalman as K
+    z = np.load(os.path.join(GOLD, "ref_kf_cv8.npz"))
+    means, covs, zs, conf = z[kind + "_means"], z[kind + "_covs"], z[kind + "_zs"], z[kind + "_conf"]
+    n = means.shape[1]
+    cur = [K.cv8_initiate(kind, z0) for z0 in z[kind + "_z0"]]
+    step = 0
+
+    def check():
+        np.testing.assert_allclose(np.array([m for m, _ in cur]), means[step], rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(np.array([c for _, c in cur]), covs[step], rtol=1e-11, atol=1e-13)
+
+    check()
+    for k in range(zs.shape[0]):
+        cur = [K.cv8_predict(kind, m, c) for m, c in cur]
+        step += 1
+        check()
+        cur = [K.cv8_update(kind, m, c, zs[k, i], conf[k, i] if k % 2 else 0.0) for i, (m, c) in enumerate(cur)]
+        step += 1
+        check()
+    mm, cc = K.cv8_multi_predict(kind, means[-1], covs[-1])
+    np.testing.assert_allclose(mm, z[kind + "_mp_mean"], rtol=1e-12)
+    np.testing.assert_allclose(cc, z[kind + "_mp_cov"], rtol=1e-11, atol=1e-13)
+    for op in (0, 1):
+        for metric in ("maha", "gaussian"):
+            got = np.array([K.cv8_gating_distance(kind, means[-1][i], covs[-1][i], z[kind + "_meas"], bool(op), metric)
+                            for i in range(n)])
+            np.testing.assert_allclose(got, z["%s_gate_%s_%d" % (kind, metric, op)], rtol=1e-10)
+
+
 def test_library_exports_every_declared_symbol():
     from boxmot_b200 import _lib, build
     path = build.build()
