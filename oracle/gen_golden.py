@@ -112,6 +112,30 @@ def main_kf():
     print("kf cv8 vectors", {k: v.shape for k, v in out.items() if k.startswith("xyah")})
 
 
+# (case, stream id, K, frames, emb_dim, tracker kwargs); MOT17 cases run without ReID
+BOTSORT_CASES = [
+    ("synth_k40_e64", 10, 40, 80, 64, {}),
+    ("synth_k100_e128", 11, 100, 50, 128, {}),
+    ("synth_k30_e32_fuse", 12, 30, 80, 32, {"fuse_first_associate": True, "appearance_thresh": 0.4}),
+    ("synth_k50_noreid", 13, 50, 80, 0, {"with_reid": False}),
+    ("MOT17_02_FRCNN", None, 0, 0, 0, {"with_reid": False}),
+]
+
+
+def main_botsort():
+    dets = {s: load_det_txt(s) for s in SEQS}
+    for name, sid, k, f, e, kw in BOTSORT_CASES:
+        if sid is None:
+            fr, em = frames_of(dets[name.replace("_", "-")].astype(np.float32).astype(np.float64)), None
+        elif e:
+            fr, em = make_stream(sid, k, f, emb_dim=e)
+        else:
+            fr, em = make_stream(sid, k, f), None
+        out = run_ref("botsort", fr, em, **kw)
+        np.savez_compressed(os.path.join(GOLD, "ref_botsort_%s.npz" % name), rows=out, kw=np.array(repr(kw)))
+        print("botsort", name, out.shape, "ids", int(out[:, 5].max()))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -139,5 +163,7 @@ if __name__ == "__main__":
         main_per_class()
     elif "--kf" in sys.argv:
         main_kf()
+    elif "--botsort" in sys.argv:
+        main_botsort()
     else:
         main()

@@ -182,4 +182,16 @@ def make_tracker(name, **overrides):
         BaseTrack.clear_count()
         args.setdefault("per_class", False)
         return ByteTrack(**args)
+    if name == "botsort":
+        # ReID backend and CMC are side inputs of the path: embeddings are passed to update()
+        # explicitly and the warp is the identity
+        import importlib
+        sys.modules.setdefault("boxmot.appearance.reid.auto_backend", types.ModuleType("x")).ReidAutoBackend = _DummyReid
+        cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
+        cmc.get_cmc_method = lambda _name: _IdentityCMC
+        mod = importlib.import_module("boxmot.trackers.botsort.botsort")
+        mod.ReidAutoBackend = _DummyReid
+        mod.get_cmc_method = lambda _name: _IdentityCMC
+        args.setdefault("per_class", False)
+        return mod.BotSort(reid_weights=None, device="cpu", half=False, **args)
     raise KeyError(name)

@@ -49,6 +49,33 @@ OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_th
 BYTETRACK_YAML = dict(min_conf=0.1, track_thresh=0.6, match_thresh=0.9, track_buffer=30, frame_rate=30)
 
 
+BOTSORT_YAML = dict(track_high_thresh=0.6, track_low_thresh=0.1, new_track_thresh=0.7, track_buffer=30,
+                    match_thresh=0.8, proximity_thresh=0.5, appearance_thresh=0.25, frame_rate=30,
+                    fuse_first_associate=False, with_reid=True)
+# case -> (stream id, K, frames, emb_dim); see oracle/gen_golden.py BOTSORT_CASES
+BOTSORT_CASES = {
+    "synth_k40_e64": (10, 40, 80, 64),
+    "synth_k100_e128": (11, 100, 50, 128),
+    "synth_k30_e32_fuse": (12, 30, 80, 32),
+    "synth_k50_noreid": (13, 50, 80, 0),
+    "MOT17_02_FRCNN": None,
+}
+
+
+def botsort_case(case):
+    """(frames, embs or None, tracker kwargs, golden rows) of a BoT-SORT fixture."""
+    from boxmot_b200.synth import make_stream
+    rows, kw = golden_rows("botsort", case)
+    spec = BOTSORT_CASES[case]
+    if spec is None:
+        return mot17_frames(case), None, kw, rows
+    sid, k, f, e = spec
+    if e:
+        fr, em = make_stream(sid, k, f, emb_dim=e)
+        return fr, em, kw, rows
+    return make_stream(sid, k, f), None, kw, rows
+
+
 def case_frames(case):
     from boxmot_b200.synth import make_stream
     if case.startswith("MOT17"):

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 from scipy.optimize import linear_sum_assignment
 
-from conftest import (BYTETRACK_YAML, OCSORT_YAML, ROOT, assert_rows_match, case_frames, golden_rows,
+from conftest import (BOTSORT_CASES, BOTSORT_YAML, BYTETRACK_YAML, OCSORT_YAML, ROOT, botsort_case, assert_rows_match, case_frames, golden_rows,
                       split_by_frame)
 from oracle import lap
 from oracle.ocsort import OcSortOracle
@@ -85,6 +85,18 @@ def test_bytetrack_oracle_matches_reference_golden(case):
     for f, d in enumerate(frames):
         got = ora.update(d)
         assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
+
+
+@pytest.mark.parametrize("case", list(BOTSORT_CASES))
+def test_botsort_oracle_matches_reference_golden(case):
+    """BoT-SORT (BASELINE configs[2] tracker): XYWH filter, IoU / embedding fusion, feature EMA."""
+    from oracle.botsort import BotSortOracle
+    frames, embs, kw, want = botsort_case(case)
+    ora = BotSortOracle(**{**BOTSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = ora.update(d, None if embs is None else embs[f].copy())
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-9)
 
 
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
