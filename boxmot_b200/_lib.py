@@ -23,6 +23,13 @@ class BytetrackConfig(ctypes.Structure):
                [(n, c_int) for n in ("track_buffer", "frame_rate")]
 
 
+class BotsortConfig(ctypes.Structure):
+    _fields_ = [(n, c_double) for n in ("track_high_thresh", "track_low_thresh", "new_track_thresh",
+                                         "match_thresh", "proximity_thresh", "appearance_thresh")] + \
+               [(n, c_int) for n in ("track_buffer", "frame_rate", "fuse_first_associate", "with_reid",
+                                      "emb_dim")]
+
+
 ASSO_FUNCS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hmiou": 4, "centroid": 5}
 
 _SIGS = {
@@ -52,6 +59,14 @@ _SIGS = {
                                       ctypes.POINTER(ctypes.c_ulonglong * 4), c_void_p]),
     "bm_bytetrack_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                   c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_botsort_create": (c_int, [ctypes.POINTER(BotsortConfig), c_int, c_int, c_int, ctypes.POINTER(c_void_p)]),
+    "bm_botsort_destroy": (c_int, [c_void_p]),
+    "bm_botsort_reset": (c_int, [c_void_p, c_void_p]),
+    "bm_botsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_botsort_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
+                                    c_void_p]),
+    "bm_botsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_lap_solve_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
                                    c_void_p, c_void_p, c_void_p]),
     "bm_lap_rect_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,

@@ -8,15 +8,21 @@
 namespace bm {
 
 // per-slot integers
-enum { BI_ID = 0, BI_STATE, BI_ACTIVATED, BI_FRAME, BI_START, BI_DETIND, BI_INREMOVED, BI_COUNT = 8 };
+enum { BI_ID = 0, BI_STATE, BI_ACTIVATED, BI_FRAME, BI_START, BI_DETIND, BI_INREMOVED, BI_NHIST, BI_COUNT = 8 };
 // TrackState (bytetrack/basetrack.py:8-12)
 enum { BT_NEW = 0, BT_TRACKED = 1, BT_LOST = 2, BT_REMOVED = 3 };
 // per-stream header
-enum { BH_NACT = 0, BH_NLOST, BH_NEXT_ID, BH_FRAME, BH_ERR, BH_LAPS, BH_MATCH, BH_BIRTHS, BH_COUNT = 8 };
+enum { BH_NACT = 0, BH_NLOST, BH_NEXT_ID, BH_FRAME, BH_ERR, BH_LAPS, BH_MATCH, BH_BIRTHS, BH_NFUPD, BH_COUNT = 12 };
+constexpr int BOT_HIST = 4;          // distinct classes remembered per track (botsort_track.py:51-64)
+constexpr int BM_ERR_CLS_HIST = 16;  // a track saw more than BOT_HIST distinct classes
+constexpr int BM_ERR_WARP = 32;      // camera-motion warp with rotation / shear (needs a dense covariance)
 
 struct ByteParams {
-    double track_thresh, min_conf, match_thresh, det_thresh;
+    double track_thresh, min_conf, match_thresh, det_thresh;   // det_thresh: births need conf >= it
     int max_time_lost;
+    // BoT-SORT only (botsort.py:49-92)
+    double proximity_thresh, appearance_thresh;
+    int fuse_first, with_reid, emb_dim;
 };
 
 struct ByteState {
@@ -30,11 +36,21 @@ struct ByteState {
     int* hdr;          // [S][BH_COUNT]
     unsigned long long* n_updates;   // [S] pool tracks that entered predict
     double* scratch;   // [S][Tcap*Dcap] materialised cost matrices (L2-resident)
+    // BoT-SORT only
+    float* feat;       // [S][Tcap][E]  smooth_feat of the slot (botsort_track.py:40-49)
+    float* dfeat;      // [S][Dcap][E]  this frame's detection features as STrack.__init__ leaves them
+    float* embd;       // [S][Tcap][Dcap] max(0, cosine distance) of (slot, high-score detection position)
+    double* chist;     // [S][2*BOT_HIST][Tcap] class votes: class ids, then accumulated confidences
+    int* fupd;         // [S][2][Dcap] (slot, detection row | birth flag << 30) feature updates of the frame
 };
 
 size_t bytetrack_step_smem(const ByteState& st);
 cudaError_t bytetrack_step_configure(size_t smem);
 cudaError_t bytetrack_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
                                   double* out, int* nout, cudaStream_t stream);
+// BoT-SORT: embedding kernel (split + feature preparation + cosine GEMM), the step, feature EMA.
+// embs [S][Dcap][E] float32 (may be NULL when with_reid = 0); warps [S][6] double or NULL (identity).
+cudaError_t botsort_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
+                                const float* embs, const double* warps, double* out, int* nout, cudaStream_t stream);
 
 }  // namespace bm

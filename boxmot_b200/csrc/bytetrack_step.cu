@@ -18,7 +18,7 @@ namespace bm {
 constexpr int BT_NT = 64;
 enum { TF_MATCHED = 1, TF_NEWLOST = 2, TF_REFIND = 4, TF_DUP = 8, TF_USED = 16, TF_AGED = 32 };
 enum { BM_NH = 0, BM_NLO, BM_NTR, BM_NP, BM_NU, BM_NUPD, BM_NR, BM_NREST, BM_NBORN, BM_NNL, BM_NRF, BM_NA2, BM_NL2,
-       BM_BAD, BM_MISC = 16 };
+       BM_BAD, BM_N1, BM_N2, BM_NFU, BM_MISC = 24 };
 
 struct ByteSmem {
     float4 *hbox, *lbox;      // [Dcap] raw high / low score detections
@@ -74,6 +74,73 @@ __device__ __forceinline__ double fuse_entry(double cost, double conf) {
     double fused = 1.0 - (sim * weight) * mask;
     if (conf < 0.5) fused = fused * 2.0;
     return fused;
+}
+
+
+// Measurement of a detection and box of a mean for the two filters:
+//   XYAH (ByteTrack): tlwh2xyah(xywh2tlwh(xyxy2xywh(det)))  (bytetrack.py:17-21), box :105-116
+//   XYWH (BoT-SORT):  xyxy2xywh(det)                         (botsort_track.py:15), box :155-159
+template <int KIND>
+__device__ __forceinline__ void det_measurement(const float4 r, double* z) {
+    if (KIND == CV8_XYAH) { det_xyah(r, z); return; }
+    const DetGeom g = det_xywh(r);
+    z[0] = g.xc; z[1] = g.yc; z[2] = g.w; z[3] = g.h;
+}
+template <int KIND>
+__device__ __forceinline__ Box mean_to_xyxy(const double* x) {
+    if (KIND == CV8_XYAH) return xyah_to_xyxy(x);
+    return Box{x[0] - x[2] / 2, x[1] - x[3] / 2, x[0] + x[2] / 2, x[1] + x[3] / 2};
+}
+
+// BoT-SORT cost entry (botsort.py:223-234 first round, :311-326 unconfirmed round)
+__device__ __forceinline__ double bot_cost(double iou_d, double conf, bool fuse, const ByteParams& pr,
+                                           const float* embd, int idx) {
+    const bool far = iou_d > pr.proximity_thresh;
+    if (fuse) iou_d = fuse_entry(iou_d, conf);
+    if (!pr.with_reid) return iou_d;
+    double e = (double)embd[idx] / 2.0;
+    if (e > pr.appearance_thresh) e = 1.0;
+    if (far) e = 1.0;
+    return fmin(iou_d, e);
+}
+
+// STrack.multi_gmc (botsort_track.py:92-104) for a warp without rotation / shear: kron(I4, R)
+// with diagonal R scales the (x, w, vx, vw) and (y, h, vy, vh) components separately and keeps
+// the covariance in block form.  Anything else needs a dense covariance: flagged, not applied.
+__device__ __forceinline__ void bot_gmc(double* x, double* P, const double* w6, int* hdr) {
+    const double r00 = w6[0], r01 = w6[1], tx = w6[2], r10 = w6[3], r11 = w6[4], ty = w6[5];
+    if (r01 != 0.0 || r10 != 0.0) { atomicOr(&hdr[BH_ERR], BM_ERR_WARP); return; }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const double r = (i & 1) ? r11 : r00;
+        x[i] = r * x[i]; x[4 + i] = r * x[4 + i];
+        P[i] = (r * P[i]) * r; P[4 + i] = (r * P[4 + i]) * r; P[8 + i] = (r * P[8 + i]) * r;
+    }
+    x[0] += tx; x[1] += ty;
+}
+
+// STrack.update_cls (botsort_track.py:51-64) after `self.cls = new_track.cls`: returns the
+// track's class.  hist: [2*BOT_HIST][Tcap] doubles (class ids, then vote sums) of one stream.
+__device__ __forceinline__ double bot_vote(double* hist, int Tcap, int slot, int& nh, double cls, double conf, int* hdr) {
+    double out = cls, best = 0.0;
+    bool found = false;
+    for (int i = 0; i < nh; i++) {
+        const double c = hist[i * Tcap + slot];
+        double sum = hist[(BOT_HIST + i) * Tcap + slot];
+        if (cls == c) { sum += conf; hist[(BOT_HIST + i) * Tcap + slot] = sum; found = true; }
+        if (sum > best) { best = sum; out = c; }
+    }
+    if (!found) {
+        if (nh < BOT_HIST) {
+            hist[nh * Tcap + slot] = cls;
+            hist[(BOT_HIST + nh) * Tcap + slot] = conf;
+            nh++;
+        } else {
+            atomicOr(&hdr[BH_ERR], BM_ERR_CLS_HIST);
+        }
+        out = cls;
+    }
+    return out;
 }
 
 struct ByteView {
@@ -135,10 +202,17 @@ __device__ inline void byte_assign(const double* cost, int nr, int nc, double th
     __syncwarp();
 }
 
+// MODE 0 = ByteTrack (XYAH filter, fuse_score in the first round), MODE 1 = BoT-SORT
+// (boxmot/trackers/botsort/botsort.py:94-411: XYWH filter, camera-motion warp, IoU / embedding
+// fusion with proximity and appearance gates, class voting, new_track_thresh; the embedding
+// distances come from bot_embed_kernel, the feature EMA is applied by bot_ema_kernel).
 // <= 146 registers: seven CTAs per SM keep all 1024 streams of the bench in one wave on 148 SMs
+enum { MODE_BYTE = 0, MODE_BOT = 1 };
+template <int MODE>
 __global__ void __launch_bounds__(BT_NT, 7)
 byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, const int* __restrict__ ndets,
-                 double* __restrict__ out, int* __restrict__ nout) {
+                 const double* __restrict__ warps, double* __restrict__ out, int* __restrict__ nout) {
+    constexpr int KIND = MODE == MODE_BOT ? CV8_XYWH : CV8_XYAH;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const int Tcap = st.Tcap, Dcap = st.Dcap;
@@ -188,20 +262,37 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         const int slot = sm.pool[p];
         double x[8], P[12];
         v.load(slot, x, P);
-        if (v.I(BI_STATE, slot) != BT_TRACKED) x[7] = 0.0;
-        xyah_predict(x, P);
+        if (v.I(BI_STATE, slot) != BT_TRACKED) {
+            x[7] = 0.0;
+            if (MODE == MODE_BOT) x[6] = 0.0;       // botsort_track.py:83-85 resets both size velocities
+        }
+        cv8_predict<KIND>(x, P);
+        if (MODE == MODE_BOT && warps) bot_gmc(x, P, warps + (size_t)s * 6, v.hdr);
         v.store(slot, x, P);
-        v.set_box(slot, xyah_to_xyxy(x));
+        v.set_box(slot, mean_to_xyxy<KIND>(x));
         sm.tflag[slot] |= TF_USED;
     }
-    for (int p = tid; p < nU; p += BT_NT) sm.tflag[sm.unc[p]] |= TF_USED;   // box is current (set at birth)
+    for (int p = tid; p < nU; p += BT_NT) {          // unconfirmed tracks are not predicted, only warped
+        const int slot = sm.unc[p];
+        sm.tflag[slot] |= TF_USED;
+        if (MODE == MODE_BOT && warps) {
+            double x[8], P[12];
+            v.load(slot, x, P);
+            bot_gmc(x, P, warps + (size_t)s * 6, v.hdr);
+            v.store(slot, x, P);
+            v.set_box(slot, mean_to_xyxy<KIND>(x));
+        }
+    }
     if (tid == 0) st.n_updates[s] += (unsigned long long)nP;
     __syncthreads();
 
     // ---- first association: pool x high-score detections, fuse_score, thresh = match_thresh (:199-219)
+    const float* embd = MODE == MODE_BOT ? st.embd + (size_t)s * Tcap * Dcap : nullptr;
     for (int e = tid; e < nP * nH; e += BT_NT) {
-        const int t = e / nH, d = e % nH;
-        cost[e] = fuse_entry(1.0 - iou_pair(v.box(sm.pool[t]), det_xyxy(sm.hbox[d])), (double)sm.hconf[d]);
+        const int t = e / nH, d = e % nH, slot = sm.pool[t];
+        const double iou_d = 1.0 - iou_pair(v.box(slot), det_xyxy(sm.hbox[d]));
+        if (MODE == MODE_BYTE) cost[e] = fuse_entry(iou_d, (double)sm.hconf[d]);
+        else cost[e] = bot_cost(iou_d, (double)sm.hconf[d], pr.fuse_first != 0, pr, embd, slot * Dcap + d);
     }
     __syncthreads();
     if (wid == 0) {
@@ -220,7 +311,7 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
                                     [&](int t) { return sm.pool[t]; });
         // detections left for the unconfirmed round: y < 0 (:252)
         const int nrest = warp_compact(nH, sm.rest, 0, [&](int d) { return sm.dflag[d] == 0; }, [&](int d) { return d; });
-        if (lane == 0) { sm.misc[BM_NUPD] = n1; sm.misc[BM_NRF] = nrf; sm.misc[BM_NR] = nr; sm.misc[BM_NREST] = nrest; }
+        if (lane == 0) { sm.misc[BM_NUPD] = n1; sm.misc[BM_N1] = n1; sm.misc[BM_NRF] = nrf; sm.misc[BM_NR] = nr; sm.misc[BM_NREST] = nrest; }
     }
     __syncthreads();
 
@@ -240,14 +331,16 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         // mark_lost (:246-250), in u_track order
         const int nnl = warp_compact(nR, sm.nlost, 0, [&](int t) { return sm.xs[t] == -1; }, [&](int t) { return sm.rtr[t]; });
         for (int k = lane; k < nnl; k += 32) { const int slot = sm.nlost[k]; sm.tflag[slot] |= TF_NEWLOST; v.I(BI_STATE, slot) = BT_LOST; }
-        if (lane == 0) { sm.misc[BM_NUPD] = n1; sm.misc[BM_NNL] = nnl; }
+        if (lane == 0) { sm.misc[BM_NUPD] = n1; sm.misc[BM_N2] = n1; sm.misc[BM_NNL] = nnl; }
     }
     __syncthreads();
 
     // ---- unconfirmed tracks x remaining high-score detections, fuse_score, thresh 0.7 (:252-264)
     for (int e = tid; e < nU * nRest; e += BT_NT) {
         const int t = e / nRest, k = e % nRest, d = sm.rest[k];
-        cost[e] = fuse_entry(1.0 - iou_pair(v.box(sm.unc[t]), det_xyxy(sm.hbox[d])), (double)sm.hconf[d]);
+        const double iou_d = 1.0 - iou_pair(v.box(sm.unc[t]), det_xyxy(sm.hbox[d]));
+        if (MODE == MODE_BYTE) cost[e] = fuse_entry(iou_d, (double)sm.hconf[d]);
+        else cost[e] = bot_cost(iou_d, (double)sm.hconf[d], true, pr, embd, sm.unc[t] * Dcap + d);
     }
     __syncthreads();
     if (wid == 0) {
@@ -282,25 +375,43 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
             slot = sm.rtr[k - nUpd]; drow = sm.hind[sm.born[k - nUpd]];
         }
         const float* r = dsrc + drow * 6;
-        det_xyah(make_float4(r[0], r[1], r[2], r[3]), z);
+        det_measurement<KIND>(make_float4(r[0], r[1], r[2], r[3]), z);
         if (k < nUpd) {
             v.load(slot, x, P);
-            xyah_update(x, P, z);
+            cv8_update<KIND>(x, P, z, 0.0);
             v.I(BI_ACTIVATED, slot) = 1;
         } else {
-            xyah_initiate(z, x, P);
+            cv8_initiate<KIND>(z, x, P);
             v.I(BI_ID, slot) = id0 + (k - nUpd) + 1;
             v.I(BI_ACTIVATED, slot) = frame == 1 ? 1 : 0;
             v.I(BI_START, slot) = frame;
             v.I(BI_INREMOVED, slot) = 0;
+            v.I(BI_NHIST, slot) = 0;
         }
         v.store(slot, x, P);
-        v.set_box(slot, xyah_to_xyxy(x));
+        v.set_box(slot, mean_to_xyxy<KIND>(x));
         v.I(BI_STATE, slot) = BT_TRACKED;
         v.I(BI_FRAME, slot) = frame;
         v.I(BI_DETIND, slot) = drow;
         v.confcls[slot] = (double)r[4];
-        v.confcls[Tcap + slot] = (double)r[5];
+        double cls = (double)r[5];
+        if (MODE == MODE_BOT) {
+            cls = bot_vote(st.chist + (size_t)s * 2 * BOT_HIST * Tcap, Tcap, slot, v.I(BI_NHIST, slot), cls, (double)r[4],
+                           v.hdr);
+            // feature EMA (botsort_track.py:40-49): first-round and unconfirmed matches, births; the
+            // low-score detections of the second round carry no feature
+            if (pr.with_reid && (k < sm.misc[BM_N1] || k >= sm.misc[BM_N2])) {
+                const int q = atomicAdd(&sm.misc[BM_NFU], 1);
+                int* fu = st.fupd + (size_t)s * 2 * Dcap;
+                fu[q] = slot;
+                fu[Dcap + q] = drow | (k >= nUpd ? 1 << 30 : 0);
+            }
+        }
+        v.confcls[Tcap + slot] = cls;
+    }
+    if (MODE == MODE_BOT) {
+        __syncthreads();
+        if (tid == 0) v.hdr[BH_NFUPD] = sm.misc[BM_NFU];
     }
     __syncthreads();
     // ---- lost tracks age out (:273-276); the flag only takes effect one frame later (:283-285)
@@ -372,15 +483,170 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
     }
 }
 
+// ============================================================================ BoT-SORT side kernels
+// bot_embed_kernel: one CTA per stream, before the step.
+//   (1) high-score split (same predicate and order as the step kernel),
+//   (2) detection features as STrack.__init__ leaves them (botsort_track.py:36-48: normalised
+//       twice, because smooth_feat aliases curr_feat on the first update_features call), fp32,
+//   (3) embedding_distance (boxmot/utils/matching.py:230-321) of every live track (active and
+//       lost lists) against every high-score detection: max(0, 1 - t.d / (|t| |d|)), a
+//       [live x E] . [E x nH] contraction with fp32 FFMA tiles, stored as float by slot.
+constexpr int BE_NT = 256, BE_TILE = 64, BE_K = 32;
+
+__device__ __forceinline__ float warp_sum_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(BM_FULL, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(BE_NT)
+bot_embed_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, const int* __restrict__ ndets,
+                 const float* __restrict__ embs) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
+    const int Tcap = st.Tcap, Dcap = st.Dcap, E = pr.emb_dim;
+    float* At = reinterpret_cast<float*>(smem_raw);            // [BE_TILE][BE_K + 1]
+    float* Bt = At + BE_TILE * (BE_K + 1);                     // [BE_TILE][BE_K + 1]
+    float* tn = Bt + BE_TILE * (BE_K + 1);                     // [Tcap] |smooth_feat| by row
+    float* dn = tn + Tcap;                                     // [Dcap] |feature| by high-score position
+    int* rows = reinterpret_cast<int*>(dn + Dcap);             // [Tcap] live slots
+    int* hind = rows + Tcap;                                   // [Dcap]
+    __shared__ int s_nh;
+    ByteView v(st, s);
+    const float* dsrc = dets + (size_t)s * Dcap * 6;
+    const int nA = v.hdr[BH_NACT], nL = v.hdr[BH_NLOST], nLive = nA + nL;
+    int nD_in = ndets[s];
+    if (nD_in > Dcap) nD_in = Dcap;
+    if (wid == 0) {
+        const int nh = warp_compact(nD_in, hind, 0, [&](int i) { return (double)dsrc[i * 6 + 4] > pr.track_thresh; },
+                                    [&](int i) { return i; });
+        if (lane == 0) s_nh = nh;
+    }
+    for (int i = tid; i < nLive; i += BE_NT) rows[i] = i < nA ? v.act[i] : v.lost[i - nA];
+    __syncthreads();
+    const int nH = s_nh;
+    const float* esrc = embs + (size_t)s * Dcap * E;
+    float* dfeat = st.dfeat + (size_t)s * Dcap * E;
+    const float* feat = st.feat + (size_t)s * Tcap * E;
+    for (int d = wid; d < nH; d += BE_NT / 32) {
+        const float* src = esrc + (size_t)hind[d] * E;
+        float* dst = dfeat + (size_t)hind[d] * E;
+        float ss = 0.f;
+        for (int e = lane; e < E; e += 32) { const float x = src[e]; ss += x * x; }
+        const float n1 = sqrtf(warp_sum_f(ss));
+        ss = 0.f;
+        for (int e = lane; e < E; e += 32) { const float x = src[e] / n1; ss += x * x; }
+        const float n2 = sqrtf(warp_sum_f(ss));
+        ss = 0.f;
+        for (int e = lane; e < E; e += 32) { const float x = (src[e] / n1) / n2; dst[e] = x; ss += x * x; }
+        ss = warp_sum_f(ss);
+        if (lane == 0) dn[d] = sqrtf(ss);
+    }
+    for (int i = wid; i < nLive; i += BE_NT / 32) {
+        const float* src = feat + (size_t)rows[i] * E;
+        float ss = 0.f;
+        for (int e = lane; e < E; e += 32) { const float x = src[e]; ss += x * x; }
+        ss = warp_sum_f(ss);
+        if (lane == 0) tn[i] = sqrtf(ss);
+    }
+    __syncthreads();
+    float* embd = st.embd + (size_t)s * Tcap * Dcap;
+    const int ty = tid / 16, tx = tid % 16;
+    for (int r0 = 0; r0 < nLive; r0 += BE_TILE) {
+        for (int c0 = 0; c0 < nH; c0 += BE_TILE) {
+            float acc[4][4] = {};
+            for (int k0 = 0; k0 < E; k0 += BE_K) {
+                for (int q = tid; q < BE_TILE * BE_K; q += BE_NT) {
+                    const int i = q / BE_K, kk = q % BE_K;
+                    const bool kin = k0 + kk < E;
+                    At[i * (BE_K + 1) + kk] = (r0 + i < nLive && kin) ? feat[(size_t)rows[r0 + i] * E + k0 + kk] : 0.f;
+                    Bt[i * (BE_K + 1) + kk] = (c0 + i < nH && kin) ? dfeat[(size_t)hind[c0 + i] * E + k0 + kk] : 0.f;
+                }
+                __syncthreads();
+#pragma unroll 8
+                for (int kk = 0; kk < BE_K; kk++) {
+                    float a[4], b[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) { a[i] = At[(ty * 4 + i) * (BE_K + 1) + kk]; b[i] = Bt[(tx * 4 + i) * (BE_K + 1) + kk]; }
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+#pragma unroll
+                        for (int j = 0; j < 4; j++) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                }
+                __syncthreads();
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int r = r0 + ty * 4 + i, c = c0 + tx * 4 + j;
+                    if (r < nLive && c < nH) {
+                        const double cs = (double)acc[i][j] / ((double)tn[r] * (double)dn[c]);
+                        embd[(size_t)rows[r] * Dcap + c] = (float)fmax(0.0, 1.0 - cs);
+                    }
+                }
+        }
+    }
+}
+
+static size_t bot_embed_smem(const ByteState& st) {
+    return sizeof(float) * (2 * BE_TILE * (BE_K + 1) + st.Tcap + st.Dcap) + sizeof(int) * (st.Tcap + st.Dcap);
+}
+
+// bot_ema_kernel: STrack.update_features (botsort_track.py:40-49) for the frame's feature
+// updates, one warp per (slot, detection): births copy the detection feature; matches blend
+// smooth = 0.9 smooth + 0.1 (feat / |feat|) and renormalise, all in float32 as the reference.
+__global__ void __launch_bounds__(256)
+bot_ema_kernel(ByteState st, ByteParams pr) {
+    const int s = blockIdx.x, lane = lane_id();
+    const int q = blockIdx.y * 8 + warp_id();
+    const int Tcap = st.Tcap, Dcap = st.Dcap, E = pr.emb_dim;
+    if (q >= st.hdr[(size_t)s * BH_COUNT + BH_NFUPD]) return;
+    const int* fu = st.fupd + (size_t)s * 2 * Dcap;
+    const int slot = fu[q], rw = fu[Dcap + q], r = rw & ((1 << 30) - 1);
+    const float* src = st.dfeat + ((size_t)s * Dcap + r) * E;
+    float* dst = st.feat + ((size_t)s * Tcap + slot) * E;
+    if (rw >> 30) {
+        for (int e = lane; e < E; e += 32) dst[e] = src[e];
+        return;
+    }
+    float ss = 0.f;
+    for (int e = lane; e < E; e += 32) { const float x = src[e]; ss += x * x; }
+    const float n1 = sqrtf(warp_sum_f(ss));
+    ss = 0.f;
+    for (int e = lane; e < E; e += 32) { const float m = 0.9f * dst[e] + 0.1f * (src[e] / n1); ss += m * m; }
+    const float n2 = sqrtf(warp_sum_f(ss));
+    for (int e = lane; e < E; e += 32) dst[e] = (0.9f * dst[e] + 0.1f * (src[e] / n1)) / n2;
+}
+
 size_t bytetrack_step_smem(const ByteState& st) { return byte_smem_bytes(st.Tcap, st.Dcap); }
 
 cudaError_t bytetrack_step_configure(size_t smem) {
-    return cudaFuncSetAttribute(byte_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(byte_step_kernel<MODE_BYTE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(byte_step_kernel<MODE_BOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
 cudaError_t bytetrack_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
                                   double* out, int* nout, cudaStream_t stream) {
-    byte_step_kernel<<<st.S, BT_NT, bytetrack_step_smem(st), stream>>>(st, pr, dets, ndets, out, nout);
+    byte_step_kernel<MODE_BYTE><<<st.S, BT_NT, bytetrack_step_smem(st), stream>>>(st, pr, dets, ndets, nullptr, out, nout);
+    return cudaGetLastError();
+}
+
+cudaError_t botsort_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
+                                const float* embs, const double* warps, double* out, int* nout, cudaStream_t stream) {
+    if (pr.with_reid) {
+        static bool once = false;
+        const size_t sm = bot_embed_smem(st);
+        if (!once) {
+            cudaError_t e = cudaFuncSetAttribute(bot_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+            if (e != cudaSuccess) return e;
+            once = true;
+        }
+        bot_embed_kernel<<<st.S, BE_NT, sm, stream>>>(st, pr, dets, ndets, embs);
+    }
+    byte_step_kernel<MODE_BOT><<<st.S, BT_NT, bytetrack_step_smem(st), stream>>>(st, pr, dets, ndets, warps, out, nout);
+    if (pr.with_reid) bot_ema_kernel<<<dim3(st.S, (st.Dcap + 7) / 8), 256, 0, stream>>>(st, pr);
     return cudaGetLastError();
 }
 

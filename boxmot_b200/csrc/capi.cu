@@ -33,10 +33,11 @@ struct OcsEngine {
     bool timing = false, timed = false;
 };
 
-struct ByteEngine {
+struct ByteEngine {      // ByteTrack and BoT-SORT share the state layout and the step kernel
     bm::ByteState st;
     bm::ByteParams pr;
     std::vector<void*> allocs;
+    bool bot = false;
 };
 
 template <typename E, typename T>
@@ -258,20 +259,22 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
 
 // ---------------------------------------------------------------------------- ByteTrack
 
-int bm_bytetrack_create(const bm_bytetrack_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
-    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
-        return fail(-1, "bm_bytetrack_create: bad argument");
-    if (track_cap > 1024) return fail(-1, "bm_bytetrack_create: track_cap must be <= 1024");
-    ByteEngine* e = new (std::nothrow) ByteEngine();
-    if (!e) return fail(-3, "out of host memory");
+static int byte_family_create(ByteEngine* e, int n_streams, int track_cap, int det_cap, void** handle) {
     bm::ByteState& st = e->st;
     st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap;
-    bm::ByteParams& pr = e->pr;
-    pr.track_thresh = cfg->track_thresh; pr.min_conf = cfg->min_conf; pr.match_thresh = cfg->match_thresh;
-    pr.det_thresh = cfg->track_thresh;                                   // bytetrack.py:152
-    pr.max_time_lost = (int)(cfg->frame_rate / 30.0 * cfg->track_buffer);   // bytetrack.py:153-154
-    const size_t S = n_streams, T = track_cap;
+    st.feat = st.dfeat = st.embd = nullptr; st.chist = nullptr; st.fupd = nullptr;
+    const size_t S = n_streams, T = track_cap, E = e->pr.emb_dim;
     cudaError_t r = cudaSuccess;
+    if (e->bot) {
+        if (r == cudaSuccess) r = dev_alloc(e, &st.chist, S * 2 * bm::BOT_HIST * T);
+        if (r == cudaSuccess) r = dev_alloc(e, &st.fupd, S * 2 * (size_t)det_cap);
+        if (e->pr.with_reid) {
+            if (r == cudaSuccess) r = dev_alloc(e, &st.feat, S * T * E);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.dfeat, S * (size_t)det_cap * E);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.embd, S * T * (size_t)det_cap);
+            if (r == cudaSuccess) r = cudaMemset(st.feat, 0, S * T * E * sizeof(float));
+        }
+    }
     if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::XA_N * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.confcls, S * 2 * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.tbox, S * 4 * T);
@@ -285,10 +288,63 @@ int bm_bytetrack_create(const bm_bytetrack_config* cfg, int n_streams, int track
     if (r != cudaSuccess) {
         for (void* p : e->allocs) cudaFree(p);
         delete e;
-        return fail(-2, "bm_bytetrack_create", r);
+        return fail(-2, "engine create", r);
     }
     *handle = e;
     return bm_bytetrack_reset(e, nullptr);
+}
+
+int bm_bytetrack_create(const bm_bytetrack_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
+        return fail(-1, "bm_bytetrack_create: bad argument");
+    if (track_cap > 1024) return fail(-1, "bm_bytetrack_create: track_cap must be <= 1024");
+    ByteEngine* e = new (std::nothrow) ByteEngine();
+    if (!e) return fail(-3, "out of host memory");
+    bm::ByteParams& pr = e->pr;
+    pr = bm::ByteParams{};
+    pr.track_thresh = cfg->track_thresh; pr.min_conf = cfg->min_conf; pr.match_thresh = cfg->match_thresh;
+    pr.det_thresh = cfg->track_thresh;                                   // bytetrack.py:152
+    pr.max_time_lost = (int)(cfg->frame_rate / 30.0 * cfg->track_buffer);   // bytetrack.py:153-154
+    return byte_family_create(e, n_streams, track_cap, det_cap, handle);
+}
+
+int bm_botsort_create(const bm_botsort_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
+        return fail(-1, "bm_botsort_create: bad argument");
+    if (track_cap > 1024) return fail(-1, "bm_botsort_create: track_cap must be <= 1024");
+    if (cfg->with_reid && cfg->emb_dim <= 0) return fail(-1, "bm_botsort_create: with_reid needs emb_dim > 0");
+    ByteEngine* e = new (std::nothrow) ByteEngine();
+    if (!e) return fail(-3, "out of host memory");
+    e->bot = true;
+    bm::ByteParams& pr = e->pr;
+    pr = bm::ByteParams{};
+    pr.track_thresh = cfg->track_high_thresh; pr.min_conf = cfg->track_low_thresh;
+    pr.match_thresh = cfg->match_thresh; pr.det_thresh = cfg->new_track_thresh;
+    pr.max_time_lost = (int)(cfg->frame_rate / 30.0 * cfg->track_buffer);   // botsort.py:76-77
+    pr.proximity_thresh = cfg->proximity_thresh; pr.appearance_thresh = cfg->appearance_thresh;
+    pr.fuse_first = cfg->fuse_first_associate ? 1 : 0; pr.with_reid = cfg->with_reid ? 1 : 0;
+    pr.emb_dim = cfg->with_reid ? cfg->emb_dim : 0;
+    return byte_family_create(e, n_streams, track_cap, det_cap, handle);
+}
+
+int bm_botsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                    const double* d_warps, double* d_out, int* d_nout, void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || !e->bot || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_botsort_step: bad argument");
+    if (e->pr.with_reid && !d_embs) return fail(-1, "bm_botsort_step: with_reid needs embeddings");
+    BM_CUDA(bm::botsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
+                                    static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int bm_botsort_destroy(void* handle) { return bm_bytetrack_destroy(handle); }
+int bm_botsort_reset(void* handle, void* stream) { return bm_bytetrack_reset(handle, stream); }
+int bm_botsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream) {
+    return bm_bytetrack_counters(handle, err_bits, out4, stream);
+}
+int bm_botsort_peek(void* handle, int si, int* n_active, int* n_lost, double* h_mean, double* h_cov, int* h_ids,
+                    void* stream) {
+    return bm_bytetrack_peek(handle, si, n_active, n_lost, h_mean, h_cov, h_ids, stream);
 }
 
 int bm_bytetrack_destroy(void* handle) {
@@ -318,7 +374,7 @@ int bm_bytetrack_reset(void* handle, void* stream) {
 int bm_bytetrack_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out, int* d_nout,
                       void* stream) {
     ByteEngine* e = static_cast<ByteEngine*>(handle);
-    if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_bytetrack_step: null argument");
+    if (!e || e->bot || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_bytetrack_step: bad argument");
     BM_CUDA(bm::bytetrack_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
                                       static_cast<cudaStream_t>(stream)));
     return 0;

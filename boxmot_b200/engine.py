@@ -8,7 +8,9 @@ import torch
 from boxmot_b200 import _lib
 
 ERR_BITS = {1: "track capacity exceeded", 2: "detection capacity exceeded",
-            4: "cost matrix larger than scratch", 8: "non-finite costs reached the assignment solver"}
+            4: "cost matrix larger than scratch", 8: "non-finite costs reached the assignment solver",
+            16: "a track saw more distinct classes than the class-vote history holds",
+            32: "camera-motion warp with rotation or shear (needs a dense covariance: not supported)"}
 
 
 def _ptr(t):
@@ -245,7 +247,7 @@ class ByteTrackEngine(_HostStepMixin):
         self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
         self.launches = 0
 
-    def close(self):
+    def close(self):     # bm_botsort_destroy is the same entry (shared engine state)
         if getattr(self, "_h", None) is not None and self._h.value:
             _lib.lib().bm_bytetrack_destroy(self._h)
             self._h = ctypes.c_void_p()
@@ -301,3 +303,83 @@ class ByteTrackEngine(_HostStepMixin):
                                                     _stream_ptr(self.device)), "bm_bytetrack_peek")
         k = na.value + nl.value
         return m[:k], P[:k].reshape(k, 8, 8), ids[:k], na.value
+
+
+class BotSortEngine(ByteTrackEngine):
+    """S independent BoT-SORT trackers (boxmot/trackers/botsort/botsort.py:49-411) per step.
+
+    ReID and CMC are side inputs: ``embs`` [S, det_cap, emb_dim] float32 row-aligned with
+    ``dets`` (required when ``with_reid``), ``warps`` [S, 2, 3] float64 or None (identity)."""
+
+    def __init__(self, n_streams, track_cap=256, det_cap=128, device="cuda:0", track_high_thresh=0.5,
+                 track_low_thresh=0.1, new_track_thresh=0.6, track_buffer=30, match_thresh=0.8,
+                 proximity_thresh=0.5, appearance_thresh=0.25, frame_rate=30, fuse_first_associate=False,
+                 with_reid=True, emb_dim=512):
+        if not torch.cuda.is_available():
+            raise RuntimeError("BotSortEngine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.S, self.Tcap, self.Dcap = int(n_streams), int(track_cap), int(det_cap)
+        self.with_reid, self.E = bool(with_reid), int(emb_dim) if with_reid else 0
+        cfg = _lib.BotsortConfig(track_high_thresh, track_low_thresh, new_track_thresh, match_thresh,
+                                 proximity_thresh, appearance_thresh, int(track_buffer), int(frame_rate),
+                                 int(bool(fuse_first_associate)), int(self.with_reid), self.E)
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_botsort_create(ctypes.byref(cfg), self.S, self.Tcap, self.Dcap,
+                                                    ctypes.byref(self._h)), "bm_botsort_create")
+            torch.cuda.synchronize(self.device)
+        self.out_rows = min(self.Tcap, self.Dcap)
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+        self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+        self.launches = 0
+
+    def step(self, dets, ndets, embs=None, warps=None, out=None, nout=None):
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (self.S, self.Dcap, 6)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        if self.with_reid:
+            assert embs is not None and embs.dtype == torch.float32 and embs.is_cuda and embs.is_contiguous()
+            assert tuple(embs.shape) == (self.S, self.Dcap, self.E)
+        if warps is not None:
+            assert warps.dtype == torch.float64 and warps.is_cuda and tuple(warps.shape) == (self.S, 2, 3)
+            assert warps.is_contiguous()
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_botsort_step(self._h, _ptr(dets), _ptr(ndets),
+                                                  _ptr(embs) if self.with_reid else None,
+                                                  _ptr(warps) if warps is not None else None,
+                                                  _ptr(out), _ptr(nout), _stream_ptr(self.device)), "bm_botsort_step")
+        self.launches += 3 if self.with_reid else 1
+        return out, nout
+
+    def step_host(self, dets_per_stream, embs_per_stream=None, warps=None):
+        """Lists of S arrays (N_s, 6) and (N_s, E); returns a list of (M_s, 8) arrays."""
+        if not hasattr(self, "_h_dets"):
+            self._h_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32).pin_memory()
+            self._h_nd = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+            self._h_embs = torch.zeros((self.S, self.Dcap, max(self.E, 1)), dtype=torch.float32).pin_memory()
+            self._h_out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64).pin_memory()
+            self._h_nout = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+        hd, hn, he = self._h_dets.numpy(), self._h_nd.numpy(), self._h_embs.numpy()
+        for s, d in enumerate(dets_per_stream):
+            n = 0 if d is None else len(d)
+            if n > self.Dcap:
+                raise RuntimeError("stream %d: %d detections exceed det_cap=%d" % (s, n, self.Dcap))
+            if n:
+                hd[s, :n] = d
+                if self.with_reid:
+                    he[s, :n] = embs_per_stream[s]
+            hn[s] = n
+        d_dets = self._h_dets.to(self.device, non_blocking=True)
+        d_nd = self._h_nd.to(self.device, non_blocking=True)
+        d_embs = self._h_embs.to(self.device, non_blocking=True) if self.with_reid else None
+        d_w = None if warps is None else torch.as_tensor(np.asarray(warps, dtype=np.float64)).reshape(
+            self.S, 2, 3).contiguous().to(self.device)
+        out, nout = self.step(d_dets, d_nd, d_embs, d_w)
+        self._h_out.copy_(out, non_blocking=True)
+        self._h_nout.copy_(nout, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
+        return [ho[s, : hn2[s]].copy() for s in range(self.S)]

@@ -17,6 +17,7 @@ def get_tracker_config(tracker_type):
 _MAPPING = {
     "ocsort": ("boxmot_b200.trackers.ocsort", "OcSort"),
     "bytetrack": ("boxmot_b200.trackers.bytetrack", "ByteTrack"),
+    "botsort": ("boxmot_b200.trackers.botsort", "BotSort"),
 }
 _REID_TRACKERS = ("strongsort", "botsort", "deepocsort", "hybridsort", "boosttrack")
 

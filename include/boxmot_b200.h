@@ -85,6 +85,32 @@ int bm_bytetrack_counters(void* handle, int* err_bits, unsigned long long* out4,
 int bm_bytetrack_peek(void* handle, int stream_index, int* n_active, int* n_lost, double* h_mean,
                       double* h_cov, int* h_ids, void* stream);
 
+/* ---- BoT-SORT engine ---------------------------------------------------------------
+ * Replaces BotSort.__init__/update and its stages (boxmot/trackers/botsort/botsort.py:49-92,
+ * :94-411), STrack incl. update_features / update_cls / multi_predict / multi_gmc
+ * (botsort_track.py:10-159), botsort_utils.py:10-81, KalmanFilterXYWH, and iou_distance /
+ * fuse_score / embedding_distance / linear_assignment (boxmot/utils/matching.py:184-227,
+ * :488-560, :230-321, :30-108).  ReID and CMC are side inputs: d_embs [S][det_cap][emb_dim]
+ * float32 rows aligned with d_dets (NULL when with_reid = 0), d_warps [S][6] float64 row-major
+ * 2x3 camera-motion warps or NULL for the identity (warps with rotation / shear set error bit
+ * 32: they need a dense covariance).  Other buffers as bm_bytetrack_step.  One frame = three
+ * launches: embedding kernel (feature preparation + cosine-distance contraction), the step,
+ * the feature EMA. */
+typedef struct bm_botsort_config {
+    double track_high_thresh, track_low_thresh, new_track_thresh, match_thresh, proximity_thresh,
+        appearance_thresh;
+    int track_buffer, frame_rate, fuse_first_associate, with_reid, emb_dim;
+} bm_botsort_config;
+int bm_botsort_create(const bm_botsort_config* cfg, int n_streams, int track_cap, int det_cap,
+                      void** handle);
+int bm_botsort_destroy(void* handle);
+int bm_botsort_reset(void* handle, void* stream);
+int bm_botsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                    const double* d_warps, double* d_out, int* d_nout, void* stream);
+int bm_botsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
+int bm_botsort_peek(void* handle, int stream_index, int* n_active, int* n_lost, double* h_mean,
+                    double* h_cov, int* h_ids, void* stream);
+
 /* Per-kernel timing of the frame step (measurement aid for bench.py's roofline): when
  * enabled, bm_ocsort_step brackets its four launches (predict, assoc, update, finalize) with
  * CUDA events on the caller's stream; bm_ocsort_kernel_times waits for the last timed step and
