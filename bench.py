@@ -27,6 +27,9 @@ if ROOT not in sys.path:
 OCSORT_YAML = dict(min_conf=0.1, det_thresh=0.6, max_age=30, min_hits=3, asso_threshold=0.3,
                    delta_t=3, asso_func="iou", inertia=0.1, use_byte=False, Q_xy_scaling=0.01,
                    Q_s_scaling=0.0001)     # boxmot/configs/trackers/ocsort.yaml defaults
+BOTSORT_YAML = dict(track_high_thresh=0.6, track_low_thresh=0.1, new_track_thresh=0.7, track_buffer=30,
+                    match_thresh=0.8, proximity_thresh=0.5, appearance_thresh=0.25, frame_rate=30,
+                    fuse_first_associate=False, with_reid=True)   # boxmot/configs/trackers/botsort.yaml
 BYTETRACK_YAML = dict(min_conf=0.1, track_thresh=0.6, match_thresh=0.9, track_buffer=30,
                       frame_rate=30)   # boxmot/configs/trackers/bytetrack.yaml defaults
 METRIC = "track-updates/sec"
@@ -48,29 +51,46 @@ def emit(line):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=290)
+    ap.add_argument("--steps", type=int, default=None, help="default 290 (botsort: 40)")
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack"],
+    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack", "botsort"],
                     help="ocsort = the headline workload (BASELINE configs[1]); bytetrack = the same "
-                         "synthetic streams through the ByteTrack engine (the tracker of configs[0])")
+                         "synthetic streams through the ByteTrack engine (the tracker of configs[0]); "
+                         "botsort = BASELINE configs[2] (200 dets/frame, 512-d embeddings)")
+    ap.add_argument("--emb-dim", type=int, default=512, help="botsort only")
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
-    ap.add_argument("--objects", type=int, default=100)
-    ap.add_argument("--det-cap", type=int, default=128)
-    ap.add_argument("--track-cap", type=int, default=256)
+    ap.add_argument("--objects", type=int, default=None, help="default 100 (botsort: 200)")
+    ap.add_argument("--det-cap", type=int, default=None, help="default 128 (botsort: 256)")
+    ap.add_argument("--track-cap", type=int, default=None, help="default 256 (botsort: 512)")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between steps")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-streams", type=int, default=4, help="cpu_baseline sample size")
     ap.add_argument("--ref-streams-per-core", type=int, default=1)
-    return ap.parse_args()
+    a = ap.parse_args()
+    bot = a.tracker == "botsort"
+    for name, dflt, dbot in (("steps", 290, 40), ("objects", 100, 200), ("det_cap", 128, 256), ("track_cap", 256, 512)):
+        if getattr(a, name) is None:
+            setattr(a, name, dbot if bot else dflt)
+    if not bot:
+        a.emb_dim = 0
+    return a
 
 
 # --------------------------------------------------------------------------- inputs
+_SHARED_EMBS = None      # [F, S, dcap, E] float32 in an anonymous shared mapping (fork workers fill it)
+
+
 def _gen_one(a):
     from boxmot_b200.synth import make_stream
-    sid, k, f, dcap = a
-    fr = make_stream(sid, k, f)
+    sid, k, f, dcap = a[:4]
+    if len(a) > 4 and a[4]:
+        fr, em = make_stream(sid, k, f, emb_dim=a[4])
+        for i, e in enumerate(em):
+            _SHARED_EMBS[i, a[5], : len(e)] = e
+    else:
+        fr = make_stream(sid, k, f)
     d = np.zeros((f, dcap, 6), np.float32)
     n = np.zeros((f,), np.int32)
     for i, x in enumerate(fr):
@@ -81,12 +101,19 @@ def _gen_one(a):
     return d, n
 
 
-def gen_inputs(first_stream, n_streams, k, n_frames, dcap, workers):
-    """dets [F,S,dcap,6] float32, ndets [F,S] int32; generated before CUDA is touched."""
+def gen_inputs(first_stream, n_streams, k, n_frames, dcap, workers, emb_dim=0):
+    """dets [F,S,dcap,6] float32, ndets [F,S] int32 (+ embs [F,S,dcap,E] float32 when emb_dim);
+    generated before CUDA is touched."""
+    import mmap
     import multiprocessing as mp
+    global _SHARED_EMBS
     dets = np.zeros((n_frames, n_streams, dcap, 6), np.float32)
     nd = np.zeros((n_frames, n_streams), np.int32)
-    jobs = [(first_stream + s, k, n_frames, dcap) for s in range(n_streams)]
+    if emb_dim:
+        shape = (n_frames, n_streams, dcap, emb_dim)
+        buf = mmap.mmap(-1, int(np.prod(shape)) * 4)
+        _SHARED_EMBS = np.frombuffer(buf, dtype=np.float32).reshape(shape)
+    jobs = [(first_stream + s, k, n_frames, dcap, emb_dim, s) for s in range(n_streams)]
     if workers > 1:
         with mp.get_context("fork").Pool(workers) as pool:
             for s, (d, n) in enumerate(pool.imap(_gen_one, jobs, chunksize=8)):
@@ -94,6 +121,8 @@ def gen_inputs(first_stream, n_streams, k, n_frames, dcap, workers):
     else:
         for s, j in enumerate(jobs):
             dets[:, s], nd[:, s] = _gen_one(j)
+    if emb_dim:
+        return dets, nd, _SHARED_EMBS
     return dets, nd
 
 
@@ -102,8 +131,12 @@ def _cpu_worker(a):
     """Runs whole streams through the oracle port; returns (timed seconds, timed updates)."""
     os.environ["OMP_NUM_THREADS"] = "1"
     from boxmot_b200.synth import make_stream
-    sids, k, warm, steps, tracker = a
-    if tracker == "bytetrack":
+    sids, k, warm, steps, tracker = a[:5]
+    emb_dim = a[5] if len(a) > 5 else 0
+    if tracker == "botsort":
+        from oracle.botsort import BotSortOracle
+        make = lambda: BotSortOracle(**BOTSORT_YAML)
+    elif tracker == "bytetrack":
         from oracle.bytetrack import ByteTrackOracle
         make = lambda: ByteTrackOracle(**BYTETRACK_YAML)
     else:
@@ -111,21 +144,26 @@ def _cpu_worker(a):
         make = lambda: OcSortOracle(**OCSORT_YAML)
     tot_t, tot_u = 0.0, 0
     for sid in sids:
-        fr = make_stream(sid, k, warm + steps)
+        if emb_dim:
+            fr, em = make_stream(sid, k, warm + steps, emb_dim=emb_dim)
+            step = lambda f: o.update(fr[f], em[f])
+        else:
+            fr = make_stream(sid, k, warm + steps)
+            step = lambda f: o.update(fr[f])
         o = make()
         for f in range(warm):
-            o.update(fr[f])
+            step(f)
         u0 = o.n_updates
         t0 = time.perf_counter()
         for f in range(warm, warm + steps):
-            o.update(fr[f])
+            step(f)
         tot_t += time.perf_counter() - t0
         tot_u += o.n_updates - u0
     return tot_t, tot_u
 
 
-def cpu_single_core(k, warm, steps, n_streams, tracker):
-    t, u = _cpu_worker((list(range(n_streams)), k, warm, steps, tracker))
+def cpu_single_core(k, warm, steps, n_streams, tracker, emb_dim=0):
+    t, u = _cpu_worker((list(range(n_streams)), k, warm, steps, tracker, emb_dim))
     return u / t, "%d streams x %d frames (after %d warm-up), K=%d, 1 core" % (n_streams, steps, warm, k)
 
 
@@ -143,7 +181,7 @@ def run_reference_arm(args):
     workers = max(1, cores - 1) if cores > 2 else cores
     per = max(1, args.ref_streams_per_core)
     steps = min(args.steps, 300)
-    jobs = [([w * per + i for i in range(per)], args.objects, args.warmup, steps, args.tracker)
+    jobs = [([w * per + i for i in range(per)], args.objects, args.warmup, steps, args.tracker, args.emb_dim)
             for w in range(workers)]
     t0 = time.perf_counter()
     with mp.get_context("fork").Pool(workers) as pool:
@@ -227,7 +265,8 @@ class ClockSampler(threading.Thread):
 #   profiles/r1_launches_lane_scan_traffic.csv   predict 55.2 + assoc 19.3 + update 72.0 + finalize 39.7 MB
 #   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
 NCU_TRAFFIC = {"ocsort": 186.1e6, "bytetrack": 41.1e6}
-TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)"}
+TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)",
+                 "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)"}
 
 
 def alg_bytes(track_updates, matches, births, dets_in, rows_out):
@@ -266,22 +305,33 @@ def run_gpu_arm(args):
     F = W + K
     cores = os.cpu_count() or 1
     t0 = time.perf_counter()
-    dets, nd = gen_inputs(rank * S, S, args.objects, F, args.det_cap, max(1, min(32, cores // world)))
+    gi = gen_inputs(rank * S, S, args.objects, F, args.det_cap, max(1, min(32, cores // world)), args.emb_dim)
+    dets, nd = gi[0], gi[1]
+    embs = gi[2] if args.emb_dim else None
     gen_s = time.perf_counter() - t0
 
     import torch
     import torch.distributed as dist
-    from boxmot_b200.engine import ByteTrackEngine, OcSortEngine
+    from boxmot_b200.engine import BotSortEngine, ByteTrackEngine, OcSortEngine
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    byte = args.tracker == "bytetrack"
-    if byte:
+    byte = args.tracker in ("bytetrack", "botsort")      # BYTE-family engines: no per-kernel timing API
+    bot = args.tracker == "botsort"
+    if bot:
+        eng = BotSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, emb_dim=args.emb_dim,
+                            **BOTSORT_YAML)
+    elif byte:
         eng = ByteTrackEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **BYTETRACK_YAML)
     else:
         eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
-    n_kernels = 1 if byte else 4
+    n_kernels = 3 if bot else 1 if byte else 4
+    d_embs = None
+    if bot:                              # device-resident embeddings, uploaded frame by frame (tens of GB)
+        d_embs = torch.empty(embs.shape, dtype=torch.float32, device=dev)
+        for f in range(F):
+            d_embs[f].copy_(torch.from_numpy(embs[f]))
     h_dets = torch.from_numpy(dets).pin_memory()
     h_nd = torch.from_numpy(nd).pin_memory()
     d_dets = h_dets.to(dev, non_blocking=True)
@@ -323,7 +373,10 @@ def run_gpu_arm(args):
 
     # (1) inputs resident in HBM
     def step_dev(f):
-        eng.step(d_dets[f], d_nd[f])
+        if bot:
+            eng.step(d_dets[f], d_nd[f], d_embs[f])
+        else:
+            eng.step(d_dets[f], d_nd[f])
 
     ms_dev, wall_dev, cnt, clocks = timed(step_dev)
 
@@ -356,7 +409,44 @@ def run_gpu_arm(args):
     # host memory every step.
     e2e = None
     pipe = None
-    if not args.no_e2e:
+    if bot and not args.no_e2e:
+        # host buffers -> engine -> host rows, every step: detections + embeddings up (pinned staging
+        # buffers), rows down; not overlapped (the embedding upload alone is S*det_cap*E*4 bytes)
+        eng.reset()
+        p_e = torch.empty(embs.shape[1:], dtype=torch.float32).pin_memory()
+        g_e = torch.empty(embs.shape[1:], dtype=torch.float32, device=dev)
+        g_d = torch.empty(d_dets.shape[1:], dtype=torch.float32, device=dev)
+        g_n = torch.empty(d_nd.shape[1:], dtype=torch.int32, device=dev)
+        h_out = torch.empty(eng.out.shape, dtype=torch.float64).pin_memory()
+        h_no = torch.empty(eng.nout.shape, dtype=torch.int32).pin_memory()
+
+        def step_e2e(f):
+            p_e.copy_(torch.from_numpy(embs[f]))
+            g_e.copy_(p_e, non_blocking=True)
+            g_d.copy_(h_dets[f], non_blocking=True)
+            g_n.copy_(h_nd[f], non_blocking=True)
+            o, n = eng.step(g_d, g_n, g_e)
+            h_out.copy_(o, non_blocking=True)
+            h_no.copy_(n, non_blocking=True)
+            torch.cuda.current_stream(dev).synchronize()
+            return int(h_no.numpy().sum())
+
+        for f in range(W):
+            step_e2e(f)
+        c0 = eng.counters()
+        barrier()
+        t0 = time.perf_counter()
+        rows_seen = sum(step_e2e(W + i) for i in range(K))
+        barrier()
+        ms_e2e = (time.perf_counter() - t0) * 1e3
+        c1 = eng.counters()
+        e2e = (ms_e2e, c1["track_updates"] - c0["track_updates"])
+
+        class _P:
+            h2d_bytes = p_e.numel() * 4 + g_d.numel() * 4 + g_n.numel() * 4
+            d2h_bytes = h_out.numel() * 8 + h_no.numel() * 4
+        pipe = _P
+    elif not args.no_e2e:
         from boxmot_b200.engine import HostPipeline
         eng.reset()
         pipe = HostPipeline(eng)
@@ -397,7 +487,8 @@ def run_gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import lap as olap
         olap.build()
-        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), args.cpu_streams, args.tracker)
+        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), 1 if bot else args.cpu_streams,
+                                    args.tracker, args.emb_dim)
         cpu = {"value": v, "unit": "track-updates/s", "cores": 1, "kind": "port", "sample": sample}
     if rank == 0:
         peaks = {}
@@ -408,13 +499,23 @@ def run_gpu_arm(args):
         dets_in = int(nd[W:W + K].sum())
         # output rows <= matched tracks (rows are emitted only for tracks updated this frame)
         nbytes = alg_bytes(cnt["track_updates"], cnt["matches"], cnt["births"], dets_in, cnt["matches"])
+        if bot:
+            # + embeddings: detection features in (4E per detection), smooth features read by the
+            # contraction (4E per live track ~ track-updates), EMA read+write (2*4E per match),
+            # distance matrix out and in again (2 * 4 bytes per track x detection pair)
+            E = args.emb_dim
+            nbytes += 4 * E * dets_in + 4 * E * cnt["track_updates"] + 8 * E * cnt["matches"] \
+                + 8 * cnt["track_updates"] * (dets_in // max(1, K * S))
         achieved = nbytes / (ms_dev * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": upd_all / (ms_all * 1e-3), "unit": "track-updates/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_all / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": ("ByteTrack (bytetrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+            "config": {"workload": ("BoT-SORT (botsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                    "512-d re-ID embeddings: cosine-distance contraction + IoU fusion + Kalman XYWH "
+                                    "(BASELINE configs[2])" if bot else
+                                    "ByteTrack (bytetrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
                                     "IoU + fuse_score cost, three thresholded lapjv-exact assignments per frame "
                                     "(tracker of BASELINE configs[0] on the configs[1] streams)" if byte else
                                     "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
@@ -426,11 +527,12 @@ def run_gpu_arm(args):
             "stream_frames_per_s": world * S * K / (ms_all * 1e-3),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC[args.tracker] if (S, args.objects, args.det_cap, args.track_cap) ==
+                         "traffic": NCU_TRAFFIC.get(args.tracker) if (S, args.objects, args.det_cap, args.track_cap) ==
                          (1024, 100, 128, 256) else None,
                          "traffic_source": "ncu dram__bytes_read+write per frame step, cold caches (profiles/r1_launches_*_traffic.csv)",
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "byte_step_kernel" if byte else
+                         "kernel": "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
+                                   "byte_step_kernel" if byte else
                                    "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize",
                          "alg_bytes_per_launch": nbytes / K, "avg_launch_ms": ms_dev / K},
             "gpu_launches": n_kernels * K * (2 if not args.no_e2e else 1),
