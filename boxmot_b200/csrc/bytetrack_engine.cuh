@@ -12,7 +12,8 @@ enum { BI_ID = 0, BI_STATE, BI_ACTIVATED, BI_FRAME, BI_START, BI_DETIND, BI_INRE
 // TrackState (bytetrack/basetrack.py:8-12)
 enum { BT_NEW = 0, BT_TRACKED = 1, BT_LOST = 2, BT_REMOVED = 3 };
 // per-stream header
-enum { BH_NACT = 0, BH_NLOST, BH_NEXT_ID, BH_FRAME, BH_ERR, BH_LAPS, BH_MATCH, BH_BIRTHS, BH_NFUPD, BH_COUNT = 12 };
+enum { BH_NACT = 0, BH_NLOST, BH_NEXT_ID, BH_FRAME, BH_ERR, BH_LAPS, BH_MATCH, BH_BIRTHS, BH_NFUPD, BH_NLIVE, BH_NH,
+       BH_COUNT = 12 };
 constexpr int BOT_HIST = 4;          // distinct classes remembered per track (botsort_track.py:51-64)
 constexpr int BM_ERR_CLS_HIST = 16;  // a track saw more than BOT_HIST distinct classes
 constexpr int BM_ERR_WARP = 32;      // camera-motion warp with rotation / shear (needs a dense covariance)
@@ -42,6 +43,11 @@ struct ByteState {
     float* embd;       // [S][Tcap][Dcap] max(0, cosine distance) of (slot, high-score detection position)
     double* chist;     // [S][2*BOT_HIST][Tcap] class votes: class ids, then accumulated confidences
     int* fupd;         // [S][2][Dcap] (slot, detection row | birth flag << 30) feature updates of the frame
+    int* elive;        // [S][Tcap] live slots (active then lost list) = rows of the embedding contraction
+    int* ehind;        // [S][Dcap] rows of the high-score detections = its columns
+    float* etn;        // [S][Tcap] |smooth_feat| by row position
+    float* edn;        // [S][Dcap] |detection feature| by column position
+    int tensor_cores;  // 1: tcgen05 contraction (csrc/cosine_tc.cuh), 0: fp32 FFMA tiles in bot_embed_kernel
 };
 
 size_t bytetrack_step_smem(const ByteState& st);

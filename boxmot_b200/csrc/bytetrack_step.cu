@@ -11,7 +11,9 @@
 // matching itself is observable).  Kalman filter: csrc/kf_xyah.cuh.
 #include "bytetrack_engine.cuh"
 #include "lap_rect.cuh"
+#include "cosine_tc.cuh"
 #include <cstdio>
+#include <cstdlib>
 
 namespace bm {
 
@@ -525,6 +527,11 @@ bot_embed_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
     for (int i = tid; i < nLive; i += BE_NT) rows[i] = i < nA ? v.act[i] : v.lost[i - nA];
     __syncthreads();
     const int nH = s_nh;
+    int* g_live = st.elive + (size_t)s * Tcap;
+    int* g_hind = st.ehind + (size_t)s * Dcap;
+    for (int i = tid; i < nLive; i += BE_NT) g_live[i] = rows[i];
+    for (int i = tid; i < nH; i += BE_NT) g_hind[i] = hind[i];
+    if (tid == 0) { v.hdr[BH_NLIVE] = nLive; v.hdr[BH_NH] = nH; }
     const float* esrc = embs + (size_t)s * Dcap * E;
     float* dfeat = st.dfeat + (size_t)s * Dcap * E;
     const float* feat = st.feat + (size_t)s * Tcap * E;
@@ -540,15 +547,16 @@ bot_embed_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         ss = 0.f;
         for (int e = lane; e < E; e += 32) { const float x = (src[e] / n1) / n2; dst[e] = x; ss += x * x; }
         ss = warp_sum_f(ss);
-        if (lane == 0) dn[d] = sqrtf(ss);
+        if (lane == 0) { dn[d] = sqrtf(ss); st.edn[(size_t)s * Dcap + d] = dn[d]; }
     }
     for (int i = wid; i < nLive; i += BE_NT / 32) {
         const float* src = feat + (size_t)rows[i] * E;
         float ss = 0.f;
         for (int e = lane; e < E; e += 32) { const float x = src[e]; ss += x * x; }
         ss = warp_sum_f(ss);
-        if (lane == 0) tn[i] = sqrtf(ss);
+        if (lane == 0) { tn[i] = sqrtf(ss); st.etn[(size_t)s * Tcap + i] = tn[i]; }
     }
+    if (st.tensor_cores) return;          // the contraction runs on the tensor cores (cosine_tc_kernel)
     __syncthreads();
     float* embd = st.embd + (size_t)s * Tcap * Dcap;
     const int ty = tid / 16, tx = tid % 16;
@@ -619,6 +627,23 @@ bot_ema_kernel(ByteState st, ByteParams pr) {
     for (int e = lane; e < E; e += 32) dst[e] = (0.9f * dst[e] + 0.1f * (src[e] / n1)) / n2;
 }
 
+// One contraction per stream for cosine_tc_kernel
+struct BotCosine {
+    ByteState st;
+    int E;
+    __device__ CosineProblem operator()(int s) const {
+        const int* hdr = st.hdr + (size_t)s * BH_COUNT;
+        CosineProblem p;
+        p.A = st.feat + (size_t)s * st.Tcap * E; p.ra = st.elive + (size_t)s * st.Tcap;
+        p.na = st.etn + (size_t)s * st.Tcap; p.nA = hdr[BH_NLIVE];
+        p.B = st.dfeat + (size_t)s * st.Dcap * E; p.rb = st.ehind + (size_t)s * st.Dcap;
+        p.nb = st.edn + (size_t)s * st.Dcap; p.nB = hdr[BH_NH];
+        p.E = E;
+        p.out = st.embd + (size_t)s * st.Tcap * st.Dcap; p.out_ld = st.Dcap;
+        return p;
+    }
+};
+
 size_t bytetrack_step_smem(const ByteState& st) { return byte_smem_bytes(st.Tcap, st.Dcap); }
 
 cudaError_t bytetrack_step_configure(size_t smem) {
@@ -644,6 +669,17 @@ cudaError_t botsort_step_launch(const ByteState& st, const ByteParams& pr, const
             once = true;
         }
         bot_embed_kernel<<<st.S, BE_NT, sm, stream>>>(st, pr, dets, ndets, embs);
+        if (st.tensor_cores) {
+            static bool once_tc = false;
+            if (!once_tc) {
+                cudaError_t e = cudaFuncSetAttribute(cosine_tc_kernel<BotCosine>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     (int)cosine_tc_smem_bytes());
+                if (e != cudaSuccess) return e;
+                once_tc = true;
+            }
+            cosine_tc_kernel<BotCosine><<<dim3((st.Tcap + TC_M - 1) / TC_M, st.S), TC_NT, cosine_tc_smem_bytes(), stream>>>(
+                BotCosine{st, pr.emb_dim});
+        }
     }
     byte_step_kernel<MODE_BOT><<<st.S, BT_NT, bytetrack_step_smem(st), stream>>>(st, pr, dets, ndets, warps, out, nout);
     if (pr.with_reid) bot_ema_kernel<<<dim3(st.S, (st.Dcap + 7) / 8), 256, 0, stream>>>(st, pr);

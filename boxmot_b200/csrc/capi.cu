@@ -3,6 +3,7 @@
 #include "ocsort_engine.cuh"
 #include "bytetrack_engine.cuh"
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <new>
@@ -263,6 +264,11 @@ static int byte_family_create(ByteEngine* e, int n_streams, int track_cap, int d
     bm::ByteState& st = e->st;
     st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap;
     st.feat = st.dfeat = st.embd = nullptr; st.chist = nullptr; st.fupd = nullptr;
+    st.elive = st.ehind = nullptr; st.etn = st.edn = nullptr;
+    {   // BM_COSINE=ffma selects the fp32 FFMA contraction (debug / comparison); default: tensor cores
+        const char* v = getenv("BM_COSINE");
+        st.tensor_cores = (v && v[0] == 'f') ? 0 : 1;
+    }
     const size_t S = n_streams, T = track_cap, E = e->pr.emb_dim;
     cudaError_t r = cudaSuccess;
     if (e->bot) {
@@ -272,6 +278,10 @@ static int byte_family_create(ByteEngine* e, int n_streams, int track_cap, int d
             if (r == cudaSuccess) r = dev_alloc(e, &st.feat, S * T * E);
             if (r == cudaSuccess) r = dev_alloc(e, &st.dfeat, S * (size_t)det_cap * E);
             if (r == cudaSuccess) r = dev_alloc(e, &st.embd, S * T * (size_t)det_cap);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.elive, S * T);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.ehind, S * (size_t)det_cap);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.etn, S * T);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.edn, S * (size_t)det_cap);
             if (r == cudaSuccess) r = cudaMemset(st.feat, 0, S * T * E * sizeof(float));
         }
     }

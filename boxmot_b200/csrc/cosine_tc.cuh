@@ -1,0 +1,201 @@
+// Cosine-distance contraction on the 5th-generation tensor cores (sm_100a tcgen05 + TMEM).
+//
+//   out[ra[i]][j] = max(0, 1 - <A[ra[i]], B[rb[j]]> / (na[i] * nb[j]))      i < nA, j < nB
+//
+// -- embedding_distance of the reference (boxmot/utils/matching.py:230-321: cdist cosine of
+// the track features against the detection features, clipped at 0) for one problem per
+// blockIdx.y.  A and B rows are gathered through index lists (track slots / detection rows),
+// fp32, K-major (a feature vector is contiguous).
+//
+// Precision: the operands are split x = hi + lo with hi = tf32(x) (rounded to nearest, low 13
+// mantissa bits zero) and lo = tf32(x - hi); three kind::tf32 MMAs (hi.hi + hi.lo + lo.hi) accumulate in fp32 in
+// TMEM, which reproduces the fp32 product to ~2^-20 relative ("3xTF32").  A single-pass tf32
+// contraction (error ~1e-4 on the cosine) was not used: the distances feed an exact
+// assignment whose result must equal the reference's.
+//
+// Structure per CTA (128 threads, one 128-row tile of A against up to 256 rows of B):
+//   for each 32-element chunk of E:   all threads gather + split the chunk of the A and B
+//     tiles into shared memory in the canonical K-major SWIZZLE_128B layout (8-row x 128-byte
+//     atoms, 16-byte chunk index XOR row%8), fence.proxy.async, barrier; one thread issues the
+//     4 x 3 tcgen05.mma (M=128, N=nB rounded up to 16, K=8) and commits to an mbarrier; all
+//     threads wait on it before the buffers are overwritten.
+//   epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns at a time) -> cosine -> global.
+// The operands are staged by ordinary loads instead of TMA because both tiles are GATHERED
+// (rows are track slots / selected detections) and need the hi/lo split on the way in; at the
+// tracker's shapes (A = hundreds of 2 KB rows per stream, read once) the kernel is bound by
+// reading A from HBM, not by the tensor pipe.
+#pragma once
+#include "common.cuh"
+
+namespace bm {
+
+constexpr int TC_M = 128, TC_KC = 32, TC_NMAX = 256, TC_NT = 128;
+constexpr uint32_t TC_TMEM_COLS = 256;
+
+__host__ __device__ inline size_t cosine_tc_smem_bytes() {
+    return 1024 /*alignment slack*/ + 2 * TC_M * 128 + 2 * TC_NMAX * 128 + 64;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// start address >> 4 in [0,14), leading byte offset >> 4 in [16,30) (unused for this layout),
+// stride byte offset >> 4 in [32,46) = 1024 B between 8-row groups, version 1 in [46,48),
+// layout type 2 (SWIZZLE_128B) in [61,64).
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32
+// (2 << 7, 2 << 10), both K-major, N >> 3 in [17,23), M >> 4 in [24,29).
+__device__ __forceinline__ uint32_t tc_idesc(int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+}
+
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+        :: "r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+
+__device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}\n" :: "r"(bar), "r"(parity) : "memory");
+}
+
+// Gather one 32-float chunk of `rows` tile rows into the hi / lo swizzled buffers.
+__device__ __forceinline__ void tc_stage(const float* __restrict__ base, const int* __restrict__ idx, int first, int count,
+                                         int tile_rows, int ld, int k0, int kmax, unsigned char* hi, unsigned char* lo) {
+    for (int q = threadIdx.x; q < tile_rows * 8; q += TC_NT) {
+        const int r = q >> 3, c = q & 7;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < count) {
+            const float* src = base + (size_t)idx[first + r] * ld + k0 + c * 4;
+            if (k0 + c * 4 + 3 < kmax && (ld & 3) == 0) v = *reinterpret_cast<const float4*>(src);
+            else {
+                float t[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int e = 0; e < 4; e++) if (k0 + c * 4 + e < kmax) t[e] = src[e];
+                v = make_float4(t[0], t[1], t[2], t[3]);
+            }
+        }
+        const float x[4] = {v.x, v.y, v.z, v.w};
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            // round to nearest tf32 (add half an ulp of the 10-bit mantissa, clear the rest): the
+            // split errors are then zero-mean instead of a systematic under-estimate
+            h[e] = (__float_as_uint(x[e]) + 0x1000u) & 0xFFFFE000u;
+            l[e] = (__float_as_uint(x[e] - __uint_as_float(h[e])) + 0x1000u) & 0xFFFFE000u;
+        }
+        const int off = r * 128 + ((c ^ (r & 7)) << 4);
+        *reinterpret_cast<uint4*>(hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+struct CosineProblem {
+    const float* A; const int* ra; const float* na; int nA;    // rows ra[0..nA) of A, norms by position
+    const float* B; const int* rb; const float* nb; int nB;
+    int E;
+    float* out; int out_ld;                                     // out[ra[i] * out_ld + j]
+};
+
+// grid = (row tiles of 128, problems); the caller provides problem(blockIdx.y).
+template <typename ProblemFn>
+__global__ void __launch_bounds__(TC_NT)
+cosine_tc_kernel(ProblemFn problem) {
+    extern __shared__ unsigned char tc_smem_raw[];
+    const CosineProblem pb = problem((int)blockIdx.y);
+    const int r0 = blockIdx.x * TC_M;
+    if (r0 >= pb.nA || pb.nB <= 0) return;                      // uniform over the CTA
+    const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    unsigned char* sm = reinterpret_cast<unsigned char*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char* a_hi = sm;
+    unsigned char* a_lo = a_hi + TC_M * 128;
+    unsigned char* b_hi = a_lo + TC_M * 128;
+    unsigned char* b_lo = b_hi + TC_NMAX * 128;
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(b_lo + TC_NMAX * 128);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+    const uint32_t bar = smem_u32(mbar);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (wid == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(tmem_slot)), "r"(TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmem_slot;
+    const int rows = min(TC_M, pb.nA - r0);
+    uint32_t phase = 0;
+    for (int c0 = 0; c0 < pb.nB; c0 += TC_NMAX) {
+        const int cols = min(TC_NMAX, pb.nB - c0);
+        const int npad = max(16, (cols + 15) & ~15);
+        const uint32_t idesc = tc_idesc(npad);
+        for (int k0 = 0; k0 < pb.E; k0 += TC_KC) {
+            tc_stage(pb.A, pb.ra, r0, rows, TC_M, pb.E, k0, pb.E, a_hi, a_lo);
+            tc_stage(pb.B, pb.rb, c0, cols, npad, pb.E, k0, pb.E, b_hi, b_lo);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t dah = tc_smem_desc(smem_u32(a_hi)), dal = tc_smem_desc(smem_u32(a_lo));
+                const uint64_t dbh = tc_smem_desc(smem_u32(b_hi)), dbl = tc_smem_desc(smem_u32(b_lo));
+#pragma unroll
+                for (int kk = 0; kk < TC_KC / 8; kk++) {          // K = 8 tf32 = 32 bytes per instruction
+                    const uint64_t adv = (uint64_t)((kk * 32) >> 4);
+                    tc_mma_tf32(tmem, dah + adv, dbh + adv, idesc, (k0 > 0 || kk > 0) ? 1u : 0u);
+                    tc_mma_tf32(tmem, dah + adv, dbl + adv, idesc, 1u);
+                    tc_mma_tf32(tmem, dal + adv, dbh + adv, idesc, 1u);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                             :: "r"(bar) : "memory");
+            }
+            tc_mbar_wait(bar, phase);
+            phase ^= 1;
+        }
+        // ---- epilogue: warp w owns TMEM lanes 32w .. 32w+31 = tile rows
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int r = wid * 32 + lane;
+        const bool rin = r < rows;
+        const float na = rin ? pb.na[r0 + r] : 1.f;
+        float* orow = rin ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
+        for (int cb = 0; cb < npad; cb += 16) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem + ((uint32_t)(wid * 32) << 16) + (uint32_t)cb;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (rin) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const int c = cb + j;
+                    if (c < cols) {
+                        const double cs = (double)__uint_as_float(v[j]) / ((double)na * (double)pb.nb[c0 + c]);
+                        orow[c] = (float)fmax(0.0, 1.0 - cs);
+                    }
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();       // every warp has drained its accumulator rows before the next column tile
+    }
+    if (wid == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(TC_TMEM_COLS) : "memory");
+    }
+}
+
+}  // namespace bm

@@ -4,6 +4,7 @@
 #include "iou.cuh"
 #include "kf_xysr.cuh"
 #include "kf_xyah.cuh"
+#include "cosine_tc.cuh"
 #include "lapjv.cuh"
 #include "lap_rect.cuh"
 #include <cstdio>
@@ -157,6 +158,36 @@ __global__ void cv8_gating_kernel(const double* mean, const double* cov, int nt,
     out[e] = cv8_gating<KIND>(x, P, zs, only_position != 0, gaussian != 0);
 }
 
+
+// ---- embedding distance (matching.py:230-321) as a stand-alone batched contraction
+__global__ void cosine_prep_kernel(const float* a, int na, const float* b, int nb, int E, int* idx, float* norms) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= na + nb) return;
+    const float* src = w < na ? a + (size_t)w * E : b + (size_t)(w - na) * E;
+    float ss = 0.f;
+    for (int e = lane; e < E; e += 32) ss += src[e] * src[e];
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(BM_FULL, ss, o);
+    if (lane == 0) { norms[w] = sqrtf(ss); idx[w] = w < na ? w : w - na; }
+}
+
+struct UnitCosine {
+    CosineProblem p;
+    __device__ CosineProblem operator()(int) const { return p; }
+};
+
+// reference form: one thread per output, fp32 FFMA dot product
+__global__ void cosine_ffma_kernel(CosineProblem p) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.nA * p.nB) return;
+    const int i = e / p.nB, j = e % p.nB;
+    const float* x = p.A + (size_t)p.ra[i] * p.E;
+    const float* y = p.B + (size_t)p.rb[j] * p.E;
+    float acc = 0.f;
+    for (int k = 0; k < p.E; k++) acc = fmaf(x[k], y[k], acc);
+    const double cs = (double)acc / ((double)p.na[i] * (double)p.nb[j]);
+    p.out[(size_t)p.ra[i] * p.out_ld + j] = (float)fmax(0.0, 1.0 - cs);
+}
+
 }  // namespace bm
 
 static int unit_fail(const char* what, cudaError_t e) {
@@ -260,6 +291,31 @@ int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_
                                                                             only_position, gaussian, d_out);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("cv8_gating_kernel", e);
+}
+
+int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out, void* d_work,
+                       int mode, void* stream) {
+    if (na <= 0 || nb <= 0) return 0;
+    if (!d_a || !d_b || !d_out || !d_work || emb_dim <= 0 || (mode != 0 && mode != 1)) return -1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int* idx = static_cast<int*>(d_work);
+    float* norms = reinterpret_cast<float*>(idx + na + nb);
+    bm::cosine_prep_kernel<<<(na + nb + 3) / 4, 128, 0, st>>>(d_a, na, d_b, nb, emb_dim, idx, norms);
+    bm::CosineProblem p;
+    p.A = d_a; p.ra = idx; p.na = norms; p.nA = na;
+    p.B = d_b; p.rb = idx + na; p.nb = norms + na; p.nB = nb;
+    p.E = emb_dim; p.out = d_out; p.out_ld = nb;
+    if (mode == 1) {
+        bm::cosine_ffma_kernel<<<(na * nb + 127) / 128, 128, 0, st>>>(p);
+    } else {
+        cudaError_t e = cudaFuncSetAttribute(bm::cosine_tc_kernel<bm::UnitCosine>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm::cosine_tc_smem_bytes());
+        if (e != cudaSuccess) return unit_fail("cosine_tc_kernel attribute", e);
+        bm::cosine_tc_kernel<bm::UnitCosine><<<dim3((na + bm::TC_M - 1) / bm::TC_M, 1), bm::TC_NT,
+                                               bm::cosine_tc_smem_bytes(), st>>>(bm::UnitCosine{p});
+    }
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("cosine kernel", e);
 }
 
 }  // extern "C"

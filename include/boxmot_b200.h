@@ -177,6 +177,13 @@ int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z
 int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_tracks, const double* d_meas,
                      int n_meas, int only_position, int gaussian, double* d_out, void* stream);
 
+/* embedding_distance (boxmot/utils/matching.py:230-321 with its defaults): d_out [na][nb] =
+ * max(0, 1 - <a_i, b_j> / (|a_i| |b_j|)) for float32 feature rows d_a [na][emb_dim],
+ * d_b [nb][emb_dim].  mode 0 = tcgen05 tensor-core contraction (3xTF32, fp32 accumulation in
+ * TMEM), 1 = fp32 FFMA.  d_work: caller-owned scratch of at least 8 * (na + nb) bytes. */
+int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out,
+                       void* d_work, int mode, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -271,3 +271,30 @@ def test_cv8_kalman_kernels_match_reference_vectors(kind):
                        "gating")
             torch.cuda.synchronize()
             np.testing.assert_allclose(out.cpu().numpy(), z["%s_gate_%s_%d" % (kind, metric, op)], rtol=1e-8)
+
+
+@pytest.mark.parametrize("shape", [(5, 3, 32), (128, 16, 64), (200, 77, 512), (300, 260, 96), (37, 130, 100)])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_cosine_distance_matches_scipy(shape, mode):
+    """bm_cosine_distance (row a14: embedding_distance) against scipy's cdist on the same float32
+    features: mode 0 is the tcgen05 / TMEM contraction (3xTF32), mode 1 the fp32 FFMA form.
+    Tolerance 2e-6 absolute on a distance in [0, 2] (fp32 accumulation of unit-norm vectors)."""
+    from scipy.spatial.distance import cdist
+    from boxmot_b200 import _lib
+    na, nb, E = shape
+    rng = np.random.default_rng(na * 1000 + nb)
+    a = rng.normal(0, 1, (na, E)).astype(np.float32)
+    b = rng.normal(0, 1, (nb, E)).astype(np.float32)
+    b[: min(nb, na)] += 3 * a[: min(nb, na)]          # some close pairs
+    a[0] *= 100.0                                      # norms are divided out
+    d_a, d_b = _dev(a), _dev(b)
+    out = torch.full((na, nb), -7.0, dtype=torch.float32, device="cuda")
+    work = torch.zeros((2 * (na + nb),), dtype=torch.int32, device="cuda")
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.lib().bm_cosine_distance(p(d_a), na, p(d_b), nb, E, p(out), p(work), mode, None), "cosine")
+    torch.cuda.synchronize()
+    want = np.maximum(0.0, cdist(a.astype(np.float64), b.astype(np.float64), "cosine"))
+    got = out.cpu().numpy()
+    err = np.abs(got - want).max()
+    print("cosine mode %d shape %s max abs err %.3g" % (mode, shape, err))
+    np.testing.assert_allclose(got, want, rtol=0, atol=2e-6 if mode else 2e-5)
