@@ -119,8 +119,10 @@ static __device__ int rect_solve_warp(const CostFn& cost, int nr, int nc, double
         const int i = base + lane;
         bool fr = false;
         if (i < nr) {
+            // a < 0: the row's cheapest option is the null sink (reduced cost 0 with u = null_cost);
+            // it is assigned there for good -- it owns no column, so no later path runs through it
             const int a = w.x[i];
-            if (a < 0 || w.y[a] != i) { fr = true; w.x[i] = -1; }
+            if (a >= 0 && w.y[a] != i) { fr = true; w.x[i] = -1; }
         }
         const unsigned b = __ballot_sync(BM_FULL, fr);
         if (fr) w.fr[n_free + __popc(b & ((1u << lane) - 1))] = i;
