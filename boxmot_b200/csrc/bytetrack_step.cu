@@ -27,13 +27,14 @@ struct ByteSmem {
     float* hconf;             // [Dcap]
     void* work;               // solver work area
     int *hind, *lind, *dflag, *rest, *rflag, *born;  // [Dcap]
-    int *pool, *unc, *rtr, *xs, *nlost, *refind, *lista, *listb, *tflag, *upd_slot, *upd_det;   // [Tcap]
+    int *pool, *unc, *rtr, *xs, *nlost, *refind, *lista, *listb, *tflag, *upd_slot, *upd_det, *rarg;   // [Tcap]
+    double* rmin;             // [Tcap] row minima of the cost matrix being built
     int* misc;
 };
 
 __host__ __device__ inline size_t byte_smem_bytes(int Tcap, int Dcap) {
     size_t b = 2 * 16 * (size_t)Dcap + (rect_work_bytes(Tcap, Dcap) + 15) / 16 * 16;
-    b += 4 * ((size_t)Dcap + 6 * (size_t)Dcap + 11 * (size_t)Tcap + BM_MISC);
+    b += 8 * (size_t)Tcap + 4 * ((size_t)Dcap + 6 * (size_t)Dcap + 12 * (size_t)Tcap + BM_MISC);
     return (b + 15) / 16 * 16;
 }
 
@@ -42,12 +43,13 @@ __device__ inline ByteSmem byte_carve(unsigned char* base, int Tcap, int Dcap) {
     m.hbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap;
     m.lbox = reinterpret_cast<float4*>(base); base += 16 * (size_t)Dcap;
     m.work = base; base += (rect_work_bytes(Tcap, Dcap) + 15) / 16 * 16;
+    m.rmin = reinterpret_cast<double*>(base); base += 8 * (size_t)Tcap;
     m.hconf = reinterpret_cast<float*>(base); base += 4 * (size_t)Dcap;
     int* q = reinterpret_cast<int*>(base);
     m.hind = q; q += Dcap; m.lind = q; q += Dcap; m.dflag = q; q += Dcap; m.rest = q; q += Dcap; m.rflag = q; q += Dcap; m.born = q; q += Dcap;
     m.pool = q; q += Tcap; m.unc = q; q += Tcap; m.rtr = q; q += Tcap; m.xs = q; q += Tcap; m.nlost = q; q += Tcap;
     m.refind = q; q += Tcap; m.lista = q; q += Tcap; m.listb = q; q += Tcap; m.tflag = q; q += Tcap;
-    m.upd_slot = q; q += Tcap; m.upd_det = q; q += Tcap;
+    m.upd_slot = q; q += Tcap; m.upd_det = q; q += Tcap; m.rarg = q; q += Tcap;
     m.misc = q;
     return m;
 }
@@ -180,6 +182,38 @@ struct ByteView {
     }
 };
 
+// iou_pair with the division skipped when the boxes do not overlap: max(0, w) * max(0, h) is
+// then exactly 0 and 0 / (area_a + area_b) is exactly +0.0 whenever that sum is positive
+// (anything else -- degenerate or non-finite boxes -- takes the full expression).
+__device__ __forceinline__ double iou_sparse(const Box& a, const Box& b) {
+    const double w = fmin(a.x2, b.x2) - fmax(a.x1, b.x1), h = fmin(a.y2, b.y2) - fmax(a.y1, b.y1);
+    if (!(w > 0.0 && h > 0.0) && (a.x2 - a.x1) * (a.y2 - a.y1) + (b.x2 - b.x1) * (b.y2 - b.y1) > 0.0) return 0.0;
+    return iou_pair(a, b);
+}
+
+// Cost matrix [nr][nc] of one association round, built a row per warp: entry (r, c) =
+// f(1 - iou(row box, detection box), detection position); the exact row minimum and its
+// lowest column go to rmin / rarg for the solver's row reduction.  dsel maps the column to the
+// detection position (nullptr = identity).
+template <typename CostOf>
+__device__ __forceinline__ void byte_cost_rows(const ByteView& v, const int* rowslot, int nr, const float4* dbox,
+                                               const int* dsel, int nc, double* cost, double* rmin, int* rarg, CostOf f) {
+    const int lane = lane_id();
+    for (int r = warp_id(); r < nr; r += BT_NT / 32) {
+        const Box a = v.box(rowslot[r]);
+        double m = CUDART_INF;
+        int arg = 0x7fffffff;
+        for (int c = lane; c < nc; c += 32) {
+            const int d = dsel ? dsel[c] : c;
+            const double cc = f(1.0 - iou_sparse(a, det_xyxy(dbox[d])), d);
+            cost[(size_t)r * nc + c] = cc;
+            if (cc < m) { m = cc; arg = c; }
+        }
+        warp_argmin(m, arg);
+        if (lane == 0) { rmin[r] = m; rarg[r] = arg; }
+    }
+}
+
 // One thresholded assignment (enhanced_linear_assignment, matching.py:30-108) by warp 0 on the
 // cost matrix in `cost` [nr][nc]: xs[r] = column or -1 (row unmatched, x < 0) or -2 (assigned
 // above the threshold: in neither list, as in the reference); colflag[c] |= 1 when y[c] >= 0.
@@ -192,7 +226,7 @@ __device__ inline void byte_assign(const double* cost, int nr, int nc, double th
         return;
     }
     RectWork w = rect_carve(sm.work, nr, nc);
-    const int bad = rect_solve_warp(DenseCost{cost, nc}, nr, nc, thresh, w, nullptr, nullptr);
+    const int bad = rect_solve_warp(DenseCost{cost, nc}, nr, nc, thresh, w, sm.rmin, sm.rarg);
     if (bad && lane == 0) sm.misc[BM_BAD] = 1;
     for (int r = lane; r < nr; r += 32) {
         const int c = w.x[r];
@@ -290,11 +324,25 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
 
     // ---- first association: pool x high-score detections, fuse_score, thresh = match_thresh (:199-219)
     const float* embd = MODE == MODE_BOT ? st.embd + (size_t)s * Tcap * Dcap : nullptr;
-    for (int e = tid; e < nP * nH; e += BT_NT) {
-        const int t = e / nH, d = e % nH, slot = sm.pool[t];
-        const double iou_d = 1.0 - iou_pair(v.box(slot), det_xyxy(sm.hbox[d]));
-        if (MODE == MODE_BYTE) cost[e] = fuse_entry(iou_d, (double)sm.hconf[d]);
-        else cost[e] = bot_cost(iou_d, (double)sm.hconf[d], pr.fuse_first != 0, pr, embd, slot * Dcap + d);
+    if (MODE == MODE_BYTE) {
+        byte_cost_rows(v, sm.pool, nP, sm.hbox, nullptr, nH, cost, sm.rmin, sm.rarg,
+                       [&](double iou_d, int d) { return fuse_entry(iou_d, (double)sm.hconf[d]); });
+    } else {
+        // the row's slot is needed for the embedding lookup: one row per warp, so it is warp-uniform
+        for (int r = wid; r < nP; r += BT_NT / 32) {
+            const int slot = sm.pool[r];
+            const Box a = v.box(slot);
+            double m = CUDART_INF;
+            int arg = 0x7fffffff;
+            for (int c = lane; c < nH; c += 32) {
+                const double cc = bot_cost(1.0 - iou_sparse(a, det_xyxy(sm.hbox[c])), (double)sm.hconf[c],
+                                           pr.fuse_first != 0, pr, embd, slot * Dcap + c);
+                cost[(size_t)r * nH + c] = cc;
+                if (cc < m) { m = cc; arg = c; }
+            }
+            warp_argmin(m, arg);
+            if (lane == 0) { sm.rmin[r] = m; sm.rarg[r] = arg; }
+        }
     }
     __syncthreads();
     if (wid == 0) {
@@ -319,10 +367,7 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
 
     // ---- second association: still-tracked leftovers x low-score detections, thresh 0.5 (:221-250)
     const int nR = sm.misc[BM_NR], nRest = sm.misc[BM_NREST];
-    for (int e = tid; e < nR * nLo; e += BT_NT) {
-        const int t = e / nLo, d = e % nLo;
-        cost[e] = 1.0 - iou_pair(v.box(sm.rtr[t]), det_xyxy(sm.lbox[d]));
-    }
+    byte_cost_rows(v, sm.rtr, nR, sm.lbox, nullptr, nLo, cost, sm.rmin, sm.rarg, [&](double iou_d, int) { return iou_d; });
     __syncthreads();
     if (wid == 0) {
         byte_assign(cost, nR, nLo, 0.5, sm, sm.xs, sm.born /*column flags unused*/, v.hdr);
@@ -338,11 +383,25 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
     __syncthreads();
 
     // ---- unconfirmed tracks x remaining high-score detections, fuse_score, thresh 0.7 (:252-264)
-    for (int e = tid; e < nU * nRest; e += BT_NT) {
-        const int t = e / nRest, k = e % nRest, d = sm.rest[k];
-        const double iou_d = 1.0 - iou_pair(v.box(sm.unc[t]), det_xyxy(sm.hbox[d]));
-        if (MODE == MODE_BYTE) cost[e] = fuse_entry(iou_d, (double)sm.hconf[d]);
-        else cost[e] = bot_cost(iou_d, (double)sm.hconf[d], true, pr, embd, sm.unc[t] * Dcap + d);
+    if (MODE == MODE_BYTE) {
+        byte_cost_rows(v, sm.unc, nU, sm.hbox, sm.rest, nRest, cost, sm.rmin, sm.rarg,
+                       [&](double iou_d, int d) { return fuse_entry(iou_d, (double)sm.hconf[d]); });
+    } else {
+        for (int r = wid; r < nU; r += BT_NT / 32) {
+            const int slot = sm.unc[r];
+            const Box a = v.box(slot);
+            double m = CUDART_INF;
+            int arg = 0x7fffffff;
+            for (int c = lane; c < nRest; c += 32) {
+                const int d = sm.rest[c];
+                const double cc = bot_cost(1.0 - iou_sparse(a, det_xyxy(sm.hbox[d])), (double)sm.hconf[d], true, pr, embd,
+                                           slot * Dcap + d);
+                cost[(size_t)r * nRest + c] = cc;
+                if (cc < m) { m = cc; arg = c; }
+            }
+            warp_argmin(m, arg);
+            if (lane == 0) { sm.rmin[r] = m; sm.rarg[r] = arg; }
+        }
     }
     __syncthreads();
     if (wid == 0) {
@@ -447,7 +506,7 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
     const int nA2 = sm.misc[BM_NA2], nL2 = sm.misc[BM_NL2];
     for (int e = tid; e < nA2 * nL2; e += BT_NT) {
         const int a = sm.lista[e / nL2], b = sm.listb[e % nL2];
-        if (1.0 - iou_pair(v.box(a), v.box(b)) < 0.15) {
+        if (1.0 - iou_sparse(v.box(a), v.box(b)) < 0.15) {
             const int tp = v.I(BI_FRAME, a) - v.I(BI_START, a), tq = v.I(BI_FRAME, b) - v.I(BI_START, b);
             atomicOr(&sm.tflag[tp > tq ? b : a], TF_DUP);
         }

@@ -69,22 +69,36 @@ __device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity) {
         "DONE_%=:\n\t}\n" :: "r"(bar), "r"(parity) : "memory");
 }
 
-// Gather one 32-float chunk of `rows` tile rows into the hi / lo swizzled buffers.
-__device__ __forceinline__ void tc_stage(const float* __restrict__ base, const int* __restrict__ idx, int first, int count,
-                                         int tile_rows, int ld, int k0, int kmax, unsigned char* hi, unsigned char* lo) {
-    for (int q = threadIdx.x; q < tile_rows * 8; q += TC_NT) {
-        const int r = q >> 3, c = q & 7;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < count) {
-            const float* src = base + (size_t)idx[first + r] * ld + k0 + c * 4;
-            if (k0 + c * 4 + 3 < kmax && (ld & 3) == 0) v = *reinterpret_cast<const float4*>(src);
+// Operand staging, split in two so that the global loads of chunk k+1 are in flight while the
+// tensor core works on chunk k: tc_fetch gathers this thread's 16-byte pieces of a tile chunk
+// into registers (piece q = tid + 128 j: row q / 8, 16-byte column q % 8), tc_store splits them
+// into hi / lo and writes the swizzled buffers.
+template <int NV>
+__device__ __forceinline__ void tc_fetch(const float* const* rowp, int tile_rows, int k0, int kmax, bool vec, float4* v) {
+#pragma unroll
+    for (int j = 0; j < NV; j++) {
+        const int q = threadIdx.x + TC_NT * j, c = q & 7;
+        v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float* src = rowp[j];
+        if ((q >> 3) < tile_rows && src) {
+            src += k0 + c * 4;
+            if (vec && k0 + c * 4 + 3 < kmax) v[j] = __ldg(reinterpret_cast<const float4*>(src));
             else {
                 float t[4] = {0.f, 0.f, 0.f, 0.f};
                 for (int e = 0; e < 4; e++) if (k0 + c * 4 + e < kmax) t[e] = src[e];
-                v = make_float4(t[0], t[1], t[2], t[3]);
+                v[j] = make_float4(t[0], t[1], t[2], t[3]);
             }
         }
-        const float x[4] = {v.x, v.y, v.z, v.w};
+    }
+}
+
+template <int NV>
+__device__ __forceinline__ void tc_store(const float4* v, int tile_rows, unsigned char* hi, unsigned char* lo) {
+#pragma unroll
+    for (int j = 0; j < NV; j++) {
+        const int q = threadIdx.x + TC_NT * j, r = q >> 3, c = q & 7;
+        if (r >= tile_rows) continue;
+        const float x[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
         uint32_t h[4], l[4];
 #pragma unroll
         for (int e = 0; e < 4; e++) {
@@ -142,9 +156,27 @@ cosine_tc_kernel(ProblemFn problem) {
         const int cols = min(TC_NMAX, pb.nB - c0);
         const int npad = max(16, (cols + 15) & ~15);
         const uint32_t idesc = tc_idesc(npad);
+        // row pointers of this thread's pieces (nullptr = zero padding)
+        constexpr int NVA = TC_M * 8 / TC_NT, NVB = TC_NMAX * 8 / TC_NT;
+        const float* pa[NVA];
+        const float* pbp[NVB];
+#pragma unroll
+        for (int j = 0; j < NVA; j++) {
+            const int r = (tid + TC_NT * j) >> 3;
+            pa[j] = r < rows ? pb.A + (size_t)pb.ra[r0 + r] * pb.E : nullptr;
+        }
+#pragma unroll
+        for (int j = 0; j < NVB; j++) {
+            const int r = (tid + TC_NT * j) >> 3;
+            pbp[j] = r < cols ? pb.B + (size_t)pb.rb[c0 + r] * pb.E : nullptr;
+        }
+        const bool vec = (pb.E & 3) == 0;
+        float4 va[NVA], vb[NVB];
+        tc_fetch<NVA>(pa, TC_M, 0, pb.E, vec, va);
+        tc_fetch<NVB>(pbp, npad, 0, pb.E, vec, vb);
         for (int k0 = 0; k0 < pb.E; k0 += TC_KC) {
-            tc_stage(pb.A, pb.ra, r0, rows, TC_M, pb.E, k0, pb.E, a_hi, a_lo);
-            tc_stage(pb.B, pb.rb, c0, cols, npad, pb.E, k0, pb.E, b_hi, b_lo);
+            tc_store<NVA>(va, TC_M, a_hi, a_lo);
+            tc_store<NVB>(vb, npad, b_hi, b_lo);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
             if (tid == 0) {
@@ -160,6 +192,10 @@ cosine_tc_kernel(ProblemFn problem) {
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                              :: "r"(bar) : "memory");
+            }
+            if (k0 + TC_KC < pb.E) {                              // next chunk's loads fly during the MMAs
+                tc_fetch<NVA>(pa, TC_M, k0 + TC_KC, pb.E, vec, va);
+                tc_fetch<NVB>(pbp, npad, k0 + TC_KC, pb.E, vec, vb);
             }
             tc_mbar_wait(bar, phase);
             phase ^= 1;
