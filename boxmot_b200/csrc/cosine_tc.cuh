@@ -13,13 +13,14 @@
 // contraction (error ~1e-4 on the cosine) was not used: the distances feed an exact
 // assignment whose result must equal the reference's.
 //
-// Structure per CTA (128 threads, one 128-row tile of A against up to 256 rows of B):
+// Structure per CTA (256 threads, one 128-row tile of A against up to 256 rows of B):
 //   for each 32-element chunk of E:   all threads gather + split the chunk of the A and B
 //     tiles into shared memory in the canonical K-major SWIZZLE_128B layout (8-row x 128-byte
 //     atoms, 16-byte chunk index XOR row%8), fence.proxy.async, barrier; one thread issues the
 //     4 x 3 tcgen05.mma (M=128, N=nB rounded up to 16, K=8) and commits to an mbarrier; all
 //     threads wait on it before the buffers are overwritten.
-//   epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns at a time) -> cosine -> global.
+//   epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns at a time; warp w reads the TMEM lane
+//     quarter w % 4 and the column blocks of parity w / 4) -> cosine -> global.
 // The operands are staged by ordinary loads instead of TMA because both tiles are GATHERED
 // (rows are track slots / selected detections) and need the hi/lo split on the way in; at the
 // tracker's shapes (A = hundreds of 2 KB rows per stream, read once) the kernel is bound by
@@ -29,7 +30,7 @@
 
 namespace bm {
 
-constexpr int TC_M = 128, TC_KC = 32, TC_NMAX = 256, TC_NT = 128;
+constexpr int TC_M = 128, TC_KC = 32, TC_NMAX = 256, TC_NT = 256;
 constexpr uint32_t TC_TMEM_COLS = 256;
 
 __host__ __device__ inline size_t cosine_tc_smem_bytes() {
@@ -202,13 +203,14 @@ cosine_tc_kernel(ProblemFn problem) {
         }
         // ---- epilogue: warp w owns TMEM lanes 32w .. 32w+31 = tile rows
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int r = wid * 32 + lane;
+        const int lq = wid & 3;                                   // TMEM lane quarter this warp may read
+        const int r = lq * 32 + lane;
         const bool rin = r < rows;
         const float na = rin ? pb.na[r0 + r] : 1.f;
         float* orow = rin ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
-        for (int cb = 0; cb < npad; cb += 16) {
+        for (int cb = 16 * (wid >> 2); cb < npad; cb += 16 * (TC_NT / 128)) {
             uint32_t v[16];
-            const uint32_t taddr = tmem + ((uint32_t)(wid * 32) << 16) + (uint32_t)cb;
+            const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)cb;
             asm volatile(
                 "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
