@@ -136,6 +136,46 @@ def main_botsort():
         print("botsort", name, out.shape, "ids", int(out[:, 5].max()))
 
 
+# (case, stream id, K, frames, emb_dim, warps, tracker kwargs)
+DEEPOCSORT_CASES = [
+    ("synth_k20_e32", 20, 20, 60, 32, False, {}),
+    ("synth_k50_e64_awoff", 21, 50, 60, 64, False, {"aw_off": True}),
+    ("synth_k40_e16_cmc", 22, 40, 60, 16, True, {}),
+    ("synth_k60_e32_cmc_dt1", 23, 60, 50, 32, True, {"delta_t": 1, "max_age": 5, "det_thresh": 0.3}),
+    ("synth_k30_noemb_giou", 24, 30, 50, 32, False, {"embedding_off": True, "asso_func": "giou"}),
+    ("synth_k100_e128", 25, 100, 40, 128, False, {}),
+]
+
+
+def deepocsort_warps(seed, n_frames):
+    """Scale + shift camera warps (the CMC side input), one 2x3 matrix per frame."""
+    rng = np.random.default_rng(seed)
+    w = np.zeros((n_frames, 2, 3))
+    w[:, 0, 0] = 1 + rng.normal(0, 0.01, n_frames)
+    w[:, 1, 1] = 1 + rng.normal(0, 0.01, n_frames)
+    w[:, :, 2] = rng.normal(0, 3, (n_frames, 2))
+    return w
+
+
+def main_deepocsort():
+    for name, sid, k, f, e, use_warps, kw in DEEPOCSORT_CASES:
+        fr, em = make_stream(sid, k, f, emb_dim=e)
+        warps = deepocsort_warps(sid, f) if use_warps else None
+        trk = ref_shim.make_tracker("deepocsort", **kw)
+        out = []
+        for i, d in enumerate(fr):
+            if warps is not None:
+                trk.cmc.warps = [warps[i].copy()]
+            r = np.asarray(trk.update(d.copy(), IMG, em[i].copy()), dtype=float)
+            r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+            out.append(np.c_[np.full(len(r), i), r])
+        out = np.vstack(out)
+        extra = {"warps": warps} if warps is not None else {}
+        np.savez_compressed(os.path.join(GOLD, "ref_deepocsort_%s.npz" % name), rows=out, kw=np.array(repr(kw)),
+                            **extra)
+        print("deepocsort", name, out.shape, "ids", int(out[:, 5].max()))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -165,5 +205,7 @@ if __name__ == "__main__":
         main_kf()
     elif "--botsort" in sys.argv:
         main_botsort()
+    elif "--deepocsort" in sys.argv:
+        main_deepocsort()
     else:
         main()

@@ -161,6 +161,17 @@ class _IdentityCMC:
         return np.eye(2, 3)
 
 
+class _QueuedCMC:
+    """CMC is a side input of the path: the harness queues one 2x3 warp per frame in
+    ``tracker.cmc.warps`` (identity when the queue is empty)."""
+
+    def __init__(self, *a, **k):
+        self.warps = []
+
+    def apply(self, img, dets=None):
+        return np.array(self.warps.pop(0), dtype=float).reshape(2, 3) if self.warps else np.eye(2, 3)
+
+
 def make_tracker(name, **overrides):
     """Instantiate a reference tracker with its YAML defaults (create_tracker's
     contract, tracker_zoo.py:39-44), ReID/CMC replaced by side-input stand-ins,
@@ -194,4 +205,14 @@ def make_tracker(name, **overrides):
         mod.get_cmc_method = lambda _name: _IdentityCMC
         args.setdefault("per_class", False)
         return mod.BotSort(reid_weights=None, device="cpu", half=False, **args)
+    if name == "deepocsort":
+        import importlib
+        sys.modules.setdefault("boxmot.appearance.reid.auto_backend", types.ModuleType("x")).ReidAutoBackend = _DummyReid
+        cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
+        cmc.get_cmc_method = lambda _name: _QueuedCMC
+        mod = importlib.import_module("boxmot.trackers.deepocsort.deepocsort")
+        mod.ReidAutoBackend = _DummyReid
+        mod.get_cmc_method = lambda _name: _QueuedCMC
+        args.setdefault("per_class", False)
+        return mod.DeepOcSort(reid_weights=None, device="cpu", half=False, **args)
     raise KeyError(name)

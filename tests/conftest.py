@@ -76,6 +76,29 @@ def botsort_case(case):
     return make_stream(sid, k, f), None, kw, rows
 
 
+DEEPOCSORT_YAML = dict(det_thresh=0.5, max_age=30, min_hits=3, iou_threshold=0.3, delta_t=3, asso_func="iou",
+                       inertia=0.2, w_association_emb=0.75, alpha_fixed_emb=0.95, aw_param=0.5,
+                       embedding_off=False, cmc_off=False, aw_off=False, Q_xy_scaling=0.01, Q_s_scaling=0.0001)
+# case -> (stream id, K, frames, emb_dim); see oracle/gen_golden.py DEEPOCSORT_CASES
+DEEPOCSORT_CASES = {
+    "synth_k20_e32": (20, 20, 60, 32),
+    "synth_k50_e64_awoff": (21, 50, 60, 64),
+    "synth_k40_e16_cmc": (22, 40, 60, 16),
+    "synth_k60_e32_cmc_dt1": (23, 60, 50, 32),
+    "synth_k30_noemb_giou": (24, 30, 50, 32),
+    "synth_k100_e128": (25, 100, 40, 128),
+}
+
+
+def deepocsort_case(case):
+    """(frames, embs, warps or None, tracker kwargs, golden rows) of a DeepOCSORT fixture."""
+    from boxmot_b200.synth import make_stream
+    z = np.load(os.path.join(GOLD, "ref_deepocsort_%s.npz" % case))
+    sid, k, f, e = DEEPOCSORT_CASES[case]
+    fr, em = make_stream(sid, k, f, emb_dim=e)
+    return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
+
+
 def case_frames(case):
     from boxmot_b200.synth import make_stream
     if case.startswith("MOT17"):

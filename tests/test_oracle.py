@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 from scipy.optimize import linear_sum_assignment
 
-from conftest import (BOTSORT_CASES, BOTSORT_YAML, BYTETRACK_YAML, OCSORT_YAML, ROOT, botsort_case, assert_rows_match, case_frames, golden_rows,
+from conftest import (DEEPOCSORT_CASES, DEEPOCSORT_YAML, deepocsort_case, BOTSORT_CASES, BOTSORT_YAML, BYTETRACK_YAML, OCSORT_YAML, ROOT, botsort_case, assert_rows_match, case_frames, golden_rows,
                       split_by_frame)
 from oracle import lap
 from oracle.ocsort import OcSortOracle
@@ -97,6 +97,19 @@ def test_botsort_oracle_matches_reference_golden(case):
     for f, d in enumerate(frames):
         got = ora.update(d, None if embs is None else embs[f].copy())
         assert_rows_match(got, want_f[f], f, box_rtol=1e-9)
+
+
+@pytest.mark.parametrize("case", list(DEEPOCSORT_CASES))
+def test_deepocsort_oracle_matches_reference_golden(case):
+    """DeepOCSORT: OC-SORT + embedding term with the adaptive top-2 weighting + CMC correction
+    (incl. the reference's doubly-warped newest observation)."""
+    from oracle.deepocsort import DeepOcSortOracle
+    frames, embs, warps, kw, want = deepocsort_case(case)
+    ora = DeepOcSortOracle(**{**DEEPOCSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = ora.update(d, None, embs[f].copy(), warp=None if warps is None else warps[f])
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
 
 
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
