@@ -18,6 +18,12 @@ class OcsortConfig(ctypes.Structure):
                                       "img_w", "img_h")]
 
 
+class DeepocsortConfig(ctypes.Structure):
+    _fields_ = [("oc", OcsortConfig)] + \
+               [(n, c_double) for n in ("w_association_emb", "alpha_fixed_emb", "aw_param")] + \
+               [(n, c_int) for n in ("embedding_off", "aw_off", "emb_dim")]
+
+
 class BytetrackConfig(ctypes.Structure):
     _fields_ = [(n, c_double) for n in ("min_conf", "track_thresh", "match_thresh")] + \
                [(n, c_int) for n in ("track_buffer", "frame_rate")]
@@ -50,6 +56,11 @@ _SIGS = {
     "bm_ocsort_stream_info": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_ocsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p,
                                c_void_p, c_void_p]),
+    "bm_deepocsort_create": (c_int, [ctypes.POINTER(DeepocsortConfig), c_int, c_int, c_int,
+                                     ctypes.POINTER(c_void_p)]),
+    "bm_deepocsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p]),
+    "bm_deepocsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
     "bm_bytetrack_create": (c_int, [ctypes.POINTER(BytetrackConfig), c_int, c_int, c_int,
                                     ctypes.POINTER(c_void_p)]),
     "bm_bytetrack_destroy": (c_int, [c_void_p]),

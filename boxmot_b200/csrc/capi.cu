@@ -30,8 +30,9 @@ struct OcsEngine {
     bm::OcsParams pr;
     std::vector<void*> allocs;
     size_t smem;
-    cudaEvent_t ev[5];
+    cudaEvent_t ev[7];
     bool timing = false, timed = false;
+    bool deep = false;
 };
 
 struct ByteEngine {      // ByteTrack and BoT-SORT share the state layout and the step kernel
@@ -55,8 +56,8 @@ extern "C" {
 const char* bm_last_error(void) { return g_err; }
 int bm_version(void) { return 100; }
 
-int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, int det_cap,
-                     int smem_cost_bytes, void** handle) {
+static int ocs_create(const bm_ocsort_config* cfg, const bm_deepocsort_config* deep, int n_streams, int track_cap,
+                      int det_cap, int smem_cost_bytes, void** handle) {
     if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
         return fail(-1, "bm_ocsort_create: bad argument");
     if (cfg->delta_t < 1 || cfg->delta_t > 16) return fail(-1, "bm_ocsort_create: delta_t out of range");
@@ -66,16 +67,31 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     bm::OcsState& st = e->st;
     st.prof = nullptr;
     st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap; st.R = cfg->delta_t;
-    st.scratch_elems = (size_t)track_cap * det_cap;
+    // DeepOCSORT keeps the masked embedding matrix next to the cost matrix
+    st.scratch_elems = (size_t)track_cap * det_cap * (deep ? 2 : 1);
     st.smem_cost_elems = smem_cost_bytes / 8;
+    st.emb = nullptr; st.embsim = nullptr; st.bornslot = nullptr; st.epos = nullptr; st.wbuf = nullptr;
+    e->deep = deep != nullptr;
     bm::OcsParams& pr = e->pr;
     pr.det_thresh = cfg->det_thresh; pr.min_conf = cfg->min_conf; pr.iou_thr = cfg->asso_threshold;
     pr.inertia = cfg->inertia; pr.q_xy = cfg->q_xy_scaling; pr.q_s = cfg->q_s_scaling;
     pr.diag = sqrt((double)cfg->img_w * cfg->img_w + (double)cfg->img_h * cfg->img_h);
     pr.max_age = cfg->max_age; pr.min_hits = cfg->min_hits; pr.delta_t = cfg->delta_t;
     pr.asso_func = cfg->asso_func; pr.use_byte = cfg->use_byte ? 1 : 0;
+    pr.emb_on = 0; pr.aw_off = 1; pr.E = 0; pr.w_emb = pr.alpha_fixed = pr.aw_param = 0.0;
     const size_t S = n_streams, T = track_cap;
     cudaError_t r = cudaSuccess;
+    if (deep) {
+        pr.emb_on = deep->embedding_off ? 0 : 1; pr.aw_off = deep->aw_off ? 1 : 0; pr.E = deep->emb_dim;
+        pr.w_emb = deep->w_association_emb; pr.alpha_fixed = deep->alpha_fixed_emb; pr.aw_param = deep->aw_param;
+        if (pr.emb_on) {
+            if (r == cudaSuccess) r = dev_alloc(e, &st.emb, S * T * (size_t)pr.E);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.embsim, S * (size_t)det_cap * T);
+            if (r == cudaSuccess) r = dev_alloc(e, &st.bornslot, S * (size_t)det_cap);
+        }
+        if (r == cudaSuccess) r = dev_alloc(e, &st.epos, S * T);
+        if (r == cudaSuccess) r = dev_alloc(e, &st.wbuf, S * ((size_t)det_cap + T));
+    }
     if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::XB_N * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.sxP, S * bm::XB_N * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.lastz, S * 4 * T);
@@ -104,10 +120,46 @@ int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, 
     return bm_ocsort_reset(e, nullptr);
 }
 
+int bm_ocsort_create(const bm_ocsort_config* cfg, int n_streams, int track_cap, int det_cap,
+                     int smem_cost_bytes, void** handle) {
+    return ocs_create(cfg, nullptr, n_streams, track_cap, det_cap, smem_cost_bytes, handle);
+}
+
+int bm_deepocsort_create(const bm_deepocsort_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
+    if (!cfg) return fail(-1, "bm_deepocsort_create: bad argument");
+    if (!cfg->embedding_off && cfg->emb_dim <= 0) return fail(-1, "bm_deepocsort_create: emb_dim must be > 0");
+    if (cfg->oc.use_byte) return fail(-1, "bm_deepocsort_create: DeepOCSORT has no BYTE round");
+    if (!(cfg->aw_param < 1.0)) return fail(-1, "bm_deepocsort_create: aw_param must be < 1");
+    bm_ocsort_config oc = cfg->oc;
+    oc.min_conf = oc.det_thresh;          // one confidence gate: scores > det_thresh (deepocsort.py:340-343)
+    return ocs_create(&oc, cfg, n_streams, track_cap, det_cap, 0, handle);
+}
+
+int bm_deepocsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_deepocsort_step: null argument");
+    if (!e->deep) return fail(-1, "bm_deepocsort_step: not a DeepOCSORT engine");
+    if (e->pr.emb_on && !d_embs) return fail(-1, "bm_deepocsort_step: embeddings required unless embedding_off");
+    BM_CUDA(bm::deepocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
+                                       static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    e->timed = e->timing;
+    return 0;
+}
+
+int bm_deepocsort_kernel_times(void* handle, float* ms6) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !ms6 || !e->deep) return fail(-1, "bm_deepocsort_kernel_times: bad argument");
+    if (!e->timed) return fail(-1, "bm_deepocsort_kernel_times: no timed step (call bm_ocsort_time_kernels first)");
+    BM_CUDA(cudaEventSynchronize(e->ev[6]));
+    for (int i = 0; i < 6; i++) BM_CUDA(cudaEventElapsedTime(&ms6[i], e->ev[i], e->ev[i + 1]));
+    return 0;
+}
+
 int bm_ocsort_destroy(void* handle) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e) return 0;
-    if (e->timing) for (int i = 0; i < 5; i++) cudaEventDestroy(e->ev[i]);
+    if (e->timing) for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
     for (void* p : e->allocs) cudaFree(p);
     delete e;
     return 0;
@@ -125,6 +177,7 @@ int bm_ocsort_reset(void* handle, void* stream) {
     BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::OI_COUNT * T * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::XB_N * T * sizeof(double), s));
     BM_CUDA(cudaMemsetAsync(st.sxP, 0, S * bm::XB_N * T * sizeof(double), s));
+    if (st.emb) BM_CUDA(cudaMemsetAsync(st.emb, 0, S * T * (size_t)e->pr.E * sizeof(float), s));
     return 0;
 }
 
@@ -132,6 +185,7 @@ int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double
                    void* stream) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_ocsort_step: null argument");
+    if (e->deep) return fail(-1, "bm_ocsort_step: DeepOCSORT engine (use bm_deepocsort_step)");
     BM_CUDA(bm::ocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
                                    static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
     e->timed = e->timing;
@@ -142,10 +196,10 @@ int bm_ocsort_time_kernels(void* handle, int enable) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e) return fail(-1, "null handle");
     if (enable && !e->timing) {
-        for (int i = 0; i < 5; i++) BM_CUDA(cudaEventCreate(&e->ev[i]));
+        for (int i = 0; i < 7; i++) BM_CUDA(cudaEventCreate(&e->ev[i]));
         e->timing = true;
     } else if (!enable && e->timing) {
-        for (int i = 0; i < 5; i++) cudaEventDestroy(e->ev[i]);
+        for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
         e->timing = e->timed = false;
     }
     return 0;
@@ -153,7 +207,7 @@ int bm_ocsort_time_kernels(void* handle, int enable) {
 
 int bm_ocsort_kernel_times(void* handle, float* ms4) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
-    if (!e || !ms4) return fail(-1, "bm_ocsort_kernel_times: bad argument");
+    if (!e || !ms4 || e->deep) return fail(-1, "bm_ocsort_kernel_times: bad argument");
     if (!e->timed) return fail(-1, "bm_ocsort_kernel_times: no timed step (call bm_ocsort_time_kernels first)");
     BM_CUDA(cudaEventSynchronize(e->ev[4]));
     for (int i = 0; i < 4; i++) BM_CUDA(cudaEventElapsedTime(&ms4[i], e->ev[i], e->ev[i + 1]));

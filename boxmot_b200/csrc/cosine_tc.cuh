@@ -119,6 +119,7 @@ struct CosineProblem {
     const float* B; const int* rb; const float* nb; int nB;
     int E;
     float* out; int out_ld;                                     // out[ra[i] * out_ld + j]
+    int raw = 0;                                                // 1: out = <A, B> as it is (na / nb unused)
 };
 
 // grid = (row tiles of 128, problems); the caller provides problem(blockIdx.y).
@@ -206,7 +207,7 @@ cosine_tc_kernel(ProblemFn problem) {
         const int lq = wid & 3;                                   // TMEM lane quarter this warp may read
         const int r = lq * 32 + lane;
         const bool rin = r < rows;
-        const float na = rin ? pb.na[r0 + r] : 1.f;
+        const float na = (rin && !pb.raw) ? pb.na[r0 + r] : 1.f;
         float* orow = rin ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
         for (int cb = 16 * (wid >> 2); cb < npad; cb += 16 * (TC_NT / 128)) {
             uint32_t v[16];
@@ -222,6 +223,7 @@ cosine_tc_kernel(ProblemFn problem) {
                 for (int j = 0; j < 16; j++) {
                     const int c = cb + j;
                     if (c < cols) {
+                        if (pb.raw) { orow[c] = __uint_as_float(v[j]); continue; }
                         const double cs = (double)__uint_as_float(v[j]) / ((double)na * (double)pb.nb[c0 + c]);
                         orow[c] = (float)fmax(0.0, 1.0 - cs);
                     }

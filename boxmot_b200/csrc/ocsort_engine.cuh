@@ -24,6 +24,9 @@ enum { AB_X1 = 0, AB_Y1, AB_X2, AB_Y2, AB_VY, AB_VX, AB_KCX, AB_KCY, AB_KVALID, 
 struct OcsParams {
     double det_thresh, min_conf, iou_thr, inertia, q_xy, q_s, diag;
     int max_age, min_hits, delta_t, asso_func, use_byte;
+    // DeepOCSORT (deepocsort.py:265-314): embedding term of the first round and its EMA
+    int emb_on, aw_off, E;         // emb_on = 0 <=> embedding_off
+    double w_emb, alpha_fixed, aw_param;
 };
 
 struct OcsState {
@@ -48,6 +51,12 @@ struct OcsState {
     int* born;                     // [S][Dcap]    detection rows that start a track, in id order
     long long* prof;               // optional [S][8] clock64 phase stamps of the association kernel (debug)
     int* hsel;                     // [S][2][Dcap] detection rows of the high-score set, then of the BYTE set
+    // DeepOCSORT only (nullptr in an OC-SORT engine)
+    float* emb;                    // [S][Tcap][E]   track embedding by slot (KalmanBoxTracker.emb)
+    float* embsim;                 // [S][Dcap][Tcap] dets_embs @ trk_embs.T by (detection row, list position)
+    int* bornslot;                 // [S][Dcap]      slot given to the k-th birth of the frame
+    int* epos;                     // [S][Tcap]      list position at contraction time (after a NaN-track removal)
+    double* wbuf;                  // [S][Dcap + Tcap] row / column weights of compute_aw_max_metric
 };
 
 struct OcsView {   // per-stream base pointers
@@ -221,4 +230,9 @@ size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr);
 cudaError_t ocsort_step_configure(size_t smem);
 cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
                                double* out, int* nout, cudaStream_t stream, cudaEvent_t* ev = nullptr);
+// DeepOCSORT frame step: embs [S][Dcap][E] float32 (ignored when embedding is off), warps
+// [S][6] float64 row-major 2x3 or nullptr (no CMC correction this frame).
+cudaError_t deepocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
+                                   const float* embs, const double* warps, double* out, int* nout,
+                                   cudaStream_t stream, cudaEvent_t* ev = nullptr);
 }  // namespace bm

@@ -23,6 +23,7 @@
 // stream cannot keep enough loads in flight for the predict / update / finalize phases.)
 #include "ocsort_engine.cuh"
 #include "lap_rect.cuh"
+#include "cosine_tc.cuh"
 #include <cstdio>
 #include <cstdlib>
 
@@ -100,8 +101,72 @@ __device__ __forceinline__ void ocs_predict_track(const OcsState& st, const OcsP
     ab[AB_KVALID * Tcap + p] = ok ? 1.0 : 0.0;
 }
 
+constexpr int BM_ERR_WARP_OCS = 32;   // camera-motion warp with rotation / shear (needs a dense covariance)
+
+// DeepOCSORT CMC correction of one track, BEFORE its predict (deepocsort.py:191-208 +
+// xysr_kf.py:111-135), for a warp without rotation / shear (diagonal 2x2 part): the block
+// form of the covariance is kept and every product is the reference's own.  Anything else
+// needs a dense covariance: flagged, not applied.
+//   * boxes go through x -> a x + tx, y -> d y + ty per corner;
+//   * the reference keeps ONE numpy array as `last_observation`, `observations[age_last]` and
+//     the detection row, so the newest observation is warped once through `last_observation`
+//     (when its sum is > 0) and once more through the `observations` window when
+//     age - age_last <= delta_t;
+//   * the Kalman mean / covariance and, while frozen, the frozen copy are warped; the ORU anchor
+//     (the LIVE history's last measurement, xysr_kf.py:184-192) is not.
+__device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, const double* w6, int delta_t) {
+    const int T = v.Tcap;
+    const double a = w6[0], tx = w6[2], d = w6[4], ty = w6[5];
+    if (w6[1] != 0.0 || w6[3] != 0.0) { atomicOr(&v.hdr[OH_ERR], BM_ERR_WARP_OCS); return; }
+    const int age = v.I(OI_AGE, slot);
+    if (v.I(OI_HITS, slot) > 0) {
+        double lo[5];
+#pragma unroll
+        for (int c = 0; c < 5; c++) lo[c] = v.lastobs[c * T + slot];
+        const double lsum = (((lo[0] + lo[1]) + lo[2]) + lo[3]) + lo[4];
+        int times = lsum > 0 ? 1 : 0;
+        if (v.I(OI_TSU, slot) <= delta_t) times++;          // age_last = age - time_since_update
+        for (int k = 0; k < times; k++) {
+            lo[0] = a * lo[0] + tx; lo[2] = a * lo[2] + tx;
+            lo[1] = d * lo[1] + ty; lo[3] = d * lo[3] + ty;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) v.lastobs[c * T + slot] = lo[c];
+        // the rest of the window; the newest observation's ring copy follows last_observation
+        for (int r = 0; r < v.R; r++) {
+            const int ra = v.ring_age[r * T + slot];
+            if (ra < 0 || ra < age - delta_t) continue;
+            if (ra == age - v.I(OI_TSU, slot)) {
+#pragma unroll
+                for (int c = 0; c < 4; c++) v.ring[(r * 4 + c) * T + slot] = lo[c];
+            } else {
+                double* q = v.ring + (size_t)(r * 4) * T + slot;
+                q[0] = a * q[0] + tx; q[2 * T] = a * q[2 * T] + tx;
+                q[T] = d * q[T] + ty; q[3 * T] = d * q[3 * T] + ty;
+            }
+        }
+    }
+    const int flags = v.I(OI_FLAGS, slot);
+    for (int pass = 0; pass < 2; pass++) {
+        if (pass == 1 && !(!(flags & OF_OBSERVED) && (flags & OF_SAVED))) break;
+        double* b = pass ? v.sxP : v.xP;
+        b[0 * T + slot] = a * b[0 * T + slot] + tx;
+        b[1 * T + slot] = d * b[1 * T + slot] + ty;
+        b[4 * T + slot] = a * b[4 * T + slot];
+        b[5 * T + slot] = d * b[5 * T + slot];
+        // Pb = {P[b][b], P[b][b+4], P[b+4][b], P[b+4][b+4]}: only the two diagonal 2x2 blocks
+        // P[:2,:2] and P[4:6,4:6] are warped by the reference (m P m^T), not the cross terms
+        b[(7 + 0) * T + slot] = (a * b[(7 + 0) * T + slot]) * a;
+        b[(7 + 3) * T + slot] = (a * b[(7 + 3) * T + slot]) * a;
+        b[(7 + 4) * T + slot] = (d * b[(7 + 4) * T + slot]) * d;
+        b[(7 + 7) * T + slot] = (d * b[(7 + 7) * T + slot]) * d;
+    }
+}
+
+template <bool DEEP>
 __global__ void __launch_bounds__(K1_NT)
-ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
+ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets,
+                   const double* __restrict__ warps) {
     const int chunks = (st.Tcap + K1_NT - 1) / K1_NT;
     if ((int)blockIdx.x >= st.S * chunks) {
         const int s = ((int)blockIdx.x - st.S * chunks) * (K1_NT / 32) + warp_id();
@@ -113,7 +178,10 @@ ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, co
     OcsView v(st, s);
     const int nT = v.hdr[OH_NLIST];
     if (p == 0) st.n_updates[s] += (unsigned long long)nT;
-    if (p < nT) ocs_predict_track(st, pr, v, s, p);
+    if (p < nT) {
+        if (DEEP && warps) docs_affine_track(v, v.order[p], warps + (size_t)s * 6, pr.delta_t);
+        ocs_predict_track(st, pr, v, s, p);
+    }
 }
 
 // ============================================================================ K2
@@ -619,6 +687,101 @@ __device__ inline void ocm_scan_rows_lane(const OcmCost& c, const OcmScreen& sc,
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// DeepOCSORT first round (association.py:427-474): total = (iou + OCM) + emb, with
+//   emb = dets_embs @ trk_embs.T (tensor-core contraction, st.embsim), emb[iou <= 0] = 0,
+//   then compute_aw_max_metric (:320-374): every row and column with >= 2 positive entries
+//   scales its weight by 1 - max(second / max - aw_param, 0) / (1 - aw_param); or emb * w
+//   with aw_off.
+// The weights need every entry of the row AND of the column, so this round materialises the
+// matrix (stream-private, L2-resident scratch): pass A a warp per row (base cost, masked
+// embedding, row top-2, IoU hit counts), pass B a thread per column (column top-2), pass C a
+// warp per row (final cost -(total), row minima for the solver, matrix maximum for lapjv's
+// padding).  Column index = list position; `remap` is set after a NaN-track removal.
+__device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, int s, const OcsSmem& sm,
+                                       const OcmCost& ocm, int nD, int nT, bool remap, double* s_cmx) {
+    const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
+    const int Tcap = st.Tcap, Dcap = st.Dcap;
+    double* cost = st.scratch + (size_t)s * st.scratch_elems;       // [nD][nT]
+    double* embm = cost + (size_t)Tcap * Dcap;                      // [nD][nT]
+    double* roww = st.wbuf + (size_t)s * (Dcap + Tcap);
+    double* colw = roww + Dcap;
+    const float* sim = st.embsim + (size_t)s * Dcap * Tcap;
+    const int* epos = st.epos + (size_t)s * Tcap;
+    const bool aw = pr.emb_on && !pr.aw_off;
+    for (int d = wid; d < nD; d += K2_NT / 32) {
+        const Box a = ocm.det(d);
+        const double cx = (a.x1 + a.x2) / 2.0, cy = (a.y1 + a.y2) / 2.0;
+        const float* srow = sim + (size_t)sm.dind[d] * Tcap;
+        double m1 = 0.0, m2 = 0.0;
+        int npos = 0, hits = 0, hit = -1;
+        for (int t = lane; t < nT; t += 32) {
+            double iou;
+            const double c = ocm.entry(a, cx, cy, t, &iou);
+            double e = 0.0;
+            if (pr.emb_on) {
+                e = (double)srow[remap ? epos[t] : t];
+                if (iou <= 0) e = 0.0;
+            }
+            cost[(size_t)d * nT + t] = c;
+            embm[(size_t)d * nT + t] = e;
+            if (e > 0) { npos++; if (e > m1) { m2 = m1; m1 = e; } else if (e > m2) m2 = e; }
+            if (iou > pr.iou_thr) { hits++; hit = t; atomicAdd(&sm.colcnt[t], 1); }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const double b1 = shfl_xor_d(m1, o), b2 = shfl_xor_d(m2, o);
+            m2 = fmax(fmin(m1, b1), fmax(m2, b2));
+            m1 = fmax(m1, b1);
+            npos += __shfl_xor_sync(BM_FULL, npos, o);
+            hits += __shfl_xor_sync(BM_FULL, hits, o);
+            hit = max(hit, __shfl_xor_sync(BM_FULL, hit, o));
+        }
+        if (lane == 0) {
+            double w = 1.0;
+            if (aw && npos >= 2) w = 1.0 - fmax(m2 / m1 - pr.aw_param, 0.0) / (1.0 - pr.aw_param);
+            roww[d] = w;
+            sm.rowcnt[d] = hits;
+            sm.hit_t[d] = hit;
+        }
+    }
+    __syncthreads();
+    if (aw) {
+        for (int t = tid; t < nT; t += K2_NT) {
+            double m1 = 0.0, m2 = 0.0;
+            int npos = 0;
+            for (int d = 0; d < nD; d++) {
+                const double e = embm[(size_t)d * nT + t];
+                if (e > 0) { npos++; if (e > m1) { m2 = m1; m1 = e; } else if (e > m2) m2 = e; }
+            }
+            colw[t] = npos >= 2 ? 1.0 - fmax(m2 / m1 - pr.aw_param, 0.0) / (1.0 - pr.aw_param) : 1.0;
+        }
+        __syncthreads();
+    }
+    double cmx = -CUDART_INF;
+    for (int d = wid; d < nD; d += K2_NT / 32) {
+        const double rw = roww[d];
+        double best = CUDART_INF;
+        int barg = 0x7fffffff;
+        for (int t = lane; t < nT; t += 32) {
+            double c = cost[(size_t)d * nT + t];
+            if (pr.emb_on) {
+                const double e = embm[(size_t)d * nT + t];
+                // w_emb = full(w); w[row] *= row_weight; w[:, col] *= col_weight; w * emb
+                const double w = aw ? (pr.w_emb * rw) * colw[t] : pr.w_emb;
+                c = -((-c) + w * e);
+                cost[(size_t)d * nT + t] = c;
+            }
+            cmx = fmax(cmx, c);
+            if (c < best) { best = c; barg = t; }
+        }
+        warp_argmin(best, barg);
+        if (lane == 0) { sm.rmin[d] = best; sm.rarg[d] = barg; }
+    }
+    for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
+    if (lane == 0) s_cmx[wid] = cmx;
+    __syncthreads();
+}
+
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
 // `alist` (indices into a detection set `abox`), cols = the nB list positions in
 // `blist` with boxes fetched by `bfetch`.  lapjv on -iou, accept pairs with iou >= thr
@@ -703,6 +866,7 @@ struct FetchLast {     // last observations (global state)
     }
 };
 
+template <bool DEEP>
 __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParams& pr, const float* __restrict__ dets,
                                               int s, unsigned char* smem_raw, OcsSmem& sm_out) {
     const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
@@ -760,6 +924,7 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
                 for (int f = 0; f < 4; f++) nan |= ab[f * Tcap + p] != ab[f * Tcap + p];
                 if (nan) continue;
                 for (int f = 0; f < AB_COUNT; f++) ab[f * Tcap + k] = ab[f * Tcap + p];
+                if (DEEP) st.epos[(size_t)s * Tcap + k] = p;
                 sm.slot_of[k] = sm.slot_of[p];
                 v.order[k] = sm.slot_of[k];
                 k++;
@@ -777,8 +942,11 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
     // ---- first round: cost[d][t] = -(iou + OCM), det-major like enhanced_associate
     // (association.py:427-461), evaluated on demand; permutation fast path (:501-503) or
     // exact LAP (:505-507)
+    __shared__ double s_cmx[K2_NT / 32];
     if (nD > 0 && nT > 0) {
-        if (pr.asso_func == ASSO_IOU)
+        if (DEEP)
+            deep_build_cost(st, pr, s, sm, ocm, nD, nT, sm.misc[M_ANYBAD] != 0, s_cmx);
+        else if (pr.asso_func == ASSO_IOU)
             ocm_scan_rows_lane(ocm, scr, nD, nT, pr.iou_thr, sm.colcnt, sm.rmin, sm.rarg, sm.rowcnt, sm.hit_t,
                                sm.cand + ocs_cand_ints(Tcap) * wid);
         else
@@ -796,8 +964,7 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
         }
         const bool fast = rmax == 1 && cmax_ == 1;           // uniform over the CTA
         double* cost = st.scratch + (size_t)s * st.scratch_elems;
-        __shared__ double s_cmx[K2_NT / 32];
-        if (!fast && nD > nT) {
+        if (!DEEP && !fast && nD > nT) {
             // WHICH zero-gain detections stay unassigned when there are more detections than
             // tracks is decided by lapjv's scan order (the reference's unmatched-detection ORDER,
             // and with it the new ids, depends on it): materialise the matrix for the
@@ -829,9 +996,13 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
                     // the padding), so the outcome does not depend on lapjv's tie-breaking and the
                     // fast exact solver applies; the null option is never taken (cost +inf).
                     RectWork w = rect_carve(sm.work, nD, nT);
-                    const OcmCostStaged oc2 = {ocm, reinterpret_cast<double*>(sm.cand), &sm.misc[M_ROW], w.spc, nT};
-                    bad = rect_solve_warp(oc2, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
-                    oc2.release();
+                    if (DEEP) {
+                        bad = rect_solve_warp(DenseCost{cost, nT}, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
+                    } else {
+                        const OcmCostStaged oc2 = {ocm, reinterpret_cast<double*>(sm.cand), &sm.misc[M_ROW], w.spc, nT};
+                        bad = rect_solve_warp(oc2, nD, nT, CUDART_INF, w, sm.rmin, sm.rarg);
+                        oc2.release();
+                    }
                     xsol = w.x;
                 } else {
                     double pad = s_cmx[0];
@@ -859,7 +1030,7 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
                 if (lane == 0) atomicAdd(&v.hdr[OH_LAPS], 1);
             }
             if (lane == 0) sm.misc[M_FAST] = fast ? 1 : 0;
-        } else if (wid == 1 && !fast && nD <= nT) {
+        } else if (!DEEP && wid == 1 && !fast && nD <= nT) {
             RectWork w = rect_carve(sm.work, nD, nT);
             const OcmCostStaged oc2 = {ocm, reinterpret_cast<double*>(sm.cand), &sm.misc[M_ROW], w.spc, nT};
             oc2.helper();
@@ -961,11 +1132,12 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
     }
 }
 
+template <bool DEEP>
 __global__ void __launch_bounds__(K2_NT, 8)
 ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     OcsSmem sm;
-    ocs_assoc_cta(st, pr, dets, blockIdx.x, smem_raw, sm);
+    ocs_assoc_cta<DEEP>(st, pr, dets, blockIdx.x, smem_raw, sm);
 }
 
 // ============================================================================ K3
@@ -1059,6 +1231,7 @@ ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, d
         const float* dr = dets + ((size_t)s * Dcap + di) * 6;
         const double det[5] = {(double)dr[0], (double)dr[1], (double)dr[2], (double)dr[3], (double)dr[4]};
         ocs_track_init(v, bslot[tid], det, (double)dr[5], di, id0 + tid);
+        if (st.bornslot) st.bornslot[(size_t)s * Dcap + tid] = bslot[tid];
     }
     if (tid >= nT && tid < nT + born) slot = bslot[tid - nT];
     __syncthreads();
@@ -1100,12 +1273,79 @@ ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, d
     if (keep) v.order[krank] = slot;      // every thread read its slot before the scans' barriers
     if (tid == 0) {
         nout[s] = n_emit;
+        v.hdr[OH_NBORN] = born;                // clamped to the free slots (read by docs_emb_kernel)
         v.hdr[OH_NLIST] = n_keep;
         v.hdr[OH_NEXT_ID] = id0 + born;
         v.hdr[OH_FRAME] = frame;
         v.hdr[OH_BIRTHS] += born;
     }
 }
+
+// ============================================================================ DeepOCSORT
+// Embedding side of the frame: update_emb for every (track, detection) update of the frame
+// (deepocsort.py:184-186, :383-384, :418-421: emb = alpha emb + (1 - alpha) det_emb, then
+// / ||emb||, alpha = dets_alpha from the detection confidence :357-360) and the raw copy for
+// births (:436-445).  One warp per pair; fp64 arithmetic, fp32 storage (the contraction that
+// consumes it is fp32-accurate).
+constexpr int K5_NT = 256;
+__global__ void __launch_bounds__(K5_NT)
+docs_emb_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const float* __restrict__ embs) {
+    const int s = blockIdx.x, lane = lane_id();
+    const int Tcap = st.Tcap, Dcap = st.Dcap, E = pr.E;
+    const int* hdr = st.hdr + (size_t)s * OH_COUNT;
+    const int nupd = hdr[OH_NUPD], nborn = hdr[OH_NBORN];
+    const int k = blockIdx.y * (K5_NT / 32) + warp_id();
+    if (k >= nupd + nborn) return;
+    int slot, di;
+    const bool birth = k >= nupd;
+    if (!birth) {
+        const int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
+        slot = upd_slot[k]; di = upd_slot[Dcap + k];
+    } else {
+        slot = st.bornslot[(size_t)s * Dcap + (k - nupd)];
+        di = st.born[(size_t)s * Dcap + (k - nupd)];
+    }
+    float* dst = st.emb + ((size_t)s * Tcap + slot) * E;
+    const float* src = embs + ((size_t)s * Dcap + di) * E;
+    if (birth) {
+        for (int e = lane; e < E; e += 32) dst[e] = src[e];
+        return;
+    }
+    const double conf = (double)dets[((size_t)s * Dcap + di) * 6 + 4];
+    const double trust = (conf - pr.det_thresh) / (1.0 - pr.det_thresh);
+    const double af = pr.alpha_fixed;
+    const double alpha = af + (1.0 - af) * (1.0 - trust);
+    double ss = 0.0;
+    for (int e = lane; e < E; e += 32) {
+        const double v = alpha * (double)dst[e] + (1.0 - alpha) * (double)src[e];
+        ss += v * v;
+    }
+    for (int o = 16; o > 0; o >>= 1) ss += shfl_xor_d(ss, o);
+    const double nrm = sqrt(ss);
+    for (int e = lane; e < E; e += 32) {
+        const double v = alpha * (double)dst[e] + (1.0 - alpha) * (double)src[e];
+        dst[e] = (float)(v / nrm);
+    }
+}
+
+// dets_embs @ trk_embs.T of one stream for cosine_tc_kernel (raw dot products): A = the
+// frame's detection embeddings gathered through the high-score list, B = the track embeddings
+// gathered through the list order; out[detection row][list position].
+struct DeepDot {
+    OcsState st;
+    const float* embs;
+    int E;
+    __device__ CosineProblem operator()(int s) const {
+        const int* hdr = st.hdr + (size_t)s * OH_COUNT;
+        CosineProblem p;
+        p.A = embs + (size_t)s * st.Dcap * E; p.ra = st.hsel + (size_t)s * 2 * st.Dcap; p.na = nullptr; p.nA = hdr[OH_ND];
+        p.B = st.emb + (size_t)s * st.Tcap * E; p.rb = st.order + (size_t)s * st.Tcap; p.nb = nullptr; p.nB = hdr[OH_NLIST];
+        p.E = E;
+        p.out = st.embsim + (size_t)s * st.Dcap * st.Tcap; p.out_ld = st.Tcap;
+        p.raw = 1;
+        return p;
+    }
+};
 
 }  // namespace bm
 
@@ -1116,7 +1356,12 @@ size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr) {
 }
 
 cudaError_t ocsort_step_configure(size_t smem) {
-    return cudaFuncSetAttribute(ocs_assoc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(ocs_assoc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(ocs_assoc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(cosine_tc_kernel<DeepDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)cosine_tc_smem_bytes());
 }
 
 // BM_DEBUG_SYNC=1 in the environment synchronises after every kernel and names the one that
@@ -1137,10 +1382,10 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
     // optional per-kernel timing: five events bracket the four launches (bm_ocsort_kernel_times)
 #define BM_EV(k) do { if (ev && (e = cudaEventRecord(ev[k], stream)) != cudaSuccess) return e; } while (0)
     BM_EV(0);
-    ocs_predict_kernel<<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets);
+    ocs_predict_kernel<false><<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets, nullptr);
     if ((e = dbg_check("ocs_predict_kernel", stream)) != cudaSuccess) return e;
     BM_EV(1);
-    ocs_assoc_kernel<<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
+    ocs_assoc_kernel<false><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel", stream)) != cudaSuccess) return e;
     BM_EV(2);
     ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
@@ -1150,6 +1395,44 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
     ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
     if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
     BM_EV(4);
+#undef BM_EV
+    return cudaGetLastError();
+}
+
+// DeepOCSORT frame step (DeepOcSort.update, deepocsort.py:316-498): CMC correction + predict,
+// embedding contraction on the tensor cores, association with the materialised first round,
+// Kalman update, finalize, embedding EMA / births.  ev: optional 7 events around the 6 launches.
+cudaError_t deepocsort_step_launch(const OcsState& st, const OcsParams& pr, const float* dets, const int* ndets,
+                                   const float* embs, const double* warps, double* out, int* nout,
+                                   cudaStream_t stream, cudaEvent_t* ev) {
+    const int c1 = (st.Tcap + K1_NT - 1) / K1_NT, c3 = (st.Dcap + K3_NT - 1) / K3_NT;
+    cudaError_t e;
+#define BM_EV(k) do { if (ev && (e = cudaEventRecord(ev[k], stream)) != cudaSuccess) return e; } while (0)
+    BM_EV(0);
+    ocs_predict_kernel<true><<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets, warps);
+    if ((e = dbg_check("ocs_predict_kernel<deep>", stream)) != cudaSuccess) return e;
+    BM_EV(1);
+    if (pr.emb_on) {
+        cosine_tc_kernel<DeepDot><<<dim3((st.Dcap + TC_M - 1) / TC_M, st.S), TC_NT, cosine_tc_smem_bytes(), stream>>>(
+            DeepDot{st, embs, pr.E});
+        if ((e = dbg_check("cosine_tc_kernel<DeepDot>", stream)) != cudaSuccess) return e;
+    }
+    BM_EV(2);
+    ocs_assoc_kernel<true><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
+    if ((e = dbg_check("ocs_assoc_kernel<deep>", stream)) != cudaSuccess) return e;
+    BM_EV(3);
+    ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
+    if ((e = dbg_check("ocs_update_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(4);
+    const int nt4 = (st.Tcap + 31) / 32 * 32;
+    ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
+    if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
+    BM_EV(5);
+    if (pr.emb_on) {
+        docs_emb_kernel<<<dim3(st.S, (st.Dcap + K5_NT / 32 - 1) / (K5_NT / 32)), K5_NT, 0, stream>>>(st, pr, dets, embs);
+        if ((e = dbg_check("docs_emb_kernel", stream)) != cudaSuccess) return e;
+    }
+    BM_EV(6);
 #undef BM_EV
     return cudaGetLastError();
 }

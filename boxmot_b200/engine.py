@@ -168,6 +168,100 @@ class OcSortEngine(_HostStepMixin):
         return x[:k], P[:k].reshape(k, 7, 7), ids[:k]
 
 
+class DeepOcSortEngine(OcSortEngine):
+    """S independent DeepOCSORT trackers (boxmot/trackers/deepocsort/deepocsort.py:265-498) per
+    step: the OC-SORT engine plus the embedding term of the first association round (tensor-core
+    contraction + adaptive top-2 weighting), the embedding EMA and the CMC correction.
+
+    ReID and CMC are side inputs: ``embs`` [S, det_cap, emb_dim] float32 row-aligned with
+    ``dets`` (required unless ``embedding_off``), ``warps`` [S, 2, 3] float64 or None."""
+
+    def __init__(self, n_streams, track_cap=256, det_cap=128, device="cuda:0", det_thresh=0.3, max_age=30,
+                 min_hits=3, iou_threshold=0.3, delta_t=3, asso_func="iou", inertia=0.2,
+                 w_association_emb=0.5, alpha_fixed_emb=0.95, aw_param=0.5, embedding_off=False,
+                 cmc_off=False, aw_off=False, Q_xy_scaling=0.01, Q_s_scaling=0.0001, emb_dim=512,
+                 img_wh=(1920, 1080)):
+        if not torch.cuda.is_available():
+            raise RuntimeError("DeepOcSortEngine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.S, self.Tcap, self.Dcap = int(n_streams), int(track_cap), int(det_cap)
+        self.emb_on, self.cmc_off = not embedding_off, bool(cmc_off)
+        self.E = int(emb_dim) if self.emb_on else 0
+        oc = _lib.OcsortConfig(det_thresh, det_thresh, iou_threshold, inertia, Q_xy_scaling, Q_s_scaling,
+                               int(max_age), int(min_hits), int(delta_t), _lib.ASSO_FUNCS[asso_func], 0,
+                               int(img_wh[0]), int(img_wh[1]))
+        cfg = _lib.DeepocsortConfig(oc, w_association_emb, alpha_fixed_emb, aw_param,
+                                    int(bool(embedding_off)), int(bool(aw_off)), self.E)
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_deepocsort_create(ctypes.byref(cfg), self.S, self.Tcap, self.Dcap,
+                                                       ctypes.byref(self._h)), "bm_deepocsort_create")
+            torch.cuda.synchronize(self.device)
+        self.out_rows = min(self.Tcap, self.Dcap)
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+        self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+        self.launches = 0
+
+    def step(self, dets, ndets, embs=None, warps=None, out=None, nout=None):
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (self.S, self.Dcap, 6)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        if self.emb_on:
+            assert embs is not None and embs.dtype == torch.float32 and embs.is_cuda and embs.is_contiguous()
+            assert tuple(embs.shape) == (self.S, self.Dcap, self.E)
+        if self.cmc_off:
+            warps = None
+        if warps is not None:
+            assert warps.dtype == torch.float64 and warps.is_cuda and tuple(warps.shape) == (self.S, 2, 3)
+            assert warps.is_contiguous()
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_deepocsort_step(self._h, _ptr(dets), _ptr(ndets),
+                                                     _ptr(embs) if self.emb_on else None,
+                                                     _ptr(warps) if warps is not None else None,
+                                                     _ptr(out), _ptr(nout), _stream_ptr(self.device)),
+                       "bm_deepocsort_step")
+        self.launches += 6 if self.emb_on else 4
+        return out, nout
+
+    def kernel_times(self):
+        """(predict+CMC, contraction, assoc, update, finalize, embedding EMA) ms of the last timed step."""
+        buf = (ctypes.c_float * 6)()
+        _lib.check(_lib.lib().bm_deepocsort_kernel_times(self._h, ctypes.byref(buf)), "bm_deepocsort_kernel_times")
+        return tuple(float(v) for v in buf)
+
+    def step_host(self, dets_per_stream, embs_per_stream=None, warps=None):
+        """Lists of S arrays (N_s, 6) and (N_s, E) (+ S 2x3 warps); returns a list of (M_s, 8) arrays."""
+        if not hasattr(self, "_h_dets"):
+            self._h_dets = torch.zeros((self.S, self.Dcap, 6), dtype=torch.float32).pin_memory()
+            self._h_nd = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+            self._h_embs = torch.zeros((self.S, self.Dcap, max(self.E, 1)), dtype=torch.float32).pin_memory()
+            self._h_out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64).pin_memory()
+            self._h_nout = torch.zeros((self.S,), dtype=torch.int32).pin_memory()
+        hd, hn, he = self._h_dets.numpy(), self._h_nd.numpy(), self._h_embs.numpy()
+        for s, d in enumerate(dets_per_stream):
+            n = 0 if d is None else len(d)
+            if n > self.Dcap:
+                raise RuntimeError("stream %d: %d detections exceed det_cap=%d" % (s, n, self.Dcap))
+            if n:
+                hd[s, :n] = d
+                if self.emb_on:
+                    he[s, :n] = embs_per_stream[s]
+            hn[s] = n
+        d_dets = self._h_dets.to(self.device, non_blocking=True)
+        d_nd = self._h_nd.to(self.device, non_blocking=True)
+        d_embs = self._h_embs.to(self.device, non_blocking=True) if self.emb_on else None
+        d_w = None if warps is None else torch.as_tensor(np.asarray(warps, dtype=np.float64)).reshape(
+            self.S, 2, 3).contiguous().to(self.device)
+        out, nout = self.step(d_dets, d_nd, d_embs, d_w)
+        self._h_out.copy_(out, non_blocking=True)
+        self._h_nout.copy_(nout, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
+        return [ho[s, : hn2[s]].copy() for s in range(self.S)]
+
 
 class HostPipeline:
     """Double-buffered host <-> device pipeline around ``OcSortEngine.step``: while frame f

@@ -18,6 +18,7 @@ _MAPPING = {
     "ocsort": ("boxmot_b200.trackers.ocsort", "OcSort"),
     "bytetrack": ("boxmot_b200.trackers.bytetrack", "ByteTrack"),
     "botsort": ("boxmot_b200.trackers.botsort", "BotSort"),
+    "deepocsort": ("boxmot_b200.trackers.deepocsort", "DeepOcSort"),
 }
 _REID_TRACKERS = ("strongsort", "botsort", "deepocsort", "hybridsort", "boosttrack")
 

@@ -59,6 +59,33 @@ int bm_ocsort_counters(void* handle, unsigned long long* out4, void* stream);
 /* Debug: when d_stamps (device, [S][8] int64) is non-null the association kernel records
  * clock64() at its phase boundaries for every stream; pass NULL to switch it off. */
 int bm_ocsort_debug_profile(void* handle, long long* d_stamps);
+/* ---- DeepOCSORT engine ------------------------------------------------------------
+ * Replaces DeepOcSort.__init__/update (boxmot/trackers/deepocsort/deepocsort.py:265-498),
+ * its KalmanBoxTracker (:51-235: update_emb :184-186, apply_affine_correction :191-208 with
+ * KalmanFilterXYSR.apply_affine_correction, xysr_kf.py:111-135) and associate with the
+ * embedding term (boxmot/utils/association.py:462-474, compute_aw_max_metric :320-374).
+ * The engine is the OC-SORT engine with the embedding state added: the handle is accepted by
+ * bm_ocsort_destroy / _reset / _status / _counters / _stream_info / _peek / _time_kernels.
+ * ReID and CMC are side inputs: the caller passes the detections' embeddings and one 2x3
+ * warp per stream.  oc.min_conf and oc.use_byte are ignored (one gate: conf > oc.det_thresh). */
+typedef struct bm_deepocsort_config {
+    bm_ocsort_config oc;
+    double w_association_emb, alpha_fixed_emb, aw_param;
+    int embedding_off, aw_off;
+    int emb_dim;
+} bm_deepocsort_config;
+int bm_deepocsort_create(const bm_deepocsort_config* cfg, int n_streams, int track_cap, int det_cap,
+                         void** handle);
+/* One frame for all streams.  d_dets / d_ndets / d_out / d_nout as bm_ocsort_step.
+ * d_embs [S][det_cap][emb_dim] float32, row-aligned with d_dets (may be NULL when
+ * embedding_off).  d_warps [S][6] float64, row-major 2x3 camera-motion warp applied to every
+ * track before its predict, or NULL (cmc_off / identity); a warp with rotation or shear sets
+ * error bit 32 (the block-form covariance cannot hold it) and is not applied. */
+int bm_deepocsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* Durations (ms) of the six launches of the last step after bm_ocsort_time_kernels(handle, 1):
+ * predict(+CMC), embedding contraction, association, Kalman update, finalize, embedding EMA. */
+int bm_deepocsort_kernel_times(void* handle, float* ms6);
 /* ---- ByteTrack engine -------------------------------------------------------------
  * Replaces ByteTrack.__init__/update (boxmot/trackers/bytetrack/bytetrack.py:132-156,
  * :158-302), STrack (:14-116), joint/sub/remove_duplicate_stracks (:308-346),
