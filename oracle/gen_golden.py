@@ -176,6 +176,48 @@ def main_deepocsort():
         print("deepocsort", name, out.shape, "ids", int(out[:, 5].max()))
 
 
+# (case, stream id, K, frames, emb_dim, warps, crowd, tracker kwargs)
+BOOSTTRACK_CASES = [
+    ("synth_k20_e32", 40, 20, 60, 32, False, False, {}),
+    ("synth_k50_e64_cmc", 41, 50, 60, 64, True, False, {}),
+    ("synth_k40_plain", 42, 40, 60, 16, False, False,
+     {"with_reid": False, "use_rich_s": False, "use_sb": False, "use_vt": False}),
+    ("synth_k60_crowd_v2", 43, 60, 40, 32, False, True, {"s_sim_corr": True, "max_age": 10}),
+    ("synth_k30_noduo", 44, 30, 50, 8, False, False, {"use_ecc": False, "use_duo_boost": False, "use_vt": False}),
+    ("synth_k30_nodlo", 45, 30, 50, 8, False, False, {"use_dlo_boost": False, "min_hits": 1, "det_thresh": 0.4}),
+]
+
+
+def boosttrack_warps(seed, n_frames):
+    """Similarity camera warps (rotation + scale + shift), one 2x3 matrix per frame."""
+    rng = np.random.default_rng(seed)
+    th, sc = rng.normal(0, 0.003, n_frames), 1 + rng.normal(0, 0.005, n_frames)
+    w = np.zeros((n_frames, 2, 3))
+    w[:, 0, 0] = sc * np.cos(th); w[:, 0, 1] = -sc * np.sin(th)
+    w[:, 1, 0] = sc * np.sin(th); w[:, 1, 1] = sc * np.cos(th)
+    w[:, :, 2] = rng.normal(0, 3, (n_frames, 2))
+    return w
+
+
+def main_boosttrack():
+    for name, sid, k, f, e, use_warps, crowd, kw in BOOSTTRACK_CASES:
+        fr, em = make_stream(sid, k, f, emb_dim=e, crowd=crowd)
+        warps = boosttrack_warps(sid, f) if use_warps else None
+        trk = ref_shim.make_tracker("boosttrack", **kw)
+        out = []
+        for i, d in enumerate(fr):
+            if warps is not None:
+                trk.cmc.warps = [warps[i].copy()]
+            r = np.asarray(trk.update(d.copy(), IMG, em[i].copy()), dtype=float)
+            r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+            out.append(np.c_[np.full(len(r), i), r])
+        out = np.vstack(out)
+        extra = {"warps": warps} if warps is not None else {}
+        np.savez_compressed(os.path.join(GOLD, "ref_boosttrack_%s.npz" % name), rows=out, kw=np.array(repr(kw)),
+                            **extra)
+        print("boosttrack", name, out.shape, "ids", int(out[:, 5].max()))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -207,5 +249,7 @@ if __name__ == "__main__":
         main_botsort()
     elif "--deepocsort" in sys.argv:
         main_deepocsort()
+    elif "--boosttrack" in sys.argv:
+        main_boosttrack()
     else:
         main()

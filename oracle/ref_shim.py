@@ -215,4 +215,15 @@ def make_tracker(name, **overrides):
         mod.get_cmc_method = lambda _name: _QueuedCMC
         args.setdefault("per_class", False)
         return mod.DeepOcSort(reid_weights=None, device="cpu", half=False, **args)
+    if name == "boosttrack":
+        import importlib
+        sys.modules.setdefault("boxmot.appearance.reid.auto_backend", types.ModuleType("x")).ReidAutoBackend = _DummyReid
+        cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
+        cmc.get_cmc_method = lambda _name: _QueuedCMC
+        mod = importlib.import_module("boxmot.trackers.boosttrack.boosttrack")
+        mod.ReidAutoBackend = _DummyReid
+        mod.get_cmc_method = lambda _name: _QueuedCMC
+        mod.KalmanBoxTracker.count = 0        # class-level id counter, never reset by the reference (F9)
+        args.setdefault("per_class", False)
+        return mod.BoostTrack(reid_weights=None, device="cpu", half=False, **args)
     raise KeyError(name)

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 from scipy.optimize import linear_sum_assignment
 
-from conftest import (DEEPOCSORT_CASES, DEEPOCSORT_YAML, deepocsort_case, BOTSORT_CASES, BOTSORT_YAML, BYTETRACK_YAML, OCSORT_YAML, ROOT, botsort_case, assert_rows_match, case_frames, golden_rows,
+from conftest import (BOOSTTRACK_CASES, BOOSTTRACK_YAML, boosttrack_case, DEEPOCSORT_CASES, DEEPOCSORT_YAML, deepocsort_case, BOTSORT_CASES, BOTSORT_YAML, BYTETRACK_YAML, OCSORT_YAML, ROOT, botsort_case, assert_rows_match, case_frames, golden_rows,
                       split_by_frame)
 from oracle import lap
 from oracle.ocsort import OcSortOracle
@@ -110,6 +110,19 @@ def test_deepocsort_oracle_matches_reference_golden(case):
     for f, d in enumerate(frames):
         got = ora.update(d, None, embs[f].copy(), warp=None if warps is None else warps[f])
         assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
+
+
+@pytest.mark.parametrize("case", list(BOOSTTRACK_CASES))
+def test_boosttrack_oracle_matches_reference_golden(case):
+    """BoostTrack(++): 8-state filter, DLO / DUO confidence boosts, soft-BIoU / Mahalanobis / shape /
+    embedding cost, camera_update with similarity warps."""
+    from oracle.boosttrack import BoostTrackOracle
+    frames, embs, warps, kw, want = boosttrack_case(case)
+    ora = BoostTrackOracle(**{**BOOSTTRACK_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = ora.update(d, None, embs[f].copy(), warp=None if warps is None else warps[f])
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-9, conf_rtol=1e-12)
 
 
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
