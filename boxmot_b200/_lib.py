@@ -24,6 +24,13 @@ class DeepocsortConfig(ctypes.Structure):
                [(n, c_int) for n in ("embedding_off", "aw_off", "emb_dim")]
 
 
+class BoosttrackConfig(ctypes.Structure):
+    _fields_ = [(n, c_double) for n in ("det_thresh", "iou_threshold", "min_box_area", "aspect_ratio_thresh",
+                                         "lambda_iou", "lambda_mhd", "lambda_shape", "dlo_boost_coef")] + \
+               [(n, c_int) for n in ("max_age", "min_hits", "use_dlo_boost", "use_duo_boost", "s_sim_corr",
+                                      "use_rich_s", "use_sb", "use_vt", "with_reid", "emb_dim")]
+
+
 class BytetrackConfig(ctypes.Structure):
     _fields_ = [(n, c_double) for n in ("min_conf", "track_thresh", "match_thresh")] + \
                [(n, c_int) for n in ("track_buffer", "frame_rate")]
@@ -61,6 +68,18 @@ _SIGS = {
     "bm_deepocsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),
     "bm_deepocsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
+    "bm_boosttrack_create": (c_int, [ctypes.POINTER(BoosttrackConfig), c_int, c_int, c_int,
+                                     ctypes.POINTER(c_void_p)]),
+    "bm_boosttrack_destroy": (c_int, [c_void_p]),
+    "bm_boosttrack_reset": (c_int, [c_void_p, c_void_p]),
+    "bm_boosttrack_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p]),
+    "bm_boosttrack_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
+                                       c_void_p]),
+    "bm_boosttrack_time_kernels": (c_int, [c_void_p, c_int]),
+    "bm_boosttrack_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
+    "bm_boosttrack_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_void_p, c_void_p, c_void_p,
+                                   c_void_p]),
     "bm_bytetrack_create": (c_int, [ctypes.POINTER(BytetrackConfig), c_int, c_int, c_int,
                                     ctypes.POINTER(c_void_p)]),
     "bm_bytetrack_destroy": (c_int, [c_void_p]),

@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libboxmot_b200.so")
-SOURCES = ["capi.cu", "ocsort_step.cu", "bytetrack_step.cu", "unit_kernels.cu"]
+SOURCES = ["capi.cu", "ocsort_step.cu", "bytetrack_step.cu", "boosttrack_step.cu", "unit_kernels.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     # fp64 products and sums must round separately, as numpy's do (see csrc/common.cuh)

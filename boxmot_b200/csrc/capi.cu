@@ -2,6 +2,8 @@
 #include "../../include/boxmot_b200.h"
 #include "ocsort_engine.cuh"
 #include "bytetrack_engine.cuh"
+#include "boosttrack_engine.cuh"
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -40,6 +42,14 @@ struct ByteEngine {      // ByteTrack and BoT-SORT share the state layout and th
     bm::ByteParams pr;
     std::vector<void*> allocs;
     bool bot = false;
+};
+
+struct BoostEngine {
+    bm::BoostState st;
+    bm::BoostParams pr;
+    std::vector<void*> allocs;
+    cudaEvent_t ev[7];
+    bool timing = false, timed = false;
 };
 
 template <typename E, typename T>
@@ -308,6 +318,173 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
             bm::xysrb_expand(pb, h_P + (size_t)p * 49);
         }
         if (h_ids) h_ids[p] = ints[bm::OI_ID * T + slot];
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- BoostTrack
+int bm_boosttrack_create(const bm_boosttrack_config* cfg, int n_streams, int track_cap, int det_cap, void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0)
+        return fail(-1, "bm_boosttrack_create: bad argument");
+    if (track_cap > 1024) return fail(-1, "bm_boosttrack_create: track_cap must be <= 1024");
+    if (cfg->with_reid && cfg->emb_dim <= 0) return fail(-1, "bm_boosttrack_create: with_reid needs emb_dim > 0");
+    if (cfg->max_age < 0) return fail(-1, "bm_boosttrack_create: max_age must be >= 0");
+    BoostEngine* e = new (std::nothrow) BoostEngine();
+    if (!e) return fail(-3, "out of host memory");
+    bm::BoostState& st = e->st;
+    bm::BoostParams& pr = e->pr;
+    st = bm::BoostState{};
+    st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap;
+    pr.det_thresh = cfg->det_thresh; pr.iou_thr = cfg->iou_threshold; pr.min_box_area = cfg->min_box_area;
+    pr.ar_thresh = cfg->aspect_ratio_thresh; pr.l_iou = cfg->lambda_iou; pr.l_mhd = cfg->lambda_mhd;
+    pr.l_shape = cfg->lambda_shape; pr.dlo_coef = cfg->dlo_boost_coef;
+    pr.max_age = cfg->max_age; pr.min_hits = cfg->min_hits; pr.use_dlo = cfg->use_dlo_boost ? 1 : 0;
+    pr.use_duo = cfg->use_duo_boost ? 1 : 0; pr.s_corr = cfg->s_sim_corr ? 1 : 0; pr.rich_s = cfg->use_rich_s ? 1 : 0;
+    pr.use_sb = cfg->use_sb ? 1 : 0; pr.use_vt = cfg->use_vt ? 1 : 0; pr.with_reid = cfg->with_reid ? 1 : 0;
+    pr.E = cfg->with_reid ? cfg->emb_dim : 0;
+    const size_t S = n_streams, T = track_cap, D = det_cap;
+    // KalmanBoxTracker.get_confidence: 0.9 ** k through the host's libm, as Python evaluates it
+    st.npow = (cfg->max_age + 2 > 8 ? cfg->max_age + 2 : 8);
+    std::vector<double> pw(st.npow);
+    for (int k = 0; k < st.npow; k++) pw[k] = std::pow(0.9, (double)k);
+    double* d_pw = nullptr;
+    cudaError_t r = cudaSuccess;
+    if (r == cudaSuccess) r = dev_alloc(e, &d_pw, (size_t)st.npow);
+    if (r == cudaSuccess) r = cudaMemcpy(d_pw, pw.data(), pw.size() * sizeof(double), cudaMemcpyHostToDevice);
+    st.powtab = d_pw;
+    if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::BTX_N * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.confcls, S * 2 * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.ints, S * bm::BTI_COUNT * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.order, S * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.hdr, S * bm::BTH_COUNT);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.n_updates, S);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.tp, S * bm::TP_COUNT * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.dconf, S * D);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.hsel, S * D);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.cost, S * D * T);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.upd, S * 2 * D);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.born, S * D);
+    if (r == cudaSuccess) r = dev_alloc(e, &st.embsim, S * D * T);      // read (as zeros) only with_reid
+    if (pr.with_reid) {
+        if (r == cudaSuccess) r = dev_alloc(e, &st.bornslot, S * D);
+        if (r == cudaSuccess) r = dev_alloc(e, &st.emb, S * T * (size_t)pr.E);
+    }
+    if (r == cudaSuccess) r = bm::boosttrack_configure(st);
+    if (r != cudaSuccess) {
+        for (void* p : e->allocs) cudaFree(p);
+        delete e;
+        return fail(-2, "bm_boosttrack_create", r);
+    }
+    *handle = e;
+    return bm_boosttrack_reset(e, nullptr);
+}
+
+int bm_boosttrack_destroy(void* handle) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e) return 0;
+    if (e->timing) for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
+    for (void* p : e->allocs) cudaFree(p);
+    delete e;
+    return 0;
+}
+
+int bm_boosttrack_reset(void* handle, void* stream) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::BoostState& st = e->st;
+    const size_t S = st.S, T = st.Tcap;
+    BM_CUDA(cudaMemsetAsync(st.hdr, 0, S * bm::BTH_COUNT * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.n_updates, 0, S * sizeof(unsigned long long), s));
+    BM_CUDA(cudaMemsetAsync(st.order, 0, S * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.ints, 0, S * bm::BTI_COUNT * T * sizeof(int), s));
+    BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::BTX_N * T * sizeof(double), s));
+    if (st.emb) BM_CUDA(cudaMemsetAsync(st.emb, 0, S * T * (size_t)e->pr.E * sizeof(float), s));
+    return 0;
+}
+
+int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_boosttrack_step: null argument");
+    if (e->pr.with_reid && !d_embs) return fail(-1, "bm_boosttrack_step: with_reid needs embeddings");
+    BM_CUDA(bm::boosttrack_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
+                                       static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    e->timed = e->timing;
+    return 0;
+}
+
+int bm_boosttrack_time_kernels(void* handle, int enable) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    if (enable && !e->timing) {
+        for (int i = 0; i < 7; i++) BM_CUDA(cudaEventCreate(&e->ev[i]));
+        e->timing = true;
+    } else if (!enable && e->timing) {
+        for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
+        e->timing = e->timed = false;
+    }
+    return 0;
+}
+
+int bm_boosttrack_kernel_times(void* handle, float* ms6) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e || !ms6) return fail(-1, "bm_boosttrack_kernel_times: bad argument");
+    if (!e->timed) return fail(-1, "bm_boosttrack_kernel_times: no timed step");
+    BM_CUDA(cudaEventSynchronize(e->ev[6]));
+    for (int i = 0; i < 6; i++) BM_CUDA(cudaEventElapsedTime(&ms6[i], e->ev[i], e->ev[i + 1]));
+    return 0;
+}
+
+int bm_boosttrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e || !out4) return fail(-1, "bm_boosttrack_counters: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int S = e->st.S;
+    std::vector<int> hdr((size_t)S * bm::BTH_COUNT);
+    std::vector<unsigned long long> nu(S);
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), e->st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(nu.data(), e->st.n_updates, nu.size() * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    int err = 0;
+    out4[0] = out4[1] = out4[2] = out4[3] = 0;
+    for (int i = 0; i < S; i++) {
+        err |= hdr[(size_t)i * bm::BTH_COUNT + bm::BTH_ERR];
+        out4[0] += nu[i];
+        out4[1] += (unsigned long long)hdr[(size_t)i * bm::BTH_COUNT + bm::BTH_LAPS];
+        out4[2] += (unsigned long long)hdr[(size_t)i * bm::BTH_COUNT + bm::BTH_MATCH];
+        out4[3] += (unsigned long long)hdr[(size_t)i * bm::BTH_COUNT + bm::BTH_BIRTHS];
+    }
+    if (err_bits) *err_bits = err;
+    return 0;
+}
+
+int bm_boosttrack_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P, int* h_ids, void* stream) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e || si < 0 || si >= e->st.S) return fail(-1, "bm_boosttrack_peek: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bm::BoostState& st = e->st;
+    const size_t T = st.Tcap;
+    std::vector<double> xp(bm::BTX_N * T);
+    std::vector<int> order(T), ints(bm::BTI_COUNT * T), hdr(bm::BTH_COUNT);
+    BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * bm::BTX_N * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(order.data(), st.order + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::BTI_COUNT * T, ints.size() * 4,
+                            cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaMemcpyAsync(hdr.data(), st.hdr + (size_t)si * bm::BTH_COUNT, hdr.size() * 4, cudaMemcpyDeviceToHost, s));
+    BM_CUDA(cudaStreamSynchronize(s));
+    const int n = hdr[bm::BTH_NLIST];
+    if (n_tracks) *n_tracks = n;
+    for (int p = 0; p < n; p++) {
+        const int slot = order[p];
+        if (h_x) for (int c = 0; c < 8; c++) h_x[p * 8 + c] = xp[c * T + slot];
+        if (h_P) {
+            double pb[16];
+            for (int c = 0; c < 16; c++) pb[c] = xp[(8 + c) * T + slot];
+            bm::bt_expand(pb, h_P + (size_t)p * 64);
+        }
+        if (h_ids) h_ids[p] = ints[bm::BTI_ID * T + slot];
     }
     return 0;
 }

@@ -262,6 +262,118 @@ class DeepOcSortEngine(OcSortEngine):
         ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
         return [ho[s, : hn2[s]].copy() for s in range(self.S)]
 
+class BoostTrackEngine:
+    """S independent BoostTrack(++) trackers (boxmot/trackers/boosttrack/boosttrack.py:154-336) per
+    step: 8-state Kalman filter, DLO / DUO confidence boosts, soft-BIoU / Mahalanobis / shape /
+    embedding score matrix, exact assignment, list bookkeeping -- all on the device.
+
+    ReID and CMC are side inputs: ``embs`` [S, det_cap, emb_dim] float32 row-aligned with ``dets``
+    (required when ``with_reid``), ``warps`` [S, 2, 3] float64 or None (no camera_update)."""
+
+    def __init__(self, n_streams, track_cap=256, det_cap=128, device="cuda:0", max_age=60, min_hits=3,
+                 det_thresh=0.6, iou_threshold=0.3, use_ecc=True, min_box_area=10, aspect_ratio_thresh=1.6,
+                 cmc_method="ecc", lambda_iou=0.5, lambda_mhd=0.25, lambda_shape=0.25, use_dlo_boost=True,
+                 use_duo_boost=True, dlo_boost_coef=0.65, s_sim_corr=False, use_rich_s=False, use_sb=False,
+                 use_vt=False, with_reid=False, emb_dim=512):
+        if not torch.cuda.is_available():
+            raise RuntimeError("BoostTrackEngine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.S, self.Tcap, self.Dcap = int(n_streams), int(track_cap), int(det_cap)
+        self.with_reid, self.use_ecc = bool(with_reid), bool(use_ecc)
+        self.E = int(emb_dim) if self.with_reid else 0
+        cfg = _lib.BoosttrackConfig(det_thresh, iou_threshold, float(min_box_area), float(aspect_ratio_thresh),
+                                    lambda_iou, lambda_mhd, lambda_shape, dlo_boost_coef, int(max_age),
+                                    int(min_hits), int(bool(use_dlo_boost)), int(bool(use_duo_boost)),
+                                    int(bool(s_sim_corr)), int(bool(use_rich_s)), int(bool(use_sb)),
+                                    int(bool(use_vt)), int(self.with_reid), self.E)
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_create(ctypes.byref(cfg), self.S, self.Tcap, self.Dcap,
+                                                       ctypes.byref(self._h)), "bm_boosttrack_create")
+            torch.cuda.synchronize(self.device)
+        self.out_rows = min(self.Tcap, self.Dcap)
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+        self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+        self.launches = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            _lib.lib().bm_boosttrack_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_reset(self._h, _stream_ptr(self.device)), "bm_boosttrack_reset")
+
+    def step(self, dets, ndets, embs=None, warps=None, out=None, nout=None):
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (self.S, self.Dcap, 6)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        if self.with_reid:
+            assert embs is not None and embs.dtype == torch.float32 and embs.is_cuda and embs.is_contiguous()
+            assert tuple(embs.shape) == (self.S, self.Dcap, self.E)
+        if not self.use_ecc:
+            warps = None
+        if warps is not None:
+            assert warps.dtype == torch.float64 and warps.is_cuda and tuple(warps.shape) == (self.S, 2, 3)
+            assert warps.is_contiguous()
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_step(self._h, _ptr(dets), _ptr(ndets),
+                                                     _ptr(embs) if self.with_reid else None,
+                                                     _ptr(warps) if warps is not None else None,
+                                                     _ptr(out), _ptr(nout), _stream_ptr(self.device)),
+                       "bm_boosttrack_step")
+        self.launches += 7 if self.with_reid else 5
+        return out, nout
+
+    def counters(self, raise_on_error=True):
+        err = ctypes.c_int(0)
+        buf = (ctypes.c_ulonglong * 4)()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_counters(self._h, ctypes.byref(err), ctypes.byref(buf),
+                                                         _stream_ptr(self.device)), "bm_boosttrack_counters")
+        if raise_on_error and err.value:
+            raise RuntimeError("BoostTrack engine error: " + "; ".join(m for b, m in ERR_BITS.items() if err.value & b))
+        out = dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
+        out["err"] = err.value
+        return out
+
+    def status(self, raise_on_error=True):
+        return self.counters(raise_on_error)
+
+    def time_kernels(self, enable=True):
+        _lib.check(_lib.lib().bm_boosttrack_time_kernels(self._h, int(bool(enable))), "bm_boosttrack_time_kernels")
+
+    def kernel_times(self):
+        """(predict, boosts, contraction, assoc+update, finalize, embedding EMA) ms of the last timed step."""
+        buf = (ctypes.c_float * 6)()
+        _lib.check(_lib.lib().bm_boosttrack_kernel_times(self._h, ctypes.byref(buf)), "bm_boosttrack_kernel_times")
+        return tuple(float(v) for v in buf)
+
+    def peek(self, stream_index):
+        n = ctypes.c_int(0)
+        x = np.zeros((self.Tcap, 8))
+        P = np.zeros((self.Tcap, 64))
+        ids = np.zeros((self.Tcap,), dtype=np.int32)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_peek(self._h, int(stream_index), ctypes.byref(n), x.ctypes.data,
+                                                     P.ctypes.data, ids.ctypes.data, _stream_ptr(self.device)),
+                       "bm_boosttrack_peek")
+        k = n.value
+        return x[:k], P[:k].reshape(k, 8, 8), ids[:k]
+
+    step_host = DeepOcSortEngine.step_host
+    emb_on = property(lambda self: self.with_reid)
+
 
 class HostPipeline:
     """Double-buffered host <-> device pipeline around ``OcSortEngine.step``: while frame f

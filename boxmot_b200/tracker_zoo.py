@@ -19,6 +19,7 @@ _MAPPING = {
     "bytetrack": ("boxmot_b200.trackers.bytetrack", "ByteTrack"),
     "botsort": ("boxmot_b200.trackers.botsort", "BotSort"),
     "deepocsort": ("boxmot_b200.trackers.deepocsort", "DeepOcSort"),
+    "boosttrack": ("boxmot_b200.trackers.boosttrack", "BoostTrack"),
 }
 _REID_TRACKERS = ("strongsort", "botsort", "deepocsort", "hybridsort", "boosttrack")
 

@@ -86,6 +86,40 @@ int bm_deepocsort_step(void* handle, const float* d_dets, const int* d_ndets, co
 /* Durations (ms) of the six launches of the last step after bm_ocsort_time_kernels(handle, 1):
  * predict(+CMC), embedding contraction, association, Kalman update, finalize, embedding EMA. */
 int bm_deepocsort_kernel_times(void* handle, float* ms6);
+/* ---- BoostTrack engine ------------------------------------------------------------
+ * Replaces BoostTrack.__init__/update (boxmot/trackers/boosttrack/boosttrack.py:154-336), its
+ * KalmanBoxTracker (:45-121) over boosttrack/kalmanfilter.py:29-157, the confidence boosts
+ * (dlo_confidence_boost :414-456, duo_confidence_boost :372-412, get_mh_dist_matrix :356-369),
+ * filter_outputs (:338-346) and boosttrack/assoc.py (shape_similarity :9-34, MhDist_similarity
+ * :37-47, iou_batch :50-66, soft_biou_batch :69-103, match :106-114, linear_assignment :117-153,
+ * associate :156-200).  ReID and CMC are side inputs: detection embeddings and one 2x3 warp per
+ * stream (any affine warp: camera_update :81-103 rebuilds the state from the warped corners). */
+typedef struct bm_boosttrack_config {
+    double det_thresh, iou_threshold, min_box_area, aspect_ratio_thresh;
+    double lambda_iou, lambda_mhd, lambda_shape, dlo_boost_coef;
+    int max_age, min_hits;
+    int use_dlo_boost, use_duo_boost, s_sim_corr, use_rich_s, use_sb, use_vt, with_reid;
+    int emb_dim;
+} bm_boosttrack_config;
+int bm_boosttrack_create(const bm_boosttrack_config* cfg, int n_streams, int track_cap, int det_cap,
+                         void** handle);
+int bm_boosttrack_destroy(void* handle);
+int bm_boosttrack_reset(void* handle, void* stream);
+/* One frame for all streams; arguments as bm_deepocsort_step (d_embs may be NULL without
+ * with_reid, d_warps NULL = no camera_update this frame).  Output rows are in the reference's
+ * order (tracker list order); the reported confidence is the BOOSTED detection confidence. */
+int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* Synchronises `stream`: OR of the per-stream error bits and cumulative {track_updates,
+ * lap_solves, matches, births}. */
+int bm_boosttrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
+/* Per-launch CUDA-event timing of the following steps: predict, boosts, embedding contraction,
+ * association, finalize, embedding EMA (ms). */
+int bm_boosttrack_time_kernels(void* handle, int enable);
+int bm_boosttrack_kernel_times(void* handle, float* ms6);
+/* Test hook: Kalman means [n][8], covariances [n][8][8] and ids of one stream in list order. */
+int bm_boosttrack_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
+                       int* h_ids, void* stream);
 /* ---- ByteTrack engine -------------------------------------------------------------
  * Replaces ByteTrack.__init__/update (boxmot/trackers/bytetrack/bytetrack.py:132-156,
  * :158-302), STrack (:14-116), joint/sub/remove_duplicate_stracks (:308-346),
