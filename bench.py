@@ -32,6 +32,22 @@ BOTSORT_YAML = dict(track_high_thresh=0.6, track_low_thresh=0.1, new_track_thres
                     fuse_first_associate=False, with_reid=True)   # boxmot/configs/trackers/botsort.yaml
 BYTETRACK_YAML = dict(min_conf=0.1, track_thresh=0.6, match_thresh=0.9, track_buffer=30,
                       frame_rate=30)   # boxmot/configs/trackers/bytetrack.yaml defaults
+DEEPOCSORT_YAML = dict(det_thresh=0.5, max_age=30, min_hits=3, iou_threshold=0.3, delta_t=3, asso_func="iou",
+                       inertia=0.2, w_association_emb=0.75, alpha_fixed_emb=0.95, aw_param=0.5, embedding_off=False,
+                       cmc_off=False, aw_off=False, Q_xy_scaling=0.01,
+                       Q_s_scaling=0.0001)   # boxmot/configs/trackers/deepocsort.yaml defaults
+BOOSTTRACK_YAML = dict(max_age=60, min_hits=3, det_thresh=0.6, iou_threshold=0.3, use_ecc=True, min_box_area=10,
+                       aspect_ratio_thresh=1.6, lambda_iou=0.5, lambda_mhd=0.25, lambda_shape=0.25,
+                       use_dlo_boost=True, use_duo_boost=True, dlo_boost_coef=0.65, s_sim_corr=False, use_rich_s=True,
+                       use_sb=True, use_vt=True, with_reid=True)   # boxmot/configs/trackers/boosttrack.yaml defaults
+EMB_TRACKERS = ("botsort", "deepocsort", "boosttrack")
+KERNEL_NAMES = {
+    "ocsort": ("ocs_predict_kernel", "ocs_assoc_kernel", "ocs_update_kernel", "ocs_finalize_kernel"),
+    "deepocsort": ("ocs_predict_kernel<deep>", "cosine_tc_kernel<DeepDot>", "ocs_assoc_kernel<deep>",
+                   "ocs_update_kernel", "ocs_finalize_kernel", "docs_emb_kernel"),
+    "boosttrack": ("bt_predict_kernel", "bt_boost_kernel", "cosine_tc_kernel<BoostDot>",
+                   "bt_assoc_kernel+bt_update_kernel", "bt_finalize_kernel", "bt_emb_kernel"),
+}
 METRIC = "track-updates/sec"
 L2_BYTES = 126 * 1024 * 1024
 
@@ -54,10 +70,12 @@ def parse():
     ap.add_argument("--steps", type=int, default=None, help="default 290 (botsort: 40)")
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack", "botsort"],
+    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack", "botsort", "deepocsort", "boosttrack"],
                     help="ocsort = the headline workload (BASELINE configs[1]); bytetrack = the same "
                          "synthetic streams through the ByteTrack engine (the tracker of configs[0]); "
-                         "botsort = BASELINE configs[2] (200 dets/frame, 512-d embeddings)")
+                         "botsort = BASELINE configs[2] (200 dets/frame, 512-d embeddings); deepocsort / boosttrack = the "
+                         "trackers of configs[4] on the configs[1] streams with 512-d embeddings (their engines keep "
+                         "per-column operands in shared memory: crowd shapes need --track-cap <= 768)")
     ap.add_argument("--emb-dim", type=int, default=512, help="botsort only")
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
     ap.add_argument("--objects", type=int, default=None, help="default 100 (botsort: 200)")
@@ -70,10 +88,11 @@ def parse():
     ap.add_argument("--ref-streams-per-core", type=int, default=1)
     a = ap.parse_args()
     bot = a.tracker == "botsort"
+    emb = a.tracker in EMB_TRACKERS
     for name, dflt, dbot in (("steps", 290, 40), ("objects", 100, 200), ("det_cap", 128, 256), ("track_cap", 256, 512)):
         if getattr(a, name) is None:
-            setattr(a, name, dbot if bot else dflt)
-    if not bot:
+            setattr(a, name, dbot if bot else (40 if (emb and name == "steps") else dflt))
+    if not emb:
         a.emb_dim = 0
     return a
 
@@ -136,6 +155,12 @@ def _cpu_worker(a):
     if tracker == "botsort":
         from oracle.botsort import BotSortOracle
         make = lambda: BotSortOracle(**BOTSORT_YAML)
+    elif tracker == "deepocsort":
+        from oracle.deepocsort import DeepOcSortOracle
+        make = lambda: DeepOcSortOracle(**DEEPOCSORT_YAML)
+    elif tracker == "boosttrack":
+        from oracle.boosttrack import BoostTrackOracle
+        make = lambda: BoostTrackOracle(**BOOSTTRACK_YAML)
     elif tracker == "bytetrack":
         from oracle.bytetrack import ByteTrackOracle
         make = lambda: ByteTrackOracle(**BYTETRACK_YAML)
@@ -146,7 +171,8 @@ def _cpu_worker(a):
     for sid in sids:
         if emb_dim:
             fr, em = make_stream(sid, k, warm + steps, emb_dim=emb_dim)
-            step = lambda f: o.update(fr[f], em[f])
+            step = (lambda f: o.update(fr[f], em[f])) if tracker == "botsort" else \
+                (lambda f: o.update(fr[f], None, em[f]))
         else:
             fr = make_stream(sid, k, warm + steps)
             step = lambda f: o.update(fr[f])
@@ -266,7 +292,9 @@ class ClockSampler(threading.Thread):
 #   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
 NCU_TRAFFIC = {"ocsort": 186.1e6, "bytetrack": 41.1e6}
 TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)",
-                 "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)"}
+                 "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)",
+                 "deepocsort": "DeepOCSORT (deepocsort.yaml, synthetic re-ID embeddings)",
+                 "boosttrack": "BoostTrack++ (boosttrack.yaml, synthetic re-ID embeddings)"}
 
 
 def alg_bytes(track_updates, matches, births, dets_in, rows_out):
@@ -312,21 +340,31 @@ def run_gpu_arm(args):
 
     import torch
     import torch.distributed as dist
-    from boxmot_b200.engine import BotSortEngine, ByteTrackEngine, OcSortEngine
+    from boxmot_b200.engine import BoostTrackEngine, BotSortEngine, ByteTrackEngine, DeepOcSortEngine, OcSortEngine
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     byte = args.tracker in ("bytetrack", "botsort")      # BYTE-family engines: no per-kernel timing API
-    bot = args.tracker == "botsort"
-    if bot:
+    bot = args.tracker in EMB_TRACKERS       # embeddings travel with the detections
+    deep, boost = args.tracker == "deepocsort", args.tracker == "boosttrack"
+    if deep:
+        eng = DeepOcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, emb_dim=args.emb_dim,
+                               **DEEPOCSORT_YAML)
+        byte = False
+    elif boost:
+        eng = BoostTrackEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, emb_dim=args.emb_dim,
+                               **BOOSTTRACK_YAML)
+        byte = False
+    elif bot:
         eng = BotSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, emb_dim=args.emb_dim,
                             **BOTSORT_YAML)
     elif byte:
         eng = ByteTrackEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **BYTETRACK_YAML)
     else:
         eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
-    n_kernels = 3 if bot else 1 if byte else 4
+    n_kernels = 6 if deep else 7 if boost else 3 if bot else 1 if byte else 4
+    knames = KERNEL_NAMES.get(args.tracker)
     d_embs = None
     if bot:                              # device-resident embeddings, uploaded frame by frame (tens of GB)
         d_embs = torch.empty(embs.shape, dtype=torch.float32, device=dev)
@@ -390,7 +428,7 @@ def run_gpu_arm(args):
         for f in range(W):
             step_dev(f)
         eng.time_kernels(True)
-        ksum = np.zeros(4)
+        ksum = np.zeros(len(knames))
         ck0 = eng.counters()
         for i in range(KB):
             if not args.no_flush:
@@ -487,7 +525,8 @@ def run_gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import lap as olap
         olap.build()
-        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), 1 if bot else args.cpu_streams,
+        v, sample = cpu_single_core(args.objects, min(W, 10), min(K, 290), 1 if args.tracker == "botsort" else
+                                    2 if bot else args.cpu_streams,
                                     args.tracker, args.emb_dim)
         cpu = {"value": v, "unit": "track-updates/s", "cores": 1, "kind": "port", "sample": sample}
     if rank == 0:
@@ -506,13 +545,22 @@ def run_gpu_arm(args):
             E = args.emb_dim
             nbytes += 4 * E * dets_in + 4 * E * cnt["track_updates"] + 8 * E * cnt["matches"] \
                 + 8 * cnt["track_updates"] * (dets_in // max(1, K * S))
+            if deep or boost:
+                # the first-round matrix is materialised (column weights / column softmax): fp64 out and in
+                nbytes += 16 * cnt["track_updates"] * (dets_in // max(1, K * S))
         achieved = nbytes / (ms_dev * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": upd_all / (ms_all * 1e-3), "unit": "track-updates/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_all / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": ("BoT-SORT (botsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+            "config": {"workload": ("DeepOCSORT (deepocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                    "512-d re-ID embeddings: tcgen05 embedding contraction + adaptive top-2 weighting + IoU/OCM cost, "
+                                    "lapjv-exact assignment, embedding EMA (tracker of BASELINE configs[4] on the configs[1] streams)" if deep else
+                                    "BoostTrack++ (boosttrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
+                                    "512-d re-ID embeddings: DLO/DUO boosts, soft-BIoU / Mahalanobis / shape / embedding score, "
+                                    "lapjv-exact assignment (tracker of BASELINE configs[4] on the configs[1] streams)" if boost else
+                                    "BoT-SORT (botsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
                                     "512-d re-ID embeddings: cosine-distance contraction + IoU fusion + Kalman XYWH "
                                     "(BASELINE configs[2])" if bot else
                                     "ByteTrack (bytetrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
@@ -531,7 +579,8 @@ def run_gpu_arm(args):
                          (1024, 100, 128, 256) else None,
                          "traffic_source": "ncu dram__bytes_read+write per frame step, cold caches (profiles/r1_launches_*_traffic.csv)",
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
+                         "kernel": "frame step = " + " + ".join(knames) if (deep or boost) else
+                                   "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
                                    "byte_step_kernel" if byte else
                                    "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize",
                          "alg_bytes_per_launch": nbytes / K, "avg_launch_ms": ms_dev / K},
@@ -539,9 +588,14 @@ def run_gpu_arm(args):
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }
-        if ksum is not None:
+        if ksum is not None and not (deep or boost):
             line["roofline"]["per_kernel"] = per_kernel(ksum, KB, kcnt, int(nd[W:W + KB].sum()))
             line["roofline"]["dominant_kernel"] = "ocs_assoc_kernel"
+        elif ksum is not None:
+            tot = float(ksum.sum()) or 1.0
+            line["roofline"]["per_kernel"] = [{"kernel": n, "avg_ms": float(m) / KB, "share": float(m) / tot}
+                                              for n, m in zip(knames, ksum)]
+            line["roofline"]["dominant_kernel"] = knames[int(np.argmax(ksum))]
         if e2e is not None:
             line["e2e"] = {"value": upd_e_all / (ms_e_all * 1e-3), "unit": "track-updates/s",
                            "h2d_bytes_per_step": int(pipe.h2d_bytes), "d2h_bytes_per_step": int(pipe.d2h_bytes),
