@@ -108,6 +108,10 @@ _SIGS = {
     "bm_kf_cv8": (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "bm_kf_cv8_gating": (c_int, [c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
                                  c_void_p]),
+    "bm_nn_cosine_distance": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                      c_void_p]),
+    "bm_min_cost_matching_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
+                                           c_void_p, c_void_p, c_void_p]),
     "bm_cosine_distance": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "bm_xysrb_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysrb_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -120,6 +120,8 @@ struct CosineProblem {
     int E;
     float* out; int out_ld;                                     // out[ra[i] * out_ld + j]
     int raw = 0;                                                // 1: out = <A, B> as it is (na / nb unused)
+                                                                // 2: out[ra[i]] = min_j (1 - clip(cos, -1, 1)): nearest
+                                                                //    neighbour over the B rows (StrongSORT's sample bank)
 };
 
 // grid = (row tiles of 128, problems); the caller provides problem(blockIdx.y).
@@ -154,6 +156,7 @@ cosine_tc_kernel(ProblemFn problem) {
     const uint32_t tmem = *tmem_slot;
     const int rows = min(TC_M, pb.nA - r0);
     uint32_t phase = 0;
+    float nn_min = CUDART_INF_F;                                // raw == 2: running minimum of this thread's columns
     for (int c0 = 0; c0 < pb.nB; c0 += TC_NMAX) {
         const int cols = min(TC_NMAX, pb.nB - c0);
         const int npad = max(16, (cols + 15) & ~15);
@@ -207,8 +210,8 @@ cosine_tc_kernel(ProblemFn problem) {
         const int lq = wid & 3;                                   // TMEM lane quarter this warp may read
         const int r = lq * 32 + lane;
         const bool rin = r < rows;
-        const float na = (rin && !pb.raw) ? pb.na[r0 + r] : 1.f;
-        float* orow = rin ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
+        const float na = (rin && pb.raw != 1) ? pb.na[r0 + r] : 1.f;
+        float* orow = (rin && pb.raw != 2) ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
         for (int cb = 16 * (wid >> 2); cb < npad; cb += 16 * (TC_NT / 128)) {
             uint32_t v[16];
             const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)cb;
@@ -223,8 +226,9 @@ cosine_tc_kernel(ProblemFn problem) {
                 for (int j = 0; j < 16; j++) {
                     const int c = cb + j;
                     if (c < cols) {
-                        if (pb.raw) { orow[c] = __uint_as_float(v[j]); continue; }
+                        if (pb.raw == 1) { orow[c] = __uint_as_float(v[j]); continue; }
                         const double cs = (double)__uint_as_float(v[j]) / ((double)na * (double)pb.nb[c0 + c]);
+                        if (pb.raw == 2) { nn_min = fminf(nn_min, (float)(1.0 - fmin(1.0, fmax(-1.0, cs)))); continue; }
                         orow[c] = (float)fmax(0.0, 1.0 - cs);
                     }
                 }
@@ -232,6 +236,14 @@ cosine_tc_kernel(ProblemFn problem) {
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();       // every warp has drained its accumulator rows before the next column tile
+    }
+    if (pb.raw == 2) {
+        // the two warp groups (column-block parity) hold partial minima of the same rows
+        float* part = reinterpret_cast<float*>(a_hi);           // staging buffers are idle now
+        part[(wid >> 2) * TC_M + (wid & 3) * 32 + lane] = nn_min;
+        __syncthreads();
+        const int r = (wid & 3) * 32 + lane;
+        if (wid < 4 && r < rows) pb.out[pb.ra[r0 + r]] = fminf(part[r], part[TC_M + r]);
     }
     if (wid == 0) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(TC_TMEM_COLS) : "memory");

@@ -5,6 +5,7 @@
 #include "kf_xysr.cuh"
 #include "kf_xyah.cuh"
 #include "cosine_tc.cuh"
+#include <algorithm>
 #include "lapjv.cuh"
 #include "lap_rect.cuh"
 #include <cstdio>
@@ -175,6 +176,88 @@ struct UnitCosine {
     __device__ CosineProblem operator()(int) const { return p; }
 };
 
+// ---- StrongSORT appearance metric (strongsort/sort/linear_assignment.py:382-413, :468-497,
+// :595-618): cost[t][d] = min over the track's stored samples of 1 - clip(<f / (|f| + 1e-8),
+// g / (|g| + 1e-8)>, -1, 1); INFTY_COST = 1e5 for a track without samples.
+__global__ void nn_prep_kernel(const float* bank, const int* nb, int T, int Bcap, const float* feats, int D, int E,
+                               int* idx, float* norms, float* out) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int nbank = T * Bcap;
+    if (w < nbank + D) {
+        bool live = true;
+        if (w < nbank) live = (w % Bcap) < nb[w / Bcap];
+        if (live) {
+            const float* src = w < nbank ? bank + (size_t)w * E : feats + (size_t)(w - nbank) * E;
+            float ss = 0.f;
+            for (int e = lane; e < E; e += 32) ss += src[e] * src[e];
+            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(BM_FULL, ss, o);
+            if (lane == 0) norms[w] = sqrtf(ss) + 1e-8f;
+        }
+    }
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nidx = Bcap > D ? Bcap : D;
+    if (g < nidx) idx[g] = g;
+    if (g < T * D && nb[g / D] <= 0) out[g] = 1e5f;
+}
+
+struct NnCosine {
+    const float *bank, *feats, *norms;
+    const int *nb, *idx;
+    int T, Bcap, D, E;
+    float* out;
+    __device__ CosineProblem operator()(int t) const {
+        CosineProblem p;
+        p.A = feats; p.ra = idx; p.na = norms + (size_t)T * Bcap; p.nA = D;
+        p.B = bank + (size_t)t * Bcap * E; p.rb = idx; p.nb = norms + (size_t)t * Bcap; p.nB = nb[t];
+        p.E = E; p.out = out + (size_t)t * D; p.out_ld = 0; p.raw = 2;
+        return p;
+    }
+};
+
+// ---- StrongSORT min_cost_matching (strongsort/sort/linear_assignment.py:14-87) on a given cost
+// matrix: entries > max_distance become max_distance + 1e-5 (:67), rectangular linear sum
+// assignment (:70, scipy), pairs whose cost is still > max_distance are rejected (:82).
+struct ClampCost {
+    static constexpr bool kBounded = false, kStaged = false;
+    const double* c; int ld; double maxd; int transposed;
+    __device__ __forceinline__ double operator()(int i, int j) const {
+        const double v = transposed ? c[(size_t)j * ld + i] : c[(size_t)i * ld + j];
+        return v > maxd ? maxd + 1e-5 : v;
+    }
+    __device__ __forceinline__ double lower(int i, int j, bool* exact) const { *exact = true; return (*this)(i, j); }
+};
+
+__global__ void __launch_bounds__(LAP_WPB * 32)
+min_cost_matching_kernel(const double* __restrict__ cost, int n_problems, int nr_max, int nc_max,
+                         const int* __restrict__ nr_, const int* __restrict__ nc_, double max_distance,
+                         int* __restrict__ x_out, int* __restrict__ y_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int wid = warp_id(), lane = lane_id();
+    const int b = blockIdx.x * LAP_WPB + wid;
+    if (b >= n_problems) return;
+    const int nr = nr_[b], nc = nc_[b];
+    int* x = x_out + (size_t)b * nr_max;
+    int* y = y_out + (size_t)b * nc_max;
+    for (int i = lane; i < nr_max; i += 32) x[i] = -1;
+    for (int j = lane; j < nc_max; j += 32) y[j] = -1;
+    if (nr <= 0 || nc <= 0) return;
+    __syncwarp();
+    const double* c = cost + (size_t)b * nr_max * nc_max;
+    const size_t wbytes = (rect_work_bytes(nr_max > nc_max ? nr_max : nc_max, nr_max > nc_max ? nr_max : nc_max) + 15) / 16 * 16;
+    const bool tr = nr > nc;                 // every row of the smaller side is assigned
+    const int n1 = tr ? nc : nr, n2 = tr ? nr : nc;
+    RectWork rw = rect_carve(smem_raw + (size_t)wid * wbytes, n1, n2);
+    const ClampCost cc = {c, nc_max, max_distance, tr ? 1 : 0};
+    rect_solve_warp(cc, n1, n2, CUDART_INF, rw, nullptr, nullptr);
+    for (int i = lane; i < n1; i += 32) {
+        const int j = rw.x[i];
+        if (j < 0 || cc(i, j) > max_distance) continue;
+        const int row = tr ? j : i, col = tr ? i : j;
+        x[row] = col;
+        y[col] = row;
+    }
+}
+
 // reference form: one thread per output, fp32 FFMA dot product
 __global__ void cosine_ffma_kernel(CosineProblem p) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -291,6 +374,44 @@ int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_
                                                                             only_position, gaussian, d_out);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("cv8_gating_kernel", e);
+}
+
+int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, int bank_cap, const float* d_feats,
+                           int n_feats, int emb_dim, float* d_out, void* d_work, void* stream) {
+    if (n_tracks <= 0 || n_feats <= 0) return 0;
+    if (!d_bank || !d_nb || !d_feats || !d_out || !d_work || bank_cap <= 0 || emb_dim <= 0) return -1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nidx = bank_cap > n_feats ? bank_cap : n_feats;
+    int* idx = static_cast<int*>(d_work);
+    float* norms = reinterpret_cast<float*>(idx + nidx);
+    const long long warps = (long long)n_tracks * bank_cap + n_feats;
+    const long long thr = std::max<long long>(warps * 32, std::max<long long>((long long)n_tracks * n_feats, nidx));
+    bm::nn_prep_kernel<<<(unsigned)((thr + 127) / 128), 128, 0, st>>>(d_bank, d_nb, n_tracks, bank_cap, d_feats, n_feats,
+                                                                     emb_dim, idx, norms, d_out);
+    cudaError_t e = cudaFuncSetAttribute(bm::cosine_tc_kernel<bm::NnCosine>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)bm::cosine_tc_smem_bytes());
+    if (e != cudaSuccess) return unit_fail("cosine_tc_kernel<NnCosine> attribute", e);
+    bm::NnCosine fn = {d_bank, d_feats, norms, d_nb, idx, n_tracks, bank_cap, n_feats, emb_dim, d_out};
+    bm::cosine_tc_kernel<bm::NnCosine><<<dim3((n_feats + bm::TC_M - 1) / bm::TC_M, n_tracks), bm::TC_NT,
+                                         bm::cosine_tc_smem_bytes(), st>>>(fn);
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("nn cosine kernel", e);
+}
+
+int bm_min_cost_matching_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                               const int* d_nc, double max_distance, int* d_x, int* d_y, void* stream) {
+    if (n_problems <= 0) return 0;
+    if (!d_cost || !d_nr || !d_nc || !d_x || !d_y || nr_max <= 0 || nc_max <= 0) return -1;
+    const int nm = nr_max > nc_max ? nr_max : nc_max;
+    const size_t wbytes = (bm::rect_work_bytes(nm, nm) + 15) / 16 * 16;
+    const size_t smem = wbytes * bm::LAP_WPB;
+    cudaError_t e = cudaFuncSetAttribute(bm::min_cost_matching_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return unit_fail("min_cost_matching smem", e);
+    const int grid = (n_problems + bm::LAP_WPB - 1) / bm::LAP_WPB;
+    bm::min_cost_matching_kernel<<<grid, bm::LAP_WPB * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, max_distance, d_x, d_y);
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("min_cost_matching_kernel", e);
 }
 
 int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out, void* d_work,

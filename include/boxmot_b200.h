@@ -238,6 +238,25 @@ int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z
 int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_tracks, const double* d_meas,
                      int n_meas, int only_position, int gaussian, double* d_out, void* stream);
 
+/* StrongSORT's appearance metric NearestNeighborDistanceMetric.distance with the cosine metric
+ * (boxmot/trackers/strongsort/sort/linear_assignment.py:595-618, _nn_cosine_distance :468-497,
+ * _cosine_distance :382-413): d_out [n_tracks][n_feats] float32 = min over the track's stored
+ * samples of 1 - clip(<f / (|f| + 1e-8), g / (|g| + 1e-8)>, -1, 1), or 1e5 (INFTY_COST, :11) for
+ * a track without samples.  d_bank [n_tracks][bank_cap][emb_dim] float32 with d_nb [n_tracks]
+ * live samples each; d_feats [n_feats][emb_dim].  One tcgen05 contraction per track (3xTF32)
+ * with the minimum taken in the epilogue.  d_work: caller-owned scratch of at least
+ * 4 * (max(bank_cap, n_feats) + n_tracks * bank_cap + n_feats) bytes. */
+int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, int bank_cap, const float* d_feats,
+                          int n_feats, int emb_dim, float* d_out, void* d_work, void* stream);
+
+/* StrongSORT's min_cost_matching on given cost matrices (strongsort/sort/linear_assignment.py:
+ * 14-87): entries > max_distance are set to max_distance + 1e-5 (:67), scipy's rectangular
+ * linear_sum_assignment (:70) is replaced by the exact rectangular solver, and assigned pairs
+ * whose cost is > max_distance are rejected (:82).  Arguments as bm_lap_rect_batch; d_x / d_y
+ * hold the accepted pairs (-1 = unmatched). */
+int bm_min_cost_matching_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                               const int* d_nc, double max_distance, int* d_x, int* d_y, void* stream);
+
 /* embedding_distance (boxmot/utils/matching.py:230-321 with its defaults): d_out [na][nb] =
  * max(0, 1 - <a_i, b_j> / (|a_i| |b_j|)) for float32 feature rows d_a [na][emb_dim],
  * d_b [nb][emb_dim].  mode 0 = tcgen05 tensor-core contraction (3xTF32, fp32 accumulation in

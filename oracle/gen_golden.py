@@ -218,6 +218,50 @@ def main_boosttrack():
         print("boosttrack", name, out.shape, "ids", int(out[:, 5].max()))
 
 
+def main_strongsort_units():
+    """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
+    reference's own functions (rows a18 / a21)."""
+    ref_shim.load()
+    from boxmot.trackers.strongsort.sort import linear_assignment as la
+    rng = np.random.default_rng(21)
+    T, D, E, B = 12, 37, 96, 20
+    metric = la.NearestNeighborDistanceMetric("cosine", 0.2, None)
+    nb = rng.integers(0, B + 1, T)
+    nb[3] = 0
+    bank = (rng.normal(0, 1, (T, B, E)) * rng.uniform(0.5, 2, (T, B, 1))).astype(np.float32)
+    feats = rng.normal(0, 1, (D, E)).astype(np.float32)
+    # a few near-duplicates so that the minimum is small somewhere
+    for t in range(T):
+        if nb[t]:
+            feats[t] = bank[t, rng.integers(0, nb[t])] * 1.7 + rng.normal(0, 0.05, E)
+    for t in range(T):
+        if nb[t]:
+            metric.samples[t] = [bank[t, i] for i in range(nb[t])]
+    nn = metric.distance(feats, list(range(T)))
+
+    class _T:       # neutral attributes: _enhance_cost_matrix multiplies by exactly 1.0
+        quality_score = 0.5
+        conf = 0.5
+
+    class _D:
+        quality_score = 0.5
+        conf = 0.5
+
+    P, N = 48, 30
+    costs = np.zeros((P, N, N))
+    nrs, ncs = rng.integers(1, N + 1, P), rng.integers(1, N + 1, P)
+    xs = -np.ones((P, N), dtype=np.int64)
+    for p in range(P):
+        c = rng.random((nrs[p], ncs[p]))
+        costs[p, : nrs[p], : ncs[p]] = c
+        m, _, _ = la.min_cost_matching(lambda tr, de, ti, di, c=c: c.copy(), 0.5, [_T()] * nrs[p], [_D()] * ncs[p])
+        for r, cc in m:
+            xs[p, r] = cc
+    np.savez_compressed(os.path.join(GOLD, "ref_strongsort_units.npz"), bank=bank, nb=nb, feats=feats, nn=nn,
+                        costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5))
+    print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -251,5 +295,7 @@ if __name__ == "__main__":
         main_deepocsort()
     elif "--boosttrack" in sys.argv:
         main_boosttrack()
+    elif "--strongsort-units" in sys.argv:
+        main_strongsort_units()
     else:
         main()

@@ -298,3 +298,79 @@ def test_cosine_distance_matches_scipy(shape, mode):
     err = np.abs(got - want).max()
     print("cosine mode %d shape %s max abs err %.3g" % (mode, shape, err))
     np.testing.assert_allclose(got, want, rtol=0, atol=2e-6 if mode else 2e-5)
+
+
+def test_strongsort_nn_cosine_distance_matches_reference_vectors():
+    """bm_nn_cosine_distance (tcgen05 contraction per track, minimum over the sample bank in the
+    epilogue) against NearestNeighborDistanceMetric.distance of the reference (row a21)."""
+    import ctypes, os
+    from conftest import GOLD
+    from boxmot_b200 import _lib
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    bank, nb, feats = z["bank"], z["nb"].astype(np.int32), z["feats"]
+    T, B, E = bank.shape
+    D = feats.shape[0]
+
+    def run(bank, nb, feats):
+        T, B, E = bank.shape
+        D = feats.shape[0]
+        d_bank, d_nb, d_f = torch.as_tensor(bank).cuda(), torch.as_tensor(nb).cuda(), torch.as_tensor(feats).cuda()
+        d_out = torch.full((T, D), -7.0, dtype=torch.float32, device="cuda")
+        d_work = torch.zeros((max(B, D) + T * B + D + 16,), dtype=torch.int32, device="cuda")
+        rc = _lib.lib().bm_nn_cosine_distance(d_bank.data_ptr(), d_nb.data_ptr(), T, B, d_f.data_ptr(), D, E,
+                                              d_out.data_ptr(), d_work.data_ptr(), None)
+        assert rc == 0
+        torch.cuda.synchronize()
+        return d_out.cpu().numpy().astype(np.float64)
+
+    np.testing.assert_allclose(run(bank, nb, feats), z["nn"], rtol=0, atol=2e-6)
+    # larger shapes than the fixture (several row tiles, a bank wider than one column tile, E = 768)
+    rng = np.random.default_rng(3)
+    T2, B2, E2, D2 = 9, 300, 768, 150
+    bank2 = rng.normal(0, 1, (T2, B2, E2)).astype(np.float32)
+    nb2 = rng.integers(0, B2 + 1, T2).astype(np.int32)
+    nb2[0], nb2[1] = 0, B2
+    feats2 = rng.normal(0, 1, (D2, E2)).astype(np.float32)
+    want = so.nn_cosine_distance([bank2[t, : nb2[t]].astype(np.float64) for t in range(T2)], feats2.astype(np.float64))
+    np.testing.assert_allclose(run(bank2, nb2, feats2), want, rtol=0, atol=3e-6)
+
+
+def test_strongsort_min_cost_matching_matches_reference_vectors():
+    """bm_min_cost_matching_batch against the reference's min_cost_matching (row a18) on the
+    fixture's 48 problems, and against the scipy-based oracle on larger random ones."""
+    import os
+    from conftest import GOLD
+    from boxmot_b200 import _lib
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+
+    def run(costs, nrs, ncs, maxd):
+        P, NR, NC = costs.shape
+        d_c = torch.as_tensor(np.ascontiguousarray(costs)).cuda()
+        d_nr, d_nc = torch.as_tensor(nrs.astype(np.int32)).cuda(), torch.as_tensor(ncs.astype(np.int32)).cuda()
+        d_x = torch.zeros((P, NR), dtype=torch.int32, device="cuda")
+        d_y = torch.zeros((P, NC), dtype=torch.int32, device="cuda")
+        rc = _lib.lib().bm_min_cost_matching_batch(d_c.data_ptr(), P, NR, NC, d_nr.data_ptr(), d_nc.data_ptr(),
+                                                   float(maxd), d_x.data_ptr(), d_y.data_ptr(), None)
+        assert rc == 0
+        torch.cuda.synchronize()
+        return d_x.cpu().numpy(), d_y.cpu().numpy()
+
+    x, y = run(z["costs"], z["nrs"], z["ncs"], float(z["max_distance"]))
+    assert np.array_equal(x, z["xs"])
+    for p in range(len(x)):
+        for r, c in enumerate(x[p]):
+            if c >= 0:
+                assert y[p, c] == r
+    rng = np.random.default_rng(8)
+    P, NR, NC = 64, 120, 90
+    costs = rng.random((P, NR, NC))
+    nrs, ncs = rng.integers(0, NR + 1, P), rng.integers(0, NC + 1, P)
+    x, _ = run(costs, nrs, ncs, 0.2)
+    for p in range(P):
+        m, _, _ = so.min_cost_matching(costs[p, : nrs[p], : ncs[p]], 0.2)
+        want = -np.ones(NR, dtype=np.int64)
+        for r, c in m:
+            want[r] = c
+        assert np.array_equal(x[p], want), p

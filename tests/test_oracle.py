@@ -125,6 +125,24 @@ def test_boosttrack_oracle_matches_reference_golden(case):
         assert_rows_match(got, want_f[f], f, box_rtol=1e-9, conf_rtol=1e-12)
 
 
+def test_strongsort_unit_oracle_matches_reference_vectors():
+    """oracle/strongsort.py against vectors produced by the reference's own
+    NearestNeighborDistanceMetric.distance and min_cost_matching."""
+    from conftest import GOLD
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    banks = [z["bank"][t, : z["nb"][t]] for t in range(len(z["nb"]))]
+    np.testing.assert_allclose(so.nn_cosine_distance(banks, z["feats"]), z["nn"], rtol=0, atol=2e-6)
+    for p in range(len(z["nrs"])):
+        nr, nc = int(z["nrs"][p]), int(z["ncs"][p])
+        m, um_r, um_c = so.min_cost_matching(z["costs"][p, :nr, :nc], float(z["max_distance"]))
+        x = -np.ones(z["xs"].shape[1], dtype=np.int64)
+        for r, c in m:
+            x[r] = c
+        assert np.array_equal(x, z["xs"][p])
+        assert sorted(um_r) == [r for r in range(nr) if x[r] < 0]
+
+
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
 def test_cv8_kalman_oracle_matches_reference_vectors(kind):
     """oracle/kalman.py cv8_* against known-answer vectors generated from the reference's
