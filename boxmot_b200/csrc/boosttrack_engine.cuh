@@ -19,6 +19,8 @@ enum { BTH_NLIST = 0, BTH_NEXT_ID, BTH_FRAME, BTH_ERR, BTH_LAPS, BTH_MATCH, BTH_
 // per-list-position operands written by the predict kernel
 enum { TP_X1 = 0, TP_Y1, TP_X2, TP_Y2, TP_CONF, TP_Z0, TP_Z1, TP_Z2, TP_Z3, TP_S0, TP_S1, TP_S2, TP_S3, TP_AGE1, TP_COUNT };
 constexpr int BTX_N = 24;            // doubles of Kalman state per track: x[8] + 4 blocks {P[b][b], P[b][b+4], P[b+4][b], P[b+4][b+4]}
+constexpr int BT_CL = 32;            // listed (not screened-out) rows per column before a column is evaluated in full
+__host__ __device__ inline size_t bt_list_doubles(int Tcap) { return (size_t)Tcap * BT_CL + ((size_t)Tcap * BT_CL + 3) / 4; }
 constexpr double BT_MH_LIMIT = 13.2767;   // assoc.py:38, boosttrack.py:377
 
 struct BoostParams {
@@ -37,7 +39,8 @@ struct BoostState {
     double* tp;          // [S][TP_COUNT][Tcap] predicted boxes / confidence / Mahalanobis operands by list position
     double* dconf;       // [S][Dcap]  detection confidence after the DLO / DUO boosts
     int* hsel;           // [S][Dcap]  detection rows with boosted conf >= det_thresh, ascending
-    double* cost;        // [S][Dcap*Tcap] association score matrix (L2-resident)
+    double* cost;        // [S][cost_stride] association score matrix (L2-resident); also the column lists' scratch
+    size_t cost_stride;  // doubles per stream: max(Dcap*Tcap, column-list scratch)
     int* upd;            // [S][2][Dcap] (slot, detection row) of the frame's matches
     int* born;           // [S][Dcap]  detection rows that start a track, in id order
     int* bornslot;       // [S][Dcap]

@@ -104,6 +104,8 @@ struct BtSmem {
     int *colcnt, *t2d, *slot_of;                            // [Tcap]
     int* misc;           // [16]
     void* work;          // solver work area
+    float* tf;           // [3][Tcap] fp32 screening table (centre x, reach for the boost pass, reach otherwise)
+    unsigned short* cand;   // [BT_NW][Tcap] per-warp list of the columns that passed the screen
 };
 
 __host__ __device__ inline size_t bt_work_bytes(int Tcap, int Dcap) {
@@ -112,7 +114,7 @@ __host__ __device__ inline size_t bt_work_bytes(int Tcap, int Dcap) {
 }
 __host__ __device__ inline size_t bt_smem_bytes(int Tcap, int Dcap) {
     const size_t t = Tcap, d = Dcap;
-    return 8 * (TP_COUNT * t + t + 4 * d + 3 * d) + 16 * d + 4 * (7 * d + 3 * t + 16) + bt_work_bytes(Tcap, Dcap) + 32;
+    return 8 * (TP_COUNT * t + t + 4 * d + 3 * d) + 16 * d + 4 * (7 * d + 3 * t + 16) + 12 * t + 2 * (BT_NT / 32) * t + bt_work_bytes(Tcap, Dcap) + 32;
 }
 __device__ inline BtSmem bt_carve(unsigned char* base, int Tcap, int Dcap) {
     BtSmem m;
@@ -129,7 +131,9 @@ __device__ inline BtSmem bt_carve(unsigned char* base, int Tcap, int Dcap) {
     m.di = k; k += Dcap; m.flag = k; k += Dcap; m.rarg = k; k += Dcap; m.rowcnt = k; k += Dcap;
     m.hit_t = k; k += Dcap; m.d2t = k; k += Dcap; m.um_d = k; k += Dcap;
     m.colcnt = k; k += Tcap; m.t2d = k; k += Tcap; m.slot_of = k; k += Tcap;
-    m.misc = k;
+    m.misc = k; k += 16;
+    m.tf = reinterpret_cast<float*>(k);
+    m.cand = reinterpret_cast<unsigned short*>(m.tf + 3 * (size_t)Tcap);
     return m;
 }
 
@@ -166,7 +170,19 @@ __device__ __forceinline__ double bt_soft_biou(const Box& a, const Box& b, doubl
     const double w = fmax(0.0, fmin(ax2, bx2) - fmax(ax1, bx1));
     const double h = fmax(0.0, fmin(ay2, by2) - fmax(ay1, by1));
     const double wh = w * h;
-    return wh / ((ax2 - ax1) * (ay2 - ay1) + (bx2 - bx1) * (by2 - by1) - wh);
+    const double den = (ax2 - ax1) * (ay2 - ay1) + (bx2 - bx1) * (by2 - by1) - wh;
+    if (wh == 0.0 && den > 0.0) return 0.0;          // 0 / den, without the division
+    return wh / den;
+}
+
+// iou_batch (assoc.py:50-66) with the same shortcut for disjoint boxes
+__device__ __forceinline__ double bt_iou(const Box& a, const Box& b) {
+    const double w = fmax(0.0, fmin(a.x2, b.x2) - fmax(a.x1, b.x1));
+    const double h = fmax(0.0, fmin(a.y2, b.y2) - fmax(a.y1, b.y1));
+    const double wh = w * h;
+    const double den = (a.x2 - a.x1) * (a.y2 - a.y1) + (b.x2 - b.x1) * (b.y2 - b.y1) - wh;
+    if (wh == 0.0 && den > 0.0) return 0.0;
+    return wh / den;
 }
 
 // x^1.5 as x * sqrt(x) carried in double-double, i.e. correctly rounded except in rare
@@ -180,6 +196,37 @@ __device__ __forceinline__ double bt_pow15(double x) {
     return hi + lo;
 }
 
+// ---------------------------------------------------------------------------------------
+// fp32 screening.  Most detection x track pairs are far apart IN X: their boxes (even after
+// soft-BIoU's growth) are disjoint and their Mahalanobis distance is beyond the 13.2767 limit
+// (mh >= dx^2 / P00), so every term of the reference's matrices is a STRUCTURAL value for them
+// (IoU = soft-BIoU = 0 exactly, Mahalanobis similarity = 0, exp(limit - min(mh, limit)) = 1).
+// One float compare per pair -- |cx_d - cx_t| > reach_t + reach_d, with margins far above the fp32
+// rounding error -- decides which pairs are surely in that state; everything else is evaluated
+// exactly in fp64.  Degenerate / non-finite boxes are never screened out (reach = +inf).
+//   tf[0][t] = centre x, tf[1][t] = max(2 half-widths, Mahalanobis radius)   (boost pass: the track
+//   box grows by <= 0.5 of its width per side), tf[2][t] = max(half-width, Mahalanobis radius).
+enum { TF_CX = 0, TF_RB, TF_RA, TF_COUNT };
+__device__ inline void bt_stage_floats(const BtSmem& sm, int T, int nT) {
+    for (int t = threadIdx.x; t < nT; t += BT_NT) {
+        const double x1 = sm.tcol[TP_X1 * T + t], x2 = sm.tcol[TP_X2 * T + t], s0 = sm.tcol[TP_S0 * T + t];
+        const double hgt = sm.tcol[TP_Y2 * T + t] - sm.tcol[TP_Y1 * T + t];
+        const bool ok = x2 > x1 && (x2 - x1) < 1e30 && s0 > 0 && s0 < 1e30 && fabs(x1) < 1e30 && hgt > 0 && hgt < 1e30;
+        const float hw = (float)((x2 - x1) * 0.5) * 1.0001f;
+        const float rmh = sqrtf((float)BT_MH_LIMIT * 1.02f / ((float)s0 * 0.999f)) * 1.001f + 0.5f;
+        sm.tf[TF_CX * T + t] = (float)((x1 + x2) * 0.5);
+        sm.tf[TF_RB * T + t] = ok ? fmaxf(2.f * hw, rmh) : CUDART_INF_F;
+        sm.tf[TF_RA * T + t] = ok ? fmaxf(hw, rmh) : CUDART_INF_F;
+    }
+}
+// far in x: grow = 1.5 for the boost pass (the detection grows by <= 0.25 of its width per side), 1 otherwise
+__device__ __forceinline__ bool bt_far_x(const float4 det, float grow, const float* tf, int which, int T, int t) {
+    const float dcx = 0.5f * (det.x + det.z), dhw = 0.5f * (det.z - det.x) * 1.0001f;
+    const float cx = tf[TF_CX * T + t];
+    const float margin = 0.05f + 1e-5f * (fabsf(dcx) + fabsf(cx));
+    return dhw > 0.f && det.w > det.y && fabsf(dcx - cx) > tf[which * T + t] + grow * dhw + margin;   // false for NaN / inf operands
+}
+
 // Stage the per-column operands of the nT listed tracks (and MhDist_similarity's column sums
 // over the detections listed in sm.dz[0..n)) into shared memory.
 __device__ inline void bt_stage_columns(const BoostState& st, int s, const BtSmem& sm, int nT) {
@@ -190,13 +237,17 @@ __device__ inline void bt_stage_columns(const BoostState& st, int s, const BtSme
         sm.tcol[f * T + t] = tp[f * T + t];
     }
 }
-__device__ inline void bt_column_sums(const BtSmem& sm, int T, int n, int nT) {
-    // np.exp(limit - min(mh, limit)).sum(0): rows are added in order
+// np.exp(limit - min(mh, limit)).sum(0) per column: a thread owns a column and adds the rows in order
+// (1.0 for a screened-out or masked pair: exp(0) == 1 exactly).
+__device__ inline void bt_column_sums(const BtSmem& sm, int T, int n, int nT, double* /*scratch*/) {
     for (int t = threadIdx.x; t < nT; t += BT_NT) {
         double acc = 0.0;
         for (int d = 0; d < n; d++) {
-            const double mh = bt_mh(sm.dz + 4 * d, sm.tcol, T, t);
-            const double e = exp(BT_MH_LIMIT - (mh > BT_MH_LIMIT ? BT_MH_LIMIT : mh));
+            double e = 1.0;
+            if (!bt_far_x(sm.dbox[d], 1.f, sm.tf, TF_RA, T, t)) {
+                const double mh = bt_mh(sm.dz + 4 * d, sm.tcol, T, t);
+                if (!(mh > BT_MH_LIMIT)) e = exp(BT_MH_LIMIT - mh);
+            }
             acc = d == 0 ? e : acc + e;
         }
         sm.colsum[t] = acc;
@@ -231,36 +282,66 @@ bt_boost_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets, c
     }
     bt_stage_columns(st, s, sm, nT);
     __syncthreads();
+    bt_stage_floats(sm, T, nT);
+    __syncthreads();
     const bool boosts = nT > 0 && nD > 0 && (pr.use_dlo || pr.use_duo);
     if (boosts) {
         const bool rich = pr.use_dlo && pr.rich_s;
-        if (rich) { bt_column_sums(sm, T, nD, nT); __syncthreads(); }
+        if (rich) { bt_column_sums(sm, T, nD, nT, st.cost + (size_t)s * st.cost_stride); __syncthreads(); }
         for (int d = wid; d < nD; d += BT_NW) {
             const float4 bf = sm.dbox[d];
             const Box a = {(double)bf.x, (double)bf.y, (double)bf.z, (double)bf.w};
             double mx = -CUDART_INF, mn = CUDART_INF;
-            int hit = 0;
-            for (int t = lane; t < nT; t += 32) {
+            int hit = 0, deferred = 0;
+            // Phase 1 evaluates the pairs that can reach a large S; a pair that is masked by the
+            // Mahalanobis limit AND has disjoint grown boxes has S = shape / 3 <= 1/3 exactly (shape
+            // similarity is exp of a non-positive number) and cannot pass the use_vt test (>= 0.8):
+            // its exp is only evaluated (phase 2) when the row maximum is still below 1/3.
+            unsigned short* cand = sm.cand + (size_t)wid * T;
+            int nc = 0;
+            for (int base = 0; base < nT; base += 32) {
+                const int t = base + lane;
+                const bool near = t < nT && !bt_far_x(bf, 1.5f, sm.tf, TF_RB, T, t);
+                if (t < nT && !near) deferred = 1;
+                const unsigned bal = __ballot_sync(BM_FULL, near);
+                if (near) cand[nc + __popc(bal & ((1u << lane) - 1))] = (unsigned short)t;
+                nc += __popc(bal);
+            }
+            __syncwarp();
+            for (int i = lane; i < nc; i += 32) {
+                const int t = cand[i];
                 const double mh = bt_mh(sm.dz + 4 * d, sm.tcol, T, t);
                 mn = fmin(mn, mh);
                 if (!pr.use_dlo) continue;
                 const Box b = bt_trk_box(sm.tcol, T, t);
                 double S;
                 if (rich) {
+                    const double sb = bt_soft_biou(a, b, sm.tcol[TP_CONF * T + t]);
+                    if (mh > BT_MH_LIMIT && sb == 0.0) { deferred = 1; continue; }
                     const double ms = bt_mh_sim(mh, sm.colsum[t]);
                     const double sh = bt_shape(a, b, pr.s_corr);
-                    const double sb = bt_soft_biou(a, b, sm.tcol[TP_CONF * T + t]);
                     S = ((ms + sh) + sb) / 3;
                 } else {
-                    S = iou_pair(a, b);
+                    S = bt_iou(a, b);
                 }
                 mx = fmax(mx, S);
                 if (S > fmax(0.95 - sm.tcol[TP_AGE1 * T + t], 0.8)) hit = 1;
             }
+            __syncwarp();
             for (int o = 16; o > 0; o >>= 1) {
                 mx = fmax(mx, shfl_xor_d(mx, o));
                 mn = fmin(mn, shfl_xor_d(mn, o));
                 hit |= __shfl_xor_sync(BM_FULL, hit, o);
+                deferred |= __shfl_xor_sync(BM_FULL, deferred, o);
+            }
+            if (deferred && !(mx >= 1.0 / 3.0)) {
+                for (int t = lane; t < nT; t += 32) {
+                    const double mh = bt_mh(sm.dz + 4 * d, sm.tcol, T, t);
+                    const Box b = bt_trk_box(sm.tcol, T, t);
+                    if (!(mh > BT_MH_LIMIT && bt_soft_biou(a, b, sm.tcol[TP_CONF * T + t]) == 0.0)) continue;
+                    mx = fmax(mx, ((0.0 + bt_shape(a, b, pr.s_corr)) + 0.0) / 3);
+                }
+                for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, shfl_xor_d(mx, o));
             }
             if (lane == 0) { sm.rowa[d] = mx; sm.rowb[d] = mn; sm.flag[d] = hit; }
         }
@@ -324,7 +405,7 @@ bt_assoc_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets) {
     const float* dsrc = dets + (size_t)s * Dcap * 6;
     const int* hs = st.hsel + (size_t)s * Dcap;
     const double* dconf = st.dconf + (size_t)s * Dcap;
-    double* cost = st.cost + (size_t)s * Dcap * T;
+    double* cost = st.cost + (size_t)s * st.cost_stride;
     const float* sim = st.embsim + (size_t)s * Dcap * T;
     int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
     int* upd_det = upd_slot + Dcap;
@@ -343,8 +424,10 @@ bt_assoc_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets) {
     for (int t = tid; t < nT; t += BT_NT) { sm.colcnt[t] = 0; sm.t2d[t] = -1; sm.slot_of[t] = v.order[t]; }
     bt_stage_columns(st, s, sm, nT);
     __syncthreads();
+    bt_stage_floats(sm, T, nT);
+    __syncthreads();
     if (nD > 0 && nT > 0) {
-        bt_column_sums(sm, T, nD, nT);
+        bt_column_sums(sm, T, nD, nT, cost);
         __syncthreads();
         const double l_emb = (((1 + pr.l_iou) + pr.l_shape) + pr.l_mhd) * 1.5;
         double cmx = -CUDART_INF;
@@ -355,22 +438,44 @@ bt_assoc_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets) {
             const float* srow = sim + (size_t)sm.di[d] * T;
             double best = CUDART_INF;
             int barg = 0x7fffffff, hits = 0, hit = -1;
-            for (int t = lane; t < nT; t += 32) {
+            unsigned short* cand = sm.cand + (size_t)wid * T;
+            int nc = 0;
+            auto account = [&](int t, double c) {
+                cost[(size_t)d * nT + t] = -c;
+                if (c > pr.iou_thr) { hits++; hit = t; atomicAdd(&sm.colcnt[t], 1); }
+                if (-c < best || (-c == best && t < barg)) { best = -c; barg = t; }
+                cmx = fmax(cmx, -c);
+            };
+            for (int base = 0; base < nT; base += 32) {
+                const int t = base + lane;
+                const bool near = t < nT && !(pr.iou_thr > 0 && bt_far_x(bf, 1.f, sm.tf, TF_RA, T, t));
+                if (t < nT && !near) {
+                    // IoU = 0, confidence term = 0 (IoU < thr), Mahalanobis similarity = 0, shape term x 0
+                    double c = 0.0;
+                    if (pr.with_reid) c = c + l_emb * (double)srow[t];
+                    account(t, c);
+                }
+                const unsigned bal = __ballot_sync(BM_FULL, near);
+                if (near) cand[nc + __popc(bal & ((1u << lane) - 1))] = (unsigned short)t;
+                nc += __popc(bal);
+            }
+            __syncwarp();
+            for (int i = lane; i < nc; i += 32) {
+                const int t = cand[i];
                 const Box b = bt_trk_box(sm.tcol, T, t);
-                const double iou = iou_pair(a, b);
+                const double iou = bt_iou(a, b);
                 double cf = dc * sm.tcol[TP_CONF * T + t];
                 if (iou < pr.iou_thr) cf = 0.0;
                 double c = iou;
                 c = c + (pr.l_iou * cf) * iou;
                 const double mh = bt_mh(sm.dz + 4 * d, sm.tcol, T, t);
                 c = c + pr.l_mhd * bt_mh_sim(mh, sm.colsum[t]);
-                c = c + (pr.l_shape * cf) * bt_shape(a, b, pr.s_corr);
+                // conf == 0 (IoU below the threshold): (lambda * 0) * shape == 0 for the finite shape term
+                if (cf != 0.0) c = c + (pr.l_shape * cf) * bt_shape(a, b, pr.s_corr);
                 if (pr.with_reid) c = c + l_emb * (double)srow[t];
-                cost[(size_t)d * nT + t] = -c;
-                if (c > pr.iou_thr) { hits++; hit = t; atomicAdd(&sm.colcnt[t], 1); }
-                if (-c < best) { best = -c; barg = t; }
-                cmx = fmax(cmx, -c);
+                account(t, c);
             }
+            __syncwarp();
             warp_argmin(best, barg);
             for (int o = 16; o > 0; o >>= 1) {
                 hits += __shfl_xor_sync(BM_FULL, hits, o);
@@ -617,8 +722,10 @@ bt_emb_kernel(BoostState st, BoostParams pr, const float* __restrict__ embs) {
     }
     float* dst = st.emb + ((size_t)s * T + slot) * E;
     const float* src = embs + ((size_t)s * Dcap + di) * E;
+    const bool vec = (E & 3) == 0;
     if (birth) {
-        for (int e = lane; e < E; e += 32) dst[e] = src[e];
+        if (vec) for (int e = lane * 4; e < E; e += 128) *reinterpret_cast<float4*>(dst + e) = __ldg(reinterpret_cast<const float4*>(src + e));
+        else for (int e = lane; e < E; e += 32) dst[e] = src[e];
         return;
     }
     const double conf = st.dconf[(size_t)s * Dcap + di];
@@ -627,14 +734,14 @@ bt_emb_kernel(BoostState st, BoostParams pr, const float* __restrict__ embs) {
     const double alpha = af + (1 - af) * (1 - trust);
     double ss = 0.0;
     for (int e = lane; e < E; e += 32) {
-        const double q = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
-        ss += q * q;
+        const double t = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
+        ss += t * t;
     }
     for (int o = 16; o > 0; o >>= 1) ss += shfl_xor_d(ss, o);
     const double nrm = sqrt(ss);
     for (int e = lane; e < E; e += 32) {
-        const double q = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
-        dst[e] = (float)(q / nrm);
+        const double t = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
+        dst[e] = (float)(t / nrm);
     }
 }
 

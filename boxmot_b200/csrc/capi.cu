@@ -4,6 +4,7 @@
 #include "bytetrack_engine.cuh"
 #include "boosttrack_engine.cuh"
 #include <cmath>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -81,6 +82,7 @@ static int ocs_create(const bm_ocsort_config* cfg, const bm_deepocsort_config* d
     st.scratch_elems = (size_t)track_cap * det_cap * (deep ? 2 : 1);
     st.smem_cost_elems = smem_cost_bytes / 8;
     st.emb = nullptr; st.embsim = nullptr; st.bornslot = nullptr; st.epos = nullptr; st.wbuf = nullptr;
+    st.deep_d = nullptr; st.deep_i = nullptr;
     e->deep = deep != nullptr;
     bm::OcsParams& pr = e->pr;
     pr.det_thresh = cfg->det_thresh; pr.min_conf = cfg->min_conf; pr.iou_thr = cfg->asso_threshold;
@@ -101,6 +103,8 @@ static int ocs_create(const bm_ocsort_config* cfg, const bm_deepocsort_config* d
         }
         if (r == cudaSuccess) r = dev_alloc(e, &st.epos, S * T);
         if (r == cudaSuccess) r = dev_alloc(e, &st.wbuf, S * ((size_t)det_cap + T));
+        if (r == cudaSuccess) r = dev_alloc(e, &st.deep_d, S * ((size_t)det_cap + 1));
+        if (r == cudaSuccess) r = dev_alloc(e, &st.deep_i, S * (3 * (size_t)det_cap + T));
     }
     if (r == cudaSuccess) r = dev_alloc(e, &st.xP, S * bm::XB_N * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.sxP, S * bm::XB_N * T);
@@ -361,7 +365,8 @@ int bm_boosttrack_create(const bm_boosttrack_config* cfg, int n_streams, int tra
     if (r == cudaSuccess) r = dev_alloc(e, &st.tp, S * bm::TP_COUNT * T);
     if (r == cudaSuccess) r = dev_alloc(e, &st.dconf, S * D);
     if (r == cudaSuccess) r = dev_alloc(e, &st.hsel, S * D);
-    if (r == cudaSuccess) r = dev_alloc(e, &st.cost, S * D * T);
+    st.cost_stride = std::max(D * T, bm::bt_list_doubles(track_cap));
+    if (r == cudaSuccess) r = dev_alloc(e, &st.cost, S * st.cost_stride);
     if (r == cudaSuccess) r = dev_alloc(e, &st.upd, S * 2 * D);
     if (r == cudaSuccess) r = dev_alloc(e, &st.born, S * D);
     if (r == cudaSuccess) r = dev_alloc(e, &st.embsim, S * D * T);      // read (as zeros) only with_reid

@@ -17,7 +17,7 @@ namespace bm {
 
 enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
 enum { OF_OBSERVED = 1, OF_SAVED = 2 };
-enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_ND, OH_NS, OH_COUNT = 12 };
+enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_ND, OH_NS, OH_DEEP, OH_COUNT = 12 };
 // association operands written by the predict kernel, indexed by LIST POSITION
 enum { AB_X1 = 0, AB_Y1, AB_X2, AB_Y2, AB_VY, AB_VX, AB_KCX, AB_KCY, AB_KVALID, AB_COUNT };
 
@@ -57,6 +57,8 @@ struct OcsState {
     int* bornslot;                 // [S][Dcap]      slot given to the k-th birth of the frame
     int* epos;                     // [S][Tcap]      list position at contraction time (after a NaN-track removal)
     double* wbuf;                  // [S][Dcap + Tcap] row / column weights of compute_aw_max_metric
+    double* deep_d;                // [S][Dcap + 1]  row minima of the materialised first round + the matrix maximum
+    int* deep_i;                   // [S][3 Dcap + Tcap] row arg-minima, IoU-hit counts per row, hit column, hits per column
 };
 
 struct OcsView {   // per-stream base pointers

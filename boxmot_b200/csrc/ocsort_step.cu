@@ -698,8 +698,10 @@ __device__ inline void ocm_scan_rows_lane(const OcmCost& c, const OcmScreen& sc,
 // embedding, row top-2, IoU hit counts), pass B a thread per column (column top-2), pass C a
 // warp per row (final cost -(total), row minima for the solver, matrix maximum for lapjv's
 // padding).  Column index = list position; `remap` is set after a NaN-track removal.
-__device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, int s, const OcsSmem& sm,
-                                       const OcmCost& ocm, int nD, int nT, bool remap, double* s_cmx) {
+template <int NT>
+__device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, int s, const OcmCost& ocm,
+                                       const int* dind, int nD, int nT, bool remap, int* colcnt, double* rmin,
+                                       int* rarg, int* rowcnt, int* hit_t, double* s_cmx) {
     const int tid = threadIdx.x, lane = lane_id(), wid = warp_id();
     const int Tcap = st.Tcap, Dcap = st.Dcap;
     double* cost = st.scratch + (size_t)s * st.scratch_elems;       // [nD][nT]
@@ -709,10 +711,10 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
     const float* sim = st.embsim + (size_t)s * Dcap * Tcap;
     const int* epos = st.epos + (size_t)s * Tcap;
     const bool aw = pr.emb_on && !pr.aw_off;
-    for (int d = wid; d < nD; d += K2_NT / 32) {
+    for (int d = wid; d < nD; d += NT / 32) {
         const Box a = ocm.det(d);
         const double cx = (a.x1 + a.x2) / 2.0, cy = (a.y1 + a.y2) / 2.0;
-        const float* srow = sim + (size_t)sm.dind[d] * Tcap;
+        const float* srow = sim + (size_t)dind[d] * Tcap;
         double m1 = 0.0, m2 = 0.0;
         int npos = 0, hits = 0, hit = -1;
         for (int t = lane; t < nT; t += 32) {
@@ -726,7 +728,7 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
             cost[(size_t)d * nT + t] = c;
             embm[(size_t)d * nT + t] = e;
             if (e > 0) { npos++; if (e > m1) { m2 = m1; m1 = e; } else if (e > m2) m2 = e; }
-            if (iou > pr.iou_thr) { hits++; hit = t; atomicAdd(&sm.colcnt[t], 1); }
+            if (iou > pr.iou_thr) { hits++; hit = t; atomicAdd(&colcnt[t], 1); }
         }
         for (int o = 16; o > 0; o >>= 1) {
             const double b1 = shfl_xor_d(m1, o), b2 = shfl_xor_d(m2, o);
@@ -740,13 +742,13 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
             double w = 1.0;
             if (aw && npos >= 2) w = 1.0 - fmax(m2 / m1 - pr.aw_param, 0.0) / (1.0 - pr.aw_param);
             roww[d] = w;
-            sm.rowcnt[d] = hits;
-            sm.hit_t[d] = hit;
+            rowcnt[d] = hits;
+            hit_t[d] = hit;
         }
     }
     __syncthreads();
     if (aw) {
-        for (int t = tid; t < nT; t += K2_NT) {
+        for (int t = tid; t < nT; t += NT) {
             double m1 = 0.0, m2 = 0.0;
             int npos = 0;
             for (int d = 0; d < nD; d++) {
@@ -758,7 +760,7 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
         __syncthreads();
     }
     double cmx = -CUDART_INF;
-    for (int d = wid; d < nD; d += K2_NT / 32) {
+    for (int d = wid; d < nD; d += NT / 32) {
         const double rw = roww[d];
         double best = CUDART_INF;
         int barg = 0x7fffffff;
@@ -775,12 +777,72 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
             if (c < best) { best = c; barg = t; }
         }
         warp_argmin(best, barg);
-        if (lane == 0) { sm.rmin[d] = best; sm.rarg[d] = barg; }
+        if (lane == 0) { rmin[d] = best; rarg[d] = barg; }
     }
     for (int o = 16; o > 0; o >>= 1) cmx = fmax(cmx, shfl_xor_d(cmx, o));
     if (lane == 0) s_cmx[wid] = cmx;
     __syncthreads();
 }
+
+// The same build as its own launch with four times the threads of the association CTA (the pass
+// is a flat loop over detection x track pairs of long fp64 chains: it wants occupancy, not the
+// association kernel's shared-memory working set).  Streams whose prediction produced a NaN box
+// are left to the association kernel, which removes the track first (OH_DEEP = 0).
+constexpr int KD_NT = 256;
+__global__ void __launch_bounds__(KD_NT)
+deep_cost_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int s = blockIdx.x, tid = threadIdx.x;
+    const int Tcap = st.Tcap, Dcap = st.Dcap;
+    int* hdr = st.hdr + (size_t)s * OH_COUNT;
+    const int nD = hdr[OH_ND], nT = hdr[OH_NLIST];
+    float4* dbox = reinterpret_cast<float4*>(smem_raw);
+    double* rmin = reinterpret_cast<double*>(dbox + Dcap);
+    int* dind = reinterpret_cast<int*>(rmin + Dcap);
+    int* rarg = dind + Dcap;
+    int* rowcnt = rarg + Dcap;
+    int* hit_t = rowcnt + Dcap;
+    int* colcnt = hit_t + Dcap;
+    __shared__ double s_cmx[KD_NT / 32];
+    __shared__ int s_bad;
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    const double* ab = st.abuf + (size_t)s * AB_COUNT * Tcap;
+    const float* dsrc = dets + (size_t)s * Dcap * 6;
+    const int* hs = st.hsel + (size_t)s * 2 * Dcap;
+    for (int d = tid; d < nD; d += KD_NT) {
+        const int i = hs[d];
+        dbox[d] = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
+        dind[d] = i;
+    }
+    for (int p = tid; p < nT; p += KD_NT) {
+        colcnt[p] = 0;
+        bool nan = false;
+        for (int f = 0; f < 4; f++) nan |= ab[f * Tcap + p] != ab[f * Tcap + p];
+        if (nan) s_bad = 1;
+    }
+    __syncthreads();
+    if (s_bad || nD <= 0 || nT <= 0) {
+        if (tid == 0) hdr[OH_DEEP] = 0;
+        return;
+    }
+    const OcmCost ocm = {dbox, ab, Tcap, pr.asso_func, pr.diag, pr.inertia};
+    deep_build_cost<KD_NT>(st, pr, s, ocm, dind, nD, nT, false, colcnt, rmin, rarg, rowcnt, hit_t, s_cmx);
+    double* od = st.deep_d + (size_t)s * (Dcap + 1);
+    int* oi = st.deep_i + (size_t)s * (3 * Dcap + Tcap);
+    for (int d = tid; d < nD; d += KD_NT) {
+        od[d] = rmin[d];
+        oi[d] = rarg[d]; oi[Dcap + d] = rowcnt[d]; oi[2 * Dcap + d] = hit_t[d];
+    }
+    for (int p = tid; p < nT; p += KD_NT) oi[3 * Dcap + p] = colcnt[p];
+    if (tid == 0) {
+        double cmx = s_cmx[0];
+        for (int i = 1; i < KD_NT / 32; i++) cmx = fmax(cmx, s_cmx[i]);
+        od[Dcap] = cmx;
+        hdr[OH_DEEP] = 1;
+    }
+}
+static size_t deep_cost_smem(const OcsState& st) { return (size_t)st.Dcap * (16 + 8 + 16) + (size_t)st.Tcap * 4; }
 
 // Second-round association shared by BYTE and OCR: rows = the nA detections listed in
 // `alist` (indices into a detection set `abox`), cols = the nB list positions in
@@ -944,9 +1006,22 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
     // exact LAP (:505-507)
     __shared__ double s_cmx[K2_NT / 32];
     if (nD > 0 && nT > 0) {
-        if (DEEP)
-            deep_build_cost(st, pr, s, sm, ocm, nD, nT, sm.misc[M_ANYBAD] != 0, s_cmx);
-        else if (pr.asso_func == ASSO_IOU)
+        if (DEEP) {
+            if (v.hdr[OH_DEEP]) {       // built by deep_cost_kernel: fetch the row / column summaries
+                const double* od = st.deep_d + (size_t)s * (Dcap + 1);
+                const int* oi = st.deep_i + (size_t)s * (3 * Dcap + Tcap);
+                for (int d = tid; d < nD; d += K2_NT) {
+                    sm.rmin[d] = od[d];
+                    sm.rarg[d] = oi[d]; sm.rowcnt[d] = oi[Dcap + d]; sm.hit_t[d] = oi[2 * Dcap + d];
+                }
+                for (int p = tid; p < nT; p += K2_NT) sm.colcnt[p] = oi[3 * Dcap + p];
+                if (tid < K2_NT / 32) s_cmx[tid] = od[Dcap];
+                __syncthreads();
+            } else {
+                deep_build_cost<K2_NT>(st, pr, s, ocm, sm.dind, nD, nT, sm.misc[M_ANYBAD] != 0, sm.colcnt, sm.rmin,
+                                       sm.rarg, sm.rowcnt, sm.hit_t, s_cmx);
+            }
+        } else if (pr.asso_func == ASSO_IOU)
             ocm_scan_rows_lane(ocm, scr, nD, nT, pr.iou_thr, sm.colcnt, sm.rmin, sm.rarg, sm.rowcnt, sm.hit_t,
                                sm.cand + ocs_cand_ints(Tcap) * wid);
         else
@@ -1307,8 +1382,10 @@ docs_emb_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const
     }
     float* dst = st.emb + ((size_t)s * Tcap + slot) * E;
     const float* src = embs + ((size_t)s * Dcap + di) * E;
+    const bool vec = (E & 3) == 0;
     if (birth) {
-        for (int e = lane; e < E; e += 32) dst[e] = src[e];
+        if (vec) for (int e = lane * 4; e < E; e += 128) *reinterpret_cast<float4*>(dst + e) = __ldg(reinterpret_cast<const float4*>(src + e));
+        else for (int e = lane; e < E; e += 32) dst[e] = src[e];
         return;
     }
     const double conf = (double)dets[((size_t)s * Dcap + di) * 6 + 4];
@@ -1317,14 +1394,14 @@ docs_emb_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, const
     const double alpha = af + (1.0 - af) * (1.0 - trust);
     double ss = 0.0;
     for (int e = lane; e < E; e += 32) {
-        const double v = alpha * (double)dst[e] + (1.0 - alpha) * (double)src[e];
-        ss += v * v;
+        const double t = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
+        ss += t * t;
     }
     for (int o = 16; o > 0; o >>= 1) ss += shfl_xor_d(ss, o);
     const double nrm = sqrt(ss);
     for (int e = lane; e < E; e += 32) {
-        const double v = alpha * (double)dst[e] + (1.0 - alpha) * (double)src[e];
-        dst[e] = (float)(v / nrm);
+        const double t = alpha * (double)dst[e] + (1 - alpha) * (double)src[e];
+        dst[e] = (float)(t / nrm);
     }
 }
 
@@ -1359,6 +1436,8 @@ cudaError_t ocsort_step_configure(size_t smem) {
     cudaError_t e = cudaFuncSetAttribute(ocs_assoc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(ocs_assoc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(deep_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cosine_tc_kernel<DeepDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)cosine_tc_smem_bytes());
@@ -1417,6 +1496,8 @@ cudaError_t deepocsort_step_launch(const OcsState& st, const OcsParams& pr, cons
             DeepDot{st, embs, pr.E});
         if ((e = dbg_check("cosine_tc_kernel<DeepDot>", stream)) != cudaSuccess) return e;
     }
+    deep_cost_kernel<<<st.S, KD_NT, deep_cost_smem(st), stream>>>(st, pr, dets);
+    if ((e = dbg_check("deep_cost_kernel", stream)) != cudaSuccess) return e;
     BM_EV(2);
     ocs_assoc_kernel<true><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel<deep>", stream)) != cudaSuccess) return e;
