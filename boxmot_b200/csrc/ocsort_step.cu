@@ -789,7 +789,7 @@ __device__ inline void deep_build_cost(const OcsState& st, const OcsParams& pr, 
 // association kernel's shared-memory working set).  Streams whose prediction produced a NaN box
 // are left to the association kernel, which removes the track first (OH_DEEP = 0).
 constexpr int KD_NT = 256;
-__global__ void __launch_bounds__(KD_NT)
+__global__ void __launch_bounds__(KD_NT, 4)
 deep_cost_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x;

@@ -69,3 +69,56 @@ def test_full_size_batch_properties(tracker):
         for j, s in enumerate(pick):
             assert nout[s] == nout2[j]
             assert np.array_equal(out[s, : nout[s]], out2[j, : nout2[j]]), (f, s)
+
+
+@pytest.mark.parametrize("tracker", ["deepocsort", "boosttrack"])
+def test_full_size_batch_properties_embedding_trackers(tracker):
+    """1024 streams with 64-d embeddings through the DeepOCSORT / BoostTrack++ engines: a sample of
+    streams equals the oracle frame by frame, rows point at distinct detections of their frame, and
+    a stream's rows do not depend on the rest of the batch (bit-identical in another batch)."""
+    from boxmot_b200.engine import BoostTrackEngine, DeepOcSortEngine
+    from boxmot_b200.synth import make_batch
+    from conftest import BOOSTTRACK_YAML, DEEPOCSORT_YAML
+    E, FR = 64, 25
+    if tracker == "deepocsort":
+        from oracle.deepocsort import DeepOcSortOracle as Oracle
+        cls, kw, conf_rtol = DeepOcSortEngine, DEEPOCSORT_YAML, 0.0
+    else:
+        from oracle.boosttrack import BoostTrackOracle as Oracle
+        cls, kw, conf_rtol = BoostTrackEngine, BOOSTTRACK_YAML, 1e-9
+    dets, nd, embs = make_batch(S, K, FR, DCAP, emb_dim=E)
+
+    def run(dets, nd, embs):
+        eng = cls(dets.shape[1], track_cap=TCAP, det_cap=DCAP, emb_dim=E, **kw)
+        d_dets = torch.as_tensor(np.ascontiguousarray(dets, dtype=np.float32)).cuda()
+        d_nd = torch.as_tensor(np.ascontiguousarray(nd)).cuda()
+        d_embs = torch.as_tensor(np.ascontiguousarray(embs)).cuda()
+        rows = []
+        for f in range(dets.shape[0]):
+            out, nout = eng.step(d_dets[f], d_nd[f], d_embs[f])
+            rows.append((out.cpu().numpy(), nout.cpu().numpy()))
+        eng.status()
+        return rows
+
+    rows = run(dets, nd, embs)
+    oracles = {s: Oracle(**kw) for s in SAMPLE}
+    for f in range(FR):
+        out, nout = rows[f]
+        for s in SAMPLE:
+            n = nd[f, s]
+            want = oracles[s].update(dets[f, s, :n], None, embs[f, s, :n].copy())
+            assert_rows_match(out[s, : nout[s]], want, f, conf_rtol=conf_rtol)
+        for s in range(0, S, 37):
+            r = out[s, : nout[s]]
+            if len(r):
+                di = r[:, 7].astype(int)
+                assert len(set(di)) == len(di) and di.min() >= 0 and di.max() < nd[f, s]
+                assert len(set(r[:, 4])) == len(r) and r[:, 4].min() >= 1
+    pick = np.arange(S)[::-16][:64]
+    rows2 = run(dets[:, pick], nd[:, pick], embs[:, pick])
+    for f in range(FR):
+        out, nout = rows[f]
+        out2, nout2 = rows2[f]
+        for j, s in enumerate(pick):
+            assert nout[s] == nout2[j]
+            assert np.array_equal(out[s, : nout[s]], out2[j, : nout2[j]]), (f, s)
