@@ -103,3 +103,19 @@ def make_batch(n_streams, n_objects, n_frames, d_max, emb_dim=0, crowd=False,
             if emb_dim:
                 embs[f, s, : len(d)] = em[f]
     return (dets, nd, embs) if emb_dim else (dets, nd)
+
+
+def mot17_embs(frames, emb_dim, seed):
+    """Seeded unit-norm float32 embeddings for det.txt rows (det.txt carries no identities, so the
+    embedding is a smooth function of the box centre + noise: neighbouring boxes of consecutive
+    frames get similar vectors, which is what makes the embedding term matter)."""
+    rng = np.random.default_rng(seed)
+    proj = rng.normal(0, 1, (4, emb_dim))
+    out = []
+    for d in frames:
+        c = np.c_[(d[:, 0] + d[:, 2]) / 400.0, (d[:, 1] + d[:, 3]) / 400.0, (d[:, 2] - d[:, 0]) / 100.0,
+                  np.ones(len(d))]
+        e = np.sin(c @ proj) + 0.05 * rng.normal(0, 1, (len(d), emb_dim))
+        e /= np.linalg.norm(e, axis=1, keepdims=True) + 1e-12
+        out.append(e.astype(np.float32))
+    return out

@@ -16,7 +16,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle import ref_shim  # noqa: E402
-from boxmot_b200.synth import make_stream  # noqa: E402
+from boxmot_b200.synth import make_stream, mot17_embs  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
 SEQS = ("MOT17-02-FRCNN", "MOT17-04-FRCNN")
@@ -218,6 +218,17 @@ def main_boosttrack():
         print("boosttrack", name, out.shape, "ids", int(out[:, 5].max()))
 
 
+def main_mot17_emb():
+    """DeepOCSORT / BoostTrack on MOT17-mini det.txt (MOT17-02-FRCNN) with seeded embeddings."""
+    dets = load_det_txt("MOT17-02-FRCNN").astype(np.float32).astype(np.float64)
+    fr = frames_of(dets)
+    em = mot17_embs(fr, 48, 77)
+    for tracker, kw in (("deepocsort", {"det_thresh": 0.3}), ("boosttrack", {"det_thresh": 0.5})):
+        out = run_ref(tracker, fr, em, **kw)
+        np.savez_compressed(os.path.join(GOLD, "ref_%s_MOT17_02_FRCNN.npz" % tracker), rows=out, kw=np.array(repr(kw)))
+        print(tracker, "MOT17_02_FRCNN", out.shape, "ids", int(out[:, 5].max()))
+
+
 def main_strongsort_units():
     """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
     reference's own functions (rows a18 / a21)."""
@@ -295,6 +306,8 @@ if __name__ == "__main__":
         main_deepocsort()
     elif "--boosttrack" in sys.argv:
         main_boosttrack()
+    elif "--mot17-emb" in sys.argv:
+        main_mot17_emb()
     elif "--strongsort-units" in sys.argv:
         main_strongsort_units()
     else:

@@ -87,15 +87,25 @@ DEEPOCSORT_CASES = {
     "synth_k60_e32_cmc_dt1": (23, 60, 50, 32),
     "synth_k30_noemb_giou": (24, 30, 50, 32),
     "synth_k100_e128": (25, 100, 40, 128),
+    "MOT17_02_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings (gen_golden --mot17-emb)
 }
+
+
+def _mot17_emb_case(case):
+    from boxmot_b200.synth import mot17_embs
+    fr = [d.astype(np.float32).astype(np.float64) for d in mot17_frames(case)]
+    return fr, mot17_embs(fr, 48, 77)
 
 
 def deepocsort_case(case):
     """(frames, embs, warps or None, tracker kwargs, golden rows) of a DeepOCSORT fixture."""
     from boxmot_b200.synth import make_stream
     z = np.load(os.path.join(GOLD, "ref_deepocsort_%s.npz" % case))
-    sid, k, f, e = DEEPOCSORT_CASES[case]
-    fr, em = make_stream(sid, k, f, emb_dim=e)
+    if case.startswith("MOT17"):
+        fr, em = _mot17_emb_case(case)
+    else:
+        sid, k, f, e = DEEPOCSORT_CASES[case]
+        fr, em = make_stream(sid, k, f, emb_dim=e)
     return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
 
 
@@ -111,6 +121,7 @@ BOOSTTRACK_CASES = {
     "synth_k60_crowd_v2": (43, 60, 40, 32, True),
     "synth_k30_noduo": (44, 30, 50, 8, False),
     "synth_k30_nodlo": (45, 30, 50, 8, False),
+    "MOT17_02_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings (gen_golden --mot17-emb)
 }
 
 
@@ -118,8 +129,11 @@ def boosttrack_case(case):
     """(frames, embs, warps or None, tracker kwargs, golden rows) of a BoostTrack fixture."""
     from boxmot_b200.synth import make_stream
     z = np.load(os.path.join(GOLD, "ref_boosttrack_%s.npz" % case))
-    sid, k, f, e, crowd = BOOSTTRACK_CASES[case]
-    fr, em = make_stream(sid, k, f, emb_dim=e, crowd=crowd)
+    if case.startswith("MOT17"):
+        fr, em = _mot17_emb_case(case)
+    else:
+        sid, k, f, e, crowd = BOOSTTRACK_CASES[case]
+        fr, em = make_stream(sid, k, f, emb_dim=e, crowd=crowd)
     return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
 
 
