@@ -35,8 +35,6 @@ class DeepOcSort(BaseTracker):
     def update(self, dets, img=None, embs=None, warp=None):
         dets = self._prepare(dets, img)
         self.check_inputs(dets, img, embs)
-        if self.per_class:
-            raise NotImplementedError("per_class DeepOCSORT is not wired to the engine")
         if not self.embedding_off and embs is None and len(dets):
             raise RuntimeError("DeepOCSORT needs `embs` unless embedding_off: the ReID backend is outside the "
                                "association path")
@@ -47,17 +45,52 @@ class DeepOcSort(BaseTracker):
                 self._skipped += 1
                 return np.asarray([])
             h, w = (img.shape[0], img.shape[1]) if img is not None else (1080, 1920)
-            self._engine = DeepOcSortEngine(1, track_cap=self._caps[0], det_cap=self._caps[1], device=self._device,
+            n = self.nr_classes if self.per_class else 1
+            self._created = np.zeros((n,), dtype=np.int64)      # tracks created so far, per class
+            self._global_ids = [[] for _ in range(n)]           # class-local id -> tracker-wide id
+            self._count = 1                                      # KalmanBoxTracker.count (deepocsort.py:301)
+            self._engine = DeepOcSortEngine(n, track_cap=self._caps[0], det_cap=self._caps[1], device=self._device,
                                             emb_dim=max(e, 1), img_wh=(w, h), **self._kw)
             for _ in range(self._skipped):     # empty frames seen before: advance the frame counter
-                self._engine.step_host([np.empty((0, 6))], [np.empty((0, max(e, 1)))])
+                self._engine.step_host([np.empty((0, 6))] * n, [np.empty((0, max(e, 1)))] * n)
         self.frame_count += 1
+        if self.per_class:
+            return self._update_per_class(dets, embs, warp)
         rows = self._engine.step_host([dets], None if self.embedding_off else [embs],
                                       None if warp is None else [np.asarray(warp, dtype=np.float64)])[0]
         self._engine.status()
         return rows if len(rows) else np.asarray([])
 
+    def _update_per_class(self, dets, embs, warp):
+        """per_class_decorator (basetracker.py:155-201): update runs once per class id on the rows of
+        that class (det_ind relative to the subset, the frame's warp applied to every class list);
+        new ids come from ONE counter while the classes are walked in order (deepocsort.py:56-58)."""
+        n = self.nr_classes
+        idx = [np.where(dets[:, 5] == c)[0] if dets.size else np.empty((0,), dtype=int) for c in range(n)]
+        per_dets = [dets[i] for i in idx]
+        per_embs = None if self.embedding_off else [
+            embs[i] if embs is not None and len(embs) else np.empty((0, self._engine.E)) for i in idx]
+        warps = None if warp is None else [np.asarray(warp, dtype=np.float64)] * n
+        rows = self._engine.step_host(per_dets, per_embs, warps)
+        self._engine.status()
+        _, created = self._engine.stream_info()
+        for c in range(n):
+            for _ in range(int(created[c] - self._created[c])):
+                self._global_ids[c].append(self._count)
+                self._count += 1
+        self._created[:] = created
+        out = []
+        for c, r in enumerate(rows):
+            if len(r):
+                r = r.copy()
+                r[:, 4] = [self._global_ids[c][int(i) - 1] for i in r[:, 4]]
+                out.append(r)
+        return np.vstack(out) if out else np.empty((0, 8))
+
     def reset(self):
         if self._engine is not None:
             self._engine.reset()
+            self._created[:] = 0
+            self._global_ids = [[] for _ in self._global_ids]
+            self._count = 1
         self.frame_count = 0

@@ -75,6 +75,36 @@ def main_per_class():
     print("ocsort per_class", out.shape, "ids", int(out[:, 5].max()))
 
 
+def per_class_emb_frames():
+    """per_class_frames() with 32-d embeddings (stream 26)."""
+    fr, em = make_stream(26, 40, 60, emb_dim=32)
+    out = []
+    for d in fr:
+        d = d.copy()
+        d[:, 5] = np.floor((d[:, 0] + d[:, 2]) / 2.0 / 640.0).clip(0, 2)
+        out.append(d)
+    return out, em
+
+
+def main_deepocsort_per_class():
+    """DeepOCSORT with per_class=True: the decorator (basetracker.py:155-201) calls update once per
+    class id, so the CMC stand-in is asked nr_classes times per frame -- queue the frame's warp
+    that many times."""
+    fr, em = per_class_emb_frames()
+    warps = deepocsort_warps(26, len(fr))
+    trk = ref_shim.make_tracker("deepocsort", per_class=True)
+    out = []
+    for i, d in enumerate(fr):
+        trk.cmc.warps = [warps[i].copy() for _ in range(trk.nr_classes)]
+        r = np.asarray(trk.update(d.copy(), IMG, em[i].copy()), dtype=float)
+        r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+        out.append(np.c_[np.full(len(r), i), r])
+    out = np.vstack(out)
+    np.savez_compressed(os.path.join(GOLD, "ref_deepocsort_synth_k40_perclass.npz"), rows=out,
+                        kw=np.array(repr({"per_class": True})), warps=warps)
+    print("deepocsort per_class", out.shape, "ids", int(out[:, 5].max()))
+
+
 def main_kf():
     """Known-answer vectors of the reference's KalmanFilterXYAH / XYWH (rows a1-a5): a chain
     initiate -> (predict -> update(conf))* on random boxes, and gating distances."""
@@ -298,6 +328,8 @@ def main():
 if __name__ == "__main__":
     if "--per-class" in sys.argv:
         main_per_class()
+    elif "--deepocsort-per-class" in sys.argv:
+        main_deepocsort_per_class()
     elif "--kf" in sys.argv:
         main_kf()
     elif "--botsort" in sys.argv:

@@ -109,6 +109,20 @@ def deepocsort_case(case):
     return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
 
 
+def deepocsort_per_class_case():
+    """(frames, embs, warps, golden rows) of the per_class DeepOCSORT fixture: three classes by image
+    column (oracle/gen_golden.py per_class_emb_frames)."""
+    from boxmot_b200.synth import make_stream
+    z = np.load(os.path.join(GOLD, "ref_deepocsort_synth_k40_perclass.npz"))
+    fr, em = make_stream(26, 40, 60, emb_dim=32)
+    out = []
+    for d in fr:
+        d = d.copy()
+        d[:, 5] = np.floor((d[:, 0] + d[:, 2]) / 2.0 / 640.0).clip(0, 2)
+        out.append(d)
+    return out, em, z["warps"], z["rows"]
+
+
 BOOSTTRACK_YAML = dict(max_age=60, min_hits=3, det_thresh=0.6, iou_threshold=0.3, use_ecc=True, min_box_area=10,
                        aspect_ratio_thresh=1.6, lambda_iou=0.5, lambda_mhd=0.25, lambda_shape=0.25,
                        use_dlo_boost=True, use_duo_boost=True, dlo_boost_coef=0.65, s_sim_corr=False,

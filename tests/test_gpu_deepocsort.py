@@ -5,7 +5,8 @@ batched engine (C-ABI bm_deepocsort_*)."""
 import numpy as np
 import pytest
 
-from conftest import DEEPOCSORT_CASES, DEEPOCSORT_YAML, assert_rows_match, deepocsort_case, split_by_frame
+from conftest import (DEEPOCSORT_CASES, DEEPOCSORT_YAML, assert_rows_match, deepocsort_case, deepocsort_per_class_case,
+                      split_by_frame)
 
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
@@ -24,6 +25,21 @@ def test_deepocsort_tracker_matches_reference_golden(case):
     for f, d in enumerate(frames):
         got = trk.update(d, IMG, embs[f].copy(), warp=None if warps is None else warps[f])
         assert_rows_match(got, want_f[f], f)
+
+
+def test_deepocsort_per_class_matches_reference_golden():
+    """per_class=True (basetracker.py:155-201): one track list per class id, the frame's warp applied
+    to each, det_ind relative to the class subset, ONE id counter walked in class order."""
+    import boxmot_b200
+    frames, embs, warps, want = deepocsort_per_class_case()
+    trk = boxmot_b200.create_tracker("deepocsort", boxmot_b200.get_tracker_config("deepocsort"), per_class=True)
+    want_f = split_by_frame(want, len(frames))
+    seen = 0
+    for f, d in enumerate(frames):
+        got = trk.update(d, IMG, embs[f].copy(), warp=warps[f])
+        assert_rows_match(got, want_f[f], f)
+        seen += len(got)
+    assert seen == len(want) and len(np.unique(want[:, 7])) == 3
 
 
 @pytest.mark.parametrize("aw_off", [False, True])

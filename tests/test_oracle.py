@@ -112,6 +112,31 @@ def test_deepocsort_oracle_matches_reference_golden(case):
         assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
 
 
+def test_deepocsort_oracle_per_class_matches_reference_golden():
+    """per_class=True: one oracle per class id, ids renumbered from the shared creation counter
+    (basetracker.py:155-201, deepocsort.py:56-58) -- the same host-side logic as the adapter."""
+    from conftest import deepocsort_per_class_case
+    from oracle.deepocsort import DeepOcSortOracle
+    frames, embs, warps, want = deepocsort_per_class_case()
+    oras = [DeepOcSortOracle(**DEEPOCSORT_YAML) for _ in range(3)]
+    gids, count = [[] for _ in oras], 1
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        rows = []
+        for c, ora in enumerate(oras):
+            sel = d[:, 5] == c
+            r = ora.update(d[sel], None, embs[f][sel].copy(), warp=warps[f])
+            while len(gids[c]) < ora.next_id - 1:
+                gids[c].append(count)
+                count += 1
+            if len(r):
+                r = r.copy()
+                r[:, 4] = [gids[c][int(i) - 1] for i in r[:, 4]]
+                rows.append(r)
+        got = np.vstack(rows) if rows else np.empty((0, 8))
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-12)
+
+
 @pytest.mark.parametrize("case", list(BOOSTTRACK_CASES))
 def test_boosttrack_oracle_matches_reference_golden(case):
     """BoostTrack(++): 8-state filter, DLO / DUO confidence boosts, soft-BIoU / Mahalanobis / shape /
