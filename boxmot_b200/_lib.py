@@ -112,6 +112,10 @@ _SIGS = {
                                       c_void_p]),
     "bm_min_cost_matching_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
                                            c_void_p, c_void_p, c_void_p]),
+    "bm_strongsort_gated_metric": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double,
+                                           c_double, c_void_p]),
+    "bm_strongsort_enhance_cost": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "bm_strongsort_iou_cost": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "bm_cosine_distance": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "bm_xysrb_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysrb_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -160,6 +160,85 @@ __global__ void cv8_gating_kernel(const double* mean, const double* cov, int nt,
 }
 
 
+// ---- StrongSORT cost post-processing (strongsort/sort/linear_assignment.py, tracker.py), one thread per
+// (track, detection) entry.  Per-track attribute table: SS_* columns, one row of SS_FIELDS doubles per track.
+enum { SS_AGE = 0, SS_HITS, SS_TSU, SS_MOTION, SS_APPEAR, SS_QUALITY, SS_HI_STREAK, SS_LO_STREAK, SS_HAS_VEL, SS_VX,
+       SS_VY, SS_CONF, SS_CLS, SS_FIELDS };
+constexpr double SS_INFTY_COST = 1e5;        // linear_assignment.py:11
+constexpr double SS_CHI2INV95_4 = 9.4877;    // matching.py chi2inv95[4]
+
+// gated_metric after metric.distance (tracker.py:186-206): gate_cost_matrix (linear_assignment.py:174-248)
+// + _apply_id_preservation_weighting (tracker.py:283-298)
+__global__ void ss_gated_metric_kernel(double* __restrict__ cost, const double* __restrict__ mean,
+                                       const double* __restrict__ cov, const double* __restrict__ trk, int nt,
+                                       const double* __restrict__ meas, int nd, double mc_lambda, double id_weight) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nt * nd) return;
+    const int t = e / nd, d = e % nd;
+    double x[8], P[12], z[4];
+    cv8_load(mean, cov, t, x, P);
+    for (int c = 0; c < 4; c++) z[c] = meas[(size_t)d * 4 + c];
+    const double* a = trk + (size_t)t * SS_FIELDS;
+    const double gd = cv8_gating<CV8_XYAH>(x, P, z, false, false);
+    double c = cost[e];
+    if (gd > SS_CHI2INV95_4) c = SS_INFTY_COST;                              // :232
+    // _compute_enhanced_motion_cost (:288-307)
+    double motion = gd * (2.0 - a[SS_MOTION]);
+    if (a[SS_HAS_VEL] != 0.0) {
+        const double dx = z[0] - (x[0] + a[SS_VX]), dy = z[1] - (x[1] + a[SS_VY]);
+        const double err = sqrt(dx * dx + dy * dy);
+        motion = motion * (1.0 + fmin(err / 50.0, 1.0));
+    }
+    // _compute_adaptive_lambda (:310-329)
+    double lam = mc_lambda + (1.0 - mc_lambda) * fmin(a[SS_AGE] / 10.0, 1.0) * 0.1;
+    lam = lam * (0.8 + 0.4 * a[SS_MOTION]);
+    if (a[SS_APPEAR] < 0.5) lam = fmin(lam * 1.2, 0.99);
+    lam = fmin(fmax(lam, 0.1), 0.99);
+    c = lam * c + (1.0 - lam) * motion;                                      // :241-243
+    // _apply_track_specific_adjustments (:332-352)
+    if (a[SS_QUALITY] > 0.8) c = c * 0.95;
+    if (a[SS_HITS] > 10.0 && a[SS_TSU] == 0.0) c = c * 0.98;
+    if (a[SS_HI_STREAK] > 3.0) c = c * 0.97;
+    if (a[SS_LO_STREAK] > 2.0) c = c * 1.05;
+    if (id_weight > 0.0) c = c * (1.0 - id_weight * fmin(a[SS_HITS] / 10.0, 1.0));   // tracker.py:294-296
+    cost[e] = c;
+}
+
+// _enhance_cost_matrix (linear_assignment.py:251-273); det [nd][3] = quality_score, conf, cls
+__global__ void ss_enhance_cost_kernel(double* __restrict__ cost, const double* __restrict__ trk, int nt,
+                                       const double* __restrict__ det, int nd) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nt * nd) return;
+    const double* a = trk + (size_t)(e / nd) * SS_FIELDS;
+    const double* b = det + (size_t)(e % nd) * 3;
+    double c = cost[e];
+    const double q = 1.0 - ((a[SS_QUALITY] + b[0]) / 2.0 - 0.5) * 0.2;       // :355-364
+    c = c * fmin(fmax(q, 0.8), 1.2);
+    if (a[SS_CLS] == b[2]) c = c * 0.9;                                      // :265-267
+    if (a[SS_CONF] > 0.7 && b[1] > 0.7) c = c * 0.9;                         // :367-379
+    else if (a[SS_CONF] < 0.3 || b[1] < 0.3) c = c * 1.1;
+    cost[e] = c;
+}
+
+// iou_cost (iou_matching.py:49-87): 1 - IoU of Track.to_tlwh() with the detections' tlwh; rows of tracks
+// with time_since_update > 1 are INFTY_COST
+__global__ void ss_iou_cost_kernel(const double* __restrict__ mean, const double* __restrict__ trk, int nt,
+                                   const double* __restrict__ tlwh, int nd, double* __restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nt * nd) return;
+    const int t = e / nd, d = e % nd;
+    if (trk[(size_t)t * SS_FIELDS + SS_TSU] > 1.0) { out[e] = SS_INFTY_COST; return; }
+    const double* m = mean + (size_t)t * 8;
+    const double h = m[3], w = m[2] * h;                 // track.py:154-157
+    const double x1 = m[0] - w / 2.0, y1 = m[1] - h / 2.0;
+    const double* b = tlwh + (size_t)d * 4;
+    const double tlx = fmax(x1, b[0]), tly = fmax(y1, b[1]);
+    const double brx = fmin(x1 + w, b[0] + b[2]), bry = fmin(y1 + h, b[1] + b[3]);
+    const double inter = fmax(0.0, brx - tlx) * fmax(0.0, bry - tly);
+    out[e] = 1.0 - inter / (w * h + b[2] * b[3] - inter);
+}
+
+
 // ---- embedding distance (matching.py:230-321) as a stand-alone batched contraction
 __global__ void cosine_prep_kernel(const float* a, int na, const float* b, int nb, int E, int* idx, float* norms) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -374,6 +453,40 @@ int bm_kf_cv8_gating(int kind, const double* d_mean, const double* d_cov, int n_
                                                                             only_position, gaussian, d_out);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("cv8_gating_kernel", e);
+}
+
+int bm_strongsort_gated_metric(double* d_cost, const double* d_mean, const double* d_cov, const double* d_trk,
+                               int n_tracks, const double* d_meas, int n_dets, double mc_lambda, double id_weight,
+                               void* stream) {
+    const int n = n_tracks * n_dets;
+    if (n <= 0) return 0;
+    if (!d_cost || !d_mean || !d_cov || !d_trk || !d_meas) return -1;
+    bm::ss_gated_metric_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_cost, d_mean, d_cov, d_trk, n_tracks, d_meas, n_dets, mc_lambda, id_weight);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("ss_gated_metric_kernel", e);
+}
+
+int bm_strongsort_enhance_cost(double* d_cost, const double* d_trk, int n_tracks, const double* d_det, int n_dets,
+                               void* stream) {
+    const int n = n_tracks * n_dets;
+    if (n <= 0) return 0;
+    if (!d_cost || !d_trk || !d_det) return -1;
+    bm::ss_enhance_cost_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_cost, d_trk, n_tracks,
+                                                                                              d_det, n_dets);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("ss_enhance_cost_kernel", e);
+}
+
+int bm_strongsort_iou_cost(const double* d_mean, const double* d_trk, int n_tracks, const double* d_tlwh, int n_dets,
+                           double* d_out, void* stream) {
+    const int n = n_tracks * n_dets;
+    if (n <= 0) return 0;
+    if (!d_mean || !d_trk || !d_tlwh || !d_out) return -1;
+    bm::ss_iou_cost_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_mean, d_trk, n_tracks,
+                                                                                          d_tlwh, n_dets, d_out);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("ss_iou_cost_kernel", e);
 }
 
 int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, int bank_cap, const float* d_feats,

@@ -257,6 +257,31 @@ int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, in
 int bm_min_cost_matching_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
                                const int* d_nc, double max_distance, int* d_x, int* d_y, void* stream);
 
+/* StrongSORT cost post-processing, one entry per (track, detection) pair.  d_trk [n_tracks][13]
+ * doubles per track: age, hits, time_since_update, motion_consistency, appearance_consistency,
+ * quality_score, high_conf_streak, low_conf_streak, has_velocity (velocity_history non-empty),
+ * velocity_history[-1] x, y, conf, cls (strongsort/sort/track.py:86-142).
+ *
+ * bm_strongsort_gated_metric: what Tracker._enhanced_match.gated_metric (sort/tracker.py:186-206)
+ * does to the matrix metric.distance returned (bm_nn_cosine_distance): gate_cost_matrix
+ * (sort/linear_assignment.py:174-248: squared Mahalanobis gate at chi2inv95[4] -> 1e5, motion cost
+ * :288-307, adaptive lambda :310-329, blend :241-243, track adjustments :332-352) and the
+ * id-preservation weighting (sort/tracker.py:283-298).  d_cost [n_tracks][n_dets] fp64 in place;
+ * d_mean [n_tracks][8], d_cov [n_tracks][8][8] (KalmanFilterXYAH state), d_meas [n_dets][4] xyah.
+ *
+ * bm_strongsort_enhance_cost: _enhance_cost_matrix (sort/linear_assignment.py:251-273) applied by
+ * min_cost_matching before the clamp; d_det [n_dets][3] = quality_score, conf, cls.
+ *
+ * bm_strongsort_iou_cost: iou_cost (sort/iou_matching.py:49-87) of Track.to_tlwh() against
+ * d_tlwh [n_dets][4]; rows of tracks with time_since_update > 1 are 1e5. */
+int bm_strongsort_gated_metric(double* d_cost, const double* d_mean, const double* d_cov, const double* d_trk,
+                               int n_tracks, const double* d_meas, int n_dets, double mc_lambda, double id_weight,
+                               void* stream);
+int bm_strongsort_enhance_cost(double* d_cost, const double* d_trk, int n_tracks, const double* d_det, int n_dets,
+                               void* stream);
+int bm_strongsort_iou_cost(const double* d_mean, const double* d_trk, int n_tracks, const double* d_tlwh, int n_dets,
+                           double* d_out, void* stream);
+
 /* embedding_distance (boxmot/utils/matching.py:230-321 with its defaults): d_out [na][nb] =
  * max(0, 1 - <a_i, b_j> / (|a_i| |b_j|)) for float32 feature rows d_a [na][emb_dim],
  * d_b [nb][emb_dim].  mode 0 = tcgen05 tensor-core contraction (3xTF32, fp32 accumulation in

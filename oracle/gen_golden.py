@@ -259,6 +259,78 @@ def main_mot17_emb():
         print(tracker, "MOT17_02_FRCNN", out.shape, "ids", int(out[:, 5].max()))
 
 
+def strongsort_gate_vectors(la, rng):
+    """Known-answer vectors of gated_metric's post-processing (gate_cost_matrix + id-preservation
+    weighting, row a22), _enhance_cost_matrix and iou_cost, from the reference's own functions on
+    the reference's own Track / Detection objects (tracks driven through predict / update so that
+    covariances, histories and scores are the ones the state machine produces; a few attributes are
+    then overwritten to reach every branch)."""
+    import types
+    from oracle import strongsort as so
+    cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
+    if not hasattr(cmc, "get_cmc_method"):
+        cmc.get_cmc_method = lambda _name: (lambda: None)
+    from boxmot.trackers.strongsort.sort import iou_matching
+    from boxmot.trackers.strongsort.sort.detection import Detection
+    from boxmot.trackers.strongsort.sort.track import Track
+    from boxmot.trackers.strongsort.sort.tracker import Tracker
+    T, D, E = 40, 57, 16
+
+    def rand_det(c=None, cls=None):
+        wh = rng.uniform(20, 200, 2)
+        c = rng.random(2) * [1800, 1000] if c is None else c
+        d = Detection(np.r_[c - wh / 2, wh], float(rng.uniform(0.05, 0.99)),
+                      float(rng.integers(0, 3)) if cls is None else cls, 0, rng.normal(0, 1, E).astype(np.float32))
+        d.quality_score = float(rng.uniform(0.1, 1.1))
+        return d
+
+    tracks = []
+    for t in range(T):
+        d = rand_det()
+        trk = Track(d, t + 1, 2, 50, 0.9)
+        for _ in range(int(rng.integers(0, 14))):
+            trk.predict()
+            if rng.random() < 0.8:
+                c = trk.mean[:2] + rng.normal(0, 4, 2)
+                trk.update(rand_det(c, trk.cls))
+        if t % 5 != 4:
+            trk.predict()          # the state gated_metric sees: predicted, time_since_update >= 1
+        if t % 7 == 0:
+            trk.appearance_consistency = float(rng.uniform(0.1, 0.5))
+        if t % 6 == 0:
+            trk.low_conf_streak = 3
+        if t % 9 == 0:
+            trk.quality_score = 0.25
+        tracks.append(trk)
+    def near(k):       # a detection the gate accepts for track k (most of the time): its own box, jittered
+        h = k.mean[3] * (1 + rng.normal(0, 0.03))
+        w = k.mean[2] * k.mean[3] * (1 + rng.normal(0, 0.03))
+        d = rand_det(k.mean[:2] + rng.normal(0, 0.04, 2) * k.mean[3])
+        d.tlwh = np.r_[d.tlwh[:2] + d.tlwh[2:] / 2 - [w / 2, h / 2], w, h]
+        return d
+
+    dets = [near(tracks[i % T]) if i < 45 else rand_det() for i in range(D)]
+    tidx, didx = list(range(T)), list(range(D))
+    cost0 = rng.uniform(0, 0.4, (T, D))
+    cost0[3] = 1e5
+    g = la.gate_cost_matrix(cost0.copy(), tracks, dets, tidx, didx, 0.995)
+    g = Tracker._apply_id_preservation_weighting(types.SimpleNamespace(id_preservation_weight=0.1), g, tracks, dets,
+                                                 tidx, didx)
+    enh = la._enhance_cost_matrix(cost0.copy(), tracks, dets, tidx, didx)
+    iou = iou_matching.iou_cost(tracks, dets, tidx, didx)
+    trk = np.zeros((T, so.TRK_FIELDS))
+    for t, k in enumerate(tracks):
+        v = k.velocity_history[-1] if k.velocity_history else np.zeros(2)
+        trk[t] = [k.age, k.hits, k.time_since_update, k.motion_consistency, k.appearance_consistency,
+                  k.quality_score, k.high_conf_streak, k.low_conf_streak, float(len(k.velocity_history) > 0),
+                  v[0], v[1], k.conf, k.cls]
+    print("strongsort gate: gated", int((g > 500).sum()), "of", g.size, "iou<1", int((iou < 1).sum()))
+    return dict(g_means=np.array([k.mean for k in tracks]), g_covs=np.array([k.covariance for k in tracks]),
+                g_trk=trk, g_tlwh=np.array([d.tlwh for d in dets]), g_dq=np.array([d.quality_score for d in dets]),
+                g_dconf=np.array([d.conf for d in dets]), g_dcls=np.array([d.cls for d in dets]), g_cost0=cost0,
+                g_gated=g, g_enh=enh, g_iou=iou, g_lambda=np.array(0.995), g_idw=np.array(0.1))
+
+
 def main_strongsort_units():
     """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
     reference's own functions (rows a18 / a21)."""
@@ -298,8 +370,9 @@ def main_strongsort_units():
         m, _, _ = la.min_cost_matching(lambda tr, de, ti, di, c=c: c.copy(), 0.5, [_T()] * nrs[p], [_D()] * ncs[p])
         for r, cc in m:
             xs[p, r] = cc
+    gate = strongsort_gate_vectors(la, rng)
     np.savez_compressed(os.path.join(GOLD, "ref_strongsort_units.npz"), bank=bank, nb=nb, feats=feats, nn=nn,
-                        costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5))
+                        costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5), **gate)
     print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))
 
 

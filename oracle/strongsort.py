@@ -7,6 +7,14 @@ Sources restated (paths under /root/reference/boxmot/trackers/strongsort/sort/):
                        _enhance_cost_matrix :251-273 is the identity for neutral quality /
                        confidence attributes, which is how the fixture drives the reference)
 
+  gated_metric         tracker.py:186-206 after metric.distance: gate_cost_matrix
+                       (linear_assignment.py:174-248 with _compute_enhanced_motion_cost :288-307,
+                       _compute_adaptive_lambda :310-329, _apply_track_specific_adjustments :332-352)
+                       and Tracker._apply_id_preservation_weighting (tracker.py:283-298)
+  enhance_cost_matrix  linear_assignment.py:251-273 (_compute_quality_factor :355-364,
+                       _compute_confidence_factor :367-379)
+  iou_cost             iou_matching.py:10-87 (tlwh IoU, INFTY_COST rows for time_since_update > 1)
+
 Parity status: pinned against the reference's own functions imported through oracle/ref_shim.py
 (tests/golden/ref_strongsort_units.npz, oracle/gen_golden.py --strongsort-units).  The fork's
 end-to-end StrongSORT (tracker.py / track.py / occlusion_handler.py) is NOT restated: as shipped
@@ -50,3 +58,95 @@ def min_cost_matching(cost, max_distance):
         else:
             m.append((r, c))
     return m, um_r, um_c
+
+
+# columns of the per-track attribute table the units take (one row per track)
+TRK_AGE, TRK_HITS, TRK_TSU, TRK_MOTION, TRK_APPEAR, TRK_QUALITY, TRK_HI_STREAK, TRK_LO_STREAK, TRK_HAS_VEL, \
+    TRK_VX, TRK_VY, TRK_CONF, TRK_CLS, TRK_FIELDS = range(14)
+CHI2INV95_4 = 9.4877
+
+
+def _project(mean, cov):
+    """KalmanFilterXYAH.project with confidence 0 (base_kalman_filter.py:86-109, xyah_kf.py)."""
+    std = np.array([1.0 / 20 * mean[3], 1.0 / 20 * mean[3], 1e-1, 1.0 / 20 * mean[3]])
+    h = np.eye(4, 8)
+    return h @ mean, np.linalg.multi_dot((h, cov, h.T)) + np.diag(np.square(std))
+
+
+def gating_distance(mean, cov, meas):
+    """base_kalman_filter.py:166-194, metric "maha"."""
+    import scipy.linalg
+    m, c = _project(mean, cov)
+    d = meas - m
+    z = scipy.linalg.solve_triangular(np.linalg.cholesky(c), d.T, lower=True, check_finite=False,
+                                      overwrite_b=True)
+    return np.sum(z * z, axis=0)
+
+
+def gated_metric(cost, means, covs, trk, meas, mc_lambda, id_weight):
+    """cost (T, D) appearance distances; means (T, 8), covs (T, 8, 8); trk (T, TRK_FIELDS);
+    meas (D, 4) detections as xyah.  Returns the (T, D) matrix matching_cascade hands to
+    min_cost_matching."""
+    out = np.array(cost, dtype=float)
+    for r in range(len(out)):
+        a = trk[r]
+        gd = gating_distance(means[r], covs[r], meas)
+        out[r, gd > CHI2INV95_4] = INFTY_COST
+        motion = gd.copy()
+        motion *= 2.0 - a[TRK_MOTION]
+        if a[TRK_HAS_VEL]:
+            pred = means[r, :2] + a[TRK_VX:TRK_VY + 1]
+            for i in range(len(meas)):
+                motion[i] *= 1.0 + min(np.linalg.norm(meas[i, :2] - pred) / 50.0, 1.0)
+        lam = mc_lambda + (1 - mc_lambda) * min(a[TRK_AGE] / 10.0, 1.0) * 0.1
+        lam = lam * (0.8 + 0.4 * a[TRK_MOTION])
+        if a[TRK_APPEAR] < 0.5:
+            lam = min(lam * 1.2, 0.99)
+        lam = np.clip(lam, 0.1, 0.99)
+        row = lam * out[r] + (1 - lam) * motion
+        if a[TRK_QUALITY] > 0.8:
+            row = row * 0.95
+        if a[TRK_HITS] > 10 and a[TRK_TSU] == 0:
+            row = row * 0.98
+        if a[TRK_HI_STREAK] > 3:
+            row = row * 0.97
+        if a[TRK_LO_STREAK] > 2:
+            row = row * 1.05
+        if id_weight > 0:
+            row = row * (1.0 - id_weight * min(a[TRK_HITS] / 10.0, 1.0))
+        out[r] = row
+    return out
+
+
+def enhance_cost_matrix(cost, trk, det_quality, det_conf, det_cls):
+    out = np.array(cost, dtype=float)
+    for r in range(out.shape[0]):
+        for c in range(out.shape[1]):
+            q = np.clip(1.0 - ((trk[r, TRK_QUALITY] + det_quality[c]) / 2.0 - 0.5) * 0.2, 0.8, 1.2)
+            out[r, c] *= q
+            if trk[r, TRK_CLS] == det_cls[c]:
+                out[r, c] *= 0.9
+            if trk[r, TRK_CONF] > 0.7 and det_conf[c] > 0.7:
+                out[r, c] *= 0.9
+            elif trk[r, TRK_CONF] < 0.3 or det_conf[c] < 0.3:
+                out[r, c] *= 1.1
+            else:
+                out[r, c] *= 1.0
+    return out
+
+
+def iou_cost(means, tsu, det_tlwh):
+    out = np.zeros((len(means), len(det_tlwh)))
+    for r, m in enumerate(means):
+        if tsu[r] > 1:
+            out[r] = INFTY_COST
+            continue
+        b = m[:4].copy()
+        b[2] *= b[3]
+        b[:2] -= b[2:] / 2
+        tl = np.maximum(b[:2], det_tlwh[:, :2])
+        br = np.minimum(b[:2] + b[2:], det_tlwh[:, :2] + det_tlwh[:, 2:])
+        wh = np.maximum(0.0, br - tl)
+        inter = wh.prod(axis=1)
+        out[r] = 1.0 - inter / (b[2:].prod() + det_tlwh[:, 2:].prod(axis=1) - inter)
+    return out

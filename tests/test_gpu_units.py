@@ -374,3 +374,81 @@ def test_strongsort_min_cost_matching_matches_reference_vectors():
         for r, c in m:
             want[r] = c
         assert np.array_equal(x[p], want), p
+
+
+def test_strongsort_cost_postprocessing_matches_reference_vectors():
+    """bm_strongsort_gated_metric (row a22: gate_cost_matrix + id-preservation weighting),
+    bm_strongsort_enhance_cost and bm_strongsort_iou_cost against the reference's own functions run
+    on its own Track / Detection objects (fixture), and against the oracle on a larger random
+    problem.  fp64 throughout; 1e-12 relative (the gate: sqrt/division order of the Cholesky solve)."""
+    import os
+    from conftest import GOLD
+    from boxmot_b200 import _lib
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+
+    def dev(a):
+        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).cuda()
+
+    def run(cost0, means, covs, trk, tlwh, det, lam, idw):
+        T, D = cost0.shape
+        xyah = tlwh.copy()
+        xyah[:, :2] += xyah[:, 2:] / 2
+        xyah[:, 2] /= xyah[:, 3]
+        d_m, d_c, d_t, d_z, d_l, d_d = dev(means), dev(covs), dev(trk), dev(xyah), dev(tlwh), dev(det)
+        g, e = dev(cost0), dev(cost0)
+        i = torch.zeros((T, D), dtype=torch.float64, device="cuda")
+        L = _lib.lib()
+        assert L.bm_strongsort_gated_metric(g.data_ptr(), d_m.data_ptr(), d_c.data_ptr(), d_t.data_ptr(), T,
+                                            d_z.data_ptr(), D, float(lam), float(idw), None) == 0
+        assert L.bm_strongsort_enhance_cost(e.data_ptr(), d_t.data_ptr(), T, d_d.data_ptr(), D, None) == 0
+        assert L.bm_strongsort_iou_cost(d_m.data_ptr(), d_t.data_ptr(), T, d_l.data_ptr(), D, i.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        return g.cpu().numpy(), e.cpu().numpy(), i.cpu().numpy(), xyah
+
+    det = np.c_[z["g_dq"], z["g_dconf"], z["g_dcls"]]
+    g, e, i, _ = run(z["g_cost0"], z["g_means"], z["g_covs"], z["g_trk"], z["g_tlwh"], det, z["g_lambda"], z["g_idw"])
+    np.testing.assert_allclose(g, z["g_gated"], rtol=1e-12, atol=0)
+    assert np.array_equal(g > 500, z["g_gated"] > 500) and (g < 1.0).sum() > 20
+    np.testing.assert_allclose(e, z["g_enh"], rtol=1e-14, atol=0)
+    np.testing.assert_allclose(i, z["g_iou"], rtol=1e-13, atol=1e-15)
+
+    # larger random problem against the oracle: 300 tracks x 400 detections
+    rng = np.random.default_rng(17)
+    T, D = 300, 400
+    from oracle import kalman as K
+    means, covs = np.zeros((T, 8)), np.zeros((T, 8, 8))
+    for t in range(T):
+        wh = rng.uniform(20, 200, 2)
+        m, c = K.cv8_initiate("xyah", np.r_[rng.random(2) * [1800, 1000], wh[0] / wh[1], wh[1]])
+        for _ in range(int(rng.integers(1, 6))):
+            m, c = K.cv8_predict("xyah", m, c)
+        means[t], covs[t] = m, c
+    trk = np.zeros((T, so.TRK_FIELDS))
+    trk[:, so.TRK_AGE] = rng.integers(1, 40, T)
+    trk[:, so.TRK_HITS] = rng.integers(1, 30, T)
+    trk[:, so.TRK_TSU] = rng.integers(0, 4, T)
+    trk[:, so.TRK_MOTION] = rng.random(T)
+    trk[:, so.TRK_APPEAR] = rng.random(T)
+    trk[:, so.TRK_QUALITY] = rng.random(T)
+    trk[:, so.TRK_HI_STREAK] = rng.integers(0, 7, T)
+    trk[:, so.TRK_LO_STREAK] = rng.integers(0, 5, T)
+    trk[:, so.TRK_HAS_VEL] = rng.integers(0, 2, T)
+    trk[:, so.TRK_VX:so.TRK_VY + 1] = rng.normal(0, 3, (T, 2))
+    trk[:, so.TRK_CONF] = rng.random(T)
+    trk[:, so.TRK_CLS] = rng.integers(0, 3, T)
+    tlwh = np.zeros((D, 4))
+    for d in range(D):
+        m = means[d % T]
+        h = m[3] * (1 + rng.normal(0, 0.04))
+        w = m[2] * m[3] * (1 + rng.normal(0, 0.04))
+        c = m[:2] + rng.normal(0, 0.05, 2) * m[3]
+        tlwh[d] = [c[0] - w / 2, c[1] - h / 2, w, h]
+    det = np.c_[rng.random(D) * 1.2, rng.random(D), rng.integers(0, 3, D)]
+    cost0 = rng.uniform(0, 0.5, (T, D))
+    g, e, i, xyah = run(cost0, means, covs, trk, tlwh, det, 0.995, 0.1)
+    want = so.gated_metric(cost0, means, covs, trk, xyah, 0.995, 0.1)
+    assert np.array_equal(g > 500, want > 500) and 100 < (want < 500).sum()
+    np.testing.assert_allclose(g, want, rtol=1e-12, atol=0)
+    np.testing.assert_allclose(e, so.enhance_cost_matrix(cost0, trk, det[:, 0], det[:, 1], det[:, 2]), rtol=1e-14)
+    np.testing.assert_allclose(i, so.iou_cost(means, trk[:, so.TRK_TSU], tlwh), rtol=1e-13, atol=1e-15)

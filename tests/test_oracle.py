@@ -168,6 +168,29 @@ def test_strongsort_unit_oracle_matches_reference_vectors():
         assert sorted(um_r) == [r for r in range(nr) if x[r] < 0]
 
 
+def test_strongsort_gate_oracle_matches_reference_vectors():
+    """gated_metric's post-processing (gate_cost_matrix + id-preservation weighting, row a22),
+    _enhance_cost_matrix and iou_cost against the reference's own functions run on the reference's
+    own Track / Detection objects (oracle/gen_golden.py strongsort_gate_vectors).  Tolerance 1e-12
+    relative: pure fp64 arithmetic in the same order."""
+    from conftest import GOLD
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    tlwh = z["g_tlwh"]
+    xyah = tlwh.copy()
+    xyah[:, :2] += xyah[:, 2:] / 2
+    xyah[:, 2] /= xyah[:, 3]
+    g = so.gated_metric(z["g_cost0"], z["g_means"], z["g_covs"], z["g_trk"], xyah, float(z["g_lambda"]),
+                        float(z["g_idw"]))
+    np.testing.assert_allclose(g, z["g_gated"], rtol=1e-12, atol=0)
+    assert (g < 1.0).sum() > 20 and (g > 500).sum() > 1000          # both sides of the gate are exercised
+    e = so.enhance_cost_matrix(z["g_cost0"], z["g_trk"], z["g_dq"], z["g_dconf"], z["g_dcls"])
+    np.testing.assert_allclose(e, z["g_enh"], rtol=1e-14, atol=0)
+    i = so.iou_cost(z["g_means"], z["g_trk"][:, so.TRK_TSU], tlwh)
+    np.testing.assert_allclose(i, z["g_iou"], rtol=1e-13, atol=1e-15)
+    assert (i == so.INFTY_COST).any() and (i < 1).sum() > 50
+
+
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
 def test_cv8_kalman_oracle_matches_reference_vectors(kind):
     """oracle/kalman.py cv8_* against known-answer vectors generated from the reference's
