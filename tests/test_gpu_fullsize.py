@@ -122,3 +122,39 @@ def test_full_size_batch_properties_embedding_trackers(tracker):
         for j, s in enumerate(pick):
             assert nout[s] == nout2[j]
             assert np.array_equal(out[s, : nout[s]], out2[j, : nout2[j]]), (f, s)
+
+
+@pytest.mark.parametrize("tracker", ["deepocsort", "boosttrack"])
+def test_crowd_density_streams_match_oracle(tracker):
+    """BASELINE configs[4] shape per stream: MOT20-like crowds of ~480 detections per frame (hot-spot
+    clustered, heavy mutual overlap) with 64-d embeddings; every stream equals a private oracle frame
+    by frame.  Caps: 768 tracks x 512 detections per stream (BoostTrack's per-stream tables then fill
+    215 KB of the 227 KB of shared memory)."""
+    from boxmot_b200.engine import BoostTrackEngine, DeepOcSortEngine
+    from boxmot_b200.synth import make_batch
+    from conftest import BOOSTTRACK_YAML, DEEPOCSORT_YAML
+    NS, KC, FR, E, TC, DC = 6, 480, 14, 64, 768, 512
+    if tracker == "deepocsort":
+        from oracle.deepocsort import DeepOcSortOracle as Oracle
+        cls, kw, conf_rtol = DeepOcSortEngine, DEEPOCSORT_YAML, 0.0
+    else:
+        from oracle.boosttrack import BoostTrackOracle as Oracle
+        cls, kw, conf_rtol = BoostTrackEngine, BOOSTTRACK_YAML, 1e-9
+    dets, nd, embs = make_batch(NS, KC, FR, DC, emb_dim=E, crowd=True, first_stream=2000)
+    assert nd.max() > 470
+    eng = cls(NS, track_cap=TC, det_cap=DC, emb_dim=E, **kw)
+    oracles = [Oracle(**kw) for _ in range(NS)]
+    d_dets = torch.as_tensor(dets.astype(np.float32)).cuda()
+    d_nd = torch.as_tensor(nd).cuda()
+    d_embs = torch.as_tensor(embs).cuda()
+    total = 0
+    for f in range(FR):
+        out, nout = eng.step(d_dets[f], d_nd[f], d_embs[f])
+        out, nout = out.cpu().numpy(), nout.cpu().numpy()
+        for s in range(NS):
+            n = nd[f, s]
+            want = oracles[s].update(dets[f, s, :n], None, embs[f, s, :n].copy())
+            assert_rows_match(out[s, : nout[s]], want, f, conf_rtol=conf_rtol)
+            total += len(want)
+    eng.status()
+    assert total > 5000
