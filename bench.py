@@ -81,6 +81,8 @@ def parse():
     ap.add_argument("--objects", type=int, default=None, help="default 100 (botsort: 200)")
     ap.add_argument("--det-cap", type=int, default=None, help="default 128 (botsort: 256)")
     ap.add_argument("--track-cap", type=int, default=None, help="default 256 (botsort: 512)")
+    ap.add_argument("--groups", type=int, default=None,
+                    help="independent stream groups stepped on CUDA streams of their own (engine.set_stream_groups)")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between steps")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -95,6 +97,9 @@ def parse():
     if not emb:
         a.emb_dim = 0
     return a
+
+
+DEFAULT_GROUPS = {"ocsort": 2, "deepocsort": 4, "boosttrack": 4}      # tracker -> stream groups per engine step (measured optimum; 1 = one chain of launches)
 
 
 # --------------------------------------------------------------------------- inputs
@@ -364,6 +369,9 @@ def run_gpu_arm(args):
     else:
         eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
     n_kernels = 6 if deep else 7 if boost else 3 if bot else 1 if byte else 4
+    groups = 1
+    if hasattr(eng, "set_stream_groups"):
+        groups = eng.set_stream_groups(args.groups if args.groups is not None else DEFAULT_GROUPS.get(args.tracker, 1))
     knames = KERNEL_NAMES.get(args.tracker)
     d_embs = None
     if bot:                              # device-resident embeddings, uploaded frame by frame (tens of GB)
@@ -567,8 +575,10 @@ def run_gpu_arm(args):
                                     "IoU + fuse_score cost, three thresholded lapjv-exact assignments per frame "
                                     "(tracker of BASELINE configs[0] on the configs[1] streams)" if byte else
                                     "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
-                                    "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])") % (S, args.objects, F),
+                                    "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])").replace("512-d", "%d-d" % args.emb_dim) % (S, args.objects, F),
                        "tracker": args.tracker,
+                       "emb_dim": args.emb_dim if args.tracker in ("botsort", "deepocsort", "boosttrack") else 0,
+                       "stream_groups": groups,
                        "streams_per_gpu": S, "objects": args.objects, "frames": F, "det_cap": args.det_cap,
                        "track_cap": args.track_cap, "partition": "streams sharded by rank, no data-path collective",
                        "l2": "no flush" if args.no_flush else "L2 flushed (252 MB memset) between timed steps, outside the event pairs"},
@@ -584,7 +594,7 @@ def run_gpu_arm(args):
                                    "byte_step_kernel" if byte else
                                    "frame step = ocs_predict + ocs_assoc + ocs_update + ocs_finalize",
                          "alg_bytes_per_launch": nbytes / K, "avg_launch_ms": ms_dev / K},
-            "gpu_launches": n_kernels * K * (2 if not args.no_e2e else 1),
+            "gpu_launches": n_kernels * groups * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }

@@ -112,6 +112,8 @@ _SIGS = {
                                       c_void_p]),
     "bm_min_cost_matching_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double,
                                            c_void_p, c_void_p, c_void_p]),
+    "bm_ocsort_set_groups": (c_int, [c_void_p, c_int]),
+    "bm_boosttrack_set_groups": (c_int, [c_void_p, c_int]),
     "bm_strongsort_gated_metric": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double,
                                            c_double, c_void_p]),
     "bm_strongsort_enhance_cost": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),

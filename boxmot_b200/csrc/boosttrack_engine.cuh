@@ -49,6 +49,21 @@ struct BoostState {
     const double* powtab;   // [npow] 0.9^k evaluated by the host's libm (KalmanBoxTracker.get_confidence)
 };
 
+// Streams [s0, s0 + n) as an engine of their own (every array is stream-major); see ocs_substate.
+inline BoostState bt_substate(const BoostState& st, int s0, int n, int E) {
+    BoostState g = st;
+    const size_t o = (size_t)s0, T = st.Tcap, D = st.Dcap;
+    g.S = n;
+    g.xP += o * BTX_N * T;  g.confcls += o * 2 * T;  g.ints += o * BTI_COUNT * T;  g.order += o * T;
+    g.hdr += o * BTH_COUNT;  g.n_updates += o;  g.tp += o * TP_COUNT * T;
+    g.dconf += o * D;  g.hsel += o * D;  g.cost += o * st.cost_stride;
+    g.upd += o * 2 * D;  g.born += o * D;
+    if (st.bornslot) g.bornslot += o * D;
+    if (st.emb) g.emb += o * T * E;
+    if (st.embsim) g.embsim += o * D * T;
+    return g;
+}
+
 struct BoostView {
     double *xP, *confcls;
     int *ints, *order, *hdr;

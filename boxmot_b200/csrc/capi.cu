@@ -28,6 +28,45 @@ int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
         if (e_ != cudaSuccess) return fail(-2, #call, e_);    \
     } while (0)
 
+// Independent groups of streams stepped on their own CUDA streams: fork from the caller's stream,
+// one chain of launches per group, join back.  The per-stream phases of a frame are short and
+// dependent (predict -> associate -> update -> finalize), and the association kernel ends with its
+// slowest CTA; with groups, one group's streaming kernels run under another group's tail.
+struct StreamGroups {
+    int n = 1;
+    std::vector<cudaStream_t> streams;
+    std::vector<cudaEvent_t> done;
+    cudaEvent_t fork = nullptr;
+    int set(int groups, int S) {
+        clear();
+        groups = groups < 1 ? 1 : (groups > S ? (S > 0 ? S : 1) : groups);
+        if (groups > 1) {
+            if (cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) != cudaSuccess) return -1;
+            for (int g = 0; g < groups; g++) {
+                cudaStream_t st; cudaEvent_t ev;
+                if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return -1;
+                streams.push_back(st);
+                if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return -1;
+                done.push_back(ev);
+            }
+        }
+        n = groups;
+        return 0;
+    }
+    void clear() {
+        for (cudaStream_t st : streams) cudaStreamDestroy(st);
+        for (cudaEvent_t ev : done) cudaEventDestroy(ev);
+        if (fork) cudaEventDestroy(fork);
+        streams.clear(); done.clear(); fork = nullptr; n = 1;
+    }
+    // streams [first, first + count) of group g out of S
+    static void span(int g, int n, int S, int* first, int* count) {
+        const int base = S / n, rem = S % n;
+        *first = g * base + (g < rem ? g : rem);
+        *count = base + (g < rem ? 1 : 0);
+    }
+};
+
 struct OcsEngine {
     bm::OcsState st;
     bm::OcsParams pr;
@@ -36,6 +75,7 @@ struct OcsEngine {
     cudaEvent_t ev[7];
     bool timing = false, timed = false;
     bool deep = false;
+    StreamGroups grp;
 };
 
 struct ByteEngine {      // ByteTrack and BoT-SORT share the state layout and the step kernel
@@ -51,6 +91,7 @@ struct BoostEngine {
     std::vector<void*> allocs;
     cudaEvent_t ev[7];
     bool timing = false, timed = false;
+    StreamGroups grp;
 };
 
 template <typename E, typename T>
@@ -155,8 +196,28 @@ int bm_deepocsort_step(void* handle, const float* d_dets, const int* d_ndets, co
     if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_deepocsort_step: null argument");
     if (!e->deep) return fail(-1, "bm_deepocsort_step: not a DeepOCSORT engine");
     if (e->pr.emb_on && !d_embs) return fail(-1, "bm_deepocsort_step: embeddings required unless embedding_off");
-    BM_CUDA(bm::deepocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
-                                       static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    cudaStream_t main = static_cast<cudaStream_t>(stream);
+    if (e->grp.n > 1 && !e->timing) {
+        const bm::OcsState& st = e->st;
+        const size_t D = st.Dcap, orow = (size_t)(st.Tcap < st.Dcap ? st.Tcap : st.Dcap) * 8;
+        BM_CUDA(cudaEventRecord(e->grp.fork, main));
+        for (int g = 0; g < e->grp.n; g++) {
+            int s0, n;
+            StreamGroups::span(g, e->grp.n, st.S, &s0, &n);
+            cudaStream_t gs = e->grp.streams[g];
+            BM_CUDA(cudaStreamWaitEvent(gs, e->grp.fork, 0));
+            BM_CUDA(bm::deepocsort_step_launch(bm::ocs_substate(st, s0, n, e->pr.E), e->pr, d_dets + s0 * D * 6,
+                                               d_ndets + s0, d_embs ? d_embs + s0 * D * e->pr.E : nullptr,
+                                               d_warps ? d_warps + (size_t)s0 * 6 : nullptr, d_out + s0 * orow,
+                                               d_nout + s0, gs, nullptr));
+            BM_CUDA(cudaEventRecord(e->grp.done[g], gs));
+            BM_CUDA(cudaStreamWaitEvent(main, e->grp.done[g], 0));
+        }
+        e->timed = false;
+        return 0;
+    }
+    BM_CUDA(bm::deepocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout, main,
+                                       e->timing ? e->ev : nullptr));
     e->timed = e->timing;
     return 0;
 }
@@ -174,6 +235,7 @@ int bm_ocsort_destroy(void* handle) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e) return 0;
     if (e->timing) for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
+    e->grp.clear();
     for (void* p : e->allocs) cudaFree(p);
     delete e;
     return 0;
@@ -200,10 +262,34 @@ int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_ocsort_step: null argument");
     if (e->deep) return fail(-1, "bm_ocsort_step: DeepOCSORT engine (use bm_deepocsort_step)");
-    BM_CUDA(bm::ocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout,
-                                   static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    cudaStream_t main = static_cast<cudaStream_t>(stream);
+    if (e->grp.n > 1 && !e->timing) {
+        const bm::OcsState& st = e->st;
+        const size_t D = st.Dcap, orow = (size_t)(st.Tcap < st.Dcap ? st.Tcap : st.Dcap) * 8;
+        BM_CUDA(cudaEventRecord(e->grp.fork, main));
+        for (int g = 0; g < e->grp.n; g++) {
+            int s0, n;
+            StreamGroups::span(g, e->grp.n, st.S, &s0, &n);
+            cudaStream_t gs = e->grp.streams[g];
+            BM_CUDA(cudaStreamWaitEvent(gs, e->grp.fork, 0));
+            BM_CUDA(bm::ocsort_step_launch(bm::ocs_substate(st, s0, n, 0), e->pr, d_dets + s0 * D * 6, d_ndets + s0,
+                                           d_out + s0 * orow, d_nout + s0, gs, nullptr));
+            BM_CUDA(cudaEventRecord(e->grp.done[g], gs));
+            BM_CUDA(cudaStreamWaitEvent(main, e->grp.done[g], 0));
+        }
+        e->timed = false;
+        return 0;
+    }
+    BM_CUDA(bm::ocsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_out, d_nout, main, e->timing ? e->ev : nullptr));
     e->timed = e->timing;
     return 0;
+}
+
+int bm_ocsort_set_groups(void* handle, int groups) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    if (e->grp.set(groups, e->st.S) != 0) return fail(-2, "bm_ocsort_set_groups: stream / event creation failed");
+    return e->grp.n;
 }
 
 int bm_ocsort_time_kernels(void* handle, int enable) {
@@ -388,6 +474,7 @@ int bm_boosttrack_destroy(void* handle) {
     BoostEngine* e = static_cast<BoostEngine*>(handle);
     if (!e) return 0;
     if (e->timing) for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
+    e->grp.clear();
     for (void* p : e->allocs) cudaFree(p);
     delete e;
     return 0;
@@ -413,10 +500,37 @@ int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, co
     BoostEngine* e = static_cast<BoostEngine*>(handle);
     if (!e || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_boosttrack_step: null argument");
     if (e->pr.with_reid && !d_embs) return fail(-1, "bm_boosttrack_step: with_reid needs embeddings");
-    BM_CUDA(bm::boosttrack_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
-                                       static_cast<cudaStream_t>(stream), e->timing ? e->ev : nullptr));
+    cudaStream_t main = static_cast<cudaStream_t>(stream);
+    if (e->grp.n > 1 && !e->timing) {
+        const bm::BoostState& st = e->st;
+        const size_t D = st.Dcap, orow = (size_t)(st.Tcap < st.Dcap ? st.Tcap : st.Dcap) * 8;
+        BM_CUDA(cudaEventRecord(e->grp.fork, main));
+        for (int g = 0; g < e->grp.n; g++) {
+            int s0, n;
+            StreamGroups::span(g, e->grp.n, st.S, &s0, &n);
+            cudaStream_t gs = e->grp.streams[g];
+            BM_CUDA(cudaStreamWaitEvent(gs, e->grp.fork, 0));
+            BM_CUDA(bm::boosttrack_step_launch(bm::bt_substate(st, s0, n, e->pr.E), e->pr, d_dets + s0 * D * 6,
+                                               d_ndets + s0, d_embs ? d_embs + s0 * D * e->pr.E : nullptr,
+                                               d_warps ? d_warps + (size_t)s0 * 6 : nullptr, d_out + s0 * orow,
+                                               d_nout + s0, gs, nullptr));
+            BM_CUDA(cudaEventRecord(e->grp.done[g], gs));
+            BM_CUDA(cudaStreamWaitEvent(main, e->grp.done[g], 0));
+        }
+        e->timed = false;
+        return 0;
+    }
+    BM_CUDA(bm::boosttrack_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout, main,
+                                       e->timing ? e->ev : nullptr));
     e->timed = e->timing;
     return 0;
+}
+
+int bm_boosttrack_set_groups(void* handle, int groups) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e) return fail(-1, "null handle");
+    if (e->grp.set(groups, e->st.S) != 0) return fail(-2, "bm_boosttrack_set_groups: stream / event creation failed");
+    return e->grp.n;
 }
 
 int bm_boosttrack_time_kernels(void* handle, int enable) {

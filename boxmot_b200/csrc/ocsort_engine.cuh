@@ -61,6 +61,30 @@ struct OcsState {
     int* deep_i;                   // [S][3 Dcap + Tcap] row arg-minima, IoU-hit counts per row, hit column, hits per column
 };
 
+// The state of streams [s0, s0 + n) as an engine of its own: every array is stream-major, so a
+// group of streams is the same layout behind offset base pointers.  Used to step independent
+// groups of streams on separate CUDA streams (capi.cu), E = embedding length (0 without).
+inline OcsState ocs_substate(const OcsState& st, int s0, int n, int E) {
+    OcsState g = st;
+    const size_t o = (size_t)s0, T = st.Tcap, D = st.Dcap;
+    g.S = n;
+    g.xP += o * XB_N * T;  g.sxP += o * XB_N * T;
+    g.lastz += o * 4 * T;  g.lastobs += o * 5 * T;  g.vel += o * 2 * T;  g.confcls += o * 2 * T;
+    g.ring += o * st.R * 4 * T;  g.ring_age += o * st.R * T;
+    g.ints += o * OI_COUNT * T;  g.order += o * T;  g.hdr += o * OH_COUNT;  g.n_updates += o;
+    g.scratch += o * st.scratch_elems;  g.abuf += o * AB_COUNT * T;
+    g.upd += o * 2 * D;  g.born += o * D;  g.hsel += o * 2 * D;
+    if (st.prof) g.prof += o * 8;
+    if (st.emb) g.emb += o * T * E;
+    if (st.embsim) g.embsim += o * D * T;
+    if (st.bornslot) g.bornslot += o * D;
+    if (st.epos) g.epos += o * T;
+    if (st.wbuf) g.wbuf += o * (D + T);
+    if (st.deep_d) g.deep_d += o * (D + 1);
+    if (st.deep_i) g.deep_i += o * (3 * D + T);
+    return g;
+}
+
 struct OcsView {   // per-stream base pointers
     double *xP, *sxP, *lastz, *lastobs, *vel, *confcls, *ring;
     int *ring_age, *ints, *order, *hdr;

@@ -136,6 +136,15 @@ class OcSortEngine(_HostStepMixin):
                                                      _stream_ptr(self.device)), "bm_ocsort_counters")
         return dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
 
+    def set_stream_groups(self, groups):
+        """Step the streams as ``groups`` independent groups on CUDA streams of their own (forked
+        from / joined into the current stream inside ``step``); returns the number in use."""
+        n = _lib.lib().bm_ocsort_set_groups(self._h, int(groups))
+        if n < 0:
+            _lib.check(n, "bm_ocsort_set_groups")
+        self.groups = n
+        return n
+
     def stream_info(self):
         """(live tracks [S], tracks created so far [S]) as int32 arrays (synchronises)."""
         n = np.zeros((self.S,), dtype=np.int32)
@@ -349,6 +358,14 @@ class BoostTrackEngine:
 
     def status(self, raise_on_error=True):
         return self.counters(raise_on_error)
+
+    def set_stream_groups(self, groups):
+        """See OcSortEngine.set_stream_groups."""
+        n = _lib.lib().bm_boosttrack_set_groups(self._h, int(groups))
+        if n < 0:
+            _lib.check(n, "bm_boosttrack_set_groups")
+        self.groups = n
+        return n
 
     def time_kernels(self, enable=True):
         _lib.check(_lib.lib().bm_boosttrack_time_kernels(self._h, int(bool(enable))), "bm_boosttrack_time_kernels")

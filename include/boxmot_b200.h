@@ -47,6 +47,15 @@ int bm_ocsort_reset(void* handle, void* stream);
  * this frame), d_nout [S] int32. */
 int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
                    int* d_nout, void* stream);
+
+/* Step the engine's streams as `groups` independent groups, each on a CUDA stream of its own
+ * (forked from and joined back into the caller's stream inside bm_ocsort_step /
+ * bm_deepocsort_step): one group's streaming kernels then run under the tail of another group's
+ * association kernel.  Results are unchanged (streams are independent, the reference runs one
+ * tracker object per video: boxmot/engine/track.py:41-53).  groups <= 1 restores the single
+ * chain; per-kernel timing (bm_ocsort_time_kernels) always uses the single chain.  Returns the
+ * number of groups in use, < 0 on error. */
+int bm_ocsort_set_groups(void* handle, int groups);
 /* Synchronises `stream`; returns the OR of all per-stream error bits in *err_bits, the
  * number of live tracks that entered predict since create/reset in *track_updates and
  * the number of lapjv solves in *lap_solves. */
@@ -110,6 +119,8 @@ int bm_boosttrack_reset(void* handle, void* stream);
  * order (tracker list order); the reported confidence is the BOOSTED detection confidence. */
 int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
                        const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* Stream groups for the BoostTrack engine; see bm_ocsort_set_groups. */
+int bm_boosttrack_set_groups(void* handle, int groups);
 /* Synchronises `stream`: OR of the per-stream error bits and cumulative {track_updates,
  * lap_solves, matches, births}. */
 int bm_boosttrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);

@@ -158,3 +158,54 @@ def test_crowd_density_streams_match_oracle(tracker):
             total += len(want)
     eng.status()
     assert total > 5000
+
+
+@pytest.mark.parametrize("tracker", ["ocsort", "deepocsort", "boosttrack"])
+def test_stream_groups_do_not_change_results(tracker):
+    """bm_ocsort_set_groups: the same batch stepped as 1, 3 and 8 groups of streams on CUDA streams of
+    their own gives bit-identical rows and counters (streams are independent; 250 is not a multiple
+    of 3 or 8, so the groups are ragged)."""
+    from boxmot_b200.engine import BoostTrackEngine, DeepOcSortEngine, OcSortEngine
+    from boxmot_b200.synth import make_batch
+    from conftest import BOOSTTRACK_YAML, DEEPOCSORT_YAML, OCSORT_YAML
+    NS, KO, FR, E = 250, 60, 20, 32
+    if tracker == "ocsort":
+        dets, nd = make_batch(NS, KO, FR, 96)
+        embs = None
+    else:
+        dets, nd, embs = make_batch(NS, KO, FR, 96, emb_dim=E)
+    d_dets = torch.as_tensor(dets.astype(np.float32)).cuda()
+    d_nd = torch.as_tensor(nd).cuda()
+    d_embs = None if embs is None else torch.as_tensor(embs).cuda()
+    rng = np.random.default_rng(3)
+    warps = np.zeros((FR, NS, 2, 3))
+    warps[:, :, 0, 0] = 1 + rng.normal(0, 0.004, (FR, NS))
+    warps[:, :, 1, 1] = 1 + rng.normal(0, 0.004, (FR, NS))
+    warps[:, :, :, 2] = rng.normal(0, 2, (FR, NS, 2))
+    d_w = torch.as_tensor(warps).cuda()
+
+    def run(groups):
+        if tracker == "ocsort":
+            eng = OcSortEngine(NS, track_cap=192, det_cap=96, **OCSORT_YAML)
+        elif tracker == "deepocsort":
+            eng = DeepOcSortEngine(NS, track_cap=192, det_cap=96, emb_dim=E, **DEEPOCSORT_YAML)
+        else:
+            eng = BoostTrackEngine(NS, track_cap=192, det_cap=96, emb_dim=E, **BOOSTTRACK_YAML)
+        assert eng.set_stream_groups(groups) == groups
+        rows = []
+        for f in range(FR):
+            out, nout = eng.step(d_dets[f], d_nd[f]) if tracker == "ocsort" else \
+                eng.step(d_dets[f], d_nd[f], d_embs[f], d_w[f])
+            rows.append((out.cpu().numpy().copy(), nout.cpu().numpy().copy()))
+        return rows, eng.status()
+
+    base, st0 = run(1)
+    assert st0["track_updates"] > 0
+    for g in (3, 8):
+        rows, st = run(g)
+        assert st == st0
+        for f in range(FR):
+            assert np.array_equal(rows[f][1], base[f][1])
+            for s in range(NS):
+                n = base[f][1][s]
+                assert np.array_equal(rows[f][0][s, :n], base[f][0][s, :n]), (g, f, s)
