@@ -139,7 +139,8 @@ class OcSortEngine(_HostStepMixin):
     def set_stream_groups(self, groups):
         """Step the streams as ``groups`` independent groups on CUDA streams of their own (forked
         from / joined into the current stream inside ``step``); returns the number in use."""
-        n = _lib.lib().bm_ocsort_set_groups(self._h, int(groups))
+        with torch.cuda.device(self.device):
+            n = _lib.lib().bm_ocsort_set_groups(self._h, int(groups))
         if n < 0:
             _lib.check(n, "bm_ocsort_set_groups")
         self.groups = n
@@ -361,7 +362,8 @@ class BoostTrackEngine:
 
     def set_stream_groups(self, groups):
         """See OcSortEngine.set_stream_groups."""
-        n = _lib.lib().bm_boosttrack_set_groups(self._h, int(groups))
+        with torch.cuda.device(self.device):
+            n = _lib.lib().bm_boosttrack_set_groups(self._h, int(groups))
         if n < 0:
             _lib.check(n, "bm_boosttrack_set_groups")
         self.groups = n

@@ -25,4 +25,9 @@ for f in range(F):
             f, tot.mean(), np.percentile(tot, 99), tot.max(), a[:, 6].max() - a[:, 0].min()))
         for i, n in enumerate(names[:6]):
             print("   %-18s mean %8.0f  p99 %8.0f  max %8.0f" % (n, d[:, i].mean(), np.percentile(d[:, i], 99), d[:, i].max()))
+        worst = np.argsort(-tot)[:8]
+        print("   slowest CTAs (stream: phases):")
+        for w in worst:
+            print("     %4d: %s  nd=%d" % (w, " ".join("%7.0f" % x for x in d[w, :6]), nd[f, w]))
+        print("   lifetime histogram (k cycles):", np.histogram(tot / 1e3, bins=[0, 80, 120, 160, 200, 240, 280, 320, 400, 1000])[0])
 eng.status()
