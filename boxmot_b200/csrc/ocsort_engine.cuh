@@ -27,6 +27,17 @@ struct OcsParams {
     // DeepOCSORT (deepocsort.py:265-314): embedding term of the first round and its EMA
     int emb_on, aw_off, E;         // emb_on = 0 <=> embedding_off
     double w_emb, alpha_fixed, aw_param;
+    int prescreen;                 // run the first-round fp32 screen as its own launch (ocs_screen_kernel)
+};
+
+// Result of the fp32 screen of one first-round row (ocs_screen_kernel -> ocs_assoc_kernel): the
+// columns that must be evaluated exactly, 10 bits each.
+struct ScanRow {
+    unsigned long long ov0, ov1;   // columns whose outward-rounded float box overlaps the detection (<= 12)
+    unsigned long long bf;         // columns whose fp32 OCM cosine is within the band of the row's best (<= 6)
+    int nov, nbf;
+    int zero_t;                    // lowest zero-motion, non-overlapping column (INT_MAX = none)
+    int dense;                     // 1 = evaluate the whole row exactly (degenerate box / list overflow)
 };
 
 struct OcsState {
@@ -51,6 +62,7 @@ struct OcsState {
     int* born;                     // [S][Dcap]    detection rows that start a track, in id order
     long long* prof;               // optional [S][8] clock64 phase stamps of the association kernel (debug)
     int* hsel;                     // [S][2][Dcap] detection rows of the high-score set, then of the BYTE set
+    ScanRow* scan;                 // [S][Dcap]    screened first-round rows (asso_func = iou; valid when hdr[OH_DEEP] == 1)
     // DeepOCSORT only (nullptr in an OC-SORT engine)
     float* emb;                    // [S][Tcap][E]   track embedding by slot (KalmanBoxTracker.emb)
     float* embsim;                 // [S][Dcap][Tcap] dets_embs @ trk_embs.T by (detection row, list position)
@@ -74,6 +86,7 @@ inline OcsState ocs_substate(const OcsState& st, int s0, int n, int E) {
     g.ints += o * OI_COUNT * T;  g.order += o * T;  g.hdr += o * OH_COUNT;  g.n_updates += o;
     g.scratch += o * st.scratch_elems;  g.abuf += o * AB_COUNT * T;
     g.upd += o * 2 * D;  g.born += o * D;  g.hsel += o * 2 * D;
+    if (st.scan) g.scan += o * D;
     if (st.prof) g.prof += o * 8;
     if (st.emb) g.emb += o * T * E;
     if (st.embsim) g.embsim += o * D * T;

@@ -557,64 +557,152 @@ __device__ inline void ocm_scan_rows(const OcmCost& c, const OcmScreen& sc, int 
 // evaluated exactly.  Results are identical to ocm_scan_rows (exact minima, lowest column on
 // ties).
 constexpr int OVL_CAP = 12;
+// The fp32 screen of one row (detection box af) against all nT tracks: one lane, no cross-lane traffic.
+// Phase 1 lists the columns whose outward-rounded float box overlaps the detection and bounds their
+// IoU in fp32.  The OCM term lies in [-|inertia|/2, |inertia|/2] and a disjoint pair has IoU = 0
+// exactly, so once some column's IoU exceeds |inertia| (+0.01: ~1e3 x the fp32 error of the bound)
+// no disjoint column can hold the row minimum: such a "strong" row needs no phase 2.
+__device__ __forceinline__ bool ocm_lane_overlaps(const float4 af, const OcmScreen& sc, int nT, float strong_thr,
+                                                  ScanRow& r) {
+    bool dense = !(((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x);
+    const float aa = (af.z - af.x) * (af.w - af.y);
+    unsigned long long ov0 = 0, ov1 = 0;
+    int nov = 0;
+    float best = 0.f;
+#pragma unroll 4
+    for (int t = 0; t < nT; t++) {
+        const float4 b = sc.boxf[t];
+        if (af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w) {
+            if (nov < 6) ov0 |= (unsigned long long)t << (10 * nov);
+            else if (nov < OVL_CAP) ov1 |= (unsigned long long)t << (10 * (nov - 6));
+            nov++;
+            const float inter = (fminf(af.z, b.z) - fmaxf(af.x, b.x)) * (fminf(af.w, b.w) - fmaxf(af.y, b.y));
+            best = fmaxf(best, __fdividef(inter, aa + (b.z - b.x) * (b.w - b.y) - inter));
+        }
+    }
+    if (nov > OVL_CAP) dense = true;
+    r.ov0 = ov0; r.ov1 = ov1; r.bf = 0; r.nov = nov; r.nbf = 0; r.zero_t = 0x7fffffff; r.dense = dense ? 1 : 0;
+    return best > strong_thr;
+}
+// Phase 2 (rows without a strong overlap): the disjoint columns whose fp32 OCM cosine is within
+// OCM_BAND of the row's best, and the lowest zero-motion column.
+__device__ __forceinline__ void ocm_lane_band(const float4 af, const OcmScreen& sc, int nT, ScanRow& r) {
+    const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
+    const float cxh = (float)cxd, cyh = (float)cyd;
+    const float cxl = (float)(cxd - (double)cxh), cyl = (float)(cyd - (double)cyh);
+    unsigned long long bl = 0;
+    int nb = 0, zero_t = 0x7fffffff;
+    float runmax = -CUDART_INF_F;
+#pragma unroll 4
+    for (int t = 0; t < nT; t++) {
+        const float4 b = sc.boxf[t];
+        const float2 mv = sc.mvf[t];
+        const float4 kc = sc.kc[t];
+        if (af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w) {
+            // listed by phase 1
+        } else if (mv.x == 0.f && mv.y == 0.f) {
+            zero_t = min(zero_t, t);
+        } else {
+            const float cs = ocm_screen_cos(kc, mv, cxh, cxl, cyh, cyl);
+            if (cs >= runmax - OCM_BAND) {
+                bl = (bl << 10) | (unsigned long long)t;
+                nb++;
+                runmax = fmaxf(runmax, cs);
+            }
+        }
+    }
+    const float lim = runmax - OCM_BAND;
+    const int nbk = min(nb, 6);
+    if (nb > 6) {
+        // the oldest retained column bounds (within one band) everything shifted out before it
+        const int t5 = (int)((bl >> 50) & 1023u);
+        if (ocm_screen_cos(sc.kc[t5], sc.mvf[t5], cxh, cxl, cyh, cyl) >= lim - OCM_BAND) r.dense = 1;
+    }
+    // survivors of the band filter (fp32 value against the FINAL maximum)
+    unsigned long long bf = 0;
+    int nbf = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        if (k < nbk) {
+            const int t = (int)((bl >> (10 * k)) & 1023u);
+            if (ocm_screen_cos(sc.kc[t], sc.mvf[t], cxh, cxl, cyh, cyl) >= lim) {
+                bf |= (unsigned long long)t << (10 * nbf);
+                nbf++;
+            }
+        }
+    }
+    r.bf = bf; r.nbf = nbf; r.zero_t = zero_t;
+}
+__device__ __forceinline__ float ocm_strong_thr(double inertia) { return (float)fabs(inertia) + 0.01f; }
+// Both phases in ONE walk over the tracks, for the association CTA's own screen: there the 32 rows of
+// a warp are walked together, so a second, divergent walk for the few weak rows would cost every lane.
+__device__ __forceinline__ ScanRow ocm_lane_screen(const float4 af, const OcmScreen& sc, int nT) {
+    const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
+    const float cxh = (float)cxd, cyh = (float)cyd;
+    const float cxl = (float)(cxd - (double)cxh), cyl = (float)(cyd - (double)cyh);
+    ScanRow r;
+    r.dense = !(((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x) ? 1 : 0;
+    unsigned long long ov0 = 0, ov1 = 0, bl = 0;
+    int nov = 0, nb = 0, zero_t = 0x7fffffff;
+    float runmax = -CUDART_INF_F;
+#pragma unroll 4
+    for (int t = 0; t < nT; t++) {
+        const float4 b = sc.boxf[t];
+        const float2 mv = sc.mvf[t];
+        const float4 kc = sc.kc[t];
+        if (af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w) {
+            if (nov < 6) ov0 |= (unsigned long long)t << (10 * nov);
+            else if (nov < OVL_CAP) ov1 |= (unsigned long long)t << (10 * (nov - 6));
+            nov++;
+        } else if (mv.x == 0.f && mv.y == 0.f) {
+            zero_t = min(zero_t, t);
+        } else {
+            const float cs = ocm_screen_cos(kc, mv, cxh, cxl, cyh, cyl);
+            if (cs >= runmax - OCM_BAND) {
+                bl = (bl << 10) | (unsigned long long)t;
+                nb++;
+                runmax = fmaxf(runmax, cs);
+            }
+        }
+    }
+    if (nov > OVL_CAP) r.dense = 1;
+    const float lim = runmax - OCM_BAND;
+    const int nbk = min(nb, 6);
+    if (nb > 6) {
+        const int t5 = (int)((bl >> 50) & 1023u);
+        if (ocm_screen_cos(sc.kc[t5], sc.mvf[t5], cxh, cxl, cyh, cyl) >= lim - OCM_BAND) r.dense = 1;
+    }
+    unsigned long long bf = 0;
+    int nbf = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        if (k < nbk) {
+            const int t = (int)((bl >> (10 * k)) & 1023u);
+            if (ocm_screen_cos(sc.kc[t], sc.mvf[t], cxh, cxl, cyh, cyl) >= lim) {
+                bf |= (unsigned long long)t << (10 * nbf);
+                nbf++;
+            }
+        }
+    }
+    r.ov0 = ov0; r.ov1 = ov1; r.bf = bf; r.nov = nov; r.nbf = nbf; r.zero_t = zero_t;
+    return r;
+}
+
+// pre: rows screened by ocs_screen_kernel (nullptr = screen here, with the CTA's own tables)
 __device__ inline void ocm_scan_rows_lane(const OcmCost& c, const OcmScreen& sc, int nD, int nT, double iou_thr,
                                           int* colcnt, double* rmin, int* rarg, int* rowcnt, int* hit_t,
-                                          int* scratch /*[3 * LANE_CAND] per warp, 8-byte aligned*/) {
+                                          int* scratch /*[3 * LANE_CAND] per warp, 8-byte aligned*/,
+                                          const ScanRow* __restrict__ pre = nullptr) {
     const int lane = lane_id(), wid = warp_id(), NW = blockDim.x >> 5;
     double* cres = reinterpret_cast<double*>(scratch);
     int* clist = scratch + 2 * LANE_CAND;
     for (int r0 = 32 * wid; r0 < nD; r0 += 32 * NW) {
         const int d = r0 + lane;
         const bool live = d < nD;
-        const float4 af = c.dbox[live ? d : r0];
-        const double cxd = ((double)af.x + (double)af.z) / 2.0, cyd = ((double)af.y + (double)af.w) / 2.0;
-        const float cxh = (float)cxd, cyh = (float)cyd;
-        const float cxl = (float)(cxd - (double)cxh), cyl = (float)(cyd - (double)cyh);
-        bool dense = !(((double)af.z - (double)af.x) * ((double)af.w - (double)af.y) > 0.0 && af.z > af.x);
-        unsigned long long ov0 = 0, ov1 = 0, bl = 0;
-        int nov = 0, nb = 0, zero_t = 0x7fffffff;
-        float runmax = -CUDART_INF_F;
-#pragma unroll 4
-        for (int t = 0; t < nT; t++) {
-            const float4 b = sc.boxf[t];
-            const float2 mv = sc.mvf[t];
-            const float4 kc = sc.kc[t];
-            if (af.x < b.z && b.x < af.z && af.y < b.w && b.y < af.w) {
-                if (nov < 6) ov0 |= (unsigned long long)t << (10 * nov);
-                else if (nov < OVL_CAP) ov1 |= (unsigned long long)t << (10 * (nov - 6));
-                nov++;
-            } else if (mv.x == 0.f && mv.y == 0.f) {
-                zero_t = min(zero_t, t);
-            } else {
-                const float cs = ocm_screen_cos(kc, mv, cxh, cxl, cyh, cyl);
-                if (cs >= runmax - OCM_BAND) {
-                    bl = (bl << 10) | (unsigned long long)t;
-                    nb++;
-                    runmax = fmaxf(runmax, cs);
-                }
-            }
-        }
-        if (nov > OVL_CAP) dense = true;
-        const float lim = runmax - OCM_BAND;
-        const int nbk = min(nb, 6);
-        if (nb > 6) {
-            // the oldest retained column bounds (within one band) everything shifted out before it
-            const int t5 = (int)((bl >> 50) & 1023u);
-            if (ocm_screen_cos(sc.kc[t5], sc.mvf[t5], cxh, cxl, cyh, cyl) >= lim - OCM_BAND) dense = true;
-        }
-        // survivors of the band filter (fp32 value against the FINAL maximum)
-        unsigned long long bf = 0;
-        int nbf = 0;
-#pragma unroll
-        for (int k = 0; k < 6; k++) {
-            if (k < nbk) {
-                const int t = (int)((bl >> (10 * k)) & 1023u);
-                if (ocm_screen_cos(sc.kc[t], sc.mvf[t], cxh, cxl, cyh, cyl) >= lim) {
-                    bf |= (unsigned long long)t << (10 * nbf);
-                    nbf++;
-                }
-            }
-        }
+        const ScanRow sr = pre ? pre[live ? d : r0] : ocm_lane_screen(c.dbox[live ? d : r0], sc, nT);
+        const unsigned long long ov0 = sr.ov0, ov1 = sr.ov1, bf = sr.bf;
+        const int nov = sr.nov, nbf = sr.nbf, zero_t = sr.zero_t;
+        const bool dense = sr.dense != 0;
         // ---- exact evaluation: the warp's candidates are pooled in shared memory so that all
         // 32 lanes evaluate (the fp64 entry is a long dependent chain), then every lane folds
         // the results of its own row; LANE_CAND candidates per round
@@ -971,11 +1059,13 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
     scr.kc = scr.boxf + Tcap;
     scr.mvf = reinterpret_cast<float2*>(scr.kc + Tcap);
     scr.cs = reinterpret_cast<float*>(scr.mvf + Tcap);
+    // rows already screened by ocs_screen_kernel (which also saw that no prediction is NaN)
+    const bool prescreened = !DEEP && pr.prescreen && pr.asso_func == ASSO_IOU && st.scan != nullptr && v.hdr[OH_DEEP] == 1;
     for (int p = tid; p < nT; p += K2_NT) {
         sm.slot_of[p] = v.order[p];
         sm.t2d[p] = -1;
         sm.colcnt[p] = 0;
-        if (ocm_screen_fill(ocm, scr, p)) sm.misc[M_ANYBAD] = 1;
+        if (!prescreened && ocm_screen_fill(ocm, scr, p)) sm.misc[M_ANYBAD] = 1;
     }
     __syncthreads();
     if (sm.misc[M_ANYBAD]) {   // NaN prediction: the reference drops the track (ocsort.py:284-288)
@@ -1023,7 +1113,7 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
             }
         } else if (pr.asso_func == ASSO_IOU)
             ocm_scan_rows_lane(ocm, scr, nD, nT, pr.iou_thr, sm.colcnt, sm.rmin, sm.rarg, sm.rowcnt, sm.hit_t,
-                               sm.cand + ocs_cand_ints(Tcap) * wid);
+                               sm.cand + ocs_cand_ints(Tcap) * wid, prescreened ? st.scan + (size_t)s * Dcap : nullptr);
         else
             ocm_scan_rows(ocm, scr, nD, nT, pr.iou_thr, sm.cand + ocs_cand_ints(Tcap) * wid, sm.colcnt, sm.rmin, sm.rarg,
                           sm.rowcnt, sm.hit_t, sm.um_d);
@@ -1204,6 +1294,66 @@ __device__ __forceinline__ void ocs_assoc_cta(const OcsState& st, const OcsParam
         if (sm.misc[M_LAPBAD]) atomicOr(&v.hdr[OH_ERR], 8);
         BM_STAMP(6);
 #undef BM_STAMP
+    }
+}
+
+// ============================================================================ K2a
+// fp32 screen of the first-round rows as its own launch (asso_func = iou): one lane per detection
+// row walks all tracks of its stream against shared-memory tables and leaves the few columns that
+// need an exact fp64 evaluation in st.scan.  <= 64 registers x 128 threads: every stream of a
+// 1024-stream batch is resident at once with all rows of a frame in ONE pass, instead of two
+// passes on the two warps of the register-heavy association CTA.  Phase 1 (every row) only tests
+// box overlap; the rows left without a strong overlap (false positives, new objects: ~10 %) are
+// packed onto the first lanes for the OCM band search (phase 2).  A stream with a NaN prediction
+// (the association kernel drops that track first) or nothing to match is left alone:
+// hdr[OH_DEEP] = 0 and the association kernel screens for itself.
+constexpr int KS_NT = 128;
+__host__ __device__ inline size_t ocs_screen_smem(int Tcap, int Dcap) {
+    return ocm_screen_bytes(Tcap, 0) + 16 + 4 * (size_t)Dcap;
+}
+__global__ void __launch_bounds__(KS_NT, 8)
+ocs_screen_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int s = blockIdx.x, tid = threadIdx.x;
+    const int Tcap = st.Tcap, Dcap = st.Dcap;
+    int* hdr = st.hdr + (size_t)s * OH_COUNT;
+    const int nD = hdr[OH_ND], nT = hdr[OH_NLIST];
+    OcmScreen scr;
+    scr.boxf = reinterpret_cast<float4*>(smem_raw);
+    scr.kc = scr.boxf + Tcap;
+    scr.mvf = reinterpret_cast<float2*>(scr.kc + Tcap);
+    scr.cs = nullptr;
+    int* bad = reinterpret_cast<int*>(scr.mvf + Tcap);     // [0] NaN prediction seen, [1] queued rows
+    int* nweak = bad + 1;
+    int* weak = bad + 4;
+    if (tid == 0) { bad[0] = 0; bad[1] = 0; }
+    __syncthreads();
+    const OcmCost ocm = {nullptr, st.abuf + (size_t)s * AB_COUNT * Tcap, Tcap, pr.asso_func, pr.diag, pr.inertia};
+    for (int p = tid; p < nT; p += KS_NT)
+        if (ocm_screen_fill(ocm, scr, p)) bad[0] = 1;
+    __syncthreads();
+    const bool ok = nD > 0 && nT > 0 && bad[0] == 0;
+    if (tid == 0) hdr[OH_DEEP] = ok ? 1 : 0;
+    if (!ok) return;
+    const int* hs = st.hsel + (size_t)s * 2 * Dcap;
+    const float* dsrc = dets + (size_t)s * Dcap * 6;
+    ScanRow* out = st.scan + (size_t)s * Dcap;
+    const float thr = ocm_strong_thr(pr.inertia);
+    for (int d = tid; d < nD; d += KS_NT) {
+        const int i = hs[d];
+        const float4 af = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
+        ScanRow r;
+        if (!ocm_lane_overlaps(af, scr, nT, thr, r) && !r.dense) weak[atomicAdd(nweak, 1)] = d;
+        out[d] = r;
+    }
+    __syncthreads();
+    const int nw = *nweak;
+    for (int k = tid; k < nw; k += KS_NT) {
+        const int d = weak[k], i = hs[d];
+        const float4 af = make_float4(dsrc[i * 6 + 0], dsrc[i * 6 + 1], dsrc[i * 6 + 2], dsrc[i * 6 + 3]);
+        ScanRow r = out[d];
+        ocm_lane_band(af, scr, nT, r);
+        out[d] = r;
     }
 }
 
@@ -1437,6 +1587,8 @@ cudaError_t ocsort_step_configure(size_t smem) {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(ocs_assoc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(ocs_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(deep_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cosine_tc_kernel<DeepDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1464,6 +1616,10 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
     ocs_predict_kernel<false><<<st.S * c1 + (st.S + K1_NT / 32 - 1) / (K1_NT / 32), K1_NT, 0, stream>>>(st, pr, dets, ndets, nullptr);
     if ((e = dbg_check("ocs_predict_kernel", stream)) != cudaSuccess) return e;
     BM_EV(1);
+    if (pr.prescreen && pr.asso_func == ASSO_IOU && st.scan) {
+        ocs_screen_kernel<<<st.S, KS_NT, ocs_screen_smem(st.Tcap, st.Dcap), stream>>>(st, pr, dets);
+        if ((e = dbg_check("ocs_screen_kernel", stream)) != cudaSuccess) return e;
+    }
     ocs_assoc_kernel<false><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel", stream)) != cudaSuccess) return e;
     BM_EV(2);

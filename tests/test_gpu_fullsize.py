@@ -209,3 +209,39 @@ def test_stream_groups_do_not_change_results(tracker):
             for s in range(NS):
                 n = base[f][1][s]
                 assert np.array_equal(rows[f][0][s, :n], base[f][0][s, :n]), (g, f, s)
+
+
+def test_prescreen_launch_does_not_change_results(monkeypatch):
+    """ocs_screen_kernel (the first-round fp32 screen as its own launch, default for batches of more
+    than 1536 streams; BM_PRESCREEN forces it): rows and counters bit-identical to the in-kernel
+    screen, and a sample of streams equals the oracle."""
+    from boxmot_b200.engine import OcSortEngine
+    from boxmot_b200.synth import make_batch
+    from conftest import OCSORT_YAML
+    from oracle.ocsort import OcSortOracle
+    NS, KO, FR = 96, 100, 30
+    dets, nd = make_batch(NS, KO, FR, 128, first_stream=300)
+    d_dets = torch.as_tensor(dets.astype(np.float32)).cuda()
+    d_nd = torch.as_tensor(nd).cuda()
+
+    def run(flag):
+        monkeypatch.setenv("BM_PRESCREEN", flag)
+        eng = OcSortEngine(NS, track_cap=256, det_cap=128, **OCSORT_YAML)
+        rows = []
+        for f in range(FR):
+            out, nout = eng.step(d_dets[f], d_nd[f])
+            rows.append((out.cpu().numpy().copy(), nout.cpu().numpy().copy()))
+        return rows, eng.status()
+
+    base, st0 = run("0")
+    rows, st1 = run("1")
+    assert st0 == st1 and st0["track_updates"] > 0
+    oracles = {s: OcSortOracle(**OCSORT_YAML) for s in (0, 41, 95)}
+    for f in range(FR):
+        assert np.array_equal(rows[f][1], base[f][1])
+        for s in range(NS):
+            n = base[f][1][s]
+            assert np.array_equal(rows[f][0][s, :n], base[f][0][s, :n]), (f, s)
+        for s, o in oracles.items():
+            want = o.update(dets[f, s, : nd[f, s]])
+            assert_rows_match(rows[f][0][s, : rows[f][1][s]], want, f)
