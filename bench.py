@@ -42,7 +42,7 @@ BOOSTTRACK_YAML = dict(max_age=60, min_hits=3, det_thresh=0.6, iou_threshold=0.3
                        use_sb=True, use_vt=True, with_reid=True)   # boxmot/configs/trackers/boosttrack.yaml defaults
 EMB_TRACKERS = ("botsort", "deepocsort", "boosttrack")
 KERNEL_NAMES = {
-    "ocsort": ("ocs_predict_kernel", "ocs_screen_kernel+ocs_assoc_kernel", "ocs_update_kernel", "ocs_finalize_kernel"),
+    "ocsort": ("ocs_predict_kernel", "ocs_assoc_kernel", "ocs_update_kernel", "ocs_finalize_kernel"),
     "deepocsort": ("ocs_predict_kernel<deep>", "cosine_tc_kernel<DeepDot>", "ocs_assoc_kernel<deep>",
                    "ocs_update_kernel", "ocs_finalize_kernel", "docs_emb_kernel"),
     "boosttrack": ("bt_predict_kernel", "bt_boost_kernel", "cosine_tc_kernel<BoostDot>",
@@ -368,7 +368,10 @@ def run_gpu_arm(args):
         eng = ByteTrackEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **BYTETRACK_YAML)
     else:
         eng = OcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, **OCSORT_YAML)
-    n_kernels = 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5
+    # OC-SORT batches of more than 1536 streams run the first-round screen as a fifth launch (capi.cu ocs_create)
+    prescreen = (not (deep or boost or bot or byte)) and (
+        os.environ.get("BM_PRESCREEN", "1" if S > 1536 else "0")[:1] == "1")
+    n_kernels = 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5 if prescreen else 4
     groups = 1
     if hasattr(eng, "set_stream_groups"):
         groups = eng.set_stream_groups(args.groups if args.groups is not None else DEFAULT_GROUPS.get(args.tracker, 1))
@@ -592,7 +595,7 @@ def run_gpu_arm(args):
                          "kernel": "frame step = " + " + ".join(knames) if (deep or boost) else
                                    "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
                                    "byte_step_kernel" if byte else
-                                   "frame step = ocs_predict + ocs_screen + ocs_assoc + ocs_update + ocs_finalize",
+                                   "frame step = ocs_predict + %socs_assoc + ocs_update + ocs_finalize" % ("ocs_screen + " if prescreen else ""),
                          "alg_bytes_per_launch": nbytes / K, "avg_launch_ms": ms_dev / K},
             "gpu_launches": n_kernels * groups * K * (2 if not args.no_e2e else 1),
             "clocks": clocks,
