@@ -99,7 +99,7 @@ def parse():
     return a
 
 
-DEFAULT_GROUPS = {"ocsort": 2, "deepocsort": 4, "boosttrack": 4}      # tracker -> stream groups per engine step (measured optimum; 1 = one chain of launches)
+DEFAULT_GROUPS = {"ocsort": 2, "deepocsort": 4, "boosttrack": 4, "botsort": 8}      # tracker -> stream groups per engine step (measured optimum; 1 = one chain of launches)
 
 
 # --------------------------------------------------------------------------- inputs

@@ -114,6 +114,7 @@ _SIGS = {
                                            c_void_p, c_void_p, c_void_p]),
     "bm_ocsort_set_groups": (c_int, [c_void_p, c_int]),
     "bm_boosttrack_set_groups": (c_int, [c_void_p, c_int]),
+    "bm_botsort_set_groups": (c_int, [c_void_p, c_int]),
     "bm_strongsort_gated_metric": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_double,
                                            c_double, c_void_p]),
     "bm_strongsort_enhance_cost": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),

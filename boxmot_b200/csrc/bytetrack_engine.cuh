@@ -50,6 +50,25 @@ struct ByteState {
     int tensor_cores;  // 1: tcgen05 contraction (csrc/cosine_tc.cuh), 0: fp32 FFMA tiles in bot_embed_kernel
 };
 
+// Streams [s0, s0 + n) as an engine of their own (every array is stream-major); see ocs_substate.
+inline ByteState byte_substate(const ByteState& st, int s0, int n, int E) {
+    ByteState g = st;
+    const size_t o = (size_t)s0, T = st.Tcap, D = st.Dcap;
+    g.S = n;
+    g.xP += o * XA_N * T;  g.confcls += o * 2 * T;  g.tbox += o * 4 * T;  g.ints += o * BI_COUNT * T;
+    g.act += o * T;  g.lost += o * T;  g.hdr += o * BH_COUNT;  g.n_updates += o;  g.scratch += o * T * D;
+    if (st.chist) g.chist += o * 2 * BOT_HIST * T;
+    if (st.fupd) g.fupd += o * 2 * D;
+    if (st.feat) g.feat += o * T * E;
+    if (st.dfeat) g.dfeat += o * D * E;
+    if (st.embd) g.embd += o * T * D;
+    if (st.elive) g.elive += o * T;
+    if (st.ehind) g.ehind += o * D;
+    if (st.etn) g.etn += o * T;
+    if (st.edn) g.edn += o * D;
+    return g;
+}
+
 size_t bytetrack_step_smem(const ByteState& st);
 cudaError_t bytetrack_step_configure(size_t smem);
 cudaError_t bytetrack_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,

@@ -83,6 +83,7 @@ struct ByteEngine {      // ByteTrack and BoT-SORT share the state layout and th
     bm::ByteParams pr;
     std::vector<void*> allocs;
     bool bot = false;
+    StreamGroups grp;
 };
 
 struct BoostEngine {
@@ -699,9 +700,34 @@ int bm_botsort_step(void* handle, const float* d_dets, const int* d_ndets, const
     ByteEngine* e = static_cast<ByteEngine*>(handle);
     if (!e || !e->bot || !d_dets || !d_ndets || !d_out || !d_nout) return fail(-1, "bm_botsort_step: bad argument");
     if (e->pr.with_reid && !d_embs) return fail(-1, "bm_botsort_step: with_reid needs embeddings");
-    BM_CUDA(bm::botsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout,
-                                    static_cast<cudaStream_t>(stream)));
+    cudaStream_t main = static_cast<cudaStream_t>(stream);
+    if (e->grp.n > 1) {
+        const bm::ByteState& st = e->st;
+        const size_t D = st.Dcap, orow = (size_t)(st.Tcap < st.Dcap ? st.Tcap : st.Dcap) * 8, E = e->pr.emb_dim;
+        BM_CUDA(cudaEventRecord(e->grp.fork, main));
+        for (int g = 0; g < e->grp.n; g++) {
+            int s0, n;
+            StreamGroups::span(g, e->grp.n, st.S, &s0, &n);
+            cudaStream_t gs = e->grp.streams[g];
+            BM_CUDA(cudaStreamWaitEvent(gs, e->grp.fork, 0));
+            BM_CUDA(bm::botsort_step_launch(bm::byte_substate(st, s0, n, (int)E), e->pr, d_dets + s0 * D * 6, d_ndets + s0,
+                                            d_embs ? d_embs + s0 * D * E : nullptr,
+                                            d_warps ? d_warps + (size_t)s0 * 6 : nullptr, d_out + s0 * orow,
+                                            d_nout + s0, gs));
+            BM_CUDA(cudaEventRecord(e->grp.done[g], gs));
+            BM_CUDA(cudaStreamWaitEvent(main, e->grp.done[g], 0));
+        }
+        return 0;
+    }
+    BM_CUDA(bm::botsort_step_launch(e->st, e->pr, d_dets, d_ndets, d_embs, d_warps, d_out, d_nout, main));
     return 0;
+}
+
+int bm_botsort_set_groups(void* handle, int groups) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || !e->bot) return fail(-1, "bm_botsort_set_groups: bad argument");
+    if (e->grp.set(groups, e->st.S) != 0) return fail(-2, "bm_botsort_set_groups: stream / event creation failed");
+    return e->grp.n;
 }
 
 int bm_botsort_destroy(void* handle) { return bm_bytetrack_destroy(handle); }
@@ -717,6 +743,7 @@ int bm_botsort_peek(void* handle, int si, int* n_active, int* n_lost, double* h_
 int bm_bytetrack_destroy(void* handle) {
     ByteEngine* e = static_cast<ByteEngine*>(handle);
     if (!e) return 0;
+    e->grp.clear();
     for (void* p : e->allocs) cudaFree(p);
     delete e;
     return 0;

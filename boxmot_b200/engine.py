@@ -558,6 +558,15 @@ class BotSortEngine(ByteTrackEngine):
         self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
         self.launches = 0
 
+    def set_stream_groups(self, groups):
+        """See OcSortEngine.set_stream_groups."""
+        with torch.cuda.device(self.device):
+            n = _lib.lib().bm_botsort_set_groups(self._h, int(groups))
+        if n < 0:
+            _lib.check(n, "bm_botsort_set_groups")
+        self.groups = n
+        return n
+
     def step(self, dets, ndets, embs=None, warps=None, out=None, nout=None):
         assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
         assert tuple(dets.shape) == (self.S, self.Dcap, 6)

@@ -179,6 +179,8 @@ int bm_botsort_destroy(void* handle);
 int bm_botsort_reset(void* handle, void* stream);
 int bm_botsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
                     const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* Stream groups for the BoT-SORT engine; see bm_ocsort_set_groups. */
+int bm_botsort_set_groups(void* handle, int groups);
 int bm_botsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
 int bm_botsort_peek(void* handle, int stream_index, int* n_active, int* n_lost, double* h_mean,
                     double* h_cov, int* h_ids, void* stream);

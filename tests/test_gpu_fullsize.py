@@ -160,14 +160,14 @@ def test_crowd_density_streams_match_oracle(tracker):
     assert total > 5000
 
 
-@pytest.mark.parametrize("tracker", ["ocsort", "deepocsort", "boosttrack"])
+@pytest.mark.parametrize("tracker", ["ocsort", "deepocsort", "boosttrack", "botsort"])
 def test_stream_groups_do_not_change_results(tracker):
     """bm_ocsort_set_groups: the same batch stepped as 1, 3 and 8 groups of streams on CUDA streams of
     their own gives bit-identical rows and counters (streams are independent; 250 is not a multiple
     of 3 or 8, so the groups are ragged)."""
-    from boxmot_b200.engine import BoostTrackEngine, DeepOcSortEngine, OcSortEngine
+    from boxmot_b200.engine import BoostTrackEngine, BotSortEngine, DeepOcSortEngine, OcSortEngine
     from boxmot_b200.synth import make_batch
-    from conftest import BOOSTTRACK_YAML, DEEPOCSORT_YAML, OCSORT_YAML
+    from conftest import BOOSTTRACK_YAML, BOTSORT_YAML, DEEPOCSORT_YAML, OCSORT_YAML
     NS, KO, FR, E = 250, 60, 20, 32
     if tracker == "ocsort":
         dets, nd = make_batch(NS, KO, FR, 96)
@@ -189,6 +189,8 @@ def test_stream_groups_do_not_change_results(tracker):
             eng = OcSortEngine(NS, track_cap=192, det_cap=96, **OCSORT_YAML)
         elif tracker == "deepocsort":
             eng = DeepOcSortEngine(NS, track_cap=192, det_cap=96, emb_dim=E, **DEEPOCSORT_YAML)
+        elif tracker == "botsort":
+            eng = BotSortEngine(NS, track_cap=192, det_cap=96, emb_dim=E, **BOTSORT_YAML)
         else:
             eng = BoostTrackEngine(NS, track_cap=192, det_cap=96, emb_dim=E, **BOOSTTRACK_YAML)
         assert eng.set_stream_groups(groups) == groups
