@@ -26,8 +26,12 @@
 namespace bm {
 
 constexpr int B1_NT = 128;
-constexpr int BT_NT = 256;           // threads of the per-stream CTAs
-constexpr int BT_NW = BT_NT / 32;
+// Threads of the per-stream CTAs (boost and association kernels): 256, or 512 when the per-stream
+// tables leave room for only one CTA per SM (crowd caps) -- the same shared memory then feeds 16
+// warps instead of 8.  The kernels stride by blockDim.x.
+constexpr int BT_NT_MAX = 512;
+#define BT_NT ((int)blockDim.x)
+#define BT_NW ((int)blockDim.x >> 5)
 constexpr int BM_ERR_LAPBAD = 8;
 
 // ============================================================================ B1
@@ -112,9 +116,13 @@ __host__ __device__ inline size_t bt_work_bytes(int Tcap, int Dcap) {
     const size_t b = rect_work_bytes(Dcap, Tcap), c = lap_work_bytes(2 * Dcap);
     return ((b > c ? b : c) + 15) / 16 * 16;
 }
-__host__ __device__ inline size_t bt_smem_bytes(int Tcap, int Dcap) {
+__host__ __device__ inline size_t bt_smem_bytes(int Tcap, int Dcap, int threads) {
     const size_t t = Tcap, d = Dcap;
-    return 8 * (TP_COUNT * t + t + 4 * d + 3 * d) + 16 * d + 4 * (7 * d + 3 * t + 16) + 12 * t + 2 * (BT_NT / 32) * t + bt_work_bytes(Tcap, Dcap) + 32;
+    return 8 * (TP_COUNT * t + t + 4 * d + 3 * d) + 16 * d + 4 * (7 * d + 3 * t + 16) + 12 * t + 2 * (threads / 32) * t + bt_work_bytes(Tcap, Dcap) + 32;
+}
+inline int bt_threads(int Tcap, int Dcap) {
+    const size_t one_per_sm = 113 * 1024, limit = 227 * 1024;
+    return bt_smem_bytes(Tcap, Dcap, 256) > one_per_sm && bt_smem_bytes(Tcap, Dcap, BT_NT_MAX) <= limit ? BT_NT_MAX : 256;
 }
 __device__ inline BtSmem bt_carve(unsigned char* base, int Tcap, int Dcap) {
     BtSmem m;
@@ -259,7 +267,8 @@ __device__ __forceinline__ double bt_mh_sim(double mh, double colsum) {
 }
 
 // ============================================================================ B2
-__global__ void __launch_bounds__(BT_NT)
+template <int MAXNT>
+__global__ void __launch_bounds__(MAXNT)
 bt_boost_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets, const int* __restrict__ ndets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
@@ -394,7 +403,8 @@ bt_boost_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets, c
 }
 
 // ============================================================================ B3
-__global__ void __launch_bounds__(BT_NT)
+template <int MAXNT>
+__global__ void __launch_bounds__(MAXNT)
 bt_assoc_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int s = blockIdx.x, tid = threadIdx.x, lane = lane_id(), wid = warp_id();
@@ -409,7 +419,7 @@ bt_assoc_kernel(BoostState st, BoostParams pr, const float* __restrict__ dets) {
     const float* sim = st.embsim + (size_t)s * Dcap * T;
     int* upd_slot = st.upd + (size_t)s * 2 * Dcap;
     int* upd_det = upd_slot + Dcap;
-    __shared__ double s_cmx[BT_NW];
+    __shared__ double s_cmx[BT_NT_MAX / 32];
     if (tid < 16) sm.misc[tid] = 0;
     for (int d = tid; d < nD; d += BT_NT) {
         const int i = hs[d];
@@ -761,13 +771,17 @@ struct BoostDot {
     }
 };
 
-size_t boosttrack_smem(const BoostState& st) { return bt_smem_bytes(st.Tcap, st.Dcap); }
+size_t boosttrack_smem(const BoostState& st) { return bt_smem_bytes(st.Tcap, st.Dcap, bt_threads(st.Tcap, st.Dcap)); }
 
 cudaError_t boosttrack_configure(const BoostState& st) {
     const int sm = (int)boosttrack_smem(st);
-    cudaError_t e = cudaFuncSetAttribute(bt_boost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    cudaError_t e = cudaFuncSetAttribute(bt_boost_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bt_assoc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    e = cudaFuncSetAttribute(bt_assoc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bt_boost_kernel<BT_NT_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bt_assoc_kernel<BT_NT_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(cosine_tc_kernel<BoostDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)cosine_tc_smem_bytes());
@@ -794,7 +808,9 @@ cudaError_t boosttrack_step_launch(const BoostState& st, const BoostParams& pr, 
     bt_predict_kernel<<<st.S * c1, B1_NT, 0, stream>>>(st, pr, warps);
     if ((e = bt_dbg("bt_predict_kernel", stream)) != cudaSuccess) return e;
     BM_EV(1);
-    bt_boost_kernel<<<st.S, BT_NT, sm, stream>>>(st, pr, dets, ndets);
+    const int nt = bt_threads(st.Tcap, st.Dcap);
+    if (nt == 256) bt_boost_kernel<256><<<st.S, 256, sm, stream>>>(st, pr, dets, ndets);
+    else bt_boost_kernel<BT_NT_MAX><<<st.S, nt, sm, stream>>>(st, pr, dets, ndets);
     if ((e = bt_dbg("bt_boost_kernel", stream)) != cudaSuccess) return e;
     BM_EV(2);
     if (pr.with_reid) {
@@ -803,7 +819,8 @@ cudaError_t boosttrack_step_launch(const BoostState& st, const BoostParams& pr, 
         if ((e = bt_dbg("cosine_tc_kernel<BoostDot>", stream)) != cudaSuccess) return e;
     }
     BM_EV(3);
-    bt_assoc_kernel<<<st.S, BT_NT, sm, stream>>>(st, pr, dets);
+    if (nt == 256) bt_assoc_kernel<256><<<st.S, 256, sm, stream>>>(st, pr, dets);
+    else bt_assoc_kernel<BT_NT_MAX><<<st.S, nt, sm, stream>>>(st, pr, dets);
     if ((e = bt_dbg("bt_assoc_kernel", stream)) != cudaSuccess) return e;
     bt_update_kernel<<<st.S * ((st.Dcap + B3U_NT - 1) / B3U_NT), B3U_NT, 0, stream>>>(st, dets);
     if ((e = bt_dbg("bt_update_kernel", stream)) != cudaSuccess) return e;
