@@ -122,6 +122,8 @@ __host__ __device__ inline size_t bt_smem_bytes(int Tcap, int Dcap, int threads)
 }
 inline int bt_threads(int Tcap, int Dcap) {
     const size_t one_per_sm = 113 * 1024, limit = 227 * 1024;
+    static const int forced = [] { const char* e = getenv("BM_BT_THREADS"); return e ? atoi(e) : 0; }();
+    if ((forced == 256 || forced == BT_NT_MAX) && bt_smem_bytes(Tcap, Dcap, forced) <= limit) return forced;
     return bt_smem_bytes(Tcap, Dcap, 256) > one_per_sm && bt_smem_bytes(Tcap, Dcap, BT_NT_MAX) <= limit ? BT_NT_MAX : 256;
 }
 __device__ inline BtSmem bt_carve(unsigned char* base, int Tcap, int Dcap) {
