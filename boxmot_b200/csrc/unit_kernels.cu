@@ -239,6 +239,55 @@ __global__ void ss_iou_cost_kernel(const double* __restrict__ mean, const double
 }
 
 
+// Feature EMA of StrongSORT's Track.update (strongsort/sort/track.py:238-268, adaptive alpha :319-335),
+// one warp per updated track: fp64 arithmetic on fp32 storage.
+__device__ __forceinline__ double warp_sum_d(double v) {
+    for (int o = 16; o > 0; o >>= 1) v += shfl_xor_d(v, o);
+    return v;
+}
+__global__ void ss_feature_update_kernel(const float* __restrict__ last, const int* __restrict__ has_last,
+                                         const float* __restrict__ feat, const double* __restrict__ conf, int n, int E,
+                                         double base_alpha, double* __restrict__ ac, double* __restrict__ sim_out,
+                                         float* __restrict__ out) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n) return;
+    const float* f = feat + (size_t)w * E;
+    const float* l = last + (size_t)w * E;
+    float* o = out + (size_t)w * E;
+    double f2 = 0.0;
+    for (int i = lane; i < E; i += 32) f2 += (double)f[i] * (double)f[i];
+    const double fn = sqrt(warp_sum_d(f2)) + 1e-8;                       // :240
+    if (!has_last[w]) {                                                  // :261-263 first feature
+        for (int i = lane; i < E; i += 32) o[i] = (float)((double)f[i] / fn);
+        if (lane == 0 && sim_out) sim_out[w] = CUDART_NAN;
+        return;
+    }
+    double dot = 0.0, n2 = 0.0, l2 = 0.0;
+    for (int i = lane; i < E; i += 32) {
+        const double a = (double)f[i] / fn, b = (double)l[i];
+        dot += a * b; n2 += a * a; l2 += b * b;
+    }
+    dot = warp_sum_d(dot); n2 = warp_sum_d(n2); l2 = warp_sum_d(l2);
+    const double sim = dot / (sqrt(n2) * sqrt(l2) + 1e-8);               // :245-247
+    const double c = conf[w];
+    const double cf = c > 0.7 ? 1.0 : (c > 0.3 ? 0.5 : 0.2);             // :324
+    const double af = sim > 0.7 ? 1.0 : (sim > 0.4 ? 0.7 : 0.4);         // :327
+    const double alpha = fmin(fmax(base_alpha * cf * af, 0.1), 0.95);    // :330-333
+    double s2 = 0.0;
+    for (int i = lane; i < E; i += 32) {
+        const double v = alpha * (double)l[i] + (1.0 - alpha) * ((double)f[i] / fn);   // :254-256
+        s2 += v * v;
+    }
+    const double sn = sqrt(warp_sum_d(s2)) + 1e-8;                       // :257
+    for (int i = lane; i < E; i += 32)
+        o[i] = (float)((alpha * (double)l[i] + (1.0 - alpha) * ((double)f[i] / fn)) / sn);
+    if (lane == 0) {
+        ac[w] = 0.9 * ac[w] + 0.1 * sim;                                 // :248
+        if (sim_out) sim_out[w] = sim;
+    }
+}
+
+
 // ---- embedding distance (matching.py:230-321) as a stand-alone batched contraction
 __global__ void cosine_prep_kernel(const float* a, int na, const float* b, int nb, int E, int* idx, float* norms) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -487,6 +536,17 @@ int bm_strongsort_iou_cost(const double* d_mean, const double* d_trk, int n_trac
                                                                                           d_tlwh, n_dets, d_out);
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("ss_iou_cost_kernel", e);
+}
+
+int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, const float* d_feat, const double* d_conf,
+                                 int n, int emb_dim, double ema_alpha, double* d_appearance_consistency,
+                                 double* d_similarity, float* d_out, void* stream) {
+    if (n <= 0) return 0;
+    if (!d_last || !d_has_last || !d_feat || !d_conf || !d_appearance_consistency || !d_out || emb_dim <= 0) return -1;
+    bm::ss_feature_update_kernel<<<(n + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_last, d_has_last, d_feat, d_conf, n, emb_dim, ema_alpha, d_appearance_consistency, d_similarity, d_out);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("ss_feature_update_kernel", e);
 }
 
 int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, int bank_cap, const float* d_feats,

@@ -295,6 +295,18 @@ int bm_strongsort_enhance_cost(double* d_cost, const double* d_trk, int n_tracks
 int bm_strongsort_iou_cost(const double* d_mean, const double* d_trk, int n_tracks, const double* d_tlwh, int n_dets,
                            double* d_out, void* stream);
 
+/* Feature EMA of StrongSORT's Track.update (strongsort/sort/track.py:238-268 with
+ * _calculate_adaptive_ema_alpha :319-335) for n updated tracks: the detection feature is normalised
+ * (|f| + 1e-8), compared with the track's newest stored feature d_last [n][emb_dim] (cosine
+ * similarity, written to d_similarity [n] when not NULL), folded into appearance_consistency
+ * (0.9 / 0.1, d_appearance_consistency [n] in place), and blended with the adaptive alpha =
+ * clip(ema_alpha * conf_factor * appearance_factor, 0.1, 0.95), renormalised: d_out [n][emb_dim]
+ * is the feature Track.update appends.  d_has_last [n] = 0 for a track without features (first
+ * feature: the normalised detection feature, consistency untouched).  fp64 arithmetic, fp32 storage. */
+int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, const float* d_feat, const double* d_conf,
+                                 int n, int emb_dim, double ema_alpha, double* d_appearance_consistency,
+                                 double* d_similarity, float* d_out, void* stream);
+
 /* embedding_distance (boxmot/utils/matching.py:230-321 with its defaults): d_out [na][nb] =
  * max(0, 1 - <a_i, b_j> / (|a_i| |b_j|)) for float32 feature rows d_a [na][emb_dim],
  * d_b [nb][emb_dim].  mode 0 = tcgen05 tensor-core contraction (3xTF32, fp32 accumulation in

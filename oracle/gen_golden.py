@@ -331,6 +331,39 @@ def strongsort_gate_vectors(la, rng):
                 g_gated=g, g_enh=enh, g_iou=iou, g_lambda=np.array(0.995), g_idw=np.array(0.1))
 
 
+def strongsort_feature_vectors(rng):
+    """Known-answer vectors of the feature EMA inside the reference's Track.update (track.py:238-268):
+    reference Track objects updated with detections whose features are a noisy copy of the track's
+    identity (similar), an unrelated vector (dissimilar) or something in between, at low / medium /
+    high confidence -- every branch of _calculate_adaptive_ema_alpha."""
+    from boxmot.trackers.strongsort.sort.detection import Detection
+    from boxmot.trackers.strongsort.sort.track import Track
+    N, E, steps = 48, 64, 5
+    ident = rng.normal(0, 1, (N, E))
+    last, feat, conf, ac0, out, ac1 = [], [], [], [], [], []
+    tracks = []
+    for n in range(N):
+        d = Detection(np.array([100.0, 100.0, 50.0, 120.0]), 0.9, 0.0, 0, (ident[n] * 3.0).astype(np.float32))
+        tracks.append(Track(d, n + 1, 2, 50, 0.9))
+    for k in range(steps):
+        for n, trk in enumerate(tracks):
+            mix = [0.05, 0.8, 3.0][(n + k) % 3]
+            f = (ident[n] + mix * rng.normal(0, 1, E)).astype(np.float32) * float(rng.uniform(0.5, 4))
+            c = float([0.95, 0.5, 0.15][(n // 3 + k) % 3])
+            d = Detection(np.array([100.0, 100.0, 50.0, 120.0]), c, 0.0, 0, f.copy())
+            last.append(np.asarray(trk.features[-1], dtype=np.float64))
+            feat.append(f)
+            conf.append(c)
+            ac0.append(trk.appearance_consistency)
+            trk.predict()
+            trk.update(d)
+            out.append(np.asarray(trk.features[-1], dtype=np.float64))
+            ac1.append(trk.appearance_consistency)
+    print("strongsort feature EMA:", len(out), "updates, consistency range", min(ac1), max(ac1))
+    return dict(f_last=np.array(last), f_feat=np.array(feat), f_conf=np.array(conf), f_ac0=np.array(ac0),
+                f_out=np.array(out), f_ac1=np.array(ac1), f_alpha=np.array(0.9))
+
+
 def main_strongsort_units():
     """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
     reference's own functions (rows a18 / a21)."""
@@ -371,6 +404,7 @@ def main_strongsort_units():
         for r, cc in m:
             xs[p, r] = cc
     gate = strongsort_gate_vectors(la, rng)
+    gate.update(strongsort_feature_vectors(rng))
     np.savez_compressed(os.path.join(GOLD, "ref_strongsort_units.npz"), bank=bank, nb=nb, feats=feats, nn=nn,
                         costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5), **gate)
     print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))

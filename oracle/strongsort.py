@@ -13,6 +13,9 @@ Sources restated (paths under /root/reference/boxmot/trackers/strongsort/sort/):
                        and Tracker._apply_id_preservation_weighting (tracker.py:283-298)
   enhance_cost_matrix  linear_assignment.py:251-273 (_compute_quality_factor :355-364,
                        _compute_confidence_factor :367-379)
+  feature_update       track.py:238-268 with _calculate_adaptive_ema_alpha :319-335 (the feature EMA
+                       of Track.update: similarity to the last stored feature, appearance
+                       consistency, adaptive alpha, renormalised blend)
   iou_cost             iou_matching.py:10-87 (tlwh IoU, INFTY_COST rows for time_since_update > 1)
 
 Parity status: pinned against the reference's own functions imported through oracle/ref_shim.py
@@ -150,3 +153,21 @@ def iou_cost(means, tsu, det_tlwh):
         inter = wh.prod(axis=1)
         out[r] = 1.0 - inter / (b[2:].prod() + det_tlwh[:, 2:].prod(axis=1) - inter)
     return out
+
+
+def feature_update(last, feat, conf, appearance_consistency, base_alpha=0.9):
+    """One Track.update feature step.  last: the track's newest stored feature or None.
+    Returns (feature to append, appearance_consistency, similarity or nan)."""
+    feat = np.asarray(feat, dtype=float)
+    new = feat / (np.linalg.norm(feat) + 1e-8)
+    if last is None:
+        return new, appearance_consistency, float("nan")
+    last = np.asarray(last, dtype=float)
+    sim = np.dot(new, last) / (np.linalg.norm(new) * np.linalg.norm(last) + 1e-8)
+    ac = 0.9 * appearance_consistency + 0.1 * sim
+    cf = 1.0 if conf > 0.7 else (0.5 if conf > 0.3 else 0.2)
+    af = 1.0 if sim > 0.7 else (0.7 if sim > 0.4 else 0.4)
+    alpha = float(np.clip(base_alpha * cf * af, 0.1, 0.95))
+    smooth = alpha * last + (1 - alpha) * new
+    smooth = smooth / (np.linalg.norm(smooth) + 1e-8)
+    return smooth, ac, sim

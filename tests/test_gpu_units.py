@@ -452,3 +452,49 @@ def test_strongsort_cost_postprocessing_matches_reference_vectors():
     np.testing.assert_allclose(g, want, rtol=1e-12, atol=0)
     np.testing.assert_allclose(e, so.enhance_cost_matrix(cost0, trk, det[:, 0], det[:, 1], det[:, 2]), rtol=1e-14)
     np.testing.assert_allclose(i, so.iou_cost(means, trk[:, so.TRK_TSU], tlwh), rtol=1e-13, atol=1e-15)
+
+
+def test_strongsort_feature_update_matches_reference_vectors():
+    """bm_strongsort_feature_update (row a16, StrongSORT form) against the features the reference's
+    Track.update appended (fixture), incl. tracks without a stored feature, and against the oracle on
+    768-d CLIPReID-shaped vectors (BASELINE configs[3])."""
+    import os
+    from conftest import GOLD
+    from boxmot_b200 import _lib
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+
+    def run(last, has, feat, conf, ac0, alpha):
+        n, E = feat.shape
+        d_l = torch.as_tensor(np.ascontiguousarray(last, dtype=np.float32)).cuda()
+        d_h = torch.as_tensor(np.ascontiguousarray(has, dtype=np.int32)).cuda()
+        d_f = torch.as_tensor(np.ascontiguousarray(feat, dtype=np.float32)).cuda()
+        d_c = torch.as_tensor(np.ascontiguousarray(conf, dtype=np.float64)).cuda()
+        d_a = torch.as_tensor(np.ascontiguousarray(ac0, dtype=np.float64)).cuda()
+        d_s = torch.zeros((n,), dtype=torch.float64, device="cuda")
+        d_o = torch.zeros((n, E), dtype=torch.float32, device="cuda")
+        assert _lib.lib().bm_strongsort_feature_update(d_l.data_ptr(), d_h.data_ptr(), d_f.data_ptr(), d_c.data_ptr(), n, E,
+                                                       float(alpha), d_a.data_ptr(), d_s.data_ptr(), d_o.data_ptr(),
+                                                       None) == 0
+        torch.cuda.synchronize()
+        return d_o.cpu().numpy(), d_a.cpu().numpy(), d_s.cpu().numpy()
+
+    n = len(z["f_out"])
+    out, ac, sim = run(z["f_last"], np.ones(n), z["f_feat"], z["f_conf"], z["f_ac0"], z["f_alpha"])
+    np.testing.assert_allclose(out, z["f_out"], rtol=0, atol=1e-6)
+    np.testing.assert_allclose(ac, z["f_ac1"], rtol=0, atol=1e-6)
+    rng = np.random.default_rng(23)
+    N, E = 513, 768
+    ident = rng.normal(0, 1, (N, E))
+    last = ident / np.linalg.norm(ident, axis=1, keepdims=True)
+    feat = (ident + rng.choice([0.05, 0.8, 3.0], (N, 1)) * rng.normal(0, 1, (N, E))) * rng.uniform(0.5, 4, (N, 1))
+    conf, ac0 = rng.uniform(0.05, 0.99, N), rng.uniform(0.3, 1.0, N)
+    has = (np.arange(N) % 7 != 0).astype(np.int32)
+    last32, feat32 = last.astype(np.float32), feat.astype(np.float32)
+    out, ac, sim = run(last32, has, feat32, conf, ac0, 0.9)
+    for i in range(N):
+        w_out, w_ac, w_sim = so.feature_update(last32[i] if has[i] else None, feat32[i], conf[i], ac0[i], 0.9)
+        if has[i] and min(abs(w_sim - 0.7), abs(w_sim - 0.4)) < 1e-6:
+            continue                      # branch decided by rounding
+        np.testing.assert_allclose(out[i], w_out, rtol=0, atol=2e-7)
+        assert abs(ac[i] - w_ac) < 1e-12 and (np.isnan(sim[i]) if not has[i] else abs(sim[i] - w_sim) < 1e-12)

@@ -191,6 +191,25 @@ def test_strongsort_gate_oracle_matches_reference_vectors():
     assert (i == so.INFTY_COST).any() and (i < 1).sum() > 50
 
 
+def test_strongsort_feature_update_oracle_matches_reference_vectors():
+    """The feature EMA of the reference's Track.update (row a16, StrongSORT form) on vectors harvested
+    from reference Track objects: every conf / similarity branch of the adaptive alpha.  1e-6: the
+    reference itself mixes float32 and float64 here."""
+    from conftest import GOLD
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    sims = []
+    for i in range(len(z["f_out"])):
+        sm, ac, sim = so.feature_update(z["f_last"][i], z["f_feat"][i], float(z["f_conf"][i]), float(z["f_ac0"][i]),
+                                        float(z["f_alpha"]))
+        np.testing.assert_allclose(sm, z["f_out"][i], rtol=0, atol=1e-6)
+        assert abs(ac - z["f_ac1"][i]) < 1e-6
+        sims.append(sim)
+    sims = np.array(sims)
+    assert (sims > 0.7).sum() > 30 and ((sims > 0.4) & (sims <= 0.7)).sum() > 30 and (sims <= 0.4).sum() > 30
+    assert np.minimum(np.abs(sims - 0.7), np.abs(sims - 0.4)).min() > 1e-5      # no branch decided by rounding
+
+
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
 def test_cv8_kalman_oracle_matches_reference_vectors(kind):
     """oracle/kalman.py cv8_* against known-answer vectors generated from the reference's
