@@ -288,6 +288,92 @@ __global__ void ss_feature_update_kernel(const float* __restrict__ last, const i
 }
 
 
+// StrongSORT Track.predict / update / mark_missed (strongsort/sort/track.py:195-317) on a flat per-track
+// table, one thread per track.  Columns 0..12 are the SS_* columns (SS_HAS_VEL = len(velocity_history),
+// capped at 10, SS_VX/VY = velocity_history[-1]); then:
+enum { ST_STATE = 13, ST_STABILITY, ST_CONFIRMED, ST_MISSED, ST_NPOS, ST_PX, ST_PY, ST_NCONF, ST_CONF0,
+       ST_CONF_CAP = 20, ST_DETIND = ST_CONF0 + ST_CONF_CAP, ST_FIELDS = ST_DETIND + 1 };
+enum { ST_TENTATIVE = 1, ST_CONFIRMED_STATE = 2, ST_DELETED = 3 };
+
+__device__ __forceinline__ double ss_norm2(double x, double y) { return sqrt(x * x + y * y); }
+
+__global__ void ss_track_kernel(int op, double* __restrict__ mean, double* __restrict__ cov, double* __restrict__ trk,
+                                const double* __restrict__ det, int n, int n_init, int max_age) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double* a = trk + (size_t)i * ST_FIELDS;
+    if (op == 2) {                                                   // mark_missed (:303-317)
+        a[ST_MISSED] += 1.0;
+        int thr = max_age;
+        if (a[SS_QUALITY] > 0.8) thr = (int)((double)max_age * 1.5);
+        else if (a[SS_QUALITY] < 0.3) thr = (int)((double)max_age * 0.5);
+        if (a[ST_STATE] == (double)ST_TENTATIVE) a[ST_STATE] = ST_DELETED;
+        else if (a[SS_TSU] > (double)thr) a[ST_STATE] = ST_DELETED;
+        return;
+    }
+    double x[8], P[12];
+    cv8_load(mean, cov, i, x, P);
+    if (op == 0) {                                                   // predict (:195-219)
+        cv8_predict<CV8_XYAH>(x, P);
+        a[SS_AGE] += 1.0;
+        a[SS_TSU] += 1.0;
+        a[SS_VX] = x[4]; a[SS_VY] = x[5];
+        a[SS_HAS_VEL] = fmin(a[SS_HAS_VEL] + 1.0, 10.0);
+        const double px = a[ST_PX], py = a[ST_PY], had = a[ST_NPOS];
+        a[ST_PX] = x[0]; a[ST_PY] = x[1];
+        a[ST_NPOS] = fmin(had + 1.0, 10.0);
+        if (had >= 1.0 && a[SS_HAS_VEL] >= 2.0) {                    // _update_motion_consistency (:379-399)
+            const double ax = x[0] - px, ay = x[1] - py;
+            const double mx = (px + x[4]) - px, my = (py + x[5]) - py;
+            const double nm = ss_norm2(mx, my);
+            double cons;
+            if (nm > 0.0) cons = fmax(0.0, 1.0 - ss_norm2(ax - mx, ay - my) / fmax(nm * 0.5, 10.0));
+            else cons = ss_norm2(ax, ay) < 5.0 ? 1.0 : 0.5;
+            a[SS_MOTION] = 0.8 * a[SS_MOTION] + 0.2 * cons;
+        }
+    } else {                                                         // update (:221-301), feature step apart
+        const double* d = det + (size_t)i * 7;
+        const double conf = d[4];
+        a[SS_CONF] = conf; a[SS_CLS] = d[5]; a[ST_DETIND] = d[6];
+        double z[4] = {d[0], d[1], d[2], d[3]};
+        cv8_update<CV8_XYAH>(x, P, z, conf);
+        int nh = (int)a[ST_NCONF];
+        if (nh >= ST_CONF_CAP) {
+            for (int k = 1; k < ST_CONF_CAP; k++) a[ST_CONF0 + k - 1] = a[ST_CONF0 + k];
+            nh = ST_CONF_CAP - 1;
+        }
+        a[ST_CONF0 + nh] = conf;
+        nh++;
+        a[ST_NCONF] = nh;
+        if (conf > 0.7) { a[SS_HI_STREAK] += 1.0; a[SS_LO_STREAK] = 0.0; }
+        else if (conf < 0.3) { a[SS_LO_STREAK] += 1.0; a[SS_HI_STREAK] = 0.0; }
+        else { a[SS_LO_STREAK] = 0.0; a[SS_HI_STREAK] = 0.0; }
+        a[SS_HITS] += 1.0;
+        a[ST_CONFIRMED] += 1.0;
+        a[SS_TSU] = 0.0;
+        double sum = 0.0;
+        for (int k = 0; k < nh; k++) sum += a[ST_CONF0 + k];
+        const double avg = sum / nh;
+        double var = 0.0;
+        for (int k = 0; k < nh; k++) { const double e = a[ST_CONF0 + k] - avg; var += e * e; }
+        const double sd = sqrt(var / nh);
+        double cq = conf;                                            // _update_quality_score (:337-359)
+        if (nh > 1) cq = 0.7 * cq + 0.3 * avg * (1.0 - sd);
+        const double q = cq + fmin(a[SS_HITS] / 20.0, 0.2) + fmax(0.0, (a[SS_APPEAR] - 0.5) * 0.2) +
+                         fmax(0.0, (a[SS_MOTION] - 0.5) * 0.1);
+        a[SS_QUALITY] = fmin(fmax(q, 0.0), 1.0);
+        const double cs = nh > 3 ? 1.0 - fmin(sd, 1.0) : 0.5;        // _update_stability_score (:361-377)
+        const double hit_rate = a[ST_CONFIRMED] / fmax(a[SS_AGE], 1.0);
+        const double cons = 0.4 * a[SS_APPEAR] + 0.3 * a[SS_MOTION] + 0.3 * cs;
+        a[ST_STABILITY] = fmin(fmax(0.5 * hit_rate + 0.5 * cons, 0.0), 1.0);
+        if (a[ST_STATE] == (double)ST_TENTATIVE &&
+            (a[SS_HITS] >= (double)n_init || (a[SS_HITS] >= 1.0 && a[SS_QUALITY] > 0.8)))
+            a[ST_STATE] = ST_CONFIRMED_STATE;
+    }
+    cv8_store(mean, cov, i, x, P);
+}
+
+
 // ---- embedding distance (matching.py:230-321) as a stand-alone batched contraction
 __global__ void cosine_prep_kernel(const float* a, int na, const float* b, int nb, int E, int* idx, float* norms) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -547,6 +633,16 @@ int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, con
         d_last, d_has_last, d_feat, d_conf, n, emb_dim, ema_alpha, d_appearance_consistency, d_similarity, d_out);
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : unit_fail("ss_feature_update_kernel", e);
+}
+
+int bm_strongsort_track(int op, double* d_mean, double* d_cov, double* d_trk, const double* d_det, int n, int n_init,
+                        int max_age, void* stream) {
+    if (n <= 0) return 0;
+    if (op < 0 || op > 2 || !d_trk || (op != 2 && (!d_mean || !d_cov)) || (op == 1 && !d_det)) return -1;
+    bm::ss_track_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(op, d_mean, d_cov, d_trk, d_det, n,
+                                                                                       n_init, max_age);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("ss_track_kernel", e);
 }
 
 int bm_nn_cosine_distance(const float* d_bank, const int* d_nb, int n_tracks, int bank_cap, const float* d_feats,

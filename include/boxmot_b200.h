@@ -307,6 +307,22 @@ int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, con
                                  int n, int emb_dim, double ema_alpha, double* d_appearance_consistency,
                                  double* d_similarity, float* d_out, void* stream);
 
+/* StrongSORT's per-track state machine (strongsort/sort/track.py) on a flat table, one row of 42
+ * doubles per track: columns 0..12 as d_trk of bm_strongsort_gated_metric (column 8 =
+ * len(velocity_history) capped at 10, 9..10 = velocity_history[-1]), 13 state (1 tentative, 2
+ * confirmed, 3 deleted), 14 stability_score, 15 confirmed_detections, 16 missed_detections,
+ * 17 len(position_history) capped at 10, 18..19 position_history[-1], 20 len(confidence_history),
+ * 21..40 confidence_history (oldest first, at most 20), 41 det_ind.  d_mean [n][8], d_cov [n][8][8].
+ *   op 0  Track.predict (:195-219): Kalman predict, age / time_since_update, velocity and position
+ *         history, motion consistency (:379-399);
+ *   op 1  Track.update (:221-301) without its feature step (run bm_strongsort_feature_update first;
+ *         its appearance consistency goes to column 4): NSA Kalman update with the detection
+ *         confidence, confidence history, streaks, hits, quality score (:337-359), stability score
+ *         (:361-377), tentative -> confirmed (:298-301); d_det [n][7] = x, y, a, h, conf, cls, det_ind;
+ *   op 2  Track.mark_missed (:303-317): quality-dependent deletion threshold. */
+int bm_strongsort_track(int op, double* d_mean, double* d_cov, double* d_trk, const double* d_det, int n, int n_init,
+                        int max_age, void* stream);
+
 /* embedding_distance (boxmot/utils/matching.py:230-321 with its defaults): d_out [na][nb] =
  * max(0, 1 - <a_i, b_j> / (|a_i| |b_j|)) for float32 feature rows d_a [na][emb_dim],
  * d_b [nb][emb_dim].  mode 0 = tcgen05 tensor-core contraction (3xTF32, fp32 accumulation in

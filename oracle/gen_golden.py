@@ -364,6 +364,71 @@ def strongsort_feature_vectors(rng):
                 f_out=np.array(out), f_ac1=np.array(ac1), f_alpha=np.array(0.9))
 
 
+def strongsort_track_row(k):
+    """A reference Track as a row of oracle.strongsort's TS_* table."""
+    from oracle import strongsort as so
+    a = np.zeros(so.TS_FIELDS)
+    v = k.velocity_history[-1] if k.velocity_history else np.zeros(2)
+    a[:13] = [k.age, k.hits, k.time_since_update, k.motion_consistency, k.appearance_consistency, k.quality_score,
+              k.high_conf_streak, k.low_conf_streak, len(k.velocity_history), v[0], v[1], k.conf, k.cls]
+    a[so.TS_STATE], a[so.TS_STABILITY] = k.state, k.stability_score
+    a[so.TS_CONFIRMED], a[so.TS_MISSED] = k.confirmed_detections, k.missed_detections
+    a[so.TS_NPOS] = len(k.position_history)
+    a[so.TS_PX:so.TS_PY + 1] = k.position_history[-1]
+    a[so.TS_NCONF] = len(k.confidence_history)
+    a[so.TS_CONF0:so.TS_CONF0 + len(k.confidence_history)] = k.confidence_history
+    a[so.TS_DETIND] = k.det_ind
+    return a
+
+
+def strongsort_track_vectors(rng):
+    """Known-answer vectors of the reference's Track.predict / update / mark_missed (track.py:195-317):
+    64 Track objects stepped for 30 frames (update with p = 0.75, else a miss), different n_init /
+    max_age, confidences from all three bands; every call is recorded as (op, state before, detection,
+    state after).  Detections carry no feature (the feature step is its own unit); the appearance
+    consistency that step would have produced is set by hand before each update."""
+    from boxmot.trackers.strongsort.sort.detection import Detection
+    from boxmot.trackers.strongsort.sort.track import Track
+    rec = {k: [] for k in ("op", "m0", "c0", "a0", "det", "par", "m1", "c1", "a1")}
+    for n in range(64):
+        n_init, max_age = [2, 3, 5][n % 3], [3, 6, 50][n % 3 if n % 2 else (n + 1) % 3]
+        c = rng.random(2) * [1800, 1000]
+        wh = rng.uniform(20, 200, 2)
+        d = Detection(np.r_[c - wh / 2, wh], float(rng.uniform(0.05, 0.99)), float(n % 3), n, None)
+        d.quality_score = float(rng.uniform(0.1, 1.0))
+        trk = Track(d, n + 1, n_init, max_age, 0.9)
+        vel = rng.normal(0, 4, 2)
+        for f in range(30):
+            ops = ["predict", "update" if rng.random() < 0.75 else "miss"]
+            for op in ops:
+                m0, c0, a0 = trk.mean.copy(), trk.covariance.copy(), strongsort_track_row(trk)
+                det = np.zeros(7)
+                if op == "predict":
+                    trk.predict()
+                elif op == "update":
+                    c = c + vel + rng.normal(0, 1.5, 2)
+                    wh = wh * (1 + rng.normal(0, 0.02, 2))
+                    band = rng.integers(0, 3)
+                    conf = float(rng.uniform(*[(0.05, 0.29), (0.31, 0.69), (0.71, 0.99)][band]))
+                    dd = Detection(np.r_[c - wh / 2, wh], conf, float(rng.integers(0, 3)), int(rng.integers(0, 50)), None)
+                    trk.appearance_consistency = float(rng.uniform(0.2, 1.0))
+                    a0 = strongsort_track_row(trk)
+                    det = np.r_[dd.to_xyah(), conf, dd.cls, dd.det_ind]
+                    trk.update(dd)
+                else:
+                    trk.mark_missed()
+                for k, v in zip(("op", "m0", "c0", "a0", "det", "par", "m1", "c1", "a1"),
+                                ({"predict": 0, "update": 1, "miss": 2}[op], m0, c0, a0, det, [n_init, max_age],
+                                 trk.mean.copy(), trk.covariance.copy(), strongsort_track_row(trk))):
+                    rec[k].append(v)
+            if trk.is_deleted():
+                break
+    out = {"t_" + k: np.array(v) for k, v in rec.items()}
+    st = out["t_a1"][:, 13]
+    print("strongsort track ops:", np.bincount(out["t_op"]), "final states", np.bincount(st.astype(int)))
+    return out
+
+
 def main_strongsort_units():
     """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
     reference's own functions (rows a18 / a21)."""
@@ -405,6 +470,7 @@ def main_strongsort_units():
             xs[p, r] = cc
     gate = strongsort_gate_vectors(la, rng)
     gate.update(strongsort_feature_vectors(rng))
+    gate.update(strongsort_track_vectors(rng))
     np.savez_compressed(os.path.join(GOLD, "ref_strongsort_units.npz"), bank=bank, nb=nb, feats=feats, nn=nn,
                         costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5), **gate)
     print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))

@@ -16,6 +16,9 @@ Sources restated (paths under /root/reference/boxmot/trackers/strongsort/sort/):
   feature_update       track.py:238-268 with _calculate_adaptive_ema_alpha :319-335 (the feature EMA
                        of Track.update: similarity to the last stored feature, appearance
                        consistency, adaptive alpha, renormalised blend)
+  track_predict / track_update / track_mark_missed
+                       track.py:195-219, :221-301 (without the feature step), :303-317 on a flat
+                       per-track table (TS_* columns)
   iou_cost             iou_matching.py:10-87 (tlwh IoU, INFTY_COST rows for time_since_update > 1)
 
 Parity status: pinned against the reference's own functions imported through oracle/ref_shim.py
@@ -171,3 +174,94 @@ def feature_update(last, feat, conf, appearance_consistency, base_alpha=0.9):
     smooth = alpha * last + (1 - alpha) * new
     smooth = smooth / (np.linalg.norm(smooth) + 1e-8)
     return smooth, ac, sim
+
+
+# ---- Track state as a flat table (one row per track), restating track.py:195-317 -------------
+# columns 0..12 are the TRK_* columns above (TRK_HAS_VEL holds len(velocity_history), capped at 10)
+(TS_STATE, TS_STABILITY, TS_CONFIRMED, TS_MISSED, TS_NPOS, TS_PX, TS_PY, TS_NCONF, TS_CONF0) = range(13, 22)
+TS_CONF_CAP = 20
+TS_DETIND = TS_CONF0 + TS_CONF_CAP
+TS_FIELDS = TS_DETIND + 1
+TENTATIVE, CONFIRMED, DELETED = 1, 2, 3
+
+
+def _motion_consistency(a, prev, cur):
+    """track.py:379-399 (a[TRK_VX:VY] is velocity_history[-1])."""
+    if a[TRK_HAS_VEL] >= 2:
+        pv = a[TRK_VX:TRK_VY + 1]
+        actual = cur - prev
+        pm = (prev + pv) - prev
+        if np.linalg.norm(pm) > 0:
+            err = np.linalg.norm(actual - pm)
+            cons = max(0, 1.0 - err / max(np.linalg.norm(pm) * 0.5, 10.0))
+        else:
+            cons = 1.0 if np.linalg.norm(actual) < 5.0 else 0.5
+        a[TRK_MOTION] = 0.8 * a[TRK_MOTION] + 0.2 * cons
+
+
+def track_predict(mean, cov, a):
+    """Track.predict (track.py:195-219) on (mean, cov, row a); returns the new mean / cov, edits a."""
+    from oracle import kalman as K
+    mean, cov = K.cv8_predict("xyah", mean, cov)
+    a[TRK_AGE] += 1
+    a[TRK_TSU] += 1
+    a[TRK_VX:TRK_VY + 1] = mean[4:6]
+    a[TRK_HAS_VEL] = min(a[TRK_HAS_VEL] + 1, 10)
+    prev = a[TS_PX:TS_PY + 1].copy()
+    had = a[TS_NPOS]
+    a[TS_PX:TS_PY + 1] = mean[:2]
+    a[TS_NPOS] = min(a[TS_NPOS] + 1, 10)
+    if had >= 1:
+        _motion_consistency(a, prev, mean[:2].copy())
+    return mean, cov
+
+
+def track_update(mean, cov, a, xyah, conf, cls, det_ind, n_init):
+    """Track.update without the feature step (track.py:221-301; run feature_update first and store
+    its appearance consistency in a[TRK_APPEAR], as the reference's order of statements does)."""
+    from oracle import kalman as K
+    a[TRK_CONF], a[TRK_CLS], a[TS_DETIND] = conf, cls, det_ind
+    mean, cov = K.cv8_update("xyah", mean, cov, xyah, conf)
+    n = int(a[TS_NCONF])
+    hist = list(a[TS_CONF0:TS_CONF0 + n]) + [conf]
+    if len(hist) > TS_CONF_CAP:
+        hist.pop(0)
+    a[TS_NCONF] = len(hist)
+    a[TS_CONF0:TS_CONF0 + len(hist)] = hist
+    if conf > 0.7:
+        a[TRK_HI_STREAK] += 1
+        a[TRK_LO_STREAK] = 0
+    elif conf < 0.3:
+        a[TRK_LO_STREAK] += 1
+        a[TRK_HI_STREAK] = 0
+    else:
+        a[TRK_LO_STREAK] = a[TRK_HI_STREAK] = 0
+    a[TRK_HITS] += 1
+    a[TS_CONFIRMED] += 1
+    a[TRK_TSU] = 0
+    cq = conf
+    if len(hist) > 1:
+        cq = 0.7 * cq + 0.3 * np.mean(hist) * (1.0 - np.std(hist))
+    q = cq + min(a[TRK_HITS] / 20.0, 0.2) + max(0, (a[TRK_APPEAR] - 0.5) * 0.2) + max(0, (a[TRK_MOTION] - 0.5) * 0.1)
+    a[TRK_QUALITY] = np.clip(q, 0.0, 1.0)
+    cs = 1.0 - min(np.std(hist), 1.0) if len(hist) > 3 else 0.5
+    hit_rate = a[TS_CONFIRMED] / max(a[TRK_AGE], 1)
+    cons = 0.4 * a[TRK_APPEAR] + 0.3 * a[TRK_MOTION] + 0.3 * cs
+    a[TS_STABILITY] = np.clip(0.5 * hit_rate + 0.5 * cons, 0.0, 1.0)
+    if a[TS_STATE] == TENTATIVE and (a[TRK_HITS] >= n_init or (a[TRK_HITS] >= 1 and a[TRK_QUALITY] > 0.8)):
+        a[TS_STATE] = CONFIRMED
+    return mean, cov
+
+
+def track_mark_missed(a, max_age):
+    """Track.mark_missed (track.py:303-317)."""
+    a[TS_MISSED] += 1
+    thr = max_age
+    if a[TRK_QUALITY] > 0.8:
+        thr = int(max_age * 1.5)
+    elif a[TRK_QUALITY] < 0.3:
+        thr = int(max_age * 0.5)
+    if a[TS_STATE] == TENTATIVE:
+        a[TS_STATE] = DELETED
+    elif a[TRK_TSU] > thr:
+        a[TS_STATE] = DELETED

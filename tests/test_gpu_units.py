@@ -498,3 +498,35 @@ def test_strongsort_feature_update_matches_reference_vectors():
             continue                      # branch decided by rounding
         np.testing.assert_allclose(out[i], w_out, rtol=0, atol=2e-7)
         assert abs(ac[i] - w_ac) < 1e-12 and (np.isnan(sim[i]) if not has[i] else abs(sim[i] - w_sim) < 1e-12)
+
+
+def test_strongsort_track_state_machine_matches_reference_vectors():
+    """bm_strongsort_track (Track.predict / update / mark_missed, track.py:195-317) against every call
+    recorded from the reference's own Track objects: Kalman state 1e-9 relative (block-form filter vs
+    scipy's Cholesky solve), table columns 1e-12, the state column exact."""
+    import os
+    from conftest import GOLD
+    from boxmot_b200 import _lib
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    ops, par = z["t_op"], z["t_par"].astype(int)
+    checked = 0
+    for op in (0, 1, 2):
+        keys = sorted(set((int(p[0]), int(p[1])) for p in par[ops == op]))
+        for n_init, max_age in keys:
+            sel = np.where((ops == op) & (par[:, 0] == n_init) & (par[:, 1] == max_age))[0]
+            d_m = torch.as_tensor(np.ascontiguousarray(z["t_m0"][sel])).cuda()
+            d_c = torch.as_tensor(np.ascontiguousarray(z["t_c0"][sel])).cuda()
+            d_a = torch.as_tensor(np.ascontiguousarray(z["t_a0"][sel])).cuda()
+            d_d = torch.as_tensor(np.ascontiguousarray(z["t_det"][sel])).cuda()
+            assert d_a.shape[1] == so.TS_FIELDS == 42
+            assert _lib.lib().bm_strongsort_track(op, d_m.data_ptr(), d_c.data_ptr(), d_a.data_ptr(), d_d.data_ptr(),
+                                                  len(sel), n_init, max_age, None) == 0
+            torch.cuda.synchronize()
+            a = d_a.cpu().numpy()
+            assert np.array_equal(a[:, so.TS_STATE], z["t_a1"][sel][:, so.TS_STATE])
+            np.testing.assert_allclose(a, z["t_a1"][sel], rtol=1e-12, atol=1e-12)
+            np.testing.assert_allclose(d_m.cpu().numpy(), z["t_m1"][sel], rtol=1e-9, atol=1e-9)
+            np.testing.assert_allclose(d_c.cpu().numpy(), z["t_c1"][sel], rtol=1e-9, atol=1e-9)
+            checked += len(sel)
+    assert checked == len(ops) > 2500

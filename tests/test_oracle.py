@@ -210,6 +210,30 @@ def test_strongsort_feature_update_oracle_matches_reference_vectors():
     assert np.minimum(np.abs(sims - 0.7), np.abs(sims - 0.4)).min() > 1e-5      # no branch decided by rounding
 
 
+def test_strongsort_track_oracle_matches_reference_vectors():
+    """Track.predict / update / mark_missed (track.py:195-317) restated on a flat table against every
+    call recorded from 64 reference Track objects (2778 calls): Kalman state, histories, scores,
+    streaks and the state transitions.  1e-12."""
+    from conftest import GOLD
+    from oracle import strongsort as so
+    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    ops = z["t_op"]
+    assert np.bincount(ops).min() > 300 and set(z["t_a1"][:, so.TS_STATE]) == {1.0, 2.0, 3.0}
+    for i in range(len(ops)):
+        m, c, a = z["t_m0"][i].copy(), z["t_c0"][i].copy(), z["t_a0"][i].copy()
+        n_init, max_age = (int(v) for v in z["t_par"][i])
+        if ops[i] == 0:
+            m, c = so.track_predict(m, c, a)
+        elif ops[i] == 1:
+            d = z["t_det"][i]
+            m, c = so.track_update(m, c, a, d[:4], d[4], d[5], d[6], n_init)
+        else:
+            so.track_mark_missed(a, max_age)
+        np.testing.assert_allclose(m, z["t_m1"][i], rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(c, z["t_c1"][i], rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(a, z["t_a1"][i], rtol=1e-12, atol=1e-12)
+
+
 @pytest.mark.parametrize("kind", ["xyah", "xywh"])
 def test_cv8_kalman_oracle_matches_reference_vectors(kind):
     """oracle/kalman.py cv8_* against known-answer vectors generated from the reference's
