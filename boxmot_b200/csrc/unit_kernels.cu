@@ -311,6 +311,28 @@ __global__ void ss_track_kernel(int op, double* __restrict__ mean, double* __res
         else if (a[SS_TSU] > (double)thr) a[ST_STATE] = ST_DELETED;
         return;
     }
+    if (op == 3) {                                                   // camera_update (:173-189); det = 2x3 warp
+        const double* w = det + (size_t)i * 7;
+        double* m = mean + (size_t)i * 8;
+        const double bw0 = m[2] * m[3];
+        const double x1 = m[0] - bw0 / 2.0, y1 = m[1] - m[3] / 2.0, x2 = x1 + bw0, y2 = y1 + m[3];   // to_tlbr (:159-171)
+        const double x1w = w[0] * x1 + w[1] * y1 + w[2], y1w = w[3] * x1 + w[4] * y1 + w[5];
+        const double x2w = w[0] * x2 + w[1] * y2 + w[2], y2w = w[3] * x2 + w[4] * y2 + w[5];
+        const double bw = x2w - x1w, bh = y2w - y1w;
+        const double cx = x1w + bw / 2.0, cy = y1w + bh / 2.0;
+        const double px = m[0], py = m[1];
+        m[0] = cx; m[1] = cy; m[2] = bw / bh; m[3] = bh;
+        if (a[SS_HAS_VEL] >= 2.0) {
+            const double ax = cx - px, ay = cy - py;
+            const double mx = (px + a[SS_VX]) - px, my = (py + a[SS_VY]) - py;
+            const double nm = ss_norm2(mx, my);
+            double cons;
+            if (nm > 0.0) cons = fmax(0.0, 1.0 - ss_norm2(ax - mx, ay - my) / fmax(nm * 0.5, 10.0));
+            else cons = ss_norm2(ax, ay) < 5.0 ? 1.0 : 0.5;
+            a[SS_MOTION] = 0.8 * a[SS_MOTION] + 0.2 * cons;
+        }
+        return;
+    }
     double x[8], P[12];
     cv8_load(mean, cov, i, x, P);
     if (op == 0) {                                                   // predict (:195-219)
@@ -638,7 +660,7 @@ int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, con
 int bm_strongsort_track(int op, double* d_mean, double* d_cov, double* d_trk, const double* d_det, int n, int n_init,
                         int max_age, void* stream) {
     if (n <= 0) return 0;
-    if (op < 0 || op > 2 || !d_trk || (op != 2 && (!d_mean || !d_cov)) || (op == 1 && !d_det)) return -1;
+    if (op < 0 || op > 3 || !d_trk || (op != 2 && !d_mean) || (op < 2 && !d_cov) || ((op == 1 || op == 3) && !d_det)) return -1;
     bm::ss_track_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(op, d_mean, d_cov, d_trk, d_det, n,
                                                                                        n_init, max_age);
     const cudaError_t e = cudaGetLastError();

@@ -319,7 +319,9 @@ int bm_strongsort_feature_update(const float* d_last, const int* d_has_last, con
  *         its appearance consistency goes to column 4): NSA Kalman update with the detection
  *         confidence, confidence history, streaks, hits, quality score (:337-359), stability score
  *         (:361-377), tentative -> confirmed (:298-301); d_det [n][7] = x, y, a, h, conf, cls, det_ind;
- *   op 2  Track.mark_missed (:303-317): quality-dependent deletion threshold. */
+ *   op 2  Track.mark_missed (:303-317): quality-dependent deletion threshold;
+ *   op 3  Track.camera_update (:173-189): the corners of to_tlbr() through the 2x3 warp in d_det [n][7]
+ *         (first six entries, row-major), mean[:4] rebuilt, motion consistency; no covariance change. */
 int bm_strongsort_track(int op, double* d_mean, double* d_cov, double* d_trk, const double* d_det, int n, int n_init,
                         int max_age, void* stream);
 

@@ -399,12 +399,18 @@ def strongsort_track_vectors(rng):
         trk = Track(d, n + 1, n_init, max_age, 0.9)
         vel = rng.normal(0, 4, 2)
         for f in range(30):
-            ops = ["predict", "update" if rng.random() < 0.75 else "miss"]
+            ops = ["camera", "predict", "update" if rng.random() < 0.75 else "miss"]
             for op in ops:
                 m0, c0, a0 = trk.mean.copy(), trk.covariance.copy(), strongsort_track_row(trk)
                 det = np.zeros(7)
                 if op == "predict":
                     trk.predict()
+                elif op == "camera":
+                    th, sc = rng.normal(0, 0.01), 1 + rng.normal(0, 0.01)
+                    wm = np.array([[sc * np.cos(th), -sc * np.sin(th), rng.normal(0, 4)],
+                                   [sc * np.sin(th), sc * np.cos(th), rng.normal(0, 4)]])
+                    det = np.r_[wm.ravel(), 0.0]
+                    trk.camera_update(wm)
                 elif op == "update":
                     c = c + vel + rng.normal(0, 1.5, 2)
                     wh = wh * (1 + rng.normal(0, 0.02, 2))
@@ -418,7 +424,7 @@ def strongsort_track_vectors(rng):
                 else:
                     trk.mark_missed()
                 for k, v in zip(("op", "m0", "c0", "a0", "det", "par", "m1", "c1", "a1"),
-                                ({"predict": 0, "update": 1, "miss": 2}[op], m0, c0, a0, det, [n_init, max_age],
+                                ({"predict": 0, "update": 1, "miss": 2, "camera": 3}[op], m0, c0, a0, det, [n_init, max_age],
                                  trk.mean.copy(), trk.covariance.copy(), strongsort_track_row(trk))):
                     rec[k].append(v)
             if trk.is_deleted():

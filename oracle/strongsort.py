@@ -265,3 +265,23 @@ def track_mark_missed(a, max_age):
         a[TS_STATE] = DELETED
     elif a[TRK_TSU] > thr:
         a[TS_STATE] = DELETED
+
+
+def track_camera_update(mean, a, warp):
+    """Track.camera_update (track.py:173-189): both corners of to_tlbr() through the 2x3 warp, the
+    mean's (x, y, a, h) rebuilt from them, motion consistency against the previous centre."""
+    w = np.asarray(warp, dtype=float).reshape(2, 3)
+    ret = mean[:4].copy()
+    ret[2] *= ret[3]
+    ret[:2] -= ret[2:] / 2
+    ret[2:] = ret[:2] + ret[2:]
+    x1, y1, x2, y2 = ret
+    x1_, y1_ = w @ np.array([x1, y1, 1.0])
+    x2_, y2_ = w @ np.array([x2, y2, 1.0])
+    bw, bh = x2_ - x1_, y2_ - y1_
+    cx, cy = x1_ + bw / 2, y1_ + bh / 2
+    prev = mean[:2].copy()
+    mean = mean.copy()
+    mean[:4] = [cx, cy, bw / bh, bh]
+    _motion_consistency(a, prev, np.array([cx, cy]))
+    return mean

@@ -501,7 +501,7 @@ def test_strongsort_feature_update_matches_reference_vectors():
 
 
 def test_strongsort_track_state_machine_matches_reference_vectors():
-    """bm_strongsort_track (Track.predict / update / mark_missed, track.py:195-317) against every call
+    """bm_strongsort_track (Track.predict / update / mark_missed / camera_update, track.py:173-317) against every call
     recorded from the reference's own Track objects: Kalman state 1e-9 relative (block-form filter vs
     scipy's Cholesky solve), table columns 1e-12, the state column exact."""
     import os
@@ -511,7 +511,7 @@ def test_strongsort_track_state_machine_matches_reference_vectors():
     z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
     ops, par = z["t_op"], z["t_par"].astype(int)
     checked = 0
-    for op in (0, 1, 2):
+    for op in (0, 1, 2, 3):
         keys = sorted(set((int(p[0]), int(p[1])) for p in par[ops == op]))
         for n_init, max_age in keys:
             sel = np.where((ops == op) & (par[:, 0] == n_init) & (par[:, 1] == max_age))[0]
@@ -529,4 +529,4 @@ def test_strongsort_track_state_machine_matches_reference_vectors():
             np.testing.assert_allclose(d_m.cpu().numpy(), z["t_m1"][sel], rtol=1e-9, atol=1e-9)
             np.testing.assert_allclose(d_c.cpu().numpy(), z["t_c1"][sel], rtol=1e-9, atol=1e-9)
             checked += len(sel)
-    assert checked == len(ops) > 2500
+    assert checked == len(ops) > 4000

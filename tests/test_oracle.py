@@ -212,11 +212,12 @@ def test_strongsort_feature_update_oracle_matches_reference_vectors():
 
 def test_strongsort_track_oracle_matches_reference_vectors():
     """Track.predict / update / mark_missed (track.py:195-317) restated on a flat table against every
-    call recorded from 64 reference Track objects (2778 calls): Kalman state, histories, scores,
+    call recorded from 64 reference Track objects (4575 calls incl. camera_update): Kalman state, histories, scores,
     streaks and the state transitions.  1e-12."""
     from conftest import GOLD
     from oracle import strongsort as so
-    z = np.load(os.path.join(GOLD, "ref_strongsort_units.npz"))
+    with np.load(os.path.join(GOLD, "ref_strongsort_units.npz")) as f:
+        z = {k: f[k] for k in f.files if k.startswith("t_")}          # decompress once, not per access
     ops = z["t_op"]
     assert np.bincount(ops).min() > 300 and set(z["t_a1"][:, so.TS_STATE]) == {1.0, 2.0, 3.0}
     for i in range(len(ops)):
@@ -227,8 +228,10 @@ def test_strongsort_track_oracle_matches_reference_vectors():
         elif ops[i] == 1:
             d = z["t_det"][i]
             m, c = so.track_update(m, c, a, d[:4], d[4], d[5], d[6], n_init)
-        else:
+        elif ops[i] == 2:
             so.track_mark_missed(a, max_age)
+        else:
+            m = so.track_camera_update(m, a, z["t_det"][i][:6])
         np.testing.assert_allclose(m, z["t_m1"][i], rtol=1e-12, atol=1e-12)
         np.testing.assert_allclose(c, z["t_c1"][i], rtol=1e-12, atol=1e-12)
         np.testing.assert_allclose(a, z["t_a1"][i], rtol=1e-12, atol=1e-12)
