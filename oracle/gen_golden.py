@@ -435,6 +435,78 @@ def strongsort_track_vectors(rng):
     return out
 
 
+def strongsort_cascade_vectors(la, rng):
+    """The reference's matching_cascade (linear_assignment.py:90-171) with the gated_metric of
+    tracker.py:186-206 on 40 reference Track objects at time_since_update 1..4 with a filled sample
+    bank, against 60 detections (most of them a jittered copy of a track's box and identity)."""
+    import types
+    from boxmot.trackers.strongsort.sort.detection import Detection
+    from boxmot.trackers.strongsort.sort.track import Track
+    from boxmot.trackers.strongsort.sort.tracker import Tracker
+    T, D, E, CAP = 40, 60, 32, 12
+    ident = rng.normal(0, 1, (T, E))
+    metric = la.NearestNeighborDistanceMetric("cosine", 0.3, None)
+    tracks = []
+    for t in range(T):
+        wh = rng.uniform(30, 150, 2) * [1, 2]
+        c = rng.random(2) * [1800, 1000]
+        d = Detection(np.r_[c - wh / 2, wh], float(rng.uniform(0.3, 0.99)), float(t % 2), t, None)
+        d.quality_score = float(rng.uniform(0.2, 1.0))
+        trk = Track(d, t + 1, 2, 50, 0.9)
+        vel = rng.normal(0, 3, 2)
+        for _ in range(int(rng.integers(2, 9))):
+            trk.predict()
+            c = c + vel + rng.normal(0, 1, 2)
+            dd = Detection(np.r_[c - wh / 2, wh], float(rng.uniform(0.2, 0.99)), float(t % 2), 0, None)
+            trk.appearance_consistency = float(rng.uniform(0.3, 1.0))
+            trk.update(dd)
+        for _ in range(1 + t % 4):
+            trk.predict()                       # time_since_update 1..4: four cascade levels
+        nb = int(rng.integers(0, CAP + 1)) if t % 9 else 0
+        metric.samples[trk.id] = [((ident[t] + 0.1 * rng.normal(0, 1, E)) * rng.uniform(0.5, 2)).astype(np.float32)
+                                  for _ in range(nb)]
+        tracks.append(trk)
+    dets = []
+    for i in range(D):
+        if i < 48:
+            k = tracks[i % T]
+            h = k.mean[3] * (1 + rng.normal(0, 0.02))
+            w = k.mean[2] * k.mean[3] * (1 + rng.normal(0, 0.02))
+            c = k.mean[:2] + rng.normal(0, 0.03, 2) * k.mean[3]
+            f = ident[i % T] + (0.1 if i % 5 else 1.5) * rng.normal(0, 1, E)
+        else:
+            w, h = rng.uniform(30, 150), rng.uniform(60, 300)
+            c = rng.random(2) * [1800, 1000]
+            f = rng.normal(0, 1, E)
+        d = Detection(np.r_[c[0] - w / 2, c[1] - h / 2, w, h], float(rng.uniform(0.05, 0.99)), float(i % 2), i,
+                      (f * rng.uniform(0.5, 2)).astype(np.float32))
+        d.quality_score = float(rng.uniform(0.1, 1.1))
+        dets.append(d)
+    fake = types.SimpleNamespace(id_preservation_weight=0.1)
+
+    def gated_metric(trs, des, ti, di):
+        cost = metric.distance(np.array([des[i].feat for i in di]), np.array([trs[i].id for i in ti]))
+        cost = la.gate_cost_matrix(cost, trs, des, ti, di, 0.995)
+        return Tracker._apply_id_preservation_weighting(fake, cost, trs, des, ti, di)
+
+    tidx, didx = list(range(T)), list(range(D))
+    m, ut, ud = la.matching_cascade(gated_metric, 0.3, 3, tracks, dets, tidx, didx)
+    bank = np.zeros((T, CAP, E), np.float32)
+    nbs = np.zeros(T, np.int32)
+    for t, k in enumerate(tracks):
+        sm = metric.samples[k.id]
+        nbs[t] = len(sm)
+        if sm:
+            bank[t, : len(sm)] = np.array(sm)
+    tlwh = np.array([d.tlwh for d in dets])
+    print("strongsort cascade:", len(m), "matches,", len(ut), "unmatched tracks,", len(ud), "unmatched detections")
+    return dict(c_means=np.array([k.mean for k in tracks]), c_covs=np.array([k.covariance for k in tracks]),
+                c_trk=np.array([strongsort_track_row(k) for k in tracks]), c_bank=bank, c_nb=nbs, c_tlwh=tlwh,
+                c_dattr=np.array([[d.quality_score, d.conf, d.cls] for d in dets]),
+                c_feats=np.array([d.feat for d in dets]), c_matches=np.array(sorted(m)).reshape(-1, 2),
+                c_ut=np.array(sorted(ut)), c_ud=np.array(sorted(ud)), c_maxd=np.array(0.3), c_depth=np.array(3))
+
+
 def main_strongsort_units():
     """Known-answer vectors of StrongSORT's appearance metric and min_cost_matching, produced by the
     reference's own functions (rows a18 / a21)."""
@@ -477,6 +549,7 @@ def main_strongsort_units():
     gate = strongsort_gate_vectors(la, rng)
     gate.update(strongsort_feature_vectors(rng))
     gate.update(strongsort_track_vectors(rng))
+    gate.update(strongsort_cascade_vectors(la, rng))
     np.savez_compressed(os.path.join(GOLD, "ref_strongsort_units.npz"), bank=bank, nb=nb, feats=feats, nn=nn,
                         costs=costs, nrs=nrs, ncs=ncs, xs=xs, max_distance=np.array(0.5), **gate)
     print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))

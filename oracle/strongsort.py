@@ -285,3 +285,29 @@ def track_camera_update(mean, a, warp):
     mean[:4] = [cx, cy, bw / bh, bh]
     _motion_consistency(a, prev, np.array([cx, cy]))
     return mean
+
+
+def matching_cascade(means, covs, trk, banks, det_xyah, det_attr, feats, track_indices, detection_indices,
+                     max_distance, cascade_depth, mc_lambda=0.995, id_weight=0.1):
+    """linear_assignment.py:90-171 with tracker.py:186-206's gated_metric as the distance, composed
+    of the restatements above.  banks: list of (n_t, E) arrays by track index."""
+    track_indices, unmatched = list(track_indices), list(detection_indices)
+    levels = {}
+    for t in track_indices:
+        levels.setdefault(int(trk[t, TRK_TSU]), []).append(t)
+    matches = []
+    for age in sorted(levels):
+        if age > cascade_depth:
+            break
+        order = sorted(levels[age], key=lambda t: -(trk[t, TRK_QUALITY] + trk[t, TS_STABILITY]))
+        if not order or not unmatched:
+            continue
+        cost = nn_cosine_distance([banks[t] for t in order], feats[unmatched])
+        cost = gated_metric(cost, means[order], covs[order], trk[order], det_xyah[unmatched], mc_lambda, id_weight)
+        cost = enhance_cost_matrix(cost, trk[order], det_attr[unmatched, 0], det_attr[unmatched, 1],
+                                   det_attr[unmatched, 2])
+        m, _, um_c = min_cost_matching(cost, max_distance)
+        matches += [(order[r], unmatched[c]) for r, c in m]
+        unmatched = [unmatched[c] for c in um_c]
+    matched_t = {t for t, _ in matches}
+    return matches, [t for t in track_indices if t not in matched_t], unmatched

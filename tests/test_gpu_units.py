@@ -530,3 +530,24 @@ def test_strongsort_track_state_machine_matches_reference_vectors():
             np.testing.assert_allclose(d_c.cpu().numpy(), z["t_c1"][sel], rtol=1e-9, atol=1e-9)
             checked += len(sel)
     assert checked == len(ops) > 4000
+
+
+def test_strongsort_matching_cascade_matches_reference_vectors():
+    """boxmot_b200.strongsort_units.matching_cascade (the cascade composed of the C-ABI units: tcgen05
+    sample-bank distance -> gate / blend / id preservation -> cost enhancement -> thresholded exact
+    assignment, level by level) against the reference's matching_cascade on its own objects: the same
+    matches, unmatched tracks and unmatched detections."""
+    import os
+    from conftest import GOLD
+    from boxmot_b200.strongsort_units import matching_cascade
+    with np.load(os.path.join(GOLD, "ref_strongsort_units.npz")) as f:
+        z = {k: f[k] for k in f.files if k.startswith("c_")}
+    tlwh = z["c_tlwh"]
+    xyah = tlwh.copy()
+    xyah[:, :2] += xyah[:, 2:] / 2
+    xyah[:, 2] /= xyah[:, 3]
+    m, ut, ud = matching_cascade(z["c_means"], z["c_covs"], z["c_trk"], z["c_bank"], z["c_nb"], xyah, z["c_dattr"],
+                                 z["c_feats"], range(len(z["c_nb"])), range(len(tlwh)), float(z["c_maxd"]),
+                                 int(z["c_depth"]))
+    assert sorted(m) == [tuple(p) for p in z["c_matches"]] and len(m) >= 15
+    assert sorted(ut) == list(z["c_ut"]) and sorted(ud) == list(z["c_ud"])

@@ -210,6 +210,29 @@ def test_strongsort_feature_update_oracle_matches_reference_vectors():
     assert np.minimum(np.abs(sims - 0.7), np.abs(sims - 0.4)).min() > 1e-5      # no branch decided by rounding
 
 
+def _cascade_inputs(z):
+    tlwh = z["c_tlwh"]
+    xyah = tlwh.copy()
+    xyah[:, :2] += xyah[:, 2:] / 2
+    xyah[:, 2] /= xyah[:, 3]
+    return xyah
+
+
+def test_strongsort_matching_cascade_oracle_matches_reference_vectors():
+    """matching_cascade with the gated appearance metric (rows a18 / a21 / a22 chained) against the
+    reference's own function on its own Track / Detection objects and sample bank."""
+    from conftest import GOLD
+    from oracle import strongsort as so
+    with np.load(os.path.join(GOLD, "ref_strongsort_units.npz")) as f:
+        z = {k: f[k] for k in f.files if k.startswith("c_")}
+    banks = [z["c_bank"][t, : z["c_nb"][t]] for t in range(len(z["c_nb"]))]
+    m, ut, ud = so.matching_cascade(z["c_means"], z["c_covs"], z["c_trk"], banks, _cascade_inputs(z), z["c_dattr"],
+                                    z["c_feats"], range(len(banks)), range(len(z["c_tlwh"])), float(z["c_maxd"]),
+                                    int(z["c_depth"]))
+    assert sorted(m) == [tuple(p) for p in z["c_matches"]] and len(m) >= 15
+    assert sorted(ut) == list(z["c_ut"]) and sorted(ud) == list(z["c_ud"])
+
+
 def test_strongsort_track_oracle_matches_reference_vectors():
     """Track.predict / update / mark_missed (track.py:195-317) restated on a flat table against every
     call recorded from 64 reference Track objects (4575 calls incl. camera_update): Kalman state, histories, scores,
