@@ -104,6 +104,11 @@ cudaError_t dev_alloc(E* e, T** p, size_t n) {
 
 }  // namespace
 
+// Lets the other translation units of the library leave a message for bm_last_error().
+namespace bm {
+void set_last_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }
+}  // namespace bm
+
 extern "C" {
 
 const char* bm_last_error(void) { return g_err; }

@@ -10,6 +10,7 @@
 #include "lap_rect.cuh"
 #include <cstdio>
 #include <limits>
+#include <mutex>
 
 namespace bm {
 
@@ -731,3 +732,82 @@ int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int e
 }
 
 }  // extern "C"
+
+// ---- bm_cosine_distance_noalloc: bm_cosine_distance for callers that cannot allocate -------
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The row-index / norm
+// scratch that bm_cosine_distance takes from the caller lives in ONE file-scope device array;
+// every GPU that loads the library holds these 128 KiB until the process exits.  In HOST code
+// the array's name is only a stand-in for the symbol, not a device address: the address handed
+// to the kernels comes from cudaGetSymbolAddress, taken once per device with that device current.
+#define BM_COSINE_NOALLOC_SCRATCH_BYTES (8 * BM_COSINE_NOALLOC_MAX_ROWS)
+static __device__ __align__(256) unsigned char g_cosine_noalloc_scratch[BM_COSINE_NOALLOC_SCRATCH_BYTES];
+
+namespace bm { void set_last_error(const char* msg); }
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoallocMaxDevices] = {};   // device address of the scratch array, per device
+
+int noalloc_fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    char msg[256];
+    if (e != cudaSuccess) snprintf(msg, sizeof(msg), "bm_cosine_distance_noalloc: %s: %s", what, cudaGetErrorString(e));
+    else snprintf(msg, sizeof(msg), "bm_cosine_distance_noalloc: %s", what);
+    bm::set_last_error(msg);
+    return code;
+}
+
+// Once per device, with that device current: resolve the symbol and opt the tensor-core kernel
+// into its dynamic shared memory.  Neither call allocates.
+int noalloc_setup(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail(-2, "cudaGetDevice", e);
+    if (dev < 0 || dev >= kNoallocMaxDevices) return noalloc_fail(-1, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_cosine_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return noalloc_fail(-2, "cudaGetSymbolAddress(g_cosine_noalloc_scratch)", e);
+        e = cudaFuncSetAttribute(bm::cosine_tc_kernel<bm::UnitCosine>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bm::cosine_tc_smem_bytes());
+        if (e != cudaSuccess) return noalloc_fail(-2, "cosine_tc_kernel attribute", e);
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int bm_cosine_distance_noalloc(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out,
+                                          int mode, void* stream) {
+    if (na <= 0 || nb <= 0) return 0;
+    if (!d_a || !d_b || !d_out || emb_dim <= 0 || (mode != 0 && mode != 1)) return noalloc_fail(-1, "bad argument");
+    if ((long long)na + (long long)nb > BM_COSINE_NOALLOC_MAX_ROWS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "na + nb = %lld exceeds BM_COSINE_NOALLOC_MAX_ROWS = %d (static scratch of %d bytes)",
+                 (long long)na + nb, BM_COSINE_NOALLOC_MAX_ROWS, BM_COSINE_NOALLOC_SCRATCH_BYTES);
+        return noalloc_fail(-4, msg);
+    }
+    void* scratch = nullptr;
+    const int rc = noalloc_setup(&scratch);
+    if (rc != 0) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // Layout as bm_cosine_distance's d_work: (na + nb) row indices, then (na + nb) norms.  The
+    // prep kernel rewrites every entry the contraction reads, so nothing of the previous call's
+    // contents survives into this one and no clearing is needed.
+    int* idx = static_cast<int*>(scratch);
+    float* norms = reinterpret_cast<float*>(idx + na + nb);
+    bm::cosine_prep_kernel<<<(na + nb + 3) / 4, 128, 0, st>>>(d_a, na, d_b, nb, emb_dim, idx, norms);
+    bm::CosineProblem p;
+    p.A = d_a; p.ra = idx; p.na = norms; p.nA = na;
+    p.B = d_b; p.rb = idx + na; p.nb = norms + na; p.nB = nb;
+    p.E = emb_dim; p.out = d_out; p.out_ld = nb;
+    if (mode == 1)
+        bm::cosine_ffma_kernel<<<(na * nb + 127) / 128, 128, 0, st>>>(p);
+    else
+        bm::cosine_tc_kernel<bm::UnitCosine><<<dim3((na + bm::TC_M - 1) / bm::TC_M, 1), bm::TC_NT,
+                                               bm::cosine_tc_smem_bytes(), st>>>(bm::UnitCosine{p});
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : noalloc_fail(-2, "kernel launch", e);
+}

@@ -332,6 +332,25 @@ int bm_strongsort_track(int op, double* d_mean, double* d_cov, double* d_trk, co
 int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out,
                        void* d_work, int mode, void* stream);
 
+/* bm_cosine_distance for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  Same result as bm_cosine_distance
+ * (same kernels), but the row-index / norm scratch lives in a file-scope static __device__ array
+ * of the library instead of a caller buffer: 8 * BM_COSINE_NOALLOC_MAX_ROWS = 128 KiB, held by
+ * every GPU that loads the library until the process exits.  The call performs no cudaMalloc /
+ * cudaFree and calls no allocating library routine; the first call on each device resolves the
+ * array's device address (cudaGetSymbolAddress) and sets the kernel's shared-memory attribute, so
+ * make that first call outside stream capture.  na + nb > BM_COSINE_NOALLOC_MAX_ROWS is refused
+ * with -4 and a message in bm_last_error().  All calls on a device SHARE the one array: it keeps
+ * the previous call's contents (every entry a call reads is rewritten by that call first, so
+ * nothing needs clearing), and two calls that overlap on the GPU (different CUDA streams, or
+ * graph branches) race on it -- serialise them on one stream.  Inputs and output are still the
+ * caller's: d_a [na][emb_dim], d_b [nb][emb_dim] float32, d_out [na][nb] float32, mode as
+ * bm_cosine_distance. */
+#define BM_COSINE_NOALLOC_MAX_ROWS 16384
+int bm_cosine_distance_noalloc(const float* d_a, int na, const float* d_b, int nb, int emb_dim, float* d_out,
+                               int mode, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
