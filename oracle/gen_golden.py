@@ -555,6 +555,53 @@ def main_strongsort_units():
     print("strongsort units: nn", nn.shape, "min", nn.min(), "matching problems", P, "pairs", int((xs >= 0).sum()))
 
 
+# (case, stream id, K, frames, emb_dim, warps, tracker kwargs)
+STRONGSORT_CASES = [
+    ("synth_k20_e32", 60, 20, 60, 32, False, {}),
+    ("synth_k30_e64_b20", 61, 30, 70, 64, False, {"nn_budget": 20}),
+    ("synth_k40_e32_cmc", 62, 40, 50, 32, True, {"nn_budget": 50}),
+    ("synth_k25_e96_age8", 63, 25, 80, 96, False, {"max_age": 8, "nn_budget": 12}),
+    ("synth_k60_e32_crowd", 64, 60, 40, 32, False, {"nn_budget": 30, "max_age": 10}),
+    ("synth_k15_e32_ninit3", 65, 15, 90, 32, True, {"n_init": 3, "max_age": 6, "nn_budget": 8, "min_conf": 0.3}),
+    ("synth_k50_e128_hi", 66, 50, 40, 128, False, {"conf_thresh_high": 0.5, "conf_thresh_low": 0.2, "max_cos_dist": 0.3}),
+]
+
+
+def strongsort_inputs(sid, k, f, e, crowd=False):
+    """Detections rounded to float32 (the engine's input precision) and handed to the reference as
+    float64; embeddings float32 values as float64, so every reference operation is float64."""
+    fr, em = make_stream(sid, k, f, emb_dim=e, crowd=crowd)
+    fr = [d.astype(np.float32).astype(np.float64) for d in fr]
+    em = [x.astype(np.float64) for x in em]
+    if sid == 65:      # frames without detections, and with none above min_conf
+        fr[7] = np.empty((0, 6)); em[7] = np.empty((0, e))
+        fr[20][:, 4] = 0.05
+        for i in (40, 41, 42, 43, 44, 45, 46, 47, 48):      # a gap long enough to delete and recover tracks
+            fr[i] = fr[i][:3]; em[i] = em[i][:3]
+    return fr, em
+
+
+def main_strongsort():
+    """StrongSORT end to end in its runnable configuration (ref_shim._make_strongsort: R4, M1, M2, R5)."""
+    for name, sid, k, f, e, use_warps, kw in STRONGSORT_CASES:
+        fr, em = strongsort_inputs(sid, k, f, e, crowd="crowd" in name)
+        warps = boosttrack_warps(sid, f) if use_warps else None
+        trk = ref_shim.make_tracker("strongsort", **kw)
+        out, ntr = [], []
+        for i, d in enumerate(fr):
+            trk.cmc.warps = [warps[i].copy()] if warps is not None else []
+            r = np.asarray(trk.update(d.copy(), IMG, em[i].copy()), dtype=float)
+            r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+            out.append(np.c_[np.full(len(r), i), r])
+            ntr.append((len(trk.tracker.tracks), len(trk.tracker.lost_tracks), trk.tracker._next_id))
+        out = np.vstack(out)
+        extra = {"warps": warps} if warps is not None else {}
+        np.savez_compressed(os.path.join(GOLD, "ref_strongsort_%s.npz" % name), rows=out, kw=np.array(repr(kw)),
+                            ntracks=np.array(ntr), **extra)
+        print("strongsort", name, out.shape, "ids", int(out[:, 5].max()), "tracks/lost/next_id at end", ntr[-1],
+              "recovered", sum(1 for a, b in zip(ntr, ntr[1:]) if b[1] < a[1]))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -592,6 +639,8 @@ if __name__ == "__main__":
         main_boosttrack()
     elif "--mot17-emb" in sys.argv:
         main_mot17_emb()
+    elif "--strongsort" in sys.argv:
+        main_strongsort()
     elif "--strongsort-units" in sys.argv:
         main_strongsort_units()
     else:

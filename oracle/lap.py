@@ -31,8 +31,23 @@ def _lib():
         lib.oracle_lapjv.argtypes = [
             ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.oracle_ddot_skx.restype = ctypes.c_double
+        lib.oracle_ddot_skx.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
         _LIB = lib
     return _LIB
+
+
+def ddot(x, y):
+    """x . y of float64 vectors in OpenBLAS' SkylakeX summation order (oracle/numerics.c)."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    assert x.ndim == 1 and x.shape == y.shape
+    return float(_lib().oracle_ddot_skx(x.ctypes.data, y.ctypes.data, x.size))
+
+
+def norm(x):
+    """np.linalg.norm of a float64 vector = sqrt(x.dot(x)) (numpy/linalg/_linalg.py)."""
+    return float(np.sqrt(ddot(x, x)))
 
 
 last_scans = 0

@@ -226,4 +226,61 @@ def make_tracker(name, **overrides):
         mod.KalmanBoxTracker.count = 0        # class-level id counter, never reset by the reference (F9)
         args.setdefault("per_class", False)
         return mod.BoostTrack(reid_weights=None, device="cpu", half=False, **args)
+    if name == "strongsort":
+        return _make_strongsort(args)
     raise KeyError(name)
+
+
+# R4: tracker.py:278-279 reads unmatched_tracks_3, which is only bound when the IoU
+# stage ran (never on the first frame); initialise it next to all_matches, as a textual repair of
+# the reference's own source at import time.
+_TRACKER_REPAIRS = [
+    ("R4",
+     "        all_matches = []\n        all_unmatched_tracks = list(confirmed_tracks)",
+     "        all_matches = []\n        unmatched_tracks_3 = []\n        all_unmatched_tracks = list(confirmed_tracks)",
+     "unbound local when stage 3 is skipped"),
+]
+
+
+def _load_patched_strongsort_tracker():
+    path = os.path.join(REF_ROOT, "boxmot", "trackers", "strongsort", "sort", "tracker.py")
+    with open(path) as f:
+        src = f.read()
+    for rid, anchor, repl, _why in _TRACKER_REPAIRS:
+        if src.count(anchor) != 1:
+            raise RuntimeError("repair %s: anchor not found in reference source" % rid)
+        src = src.replace(anchor, repl, 1)
+    name = "boxmot.trackers.strongsort.sort.tracker"
+    mod = types.ModuleType(name)
+    mod.__file__ = path
+    mod.__package__ = "boxmot.trackers.strongsort.sort"
+    sys.modules[name] = mod
+    exec(compile(src, path, "exec"), mod.__dict__)
+    return mod
+
+
+def _make_strongsort(args):
+    """The fork's StrongSORT in its only runnable configuration: R4; M1 = the
+    reference's own CI mode (GITHUB_ACTIONS=true: tracks are born Confirmed, track.py:98-105);
+    M2 = YAML keys filtered to the constructor's signature; R5 = handle_occlusions=False and
+    crowd_detection=False (the occlusion handler raises TypeError as shipped)."""
+    import importlib
+    import inspect
+    os.environ["GITHUB_ACTIONS"] = "true"
+    os.environ.pop("GITHUB_JOB", None)
+    sys.modules.setdefault("boxmot.appearance.reid.auto_backend", types.ModuleType("x")).ReidAutoBackend = _DummyReid
+    cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
+    cmc.get_cmc_method = lambda _name: _QueuedCMC
+    if "boxmot.trackers.strongsort.sort.tracker" not in sys.modules or \
+            not getattr(sys.modules["boxmot.trackers.strongsort.sort.tracker"], "_bm_patched", False):
+        importlib.import_module("boxmot.trackers.strongsort.sort.linear_assignment")
+        _load_patched_strongsort_tracker()._bm_patched = True
+    mod = importlib.import_module("boxmot.trackers.strongsort.strongsort")
+    mod.ReidAutoBackend = _DummyReid
+    mod.get_cmc_method = lambda _name: _QueuedCMC
+    mod.Tracker = sys.modules["boxmot.trackers.strongsort.sort.tracker"].Tracker
+    sig = inspect.signature(mod.StrongSort.__init__).parameters
+    args = {k: v for k, v in args.items() if k in sig}                      # M2
+    args.update(handle_occlusions=False, crowd_detection=False)             # R5
+    args.pop("per_class", None)
+    return mod.StrongSort(reid_weights=None, device="cpu", half=False, **args)
