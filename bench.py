@@ -40,13 +40,18 @@ BOOSTTRACK_YAML = dict(max_age=60, min_hits=3, det_thresh=0.6, iou_threshold=0.3
                        aspect_ratio_thresh=1.6, lambda_iou=0.5, lambda_mhd=0.25, lambda_shape=0.25,
                        use_dlo_boost=True, use_duo_boost=True, dlo_boost_coef=0.65, s_sim_corr=False, use_rich_s=True,
                        use_sb=True, use_vt=True, with_reid=True)   # boxmot/configs/trackers/boosttrack.yaml defaults
-EMB_TRACKERS = ("botsort", "deepocsort", "boosttrack")
+STRONGSORT_ARGS = dict(min_conf=0.1, max_cos_dist=0.15, max_iou_dist=0.7, max_age=50, n_init=2, nn_budget=50,
+                       mc_lambda=0.995, ema_alpha=0.9, conf_thresh_high=0.7, conf_thresh_low=0.3,
+                       id_preservation_weight=0.1)   # StrongSort.__init__ defaults, 50-deep sample bank (BASELINE configs[3])
+EMB_TRACKERS = ("botsort", "deepocsort", "boosttrack", "strongsort")
 KERNEL_NAMES = {
     "ocsort": ("ocs_predict_kernel", "ocs_assoc_kernel", "ocs_update_kernel", "ocs_finalize_kernel"),
     "deepocsort": ("ocs_predict_kernel<deep>", "cosine_tc_kernel<DeepDot>", "ocs_assoc_kernel<deep>",
                    "ocs_update_kernel", "ocs_finalize_kernel", "docs_emb_kernel"),
     "boosttrack": ("bt_predict_kernel", "bt_boost_kernel", "cosine_tc_kernel<BoostDot>",
                    "bt_assoc_kernel+bt_update_kernel", "bt_finalize_kernel", "bt_emb_kernel"),
+    "strongsort": ("ss_prep_kernel", "cosine_tc_kernel<SsBank>", "ss_cost_kernel", "ss_match_kernel",
+                   "ss_update_kernel", "ss_finalize_kernel"),
 }
 METRIC = "track-updates/sec"
 L2_BYTES = 126 * 1024 * 1024
@@ -70,13 +75,14 @@ def parse():
     ap.add_argument("--steps", type=int, default=None, help="default 290 (botsort: 40)")
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack", "botsort", "deepocsort", "boosttrack"],
+    ap.add_argument("--tracker", default="ocsort", choices=["ocsort", "bytetrack", "botsort", "deepocsort", "boosttrack", "strongsort"],
                     help="ocsort = the headline workload (BASELINE configs[1]); bytetrack = the same "
                          "synthetic streams through the ByteTrack engine (the tracker of configs[0]); "
                          "botsort = BASELINE configs[2] (200 dets/frame, 512-d embeddings); deepocsort / boosttrack = the "
                          "trackers of configs[4] on the configs[1] streams with 512-d embeddings (their engines keep "
                          "per-column operands in shared memory: crowd shapes need --track-cap <= 768)")
-    ap.add_argument("--emb-dim", type=int, default=512, help="botsort only")
+    ap.add_argument("--emb-dim", type=int, default=None, help="embedding trackers: default 512 (strongsort: 768)")
+    ap.add_argument("--pool-cap", type=int, default=None, help="strongsort: feature vectors stored per stream")
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
     ap.add_argument("--objects", type=int, default=None, help="default 100 (botsort: 200)")
     ap.add_argument("--det-cap", type=int, default=None, help="default 128 (botsort: 256)")
@@ -91,6 +97,16 @@ def parse():
     a = ap.parse_args()
     bot = a.tracker == "botsort"
     emb = a.tracker in EMB_TRACKERS
+    if a.tracker == "strongsort":
+        # BASELINE configs[3]: 768-d embeddings, 50-deep sample bank.  Born-Confirmed tracks (the fork's only
+        # runnable mode) make every low-confidence detection a track that lives max_age frames: ~12 live
+        # tracks per object at steady state, hence the track / pool capacities and the long warm-up.
+        for name, v in (("steps", 30), ("warmup", 90), ("objects", 100), ("det_cap", 128), ("track_cap", 2048),
+                        ("pool_cap", 4608), ("emb_dim", 768), ("streams", 256)):
+            if getattr(a, name) is None or (name in ("warmup", "streams") and getattr(a, name) == ap.get_default(name)):
+                setattr(a, name, v)
+    if a.emb_dim is None:
+        a.emb_dim = 512
     for name, dflt, dbot in (("steps", 290, 40), ("objects", 100, 200), ("det_cap", 128, 256), ("track_cap", 256, 512)):
         if getattr(a, name) is None:
             setattr(a, name, dbot if bot else (40 if (emb and name == "steps") else dflt))
@@ -99,7 +115,7 @@ def parse():
     return a
 
 
-DEFAULT_GROUPS = {"ocsort": 2, "deepocsort": 4, "boosttrack": 4, "botsort": 8}      # tracker -> stream groups per engine step (measured optimum; 1 = one chain of launches)
+DEFAULT_GROUPS = {"strongsort": 1, "ocsort": 2, "deepocsort": 4, "boosttrack": 4, "botsort": 8}      # tracker -> stream groups per engine step (measured optimum; 1 = one chain of launches)
 
 
 # --------------------------------------------------------------------------- inputs
@@ -166,6 +182,9 @@ def _cpu_worker(a):
     elif tracker == "boosttrack":
         from oracle.boosttrack import BoostTrackOracle
         make = lambda: BoostTrackOracle(**BOOSTTRACK_YAML)
+    elif tracker == "strongsort":
+        from oracle.strongsort_tracker import StrongSortOracle
+        make = lambda: StrongSortOracle(**STRONGSORT_ARGS)
     elif tracker == "bytetrack":
         from oracle.bytetrack import ByteTrackOracle
         make = lambda: ByteTrackOracle(**BYTETRACK_YAML)
@@ -176,7 +195,7 @@ def _cpu_worker(a):
     for sid in sids:
         if emb_dim:
             fr, em = make_stream(sid, k, warm + steps, emb_dim=emb_dim)
-            step = (lambda f: o.update(fr[f], em[f])) if tracker == "botsort" else \
+            step = (lambda f: o.update(fr[f], em[f])) if tracker in ("botsort", "strongsort") else \
                 (lambda f: o.update(fr[f], None, em[f]))
         else:
             fr = make_stream(sid, k, warm + steps)
@@ -299,7 +318,8 @@ NCU_TRAFFIC = {"ocsort": 186.1e6, "bytetrack": 41.1e6}
 TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)",
                  "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)",
                  "deepocsort": "DeepOCSORT (deepocsort.yaml, synthetic re-ID embeddings)",
-                 "boosttrack": "BoostTrack++ (boosttrack.yaml, synthetic re-ID embeddings)"}
+                 "boosttrack": "BoostTrack++ (boosttrack.yaml, synthetic re-ID embeddings)",
+                 "strongsort": "StrongSORT (constructor defaults, nn_budget 50, tracks born Confirmed; synthetic re-ID embeddings)"}
 
 
 def alg_bytes(track_updates, matches, births, dets_in, rows_out):
@@ -345,7 +365,8 @@ def run_gpu_arm(args):
 
     import torch
     import torch.distributed as dist
-    from boxmot_b200.engine import BoostTrackEngine, BotSortEngine, ByteTrackEngine, DeepOcSortEngine, OcSortEngine
+    from boxmot_b200.engine import (BoostTrackEngine, BotSortEngine, ByteTrackEngine, DeepOcSortEngine, OcSortEngine,
+                                    StrongSortEngine)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -353,7 +374,12 @@ def run_gpu_arm(args):
     byte = args.tracker in ("bytetrack", "botsort")      # BYTE-family engines: no per-kernel timing API
     bot = args.tracker in EMB_TRACKERS       # embeddings travel with the detections
     deep, boost = args.tracker == "deepocsort", args.tracker == "boosttrack"
-    if deep:
+    strong = args.tracker == "strongsort"
+    if strong:
+        eng = StrongSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, pool_cap=args.pool_cap, device=dev,
+                               emb_dim=args.emb_dim, **STRONGSORT_ARGS)
+        byte = False
+    elif deep:
         eng = DeepOcSortEngine(S, track_cap=args.track_cap, det_cap=args.det_cap, device=dev, emb_dim=args.emb_dim,
                                **DEEPOCSORT_YAML)
         byte = False
@@ -371,7 +397,7 @@ def run_gpu_arm(args):
     # OC-SORT batches of more than 1536 streams run the first-round screen as a fifth launch (capi.cu ocs_create)
     prescreen = (not (deep or boost or bot or byte)) and (
         os.environ.get("BM_PRESCREEN", "1" if S > 1536 else "0")[:1] == "1")
-    n_kernels = 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5 if prescreen else 4
+    n_kernels = 6 if strong else 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5 if prescreen else 4
     groups = 1
     if hasattr(eng, "set_stream_groups"):
         groups = eng.set_stream_groups(args.groups if args.groups is not None else DEFAULT_GROUPS.get(args.tracker, 1))
@@ -556,6 +582,12 @@ def run_gpu_arm(args):
             E = args.emb_dim
             nbytes += 4 * E * dets_in + 4 * E * cnt["track_updates"] + 8 * E * cnt["matches"] \
                 + 8 * cnt["track_updates"] * (dets_in // max(1, K * S))
+            if strong:
+                # the sample bank: every distinct stored vector is read once by the contraction (fp32 shadow,
+                # 4E bytes; the reference's nominal T*B*E is ~10x that because its lists hold each vector ~10
+                # times); fp64 cost matrix out and in (16 bytes per pair); new feature fp64 + fp32 per match
+                nbytes += 4 * E * cnt.get("bank_rows", 0) + 16 * cnt["track_updates"] * (dets_in // max(1, K * S)) \
+                    + 12 * E * cnt["matches"]
             if deep or boost:
                 # the first-round matrix is materialised (column weights / column softmax): fp64 out and in
                 nbytes += 16 * cnt["track_updates"] * (dets_in // max(1, K * S))
@@ -568,6 +600,10 @@ def run_gpu_arm(args):
             "config": {"workload": ("DeepOCSORT (deepocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
                                     "512-d re-ID embeddings: tcgen05 embedding contraction + adaptive top-2 weighting + IoU/OCM cost, "
                                     "lapjv-exact assignment, embedding EMA (tracker of BASELINE configs[4] on the configs[1] streams)" if deep else
+                                    "StrongSORT (constructor defaults, nn_budget 50, occlusion handler off, tracks born Confirmed = the fork's "
+                                    "runnable mode) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, 512-d re-ID "
+                                    "embeddings: tcgen05 sample-bank contraction, Mahalanobis-gated three-stage cascade with scipy-exact "
+                                    "assignments, NSA Kalman update, adaptive feature EMA, id recovery, partial_fit (BASELINE configs[3])" if strong else
                                     "BoostTrack++ (boosttrack.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
                                     "512-d re-ID embeddings: DLO/DUO boosts, soft-BIoU / Mahalanobis / shape / embedding score, "
                                     "lapjv-exact assignment (tracker of BASELINE configs[4] on the configs[1] streams)" if boost else
@@ -580,7 +616,7 @@ def run_gpu_arm(args):
                                     "OC-SORT (ocsort.yaml) on %d concurrent synthetic streams/GPU x %d objects/frame x %d frames, "
                                     "IoU + OCM velocity cost, lapjv-exact assignment (BASELINE configs[1])").replace("512-d", "%d-d" % args.emb_dim) % (S, args.objects, F),
                        "tracker": args.tracker,
-                       "emb_dim": args.emb_dim if args.tracker in ("botsort", "deepocsort", "boosttrack") else 0,
+                       "emb_dim": args.emb_dim if args.tracker in EMB_TRACKERS else 0,
                        "stream_groups": groups,
                        "streams_per_gpu": S, "objects": args.objects, "frames": F, "det_cap": args.det_cap,
                        "track_cap": args.track_cap, "partition": "streams sharded by rank, no data-path collective",
@@ -592,7 +628,7 @@ def run_gpu_arm(args):
                          (1024, 100, 128, 256) else None,
                          "traffic_source": "ncu dram__bytes_read+write per frame step, cold caches (profiles/r1_launches_*_traffic.csv)",
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
-                         "kernel": "frame step = " + " + ".join(knames) if (deep or boost) else
+                         "kernel": "frame step = " + " + ".join(knames) if (deep or boost or strong) else
                                    "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
                                    "byte_step_kernel" if byte else
                                    "frame step = ocs_predict + %socs_assoc + ocs_update + ocs_finalize" % ("ocs_screen + " if prescreen else ""),
@@ -601,7 +637,7 @@ def run_gpu_arm(args):
             "clocks": clocks,
             "counters": cnt, "input_gen_s": gen_s, "wall_s_timed_loop": wall_dev,
         }
-        if ksum is not None and not (deep or boost):
+        if ksum is not None and not (deep or boost or strong):
             line["roofline"]["per_kernel"] = per_kernel(ksum, KB, kcnt, int(nd[W:W + KB].sum()))
             line["roofline"]["dominant_kernel"] = "ocs_assoc_kernel"
         elif ksum is not None:

@@ -43,6 +43,12 @@ class BotsortConfig(ctypes.Structure):
                                       "emb_dim")]
 
 
+class StrongsortConfig(ctypes.Structure):
+    _fields_ = [(n, c_double) for n in ("min_conf", "max_cos_dist", "max_iou_dist", "mc_lambda", "ema_alpha",
+                                         "conf_thresh_high", "conf_thresh_low", "id_preservation_weight")] + \
+               [(n, c_int) for n in ("max_age", "n_init", "nn_budget", "born_confirmed", "emb_dim")]
+
+
 ASSO_FUNCS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hmiou": 4, "centroid": 5}
 
 _SIGS = {
@@ -123,6 +129,19 @@ _SIGS = {
     "bm_strongsort_track": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "bm_strongsort_iou_cost": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "bm_cosine_distance": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "bm_strongsort_create": (c_int, [ctypes.POINTER(StrongsortConfig), c_int, c_int, c_int, c_int,
+                                     ctypes.POINTER(c_void_p)]),
+    "bm_strongsort_destroy": (c_int, [c_void_p]),
+    "bm_linear_sum_assignment_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                               c_void_p]),
+    "bm_strongsort_reset": (c_int, [c_void_p, c_void_p]),
+    "bm_strongsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_strongsort_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
+                                       c_void_p]),
+    "bm_strongsort_time_kernels": (c_int, [c_void_p, c_int]),
+    "bm_strongsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
+    "bm_strongsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_void_p, c_void_p,
+                                   c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_cosine_distance_noalloc": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p]),
     "bm_xysrb_predict": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_void_p]),
     "bm_xysrb_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -1,0 +1,1201 @@
+// Device-resident, stream-batched StrongSORT engine (the fork's "enhanced" StrongSORT in its
+// runnable configuration: SURVEY 8(c) R4 / M1 / M2 / R5) and its C-ABI (bm_strongsort_*).
+//
+// Replaces StrongSort.update (boxmot/trackers/strongsort/strongsort.py:115-205, :301-327, :329-359),
+// Tracker.predict / update / _enhanced_match / _attempt_id_recovery / _initiate_track
+// (sort/tracker.py:102-111, :118-181, :183-281, :300-351, :395-410), matching_cascade /
+// min_cost_matching / gate_cost_matrix and helpers, NearestNeighborDistanceMetric.distance /
+// partial_fit (sort/linear_assignment.py:14-87, :90-171, :174-379, :538-618), iou_cost
+// (sort/iou_matching.py:49-87) and Track (sort/track.py:78-317).
+//
+// One frame of all S streams = six launches, no host synchronisation:
+//   K1 ss_prep_kernel     CTA per stream: min_conf gate, detection quality (:301-327), stable sort
+//                         by quality (:190), camera_update + Track.predict for every track
+//   K2 cosine_tc_kernel   tcgen05 contraction: every stored bank feature x every detection
+//   K3 ss_cost_kernel     gated_metric + _enhance_cost_matrix for (confirmed track, detection)
+//   K4 ss_match_kernel    warp per stream: the three-stage cascade; every assignment is solved by a
+//                         step-for-step emulation of scipy's rectangular linear_sum_assignment
+//   K5 ss_update_kernel   warp per updated track: adaptive feature EMA + NSA Kalman update + scores
+//   K6 ss_finalize_kernel CTA per stream: mark_missed, id recovery, births, lost buffer,
+//                         partial_fit, output rows, list of live bank features for the next frame
+//
+// Feature storage.  The reference re-adds all (<= 10) features of every confirmed track to the
+// target's sample list EVERY frame, so a sample list of `budget` entries holds ~budget/10 distinct
+// vectors.  Here a feature vector is stored once, in a per-stream POOL of slots (fp64 for the EMA
+// chain and the quality norm, an fp32 shadow for the contraction); the track's ring of 10 and
+// its sample list hold slot numbers.  partial_fit is then integer bookkeeping, and the
+// contraction reads every distinct vector once per frame instead of once per copy.
+//
+// partial_fit's "keep the best `budget` by np.linalg.norm(feature)" ranks unit vectors by the last
+// ulp of a BLAS dot product.  The engine evaluates that norm in the summation order of OpenBLAS'
+// SkylakeX ddot kernel (warp_ddot_skx; the same order as oracle/numerics.c), which is what the
+// reference executed when the fixtures were generated; within one quality value list order is
+// insertion order (Python's sort is stable), so "drop the worst" = lowest quality, newest entry.
+#include "../../include/boxmot_b200.h"
+#include "strongsort_units.cuh"
+#include "cosine_tc.cuh"
+#include <cstdio>
+#include <new>
+#include <vector>
+
+namespace bm {
+
+void set_last_error(const char* msg);
+
+enum { SH_NTRACKS = 0, SH_NLOST, SH_NTFREE, SH_NPFREE, SH_NPFREED, SH_NEXT_ID, SH_FRAME, SH_ERR, SH_NHIST, SH_NLIVE,
+       SH_NDET, SH_NUPD, SH_STAGE3, SH_NUNM, SH_LSA, SH_MATCH, SH_BIRTHS, SH_HADDETS, SH_COUNT = 20 };
+enum { TI_ID = 0, TI_NRING, TI_NBANK, TI_NDIST, TI_LOSTFRAME, TI_SEQ, TI_NUPD, TI_MISS, TI_COUNT };
+// sorted detection table
+enum { DT_TLWH = 0, DT_XYAH = 4, DT_CONF = 8, DT_CLS, DT_DETIND, DT_QUALITY, DT_NORM, DT_COUNT };
+constexpr int SS_RING = 10;          // track.py:109 max_features
+constexpr int SS_LOST = 30;          // tracker.py:100 id_recovery_buffer_size
+constexpr int SS_MAXUPD = 3;         // a track can be matched by the cascade and by both of its IoU-stage rows
+enum { SS_ERR_TRACKS = 1, SS_ERR_DETS = 2, SS_ERR_POOL = 8, SS_ERR_LSA = 16 };
+
+struct SsParams {
+    double min_conf, max_cos_dist, max_iou_dist, mc_lambda, ema_alpha, conf_hi, conf_lo, id_weight;
+    int max_age, n_init, budget, born_confirmed, E;
+};
+
+struct SsState {
+    int S, Tcap, Dcap, Pcap, B, M;       // M = 2 * Tcap + Dcap: bound of an assignment problem's side
+    double *mean, *covb, *tab;           // [S][Tcap][8], [S][Tcap][12], [S][Tcap][ST_FIELDS]
+    int *tint, *ring;                    // [S][Tcap][TI_COUNT], [S][Tcap][SS_RING]
+    int *bslot, *bseq, *dslot, *dcnt;    // [S][Tcap][B] sample list entries (slot, seq); distinct slots and counts
+    double* bminq;                       // [S][Tcap]
+    int *upd, *order, *lost, *tfree, *hdr;   // [S][Tcap][3], [S][Tcap], [S][32], [S][Tcap], [S][SH_COUNT]
+    unsigned long long* n_updates;       // [S]
+    double* pool; float* pool32;         // [S][Pcap][E]
+    double* pq;                          // [S][Pcap] np.linalg.norm of the stored vector
+    int *pbank, *pring, *pfree, *pfreed, *live;   // [S][Pcap]
+    float *lnorm, *dist;                 // [S][Pcap], [S][Pcap][Dcap]
+    double* cost;                        // [S][Tcap][Dcap]
+    double* dtab; int* dord; float* dnormf;   // [S][Dcap][DT_COUNT], [S][Dcap], [S][Dcap]
+    int *ulist, *unm, *wki;              // [S][Dcap], [S][Dcap], [S][WKI]
+    double *wkd, *sims;                  // [S][3*M], [S][32][Dcap]
+    size_t wki_stride;
+};
+
+struct SsView {
+    const SsState& st; int s;
+    __device__ SsView(const SsState& st_, int s_) : st(st_), s(s_) {}
+    __device__ int* hdr() const { return st.hdr + (size_t)s * SH_COUNT; }
+    __device__ int* order() const { return st.order + (size_t)s * st.Tcap; }
+    __device__ double* mean(int t) const { return st.mean + ((size_t)s * st.Tcap + t) * 8; }
+    __device__ double* covb(int t) const { return st.covb + ((size_t)s * st.Tcap + t) * 12; }
+    __device__ double* tab(int t) const { return st.tab + ((size_t)s * st.Tcap + t) * ST_FIELDS; }
+    __device__ int* tint(int t) const { return st.tint + ((size_t)s * st.Tcap + t) * TI_COUNT; }
+    __device__ int* ring(int t) const { return st.ring + ((size_t)s * st.Tcap + t) * SS_RING; }
+    __device__ int* bslot(int t) const { return st.bslot + ((size_t)s * st.Tcap + t) * st.B; }
+    __device__ int* bseq(int t) const { return st.bseq + ((size_t)s * st.Tcap + t) * st.B; }
+    __device__ int* dslot(int t) const { return st.dslot + ((size_t)s * st.Tcap + t) * st.B; }
+    __device__ int* dcnt(int t) const { return st.dcnt + ((size_t)s * st.Tcap + t) * st.B; }
+    __device__ double& bminq(int t) const { return st.bminq[(size_t)s * st.Tcap + t]; }
+    __device__ int* upd(int t) const { return st.upd + ((size_t)s * st.Tcap + t) * SS_MAXUPD; }
+    __device__ double* pool(int p, int E) const { return st.pool + ((size_t)s * st.Pcap + p) * E; }
+    __device__ float* pool32(int p, int E) const { return st.pool32 + ((size_t)s * st.Pcap + p) * E; }
+    __device__ double* pq() const { return st.pq + (size_t)s * st.Pcap; }
+    __device__ int* pbank() const { return st.pbank + (size_t)s * st.Pcap; }
+    __device__ int* pring() const { return st.pring + (size_t)s * st.Pcap; }
+    __device__ int* pfree() const { return st.pfree + (size_t)s * st.Pcap; }
+    __device__ int* pfreed() const { return st.pfreed + (size_t)s * st.Pcap; }
+    __device__ double* dtab(int k) const { return st.dtab + ((size_t)s * st.Dcap + k) * DT_COUNT; }
+    __device__ int* dord() const { return st.dord + (size_t)s * st.Dcap; }
+    __device__ double* cost() const { return st.cost + (size_t)s * st.Tcap * st.Dcap; }
+    __device__ float* dist() const { return st.dist + (size_t)s * st.Pcap * st.Dcap; }
+};
+
+// ---------------------------------------------------------------------------------------------
+// x . y in the summation order of OpenBLAS' SkylakeX ddot (see the file header): lane L owns the
+// FMA accumulator of elements i = L (mod 32); lanes l and l + 4 of each group of eight are
+// folded, the four groups added left to right, then (s0 + s2) + (s1 + s3); the tail beyond the
+// last multiple of 32 is folded in element by element.  All lanes return the result.
+template <typename FX, typename FY>
+__device__ __forceinline__ double warp_ddot_skx(FX x, FY y, int n) {
+    const int lane = lane_id();
+    const int n1 = n & ~31;
+    double acc = 0.0;
+    for (int i = lane; i < n1; i += 32) acc = __fma_rn(x(i), y(i), acc);
+    double dot = 0.0;
+    if (n1) {
+        const double a = acc + __shfl_down_sync(BM_FULL, acc, 4);       // valid on lanes 8k + l, l < 4
+        const double a1 = __shfl_sync(BM_FULL, a, (lane & 3) + 8), a2 = __shfl_sync(BM_FULL, a, (lane & 3) + 16),
+                     a3 = __shfl_sync(BM_FULL, a, (lane & 3) + 24), a0 = __shfl_sync(BM_FULL, a, lane & 3);
+        const double sl = ((a0 + a1) + a2) + a3;                        // s[lane & 3]
+        const double s0 = __shfl_sync(BM_FULL, sl, 0), s1 = __shfl_sync(BM_FULL, sl, 1),
+                     s2 = __shfl_sync(BM_FULL, sl, 2), s3 = __shfl_sync(BM_FULL, sl, 3);
+        dot = (s0 + s2) + (s1 + s3);
+    }
+    for (int i = n1; i < n; i++) dot = __fma_rn(y(i), x(i), dot);
+    return dot;
+}
+
+__device__ __forceinline__ void ss_set_err(int* hdr, int bit) { atomicOr(&hdr[SH_ERR], bit); }
+
+// Pool slot allocation (pop only; frees are deferred to the finalize kernel's merge, so pops and
+// pushes never run concurrently).  Returns -1 and sets the error bit when the pool is exhausted.
+__device__ __forceinline__ int ss_pool_pop(const SsView& v) {
+    const int n = atomicSub(&v.hdr()[SH_NPFREE], 1);
+    if (n <= 0) { atomicAdd(&v.hdr()[SH_NPFREE], 1); ss_set_err(v.hdr(), SS_ERR_POOL); return -1; }
+    return v.pfree()[n - 1];
+}
+__device__ __forceinline__ void ss_pool_release(const SsView& v, int p) {      // deferred
+    const int k = atomicAdd(&v.hdr()[SH_NPFREED], 1);
+    v.pfreed()[k] = p;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: detections (gate, quality, stable sort by quality) and tracks (camera_update, predict)
+__global__ void __launch_bounds__(256)
+ss_prep_kernel(SsState st, SsParams pr, const float* __restrict__ dets, const int* __restrict__ ndets,
+               const float* __restrict__ embs, const double* __restrict__ warps) {
+    extern __shared__ __align__(16) unsigned char ss_smem[];
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    SsView v(st, s);
+    int* hdr = v.hdr();
+    double* q = reinterpret_cast<double*>(ss_smem);           // [Dcap]
+    double* nrm = q + st.Dcap;                                // [Dcap]
+    int* sel = reinterpret_cast<int*>(nrm + st.Dcap);         // [Dcap]
+    __shared__ int s_n;
+    int nd = ndets[s];
+    if (nd > st.Dcap) { if (tid == 0) ss_set_err(hdr, SS_ERR_DETS); nd = st.Dcap; }
+    const float* D = dets + (size_t)s * st.Dcap * 6;
+    if (wid == 0) {
+        const int n = warp_compact(nd, sel, 0, [&](int i) { return (double)D[i * 6 + 4] >= pr.min_conf; },
+                                   [&](int i) { return i; });
+        if (lane == 0) s_n = n;
+    }
+    __syncthreads();
+    const int n = s_n;
+    // feature norms (np.linalg.norm of the raw feature: strongsort.py:308, track.py:114, :240)
+    for (int k = wid; k < n; k += blockDim.x >> 5) {
+        const float* f = embs + ((size_t)s * st.Dcap + sel[k]) * pr.E;
+        auto fx = [&](int i) { return (double)f[i]; };
+        const double d = warp_ddot_skx(fx, fx, pr.E);
+        if (lane == 0) nrm[k] = sqrt(d);
+    }
+    __syncthreads();
+    for (int k = tid; k < n; k += blockDim.x) {              // _compute_detection_quality (:301-327)
+        const float* b = D + sel[k] * 6;
+        const double conf = (double)b[4];
+        const double w = (double)b[2] - (double)b[0], h = (double)b[3] - (double)b[1];
+        double ql = 0.7 * conf + 0.3 * fmin(nrm[k] / 10.0, 1.0);
+        if (h > 0.0) ql = 0.9 * ql + 0.1 * fmax(0.1, 1.0 - fabs(w / h - 0.5) / 2.0);
+        q[k] = ql;
+    }
+    __syncthreads();
+    for (int k = tid; k < n; k += blockDim.x) {              // detections.sort(key=quality, reverse=True): stable
+        const double qk = q[k];
+        int rank = 0;
+        for (int j = 0; j < n; j++) rank += (q[j] > qk || (q[j] == qk && j < k)) ? 1 : 0;
+        const float* b = D + sel[k] * 6;
+        double* d = v.dtab(rank);
+        const double x1 = b[0], y1 = b[1], w = (double)b[2] - (double)b[0], h = (double)b[3] - (double)b[1];
+        d[DT_TLWH] = x1; d[DT_TLWH + 1] = y1; d[DT_TLWH + 2] = w; d[DT_TLWH + 3] = h;
+        d[DT_XYAH] = x1 + w / 2.0; d[DT_XYAH + 1] = y1 + h / 2.0; d[DT_XYAH + 2] = w / h; d[DT_XYAH + 3] = h;
+        d[DT_CONF] = b[4]; d[DT_CLS] = b[5]; d[DT_DETIND] = sel[k]; d[DT_QUALITY] = qk; d[DT_NORM] = nrm[k];
+        v.dord()[rank] = sel[k];
+        st.dnormf[(size_t)s * st.Dcap + rank] = (float)(nrm[k] + 1e-8);
+    }
+    // tracks: camera_update (strongsort.py:168-172, only with detections) and Track.predict
+    const int nT = hdr[SH_NTRACKS];
+    const double ident[6] = {1, 0, 0, 0, 1, 0};
+    for (int p = tid; p < nT; p += blockDim.x) {
+        const int t = v.order()[p];
+        double* a = v.tab(t);
+        double* m = v.mean(t);
+        if (n > 0) {
+            double w[6];
+            for (int c = 0; c < 6; c++) w[c] = warps ? warps[(size_t)s * 6 + c] : ident[c];
+            ss_track_camera(m, a, w);
+        }
+        double x[8], P[12];
+        double* C = v.covb(t);
+        for (int c = 0; c < 8; c++) x[c] = m[c];
+        for (int c = 0; c < 12; c++) P[c] = C[c];
+        ss_track_predict(x, P, a);
+        for (int c = 0; c < 8; c++) m[c] = x[c];
+        for (int c = 0; c < 12; c++) C[c] = P[c];
+        int* ti = v.tint(t);
+        ti[TI_NUPD] = 0; ti[TI_MISS] = 0;
+    }
+    if (tid == 0) {
+        hdr[SH_NDET] = n;
+        hdr[SH_FRAME] += 1;
+        hdr[SH_NUPD] = 0; hdr[SH_STAGE3] = 0; hdr[SH_NUNM] = 0;
+        st.n_updates[s] += (unsigned long long)nT;
+    }
+}
+
+// K2 problem: every live bank feature (rows gathered through `live`) against the sorted detections
+struct SsBankProblem {
+    SsState st; int E; const float* embs;
+    __device__ CosineProblem operator()(int s) const {
+        CosineProblem p;
+        const int* hdr = st.hdr + (size_t)s * SH_COUNT;
+        p.A = st.pool32 + (size_t)s * st.Pcap * E; p.ra = st.live + (size_t)s * st.Pcap;
+        p.na = st.lnorm + (size_t)s * st.Pcap; p.nA = hdr[SH_NLIVE];
+        p.B = embs + (size_t)s * st.Dcap * E; p.rb = st.dord + (size_t)s * st.Dcap;
+        p.nb = st.dnormf + (size_t)s * st.Dcap; p.nB = hdr[SH_NDET];
+        p.E = E; p.out = st.dist + (size_t)s * st.Pcap * st.Dcap; p.out_ld = st.Dcap; p.raw = 0;
+        return p;
+    }
+};
+
+// K3: gated_metric (tracker.py:186-206) followed by _enhance_cost_matrix (linear_assignment.py:251-273,
+// the first thing min_cost_matching does to the metric's matrix) for every (confirmed track, detection)
+__global__ void __launch_bounds__(256)
+ss_cost_kernel(SsState st, SsParams pr) {
+    const int s = blockIdx.y;
+    SsView v(st, s);
+    const int nT = v.hdr()[SH_NTRACKS], n = v.hdr()[SH_NDET];
+    const int total = nT * n;
+    const float* dist = v.dist();
+    double* cost = v.cost();
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        const int p = e / n, k = e % n;
+        const int t = v.order()[p];
+        const double* a = v.tab(t);
+        if (a[ST_STATE] != (double)ST_CONFIRMED_STATE) continue;
+        const int* ti = v.tint(t);
+        double app = SS_INFTY_COST;                              // metric.distance: no samples (:616-617)
+        if (ti[TI_NBANK] > 0) {
+            float mn = CUDART_INF_F;
+            const int* ds = v.dslot(t);
+            for (int i = 0; i < ti[TI_NDIST]; i++) mn = fminf(mn, dist[(size_t)ds[i] * st.Dcap + k]);
+            app = (double)mn;
+        }
+        const double* d = v.dtab(k);
+        double c = ss_gated_entry(app, v.mean(t), v.covb(t), a, d + DT_XYAH, pr.mc_lambda, pr.id_weight);
+        cost[(size_t)p * st.Dcap + k] = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// scipy.optimize.linear_sum_assignment (rectangular_lsap.cpp: Crouse's shortest augmenting path),
+// emulated step for step by one warp so that ties -- duplicated candidate rows of the IoU stage,
+// clamped entries -- resolve as in the reference.  The caller passes nr <= nc (it transposes as
+// scipy does); col4row[i] is the column of row i on return.
+struct LsaWork {
+    double *u, *v, *spc;                       // [nr] [nc] [nc]
+    int *path, *col4row, *row4col, *remaining, *srl, *scl;
+};
+__device__ __forceinline__ LsaWork lsa_carve(double* wd, int* wi, int M) {
+    LsaWork w;
+    w.u = wd; w.v = wd + M; w.spc = wd + 2 * M;
+    w.path = wi; w.col4row = wi + M; w.row4col = wi + 2 * M; w.remaining = wi + 3 * M; w.srl = wi + 4 * M;
+    w.scl = wi + 5 * M;
+    return w;
+}
+
+template <typename CostFn>
+__device__ int lsa_scipy_warp(const CostFn& cost, int nr, int nc, const LsaWork& w) {
+    const int lane = lane_id();
+    for (int i = lane; i < nr; i += 32) { w.u[i] = 0.0; w.col4row[i] = -1; }
+    for (int j = lane; j < nc; j += 32) { w.v[j] = 0.0; w.row4col[j] = -1; }
+    __syncwarp();
+    for (int cur = 0; cur < nr; cur++) {
+        for (int j = lane; j < nc; j += 32) { w.remaining[j] = nc - j - 1; w.spc[j] = CUDART_INF; }
+        __syncwarp();
+        double min_val = 0.0;
+        int num_remaining = nc, i = cur, nsr = 0, nsc = 0, sink = -1;
+        while (sink == -1) {
+            if (lane == 0) w.srl[nsr] = i;
+            nsr++;
+            const double ui = w.u[i];
+            double bv = CUDART_INF;
+            int bit = 0x7fffffff, bun = 0;
+            for (int it = lane; it < num_remaining; it += 32) {
+                const int j = w.remaining[it];
+                const double r = ((min_val + cost(i, j)) - ui) - w.v[j];
+                double sj = w.spc[j];
+                if (r < sj) { sj = r; w.spc[j] = r; w.path[j] = i; }
+                const int un = w.row4col[j] == -1;
+                if (sj < bv || (sj == bv && un)) { bv = sj; bit = it; bun = un; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ov = shfl_xor_d(bv, o);
+                const int oit = __shfl_xor_sync(BM_FULL, bit, o), oun = __shfl_xor_sync(BM_FULL, bun, o);
+                bool take;
+                if (ov != bv) take = ov < bv;
+                else if (oun != bun) take = oun > bun;                 // an unassigned column wins a tie ...
+                else take = oun ? (oit > bit) : (oit < bit);           // ... the last such; else the first column
+                if (take) { bv = ov; bit = oit; bun = oun; }
+            }
+            if (!(bv < CUDART_INF)) return 1;                          // infeasible (NaN costs)
+            min_val = bv;
+            const int j = w.remaining[bit];
+            __syncwarp();
+            if (lane == 0) { w.remaining[bit] = w.remaining[num_remaining - 1]; w.scl[nsc] = j; }
+            num_remaining--;
+            nsc++;
+            const int rj = w.row4col[j];
+            __syncwarp();
+            if (rj == -1) sink = j; else i = rj;
+        }
+        // dual variables
+        for (int k = lane; k < nsr; k += 32) {
+            const int r = w.srl[k];
+            if (r == cur) w.u[r] += min_val;
+            else w.u[r] += min_val - w.spc[w.col4row[r]];
+        }
+        for (int k = lane; k < nsc; k += 32) { const int j = w.scl[k]; w.v[j] -= min_val - w.spc[j]; }
+        __syncwarp();
+        if (lane == 0) {                                               // augment
+            int j = sink;
+            while (true) {
+                const int r = w.path[j];
+                w.row4col[j] = r;
+                const int t = w.col4row[r];
+                w.col4row[r] = j;
+                j = t;
+                if (r == cur) break;
+            }
+        }
+        __syncwarp();
+    }
+    return 0;
+}
+
+// min_cost_matching (linear_assignment.py:14-87) on rows `rows[0..nr)` (track list positions, duplicates
+// allowed) and columns `cols[0..nc)` (sorted detection indices) of the stored matrix `c` (by list
+// position and detection): clamp at max_distance + 1e-5, assign, reject pairs above max_distance.
+// match_col[r] = accepted column position of row r or -1; the unmatched detections are returned in
+// `cols` in scipy's order (never-assigned columns ascending, then the rejected ones in row order).
+struct SsClampCost {
+    const double* c; int ld; const int* rows; const int* cols; double maxd; bool tr; const int* tsu_gate;
+    __device__ __forceinline__ double at(int r, int cpos) const {
+        const double x = c[(size_t)rows[r] * ld + cols[cpos]];
+        return x > maxd ? maxd + 1e-5 : x;
+    }
+    __device__ __forceinline__ double operator()(int i, int j) const { return tr ? at(j, i) : at(i, j); }
+};
+
+__device__ int ss_min_cost_matching(const double* c, int ld, const int* rows, int nr, int* cols, int& nc, double maxd,
+                                    const LsaWork& w, int* match_col, int* tmp) {
+    const int lane = lane_id();
+    const bool tr = nc < nr;
+    SsClampCost cf{c, ld, rows, cols, maxd, tr, nullptr};
+    if (lsa_scipy_warp(cf, tr ? nc : nr, tr ? nr : nc, w)) return 1;
+    // row -> column of the original orientation, into match_col (w.srl is free after the solve)
+    for (int r = lane; r < nr; r += 32) match_col[r] = tr ? w.row4col[r] : w.col4row[r];
+    __syncwarp();
+    // unmatched detections: columns without a row, ascending; then rejected assignments in row order
+    int* colrow = w.scl;                                               // col position -> row or -1
+    for (int j = lane; j < nc; j += 32) colrow[j] = tr ? w.col4row[j] : w.row4col[j];
+    __syncwarp();
+    int k = warp_compact(nc, tmp, 0, [&](int j) { return colrow[j] < 0; }, [&](int j) { return cols[j]; });
+    k = warp_compact(nr, tmp, k, [&](int r) { return match_col[r] >= 0 && cf.at(r, match_col[r]) > maxd; },
+                     [&](int r) { return cols[match_col[r]]; });
+    for (int r = lane; r < nr; r += 32)
+        if (match_col[r] >= 0) match_col[r] = cf.at(r, match_col[r]) > maxd ? -1 : cols[match_col[r]];
+    __syncwarp();
+    for (int j = lane; j < k; j += 32) cols[j] = tmp[j];
+    nc = k;
+    __syncwarp();
+    return 0;
+}
+
+// Unit-testable form: one warp per problem on stored matrices, scipy's own transposition rule.
+struct LsaDense {
+    const double* c; int ld; bool tr;
+    __device__ __forceinline__ double operator()(int i, int j) const { return tr ? c[(size_t)j * ld + i] : c[(size_t)i * ld + j]; }
+};
+__global__ void __launch_bounds__(128)
+lsa_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, int nc_max, const int* __restrict__ nr_,
+                 const int* __restrict__ nc_, int* __restrict__ x_out, double* wd, int* wi, int M) {
+    const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = lane_id();
+    if (b >= n_problems) return;
+    const int nr = nr_[b], nc = nc_[b];
+    int* x = x_out + (size_t)b * nr_max;
+    for (int i = lane; i < nr_max; i += 32) x[i] = -1;
+    if (nr <= 0 || nc <= 0) return;
+    LsaWork w = lsa_carve(wd + (size_t)b * 3 * M, wi + (size_t)b * 6 * M, M);
+    const bool tr = nc < nr;
+    LsaDense cf{cost + (size_t)b * nr_max * nc_max, nc_max, tr};
+    if (lsa_scipy_warp(cf, tr ? nc : nr, tr ? nr : nc, w)) return;
+    for (int r = lane; r < nr; r += 32) x[r] = tr ? w.row4col[r] : w.col4row[r];
+}
+
+// K4: Tracker._enhanced_match (tracker.py:183-281), one warp per stream
+constexpr int SS_MATCH_WPB = 4;
+__global__ void __launch_bounds__(SS_MATCH_WPB * 32)
+ss_match_kernel(SsState st, SsParams pr) {
+    const int s = blockIdx.x * SS_MATCH_WPB + (threadIdx.x >> 5), lane = lane_id();
+    if (s >= st.S) return;
+    SsView v(st, s);
+    int* hdr = v.hdr();
+    const int nT = hdr[SH_NTRACKS], n = hdr[SH_NDET];
+    const int Tc = st.Tcap, Dc = st.Dcap, M = st.M;
+    // integer work area
+    int* wi = st.wki + (size_t)s * st.wki_stride;
+    int* tmatched = wi;               wi += Tc;        // by list position: matched in stage 1 / 2
+    int* byage = wi;                  wi += Tc;        // confirmed unmatched positions grouped by time_since_update
+    int* lvl = wi;                    wi += Tc;        // the level's rows ordered by priority
+    int* rows3 = wi;                  wi += 2 * Tc;    // IoU-stage candidate rows
+    int* mcol = wi;                   wi += 2 * Tc;    // match column of a row
+    int* cols = wi;                   wi += Dc;
+    int* tmp = wi;                    wi += 2 * Tc + Dc;
+    int* dmatched = wi;               wi += Dc;
+    int* agecnt = wi;                 wi += pr.max_age + 2;
+    LsaWork w = lsa_carve(st.wkd + (size_t)s * 3 * M, wi, M);
+    int* ulist = st.ulist + (size_t)s * Dc;
+    int* unm = st.unm + (size_t)s * Dc;
+    double* cost = v.cost();
+
+    for (int p = lane; p < nT; p += 32) tmatched[p] = 0;
+    for (int k = lane; k < n; k += 32) dmatched[k] = 0;
+    __syncwarp();
+    if (n == 0) {                                   // tracker.update([]): nothing matches, the IoU stage is skipped
+        if (lane == 0) { hdr[SH_NUNM] = 0; hdr[SH_STAGE3] = 0; hdr[SH_NUPD] = 0; }
+        return;
+    }
+    int nupd = 0, bad = 0, nlsa = 0, nmatch = 0;
+    auto record = [&](int p, int k) {               // lane 0: match (track at list position p, detection k)
+        int* ti = v.tint(v.order()[p]);
+        const int c = ti[TI_NUPD];
+        if (c == 0) ulist[nupd++] = p;
+        if (c < SS_MAXUPD) v.upd(v.order()[p])[c] = k;
+        ti[TI_NUPD] = c + 1;
+        nmatch++;
+    };
+    // ---- stages 1 and 2: matching_cascade over the appearance metric
+    for (int stage = 0; stage < 2; stage++) {
+        const double thr = stage == 0 ? pr.max_cos_dist * 0.8 : pr.max_cos_dist;
+        int nc = warp_compact(n, cols, 0, [&](int k) {
+            const double c = v.dtab(k)[DT_CONF];
+            const bool in = stage == 0 ? c >= pr.conf_hi : (c >= pr.conf_lo && c < pr.conf_hi);
+            return in && !dmatched[k];
+        }, [&](int k) { return k; });
+        if (nc == 0) continue;
+        // group the confirmed, still unmatched tracks by time_since_update (stable in list order)
+        for (int a = lane; a <= pr.max_age + 1; a += 32) agecnt[a] = 0;
+        __syncwarp();
+        for (int p = lane; p < nT; p += 32) {
+            const double* a = v.tab(v.order()[p]);
+            const int age = (int)a[SS_TSU];
+            if (a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && age <= pr.max_age) atomicAdd(&agecnt[age], 1);
+        }
+        __syncwarp();
+        if (lane == 0) {                            // exclusive prefix; agecnt[a] becomes the write cursor of age a
+            int run = 0;
+            for (int a = 0; a <= pr.max_age; a++) { const int c = agecnt[a]; agecnt[a] = run; run += c; }
+            agecnt[pr.max_age + 1] = run;
+        }
+        __syncwarp();
+        for (int base = 0; base < nT; base += 32) {
+            const int p = base + lane;
+            int age = -1;
+            if (p < nT) {
+                const double* a = v.tab(v.order()[p]);
+                const int g = (int)a[SS_TSU];
+                if (a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && g <= pr.max_age) age = g;
+            }
+            const unsigned peers = __match_any_sync(BM_FULL, age);
+            if (age >= 0) {
+                const int rank = __popc(peers & ((1u << lane) - 1));
+                byage[agecnt[age] + rank] = p;
+            }
+            __syncwarp();
+            if (age >= 0 && (peers & ((1u << lane) - 1)) == 0) agecnt[age] += __popc(peers);
+            __syncwarp();
+        }
+        // agecnt[a] is now the END of age a's run; its start is the end of the previous non-empty age
+        int start = 0;
+        for (int age = 0; age <= pr.max_age && nc > 0; age++) {
+            const int end = agecnt[age];
+            const int m = end - start;
+            if (m <= 0) continue;
+            // _prioritize_tracks_by_quality (:276-285): stable sort by -(quality + stability)
+            for (int i = lane; i < m; i += 32) {
+                const int p = byage[start + i];
+                const double* a = v.tab(v.order()[p]);
+                const double key = -(a[SS_QUALITY] + a[ST_STABILITY]);
+                int rank = 0;
+                for (int j = 0; j < m; j++) {
+                    const double* b = v.tab(v.order()[byage[start + j]]);
+                    const double kj = -(b[SS_QUALITY] + b[ST_STABILITY]);
+                    rank += (kj < key || (kj == key && j < i)) ? 1 : 0;
+                }
+                lvl[rank] = p;
+            }
+            __syncwarp();
+            bad |= ss_min_cost_matching(cost, Dc, lvl, m, cols, nc, thr, w, mcol, tmp);
+            nlsa++;
+            if (lane == 0)
+                for (int r = 0; r < m; r++)
+                    if (mcol[r] >= 0) { tmatched[lvl[r]] = 1; dmatched[mcol[r]] = 1; record(lvl[r], mcol[r]); }
+            __syncwarp();
+            start = end;
+        }
+        nupd = __shfl_sync(BM_FULL, nupd, 0);
+        nmatch = __shfl_sync(BM_FULL, nmatch, 0);
+    }
+    // ---- stage 3: IoU matching.  Candidates = every non-tentative track (matched or not), then
+    // AGAIN the unmatched ones with time_since_update == 1 (tracker.py:257-259: the list is a concatenation)
+    int nr3 = warp_compact(nT, rows3, 0, [&](int p) { return v.tab(v.order()[p])[ST_STATE] != (double)ST_TENTATIVE; },
+                           [&](int p) { return p; });
+    nr3 = warp_compact(nT, rows3, nr3, [&](int p) {
+        const double* a = v.tab(v.order()[p]);
+        return a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && a[SS_TSU] == 1.0;
+    }, [&](int p) { return p; });
+    int nc3 = warp_compact(n, cols, 0, [&](int k) { return !dmatched[k] && !(v.dtab(k)[DT_CONF] < pr.conf_lo); },
+                           [&](int k) { return k; });
+    if (nr3 > 0 && nc3 > 0) {
+        // iou_cost (iou_matching.py:49-87) + _enhance_cost_matrix into the stage matrix (stages 1 / 2 are done)
+        for (int p = 0; p < nT; p++) {
+            const int t = v.order()[p];
+            const double* a = v.tab(t);
+            if (a[ST_STATE] == (double)ST_TENTATIVE) continue;
+            const bool far = a[SS_TSU] > 1.0;
+            for (int j = lane; j < nc3; j += 32) {
+                const int k = cols[j];
+                const double* d = v.dtab(k);
+                const double c = far ? SS_INFTY_COST : ss_iou_entry(v.mean(t), d + DT_TLWH);
+                cost[(size_t)p * Dc + k] = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
+            }
+        }
+        __syncwarp();
+        bad |= ss_min_cost_matching(cost, Dc, rows3, nr3, cols, nc3, pr.max_iou_dist, w, mcol, tmp);
+        nlsa++;
+        if (lane == 0) {
+            for (int r = 0; r < nr3; r++) {
+                const int p = rows3[r];
+                if (mcol[r] >= 0) { dmatched[mcol[r]] = 1; record(p, mcol[r]); }
+                else v.tint(v.order()[p])[TI_MISS] = 1;        // unmatched_tracks_3 -> mark_missed
+            }
+            hdr[SH_STAGE3] = 1;
+        }
+        __syncwarp();
+        nupd = __shfl_sync(BM_FULL, nupd, 0);
+        nmatch = __shfl_sync(BM_FULL, nmatch, 0);
+    }
+    // all_unmatched_detections: ascending (sorted) detection index
+    const int nunm = warp_compact(n, unm, 0, [&](int k) { return !dmatched[k]; }, [&](int k) { return k; });
+    if (lane == 0) {
+        hdr[SH_NUNM] = nunm; hdr[SH_NUPD] = nupd;
+        hdr[SH_LSA] += nlsa; hdr[SH_MATCH] += nmatch;
+        if (bad) ss_set_err(hdr, SS_ERR_LSA);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Feature step of Track.update (track.py:238-268 with _calculate_adaptive_ema_alpha :319-335) by one
+// warp: the new smoothed feature goes to a fresh pool slot that is pushed on the track's ring.
+__device__ void ss_feature_step(const SsView& v, const SsParams& pr, int t, int k, const float* embs) {
+    const int lane = lane_id(), E = pr.E;
+    int* ti = v.tint(t);
+    int* ring = v.ring(t);
+    double* a = v.tab(t);
+    const double* d = v.dtab(k);
+    const float* f = embs + ((size_t)v.s * v.st.Dcap + v.dord()[k]) * E;
+    const double fn = d[DT_NORM] + 1e-8;
+    const int nring = ti[TI_NRING];
+    int slot = -1;
+    if (lane == 0) slot = ss_pool_pop(v);
+    slot = __shfl_sync(BM_FULL, slot, 0);
+    if (slot < 0) return;
+    double* out = v.pool(slot, E);
+    float* out32 = v.pool32(slot, E);
+    auto nw = [&](int i) { return (double)f[i] / fn; };
+    if (nring == 0) {                                           // first feature (:261-263)
+        for (int i = lane; i < E; i += 32) { const double x = nw(i); out[i] = x; out32[i] = (float)x; }
+    } else {
+        const int ls = ring[nring - 1];
+        const double* last = v.pool(ls, E);
+        auto lf = [&](int i) { return last[i]; };
+        const double dot = warp_ddot_skx(nw, lf, E);
+        const double nn = sqrt(warp_ddot_skx(nw, nw, E));
+        const double nl = v.pq()[ls];
+        const double sim = dot / (nn * nl + 1e-8);             // :245-247
+        const double conf = d[DT_CONF];
+        const double cf = conf > 0.7 ? 1.0 : (conf > 0.3 ? 0.5 : 0.2);
+        const double af = sim > 0.7 ? 1.0 : (sim > 0.4 ? 0.7 : 0.4);
+        const double alpha = fmin(fmax(pr.ema_alpha * cf * af, 0.1), 0.95);
+        const double om = 1.0 - alpha;
+        auto sm = [&](int i) { return alpha * last[i] + om * nw(i); };
+        const double sn = sqrt(warp_ddot_skx(sm, sm, E)) + 1e-8;   // :257
+        for (int i = lane; i < E; i += 32) { const double x = sm(i) / sn; out[i] = x; out32[i] = (float)x; }
+        if (lane == 0) a[SS_APPEAR] = 0.9 * a[SS_APPEAR] + 0.1 * sim;   // :248
+    }
+    __syncwarp();
+    auto of = [&](int i) { return out[i]; };
+    const double qn = sqrt(warp_ddot_skx(of, of, E));           // partial_fit's quality of this vector (:560)
+    if (lane == 0) {
+        v.pq()[slot] = qn;
+        v.pbank()[slot] = 0;
+        v.pring()[slot] = 1;
+        if (nring == SS_RING) {                                 // features[-max_features:] (:266-268)
+            const int old = ring[0];
+            for (int i = 1; i < SS_RING; i++) ring[i - 1] = ring[i];
+            ring[SS_RING - 1] = slot;
+            v.pring()[old] = 0;
+            if (v.pbank()[old] == 0) ss_pool_release(v, old);
+        } else {
+            ring[nring] = slot;
+            ti[TI_NRING] = nring + 1;
+        }
+    }
+    __syncwarp();
+}
+
+__device__ void ss_apply_update(const SsView& v, const SsParams& pr, int t, int k, const float* embs) {
+    ss_feature_step(v, pr, t, k, embs);
+    if (lane_id() == 0) {
+        const double* d = v.dtab(k);
+        double* m = v.mean(t);
+        double* C = v.covb(t);
+        double x[8], P[12];
+        for (int c = 0; c < 8; c++) x[c] = m[c];
+        for (int c = 0; c < 12; c++) P[c] = C[c];
+        const double d7[7] = {d[DT_XYAH], d[DT_XYAH + 1], d[DT_XYAH + 2], d[DT_XYAH + 3], d[DT_CONF], d[DT_CLS],
+                              d[DT_DETIND]};
+        ss_track_update(x, P, v.tab(t), d7, pr.n_init);
+        for (int c = 0; c < 8; c++) m[c] = x[c];
+        for (int c = 0; c < 12; c++) C[c] = P[c];
+    }
+    __syncwarp();
+}
+
+// K5: Track.update for every matched track, in match order (a track matched twice is updated twice)
+__global__ void __launch_bounds__(128)
+ss_update_kernel(SsState st, SsParams pr, const float* __restrict__ embs) {
+    const int s = blockIdx.y, u = blockIdx.x * 4 + (threadIdx.x >> 5);
+    SsView v(st, s);
+    if (u >= v.hdr()[SH_NUPD]) return;
+    const int t = v.order()[st.ulist[(size_t)s * st.Dcap + u]];
+    const int c = min(v.tint(t)[TI_NUPD], SS_MAXUPD);
+    for (int i = 0; i < c; i++) ss_apply_update(v, pr, t, v.upd(t)[i], embs);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sample list of one target (NearestNeighborDistanceMetric.samples[target]) as slot references.
+// Removes the worst entry = lowest quality, newest (largest seq); all lanes converged.
+__device__ void ss_bank_evict(const SsView& v, int t) {
+    const int lane = lane_id();
+    int* ti = v.tint(t);
+    int* bs = v.bslot(t);
+    int* bq = v.bseq(t);
+    const int n = ti[TI_NBANK];
+    const double* pq = v.pq();
+    double wq = CUDART_INF;
+    int wseq = -1, wi = -1;
+    for (int i = lane; i < n; i += 32) {
+        const double q = pq[bs[i]];
+        if (q < wq || (q == wq && bq[i] > wseq)) { wq = q; wseq = bq[i]; wi = i; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const double oq = shfl_xor_d(wq, o);
+        const int os = __shfl_xor_sync(BM_FULL, wseq, o), oi = __shfl_xor_sync(BM_FULL, wi, o);
+        if (oq < wq || (oq == wq && os > wseq)) { wq = oq; wseq = os; wi = oi; }
+    }
+    if (lane == 0) {
+        const int slot = bs[wi];
+        bs[wi] = bs[n - 1]; bq[wi] = bq[n - 1];
+        ti[TI_NBANK] = n - 1;
+        int* ds = v.dslot(t);
+        int* dc = v.dcnt(t);
+        const int nd = ti[TI_NDIST];
+        for (int i = 0; i < nd; i++)
+            if (ds[i] == slot) {
+                if (--dc[i] == 0) { ds[i] = ds[nd - 1]; dc[i] = dc[nd - 1]; ti[TI_NDIST] = nd - 1; }
+                break;
+            }
+        if (--v.pbank()[slot] == 0 && v.pring()[slot] == 0) ss_pool_release(v, slot);
+    }
+    __syncwarp();
+    // new minimum quality
+    double mq = CUDART_INF;
+    for (int i = lane; i < n - 1; i += 32) mq = fmin(mq, pq[bs[i]]);
+    for (int o = 16; o > 0; o >>= 1) mq = fmin(mq, shfl_xor_d(mq, o));
+    if (lane == 0) v.bminq(t) = mq;
+    __syncwarp();
+}
+
+// samples[target].append(feature) + the budget rule (linear_assignment.py:553-573)
+__device__ void ss_bank_append(const SsView& v, const SsParams& pr, int t, int slot) {
+    const int lane = lane_id();
+    int* ti = v.tint(t);
+    const double q = v.pq()[slot];
+    const int n = ti[TI_NBANK];
+    if (n >= pr.budget && !(q > v.bminq(t))) return;            // it would be the entry that is dropped again
+    if (n >= pr.budget) ss_bank_evict(v, t);
+    if (lane == 0) {
+        const int m = ti[TI_NBANK];
+        v.bslot(t)[m] = slot;
+        v.bseq(t)[m] = ti[TI_SEQ]++;
+        ti[TI_NBANK] = m + 1;
+        v.bminq(t) = m == 0 ? q : fmin(v.bminq(t), q);
+        v.pbank()[slot] += 1;
+        int* ds = v.dslot(t);
+        int* dc = v.dcnt(t);
+        const int nd = ti[TI_NDIST];
+        int i = 0;
+        for (; i < nd; i++) if (ds[i] == slot) { dc[i]++; break; }
+        if (i == nd) { ds[nd] = slot; dc[nd] = 1; ti[TI_NDIST] = nd + 1; }
+    }
+    __syncwarp();
+}
+
+// Everything a track holds goes back to the pool (the track left the lost buffer or never entered it)
+__device__ void ss_track_release(const SsView& v, int t) {       // one thread
+    int* ti = v.tint(t);
+    for (int i = 0; i < ti[TI_NRING]; i++) {
+        const int p = v.ring(t)[i];
+        v.pring()[p] = 0;
+        if (v.pbank()[p] == 0) ss_pool_release(v, p);
+    }
+    for (int i = 0; i < ti[TI_NBANK]; i++) {
+        const int p = v.bslot(t)[i];
+        if (--v.pbank()[p] == 0 && v.pring()[p] == 0) ss_pool_release(v, p);
+    }
+    ti[TI_NRING] = 0; ti[TI_NBANK] = 0; ti[TI_NDIST] = 0;
+    int* hdr = v.hdr();
+    v.st.tfree[(size_t)v.s * v.st.Tcap + hdr[SH_NTFREE]++] = t;
+}
+
+// K6: the rest of Tracker.update (tracker.py:137-181) and StrongSort._format_outputs
+__global__ void __launch_bounds__(256)
+ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, double* __restrict__ out,
+                   int* __restrict__ nout, int out_rows) {
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+    SsView v(st, s);
+    int* hdr = v.hdr();
+    int* order = v.order();
+    int* unm = st.unm + (size_t)s * st.Dcap;
+    int* lost = st.lost + (size_t)s * 32;
+    double* sims = st.sims + (size_t)s * 32 * st.Dcap;
+    int* born = st.ulist + (size_t)s * st.Dcap;          // reused: track slots of this frame's births
+    const int E = pr.E;
+    __shared__ int s_rec_l, s_rec_u, s_nb, s_anyconf;
+    int nT = hdr[SH_NTRACKS];
+    const int n = hdr[SH_NDET];
+    // (a) mark_missed for the IoU stage's unmatched rows (tracker.py:141-142)
+    for (int p = tid; p < nT; p += blockDim.x) {
+        const int t = order[p];
+        if (v.tint(t)[TI_MISS]) ss_track_mark_missed(v.tab(t), pr.max_age);
+    }
+    __syncthreads();
+    // (b) _attempt_id_recovery (tracker.py:300-351)
+    const int nlost = hdr[SH_NLOST];
+    int nunm = hdr[SH_NUNM];
+    if (nlost > 0 && nunm > 0) {
+        for (int e = wid; e < nlost * nunm; e += nw) {
+            const int li = e / nunm, uj = e % nunm;
+            const int t = lost[li], k = unm[uj];
+            const int nr = v.tint(t)[TI_NRING];
+            double sim = -CUDART_INF;
+            if (nr > 0) {
+                const int ls = v.ring(t)[nr - 1];
+                const double* tf = v.pool(ls, E);
+                const float* f = embs + ((size_t)s * st.Dcap + v.dord()[k]) * E;
+                double acc = 0.0;
+                for (int i = lane; i < E; i += 32) acc += (double)f[i] * tf[i];
+                for (int o = 16; o > 0; o >>= 1) acc += shfl_xor_d(acc, o);
+                sim = acc / (v.dtab(k)[DT_NORM] * v.pq()[ls]);
+            }
+            if (lane == 0) sims[li * st.Dcap + uj] = sim;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        s_rec_l = -1; s_rec_u = -1;
+        if (nlost > 0 && nunm > 0)
+            for (int li = 0; li < nlost && s_rec_l < 0; li++) {
+                if (v.tint(lost[li])[TI_NRING] == 0) continue;
+                int b = 0;
+                for (int uj = 1; uj < nunm; uj++) if (sims[li * st.Dcap + uj] > sims[li * st.Dcap + b]) b = uj;
+                if (sims[li * st.Dcap + b] > 0.7) { s_rec_l = li; s_rec_u = b; }
+            }
+    }
+    __syncthreads();
+    if (s_rec_l >= 0) {
+        const int t = lost[s_rec_l], k = unm[s_rec_u];
+        if (wid == 0) {
+            if (lane == 0) { v.tab(t)[ST_STATE] = ST_TENTATIVE; v.tab(t)[SS_TSU] = 0.0; }   // "state = 1" (:337)
+            __syncwarp();
+            ss_apply_update(v, pr, t, k, embs);
+            if (lane == 0) {
+                if (nT < st.Tcap) order[nT] = t; else ss_set_err(hdr, SS_ERR_TRACKS);
+                for (int i = s_rec_l; i + 1 < nlost; i++) lost[i] = lost[i + 1];
+                hdr[SH_NLOST] = nlost - 1;
+                for (int i = s_rec_u; i + 1 < nunm; i++) unm[i] = unm[i + 1];
+                hdr[SH_MATCH] += 1;
+            }
+        }
+        __syncthreads();
+        if (nT < st.Tcap) nT++;
+        nunm--;
+    }
+    __syncthreads();
+    // (c) _initiate_track for the remaining unmatched detections, in order (tracker.py:147-150, :395-410)
+    if (tid == 0) {
+        int nb = 0;
+        for (int j = 0; j < nunm; j++) {
+            if (hdr[SH_NTFREE] <= 0 || nT + nb >= st.Tcap) { ss_set_err(hdr, SS_ERR_TRACKS); break; }
+            const int t = st.tfree[(size_t)s * st.Tcap + --hdr[SH_NTFREE]];
+            born[j] = t;
+            v.tint(t)[TI_ID] = hdr[SH_NEXT_ID]++;
+            order[nT + nb] = t;
+            nb++;
+        }
+        s_nb = nb;
+        hdr[SH_BIRTHS] += nb;
+    }
+    __syncthreads();
+    const int nb = s_nb;
+    for (int j = wid; j < nb; j += nw) {
+        const int t = born[j], k = unm[j];
+        const double* d = v.dtab(k);
+        int* ti = v.tint(t);
+        if (lane == 0) {
+            double x[8], P[12];
+            cv8_initiate<CV8_XYAH>(d + DT_XYAH, x, P);
+            for (int c = 0; c < 8; c++) v.mean(t)[c] = x[c];
+            for (int c = 0; c < 12; c++) v.covb(t)[c] = P[c];
+            double* a = v.tab(t);
+            for (int c = 0; c < ST_FIELDS; c++) a[c] = 0.0;
+            a[SS_AGE] = 1.0; a[SS_HITS] = 1.0; a[SS_MOTION] = 1.0; a[SS_APPEAR] = 1.0;
+            a[SS_QUALITY] = d[DT_QUALITY];
+            a[SS_HI_STREAK] = d[DT_CONF] > 0.7 ? 1.0 : 0.0;
+            a[SS_CONF] = d[DT_CONF]; a[SS_CLS] = d[DT_CLS];
+            a[ST_STATE] = pr.born_confirmed ? (double)ST_CONFIRMED_STATE : (double)ST_TENTATIVE;
+            a[ST_CONFIRMED] = 1.0; a[ST_NPOS] = 1.0; a[ST_PX] = d[DT_XYAH]; a[ST_PY] = d[DT_XYAH + 1];
+            a[ST_NCONF] = 1.0; a[ST_CONF0] = d[DT_CONF]; a[ST_DETIND] = d[DT_DETIND];
+            ti[TI_NRING] = 0; ti[TI_NBANK] = 0; ti[TI_NDIST] = 0; ti[TI_SEQ] = 0; ti[TI_NUPD] = 0; ti[TI_MISS] = 0;
+            ti[TI_LOSTFRAME] = 0;
+        }
+        __syncwarp();
+        ss_feature_step(v, pr, t, k, embs);                 // first feature: the normalised detection feature
+    }
+    __syncthreads();
+    nT += nb;
+    // (d) deleted tracks -> lost buffer (tracker.py:152-163), compaction of the list
+    if (tid == 0) {
+        const int now = n > 0 ? hdr[SH_FRAME] : hdr[SH_NHIST];      // frame_id is None for tracker.update([])
+        int nl = hdr[SH_NLOST], w = 0;
+        for (int p = 0; p < nT; p++) {
+            const int t = order[p];
+            if (v.tab(t)[ST_STATE] != (double)ST_DELETED) { order[w++] = t; continue; }
+            bool kept = false;
+            if (nl < SS_LOST) { v.tint(t)[TI_LOSTFRAME] = now; lost[nl++] = t; kept = true; }
+            int k2 = 0;
+            for (int i = 0; i < nl; i++) {
+                const int lt = lost[i];
+                if (now - v.tint(lt)[TI_LOSTFRAME] < pr.max_age) lost[k2++] = lt;
+                else ss_track_release(v, lt);
+            }
+            nl = k2;
+            if (!kept) ss_track_release(v, t);
+        }
+        hdr[SH_NLOST] = nl;
+        hdr[SH_NTRACKS] = w;
+        hdr[SH_NHIST] = min(hdr[SH_NHIST] + 1, 100);
+        int any = 0;
+        for (int p = 0; p < w && !any; p++) any = v.tab(order[p])[ST_STATE] == (double)ST_CONFIRMED_STATE;
+        s_anyconf = any;
+    }
+    __syncthreads();
+    nT = hdr[SH_NTRACKS];
+    // (e) metric.partial_fit (tracker.py:165-178, linear_assignment.py:538-593)
+    if (s_anyconf) {
+        const int keep = pr.budget / 4 < 5 ? pr.budget / 4 : 5;
+        const int nl = hdr[SH_NLOST];
+        for (int p = wid; p < nT + nl; p += nw) {
+            const int t = p < nT ? order[p] : lost[p - nT];
+            int* ti = v.tint(t);
+            if (p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE) {
+                const int nr = ti[TI_NRING];
+                for (int i = 0; i < nr; i++) ss_bank_append(v, pr, t, v.ring(t)[i]);
+            } else {
+                while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);        // inactive target (:575-593)
+            }
+        }
+    }
+    __syncthreads();
+    // (f) _format_outputs (strongsort.py:329-359): confirmed tracks updated this frame, in list order
+    if (wid == 0) {
+        double* o = out + (size_t)s * out_rows * 8;
+        int k = 0;
+        for (int base = 0; base < nT; base += 32) {
+            const int p = base + lane;
+            bool ok = false;
+            int t = 0;
+            if (p < nT) {
+                t = order[p];
+                const double* a = v.tab(t);
+                ok = a[ST_STATE] == (double)ST_CONFIRMED_STATE && a[SS_TSU] < 1.0;
+            }
+            const unsigned b = __ballot_sync(BM_FULL, ok);
+            if (ok) {
+                const int r = k + __popc(b & ((1u << lane) - 1));
+                if (r < out_rows) {
+                    const double* m = v.mean(t);
+                    const double* a = v.tab(t);
+                    const double w = m[2] * m[3];
+                    const double x1 = m[0] - w / 2.0, y1 = m[1] - m[3] / 2.0;       // to_tlbr (track.py:144-171)
+                    double* row = o + (size_t)r * 8;
+                    row[0] = x1; row[1] = y1; row[2] = x1 + w; row[3] = y1 + m[3];
+                    row[4] = v.tint(t)[TI_ID]; row[5] = a[SS_CONF]; row[6] = a[SS_CLS]; row[7] = a[ST_DETIND];
+                }
+            }
+            k += __popc(b);
+        }
+        if (lane == 0) nout[s] = k < out_rows ? k : out_rows;
+    }
+    __syncthreads();
+    // (g) merge the deferred frees, rebuild the list of features some sample list references
+    if (tid == 0) {
+        const int nf = hdr[SH_NPFREED];
+        int np = hdr[SH_NPFREE];
+        for (int i = 0; i < nf; i++) v.pfree()[np++] = v.pfreed()[i];
+        hdr[SH_NPFREE] = np; hdr[SH_NPFREED] = 0;
+        hdr[SH_NLIVE] = 0;
+    }
+    __syncthreads();
+    int* live = st.live + (size_t)s * st.Pcap;
+    float* lnorm = st.lnorm + (size_t)s * st.Pcap;
+    for (int p = tid; p < st.Pcap; p += blockDim.x)
+        if (v.pbank()[p] > 0) {
+            const int k = atomicAdd(&hdr[SH_NLIVE], 1);
+            live[k] = p;
+            lnorm[k] = (float)(v.pq()[p] + 1e-8);
+        }
+}
+
+__global__ void ss_reset_kernel(SsState st) {
+    const int s = blockIdx.x;
+    SsView v(st, s);
+    int* hdr = v.hdr();
+    for (int i = threadIdx.x; i < st.Tcap; i += blockDim.x) st.tfree[(size_t)s * st.Tcap + i] = st.Tcap - 1 - i;
+    for (int i = threadIdx.x; i < st.Pcap; i += blockDim.x) {
+        v.pfree()[i] = st.Pcap - 1 - i; v.pbank()[i] = 0; v.pring()[i] = 0;
+    }
+    for (int i = threadIdx.x; i < st.Tcap * TI_COUNT; i += blockDim.x) st.tint[(size_t)s * st.Tcap * TI_COUNT + i] = 0;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < SH_COUNT; i++) hdr[i] = 0;
+        hdr[SH_NTFREE] = st.Tcap; hdr[SH_NPFREE] = st.Pcap; hdr[SH_NEXT_ID] = 1;
+        st.n_updates[s] = 0;
+    }
+}
+
+}  // namespace bm
+
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct SsEngine {
+    bm::SsState st;
+    bm::SsParams pr;
+    std::vector<void*> allocs;
+    int device = 0;
+    cudaEvent_t ev[7];
+    bool timing = false, timed = false;
+};
+
+int ss_fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    char msg[256];
+    if (e != cudaSuccess) snprintf(msg, sizeof(msg), "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(msg, sizeof(msg), "%s", what);
+    bm::set_last_error(msg);
+    return code;
+}
+
+template <typename T>
+cudaError_t ss_alloc(SsEngine* e, T** p, size_t n) {
+    cudaError_t r = cudaMalloc(reinterpret_cast<void**>(p), n * sizeof(T));
+    if (r == cudaSuccess) e->allocs.push_back(*p);
+    return r;
+}
+
+#define SS_CUDA(call)                                            \
+    do {                                                         \
+        cudaError_t e_ = (call);                                 \
+        if (e_ != cudaSuccess) return ss_fail(-2, #call, e_);    \
+    } while (0)
+
+size_t ss_prep_smem(int Dcap) { return (size_t)Dcap * (8 + 8 + 4) + 16; }
+
+}  // namespace
+
+extern "C" {
+
+int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int track_cap, int det_cap, int pool_cap,
+                         void** handle) {
+    if (!cfg || !handle || n_streams <= 0 || track_cap <= 0 || det_cap <= 0 || pool_cap <= 0 || cfg->emb_dim <= 0)
+        return ss_fail(-1, "bm_strongsort_create: bad argument");
+    if (cfg->nn_budget < 1 || cfg->nn_budget > 1024) return ss_fail(-1, "bm_strongsort_create: nn_budget must be in 1..1024");
+    if (cfg->max_age < 1 || cfg->max_age > 4096) return ss_fail(-1, "bm_strongsort_create: max_age out of range");
+    SsEngine* e = new (std::nothrow) SsEngine();
+    if (!e) return ss_fail(-3, "out of host memory");
+    bm::SsState& st = e->st;
+    bm::SsParams& pr = e->pr;
+    pr.min_conf = cfg->min_conf; pr.max_cos_dist = cfg->max_cos_dist; pr.max_iou_dist = cfg->max_iou_dist;
+    pr.mc_lambda = cfg->mc_lambda; pr.ema_alpha = cfg->ema_alpha; pr.conf_hi = cfg->conf_thresh_high;
+    pr.conf_lo = cfg->conf_thresh_low; pr.id_weight = cfg->id_preservation_weight;
+    pr.max_age = cfg->max_age; pr.n_init = cfg->n_init; pr.budget = cfg->nn_budget;
+    pr.born_confirmed = cfg->born_confirmed; pr.E = cfg->emb_dim;
+    st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap; st.Pcap = pool_cap; st.B = cfg->nn_budget;
+    st.M = 2 * track_cap + det_cap;
+    const size_t S = n_streams, T = track_cap, D = det_cap, P = pool_cap, B = st.B, M = st.M, E = pr.E;
+    st.wki_stride = T * 3 + 2 * T + 2 * T + D + (2 * T + D) + D + (size_t)pr.max_age + 2 + 6 * M + 8;
+    cudaError_t r = cudaGetDevice(&e->device);
+    auto A = [&](auto** p, size_t n) { if (r == cudaSuccess) r = ss_alloc(e, p, n); };
+    A(&st.mean, S * T * 8); A(&st.covb, S * T * 12); A(&st.tab, S * T * bm::ST_FIELDS);
+    A(&st.tint, S * T * bm::TI_COUNT); A(&st.ring, S * T * bm::SS_RING);
+    A(&st.bslot, S * T * B); A(&st.bseq, S * T * B); A(&st.dslot, S * T * B); A(&st.dcnt, S * T * B);
+    A(&st.bminq, S * T); A(&st.upd, S * T * bm::SS_MAXUPD); A(&st.order, S * T); A(&st.lost, S * 32);
+    A(&st.tfree, S * T); A(&st.hdr, S * bm::SH_COUNT); A(&st.n_updates, S);
+    A(&st.pool, S * P * E); A(&st.pool32, S * P * E); A(&st.pq, S * P);
+    A(&st.pbank, S * P); A(&st.pring, S * P); A(&st.pfree, S * P); A(&st.pfreed, S * P); A(&st.live, S * P);
+    A(&st.lnorm, S * P); A(&st.dist, S * P * D); A(&st.cost, S * T * D);
+    A(&st.dtab, S * D * bm::DT_COUNT); A(&st.dord, S * D); A(&st.dnormf, S * D);
+    A(&st.ulist, S * D); A(&st.unm, S * D); A(&st.wki, S * st.wki_stride);
+    A(&st.wkd, S * 3 * M); A(&st.sims, S * 32 * D);
+    for (int i = 0; i < 7 && r == cudaSuccess; i++) r = cudaEventCreate(&e->ev[i]);
+    if (r == cudaSuccess)
+        r = cudaFuncSetAttribute(bm::cosine_tc_kernel<bm::SsBankProblem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bm::cosine_tc_smem_bytes());
+    if (r == cudaSuccess && ss_prep_smem(det_cap) > 48 * 1024)
+        r = cudaFuncSetAttribute(bm::ss_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)ss_prep_smem(det_cap));
+    if (r == cudaSuccess) {
+        bm::ss_reset_kernel<<<n_streams, 256>>>(st);
+        r = cudaGetLastError();
+        if (r == cudaSuccess) r = cudaDeviceSynchronize();
+    }
+    if (r != cudaSuccess) {
+        for (void* p : e->allocs) cudaFree(p);
+        delete e;
+        return ss_fail(-2, "bm_strongsort_create", r);
+    }
+    *handle = e;
+    return 0;
+}
+
+int bm_linear_sum_assignment_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                                   const int* d_nc, int* d_x, void* d_work, void* stream) {
+    if (n_problems <= 0) return 0;
+    if (!d_cost || !d_nr || !d_nc || !d_x || !d_work || nr_max <= 0 || nc_max <= 0)
+        return ss_fail(-1, "bm_linear_sum_assignment_batch: bad argument");
+    const int M = nr_max > nc_max ? nr_max : nc_max;
+    double* wd = static_cast<double*>(d_work);
+    int* wi = reinterpret_cast<int*>(wd + (size_t)n_problems * 3 * M);
+    bm::lsa_batch_kernel<<<(n_problems + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, d_x, wd, wi, M);
+    SS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int bm_strongsort_destroy(void* handle) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e) return 0;
+    for (void* p : e->allocs) cudaFree(p);
+    for (int i = 0; i < 7; i++) cudaEventDestroy(e->ev[i]);
+    delete e;
+    return 0;
+}
+
+int bm_strongsort_reset(void* handle, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e) return ss_fail(-1, "bm_strongsort_reset: null handle");
+    bm::ss_reset_kernel<<<e->st.S, 256, 0, static_cast<cudaStream_t>(stream)>>>(e->st);
+    SS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_embs || !d_out || !d_nout) return ss_fail(-1, "bm_strongsort_step: bad argument");
+    const bm::SsState& st = e->st;
+    const bm::SsParams& pr = e->pr;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool tm = e->timing;
+    if (tm) cudaEventRecord(e->ev[0], s);
+    bm::ss_prep_kernel<<<st.S, 256, ss_prep_smem(st.Dcap), s>>>(st, pr, d_dets, d_ndets, d_embs, d_warps);
+    if (tm) cudaEventRecord(e->ev[1], s);
+    bm::SsBankProblem pb{st, pr.E, d_embs};
+    bm::cosine_tc_kernel<bm::SsBankProblem><<<dim3((st.Pcap + bm::TC_M - 1) / bm::TC_M, st.S), bm::TC_NT,
+                                              bm::cosine_tc_smem_bytes(), s>>>(pb);
+    if (tm) cudaEventRecord(e->ev[2], s);
+    bm::ss_cost_kernel<<<dim3(8, st.S), 256, 0, s>>>(st, pr);
+    if (tm) cudaEventRecord(e->ev[3], s);
+    bm::ss_match_kernel<<<(st.S + bm::SS_MATCH_WPB - 1) / bm::SS_MATCH_WPB, bm::SS_MATCH_WPB * 32, 0, s>>>(st, pr);
+    if (tm) cudaEventRecord(e->ev[4], s);
+    bm::ss_update_kernel<<<dim3((st.Dcap + 3) / 4, st.S), 128, 0, s>>>(st, pr, d_embs);
+    if (tm) cudaEventRecord(e->ev[5], s);
+    bm::ss_finalize_kernel<<<st.S, 256, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
+    if (tm) { cudaEventRecord(e->ev[6], s); e->timed = true; }
+    SS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e) return ss_fail(-1, "bm_strongsort_counters: null handle");
+    const bm::SsState& st = e->st;
+    SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    std::vector<int> hdr((size_t)st.S * bm::SH_COUNT);
+    std::vector<unsigned long long> nu(st.S);
+    SS_CUDA(cudaMemcpy(hdr.data(), st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(nu.data(), st.n_updates, nu.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    int err = 0;
+    unsigned long long o[4] = {0, 0, 0, 0};
+    for (int s = 0; s < st.S; s++) {
+        const int* h = hdr.data() + (size_t)s * bm::SH_COUNT;
+        err |= h[bm::SH_ERR];
+        o[0] += nu[s]; o[1] += (unsigned)h[bm::SH_LSA]; o[2] += (unsigned)h[bm::SH_MATCH]; o[3] += (unsigned)h[bm::SH_BIRTHS];
+    }
+    if (err_bits) *err_bits = err;
+    if (out4) for (int i = 0; i < 4; i++) out4[i] = o[i];
+    return 0;
+}
+
+int bm_strongsort_time_kernels(void* handle, int enable) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e) return ss_fail(-1, "bm_strongsort_time_kernels: null handle");
+    e->timing = enable != 0; e->timed = false;
+    return 0;
+}
+
+int bm_strongsort_kernel_times(void* handle, float* ms6) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e || !ms6) return ss_fail(-1, "bm_strongsort_kernel_times: bad argument");
+    if (!e->timed) return ss_fail(-1, "bm_strongsort_kernel_times: no timed step");
+    SS_CUDA(cudaEventSynchronize(e->ev[6]));
+    for (int i = 0; i < 6; i++) SS_CUDA(cudaEventElapsedTime(&ms6[i], e->ev[i], e->ev[i + 1]));
+    return 0;
+}
+
+int bm_strongsort_peek(void* handle, int stream_index, int* n_tracks, int* n_lost, double* h_mean, double* h_cov,
+                       double* h_tab, int* h_ids, int* h_nbank, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e || stream_index < 0 || stream_index >= e->st.S) return ss_fail(-1, "bm_strongsort_peek: bad argument");
+    const bm::SsState& st = e->st;
+    const size_t s = stream_index, T = st.Tcap;
+    SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    std::vector<int> hdr(bm::SH_COUNT), order(T), tint(T * bm::TI_COUNT);
+    std::vector<double> mean(T * 8), covb(T * 12), tab(T * bm::ST_FIELDS);
+    SS_CUDA(cudaMemcpy(hdr.data(), st.hdr + s * bm::SH_COUNT, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(order.data(), st.order + s * T, T * sizeof(int), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(tint.data(), st.tint + s * T * bm::TI_COUNT, tint.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(mean.data(), st.mean + s * T * 8, mean.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(covb.data(), st.covb + s * T * 12, covb.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(tab.data(), st.tab + s * T * bm::ST_FIELDS, tab.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    const int n = hdr[bm::SH_NTRACKS];
+    if (n_tracks) *n_tracks = n;
+    if (n_lost) *n_lost = hdr[bm::SH_NLOST];
+    for (int p = 0; p < n; p++) {
+        const int t = order[p];
+        if (h_mean) for (int c = 0; c < 8; c++) h_mean[(size_t)p * 8 + c] = mean[(size_t)t * 8 + c];
+        if (h_cov) bm::xyah_expand(covb.data() + (size_t)t * 12, h_cov + (size_t)p * 64);
+        if (h_tab) for (int c = 0; c < bm::ST_FIELDS; c++) h_tab[(size_t)p * bm::ST_FIELDS + c] = tab[(size_t)t * bm::ST_FIELDS + c];
+        if (h_ids) h_ids[p] = tint[(size_t)t * bm::TI_COUNT + bm::TI_ID];
+        if (h_nbank) h_nbank[p] = tint[(size_t)t * bm::TI_COUNT + bm::TI_NBANK];
+    }
+    return 0;
+}
+
+}  // extern "C"

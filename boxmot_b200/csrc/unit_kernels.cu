@@ -5,6 +5,7 @@
 #include "kf_xysr.cuh"
 #include "kf_xyah.cuh"
 #include "cosine_tc.cuh"
+#include "strongsort_units.cuh"
 #include <algorithm>
 #include "lapjv.cuh"
 #include "lap_rect.cuh"
@@ -162,14 +163,7 @@ __global__ void cv8_gating_kernel(const double* mean, const double* cov, int nt,
 
 
 // ---- StrongSORT cost post-processing (strongsort/sort/linear_assignment.py, tracker.py), one thread per
-// (track, detection) entry.  Per-track attribute table: SS_* columns, one row of SS_FIELDS doubles per track.
-enum { SS_AGE = 0, SS_HITS, SS_TSU, SS_MOTION, SS_APPEAR, SS_QUALITY, SS_HI_STREAK, SS_LO_STREAK, SS_HAS_VEL, SS_VX,
-       SS_VY, SS_CONF, SS_CLS, SS_FIELDS };
-constexpr double SS_INFTY_COST = 1e5;        // linear_assignment.py:11
-constexpr double SS_CHI2INV95_4 = 9.4877;    // matching.py chi2inv95[4]
-
-// gated_metric after metric.distance (tracker.py:186-206): gate_cost_matrix (linear_assignment.py:174-248)
-// + _apply_id_preservation_weighting (tracker.py:283-298)
+// (track, detection) entry; the per-entry arithmetic lives in strongsort_units.cuh (shared with the engine).
 __global__ void ss_gated_metric_kernel(double* __restrict__ cost, const double* __restrict__ mean,
                                        const double* __restrict__ cov, const double* __restrict__ trk, int nt,
                                        const double* __restrict__ meas, int nd, double mc_lambda, double id_weight) {
@@ -179,30 +173,7 @@ __global__ void ss_gated_metric_kernel(double* __restrict__ cost, const double* 
     double x[8], P[12], z[4];
     cv8_load(mean, cov, t, x, P);
     for (int c = 0; c < 4; c++) z[c] = meas[(size_t)d * 4 + c];
-    const double* a = trk + (size_t)t * SS_FIELDS;
-    const double gd = cv8_gating<CV8_XYAH>(x, P, z, false, false);
-    double c = cost[e];
-    if (gd > SS_CHI2INV95_4) c = SS_INFTY_COST;                              // :232
-    // _compute_enhanced_motion_cost (:288-307)
-    double motion = gd * (2.0 - a[SS_MOTION]);
-    if (a[SS_HAS_VEL] != 0.0) {
-        const double dx = z[0] - (x[0] + a[SS_VX]), dy = z[1] - (x[1] + a[SS_VY]);
-        const double err = sqrt(dx * dx + dy * dy);
-        motion = motion * (1.0 + fmin(err / 50.0, 1.0));
-    }
-    // _compute_adaptive_lambda (:310-329)
-    double lam = mc_lambda + (1.0 - mc_lambda) * fmin(a[SS_AGE] / 10.0, 1.0) * 0.1;
-    lam = lam * (0.8 + 0.4 * a[SS_MOTION]);
-    if (a[SS_APPEAR] < 0.5) lam = fmin(lam * 1.2, 0.99);
-    lam = fmin(fmax(lam, 0.1), 0.99);
-    c = lam * c + (1.0 - lam) * motion;                                      // :241-243
-    // _apply_track_specific_adjustments (:332-352)
-    if (a[SS_QUALITY] > 0.8) c = c * 0.95;
-    if (a[SS_HITS] > 10.0 && a[SS_TSU] == 0.0) c = c * 0.98;
-    if (a[SS_HI_STREAK] > 3.0) c = c * 0.97;
-    if (a[SS_LO_STREAK] > 2.0) c = c * 1.05;
-    if (id_weight > 0.0) c = c * (1.0 - id_weight * fmin(a[SS_HITS] / 10.0, 1.0));   // tracker.py:294-296
-    cost[e] = c;
+    cost[e] = ss_gated_entry(cost[e], x, P, trk + (size_t)t * SS_FIELDS, z, mc_lambda, id_weight);
 }
 
 // _enhance_cost_matrix (linear_assignment.py:251-273); det [nd][3] = quality_score, conf, cls
@@ -210,33 +181,18 @@ __global__ void ss_enhance_cost_kernel(double* __restrict__ cost, const double* 
                                        const double* __restrict__ det, int nd) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nt * nd) return;
-    const double* a = trk + (size_t)(e / nd) * SS_FIELDS;
     const double* b = det + (size_t)(e % nd) * 3;
-    double c = cost[e];
-    const double q = 1.0 - ((a[SS_QUALITY] + b[0]) / 2.0 - 0.5) * 0.2;       // :355-364
-    c = c * fmin(fmax(q, 0.8), 1.2);
-    if (a[SS_CLS] == b[2]) c = c * 0.9;                                      // :265-267
-    if (a[SS_CONF] > 0.7 && b[1] > 0.7) c = c * 0.9;                         // :367-379
-    else if (a[SS_CONF] < 0.3 || b[1] < 0.3) c = c * 1.1;
-    cost[e] = c;
+    cost[e] = ss_enhance_entry(cost[e], trk + (size_t)(e / nd) * SS_FIELDS, b[0], b[1], b[2]);
 }
 
-// iou_cost (iou_matching.py:49-87): 1 - IoU of Track.to_tlwh() with the detections' tlwh; rows of tracks
-// with time_since_update > 1 are INFTY_COST
+// iou_cost (iou_matching.py:49-87): rows of tracks with time_since_update > 1 are INFTY_COST
 __global__ void ss_iou_cost_kernel(const double* __restrict__ mean, const double* __restrict__ trk, int nt,
                                    const double* __restrict__ tlwh, int nd, double* __restrict__ out) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nt * nd) return;
     const int t = e / nd, d = e % nd;
     if (trk[(size_t)t * SS_FIELDS + SS_TSU] > 1.0) { out[e] = SS_INFTY_COST; return; }
-    const double* m = mean + (size_t)t * 8;
-    const double h = m[3], w = m[2] * h;                 // track.py:154-157
-    const double x1 = m[0] - w / 2.0, y1 = m[1] - h / 2.0;
-    const double* b = tlwh + (size_t)d * 4;
-    const double tlx = fmax(x1, b[0]), tly = fmax(y1, b[1]);
-    const double brx = fmin(x1 + w, b[0] + b[2]), bry = fmin(y1 + h, b[1] + b[3]);
-    const double inter = fmax(0.0, brx - tlx) * fmax(0.0, bry - tly);
-    out[e] = 1.0 - inter / (w * h + b[2] * b[3] - inter);
+    out[e] = ss_iou_entry(mean + (size_t)t * 8, tlwh + (size_t)d * 4);
 }
 
 
@@ -289,110 +245,19 @@ __global__ void ss_feature_update_kernel(const float* __restrict__ last, const i
 }
 
 
-// StrongSORT Track.predict / update / mark_missed (strongsort/sort/track.py:195-317) on a flat per-track
-// table, one thread per track.  Columns 0..12 are the SS_* columns (SS_HAS_VEL = len(velocity_history),
-// capped at 10, SS_VX/VY = velocity_history[-1]); then:
-enum { ST_STATE = 13, ST_STABILITY, ST_CONFIRMED, ST_MISSED, ST_NPOS, ST_PX, ST_PY, ST_NCONF, ST_CONF0,
-       ST_CONF_CAP = 20, ST_DETIND = ST_CONF0 + ST_CONF_CAP, ST_FIELDS = ST_DETIND + 1 };
-enum { ST_TENTATIVE = 1, ST_CONFIRMED_STATE = 2, ST_DELETED = 3 };
-
-__device__ __forceinline__ double ss_norm2(double x, double y) { return sqrt(x * x + y * y); }
-
+// StrongSORT Track.predict / update / mark_missed / camera_update (strongsort/sort/track.py:173-317) on a
+// flat per-track table, one thread per track (strongsort_units.cuh).
 __global__ void ss_track_kernel(int op, double* __restrict__ mean, double* __restrict__ cov, double* __restrict__ trk,
                                 const double* __restrict__ det, int n, int n_init, int max_age) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double* a = trk + (size_t)i * ST_FIELDS;
-    if (op == 2) {                                                   // mark_missed (:303-317)
-        a[ST_MISSED] += 1.0;
-        int thr = max_age;
-        if (a[SS_QUALITY] > 0.8) thr = (int)((double)max_age * 1.5);
-        else if (a[SS_QUALITY] < 0.3) thr = (int)((double)max_age * 0.5);
-        if (a[ST_STATE] == (double)ST_TENTATIVE) a[ST_STATE] = ST_DELETED;
-        else if (a[SS_TSU] > (double)thr) a[ST_STATE] = ST_DELETED;
-        return;
-    }
-    if (op == 3) {                                                   // camera_update (:173-189); det = 2x3 warp
-        const double* w = det + (size_t)i * 7;
-        double* m = mean + (size_t)i * 8;
-        const double bw0 = m[2] * m[3];
-        const double x1 = m[0] - bw0 / 2.0, y1 = m[1] - m[3] / 2.0, x2 = x1 + bw0, y2 = y1 + m[3];   // to_tlbr (:159-171)
-        const double x1w = w[0] * x1 + w[1] * y1 + w[2], y1w = w[3] * x1 + w[4] * y1 + w[5];
-        const double x2w = w[0] * x2 + w[1] * y2 + w[2], y2w = w[3] * x2 + w[4] * y2 + w[5];
-        const double bw = x2w - x1w, bh = y2w - y1w;
-        const double cx = x1w + bw / 2.0, cy = y1w + bh / 2.0;
-        const double px = m[0], py = m[1];
-        m[0] = cx; m[1] = cy; m[2] = bw / bh; m[3] = bh;
-        if (a[SS_HAS_VEL] >= 2.0) {
-            const double ax = cx - px, ay = cy - py;
-            const double mx = (px + a[SS_VX]) - px, my = (py + a[SS_VY]) - py;
-            const double nm = ss_norm2(mx, my);
-            double cons;
-            if (nm > 0.0) cons = fmax(0.0, 1.0 - ss_norm2(ax - mx, ay - my) / fmax(nm * 0.5, 10.0));
-            else cons = ss_norm2(ax, ay) < 5.0 ? 1.0 : 0.5;
-            a[SS_MOTION] = 0.8 * a[SS_MOTION] + 0.2 * cons;
-        }
-        return;
-    }
+    if (op == 2) { ss_track_mark_missed(a, max_age); return; }
+    if (op == 3) { ss_track_camera(mean + (size_t)i * 8, a, det + (size_t)i * 7); return; }
     double x[8], P[12];
     cv8_load(mean, cov, i, x, P);
-    if (op == 0) {                                                   // predict (:195-219)
-        cv8_predict<CV8_XYAH>(x, P);
-        a[SS_AGE] += 1.0;
-        a[SS_TSU] += 1.0;
-        a[SS_VX] = x[4]; a[SS_VY] = x[5];
-        a[SS_HAS_VEL] = fmin(a[SS_HAS_VEL] + 1.0, 10.0);
-        const double px = a[ST_PX], py = a[ST_PY], had = a[ST_NPOS];
-        a[ST_PX] = x[0]; a[ST_PY] = x[1];
-        a[ST_NPOS] = fmin(had + 1.0, 10.0);
-        if (had >= 1.0 && a[SS_HAS_VEL] >= 2.0) {                    // _update_motion_consistency (:379-399)
-            const double ax = x[0] - px, ay = x[1] - py;
-            const double mx = (px + x[4]) - px, my = (py + x[5]) - py;
-            const double nm = ss_norm2(mx, my);
-            double cons;
-            if (nm > 0.0) cons = fmax(0.0, 1.0 - ss_norm2(ax - mx, ay - my) / fmax(nm * 0.5, 10.0));
-            else cons = ss_norm2(ax, ay) < 5.0 ? 1.0 : 0.5;
-            a[SS_MOTION] = 0.8 * a[SS_MOTION] + 0.2 * cons;
-        }
-    } else {                                                         // update (:221-301), feature step apart
-        const double* d = det + (size_t)i * 7;
-        const double conf = d[4];
-        a[SS_CONF] = conf; a[SS_CLS] = d[5]; a[ST_DETIND] = d[6];
-        double z[4] = {d[0], d[1], d[2], d[3]};
-        cv8_update<CV8_XYAH>(x, P, z, conf);
-        int nh = (int)a[ST_NCONF];
-        if (nh >= ST_CONF_CAP) {
-            for (int k = 1; k < ST_CONF_CAP; k++) a[ST_CONF0 + k - 1] = a[ST_CONF0 + k];
-            nh = ST_CONF_CAP - 1;
-        }
-        a[ST_CONF0 + nh] = conf;
-        nh++;
-        a[ST_NCONF] = nh;
-        if (conf > 0.7) { a[SS_HI_STREAK] += 1.0; a[SS_LO_STREAK] = 0.0; }
-        else if (conf < 0.3) { a[SS_LO_STREAK] += 1.0; a[SS_HI_STREAK] = 0.0; }
-        else { a[SS_LO_STREAK] = 0.0; a[SS_HI_STREAK] = 0.0; }
-        a[SS_HITS] += 1.0;
-        a[ST_CONFIRMED] += 1.0;
-        a[SS_TSU] = 0.0;
-        double sum = 0.0;
-        for (int k = 0; k < nh; k++) sum += a[ST_CONF0 + k];
-        const double avg = sum / nh;
-        double var = 0.0;
-        for (int k = 0; k < nh; k++) { const double e = a[ST_CONF0 + k] - avg; var += e * e; }
-        const double sd = sqrt(var / nh);
-        double cq = conf;                                            // _update_quality_score (:337-359)
-        if (nh > 1) cq = 0.7 * cq + 0.3 * avg * (1.0 - sd);
-        const double q = cq + fmin(a[SS_HITS] / 20.0, 0.2) + fmax(0.0, (a[SS_APPEAR] - 0.5) * 0.2) +
-                         fmax(0.0, (a[SS_MOTION] - 0.5) * 0.1);
-        a[SS_QUALITY] = fmin(fmax(q, 0.0), 1.0);
-        const double cs = nh > 3 ? 1.0 - fmin(sd, 1.0) : 0.5;        // _update_stability_score (:361-377)
-        const double hit_rate = a[ST_CONFIRMED] / fmax(a[SS_AGE], 1.0);
-        const double cons = 0.4 * a[SS_APPEAR] + 0.3 * a[SS_MOTION] + 0.3 * cs;
-        a[ST_STABILITY] = fmin(fmax(0.5 * hit_rate + 0.5 * cons, 0.0), 1.0);
-        if (a[ST_STATE] == (double)ST_TENTATIVE &&
-            (a[SS_HITS] >= (double)n_init || (a[SS_HITS] >= 1.0 && a[SS_QUALITY] > 0.8)))
-            a[ST_STATE] = ST_CONFIRMED_STATE;
-    }
+    if (op == 0) ss_track_predict(x, P, a);
+    else ss_track_update(x, P, a, det + (size_t)i * 7, n_init);
     cv8_store(mean, cov, i, x, P);
 }
 

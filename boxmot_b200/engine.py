@@ -617,3 +617,118 @@ class BotSortEngine(ByteTrackEngine):
         torch.cuda.current_stream(self.device).synchronize()
         ho, hn2 = self._h_out.numpy(), self._h_nout.numpy()
         return [ho[s, : hn2[s]].copy() for s in range(self.S)]
+
+
+SS_ERR_BITS = {1: "track capacity exceeded", 2: "detection capacity exceeded", 8: "feature pool capacity exceeded",
+               16: "non-finite costs reached the assignment solver"}
+
+
+class StrongSortEngine:
+    """S independent StrongSORT trackers (the fork's "enhanced" StrongSORT, boxmot/trackers/strongsort/
+    strongsort.py:115-205 over sort/tracker.py, sort/track.py, sort/linear_assignment.py) per step, all on
+    the device: detection quality sort, camera_update + Kalman predict, the sample-bank cosine metric on the
+    tensor cores, Mahalanobis-gated three-stage cascade with scipy-exact assignments, adaptive feature EMA,
+    id recovery from the lost buffer, partial_fit.
+
+    The reference runs only in one configuration: occlusion handling and crowd detection off,
+    and tracks born Confirmed as in its own CI mode (``born_confirmed=True``).  ReID and CMC are side inputs:
+    ``embs`` [S, det_cap, emb_dim] float32 (required), ``warps`` [S, 2, 3] float64 or None (identity)."""
+
+    def __init__(self, n_streams, track_cap=512, det_cap=128, pool_cap=None, device="cuda:0", min_conf=0.1,
+                 max_cos_dist=0.15, max_iou_dist=0.7, max_age=50, n_init=2, nn_budget=150, mc_lambda=0.995,
+                 ema_alpha=0.9, conf_thresh_high=0.7, conf_thresh_low=0.3, id_preservation_weight=0.1,
+                 born_confirmed=True, emb_dim=512, **_ignored):
+        if not torch.cuda.is_available():
+            raise RuntimeError("StrongSortEngine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.S, self.Tcap, self.Dcap, self.E = int(n_streams), int(track_cap), int(det_cap), int(emb_dim)
+        self.Pcap = int(pool_cap) if pool_cap else 4 * self.Tcap
+        cfg = _lib.StrongsortConfig(min_conf, max_cos_dist, max_iou_dist, mc_lambda, ema_alpha, conf_thresh_high,
+                                    conf_thresh_low, id_preservation_weight, int(max_age), int(n_init),
+                                    int(nn_budget), int(bool(born_confirmed)), self.E)
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_create(ctypes.byref(cfg), self.S, self.Tcap, self.Dcap, self.Pcap,
+                                                       ctypes.byref(self._h)), "bm_strongsort_create")
+        self.out_rows = self.Dcap
+        self.out = torch.zeros((self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+        self.nout = torch.zeros((self.S,), dtype=torch.int32, device=self.device)
+        self.launches = 0
+        self.with_reid = True
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            _lib.lib().bm_strongsort_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_reset(self._h, _stream_ptr(self.device)), "bm_strongsort_reset")
+
+    def step(self, dets, ndets, embs=None, warps=None, out=None, nout=None):
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (self.S, self.Dcap, 6)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.numel() == self.S
+        assert embs is not None and embs.dtype == torch.float32 and embs.is_cuda and embs.is_contiguous()
+        assert tuple(embs.shape) == (self.S, self.Dcap, self.E)
+        if warps is not None:
+            assert warps.dtype == torch.float64 and warps.is_cuda and tuple(warps.shape) == (self.S, 2, 3)
+            assert warps.is_contiguous()
+        out = self.out if out is None else out
+        nout = self.nout if nout is None else nout
+        assert out.dtype == torch.float64 and tuple(out.shape) == (self.S, self.out_rows, 8) and out.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_step(self._h, _ptr(dets), _ptr(ndets), _ptr(embs),
+                                                     _ptr(warps) if warps is not None else None,
+                                                     _ptr(out), _ptr(nout), _stream_ptr(self.device)),
+                       "bm_strongsort_step")
+        self.launches += 6
+        return out, nout
+
+    def counters(self, raise_on_error=True):
+        err = ctypes.c_int(0)
+        buf = (ctypes.c_ulonglong * 4)()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_counters(self._h, ctypes.byref(err), ctypes.byref(buf),
+                                                         _stream_ptr(self.device)), "bm_strongsort_counters")
+        if raise_on_error and err.value:
+            raise RuntimeError("StrongSORT engine error: " + "; ".join(m for b, m in SS_ERR_BITS.items() if err.value & b))
+        out = dict(zip(("track_updates", "lap_solves", "matches", "births"), [int(v) for v in buf]))
+        out["err"] = err.value
+        return out
+
+    def status(self, raise_on_error=True):
+        return self.counters(raise_on_error)
+
+    def time_kernels(self, enable=True):
+        _lib.check(_lib.lib().bm_strongsort_time_kernels(self._h, int(bool(enable))), "bm_strongsort_time_kernels")
+
+    def kernel_times(self):
+        """(prepare+predict, bank contraction, cost matrix, cascade, updates, finalize) ms of the last timed step."""
+        buf = (ctypes.c_float * 6)()
+        _lib.check(_lib.lib().bm_strongsort_kernel_times(self._h, ctypes.byref(buf)), "bm_strongsort_kernel_times")
+        return tuple(float(v) for v in buf)
+
+    def peek(self, stream_index):
+        """(means [n,8], covariances [n,8,8], table rows [n,42], ids [n], sample-list lengths [n], n_lost)."""
+        n, nl = ctypes.c_int(0), ctypes.c_int(0)
+        x = np.zeros((self.Tcap, 8))
+        P = np.zeros((self.Tcap, 64))
+        tab = np.zeros((self.Tcap, 42))
+        ids = np.zeros((self.Tcap,), dtype=np.int32)
+        nb = np.zeros((self.Tcap,), dtype=np.int32)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_peek(self._h, int(stream_index), ctypes.byref(n), ctypes.byref(nl),
+                                                     x.ctypes.data, P.ctypes.data, tab.ctypes.data, ids.ctypes.data,
+                                                     nb.ctypes.data, _stream_ptr(self.device)), "bm_strongsort_peek")
+        k = n.value
+        return x[:k], P[:k].reshape(k, 8, 8), tab[:k], ids[:k], nb[:k], nl.value
+
+    step_host = DeepOcSortEngine.step_host
+    emb_on = property(lambda self: True)

@@ -119,3 +119,21 @@ def mot17_embs(frames, emb_dim, seed):
         e /= np.linalg.norm(e, axis=1, keepdims=True) + 1e-12
         out.append(e.astype(np.float32))
     return out
+
+
+def strongsort_stream(stream_id, n_objects, n_frames, emb_dim, crowd=False):
+    """make_stream for the StrongSORT fixtures: detections rounded to float32 (the engine's input
+    precision) and returned as float64, embeddings float32 values as float64 (so every operation of
+    the reference is float64).  Stream 65 also gets frames without detections, a frame with nothing
+    above min_conf and a gap long enough to delete tracks and recover them from the lost buffer."""
+    fr, em = make_stream(stream_id, n_objects, n_frames, emb_dim=emb_dim, crowd=crowd)
+    fr = [d.astype(np.float32).astype(np.float64) for d in fr]
+    em = [x.astype(np.float64) for x in em]
+    if stream_id == 65:
+        fr[7] = np.empty((0, 6))
+        em[7] = np.empty((0, emb_dim))
+        fr[20][:, 4] = 0.05
+        for i in range(40, 49):
+            fr[i] = fr[i][:3]
+            em[i] = em[i][:3]
+    return fr, em

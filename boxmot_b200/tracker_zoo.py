@@ -1,7 +1,14 @@
 """create_tracker / get_tracker_config with the reference signature
 (boxmot/tracker_zoo.py:8-93): YAML ``default`` values become constructor arguments,
-unknown tracker names print a message and raise KeyError, ReID arguments are accepted
-and ignored (embeddings are a side input passed to ``update``)."""
+unknown tracker names print a message and raise KeyError.
+
+Side-input contract (all six trackers): ReID models and camera-motion estimators are OUTSIDE the
+association path.  ``reid_weights`` / ``device`` / ``half`` are accepted and ignored; the trackers that
+use appearance (botsort, deepocsort, boosttrack with_reid, strongsort) need the detections'
+embeddings as ``update(dets, img, embs)`` -- the reference runs its ReID backend when ``embs`` is
+None, these classes raise RuntimeError instead -- and take the 2x3 warp that the reference's
+``self.cmc.apply(img, dets)`` would return as the extra keyword ``update(..., warp=H)`` (identity /
+no correction when omitted)."""
 from pathlib import Path
 
 import yaml
@@ -20,6 +27,7 @@ _MAPPING = {
     "botsort": ("boxmot_b200.trackers.botsort", "BotSort"),
     "deepocsort": ("boxmot_b200.trackers.deepocsort", "DeepOcSort"),
     "boosttrack": ("boxmot_b200.trackers.boosttrack", "BoostTrack"),
+    "strongsort": ("boxmot_b200.trackers.strongsort", "StrongSort"),
 }
 _REID_TRACKERS = ("strongsort", "botsort", "deepocsort", "hybridsort", "boosttrack")
 
@@ -41,4 +49,9 @@ def create_tracker(tracker_type, tracker_config=None, reid_weights=None, device=
         tracker_args.update({"reid_weights": reid_weights, "device": device, "half": half})
         if tracker_type == "strongsort":
             tracker_args.pop("per_class")
+            # M2: strongsort.yaml carries six keys StrongSort.__init__ does not take
+            # (the reference raises TypeError here); only the constructor's own arguments are passed
+            import inspect
+            accepted = inspect.signature(tracker_class.__init__).parameters
+            tracker_args = {k: v for k, v in tracker_args.items() if k in accepted}
     return tracker_class(**tracker_args)

@@ -185,6 +185,54 @@ int bm_botsort_counters(void* handle, int* err_bits, unsigned long long* out4, v
 int bm_botsort_peek(void* handle, int stream_index, int* n_active, int* n_lost, double* h_mean,
                     double* h_cov, int* h_ids, void* stream);
 
+/* ---- StrongSORT engine ---------------------------------------------------------------
+ * Replaces StrongSort.__init__/update/_compute_detection_quality/_format_outputs
+ * (boxmot/trackers/strongsort/strongsort.py:43-113, :115-205, :301-327, :329-359), Tracker
+ * (sort/tracker.py:102-111 predict, :118-181 update, :183-281 _enhanced_match, :283-298
+ * _apply_id_preservation_weighting, :300-351 _attempt_id_recovery, :395-410 _initiate_track),
+ * matching_cascade / min_cost_matching / gate_cost_matrix and helpers / NearestNeighborDistanceMetric
+ * (sort/linear_assignment.py:14-87, :90-171, :174-379, :499-618), iou_cost (sort/iou_matching.py:49-87),
+ * Track (sort/track.py:78-317) and scipy.optimize.linear_sum_assignment as called at
+ * linear_assignment.py:70 (emulated step for step, so ties resolve as scipy's do).
+ * The fork runs only in one configuration: R4 (unmatched_tracks_3 initialised), the
+ * occlusion handler and crowd detection off (R5), and -- for anything to be confirmed -- tracks born
+ * Confirmed as under GITHUB_ACTIONS=true (M1: born_confirmed = 1).  ReID and CMC are side inputs:
+ * d_embs [S][det_cap][emb_dim] float32 (required), d_warps [S][6] float64 row-major 2x3 warps or
+ * NULL for the identity (camera_update runs either way, strongsort.py:168-172; any affine warp).
+ * Output rows are the first 8 of the fork's 10 columns, in tracker.tracks order.
+ * pool_cap: feature vectors stored per stream (each distinct vector once: the <= 10 features of
+ * every track and whatever its sample list of nn_budget entries still references). */
+typedef struct bm_strongsort_config {
+    double min_conf, max_cos_dist, max_iou_dist, mc_lambda, ema_alpha, conf_thresh_high, conf_thresh_low,
+        id_preservation_weight;
+    int max_age, n_init, nn_budget, born_confirmed, emb_dim;
+} bm_strongsort_config;
+int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int track_cap, int det_cap, int pool_cap,
+                         void** handle);
+int bm_strongsort_destroy(void* handle);
+/* scipy.optimize.linear_sum_assignment (StrongSORT's solver, sort/linear_assignment.py:70) for a batch
+ * of stored matrices, emulated step for step (Crouse's shortest augmenting path as in scipy's
+ * rectangular_lsap.cpp: rows in order, the `remaining` column list with its swap-removal, ties to an
+ * unassigned column, transposition when nc < nr), so that the result equals scipy's also when the optimum
+ * is not unique.  d_cost [B][nr_max][nc_max] float64, d_x [B][nr_max] = column of each row or -1.
+ * d_work: caller-owned scratch of at least B * 48 * max(nr_max, nc_max) bytes. */
+int bm_linear_sum_assignment_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                                   const int* d_nc, int* d_x, void* d_work, void* stream);
+int bm_strongsort_reset(void* handle, void* stream);
+/* One frame for all streams; buffers as bm_botsort_step, out_rows = det_cap.  Error bits (see
+ * bm_strongsort_counters): 1 track_cap, 2 det_cap, 8 pool_cap exceeded, 16 assignment guard. */
+int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
+                       const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* out4 = {tracks entering predict, assignments solved, matches (Track.update calls), births}. */
+int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
+/* Per-launch CUDA-event timing: prepare+predict, bank contraction, cost matrix, cascade, updates, finalize (ms). */
+int bm_strongsort_time_kernels(void* handle, int enable);
+int bm_strongsort_kernel_times(void* handle, float* ms6);
+/* Test hook: tracks of one stream in list order: means [n][8], covariances [n][64], table rows
+ * [n][42] (bm_strongsort_track's columns), ids, sample-list lengths; any pointer may be NULL. */
+int bm_strongsort_peek(void* handle, int stream_index, int* n_tracks, int* n_lost, double* h_mean, double* h_cov,
+                       double* h_tab, int* h_ids, int* h_nbank, void* stream);
+
 /* Per-kernel timing of the frame step (measurement aid for bench.py's roofline): when
  * enabled, bm_ocsort_step brackets its four launches (predict, assoc, update, finalize) with
  * CUDA events on the caller's stream; bm_ocsort_kernel_times waits for the last timed step and

@@ -16,7 +16,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle import ref_shim  # noqa: E402
-from boxmot_b200.synth import make_stream, mot17_embs  # noqa: E402
+from boxmot_b200.synth import make_stream, mot17_embs, strongsort_stream  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
 SEQS = ("MOT17-02-FRCNN", "MOT17-04-FRCNN")
@@ -568,17 +568,7 @@ STRONGSORT_CASES = [
 
 
 def strongsort_inputs(sid, k, f, e, crowd=False):
-    """Detections rounded to float32 (the engine's input precision) and handed to the reference as
-    float64; embeddings float32 values as float64, so every reference operation is float64."""
-    fr, em = make_stream(sid, k, f, emb_dim=e, crowd=crowd)
-    fr = [d.astype(np.float32).astype(np.float64) for d in fr]
-    em = [x.astype(np.float64) for x in em]
-    if sid == 65:      # frames without detections, and with none above min_conf
-        fr[7] = np.empty((0, 6)); em[7] = np.empty((0, e))
-        fr[20][:, 4] = 0.05
-        for i in (40, 41, 42, 43, 44, 45, 46, 47, 48):      # a gap long enough to delete and recover tracks
-            fr[i] = fr[i][:3]; em[i] = em[i][:3]
-    return fr, em
+    return strongsort_stream(sid, k, f, e, crowd)
 
 
 def main_strongsort():

@@ -151,6 +151,31 @@ def boosttrack_case(case):
     return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
 
 
+# the constructor defaults of the reference's StrongSort that strongsort.yaml also carries
+STRONGSORT_YAML = dict(min_conf=0.1, ema_alpha=0.9, max_cos_dist=0.15, max_iou_dist=0.7, max_age=50, n_init=2,
+                       mc_lambda=0.995, nn_budget=150, conf_thresh_high=0.7, conf_thresh_low=0.3,
+                       id_preservation_weight=0.1)
+# case -> (stream id, K, frames, emb_dim); see oracle/gen_golden.py STRONGSORT_CASES
+STRONGSORT_CASES = {
+    "synth_k20_e32": (60, 20, 60, 32),
+    "synth_k30_e64_b20": (61, 30, 70, 64),
+    "synth_k40_e32_cmc": (62, 40, 50, 32),
+    "synth_k25_e96_age8": (63, 25, 80, 96),
+    "synth_k60_e32_crowd": (64, 60, 40, 32),
+    "synth_k15_e32_ninit3": (65, 15, 90, 32),
+    "synth_k50_e128_hi": (66, 50, 40, 128),
+}
+
+
+def strongsort_case(case):
+    """(frames, embs, warps or None, tracker kwargs, golden rows) of a StrongSORT fixture."""
+    from boxmot_b200.synth import strongsort_stream
+    z = np.load(os.path.join(GOLD, "ref_strongsort_%s.npz" % case))
+    sid, k, f, e = STRONGSORT_CASES[case]
+    fr, em = strongsort_stream(sid, k, f, e, crowd="crowd" in case)
+    return fr, em, (z["warps"] if "warps" in z.files else None), eval(str(z["kw"])), z["rows"]
+
+
 def case_frames(case):
     from boxmot_b200.synth import make_stream
     if case.startswith("MOT17"):

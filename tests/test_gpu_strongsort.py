@@ -1,0 +1,140 @@
+"""End-to-end GPU parity of the StrongSORT engine (the fork's "enhanced" StrongSORT in its runnable
+configuration, SURVEY 8(c): R4, M1, M2, R5) against reference-generated golden fixtures and the
+numpy oracle, through create_tracker("strongsort") and the batched engine (C-ABI bm_strongsort_*).
+
+ids / conf / cls / det_ind and the row order are exact; boxes (Kalman posterior) within 1e-6.  The
+fixtures cover sample lists below and far above nn_budget (partial_fit's norm ranking, reproduced in
+OpenBLAS' ddot summation order), id recovery from the lost buffer, tentative survivors (n_init=3),
+frames without detections, camera warps with rotation, and the IoU stage's duplicated rows."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from conftest import STRONGSORT_CASES, STRONGSORT_YAML, assert_rows_match, split_by_frame, strongsort_case
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+IMG = np.zeros((1080, 1920, 3), np.uint8)
+
+
+@pytest.mark.parametrize("case", list(STRONGSORT_CASES))
+def test_strongsort_tracker_matches_reference_golden(case):
+    import boxmot_b200
+    frames, embs, warps, kw, want = strongsort_case(case)
+    trk = boxmot_b200.create_tracker("strongsort", boxmot_b200.get_tracker_config("strongsort"),
+                                     evolve_param_dict={**STRONGSORT_YAML, **kw})
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = trk.update(d, IMG, embs[f].copy(), warp=None if warps is None else warps[f])
+        assert_rows_match(got, want_f[f], f)
+
+
+def test_create_tracker_strongsort_from_yaml_defaults():
+    """The reference's own create_tracker('strongsort') raises TypeError (M2); here the YAML's extra keys
+    are dropped and the first frame returns one row per detection above min_conf (tracks are born
+    Confirmed, the reference's CI mode) with 8 columns (F7)."""
+    import boxmot_b200
+    trk = boxmot_b200.create_tracker("strongsort", boxmot_b200.get_tracker_config("strongsort"), None, "cpu", False)
+    rng = np.random.default_rng(0)
+    dets = np.array([[100, 100, 160, 260, 0.9, 0], [400, 300, 470, 480, 0.05, 0], [800, 200, 850, 330, 0.6, 1]], float)
+    embs = rng.normal(0, 1, (3, 64))
+    out = trk.update(dets, IMG, embs)
+    assert out.shape == (2, 8)
+    assert sorted(out[:, 7].tolist()) == [0.0, 2.0] and sorted(out[:, 4].tolist()) == [1.0, 2.0]
+    assert trk.update(np.empty((0, 6)), IMG, np.empty((0, 64))).size == 0
+    with pytest.raises(AssertionError):
+        trk.update(np.zeros((2, 5)), IMG, np.zeros((2, 64)))
+
+
+def test_strongsort_engine_batched_streams_match_oracle():
+    """12 streams stepped together with per-stream similarity warps; every stream equals a private oracle
+    in its output rows AND in its track table (Kalman state, scores, histories) and sample-list sizes."""
+    from boxmot_b200.engine import StrongSortEngine
+    from boxmot_b200.synth import make_batch
+    from oracle import strongsort as so
+    from oracle.strongsort_tracker import StrongSortOracle
+    S, K, F, D, E = 12, 20, 45, 64, 64
+    kw = dict(STRONGSORT_YAML, nn_budget=25, max_age=12)
+    dets, nd, embs = make_batch(S, K, F, D, emb_dim=E, first_stream=1700)
+    dets = dets.astype(np.float32)
+    eng = StrongSortEngine(S, track_cap=512, det_cap=D, pool_cap=2048, emb_dim=E, **kw)
+    oracles = [StrongSortOracle(**kw) for _ in range(S)]
+    rng = np.random.default_rng(8)
+    d_dets, d_nd, d_embs = torch.as_tensor(dets).cuda(), torch.as_tensor(nd).cuda(), torch.as_tensor(embs).cuda()
+    for f in range(F):
+        th, sc = rng.normal(0, 0.002, S), 1 + rng.normal(0, 0.004, S)
+        w = np.zeros((S, 2, 3))
+        w[:, 0, 0] = sc * np.cos(th); w[:, 0, 1] = -sc * np.sin(th)
+        w[:, 1, 0] = sc * np.sin(th); w[:, 1, 1] = sc * np.cos(th)
+        w[:, :, 2] = rng.normal(0, 2, (S, 2))
+        out, nout = eng.step(d_dets[f], d_nd[f], d_embs[f], torch.as_tensor(w).cuda())
+        out, nout = out.cpu().numpy(), nout.cpu().numpy()
+        for s in range(S):
+            n = nd[f, s]
+            want = oracles[s].update(dets[f, s, :n].astype(np.float64), embs[f, s, :n].astype(np.float64), w[s])
+            assert_rows_match(out[s, : nout[s]], want, f)
+        if f % 11 == 10 or f == F - 1:
+            for s in range(0, S, 5):
+                x, P, tab, ids, nb, nl = eng.peek(s)
+                o = oracles[s]
+                assert np.array_equal(ids, [t.id for t in o.tracks]) and nl == len(o.lost)
+                otab = np.array([t.a for t in o.tracks])
+                otab[:, so.TS_MISSED] = tab[:, so.TS_MISSED]      # never read (a duplicated IoU row counts twice)
+                np.testing.assert_allclose(tab, otab, rtol=1e-9, atol=1e-9)
+                np.testing.assert_allclose(x, np.array([t.mean for t in o.tracks]), rtol=1e-9, atol=1e-9)
+                np.testing.assert_allclose(P, np.array([t.cov for t in o.tracks]), rtol=1e-8, atol=1e-9)
+                assert np.array_equal(nb, [len(o.bank.get(t.id, [])) for t in o.tracks])
+    c = eng.counters()
+    assert c["track_updates"] == sum(o.n_updates for o in oracles)
+
+
+def _lsa(cost_list):
+    from boxmot_b200 import _lib
+    B = len(cost_list)
+    nr_max = max(c.shape[0] for c in cost_list)
+    nc_max = max(c.shape[1] for c in cost_list)
+    buf = np.zeros((B, nr_max, nc_max))
+    for b, c in enumerate(cost_list):
+        buf[b, : c.shape[0], : c.shape[1]] = c
+    d_c = torch.as_tensor(buf).cuda()
+    d_nr = torch.as_tensor(np.array([c.shape[0] for c in cost_list], np.int32)).cuda()
+    d_nc = torch.as_tensor(np.array([c.shape[1] for c in cost_list], np.int32)).cuda()
+    d_x = torch.full((B, nr_max), -7, dtype=torch.int32, device="cuda")
+    work = torch.zeros((B * 48 * max(nr_max, nc_max) + 64,), dtype=torch.uint8, device="cuda")
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.lib().bm_linear_sum_assignment_batch(p(d_c), B, nr_max, nc_max, p(d_nr), p(d_nc), p(d_x), p(work),
+                                                         None), "lsa")
+    torch.cuda.synchronize()
+    return d_x.cpu().numpy()
+
+
+def test_linear_sum_assignment_equals_scipy_including_ties():
+    """bm_linear_sum_assignment_batch against scipy.optimize.linear_sum_assignment itself: random costs
+    (unique optimum), small-integer costs, duplicated rows / columns and clamped matrices, where the optimum
+    is NOT unique and only an emulation of scipy's own tie-breaking returns the same pairs."""
+    from scipy.optimize import linear_sum_assignment
+    rng = np.random.default_rng(3)
+    probs = []
+    for t in range(240):
+        nr, nc = rng.integers(1, 40), rng.integers(1, 40)
+        kind = t % 4
+        if kind == 0:
+            c = rng.uniform(0, 1, (nr, nc))
+        elif kind == 1:
+            c = rng.integers(0, 4, (nr, nc)).astype(float)
+        elif kind == 2:                                  # duplicated rows and columns
+            c = rng.uniform(0, 1, (nr, nc))
+            for _ in range(3):
+                c[rng.integers(0, nr)] = c[rng.integers(0, nr)]
+                c[:, rng.integers(0, nc)] = c[:, rng.integers(0, nc)]
+        else:                                            # min_cost_matching's clamp: many equal entries
+            c = rng.uniform(0, 1, (nr, nc))
+            c[c > 0.35] = 0.35 + 1e-5
+        probs.append(c)
+    x = _lsa(probs)
+    for b, c in enumerate(probs):
+        rows, cols = linear_sum_assignment(c)
+        want = np.full(c.shape[0], -1)
+        want[rows] = cols
+        assert np.array_equal(x[b, : c.shape[0]], want), (b, c.shape)

@@ -305,3 +305,59 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(L, name), "missing export " + name
     assert set(_lib.EXPORTS) == declared
+
+
+@pytest.mark.parametrize("case", ["synth_k20_e32", "synth_k25_e96_age8", "synth_k15_e32_ninit3"])
+def test_strongsort_oracle_matches_reference_golden(case):
+    """The end-to-end StrongSORT oracle (oracle/strongsort_tracker.py) against rows produced by the
+    imported reference (R4 / M1 / M2 / R5): sample lists far above nn_budget, id recovery, tentative
+    survivors, empty frames.  The remaining four fixtures are checked through the GPU tests (the
+    oracle matches all seven: oracle/gen_golden.py --strongsort, tools/check_strongsort.py)."""
+    from conftest import strongsort_case
+    from oracle.strongsort_tracker import StrongSortOracle
+    frames, embs, warps, kw, want = strongsort_case(case)
+    o = StrongSortOracle(**kw)
+    want_f = split_by_frame(want, len(frames))
+    for f, d in enumerate(frames):
+        got = o.update(d, embs[f], None if warps is None else warps[f])
+        assert_rows_match(got, want_f[f], f, box_rtol=1e-9)
+
+
+def test_ddot_restatement_equals_numpy_on_the_authoring_cpu():
+    """oracle/numerics.c restates OpenBLAS' SkylakeX ddot order (what decides partial_fit's ranking of
+    unit vectors).  Where numpy dispatches that kernel -- the authoring container -- np.dot and the
+    restatement must agree to the last bit; elsewhere the reference itself would rank differently."""
+    threadpoolctl = pytest.importorskip("threadpoolctl")
+    arch = {i.get("architecture") for i in threadpoolctl.threadpool_info() if i.get("user_api") == "blas"}
+    if arch != {"SkylakeX"}:
+        pytest.skip("numpy's BLAS dispatches %s, not the SkylakeX kernels" % sorted(arch))
+    rng = np.random.default_rng(0)
+    for n in (32, 64, 96, 128, 512, 768, 100, 37, 1000):
+        for _ in range(300):
+            x = rng.normal(0, 1, n)
+            x /= np.linalg.norm(x)
+            y = rng.normal(0, 1, n)
+            assert lap.ddot(x, x) == float(np.dot(x, x)) and lap.ddot(x, y) == float(np.dot(x, y))
+            assert lap.norm(x) == float(np.linalg.norm(x))
+
+
+def test_iou_family_oracle_equals_reference_functions():
+    """oracle/assoc.py's six association functions against boxmot.utils.iou.AssociationFunction of the
+    imported reference (authoring container only: the GPU box has no /root/reference)."""
+    from oracle import ref_shim
+    if not ref_shim.available():
+        pytest.skip("reference tree not present")
+    ref_shim.load()
+    from boxmot.utils.iou import AssociationFunction
+    from oracle import assoc
+    rng = np.random.default_rng(5)
+    a = rng.uniform(0, 900, (40, 2))
+    a = np.c_[a, a + rng.uniform(5, 300, (40, 2))]
+    b = rng.uniform(0, 900, (55, 2))
+    b = np.c_[b, b + rng.uniform(5, 300, (55, 2))]
+    b[:10] = a[:10] + rng.normal(0, 3, (10, 4))
+    b[10] = a[10]
+    for name in ("iou", "giou", "diou", "ciou", "hmiou", "centroid"):
+        ref = AssociationFunction(w=1920, h=1080, asso_mode=name).asso_func(a, b)
+        mine = assoc.asso_func(name, 1920, 1080)(a, b)
+        assert np.array_equal(np.asarray(ref), np.asarray(mine)), name
