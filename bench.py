@@ -102,7 +102,7 @@ def parse():
         # runnable mode) make every low-confidence detection a track that lives max_age frames: ~12 live
         # tracks per object at steady state, hence the track / pool capacities and the long warm-up.
         for name, v in (("steps", 30), ("warmup", 90), ("objects", 100), ("det_cap", 128), ("track_cap", 2048),
-                        ("pool_cap", 4608), ("emb_dim", 768), ("streams", 256)):
+                        ("pool_cap", 8192), ("emb_dim", 768), ("streams", 256)):
             if getattr(a, name) is None or (name in ("warmup", "streams") and getattr(a, name) == ap.get_default(name)):
                 setattr(a, name, v)
     if a.emb_dim is None:

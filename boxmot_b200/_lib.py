@@ -138,6 +138,8 @@ _SIGS = {
     "bm_strongsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_strongsort_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
                                        c_void_p]),
+    "bm_strongsort_usage": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                    c_void_p]),
     "bm_strongsort_time_kernels": (c_int, [c_void_p, c_int]),
     "bm_strongsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
     "bm_strongsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_void_p, c_void_p,

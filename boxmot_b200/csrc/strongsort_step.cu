@@ -34,6 +34,7 @@
 #include "../../include/boxmot_b200.h"
 #include "strongsort_units.cuh"
 #include "cosine_tc.cuh"
+#include <algorithm>
 #include <cstdio>
 #include <new>
 #include <vector>
@@ -44,7 +45,7 @@ void set_last_error(const char* msg);
 
 enum { SH_NTRACKS = 0, SH_NLOST, SH_NTFREE, SH_NPFREE, SH_NPFREED, SH_NEXT_ID, SH_FRAME, SH_ERR, SH_NHIST, SH_NLIVE,
        SH_NDET, SH_NUPD, SH_STAGE3, SH_NUNM, SH_LSA, SH_MATCH, SH_BIRTHS, SH_HADDETS, SH_COUNT = 20 };
-enum { TI_ID = 0, TI_NRING, TI_NBANK, TI_NDIST, TI_LOSTFRAME, TI_SEQ, TI_NUPD, TI_MISS, TI_COUNT };
+enum { TI_ID = 0, TI_NRING, TI_NBANK, TI_NDIST, TI_LOSTFRAME, TI_SEQ, TI_NUPD, TI_MISS, TI_FEAS, TI_COUNT };
 // sorted detection table
 enum { DT_TLWH = 0, DT_XYAH = 4, DT_CONF = 8, DT_CLS, DT_DETIND, DT_QUALITY, DT_NORM, DT_COUNT };
 constexpr int SS_RING = 10;          // track.py:109 max_features
@@ -217,7 +218,7 @@ ss_prep_kernel(SsState st, SsParams pr, const float* __restrict__ dets, const in
         for (int c = 0; c < 8; c++) m[c] = x[c];
         for (int c = 0; c < 12; c++) C[c] = P[c];
         int* ti = v.tint(t);
-        ti[TI_NUPD] = 0; ti[TI_MISS] = 0;
+        ti[TI_NUPD] = 0; ti[TI_MISS] = 0; ti[TI_FEAS] = 0;
     }
     if (tid == 0) {
         hdr[SH_NDET] = n;
@@ -267,7 +268,15 @@ ss_cost_kernel(SsState st, SsParams pr) {
         }
         const double* d = v.dtab(k);
         double c = ss_gated_entry(app, v.mean(t), v.covb(t), a, d + DT_XYAH, pr.mc_lambda, pr.id_weight);
-        cost[(size_t)p * st.Dcap + k] = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
+        c = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
+        cost[(size_t)p * st.Dcap + k] = c;
+        // bit 0 / 1: some high- / medium-confidence detection is within the stage's threshold of this track
+        // (the cascade skips the assignment of a level none of whose tracks has the stage's bit)
+        const double cf = d[DT_CONF];
+        int bit = 0;
+        if (cf >= pr.conf_hi) { if (c <= pr.max_cos_dist * 0.8) bit = 1; }
+        else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bit = 2; }
+        if (bit && !(v.tint(t)[TI_FEAS] & bit)) atomicOr(&v.tint(t)[TI_FEAS], bit);
     }
 }
 
@@ -305,6 +314,7 @@ __device__ int lsa_scipy_warp(const CostFn& cost, int nr, int nc, const LsaWork&
             const double ui = w.u[i];
             double bv = CUDART_INF;
             int bit = 0x7fffffff, bun = 0;
+#pragma unroll 4
             for (int it = lane; it < num_remaining; it += 32) {
                 const int j = w.remaining[it];
                 const double r = ((min_val + cost(i, j)) - ui) - w.v[j];
@@ -364,19 +374,22 @@ __device__ int lsa_scipy_warp(const CostFn& cost, int nr, int nc, const LsaWork&
 // match_col[r] = accepted column position of row r or -1; the unmatched detections are returned in
 // `cols` in scipy's order (never-assigned columns ascending, then the rejected ones in row order).
 struct SsClampCost {
-    const double* c; int ld; const int* rows; const int* cols; double maxd; bool tr; const int* tsu_gate;
+    const double* c; int ld; const int* rows; const int* cols; double maxd; bool tr;
+    const int* far;      // optional, by list position: the whole row is above max_distance (never stored)
     __device__ __forceinline__ double at(int r, int cpos) const {
-        const double x = c[(size_t)rows[r] * ld + cols[cpos]];
+        const int p = rows[r];
+        if (far && far[p]) return maxd + 1e-5;
+        const double x = c[(size_t)p * ld + cols[cpos]];
         return x > maxd ? maxd + 1e-5 : x;
     }
     __device__ __forceinline__ double operator()(int i, int j) const { return tr ? at(j, i) : at(i, j); }
 };
 
 __device__ int ss_min_cost_matching(const double* c, int ld, const int* rows, int nr, int* cols, int& nc, double maxd,
-                                    const LsaWork& w, int* match_col, int* tmp) {
+                                    const LsaWork& w, int* match_col, int* tmp, const int* far = nullptr) {
     const int lane = lane_id();
     const bool tr = nc < nr;
-    SsClampCost cf{c, ld, rows, cols, maxd, tr, nullptr};
+    SsClampCost cf{c, ld, rows, cols, maxd, tr, far};
     if (lsa_scipy_warp(cf, tr ? nc : nr, tr ? nr : nc, w)) return 1;
     // row -> column of the original orientation, into match_col (w.srl is free after the solve)
     for (int r = lane; r < nr; r += 32) match_col[r] = tr ? w.row4col[r] : w.col4row[r];
@@ -420,8 +433,11 @@ lsa_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, in
 
 // K4: Tracker._enhanced_match (tracker.py:183-281), one warp per stream
 constexpr int SS_MATCH_WPB = 4;
+constexpr int SS_LSA_SMEM_M = 160;        // assignment problems with both sides <= this run out of shared memory
 __global__ void __launch_bounds__(SS_MATCH_WPB * 32)
 ss_match_kernel(SsState st, SsParams pr) {
+    __shared__ double s_lsa_d[SS_MATCH_WPB][3 * SS_LSA_SMEM_M];
+    __shared__ int s_lsa_i[SS_MATCH_WPB][6 * SS_LSA_SMEM_M];
     const int s = blockIdx.x * SS_MATCH_WPB + (threadIdx.x >> 5), lane = lane_id();
     if (s >= st.S) return;
     SsView v(st, s);
@@ -439,7 +455,8 @@ ss_match_kernel(SsState st, SsParams pr) {
     int* tmp = wi;                    wi += 2 * Tc + Dc;
     int* dmatched = wi;               wi += Dc;
     int* agecnt = wi;                 wi += pr.max_age + 2;
-    LsaWork w = lsa_carve(st.wkd + (size_t)s * 3 * M, wi, M);
+    const LsaWork w_glob = lsa_carve(st.wkd + (size_t)s * 3 * M, wi, M);
+    const LsaWork w_smem = lsa_carve(s_lsa_d[threadIdx.x >> 5], s_lsa_i[threadIdx.x >> 5], SS_LSA_SMEM_M);
     int* ulist = st.ulist + (size_t)s * Dc;
     int* unm = st.unm + (size_t)s * Dc;
     double* cost = v.cost();
@@ -507,6 +524,22 @@ ss_match_kernel(SsState st, SsParams pr) {
             const int end = agecnt[age];
             const int m = end - start;
             if (m <= 0) continue;
+            // A level none of whose tracks is within the threshold of any detection of the stage is a matrix of
+            // equal (clamped) entries: scipy assigns row i to column i (transposed: column j to row j), every
+            // pair is rejected, and the detections are handed on as [m, nc) followed by [0, m) when m < nc.
+            int feas = 0;
+            for (int i = lane; i < m; i += 32) feas |= v.tint(v.order()[byage[start + i]])[TI_FEAS] & (1 << stage);
+            feas = __any_sync(BM_FULL, feas != 0);
+            if (!feas) {
+                if (m < nc) {
+                    for (int j = lane; j < nc; j += 32) tmp[j] = cols[j < nc - m ? j + m : j - (nc - m)];
+                    __syncwarp();
+                    for (int j = lane; j < nc; j += 32) cols[j] = tmp[j];
+                    __syncwarp();
+                }
+                start = end;
+                continue;
+            }
             // _prioritize_tracks_by_quality (:276-285): stable sort by -(quality + stability)
             for (int i = lane; i < m; i += 32) {
                 const int p = byage[start + i];
@@ -521,7 +554,8 @@ ss_match_kernel(SsState st, SsParams pr) {
                 lvl[rank] = p;
             }
             __syncwarp();
-            bad |= ss_min_cost_matching(cost, Dc, lvl, m, cols, nc, thr, w, mcol, tmp);
+            bad |= ss_min_cost_matching(cost, Dc, lvl, m, cols, nc, thr, (m <= SS_LSA_SMEM_M && nc <= SS_LSA_SMEM_M) ? w_smem : w_glob,
+                                        mcol, tmp);
             nlsa++;
             if (lane == 0)
                 for (int r = 0; r < m; r++)
@@ -543,21 +577,25 @@ ss_match_kernel(SsState st, SsParams pr) {
     int nc3 = warp_compact(n, cols, 0, [&](int k) { return !dmatched[k] && !(v.dtab(k)[DT_CONF] < pr.conf_lo); },
                            [&](int k) { return k; });
     if (nr3 > 0 && nc3 > 0) {
-        // iou_cost (iou_matching.py:49-87) + _enhance_cost_matrix into the stage matrix (stages 1 / 2 are done)
-        for (int p = 0; p < nT; p++) {
+        // iou_cost (iou_matching.py:49-87) + _enhance_cost_matrix into the stage matrix (stages 1 / 2 are done).
+        // Rows of tracks with time_since_update > 1 are INFTY_COST times positive factors: above any
+        // threshold, so the clamped entry is the same constant whatever the factors are.
+        int nnear = warp_compact(nT, tmp, 0, [&](int p) {
+            const double* a = v.tab(v.order()[p]);
+            return a[ST_STATE] != (double)ST_TENTATIVE && !(a[SS_TSU] > 1.0);
+        }, [&](int p) { return p; });
+        for (int e = lane; e < nnear * nc3; e += 32) {
+            const int p = tmp[e / nc3], k = cols[e % nc3];
             const int t = v.order()[p];
             const double* a = v.tab(t);
-            if (a[ST_STATE] == (double)ST_TENTATIVE) continue;
-            const bool far = a[SS_TSU] > 1.0;
-            for (int j = lane; j < nc3; j += 32) {
-                const int k = cols[j];
-                const double* d = v.dtab(k);
-                const double c = far ? SS_INFTY_COST : ss_iou_entry(v.mean(t), d + DT_TLWH);
-                cost[(size_t)p * Dc + k] = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
-            }
+            const double* d = v.dtab(k);
+            cost[(size_t)p * Dc + k] = ss_enhance_entry(ss_iou_entry(v.mean(t), d + DT_TLWH), a, d[DT_QUALITY], d[DT_CONF],
+                                                        d[DT_CLS]);
         }
+        for (int p = lane; p < nT; p += 32) lvl[p] = v.tab(v.order()[p])[SS_TSU] > 1.0 ? 1 : 0;
         __syncwarp();
-        bad |= ss_min_cost_matching(cost, Dc, rows3, nr3, cols, nc3, pr.max_iou_dist, w, mcol, tmp);
+        bad |= ss_min_cost_matching(cost, Dc, rows3, nr3, cols, nc3, pr.max_iou_dist,
+                                    (nr3 <= SS_LSA_SMEM_M && nc3 <= SS_LSA_SMEM_M) ? w_smem : w_glob, mcol, tmp, lvl);
         nlsa++;
         if (lane == 0) {
             for (int r = 0; r < nr3; r++) {
@@ -768,7 +806,7 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     double* sims = st.sims + (size_t)s * 32 * st.Dcap;
     int* born = st.ulist + (size_t)s * st.Dcap;          // reused: track slots of this frame's births
     const int E = pr.E;
-    __shared__ int s_rec_l, s_rec_u, s_nb, s_anyconf;
+    __shared__ int s_rec_l, s_rec_u, s_nb;
     int nT = hdr[SH_NTRACKS];
     const int n = hdr[SH_NDET];
     // (a) mark_missed for the IoU stage's unmatched rows (tracker.py:141-142)
@@ -872,34 +910,67 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     __syncthreads();
     nT += nb;
     // (d) deleted tracks -> lost buffer (tracker.py:152-163), compaction of the list
-    if (tid == 0) {
-        const int now = n > 0 ? hdr[SH_FRAME] : hdr[SH_NHIST];      // frame_id is None for tracker.update([])
-        int nl = hdr[SH_NLOST], w = 0;
-        for (int p = 0; p < nT; p++) {
-            const int t = order[p];
-            if (v.tab(t)[ST_STATE] != (double)ST_DELETED) { order[w++] = t; continue; }
-            bool kept = false;
-            if (nl < SS_LOST) { v.tint(t)[TI_LOSTFRAME] = now; lost[nl++] = t; kept = true; }
-            int k2 = 0;
-            for (int i = 0; i < nl; i++) {
-                const int lt = lost[i];
-                if (now - v.tint(lt)[TI_LOSTFRAME] < pr.max_age) lost[k2++] = lt;
-                else ss_track_release(v, lt);
-            }
-            nl = k2;
-            if (!kept) ss_track_release(v, t);
+    __shared__ int s_ndel, s_w;
+    int* dellist = st.wki + (size_t)s * st.wki_stride;   // the match kernel's scratch (>= Tcap ints) is free now
+    if (wid == 0) {
+        int k = 0;
+        for (int base = 0; base < nT; base += 32) {
+            const int p = base + lane;
+            const bool del = p < nT && v.tab(order[p])[ST_STATE] == (double)ST_DELETED;
+            const unsigned b = __ballot_sync(BM_FULL, del);
+            if (del) dellist[k + __popc(b & ((1u << lane) - 1))] = order[p];
+            k += __popc(b);
         }
-        hdr[SH_NLOST] = nl;
-        hdr[SH_NTRACKS] = w;
-        hdr[SH_NHIST] = min(hdr[SH_NHIST] + 1, 100);
-        int any = 0;
-        for (int p = 0; p < w && !any; p++) any = v.tab(order[p])[ST_STATE] == (double)ST_CONFIRMED_STATE;
-        s_anyconf = any;
+        if (lane == 0) s_ndel = k;
     }
     __syncthreads();
-    nT = hdr[SH_NTRACKS];
+    const int ndel = s_ndel;
+    if (ndel > 0) {
+        if (tid == 0) {
+            const int now = n > 0 ? hdr[SH_FRAME] : hdr[SH_NHIST];      // frame_id is None for tracker.update([])
+            int nl = hdr[SH_NLOST];
+            for (int i0 = 0; i0 < ndel; i0++) {
+                const int t = dellist[i0];
+                bool kept = false;
+                if (nl < SS_LOST) { v.tint(t)[TI_LOSTFRAME] = now; lost[nl++] = t; kept = true; }
+                int k2 = 0;
+                for (int i = 0; i < nl; i++) {
+                    const int lt = lost[i];
+                    if (now - v.tint(lt)[TI_LOSTFRAME] < pr.max_age) lost[k2++] = lt;
+                    else ss_track_release(v, lt);
+                }
+                nl = k2;
+                if (!kept) ss_track_release(v, t);
+            }
+            hdr[SH_NLOST] = nl;
+        }
+        __syncthreads();
+        if (wid == 0) {                                  // stable compaction of the list, in place
+            int k = 0;
+            for (int base = 0; base < nT; base += 32) {
+                const int p = base + lane;
+                const int t = p < nT ? order[p] : 0;
+                const bool keep = p < nT && v.tab(t)[ST_STATE] != (double)ST_DELETED;
+                const unsigned b = __ballot_sync(BM_FULL, keep);
+                __syncwarp();
+                if (keep) order[k + __popc(b & ((1u << lane) - 1))] = t;
+                k += __popc(b);
+                __syncwarp();
+            }
+            if (lane == 0) s_w = k;
+        }
+        __syncthreads();
+        nT = s_w;
+    }
+    if (tid == 0) {
+        hdr[SH_NTRACKS] = nT;
+        hdr[SH_NHIST] = min(hdr[SH_NHIST] + 1, 100);
+    }
+    int anyc = 0;
+    for (int p = tid; p < nT; p += blockDim.x) anyc |= v.tab(order[p])[ST_STATE] == (double)ST_CONFIRMED_STATE;
+    anyc = __syncthreads_or(anyc);
     // (e) metric.partial_fit (tracker.py:165-178, linear_assignment.py:538-593)
-    if (s_anyconf) {
+    if (anyc) {
         const int keep = pr.budget / 4 < 5 ? pr.budget / 4 : 5;
         const int nl = hdr[SH_NLOST];
         for (int p = wid; p < nT + nl; p += nw) {
@@ -907,7 +978,14 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
             int* ti = v.tint(t);
             if (p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE) {
                 const int nr = ti[TI_NRING];
-                for (int i = 0; i < nr; i++) ss_bank_append(v, pr, t, v.ring(t)[i]);
+                // a full sample list takes a feature only if its quality beats the list's minimum: when none
+                // of the ring's features does (the steady state), all <= 10 appends are no-ops
+                bool any = ti[TI_NBANK] < pr.budget;
+                if (!any) {
+                    const bool better = lane < nr && v.pq()[v.ring(t)[lane]] > v.bminq(t);
+                    any = __any_sync(BM_FULL, better);
+                }
+                if (any) for (int i = 0; i < nr; i++) ss_bank_append(v, pr, t, v.ring(t)[i]);
             } else {
                 while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);        // inactive target (:575-593)
             }
@@ -946,12 +1024,11 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     }
     __syncthreads();
     // (g) merge the deferred frees, rebuild the list of features some sample list references
-    if (tid == 0) {
-        const int nf = hdr[SH_NPFREED];
-        int np = hdr[SH_NPFREE];
-        for (int i = 0; i < nf; i++) v.pfree()[np++] = v.pfreed()[i];
-        hdr[SH_NPFREE] = np; hdr[SH_NPFREED] = 0;
-        hdr[SH_NLIVE] = 0;
+    {
+        const int nf = hdr[SH_NPFREED], np = hdr[SH_NPFREE];
+        for (int i = tid; i < nf; i += blockDim.x) v.pfree()[np + i] = v.pfreed()[i];
+        __syncthreads();
+        if (tid == 0) { hdr[SH_NPFREE] = np + nf; hdr[SH_NPFREED] = 0; hdr[SH_NLIVE] = 0; }
     }
     __syncthreads();
     int* live = st.live + (size_t)s * st.Pcap;
@@ -1150,6 +1227,26 @@ int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4
     }
     if (err_bits) *err_bits = err;
     if (out4) for (int i = 0; i < 4; i++) out4[i] = o[i];
+    return 0;
+}
+
+int bm_strongsort_usage(void* handle, int* max_tracks, int* max_pool_used, int* max_live, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e) return ss_fail(-1, "bm_strongsort_usage: null handle");
+    const bm::SsState& st = e->st;
+    SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    std::vector<int> hdr((size_t)st.S * bm::SH_COUNT);
+    SS_CUDA(cudaMemcpy(hdr.data(), st.hdr, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    int mt = 0, mp = 0, ml = 0;
+    for (int s = 0; s < st.S; s++) {
+        const int* h = hdr.data() + (size_t)s * bm::SH_COUNT;
+        mt = std::max(mt, h[bm::SH_NTRACKS] + h[bm::SH_NLOST]);
+        mp = std::max(mp, st.Pcap - h[bm::SH_NPFREE]);
+        ml = std::max(ml, h[bm::SH_NLIVE]);
+    }
+    if (max_tracks) *max_tracks = mt;
+    if (max_pool_used) *max_pool_used = mp;
+    if (max_live) *max_live = ml;
     return 0;
 }
 

@@ -706,6 +706,14 @@ class StrongSortEngine:
     def status(self, raise_on_error=True):
         return self.counters(raise_on_error)
 
+    def usage(self):
+        """Over all streams: (track slots in use, pool slots in use, vectors referenced by a sample list)."""
+        a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_strongsort_usage(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c),
+                                                      _stream_ptr(self.device)), "bm_strongsort_usage")
+        return {"max_tracks": a.value, "max_pool_used": b.value, "max_live": c.value}
+
     def time_kernels(self, enable=True):
         _lib.check(_lib.lib().bm_strongsort_time_kernels(self._h, int(bool(enable))), "bm_strongsort_time_kernels")
 

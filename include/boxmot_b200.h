@@ -225,6 +225,9 @@ int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, co
                        const double* d_warps, double* d_out, int* d_nout, void* stream);
 /* out4 = {tracks entering predict, assignments solved, matches (Track.update calls), births}. */
 int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);
+/* Capacity planning: over all streams, the largest number of track slots in use (tracks + lost buffer),
+ * of pool slots in use and of vectors referenced by a sample list (rows of the contraction) right now. */
+int bm_strongsort_usage(void* handle, int* max_tracks, int* max_pool_used, int* max_live, void* stream);
 /* Per-launch CUDA-event timing: prepare+predict, bank contraction, cost matrix, cascade, updates, finalize (ms). */
 int bm_strongsort_time_kernels(void* handle, int enable);
 int bm_strongsort_kernel_times(void* handle, float* ms6);
