@@ -598,6 +598,47 @@ int bm_cosine_distance(const float* d_a, int na, const float* d_b, int nb, int e
 
 }  // extern "C"
 
+// ---- bm_pack_rows: the engines' padded output rows as one dense ragged buffer ---------------
+// Stream s owns rows [offsets[s], offsets[s + 1]) of `rows`; both destinations may be mapped pinned
+// HOST memory, in which case the kernel's stores are the device-to-host transfer (64 bytes per row
+// that exists instead of a copy of the whole padded array).
+namespace bm {
+__global__ void __launch_bounds__(256)
+pack_rows_kernel(const double* __restrict__ out, const int* __restrict__ nout, int S, int out_rows,
+                 double* __restrict__ rows, int* __restrict__ offsets) {
+    __shared__ int s_part[8];
+    __shared__ int s_off;
+    const int s = blockIdx.x, tid = threadIdx.x;
+    int acc = 0;
+    for (int i = tid; i < s; i += blockDim.x) acc += nout[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(BM_FULL, acc, o);
+    if ((tid & 31) == 0) s_part[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+        int t = 0;
+        for (int i = 0; i < 8; i++) t += s_part[i];
+        s_off = t;
+        offsets[s] = t;
+        if (s == S - 1) offsets[S] = t + nout[s];
+    }
+    __syncthreads();
+    const int off = s_off, n = nout[s];
+    const double2* src = reinterpret_cast<const double2*>(out + (size_t)s * out_rows * 8);
+    double2* dst = reinterpret_cast<double2*>(rows + (size_t)off * 8);
+    for (int i = tid; i < n * 4; i += blockDim.x) dst[i] = src[i];
+}
+}  // namespace bm
+
+extern "C" int bm_pack_rows(const double* d_out, const int* d_nout, int n_streams, int out_rows, double* rows_dst,
+                            int* offsets_dst, void* stream) {
+    if (n_streams <= 0) return 0;
+    if (!d_out || !d_nout || !rows_dst || !offsets_dst || out_rows <= 0) return -1;
+    bm::pack_rows_kernel<<<n_streams, 256, 0, static_cast<cudaStream_t>(stream)>>>(d_out, d_nout, n_streams, out_rows,
+                                                                                   rows_dst, offsets_dst);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("pack_rows_kernel", e);
+}
+
 // ---- bm_cosine_distance_noalloc: bm_cosine_distance for callers that cannot allocate -------
 // (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The row-index / norm
 // scratch that bm_cosine_distance takes from the caller lives in ONE file-scope device array;

@@ -395,57 +395,83 @@ class BoostTrackEngine:
 
 
 class HostPipeline:
-    """Double-buffered host <-> device pipeline around ``OcSortEngine.step``: while frame f
-    is being associated, the detections of frame f+1 upload on a copy stream and the rows
-    of frame f-1 download on another.  ``submit`` returns the finished result of the
-    PREVIOUS frame (numpy views of pinned buffers, valid until the next ``submit``)."""
+    """Host <-> device pipeline around an engine's ``step`` for callers with HOST buffers: while frame f is
+    being associated, the inputs of frame f+1 (detections, and embeddings / warps for the engines that take
+    them) upload on a copy stream from pinned staging buffers; the rows a frame emits are packed on the
+    device (``bm_pack_rows``) and written by that kernel STRAIGHT INTO mapped pinned host memory, so the
+    device-to-host traffic is 64 bytes per row that exists plus the offsets, not the padded output array.
+    ``submit`` returns the finished result of the PREVIOUS frame as ``(rows, offsets)``: stream s owns
+    ``rows[offsets[s]:offsets[s + 1]]`` (numpy views of pinned buffers, valid until the next ``submit``)."""
 
     def __init__(self, engine):
         e = self.eng = engine
         dev = e.device
-        self.s_in, self.s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self.E = int(getattr(e, "E", 0) or 0) if getattr(e, "emb_on", False) or getattr(e, "with_reid", False) else 0
+        self.s_in = torch.cuda.Stream(dev)
         mk = lambda shape, dt: [torch.zeros(shape, dtype=dt, device=dev) for _ in range(2)]
         pin = lambda shape, dt: [torch.zeros(shape, dtype=dt).pin_memory() for _ in range(2)]
         self.d_dets, self.d_nd = mk((e.S, e.Dcap, 6), torch.float32), mk((e.S,), torch.int32)
+        self.d_embs = mk((e.S, e.Dcap, self.E), torch.float32) if self.E else None
+        self.d_warps = mk((e.S, 2, 3), torch.float64)
         self.d_out, self.d_nout = mk((e.S, e.out_rows, 8), torch.float64), mk((e.S,), torch.int32)
-        self.h_out, self.h_nout = pin((e.S, e.out_rows, 8), torch.float64), pin((e.S,), torch.int32)
+        self.h_rows, self.h_off = pin((e.S * e.out_rows, 8), torch.float64), pin((e.S + 1,), torch.int32)
         self.ev_in = [torch.cuda.Event() for _ in range(2)]
         self.ev_comp = [torch.cuda.Event() for _ in range(2)]
-        self.ev_out = [torch.cuda.Event() for _ in range(2)]
         self.n = 0
-        self.h2d_bytes = e.S * e.Dcap * 6 * 4 + e.S * 4
-        self.d2h_bytes = e.S * e.out_rows * 8 * 8 + e.S * 4
+        self.h2d_bytes = e.S * e.Dcap * 6 * 4 + e.S * 4 + e.S * e.Dcap * self.E * 4
+        self.d2h_rows = 0            # rows written to host memory so far
+        self.d2h_frames = 0
 
-    def submit(self, h_dets, h_nd):
-        """h_dets [S,det_cap,6] float32 / h_nd [S] int32 pinned host tensors of the next frame."""
+    @property
+    def d2h_bytes(self):
+        """Average bytes the device wrote to host memory per frame: 64 per emitted row + the offsets."""
+        f = max(1, self.d2h_frames)
+        return self.d2h_rows * 64 // f + (self.eng.S + 1) * 4
+
+    def submit(self, h_dets, h_nd, h_embs=None, h_warps=None):
+        """Pinned host tensors of the next frame: h_dets [S,det_cap,6] float32, h_nd [S] int32,
+        h_embs [S,det_cap,E] float32 (engines with embeddings), h_warps [S,2,3] float64 or None."""
         b = self.n & 1
-        cur = torch.cuda.current_stream(self.eng.device)
+        e = self.eng
+        cur = torch.cuda.current_stream(e.device)
         if self.n >= 2:
-            self.s_in.wait_event(self.ev_comp[b])      # frame n-2 has consumed d_dets[b]
+            self.s_in.wait_event(self.ev_comp[b])      # frame n-2 has consumed the device inputs [b]
         with torch.cuda.stream(self.s_in):
             self.d_dets[b].copy_(h_dets, non_blocking=True)
             self.d_nd[b].copy_(h_nd, non_blocking=True)
+            if self.E:
+                self.d_embs[b].copy_(h_embs, non_blocking=True)
+            if h_warps is not None:
+                self.d_warps[b].copy_(h_warps, non_blocking=True)
             self.ev_in[b].record(self.s_in)
         cur.wait_event(self.ev_in[b])
-        if self.n >= 2:
-            cur.wait_event(self.ev_out[b])             # rows of frame n-2 have left d_out[b]
-        self.eng.step(self.d_dets[b], self.d_nd[b], out=self.d_out[b], nout=self.d_nout[b])
+        if self.E or h_warps is not None:
+            e.step(self.d_dets[b], self.d_nd[b], self.d_embs[b] if self.E else None,
+                   self.d_warps[b] if h_warps is not None else None, out=self.d_out[b], nout=self.d_nout[b])
+        else:
+            e.step(self.d_dets[b], self.d_nd[b], out=self.d_out[b], nout=self.d_nout[b])
+        with torch.cuda.device(e.device):
+            _lib.check(_lib.lib().bm_pack_rows(_ptr(self.d_out[b]), _ptr(self.d_nout[b]), e.S, e.out_rows,
+                                               ctypes.c_void_p(self.h_rows[b].data_ptr()),
+                                               ctypes.c_void_p(self.h_off[b].data_ptr()), _stream_ptr(e.device)),
+                       "bm_pack_rows")
         self.ev_comp[b].record(cur)
-        self.s_out.wait_event(self.ev_comp[b])
-        with torch.cuda.stream(self.s_out):
-            self.h_out[b].copy_(self.d_out[b], non_blocking=True)
-            self.h_nout[b].copy_(self.d_nout[b], non_blocking=True)
-            self.ev_out[b].record(self.s_out)
         self.n += 1
         return self._result(1 - b) if self.n >= 2 else None
 
     def _result(self, b):
-        self.ev_out[b].synchronize()
-        return self.h_out[b].numpy(), self.h_nout[b].numpy()
+        self.ev_comp[b].synchronize()
+        off = self.h_off[b].numpy()
+        return self.h_rows[b].numpy()[: off[-1]], off
 
     def drain(self):
         """Result of the last submitted frame."""
         return self._result((self.n - 1) & 1) if self.n else None
+
+    def account(self, result):
+        """Bookkeeping for ``d2h_bytes``: call with every result consumed."""
+        self.d2h_rows += int(result[1][-1])
+        self.d2h_frames += 1
 
 
 class ByteTrackEngine(_HostStepMixin):

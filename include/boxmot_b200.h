@@ -254,6 +254,15 @@ int bm_ocsort_stream_info(void* handle, int* h_n_tracks, int* h_next_id, void* s
 int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, double* h_P,
                    int* h_ids, void* stream);
 
+/* The step functions' padded rows d_out [S][out_rows][8] / d_nout [S] as ONE dense ragged buffer:
+ * stream s owns rows [offsets[s], offsets[s + 1]) of rows_dst (offsets_dst has S + 1 entries, the last
+ * one the total).  What BaseTracker.update returns per stream (basetracker.py:67-81: an (M, 8) array) for
+ * all streams at once.  rows_dst / offsets_dst may be device memory or MAPPED PINNED HOST memory: then
+ * the kernel's stores are the device-to-host transfer, 64 bytes per emitted row instead of the padded
+ * array.  rows_dst must hold sum(nout) rows (S * out_rows always suffices). */
+int bm_pack_rows(const double* d_out, const int* d_nout, int n_streams, int out_rows, double* rows_dst,
+                 int* offsets_dst, void* stream);
+
 /* ---- unit-testable kernels ---------------------------------------------------- */
 
 /* lap.lapjv(cost, extend_cost=True, cost_limit) for a batch of problems (call sites:

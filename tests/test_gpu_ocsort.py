@@ -85,8 +85,8 @@ def test_input_validation_matches_reference_asserts():
 
 
 def test_host_pipeline_matches_direct_stepping():
-    """The double-buffered H2D / step / D2H pipeline returns, one frame late, exactly the
-    rows a synchronous step returns."""
+    """The double-buffered H2D / step / pack-into-pinned-host-memory pipeline returns, one frame late,
+    exactly the rows a synchronous step returns, as one dense ragged buffer (rows, offsets)."""
     from boxmot_b200.engine import HostPipeline, OcSortEngine
     from boxmot_b200.synth import make_batch
     S, K, F, D = 16, 30, 20, 64
@@ -110,10 +110,48 @@ def test_host_pipeline_matches_direct_stepping():
     eng.status()
     assert len(got) == F
     for f in range(F):
-        assert np.array_equal(got[f][1], want[f][1])
+        rows, off = got[f]
+        assert np.array_equal(np.diff(off), want[f][1]) and off[0] == 0 and len(rows) == off[-1]
         for s in range(S):
             n = want[f][1][s]
-            assert np.array_equal(got[f][0][s, :n], want[f][0][s, :n])
+            assert np.array_equal(rows[off[s]:off[s + 1]], want[f][0][s, :n])
+
+
+def test_host_pipeline_with_embeddings_and_warps_matches_direct_stepping():
+    """The same pipeline for an engine with embedding and warp side inputs (DeepOCSORT)."""
+    from conftest import DEEPOCSORT_YAML
+    from boxmot_b200.engine import DeepOcSortEngine, HostPipeline
+    from boxmot_b200.synth import make_batch
+    S, K, F, D, E = 8, 25, 15, 64, 32
+    dets, nd, embs = make_batch(S, K, F, D, emb_dim=E, first_stream=340)
+    h_dets = torch.as_tensor(dets.astype(np.float32)).pin_memory()
+    h_nd = torch.as_tensor(nd).pin_memory()
+    h_embs = torch.as_tensor(embs).pin_memory()
+    rng = np.random.default_rng(2)
+    w = np.zeros((F, S, 2, 3))
+    w[:, :, 0, 0] = 1 + rng.normal(0, 0.01, (F, S)); w[:, :, 1, 1] = 1 + rng.normal(0, 0.01, (F, S))
+    w[:, :, :, 2] = rng.normal(0, 2, (F, S, 2))
+    h_w = torch.as_tensor(w).pin_memory()
+    ref = DeepOcSortEngine(S, track_cap=128, det_cap=D, emb_dim=E, **DEEPOCSORT_YAML)
+    want = []
+    for f in range(F):
+        out, nout = ref.step(h_dets[f].cuda(), h_nd[f].cuda(), h_embs[f].cuda(), h_w[f].cuda())
+        want.append((out.cpu().numpy().copy(), nout.cpu().numpy().copy()))
+    eng = DeepOcSortEngine(S, track_cap=128, det_cap=D, emb_dim=E, **DEEPOCSORT_YAML)
+    pipe = HostPipeline(eng)
+    got = []
+    for f in range(F):
+        r = pipe.submit(h_dets[f], h_nd[f], h_embs[f], h_w[f])
+        if r is not None:
+            got.append((r[0].copy(), r[1].copy()))
+    r = pipe.drain()
+    got.append((r[0].copy(), r[1].copy()))
+    eng.status()
+    for f in range(F):
+        rows, off = got[f]
+        assert np.array_equal(np.diff(off), want[f][1])
+        for s in range(S):
+            assert np.array_equal(rows[off[s]:off[s + 1]], want[f][0][s, : want[f][1][s]])
 
 
 def test_ocsort_per_class_matches_reference_golden():
