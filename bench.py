@@ -91,6 +91,8 @@ def parse():
                     help="independent stream groups stepped on CUDA streams of their own (engine.set_stream_groups)")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between steps")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sub-configs", dest="sub_configs", action="store_false",
+                    help="headline run only: skip the short sub-runs of BASELINE configs[0], [2], [3], [4]")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-streams", type=int, default=4, help="cpu_baseline sample size")
     ap.add_argument("--ref-streams-per-core", type=int, default=1)
@@ -627,10 +629,88 @@ def run_gpu_arm(args):
                            "ms_per_step": ms_e_all / K}
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    # free the device before a sub-run of another configuration
+    eng.close()
+    del eng, d_dets, d_nd, d_embs, h_dets, h_nd, flush_buf, pipe
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return line
+
+
+# --------------------------------------------------------------------------- the other BASELINE configs
+# Short driver-timed sub-runs of the configurations the headline line does not cover (single GPU only),
+# attached to the headline line as "configs": device value, ms/step, roofline fraction, e2e.
+SUB_CONFIGS = [
+    ("C3_botsort_1024x200_e512", ["--tracker", "botsort", "--steps", "10", "--warmup", "10"]),
+    ("C4_strongsort_256x100_e768_b50", ["--tracker", "strongsort", "--steps", "8", "--warmup", "70"]),
+    ("C5_deepocsort_crowd_1024x480_e512", ["--tracker", "deepocsort", "--objects", "480", "--det-cap", "512",
+                                          "--track-cap", "768", "--emb-dim", "512", "--steps", "4", "--warmup", "6"]),
+    ("C5_boosttrack_crowd_1024x480_e512", ["--tracker", "boosttrack", "--objects", "480", "--det-cap", "512",
+                                           "--track-cap", "768", "--emb-dim", "512", "--steps", "4", "--warmup", "6"]),
+]
+
+
+def c1_single_stream_latency():
+    """BASELINE configs[0]: create_tracker("bytetrack").update() on MOT17-mini det.txt (MOT17-04-FRCNN, the
+    fixture tests/golden/mot17_mini_dets.npz), one stream, frame by frame from host arrays: the latency the
+    reference's own performance test bounds (tests/performance/test_tracking_p.py:53-58, < 5 ms), next to the
+    oracle port on one host core."""
+    import boxmot_b200
+    from oracle.bytetrack import ByteTrackOracle
+    z = np.load(os.path.join(ROOT, "tests", "golden", "mot17_mini_dets.npz"))["MOT17_04_FRCNN"]
+    n = int(z[:, 0].max())
+    frames = [np.c_[z[z[:, 0] == f][:, 1:], np.zeros((z[:, 0] == f).sum())].astype(np.float64) for f in range(1, n + 1)]
+    img = np.zeros((1080, 1920, 3), np.uint8)
+    trk = boxmot_b200.create_tracker("bytetrack", boxmot_b200.get_tracker_config("bytetrack"))
+    for d in frames[:50]:
+        trk.update(d, img)
+    t0 = time.perf_counter()
+    for d in frames[50:]:
+        trk.update(d, img)
+    gpu_ms = (time.perf_counter() - t0) * 1e3 / max(1, len(frames) - 50)
+    o = ByteTrackOracle(**BYTETRACK_YAML)
+    for d in frames[:50]:
+        o.update(d)
+    t0 = time.perf_counter()
+    for d in frames[50:]:
+        o.update(d)
+    cpu_ms = (time.perf_counter() - t0) * 1e3 / max(1, len(frames) - 50)
+    return {"workload": "ByteTrack on MOT17-mini MOT17-04-FRCNN det.txt, single stream, update() from host arrays",
+            "frames": len(frames) - 50, "update_ms": gpu_ms, "oracle_port_update_ms": cpu_ms,
+            "note": "one stream cannot fill a GPU: this is launch + copy latency, not throughput"}
+
+
+def run_sub_configs(headline_argv):
+    import copy
+    out = {}
+    for name, extra in SUB_CONFIGS:
+        argv = [a for a in headline_argv if a in ("--no-flush",)] + extra + ["--no-cpu-baseline"]
+        old = sys.argv
+        try:
+            sys.argv = [old[0]] + argv
+            a = parse()
+            t0 = time.perf_counter()
+            line = run_gpu_arm(a)
+            out[name] = {"value": line["value"], "unit": line["unit"], "ms_per_step": line["ms_per_step"],
+                         "steps": line["steps"], "warmup": line["warmup"],
+                         "roofline_frac": line["roofline"]["frac"], "achieved_gbs": line["roofline"]["achieved"],
+                         "dominant_kernel": line["roofline"].get("dominant_kernel"),
+                         "per_kernel_ms": {k["kernel"]: k["avg_ms"] for k in line["roofline"].get("per_kernel", [])},
+                         "e2e": line.get("e2e"), "config": line["config"], "counters": line["counters"],
+                         "wall_s": time.perf_counter() - t0}
+        except Exception as ex:        # a sub-run must never take the headline line down
+            out[name] = {"error": repr(ex)[:300]}
+        finally:
+            sys.argv = old
+    try:
+        out["C1_bytetrack_mot17mini_single_stream"] = c1_single_stream_latency()
+    except Exception as ex:
+        out["C1_bytetrack_mot17mini_single_stream"] = {"error": repr(ex)[:300]}
+    return out
 
 
 def main():
@@ -643,8 +723,13 @@ def main():
     os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
-    else:
-        run_gpu_arm(args)
+        return
+    line = run_gpu_arm(args)
+    if line is not None and int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.tracker == "ocsort" \
+            and args.sub_configs and (args.streams, args.objects) == (1024, 100):
+        line["configs"] = run_sub_configs(sys.argv[1:])
+    if line is not None:
+        emit(line)
 
 
 if __name__ == "__main__":
