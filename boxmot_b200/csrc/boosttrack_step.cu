@@ -775,18 +775,16 @@ struct BoostDot {
 
 size_t boosttrack_smem(const BoostState& st) { return bt_smem_bytes(st.Tcap, st.Dcap, bt_threads(st.Tcap, st.Dcap)); }
 
-cudaError_t boosttrack_configure(const BoostState& st) {
-    const int sm = (int)boosttrack_smem(st);
-    cudaError_t e = cudaFuncSetAttribute(bt_boost_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+cudaError_t boosttrack_configure(const BoostState&) {
+    cudaError_t e = smem_optin(bt_boost_kernel<256>);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bt_assoc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    e = smem_optin(bt_assoc_kernel<256>);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bt_boost_kernel<BT_NT_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    e = smem_optin(bt_boost_kernel<BT_NT_MAX>);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bt_assoc_kernel<BT_NT_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    e = smem_optin(bt_assoc_kernel<BT_NT_MAX>);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(cosine_tc_kernel<BoostDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)cosine_tc_smem_bytes());
+    return smem_optin(cosine_tc_kernel<BoostDot>);
 }
 
 static cudaError_t bt_dbg(const char* name, cudaStream_t stream) {

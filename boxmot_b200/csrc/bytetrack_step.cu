@@ -705,10 +705,14 @@ struct BotCosine {
 
 size_t bytetrack_step_smem(const ByteState& st) { return byte_smem_bytes(st.Tcap, st.Dcap); }
 
-cudaError_t bytetrack_step_configure(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(byte_step_kernel<MODE_BYTE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+cudaError_t bytetrack_step_configure(size_t) {
+    cudaError_t e = smem_optin(byte_step_kernel<MODE_BYTE>);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(byte_step_kernel<MODE_BOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = smem_optin(byte_step_kernel<MODE_BOT>);
+    if (e != cudaSuccess) return e;
+    e = smem_optin(bot_embed_kernel);
+    if (e != cudaSuccess) return e;
+    return smem_optin(cosine_tc_kernel<BotCosine>);
 }
 
 cudaError_t bytetrack_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
@@ -720,22 +724,9 @@ cudaError_t bytetrack_step_launch(const ByteState& st, const ByteParams& pr, con
 cudaError_t botsort_step_launch(const ByteState& st, const ByteParams& pr, const float* dets, const int* ndets,
                                 const float* embs, const double* warps, double* out, int* nout, cudaStream_t stream) {
     if (pr.with_reid) {
-        static bool once = false;
         const size_t sm = bot_embed_smem(st);
-        if (!once) {
-            cudaError_t e = cudaFuncSetAttribute(bot_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-            if (e != cudaSuccess) return e;
-            once = true;
-        }
         bot_embed_kernel<<<st.S, BE_NT, sm, stream>>>(st, pr, dets, ndets, embs);
         if (st.tensor_cores) {
-            static bool once_tc = false;
-            if (!once_tc) {
-                cudaError_t e = cudaFuncSetAttribute(cosine_tc_kernel<BotCosine>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                     (int)cosine_tc_smem_bytes());
-                if (e != cudaSuccess) return e;
-                once_tc = true;
-            }
             cosine_tc_kernel<BotCosine><<<dim3((st.Tcap + TC_M - 1) / TC_M, st.S), TC_NT, cosine_tc_smem_bytes(), stream>>>(
                 BotCosine{st, pr.emb_dim});
         }

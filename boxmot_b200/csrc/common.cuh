@@ -48,4 +48,22 @@ enum : int {
     BM_ERR_SCRATCH = 4,          // cost matrix larger than the scratch region
 };
 
+// Opt a kernel into the device's whole dynamic shared-memory range.  The attribute belongs to the kernel
+// AND the current device and is process-global, so an engine must never set it to its OWN need: a second
+// engine with smaller capacities would lower it under the first one's launches (and an engine on another
+// device would never get the opt-in at all).  Called at every engine create with that engine's device
+// current; the value only depends on the device, so repeating it is harmless.
+template <typename Kernel>
+inline cudaError_t smem_optin(Kernel kernel) {
+    int dev = 0, optin = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e != cudaSuccess) return e;
+    cudaFuncAttributes fa;
+    e = cudaFuncGetAttributes(&fa, kernel);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
+}
+
 }  // namespace bm

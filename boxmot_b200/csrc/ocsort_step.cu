@@ -1582,17 +1582,16 @@ size_t ocsort_step_smem(const OcsState& st, const OcsParams& pr) {
     return ocs_smem_bytes(st.Tcap, st.Dcap, pr.use_byte);
 }
 
-cudaError_t ocsort_step_configure(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(ocs_assoc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+cudaError_t ocsort_step_configure(size_t) {
+    cudaError_t e = smem_optin(ocs_assoc_kernel<false>);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(ocs_assoc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = smem_optin(ocs_assoc_kernel<true>);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(ocs_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    e = smem_optin(ocs_screen_kernel);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(deep_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    e = smem_optin(deep_cost_kernel);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(cosine_tc_kernel<DeepDot>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)cosine_tc_smem_bytes());
+    return smem_optin(cosine_tc_kernel<DeepDot>);
 }
 
 // BM_DEBUG_SYNC=1 in the environment synchronises after every kernel and names the one that

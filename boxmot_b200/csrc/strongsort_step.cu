@@ -1131,12 +1131,8 @@ int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int tra
     A(&st.ulist, S * D); A(&st.unm, S * D); A(&st.wki, S * st.wki_stride);
     A(&st.wkd, S * 3 * M); A(&st.sims, S * 32 * D);
     for (int i = 0; i < 7 && r == cudaSuccess; i++) r = cudaEventCreate(&e->ev[i]);
-    if (r == cudaSuccess)
-        r = cudaFuncSetAttribute(bm::cosine_tc_kernel<bm::SsBankProblem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)bm::cosine_tc_smem_bytes());
-    if (r == cudaSuccess && ss_prep_smem(det_cap) > 48 * 1024)
-        r = cudaFuncSetAttribute(bm::ss_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)ss_prep_smem(det_cap));
+    if (r == cudaSuccess) r = bm::smem_optin(bm::cosine_tc_kernel<bm::SsBankProblem>);
+    if (r == cudaSuccess) r = bm::smem_optin(bm::ss_prep_kernel);
     if (r == cudaSuccess) {
         bm::ss_reset_kernel<<<n_streams, 256>>>(st);
         r = cudaGetLastError();

@@ -173,3 +173,42 @@ def test_ocsort_per_class_matches_reference_golden():
         assert_rows_match(got, want_f[f], f)
         seen += len(got)
     assert seen == len(want) and len(np.unique(want[:, 7])) == 3     # rows of three classes
+
+
+def test_two_live_engines_with_different_capacities_step_alternately():
+    """The dynamic shared-memory opt-in of a kernel is process-global: an engine created with small
+    capacities must not lower it under a live engine with large ones (and vice versa).  OC-SORT, ByteTrack
+    and BoostTrack engines of two sizes each are stepped alternately; results equal separately stepped engines."""
+    from conftest import BOOSTTRACK_YAML, BYTETRACK_YAML
+    from boxmot_b200.engine import BoostTrackEngine, ByteTrackEngine, OcSortEngine
+    from boxmot_b200.synth import make_batch
+    S, K, F = 4, 30, 12
+    for make in (lambda t, d: OcSortEngine(S, track_cap=t, det_cap=d, **OCSORT_YAML),
+                 lambda t, d: ByteTrackEngine(S, track_cap=t, det_cap=d, **BYTETRACK_YAML),
+                 lambda t, d: BoostTrackEngine(S, track_cap=t, det_cap=d, **dict(BOOSTTRACK_YAML, with_reid=False))):
+        outs = {}
+        for order in ("solo", "mixed"):
+            big = make(512, 512)
+            small = make(128, 64) if order == "mixed" else None
+            got = []
+            for caps, eng in ((512, big), (64, small)):
+                if eng is None:
+                    continue
+                dets, nd = make_batch(S, K, F, caps, first_stream=900)
+                eng._d = torch.as_tensor(dets.astype(np.float32)).cuda()
+                eng._n = torch.as_tensor(nd).cuda()
+            for f in range(F):
+                o, n = big.step(big._d[f], big._n[f])
+                got.append((o.cpu().numpy().copy(), n.cpu().numpy().copy()))
+                if small is not None:
+                    small.step(small._d[f], small._n[f])
+            big.status()
+            if small is not None:
+                small.status()
+                small.close()
+            big.close()
+            outs[order] = got
+        for (a, na), (b, nb) in zip(outs["solo"], outs["mixed"]):
+            assert np.array_equal(na, nb)
+            for s in range(S):
+                assert np.array_equal(a[s, : na[s]], b[s, : nb[s]])
