@@ -8,7 +8,9 @@
 namespace bm {
 
 // per-slot integers
-enum { BI_ID = 0, BI_STATE, BI_ACTIVATED, BI_FRAME, BI_START, BI_DETIND, BI_INREMOVED, BI_NHIST, BI_COUNT = 8 };
+enum { BI_ID = 0, BI_STATE, BI_ACTIVATED, BI_FRAME, BI_START, BI_DETIND, BI_INREMOVED, BI_NHIST,
+       BI_DENSE,          // BoT-SORT: the covariance lives in the dense side array dP (after a rotating warp)
+       BI_COUNT };
 // TrackState (bytetrack/basetrack.py:8-12)
 enum { BT_NEW = 0, BT_TRACKED = 1, BT_LOST = 2, BT_REMOVED = 3 };
 // per-stream header
@@ -42,6 +44,7 @@ struct ByteState {
     float* dfeat;      // [S][Dcap][E]  this frame's detection features as STrack.__init__ leaves them
     float* embd;       // [S][Tcap][Dcap] max(0, cosine distance) of (slot, high-score detection position)
     double* chist;     // [S][2*BOT_HIST][Tcap] class votes: class ids, then accumulated confidences
+    double* dP;        // [S][64][Tcap] dense 8x8 covariance of the tracks with BI_DENSE (multi_gmc with rotation)
     int* fupd;         // [S][2][Dcap] (slot, detection row | birth flag << 30) feature updates of the frame
     int* elive;        // [S][Tcap] live slots (active then lost list) = rows of the embedding contraction
     int* ehind;        // [S][Dcap] rows of the high-score detections = its columns
@@ -58,6 +61,7 @@ inline ByteState byte_substate(const ByteState& st, int s0, int n, int E) {
     g.xP += o * XA_N * T;  g.confcls += o * 2 * T;  g.tbox += o * 4 * T;  g.ints += o * BI_COUNT * T;
     g.act += o * T;  g.lost += o * T;  g.hdr += o * BH_COUNT;  g.n_updates += o;  g.scratch += o * T * D;
     if (st.chist) g.chist += o * 2 * BOT_HIST * T;
+    if (st.dP) g.dP += o * 64 * T;
     if (st.fupd) g.fupd += o * 2 * D;
     if (st.feat) g.feat += o * T * E;
     if (st.dfeat) g.dfeat += o * D * E;

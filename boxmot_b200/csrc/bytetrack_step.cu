@@ -110,10 +110,11 @@ __device__ __forceinline__ double bot_cost(double iou_d, double conf, bool fuse,
 
 // STrack.multi_gmc (botsort_track.py:92-104) for a warp without rotation / shear: kron(I4, R)
 // with diagonal R scales the (x, w, vx, vw) and (y, h, vy, vh) components separately and keeps
-// the covariance in block form.  Anything else needs a dense covariance: flagged, not applied.
+// the covariance in block form.  Warps with rotation / shear go through the dense slow path
+// (botd_predict_gmc): the callers switch the track over first.
 __device__ __forceinline__ void bot_gmc(double* x, double* P, const double* w6, int* hdr) {
     const double r00 = w6[0], r01 = w6[1], tx = w6[2], r10 = w6[3], r11 = w6[4], ty = w6[5];
-    if (r01 != 0.0 || r10 != 0.0) { atomicOr(&hdr[BH_ERR], BM_ERR_WARP); return; }
+    if (r01 != 0.0 || r10 != 0.0) { atomicOr(&hdr[BH_ERR], BM_ERR_WARP); return; }   // not reached
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         const double r = (i & 1) ? r11 : r00;
@@ -148,12 +149,13 @@ __device__ __forceinline__ double bot_vote(double* hist, int Tcap, int slot, int
 }
 
 struct ByteView {
-    double *xP, *confcls, *tbox;
+    double *xP, *confcls, *tbox, *dP;
     int *ints, *act, *lost, *hdr;
     int Tcap;
     __device__ ByteView(const ByteState& st, int s) : Tcap(st.Tcap) {
         const size_t T = st.Tcap;
         xP = st.xP + (size_t)s * XA_N * T;
+        dP = st.dP ? st.dP + (size_t)s * 64 * T : nullptr;
         confcls = st.confcls + (size_t)s * 2 * T;
         tbox = st.tbox + (size_t)s * 4 * T;
         ints = st.ints + (size_t)s * BI_COUNT * T;
@@ -181,6 +183,116 @@ struct ByteView {
         for (int c = 0; c < 12; c++) xP[(8 + c) * Tcap + slot] = P[c];
     }
 };
+
+// ---- dense 8x8 slow path of the XYWH filter (BoT-SORT tracks that saw a camera-motion warp with
+// rotation / shear: kron(I4, R) couples x<->y, w<->h and their velocities, botsort_track.py:91-104).
+// The reference's own dense expressions (base_kalman_filter.py:111-155, xywh_kf.py:29-66); kept out of line
+// so that the register budget of the step kernel's common path is untouched.
+__device__ __forceinline__ void botd_load(const ByteView& v, int slot, double* x, double* P) {
+    for (int c = 0; c < 8; c++) x[c] = v.xP[c * v.Tcap + slot];
+    for (int c = 0; c < 64; c++) P[c] = v.dP[(size_t)c * v.Tcap + slot];
+}
+__device__ __forceinline__ void botd_store(const ByteView& v, int slot, const double* x, const double* P) {
+    for (int c = 0; c < 8; c++) v.xP[c * v.Tcap + slot] = x[c];
+    for (int c = 0; c < 64; c++) v.dP[(size_t)c * v.Tcap + slot] = P[c];
+}
+__device__ __noinline__ void bot_make_dense(const ByteView& v, int slot) {
+    double pb[12], P[64];
+    for (int c = 0; c < 12; c++) pb[c] = v.xP[(8 + c) * v.Tcap + slot];
+    xyah_expand(pb, P);
+    for (int c = 0; c < 64; c++) v.dP[(size_t)c * v.Tcap + slot] = P[c];
+    v.I(BI_DENSE, slot) = 1;
+}
+// multi_predict (optional) followed by multi_gmc with any 2x3 warp (optional), on a dense track
+__device__ __noinline__ void botd_predict_gmc(const ByteView& v, int slot, bool zero_size_vel, bool predict, const double* w6) {
+    double x[8], P[64];
+    botd_load(v, slot, x, P);
+    if (predict) {
+        if (zero_size_vel) { x[6] = 0.0; x[7] = 0.0; }
+        double sp[4], sv[4];
+        cv8_std<CV8_XYWH>(x, 1.0, 1.0, 1e-2, 1e-5, sp, sv);
+        for (int i = 0; i < 4; i++) x[i] = x[i] + x[4 + i];
+        for (int i = 0; i < 4; i++)                      // F P
+            for (int j = 0; j < 8; j++) P[i * 8 + j] = P[i * 8 + j] + P[(i + 4) * 8 + j];
+        for (int i = 0; i < 8; i++)                      // (F P) F^T
+            for (int j = 0; j < 4; j++) P[i * 8 + j] = P[i * 8 + j] + P[i * 8 + j + 4];
+        for (int i = 0; i < 4; i++) { P[i * 9] = P[i * 9] + sp[i] * sp[i]; P[(4 + i) * 9] = P[(4 + i) * 9] + sv[i] * sv[i]; }
+    }
+    if (w6) {
+        const double r[4] = {w6[0], w6[1], w6[3], w6[4]};
+        for (int b = 0; b < 4; b++) {                    // mean = R8x8 . mean (+ t on the first pair)
+            const double a = x[2 * b], c = x[2 * b + 1];
+            x[2 * b] = r[0] * a + r[1] * c;
+            x[2 * b + 1] = r[2] * a + r[3] * c;
+        }
+        x[0] += w6[2]; x[1] += w6[5];
+        double T[64];
+        for (int bi = 0; bi < 4; bi++)                   // T = R8x8 . P
+            for (int j = 0; j < 8; j++) {
+                const double a = P[(2 * bi) * 8 + j], c = P[(2 * bi + 1) * 8 + j];
+                T[(2 * bi) * 8 + j] = r[0] * a + r[1] * c;
+                T[(2 * bi + 1) * 8 + j] = r[2] * a + r[3] * c;
+            }
+        for (int i = 0; i < 8; i++)                      // P = T . R8x8^T
+            for (int bj = 0; bj < 4; bj++) {
+                const double a = T[i * 8 + 2 * bj], c = T[i * 8 + 2 * bj + 1];
+                P[i * 8 + 2 * bj] = a * r[0] + c * r[1];
+                P[i * 8 + 2 * bj + 1] = a * r[2] + c * r[3];
+            }
+    }
+    botd_store(v, slot, x, P);
+}
+// KalmanFilterXYWH.update (base_kalman_filter.py:129-155) with a dense covariance
+__device__ __noinline__ void botd_update(const ByteView& v, int slot, const double* z) {
+    double x[8], P[64];
+    botd_load(v, slot, x, P);
+    double sp[4], sv[4];
+    cv8_std<CV8_XYWH>(x, 1.0, 1.0, 1e-1, 0.0, sp, sv);
+    double S[16], L[16];
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) S[i * 4 + j] = P[i * 8 + j] + (i == j ? sp[i] * sp[i] : 0.0);
+    for (int i = 0; i < 16; i++) L[i] = 0.0;
+    for (int j = 0; j < 4; j++) {                        // cho_factor (lower)
+        double d = S[j * 4 + j];
+        for (int k = 0; k < j; k++) d -= L[j * 4 + k] * L[j * 4 + k];
+        d = sqrt(d);
+        L[j * 4 + j] = d;
+        for (int i = j + 1; i < 4; i++) {
+            double a = S[i * 4 + j];
+            for (int k = 0; k < j; k++) a -= L[i * 4 + k] * L[j * 4 + k];
+            L[i * 4 + j] = a / d;
+        }
+    }
+    double K[32];                                        // K = P H^T S^-1: cho_solve per row of P[:, :4]
+    for (int r = 0; r < 8; r++) {
+        double b[4];
+        for (int i = 0; i < 4; i++) b[i] = P[r * 8 + i];
+        for (int i = 0; i < 4; i++) { for (int k = 0; k < i; k++) b[i] -= L[i * 4 + k] * b[k]; b[i] = b[i] / L[i * 4 + i]; }
+        for (int i = 3; i >= 0; i--) { for (int k = i + 1; k < 4; k++) b[i] -= L[k * 4 + i] * b[k]; b[i] = b[i] / L[i * 4 + i]; }
+        for (int i = 0; i < 4; i++) K[r * 4 + i] = b[i];
+    }
+    double inn[4];
+    for (int i = 0; i < 4; i++) inn[i] = z[i] - x[i];
+    for (int r = 0; r < 8; r++) {
+        double acc = 0.0;
+        for (int i = 0; i < 4; i++) acc += inn[i] * K[r * 4 + i];
+        x[r] = x[r] + acc;
+    }
+    double SK[32];                                       // S K^T (4 x 8); multi_dot evaluates K (S K^T)
+    for (int i = 0; i < 4; i++)
+        for (int r = 0; r < 8; r++) {
+            double acc = 0.0;
+            for (int k = 0; k < 4; k++) acc += S[i * 4 + k] * K[r * 4 + k];
+            SK[i * 8 + r] = acc;
+        }
+    for (int a = 0; a < 8; a++)
+        for (int b = 0; b < 8; b++) {
+            double acc = 0.0;
+            for (int k = 0; k < 4; k++) acc += K[a * 4 + k] * SK[k * 8 + b];
+            P[a * 8 + b] = P[a * 8 + b] - acc;
+        }
+    botd_store(v, slot, x, P);
+}
 
 // iou_pair with the division skipped when the boxes do not overlap: max(0, w) * max(0, h) is
 // then exactly 0 and 0 / (area_a + area_b) is exactly +0.0 whenever that sum is positive
@@ -294,8 +406,19 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         sm.lbox[d] = make_float4(r[0], r[1], r[2], r[3]);
     }
     // ---- STrack.multi_predict on the pool (:41-54); unconfirmed tracks are NOT predicted
+    const double* w6 = (MODE == MODE_BOT && warps) ? warps + (size_t)s * 6 : nullptr;
+    const bool rot = w6 && (w6[1] != 0.0 || w6[3] != 0.0);
     for (int p = tid; p < nP; p += BT_NT) {
         const int slot = sm.pool[p];
+        if (MODE == MODE_BOT && v.dP && (rot || v.I(BI_DENSE, slot))) {      // dense covariance (slow path)
+            if (!v.I(BI_DENSE, slot)) bot_make_dense(v, slot);
+            botd_predict_gmc(v, slot, v.I(BI_STATE, slot) != BT_TRACKED, true, w6);
+            double xm[8];
+            for (int c = 0; c < 8; c++) xm[c] = v.xP[c * Tcap + slot];
+            v.set_box(slot, mean_to_xyxy<KIND>(xm));
+            sm.tflag[slot] |= TF_USED;
+            continue;
+        }
         double x[8], P[12];
         v.load(slot, x, P);
         if (v.I(BI_STATE, slot) != BT_TRACKED) {
@@ -312,6 +435,14 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         const int slot = sm.unc[p];
         sm.tflag[slot] |= TF_USED;
         if (MODE == MODE_BOT && warps) {
+            if (v.dP && (rot || v.I(BI_DENSE, slot))) {
+                if (!v.I(BI_DENSE, slot)) bot_make_dense(v, slot);
+                botd_predict_gmc(v, slot, false, false, w6);
+                double xm[8];
+                for (int c = 0; c < 8; c++) xm[c] = v.xP[c * Tcap + slot];
+                v.set_box(slot, mean_to_xyxy<KIND>(xm));
+                continue;
+            }
             double x[8], P[12];
             v.load(slot, x, P);
             bot_gmc(x, P, warps + (size_t)s * 6, v.hdr);
@@ -437,19 +568,25 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         }
         const float* r = dsrc + drow * 6;
         det_measurement<KIND>(make_float4(r[0], r[1], r[2], r[3]), z);
-        if (k < nUpd) {
+        const bool dense = MODE == MODE_BOT && v.dP && k < nUpd && v.I(BI_DENSE, slot);
+        if (dense) {
+            botd_update(v, slot, z);
+            for (int c = 0; c < 8; c++) x[c] = v.xP[c * Tcap + slot];
+            v.I(BI_ACTIVATED, slot) = 1;
+        } else if (k < nUpd) {
             v.load(slot, x, P);
             cv8_update<KIND>(x, P, z, 0.0);
             v.I(BI_ACTIVATED, slot) = 1;
         } else {
             cv8_initiate<KIND>(z, x, P);
+            if (MODE == MODE_BOT) v.I(BI_DENSE, slot) = 0;
             v.I(BI_ID, slot) = id0 + (k - nUpd) + 1;
             v.I(BI_ACTIVATED, slot) = frame == 1 ? 1 : 0;
             v.I(BI_START, slot) = frame;
             v.I(BI_INREMOVED, slot) = 0;
             v.I(BI_NHIST, slot) = 0;
         }
-        v.store(slot, x, P);
+        if (!dense) v.store(slot, x, P);
         v.set_box(slot, mean_to_xyxy<KIND>(x));
         v.I(BI_STATE, slot) = BT_TRACKED;
         v.I(BI_FRAME, slot) = frame;

@@ -128,7 +128,7 @@ static int ocs_create(const bm_ocsort_config* cfg, const bm_deepocsort_config* d
     // DeepOCSORT keeps the masked embedding matrix next to the cost matrix
     st.scratch_elems = (size_t)track_cap * det_cap * (deep ? 2 : 1);
     st.smem_cost_elems = smem_cost_bytes / 8;
-    st.emb = nullptr; st.embsim = nullptr; st.bornslot = nullptr; st.epos = nullptr; st.wbuf = nullptr;
+    st.emb = nullptr; st.embsim = nullptr; st.bornslot = nullptr; st.epos = nullptr; st.wbuf = nullptr; st.dP = nullptr;
     st.deep_d = nullptr; st.deep_i = nullptr;
     e->deep = deep != nullptr;
     bm::OcsParams& pr = e->pr;
@@ -156,6 +156,7 @@ static int ocs_create(const bm_ocsort_config* cfg, const bm_deepocsort_config* d
         }
         if (r == cudaSuccess) r = dev_alloc(e, &st.epos, S * T);
         if (r == cudaSuccess) r = dev_alloc(e, &st.wbuf, S * ((size_t)det_cap + T));
+        if (r == cudaSuccess) r = dev_alloc(e, &st.dP, S * 98 * T);      // dense covariances (tracks that saw a rotating warp)
         if (r == cudaSuccess) r = dev_alloc(e, &st.deep_d, S * ((size_t)det_cap + 1));
         if (r == cudaSuccess) r = dev_alloc(e, &st.deep_i, S * (3 * (size_t)det_cap + T));
     }
@@ -401,9 +402,10 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const bm::OcsState& st = e->st;
     const size_t T = st.Tcap;
-    std::vector<double> xp(bm::XB_N * T);
+    std::vector<double> xp(bm::XB_N * T), dp(st.dP ? 49 * T : 0);
     std::vector<int> order(T), ints(bm::OI_COUNT * T), hdr(bm::OH_COUNT);
     BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * bm::XB_N * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    if (st.dP) BM_CUDA(cudaMemcpyAsync(dp.data(), st.dP + (size_t)si * 98 * T, dp.size() * 8, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(order.data(), st.order + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::OI_COUNT * T, ints.size() * 4,
                             cudaMemcpyDeviceToHost, s));
@@ -415,7 +417,9 @@ int bm_ocsort_peek(void* handle, int si, int* n_tracks, double* h_x, double* h_P
     for (int p = 0; p < n; p++) {
         const int slot = order[p];
         if (h_x) for (int c = 0; c < 7; c++) h_x[p * 7 + c] = xp[c * T + slot];
-        if (h_P) {
+        if (h_P && st.dP && (ints[bm::OI_FLAGS * T + slot] & bm::OF_DENSE)) {
+            for (int c = 0; c < 49; c++) h_P[(size_t)p * 49 + c] = dp[c * T + slot];
+        } else if (h_P) {
             double pb[13];
             for (int c = 0; c < 13; c++) pb[c] = xp[(7 + c) * T + slot];
             bm::xysrb_expand(pb, h_P + (size_t)p * 49);
@@ -626,7 +630,7 @@ int bm_boosttrack_peek(void* handle, int si, int* n_tracks, double* h_x, double*
 static int byte_family_create(ByteEngine* e, int n_streams, int track_cap, int det_cap, void** handle) {
     bm::ByteState& st = e->st;
     st.S = n_streams; st.Tcap = track_cap; st.Dcap = det_cap;
-    st.feat = st.dfeat = st.embd = nullptr; st.chist = nullptr; st.fupd = nullptr;
+    st.feat = st.dfeat = st.embd = nullptr; st.chist = nullptr; st.fupd = nullptr; st.dP = nullptr;
     st.elive = st.ehind = nullptr; st.etn = st.edn = nullptr;
     {   // BM_COSINE=ffma selects the fp32 FFMA contraction (debug / comparison); default: tensor cores
         const char* v = getenv("BM_COSINE");
@@ -636,6 +640,7 @@ static int byte_family_create(ByteEngine* e, int n_streams, int track_cap, int d
     cudaError_t r = cudaSuccess;
     if (e->bot) {
         if (r == cudaSuccess) r = dev_alloc(e, &st.chist, S * 2 * bm::BOT_HIST * T);
+        if (r == cudaSuccess) r = dev_alloc(e, &st.dP, S * 64 * T);       // dense covariances (tracks that saw a rotating warp)
         if (r == cudaSuccess) r = dev_alloc(e, &st.fupd, S * 2 * (size_t)det_cap);
         if (e->pr.with_reid) {
             if (r == cudaSuccess) r = dev_alloc(e, &st.feat, S * T * E);
@@ -811,9 +816,10 @@ int bm_bytetrack_peek(void* handle, int si, int* n_active, int* n_lost, double* 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const bm::ByteState& st = e->st;
     const size_t T = st.Tcap;
-    std::vector<double> xp(bm::XA_N * T);
+    std::vector<double> xp(bm::XA_N * T), dp(st.dP ? 64 * T : 0);
     std::vector<int> act(T), lost(T), ints(bm::BI_COUNT * T), hdr(bm::BH_COUNT);
     BM_CUDA(cudaMemcpyAsync(xp.data(), st.xP + (size_t)si * bm::XA_N * T, xp.size() * 8, cudaMemcpyDeviceToHost, s));
+    if (st.dP) BM_CUDA(cudaMemcpyAsync(dp.data(), st.dP + (size_t)si * 64 * T, dp.size() * 8, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(act.data(), st.act + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(lost.data(), st.lost + (size_t)si * T, T * 4, cudaMemcpyDeviceToHost, s));
     BM_CUDA(cudaMemcpyAsync(ints.data(), st.ints + (size_t)si * bm::BI_COUNT * T, ints.size() * 4,
@@ -826,7 +832,9 @@ int bm_bytetrack_peek(void* handle, int si, int* n_active, int* n_lost, double* 
     for (int p = 0; p < na + nl; p++) {
         const int slot = p < na ? act[p] : lost[p - na];
         if (h_mean) for (int c = 0; c < 8; c++) h_mean[p * 8 + c] = xp[c * T + slot];
-        if (h_cov) {
+        if (h_cov && st.dP && ints[bm::BI_DENSE * T + slot]) {
+            for (int c = 0; c < 64; c++) h_cov[(size_t)p * 64 + c] = dp[c * T + slot];
+        } else if (h_cov) {
             double pb[12];
             for (int c = 0; c < 12; c++) pb[c] = xp[(8 + c) * T + slot];
             bm::xyah_expand(pb, h_cov + (size_t)p * 64);

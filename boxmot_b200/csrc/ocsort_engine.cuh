@@ -16,7 +16,8 @@
 namespace bm {
 
 enum { OI_ID = 0, OI_TSU, OI_HITS, OI_STREAK, OI_AGE, OI_DETIND, OI_FLAGS, OI_NNONE, OI_COUNT };
-enum { OF_OBSERVED = 1, OF_SAVED = 2 };
+enum { OF_OBSERVED = 1, OF_SAVED = 2,
+       OF_DENSE = 4 };   // the covariance (live and frozen copy) lives in the dense side array dP (after a rotating warp)
 enum { OH_NLIST = 0, OH_NEXT_ID, OH_FRAME, OH_ERR, OH_LAPS, OH_MATCH, OH_BIRTHS, OH_NUPD, OH_NBORN, OH_ND, OH_NS, OH_DEEP, OH_COUNT = 12 };
 // association operands written by the predict kernel, indexed by LIST POSITION
 enum { AB_X1 = 0, AB_Y1, AB_X2, AB_Y2, AB_VY, AB_VX, AB_KCX, AB_KCY, AB_KVALID, AB_COUNT };
@@ -68,6 +69,7 @@ struct OcsState {
     float* embsim;                 // [S][Dcap][Tcap] dets_embs @ trk_embs.T by (detection row, list position)
     int* bornslot;                 // [S][Dcap]      slot given to the k-th birth of the frame
     int* epos;                     // [S][Tcap]      list position at contraction time (after a NaN-track removal)
+    double* dP;                    // [S][2][49][Tcap] dense 7x7 covariance, live then frozen copy, of the tracks with OF_DENSE
     double* wbuf;                  // [S][Dcap + Tcap] row / column weights of compute_aw_max_metric
     double* deep_d;                // [S][Dcap + 1]  row minima of the materialised first round + the matrix maximum
     int* deep_i;                   // [S][3 Dcap + Tcap] row arg-minima, IoU-hit counts per row, hit column, hits per column
@@ -92,6 +94,7 @@ inline OcsState ocs_substate(const OcsState& st, int s0, int n, int E) {
     if (st.embsim) g.embsim += o * D * T;
     if (st.bornslot) g.bornslot += o * D;
     if (st.epos) g.epos += o * T;
+    if (st.dP) g.dP += o * 98 * T;
     if (st.wbuf) g.wbuf += o * (D + T);
     if (st.deep_d) g.deep_d += o * (D + 1);
     if (st.deep_i) g.deep_i += o * (3 * D + T);
@@ -99,7 +102,7 @@ inline OcsState ocs_substate(const OcsState& st, int s0, int n, int E) {
 }
 
 struct OcsView {   // per-stream base pointers
-    double *xP, *sxP, *lastz, *lastobs, *vel, *confcls, *ring;
+    double *xP, *sxP, *lastz, *lastobs, *vel, *confcls, *ring, *dP;
     int *ring_age, *ints, *order, *hdr;
     int Tcap, R;
     __device__ OcsView(const OcsState& st, int s) : Tcap(st.Tcap), R(st.R) {
@@ -115,6 +118,7 @@ struct OcsView {   // per-stream base pointers
         ints = st.ints + (size_t)s * OI_COUNT * T;
         order = st.order + (size_t)s * T;
         hdr = st.hdr + (size_t)s * OH_COUNT;
+        dP = st.dP ? st.dP + (size_t)s * 98 * T : nullptr;
     }
     __device__ __forceinline__ int& I(int f, int slot) const { return ints[f * Tcap + slot]; }
 };
@@ -130,6 +134,28 @@ __device__ __forceinline__ void store_xP(double* base, int Tcap, int slot, const
     for (int c = 0; c < 7; c++) base[c * Tcap + slot] = x[c];
 #pragma unroll
     for (int c = 0; c < 13; c++) base[(7 + c) * Tcap + slot] = Pb[c];
+}
+
+// Dense 7x7 covariance of a track with OF_DENSE (which = 0 live, 1 frozen copy); the mean stays in xP / sxP.
+__device__ __forceinline__ void load_dense(const OcsView& v, int which, int slot, double* P) {
+    const double* b = v.dP + (size_t)which * 49 * v.Tcap + slot;
+    for (int c = 0; c < 49; c++) P[c] = b[(size_t)c * v.Tcap];
+}
+__device__ __forceinline__ void store_dense(const OcsView& v, int which, int slot, const double* P) {
+    double* b = v.dP + (size_t)which * 49 * v.Tcap + slot;
+    for (int c = 0; c < 49; c++) b[(size_t)c * v.Tcap] = P[c];
+}
+// Switch a track to the dense covariance (both copies), expanding the block form.
+__device__ inline void ocs_make_dense(const OcsView& v, int slot) {
+    const int T = v.Tcap;
+    for (int which = 0; which < 2; which++) {
+        const double* src = which ? v.sxP : v.xP;
+        double pb[13], P[49];
+        for (int c = 0; c < 13; c++) pb[c] = src[(7 + c) * T + slot];
+        xysrb_expand(pb, P);
+        store_dense(v, which, slot, P);
+    }
+    v.I(OI_FLAGS, slot) |= OF_DENSE;
 }
 
 // Observation `delta_t` steps back (ocsort.py:17-28 / :146-152): the stored box of age
@@ -206,8 +232,28 @@ __device__ inline void ocs_track_update(const OcsView& v, int slot, const double
 
     double z[4];
     xyxy_to_z(det, z);
-    double x[7], P[13];
     int flags = v.I(OI_FLAGS, slot);
+    if (flags & OF_DENSE) {                      // after a rotating CMC warp: the reference's dense arithmetic
+        double xd[7], Pd[49];
+        if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
+            for (int c = 0; c < 7; c++) xd[c] = v.sxP[c * T + slot];
+            load_dense(v, 1, slot, Pd);
+            double z1[4];
+            for (int c = 0; c < 4; c++) z1[c] = v.lastz[c * T + slot];
+            xysr_oru_replay(xd, Pd, z1, z, v.I(OI_NNONE, slot) + 1, kc);
+        } else {
+            for (int c = 0; c < 7; c++) xd[c] = v.xP[c * T + slot];
+            load_dense(v, 0, slot, Pd);
+        }
+        xysr_update(xd, Pd, z);
+        for (int c = 0; c < 7; c++) v.xP[c * T + slot] = xd[c];
+        store_dense(v, 0, slot, Pd);
+        for (int c = 0; c < 4; c++) v.lastz[c * T + slot] = z[c];
+        v.I(OI_FLAGS, slot) = flags | OF_OBSERVED;
+        v.I(OI_NNONE, slot) = 0;
+        return;
+    }
+    double x[7], P[13];
     if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
         load_xP(v.sxP, T, slot, x, P);
         double z1[4];
@@ -231,6 +277,7 @@ __device__ inline void ocs_track_miss(const OcsView& v, int slot) {
     int flags = v.I(OI_FLAGS, slot);
     if (flags & OF_OBSERVED) {
         for (int c = 0; c < XB_N; c++) v.sxP[c * T + slot] = v.xP[c * T + slot];
+        if (flags & OF_DENSE) { double P[49]; load_dense(v, 0, slot, P); store_dense(v, 1, slot, P); }
         flags |= OF_SAVED;
     }
     v.I(OI_FLAGS, slot) = flags & ~OF_OBSERVED;

@@ -76,11 +76,22 @@ __device__ __forceinline__ void ocs_predict_track(const OcsState& st, const OcsP
     const int Tcap = st.Tcap;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
-    double x[7], P[13];
-    load_xP(v.xP, Tcap, slot, x, P);
-    if (x[6] + x[2] <= 0) x[6] *= 0.0;
-    xysrb_predict(x, P, kc);
-    store_xP(v.xP, Tcap, slot, x, P);
+    double x[7];
+    if (v.I(OI_FLAGS, slot) & OF_DENSE) {
+        double Pd[49];
+        for (int c = 0; c < 7; c++) x[c] = v.xP[c * Tcap + slot];
+        load_dense(v, 0, slot, Pd);
+        if (x[6] + x[2] <= 0) x[6] *= 0.0;
+        xysr_predict(x, Pd, kc);
+        for (int c = 0; c < 7; c++) v.xP[c * Tcap + slot] = x[c];
+        store_dense(v, 0, slot, Pd);
+    } else {
+        double P[13];
+        load_xP(v.xP, Tcap, slot, x, P);
+        if (x[6] + x[2] <= 0) x[6] *= 0.0;
+        xysrb_predict(x, P, kc);
+        store_xP(v.xP, Tcap, slot, x, P);
+    }
     const int age = v.I(OI_AGE, slot) + 1;
     v.I(OI_AGE, slot) = age;
     const int tsu = v.I(OI_TSU, slot);
@@ -101,23 +112,43 @@ __device__ __forceinline__ void ocs_predict_track(const OcsState& st, const OcsP
     ab[AB_KVALID * Tcap + p] = ok ? 1.0 : 0.0;
 }
 
-constexpr int BM_ERR_WARP_OCS = 32;   // camera-motion warp with rotation / shear (needs a dense covariance)
-
 // DeepOCSORT CMC correction of one track, BEFORE its predict (deepocsort.py:191-208 +
-// xysr_kf.py:111-135), for a warp without rotation / shear (diagonal 2x2 part): the block
-// form of the covariance is kept and every product is the reference's own.  Anything else
-// needs a dense covariance: flagged, not applied.
-//   * boxes go through x -> a x + tx, y -> d y + ty per corner;
+// xysr_kf.py:111-135), for any 2x3 warp [m | t]:
+//   * boxes: both corners through p -> m p + t;
 //   * the reference keeps ONE numpy array as `last_observation`, `observations[age_last]` and
 //     the detection row, so the newest observation is warped once through `last_observation`
 //     (when its sum is > 0) and once more through the `observations` window when
 //     age - age_last <= delta_t;
-//   * the Kalman mean / covariance and, while frozen, the frozen copy are warped; the ORU anchor
-//     (the LIVE history's last measurement, xysr_kf.py:184-192) is not.
+//   * the Kalman mean / covariance and, while frozen, the frozen copy are warped (x[:2], x[4:6],
+//     P[:2,:2], P[4:6,4:6] -- not the cross blocks); the ORU anchor (the LIVE history's last
+//     measurement, xysr_kf.py:184-192) is not.
+// A warp without rotation / shear (m diagonal) keeps the covariance's block structure and is applied to
+// the 13-entry block form with the reference's own products.  Any other warp couples x and y: the track
+// switches to the dense 7x7 covariance (OF_DENSE, side array dP) for the rest of its life and every
+// later predict / update / ORU replay of it runs the dense arithmetic (kf_xysr.cuh xysr_*).
+__device__ __forceinline__ void docs_warp_box(double* b0, double* b1, double* b2, double* b3, const double* w6) {
+    const double x1 = *b0, y1 = *b1, x2 = *b2, y2 = *b3;
+    *b0 = (w6[0] * x1 + w6[1] * y1) + w6[2];
+    *b1 = (w6[3] * x1 + w6[4] * y1) + w6[5];
+    *b2 = (w6[0] * x2 + w6[1] * y2) + w6[2];
+    *b3 = (w6[3] * x2 + w6[4] * y2) + w6[5];
+}
+// P[o:o+2, o:o+2] <- (m @ P2) @ m.T on a dense 7x7
+__device__ __forceinline__ void docs_warp_block(double* P, int o, const double* w6) {
+    const double p00 = P[o * 7 + o], p01 = P[o * 7 + o + 1], p10 = P[(o + 1) * 7 + o], p11 = P[(o + 1) * 7 + o + 1];
+    const double m00 = w6[0], m01 = w6[1], m10 = w6[3], m11 = w6[4];
+    const double t00 = m00 * p00 + m01 * p10, t01 = m00 * p01 + m01 * p11;
+    const double t10 = m10 * p00 + m11 * p10, t11 = m10 * p01 + m11 * p11;
+    P[o * 7 + o] = t00 * m00 + t01 * m01;
+    P[o * 7 + o + 1] = t00 * m10 + t01 * m11;
+    P[(o + 1) * 7 + o] = t10 * m00 + t11 * m01;
+    P[(o + 1) * 7 + o + 1] = t10 * m10 + t11 * m11;
+}
 __device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, const double* w6, int delta_t) {
     const int T = v.Tcap;
     const double a = w6[0], tx = w6[2], d = w6[4], ty = w6[5];
-    if (w6[1] != 0.0 || w6[3] != 0.0) { atomicOr(&v.hdr[OH_ERR], BM_ERR_WARP_OCS); return; }
+    const bool rot = w6[1] != 0.0 || w6[3] != 0.0;
+    if (rot && !v.dP) { atomicOr(&v.hdr[OH_ERR], 32); return; }
     const int age = v.I(OI_AGE, slot);
     if (v.I(OI_HITS, slot) > 0) {
         double lo[5];
@@ -127,8 +158,11 @@ __device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, co
         int times = lsum > 0 ? 1 : 0;
         if (v.I(OI_TSU, slot) <= delta_t) times++;          // age_last = age - time_since_update
         for (int k = 0; k < times; k++) {
-            lo[0] = a * lo[0] + tx; lo[2] = a * lo[2] + tx;
-            lo[1] = d * lo[1] + ty; lo[3] = d * lo[3] + ty;
+            if (rot) docs_warp_box(&lo[0], &lo[1], &lo[2], &lo[3], w6);
+            else {
+                lo[0] = a * lo[0] + tx; lo[2] = a * lo[2] + tx;
+                lo[1] = d * lo[1] + ty; lo[3] = d * lo[3] + ty;
+            }
         }
 #pragma unroll
         for (int c = 0; c < 4; c++) v.lastobs[c * T + slot] = lo[c];
@@ -141,15 +175,32 @@ __device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, co
                 for (int c = 0; c < 4; c++) v.ring[(r * 4 + c) * T + slot] = lo[c];
             } else {
                 double* q = v.ring + (size_t)(r * 4) * T + slot;
-                q[0] = a * q[0] + tx; q[2 * T] = a * q[2 * T] + tx;
-                q[T] = d * q[T] + ty; q[3 * T] = d * q[3 * T] + ty;
+                if (rot) docs_warp_box(&q[0], &q[T], &q[2 * T], &q[3 * T], w6);
+                else {
+                    q[0] = a * q[0] + tx; q[2 * T] = a * q[2 * T] + tx;
+                    q[T] = d * q[T] + ty; q[3 * T] = d * q[3 * T] + ty;
+                }
             }
         }
     }
-    const int flags = v.I(OI_FLAGS, slot);
+    int flags = v.I(OI_FLAGS, slot);
+    if (rot && !(flags & OF_DENSE)) { ocs_make_dense(v, slot); flags |= OF_DENSE; }
     for (int pass = 0; pass < 2; pass++) {
         if (pass == 1 && !(!(flags & OF_OBSERVED) && (flags & OF_SAVED))) break;
         double* b = pass ? v.sxP : v.xP;
+        if (flags & OF_DENSE) {
+            const double x0 = b[0 * T + slot], x1 = b[1 * T + slot], x4 = b[4 * T + slot], x5 = b[5 * T + slot];
+            b[0 * T + slot] = (w6[0] * x0 + w6[1] * x1) + tx;
+            b[1 * T + slot] = (w6[3] * x0 + w6[4] * x1) + ty;
+            b[4 * T + slot] = w6[0] * x4 + w6[1] * x5;
+            b[5 * T + slot] = w6[3] * x4 + w6[4] * x5;
+            double P[49];
+            load_dense(v, pass, slot, P);
+            docs_warp_block(P, 0, w6);
+            docs_warp_block(P, 4, w6);
+            store_dense(v, pass, slot, P);
+            continue;
+        }
         b[0 * T + slot] = a * b[0 * T + slot] + tx;
         b[1 * T + slot] = d * b[1 * T + slot] + ty;
         b[4 * T + slot] = a * b[4 * T + slot];

@@ -152,6 +152,33 @@ BOTSORT_CASES = [
 ]
 
 
+# BoT-SORT with similarity camera warps (rotation): multi_gmc's kron(I4, R) couples x<->y, w<->h
+BOTSORT_ROT_CASES = [
+    ("synth_k30_e32_rot", 14, 30, 60, 32, {}),
+    ("synth_k40_noreid_rot", 15, 40, 50, 0, {"with_reid": False, "track_buffer": 10}),
+]
+
+
+def main_botsort_rot():
+    for name, sid, k, f, e, kw in BOTSORT_ROT_CASES:
+        if e:
+            fr, em = make_stream(sid, k, f, emb_dim=e)
+        else:
+            fr, em = make_stream(sid, k, f), None
+        warps = boosttrack_warps(sid, f)
+        warps[::6] = deepocsort_warps(sid, f)[::6]          # some rotation-free warps on dense tracks
+        trk = ref_shim.make_tracker("botsort", **kw)
+        out = []
+        for i, d in enumerate(fr):
+            trk.cmc.warps = [warps[i].copy()]
+            r = np.asarray(trk.update(d.copy(), IMG, None if em is None else em[i].copy()), dtype=float)
+            r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+            out.append(np.c_[np.full(len(r), i), r])
+        out = np.vstack(out)
+        np.savez_compressed(os.path.join(GOLD, "ref_botsort_%s.npz" % name), rows=out, kw=np.array(repr(kw)), warps=warps)
+        print("botsort", name, out.shape, "ids", int(out[:, 5].max()))
+
+
 def main_botsort():
     dets = {s: load_det_txt(s) for s in SEQS}
     for name, sid, k, f, e, kw in BOTSORT_CASES:
@@ -174,6 +201,10 @@ DEEPOCSORT_CASES = [
     ("synth_k60_e32_cmc_dt1", 23, 60, 50, 32, True, {"delta_t": 1, "max_age": 5, "det_thresh": 0.3}),
     ("synth_k30_noemb_giou", 24, 30, 50, 32, False, {"embedding_off": True, "asso_func": "giou"}),
     ("synth_k100_e128", 25, 100, 40, 128, False, {}),
+    # similarity warps (rotation + scale + shift), what the tracker's own CMC (`sof`, deepocsort.py:311,
+    # estimateAffinePartial2D) produces: the covariance's x / y blocks get coupled
+    ("synth_k30_e32_rot", 27, 30, 60, 32, "sim", {}),
+    ("synth_k50_e16_rot_age5", 28, 50, 50, 16, "sim", {"max_age": 5, "det_thresh": 0.3, "delta_t": 2}),
 ]
 
 
@@ -187,10 +218,14 @@ def deepocsort_warps(seed, n_frames):
     return w
 
 
-def main_deepocsort():
+def main_deepocsort(only=None):
     for name, sid, k, f, e, use_warps, kw in DEEPOCSORT_CASES:
+        if only and only not in name:
+            continue
         fr, em = make_stream(sid, k, f, emb_dim=e)
-        warps = deepocsort_warps(sid, f) if use_warps else None
+        warps = (boosttrack_warps(sid, f) if use_warps == "sim" else deepocsort_warps(sid, f)) if use_warps else None
+        if use_warps == "sim":
+            warps[::7] = deepocsort_warps(sid, f)[::7]        # every 7th frame a rotation-free warp on dense tracks
         trk = ref_shim.make_tracker("deepocsort", **kw)
         out = []
         for i, d in enumerate(fr):
@@ -621,8 +656,12 @@ if __name__ == "__main__":
         main_deepocsort_per_class()
     elif "--kf" in sys.argv:
         main_kf()
+    elif "--botsort-rot" in sys.argv:
+        main_botsort_rot()
     elif "--botsort" in sys.argv:
         main_botsort()
+    elif "--deepocsort-rot" in sys.argv:
+        main_deepocsort(only="_rot")
     elif "--deepocsort" in sys.argv:
         main_deepocsort()
     elif "--boosttrack" in sys.argv:

@@ -199,10 +199,10 @@ def make_tracker(name, **overrides):
         import importlib
         sys.modules.setdefault("boxmot.appearance.reid.auto_backend", types.ModuleType("x")).ReidAutoBackend = _DummyReid
         cmc = sys.modules.setdefault("boxmot.motion.cmc", types.ModuleType("boxmot.motion.cmc"))
-        cmc.get_cmc_method = lambda _name: _IdentityCMC
+        cmc.get_cmc_method = lambda _name: _QueuedCMC
         mod = importlib.import_module("boxmot.trackers.botsort.botsort")
         mod.ReidAutoBackend = _DummyReid
-        mod.get_cmc_method = lambda _name: _IdentityCMC
+        mod.get_cmc_method = lambda _name: _QueuedCMC
         args.setdefault("per_class", False)
         return mod.BotSort(reid_weights=None, device="cpu", half=False, **args)
     if name == "deepocsort":

@@ -58,8 +58,15 @@ BOTSORT_CASES = {
     "synth_k100_e128": (11, 100, 50, 128),
     "synth_k30_e32_fuse": (12, 30, 80, 32),
     "synth_k50_noreid": (13, 50, 80, 0),
+    "synth_k30_e32_rot": (14, 30, 60, 32),           # similarity camera warps: multi_gmc with rotation (dense covariance)
+    "synth_k40_noreid_rot": (15, 40, 50, 0),
     "MOT17_02_FRCNN": None,
 }
+
+
+def botsort_warps(case):
+    z = np.load(os.path.join(GOLD, "ref_botsort_%s.npz" % case))
+    return z["warps"] if "warps" in z.files else None
 
 
 def botsort_case(case):
@@ -87,6 +94,8 @@ DEEPOCSORT_CASES = {
     "synth_k60_e32_cmc_dt1": (23, 60, 50, 32),
     "synth_k30_noemb_giou": (24, 30, 50, 32),
     "synth_k100_e128": (25, 100, 40, 128),
+    "synth_k30_e32_rot": (27, 30, 60, 32),           # similarity warps: rotation couples x and y (dense covariance)
+    "synth_k50_e16_rot_age5": (28, 50, 50, 16),
     "MOT17_02_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings (gen_golden --mot17-emb)
 }
 

@@ -19,9 +19,11 @@ def test_botsort_tracker_matches_reference_golden(case):
     frames, embs, kw, want = botsort_case(case)
     trk = boxmot_b200.create_tracker("botsort", boxmot_b200.get_tracker_config("botsort"),
                                      evolve_param_dict={**BOTSORT_YAML, **kw})
+    from conftest import botsort_warps
+    warps = botsort_warps(case)
     want_f = split_by_frame(want, len(frames))
     for f, d in enumerate(frames):
-        got = trk.update(d, IMG, None if embs is None else embs[f].copy())
+        got = trk.update(d, IMG, None if embs is None else embs[f].copy(), warp=None if warps is None else warps[f])
         assert_rows_match(got, want_f[f], f)
 
 
@@ -55,26 +57,35 @@ def test_botsort_engine_batched_streams_match_oracle():
         np.testing.assert_allclose(cov, np.array([t.cov for t in trk]), rtol=1e-9, atol=1e-12)
 
 
-def test_botsort_scale_and_shift_warp_matches_oracle_and_rotation_is_refused():
-    """multi_gmc (botsort_track.py:92-104): warps without rotation keep the block covariance
-    and are applied exactly; a rotation needs a dense covariance and raises."""
+def test_botsort_warps_match_oracle_block_and_dense_covariance():
+    """multi_gmc (botsort_track.py:92-104): warps without rotation keep the block covariance and are applied
+    exactly; a warp with rotation couples x<->y, w<->h (kron(I4, R)) and moves the track to the dense 8x8
+    covariance for the rest of its life (dense predict / Cholesky update of the XYWH filter)."""
     from boxmot_b200.engine import BotSortEngine
     from boxmot_b200.synth import make_stream
     from oracle.botsort import BotSortOracle
     kw = dict(BOTSORT_YAML, with_reid=False)
-    eng = BotSortEngine(1, track_cap=64, det_cap=64, **kw)
-    ora = BotSortOracle(**kw)
-    frames = make_stream(21, 20, 30)
+    eng = BotSortEngine(2, track_cap=64, det_cap=64, **kw)
+    ora = [BotSortOracle(**kw), BotSortOracle(**kw)]
+    frames = make_stream(21, 20, 45)
+    rng = np.random.default_rng(4)
     for f, d in enumerate(frames):
-        w = np.array([[1.0 + 0.002 * (f % 3), 0.0, 1.5 * (f % 4)], [0.0, 1.0 - 0.001 * (f % 2), -0.75 * (f % 3)]])
-        got = eng.step_host([d], None, [w])[0]
-        want = ora.update(d, None, w)
-        assert_rows_match(got, want, f)
+        w0 = np.array([[1.0 + 0.002 * (f % 3), 0.0, 1.5 * (f % 4)], [0.0, 1.0 - 0.001 * (f % 2), -0.75 * (f % 3)]])
+        th, sc = rng.normal(0, 0.004), 1 + rng.normal(0, 0.004)
+        w1 = np.array([[sc * np.cos(th), -sc * np.sin(th), rng.normal(0, 2)], [sc * np.sin(th), sc * np.cos(th), rng.normal(0, 2)]])
+        if f % 4 == 3:
+            w1 = w0                              # a rotation-free warp on tracks that are already dense
+        got = eng.step_host([d, d], None, [w0, w1])
+        for s, w in enumerate((w0, w1)):
+            assert_rows_match(got[s], ora[s].update(d, None, w), f)
     eng.status()
-    rot = np.array([[0.999, -0.04, 0.0], [0.04, 0.999, 0.0]])
-    eng.step_host([frames[0]], None, [rot])
-    with pytest.raises(RuntimeError, match="warp"):
-        eng.status()
+    for s in range(2):
+        mean, cov, ids, na = eng.peek(s)
+        trk = ora[s].active + ora[s].lost
+        assert np.array_equal(ids, [t.id for t in trk])
+        np.testing.assert_allclose(mean, np.array([t.mean for t in trk]), rtol=1e-8, atol=1e-8)
+        np.testing.assert_allclose(cov, np.array([t.cov for t in trk]), rtol=1e-7, atol=1e-9)
+    assert np.abs(cov[:, 0, 1]).max() > 0            # stream 1 really carries the x / y coupling
 
 
 def test_botsort_class_votes_follow_the_reference():

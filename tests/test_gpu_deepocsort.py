@@ -79,17 +79,44 @@ def test_deepocsort_engine_batched_streams_match_oracle(aw_off):
         np.testing.assert_allclose(P, np.array([t.kf.P for t in trk]), rtol=1e-9, atol=1e-12)
 
 
-def test_deepocsort_rotation_warp_is_refused():
+def test_deepocsort_rotation_warps_match_oracle_including_dense_covariance():
+    """apply_affine_correction with a similarity warp (rotation): x and y couple, so the engine moves the
+    track to its dense 7x7 covariance (kf_xysr.cuh xysr_*) for the rest of its life -- later predicts,
+    updates, freezes and ORU replays included.  Rows equal the oracle's; Kalman state within 1e-8."""
     from boxmot_b200.engine import DeepOcSortEngine
-    from boxmot_b200.synth import make_stream
-    eng = DeepOcSortEngine(1, track_cap=64, det_cap=64, emb_dim=16, **DEEPOCSORT_YAML)
-    fr, em = make_stream(31, 10, 3, emb_dim=16)
-    eng.step_host([fr[0]], [em[0]])
+    from boxmot_b200.synth import make_batch
+    from oracle.deepocsort import DeepOcSortOracle
+    S, K, F, D, E = 8, 25, 40, 64, 16
+    kw = dict(DEEPOCSORT_YAML, det_thresh=0.4, max_age=6)
+    dets, nd, embs = make_batch(S, K, F, D, emb_dim=E, first_stream=1500)
+    eng = DeepOcSortEngine(S, track_cap=128, det_cap=D, emb_dim=E, **kw)
+    oracles = [DeepOcSortOracle(**kw) for _ in range(S)]
+    rng = np.random.default_rng(9)
+    d_dets, d_nd, d_embs = torch.as_tensor(dets.astype(np.float32)).cuda(), torch.as_tensor(nd).cuda(), torch.as_tensor(embs).cuda()
+    for f in range(F):
+        th, sc = rng.normal(0, 0.004, S), 1 + rng.normal(0, 0.005, S)
+        if f % 5 == 4:
+            th[:] = 0.0                       # rotation-free warps on tracks that are already dense
+        w = np.zeros((S, 2, 3))
+        w[:, 0, 0] = sc * np.cos(th); w[:, 0, 1] = -sc * np.sin(th)
+        w[:, 1, 0] = sc * np.sin(th); w[:, 1, 1] = sc * np.cos(th)
+        w[:, :, 2] = rng.normal(0, 2, (S, 2))
+        w[S - 1] = [[1, 0, 0], [0, 1, 0]]     # one stream never rotates: stays in block form
+        out, nout = eng.step(d_dets[f], d_nd[f], d_embs[f], torch.as_tensor(w).cuda())
+        out, nout = out.cpu().numpy(), nout.cpu().numpy()
+        for s in range(S):
+            n = nd[f, s]
+            want = oracles[s].update(dets[f, s, :n], None, embs[f, s, :n].copy(), warp=w[s])
+            assert_rows_match(out[s, : nout[s]], want, f)
     eng.status()
-    rot = np.array([[0.999, -0.04, 0.0], [0.04, 0.999, 0.0]])
-    eng.step_host([fr[1]], [em[1]], [rot])
-    with pytest.raises(RuntimeError, match="warp"):
-        eng.status()
+    for s in (0, 3, S - 1):
+        x, P, ids = eng.peek(s)
+        trk = oracles[s].tracks
+        assert np.array_equal(ids, [t.id - 1 for t in trk])
+        np.testing.assert_allclose(x, np.array([t.kf.x for t in trk]), rtol=1e-8, atol=1e-8)
+        np.testing.assert_allclose(P, np.array([t.kf.P for t in trk]), rtol=1e-7, atol=1e-9)
+        if s < S - 1 and len(trk):
+            assert np.abs(P[:, 0, 1]).max() > 0      # the x / y coupling is really there
 
 
 def test_deepocsort_embedding_decides_between_overlapping_candidates():

@@ -91,11 +91,13 @@ def test_bytetrack_oracle_matches_reference_golden(case):
 def test_botsort_oracle_matches_reference_golden(case):
     """BoT-SORT (BASELINE configs[2] tracker): XYWH filter, IoU / embedding fusion, feature EMA."""
     from oracle.botsort import BotSortOracle
+    from conftest import botsort_warps
     frames, embs, kw, want = botsort_case(case)
+    warps = botsort_warps(case)
     ora = BotSortOracle(**{**BOTSORT_YAML, **kw})
     want_f = split_by_frame(want, len(frames))
     for f, d in enumerate(frames):
-        got = ora.update(d, None if embs is None else embs[f].copy())
+        got = ora.update(d, None if embs is None else embs[f].copy(), None if warps is None else warps[f])
         assert_rows_match(got, want_f[f], f, box_rtol=1e-9)
 
 
