@@ -283,15 +283,20 @@ def main_boosttrack():
         print("boosttrack", name, out.shape, "ids", int(out[:, 5].max()))
 
 
-def main_mot17_emb():
-    """DeepOCSORT / BoostTrack on MOT17-mini det.txt (MOT17-02-FRCNN) with seeded embeddings."""
-    dets = load_det_txt("MOT17-02-FRCNN").astype(np.float32).astype(np.float64)
-    fr = frames_of(dets)
-    em = mot17_embs(fr, 48, 77)
-    for tracker, kw in (("deepocsort", {"det_thresh": 0.3}), ("boosttrack", {"det_thresh": 0.5})):
-        out = run_ref(tracker, fr, em, **kw)
-        np.savez_compressed(os.path.join(GOLD, "ref_%s_MOT17_02_FRCNN.npz" % tracker), rows=out, kw=np.array(repr(kw)))
-        print(tracker, "MOT17_02_FRCNN", out.shape, "ids", int(out[:, 5].max()))
+def main_mot17_emb(seqs=("MOT17-02-FRCNN",)):
+    """DeepOCSORT / BoostTrack (and, for MOT17-04, BoT-SORT) on MOT17-mini det.txt with seeded embeddings."""
+    for seq in seqs:
+        dets = load_det_txt(seq).astype(np.float32).astype(np.float64)
+        fr = frames_of(dets)
+        em = mot17_embs(fr, 48, 77)
+        name = seq.replace("-", "_")
+        todo = [("deepocsort", {"det_thresh": 0.3}), ("boosttrack", {"det_thresh": 0.5})]
+        if seq != "MOT17-02-FRCNN":
+            todo.append(("botsort", {}))                       # with ReID on the seeded embeddings
+        for tracker, kw in todo:
+            out = run_ref(tracker, fr, em, **kw)
+            np.savez_compressed(os.path.join(GOLD, "ref_%s_%s.npz" % (tracker, name)), rows=out, kw=np.array(repr(kw)))
+            print(tracker, name, out.shape, "ids", int(out[:, 5].max()))
 
 
 def strongsort_gate_vectors(la, rng):
@@ -666,6 +671,8 @@ if __name__ == "__main__":
         main_deepocsort()
     elif "--boosttrack" in sys.argv:
         main_boosttrack()
+    elif "--mot17-04-emb" in sys.argv:
+        main_mot17_emb(("MOT17-04-FRCNN",))
     elif "--mot17-emb" in sys.argv:
         main_mot17_emb()
     elif "--strongsort" in sys.argv:

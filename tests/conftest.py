@@ -61,6 +61,7 @@ BOTSORT_CASES = {
     "synth_k30_e32_rot": (14, 30, 60, 32),           # similarity camera warps: multi_gmc with rotation (dense covariance)
     "synth_k40_noreid_rot": (15, 40, 50, 0),
     "MOT17_02_FRCNN": None,
+    "MOT17_04_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings, with ReID (gen_golden --mot17-04-emb)
 }
 
 
@@ -74,6 +75,9 @@ def botsort_case(case):
     from boxmot_b200.synth import make_stream
     rows, kw = golden_rows("botsort", case)
     spec = BOTSORT_CASES[case]
+    if case == "MOT17_04_FRCNN":
+        fr, em = _mot17_emb_case(case)
+        return fr, em, kw, rows
     if spec is None:
         return mot17_frames(case), None, kw, rows
     sid, k, f, e = spec
@@ -97,6 +101,7 @@ DEEPOCSORT_CASES = {
     "synth_k30_e32_rot": (27, 30, 60, 32),           # similarity warps: rotation couples x and y (dense covariance)
     "synth_k50_e16_rot_age5": (28, 50, 50, 16),
     "MOT17_02_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings (gen_golden --mot17-emb)
+    "MOT17_04_FRCNN": None,
 }
 
 
@@ -145,6 +150,7 @@ BOOSTTRACK_CASES = {
     "synth_k30_noduo": (44, 30, 50, 8, False),
     "synth_k30_nodlo": (45, 30, 50, 8, False),
     "MOT17_02_FRCNN": None,      # real det.txt rows + seeded 48-d embeddings (gen_golden --mot17-emb)
+    "MOT17_04_FRCNN": None,
 }
 
 

@@ -124,6 +124,67 @@ def test_full_size_batch_properties_embedding_trackers(tracker):
             assert np.array_equal(out[s, : nout[s]], out2[j, : nout2[j]]), (f, s)
 
 
+@pytest.mark.parametrize("tracker", ["botsort", "strongsort"])
+def test_config_shape_batch_properties_botsort_strongsort(tracker):
+    """BASELINE configs[2] / configs[3] shapes per stream -- BoT-SORT with 200 detections per frame and 512-d
+    embeddings (512 streams), StrongSORT with 100 detections per frame, 768-d embeddings and a 50-deep sample
+    bank (96 streams) -- checked through size-independent properties: a sample of streams equals the CPU
+    oracle frame by frame, rows point at distinct detections of their frame with ids >= 1, and a stream's
+    rows do not depend on the rest of the batch (bit-identical when stepped in another batch)."""
+    from boxmot_b200.engine import BotSortEngine, StrongSortEngine
+    from boxmot_b200.synth import make_batch
+    from conftest import BOTSORT_YAML, STRONGSORT_YAML
+    if tracker == "botsort":
+        from oracle.botsort import BotSortOracle as Oracle
+        NS, KO, FR, E, DC = 512, 200, 10, 512, 256
+        kw = BOTSORT_YAML
+        make = lambda n: BotSortEngine(n, track_cap=512, det_cap=DC, emb_dim=E, **kw)
+        upd = lambda o, d, e: o.update(d, e.copy())
+        sample = (0, 255, 511)
+    else:
+        from oracle.strongsort_tracker import StrongSortOracle as Oracle
+        NS, KO, FR, E, DC = 96, 100, 30, 768, 128
+        kw = dict(STRONGSORT_YAML, nn_budget=50)
+        make = lambda n: StrongSortEngine(n, track_cap=1024, det_cap=DC, pool_cap=4096, emb_dim=E, **kw)
+        upd = lambda o, d, e: o.update(d.astype(np.float64), e.astype(np.float64))
+        sample = (0, 95)
+    dets, nd, embs = make_batch(NS, KO, FR, DC, emb_dim=E)
+    dets = dets.astype(np.float32)
+
+    def run(dets, nd, embs):
+        eng = make(dets.shape[1])
+        d_dets, d_nd = torch.as_tensor(np.ascontiguousarray(dets)).cuda(), torch.as_tensor(np.ascontiguousarray(nd)).cuda()
+        rows = []
+        for f in range(dets.shape[0]):
+            out, nout = eng.step(d_dets[f], d_nd[f], torch.as_tensor(np.ascontiguousarray(embs[f])).cuda())
+            rows.append((out.cpu().numpy(), nout.cpu().numpy()))
+        eng.status()
+        eng.close()
+        return rows
+
+    rows = run(dets, nd, embs)
+    oracles = {s: Oracle(**kw) for s in sample}
+    for f in range(FR):
+        out, nout = rows[f]
+        for s in sample:
+            n = nd[f, s]
+            assert_rows_match(out[s, : nout[s]], upd(oracles[s], dets[f, s, :n], embs[f, s, :n]), f)
+        for s in range(0, NS, 7):
+            r = out[s, : nout[s]]
+            if len(r):
+                di = r[:, 7].astype(int)
+                assert len(set(di)) == len(di) and di.min() >= 0 and di.max() < nd[f, s]
+                assert len(set(r[:, 4])) == len(r) and r[:, 4].min() >= 1
+    pick = np.arange(NS)[::-5][:16]
+    rows2 = run(dets[:, pick], nd[:, pick], embs[:, pick])
+    for f in range(FR):
+        out, nout = rows[f]
+        out2, nout2 = rows2[f]
+        for j, s in enumerate(pick):
+            assert nout[s] == nout2[j]
+            assert np.array_equal(out[s, : nout[s]], out2[j, : nout2[j]]), (f, s)
+
+
 @pytest.mark.parametrize("tracker", ["deepocsort", "boosttrack"])
 def test_crowd_density_streams_match_oracle(tracker):
     """BASELINE configs[4] shape per stream: MOT20-like crowds of ~480 detections per frame (hot-spot
