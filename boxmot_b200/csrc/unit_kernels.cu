@@ -639,6 +639,55 @@ extern "C" int bm_pack_rows(const double* d_out, const int* d_nout, int n_stream
     return e == cudaSuccess ? 0 : unit_fail("pack_rows_kernel", e);
 }
 
+// ---- bm_pack_mot_rows: convert_to_mot_format (boxmot/engine/utils.py:101-146, ndarray branch) for every
+// stream of a frame, fused with the ragged packing of bm_pack_rows: 9 columns per row =
+// frame, id, left, top, width, height (rounded half-to-even like np.round, as int32), 1, class, confidence.
+namespace bm {
+__global__ void __launch_bounds__(256)
+pack_mot_rows_kernel(const double* __restrict__ out, const int* __restrict__ nout, int S, int out_rows, int frame_idx,
+                     double* __restrict__ rows, int* __restrict__ offsets) {
+    __shared__ int s_part[8];
+    __shared__ int s_off;
+    const int s = blockIdx.x, tid = threadIdx.x;
+    int acc = 0;
+    for (int i = tid; i < s; i += blockDim.x) acc += nout[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(BM_FULL, acc, o);
+    if ((tid & 31) == 0) s_part[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+        int t = 0;
+        for (int i = 0; i < 8; i++) t += s_part[i];
+        s_off = t;
+        offsets[s] = t;
+        if (s == S - 1) offsets[S] = t + nout[s];
+    }
+    __syncthreads();
+    const int n = nout[s];
+    for (int i = tid; i < n; i += blockDim.x) {
+        const double* r = out + ((size_t)s * out_rows + i) * 8;
+        double* d = rows + (size_t)(s_off + i) * 9;
+        const double w = r[2] - r[0], h = r[3] - r[1];          // ops.xyxy2ltwh
+        d[0] = (double)frame_idx;
+        d[1] = (double)(int)r[4];
+        d[2] = (double)(int)rint(r[0]); d[3] = (double)(int)rint(r[1]);
+        d[4] = (double)(int)rint(w); d[5] = (double)(int)rint(h);
+        d[6] = 1.0;
+        d[7] = (double)(int)r[6];
+        d[8] = r[5];
+    }
+}
+}  // namespace bm
+
+extern "C" int bm_pack_mot_rows(const double* d_out, const int* d_nout, int n_streams, int out_rows, int frame_idx,
+                                double* rows_dst, int* offsets_dst, void* stream) {
+    if (n_streams <= 0) return 0;
+    if (!d_out || !d_nout || !rows_dst || !offsets_dst || out_rows <= 0) return -1;
+    bm::pack_mot_rows_kernel<<<n_streams, 256, 0, static_cast<cudaStream_t>(stream)>>>(d_out, d_nout, n_streams, out_rows,
+                                                                                       frame_idx, rows_dst, offsets_dst);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : unit_fail("pack_mot_rows_kernel", e);
+}
+
 // ---- bm_cosine_distance_noalloc: bm_cosine_distance for callers that cannot allocate -------
 // (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The row-index / norm
 // scratch that bm_cosine_distance takes from the caller lives in ONE file-scope device array;

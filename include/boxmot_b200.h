@@ -263,6 +263,14 @@ int bm_ocsort_peek(void* handle, int stream_index, int* n_tracks, double* h_x, d
 int bm_pack_rows(const double* d_out, const int* d_nout, int n_streams, int out_rows, double* rows_dst,
                  int* offsets_dst, void* stream);
 
+/* convert_to_mot_format (boxmot/engine/utils.py:101-146, the ndarray branch) for all streams of a frame,
+ * fused with bm_pack_rows' ragged packing: rows_dst [sum(nout)][9] float64 = frame_idx, id, left, top,
+ * width, height (xyxy2ltwh, rounded half-to-even as np.round, cast to int32), 1, class, confidence --
+ * what write_mot_results (:149-172) prints with "%d,%d,%d,%d,%d,%d,%d,%d,%.6f".  Destinations as
+ * bm_pack_rows (device or mapped pinned host memory). */
+int bm_pack_mot_rows(const double* d_out, const int* d_nout, int n_streams, int out_rows, int frame_idx,
+                     double* rows_dst, int* offsets_dst, void* stream);
+
 /* ---- unit-testable kernels ---------------------------------------------------- */
 
 /* lap.lapjv(cost, extend_cost=True, cost_limit) for a batch of problems (call sites:

@@ -632,6 +632,33 @@ def main_strongsort():
               "recovered", sum(1 for a, b in zip(ntr, ntr[1:]) if b[1] < a[1]))
 
 
+def main_mot_writer():
+    """The reference's own convert_to_mot_format + write_mot_results (boxmot/engine/utils.py:101-172) on
+    the ByteTrack MOT17-02-FRCNN golden rows -> tests/golden/ref_mot_results_bytetrack_MOT17_02_FRCNN.txt.
+    engine/utils.py imports ultralytics (absent), so the two functions are executed from their source text;
+    R6: the fork's rewritten utils/ops.py has no `xyxy2ltwh` (convert_to_mot_format raises AttributeError as
+    shipped); it is the same map as the fork's own `xyxy2tlwh` (x1, y1, x2 - x1, y2 - y1), injected here."""
+    import tempfile
+    from pathlib import Path
+    ref_shim.load()
+    from boxmot.utils import ops
+    if not hasattr(ops, "xyxy2ltwh"):
+        ops.xyxy2ltwh = ops.xyxy2tlwh                      # R6
+    src = open(os.path.join(ref_shim.REF_ROOT, "boxmot", "engine", "utils.py")).read()
+    src = src[src.index("def convert_to_mot_format("):].split("\ndef eval_setup")[0]
+    g = {"ops": ops, "np": np}
+    exec("from pathlib import Path\nfrom typing import Union\nimport torch\nResults = object\n" + src, g)
+    z = np.load(os.path.join(GOLD, "ref_bytetrack_MOT17_02_FRCNN.npz"))["rows"]
+    path = Path(tempfile.mkdtemp()) / "MOT17-02-FRCNN.txt"
+    for f in range(int(z[:, 0].max()) + 1):
+        r = z[z[:, 0] == f][:, 1:]
+        if r.size:
+            g["write_mot_results"](path, g["convert_to_mot_format"](r, f + 1))
+    txt = path.read_text()
+    open(os.path.join(GOLD, "ref_mot_results_bytetrack_MOT17_02_FRCNN.txt"), "w").write(txt)
+    print("mot writer:", len(txt.splitlines()), "rows;", txt.splitlines()[0])
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     dets = {s: load_det_txt(s) for s in SEQS}
@@ -677,6 +704,8 @@ if __name__ == "__main__":
         main_mot17_emb()
     elif "--strongsort" in sys.argv:
         main_strongsort()
+    elif "--mot-writer" in sys.argv:
+        main_mot_writer()
     elif "--strongsort-units" in sys.argv:
         main_strongsort_units()
     else:
