@@ -59,6 +59,7 @@ _SIGS = {
     "bm_ocsort_destroy": (c_int, [c_void_p]),
     "bm_ocsort_reset": (c_int, [c_void_p, c_void_p]),
     "bm_ocsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bm_ocsort_step_frames": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "bm_ocsort_status": (c_int, [c_void_p, ctypes.POINTER(c_int),
                                  ctypes.POINTER(ctypes.c_ulonglong),
                                  ctypes.POINTER(ctypes.c_ulonglong), c_void_p]),
@@ -140,6 +141,7 @@ _SIGS = {
                                        c_void_p]),
     "bm_strongsort_usage": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                     c_void_p]),
+    "bm_strongsort_debug_copy": (c_int, [c_void_p, c_int, c_int, c_void_p, ctypes.c_size_t, c_void_p]),
     "bm_strongsort_time_kernels": (c_int, [c_void_p, c_int]),
     "bm_strongsort_kernel_times": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_float * 6)]),
     "bm_strongsort_peek": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_void_p, c_void_p,

@@ -119,7 +119,7 @@ __device__ __forceinline__ void bot_gmc(double* x, double* P, const double* w6, 
     for (int i = 0; i < 4; i++) {
         const double r = (i & 1) ? r11 : r00;
         x[i] = r * x[i]; x[4 + i] = r * x[4 + i];
-        P[i] = (r * P[i]) * r; P[4 + i] = (r * P[4 + i]) * r; P[8 + i] = (r * P[8 + i]) * r;
+        P[i] = (r * P[i]) * r; P[4 + i] = (r * P[4 + i]) * r; P[8 + i] = (r * P[8 + i]) * r; P[12 + i] = (r * P[12 + i]) * r;
     }
     x[0] += tx; x[1] += ty;
 }
@@ -174,13 +174,13 @@ struct ByteView {
 #pragma unroll
         for (int c = 0; c < 8; c++) x[c] = xP[c * Tcap + slot];
 #pragma unroll
-        for (int c = 0; c < 12; c++) P[c] = xP[(8 + c) * Tcap + slot];
+        for (int c = 0; c < XA_P; c++) P[c] = xP[(8 + c) * Tcap + slot];
     }
     __device__ __forceinline__ void store(int slot, const double* x, const double* P) const {
 #pragma unroll
         for (int c = 0; c < 8; c++) xP[c * Tcap + slot] = x[c];
 #pragma unroll
-        for (int c = 0; c < 12; c++) xP[(8 + c) * Tcap + slot] = P[c];
+        for (int c = 0; c < XA_P; c++) xP[(8 + c) * Tcap + slot] = P[c];
     }
 };
 
@@ -197,8 +197,8 @@ __device__ __forceinline__ void botd_store(const ByteView& v, int slot, const do
     for (int c = 0; c < 64; c++) v.dP[(size_t)c * v.Tcap + slot] = P[c];
 }
 __device__ __noinline__ void bot_make_dense(const ByteView& v, int slot) {
-    double pb[12], P[64];
-    for (int c = 0; c < 12; c++) pb[c] = v.xP[(8 + c) * v.Tcap + slot];
+    double pb[XA_P], P[64];
+    for (int c = 0; c < XA_P; c++) pb[c] = v.xP[(8 + c) * v.Tcap + slot];
     xyah_expand(pb, P);
     for (int c = 0; c < 64; c++) v.dP[(size_t)c * v.Tcap + slot] = P[c];
     v.I(BI_DENSE, slot) = 1;
@@ -419,13 +419,13 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
             sm.tflag[slot] |= TF_USED;
             continue;
         }
-        double x[8], P[12];
+        double x[8], P[XA_P];
         v.load(slot, x, P);
         if (v.I(BI_STATE, slot) != BT_TRACKED) {
             x[7] = 0.0;
             if (MODE == MODE_BOT) x[6] = 0.0;       // botsort_track.py:83-85 resets both size velocities
         }
-        cv8_predict<KIND>(x, P);
+        cv8_predict<KIND, true>(x, P);       // STrack.multi_predict
         if (MODE == MODE_BOT && warps) bot_gmc(x, P, warps + (size_t)s * 6, v.hdr);
         v.store(slot, x, P);
         v.set_box(slot, mean_to_xyxy<KIND>(x));
@@ -443,7 +443,7 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
                 v.set_box(slot, mean_to_xyxy<KIND>(xm));
                 continue;
             }
-            double x[8], P[12];
+            double x[8], P[XA_P];
             v.load(slot, x, P);
             bot_gmc(x, P, warps + (size_t)s * 6, v.hdr);
             v.store(slot, x, P);
@@ -559,7 +559,7 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
     // ---- STrack.update / re_activate (:68-103) for every matched pair; activate (:56-66) for births
     const int nUpd = sm.misc[BM_NUPD], nBorn = sm.misc[BM_NBORN];
     for (int k = tid; k < nUpd + nBorn; k += BT_NT) {
-        double x[8], P[12], z[4];
+        double x[8], P[XA_P], z[4];
         int slot, drow;
         if (k < nUpd) {
             slot = sm.upd_slot[k]; drow = sm.upd_det[k];

@@ -299,6 +299,41 @@ int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double
     return 0;
 }
 
+int bm_ocsort_step_frames(void* handle, const float* d_dets, const int* d_ndets, double* d_out, int* d_nout,
+                          int n_frames, void* stream) {
+    OcsEngine* e = static_cast<OcsEngine*>(handle);
+    if (!e || !d_dets || !d_ndets || !d_out || !d_nout || n_frames < 0) return fail(-1, "bm_ocsort_step_frames: bad argument");
+    if (e->deep) return fail(-1, "bm_ocsort_step_frames: DeepOCSORT engine");
+    const bm::OcsState& st = e->st;
+    const size_t S = st.S, D = st.Dcap, orow = (size_t)(st.Tcap < st.Dcap ? st.Tcap : st.Dcap) * 8;
+    cudaStream_t main = static_cast<cudaStream_t>(stream);
+    if (e->grp.n <= 1) {
+        for (int f = 0; f < n_frames; f++)
+            BM_CUDA(bm::ocsort_step_launch(st, e->pr, d_dets + f * S * D * 6, d_ndets + f * S, d_out + f * S * orow,
+                                           d_nout + f * S, main, nullptr));
+        e->timed = false;
+        return 0;
+    }
+    // every group runs its chain of launches for ALL frames back to back on its own CUDA stream: a group that
+    // is waiting for the slowest of its streams no longer holds the others back frame by frame
+    BM_CUDA(cudaEventRecord(e->grp.fork, main));
+    for (int g = 0; g < e->grp.n; g++) BM_CUDA(cudaStreamWaitEvent(e->grp.streams[g], e->grp.fork, 0));
+    for (int f = 0; f < n_frames; f++)
+        for (int g = 0; g < e->grp.n; g++) {
+            int s0, n;
+            StreamGroups::span(g, e->grp.n, st.S, &s0, &n);
+            BM_CUDA(bm::ocsort_step_launch(bm::ocs_substate(st, s0, n, 0), e->pr, d_dets + (f * S + s0) * D * 6,
+                                           d_ndets + f * S + s0, d_out + (f * S + s0) * orow, d_nout + f * S + s0,
+                                           e->grp.streams[g], nullptr));
+        }
+    for (int g = 0; g < e->grp.n; g++) {
+        BM_CUDA(cudaEventRecord(e->grp.done[g], e->grp.streams[g]));
+        BM_CUDA(cudaStreamWaitEvent(main, e->grp.done[g], 0));
+    }
+    e->timed = false;
+    return 0;
+}
+
 int bm_ocsort_set_groups(void* handle, int groups) {
     OcsEngine* e = static_cast<OcsEngine*>(handle);
     if (!e) return fail(-1, "null handle");
@@ -835,8 +870,8 @@ int bm_bytetrack_peek(void* handle, int si, int* n_active, int* n_lost, double* 
         if (h_cov && st.dP && ints[bm::BI_DENSE * T + slot]) {
             for (int c = 0; c < 64; c++) h_cov[(size_t)p * 64 + c] = dp[c * T + slot];
         } else if (h_cov) {
-            double pb[12];
-            for (int c = 0; c < 12; c++) pb[c] = xp[(8 + c) * T + slot];
+            double pb[bm::XA_P];
+            for (int c = 0; c < bm::XA_P; c++) pb[c] = xp[(8 + c) * T + slot];
             bm::xyah_expand(pb, h_cov + (size_t)p * 64);
         }
         if (h_ids) h_ids[p] = ints[bm::BI_ID * T + slot];

@@ -1,20 +1,24 @@
-// KalmanFilterXYAH (boxmot/motion/kalman_filters/aabb/xyah_kf.py over
-// base_kalman_filter.py:24-155) in block form.
+// KalmanFilterXYAH / KalmanFilterXYWH (boxmot/motion/kalman_filters/aabb/xyah_kf.py, xywh_kf.py over
+// base_kalman_filter.py:24-194) in block form, BIT-IDENTICAL to the reference's numpy / scipy arithmetic.
 //
-// State (x, y, a, h, vx, vy, va, vh); F = I + shift, H = [I4 0], P0 / Q / R diagonal
-// (xyah_kf.py:17-62), so the 8x8 covariance only ever couples (pos_i, vel_i): it is stored as
-// 12 numbers  P[i] = var(pos_i), P[4+i] = cov(pos_i, vel_i), P[8+i] = var(vel_i)  and every
-// formula below is the reference's dense expression restricted to the entries that can be
-// non-zero (the dropped terms are exact zeros).  Differences to the reference are at the
-// rounding level only: the dense update is not bit-symmetric (K (S K^T)) and scipy's
-// cho_solve multiplies by reciprocals inside OpenBLAS; tests bound the state at 1e-9.
+// State (x, y, a|w, h, vx, vy, va|vw, vh); F = I + shift, H = [I4 0], P0 / Q / R diagonal, so the 8x8
+// covariance only ever couples (pos_i, vel_i).  It is stored as 16 numbers
+//     P[i] = P[i][i],  P[4+i] = P[i][i+4],  P[8+i] = P[i+4][i],  P[12+i] = P[i+4][i+4]
+// -- BOTH off-diagonal entries, because the reference's update `P - K (S K^T)` is not bit-symmetric.
+// Every formula below is the reference's dense expression restricted to the entries that can be
+// non-zero, in the reference's own operation order: each matrix-product entry has at most one
+// non-zero term (exact whatever FMA the BLAS kernel uses) or two terms of coefficient 1; scipy's
+// cho_solve / solve_triangular on the (diagonal) innovation covariance multiply by the RECIPROCAL of
+// the Cholesky diagonal (OpenBLAS' trsm kernels invert the diagonal once), which is reproduced.
+// Checked bit for bit against the scipy-based oracle (tests/test_gpu_units.py).
 #pragma once
 #include "common.cuh"
 #include "iou.cuh"
 
 namespace bm {
 
-constexpr int XA_N = 20;                       // 8 mean + 12 covariance
+constexpr int XA_N = 24;                       // 8 mean + 16 covariance
+constexpr int XA_P = 16;
 constexpr double XA_W_POS = 1.0 / 20, XA_W_VEL = 1.0 / 160;   // base_kalman_filter.py:40-41
 
 // Noise standard deviations of the two constant-velocity box filters:
@@ -44,23 +48,25 @@ __device__ __forceinline__ void cv8_initiate(const double* z, double* x, double*
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         x[i] = z[i]; x[4 + i] = 0.0;
-        P[i] = sp[i] * sp[i]; P[4 + i] = 0.0; P[8 + i] = sv[i] * sv[i];
+        P[i] = sp[i] * sp[i]; P[4 + i] = 0.0; P[8 + i] = 0.0; P[12 + i] = sv[i] * sv[i];
     }
 }
 
-// predict / multi_predict (base_kalman_filter.py:62-77, :111-127)
-template <int KIND>
+// predict (base_kalman_filter.py:62-77): multi_dot((F, P, F^T)) evaluates F (P F^T) for square factors;
+// multi_predict (:111-127, MULTI = true): np.dot(np.dot(F, P), F^T).  The two differ in the order of
+// the four-term sum of P[i][i] once the two off-diagonal entries differ in their last bits.
+template <int KIND, bool MULTI = false>
 __device__ __forceinline__ void cv8_predict(double* x, double* P) {
     double sp[4], sv[4];
     cv8_std<KIND>(x, 1.0, 1.0, 1e-2, 1e-5, sp, sv);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         x[i] = x[i] + x[4 + i];
-        const double pp = P[i], pv = P[4 + i], vv = P[8 + i];
-        // (F P)[i][i] = pp + pv, (F P)[i][i+4] = pv + vv; then (F P) F^T
-        P[i] = ((pp + pv) + (pv + vv)) + sp[i] * sp[i];
-        P[4 + i] = pv + vv;
-        P[8 + i] = vv + sv[i] * sv[i];
+        const double a = P[i], b = P[4 + i], c = P[8 + i], d = P[12 + i];
+        P[i] = (MULTI ? (a + c) + (b + d) : (a + b) + (c + d)) + sp[i] * sp[i];
+        P[4 + i] = b + d;
+        P[8 + i] = c + d;
+        P[12 + i] = d + sv[i] * sv[i];
     }
 }
 
@@ -76,23 +82,24 @@ __device__ __forceinline__ void cv8_project(const double* x, const double* P, do
     }
 }
 
-// update (base_kalman_filter.py:129-155)
+// update (base_kalman_filter.py:129-155): K = cho_solve(cho_factor(S), (P H^T)^T)^T uses column i of P
+// (P[i][i], P[i+4][i]) and the reciprocal of sqrt(S_ii) twice; P <- P - K (S K^T)
 template <int KIND>
 __device__ __forceinline__ void cv8_update(double* x, double* P, const double* z, double confidence) {
     double S[4];
     cv8_project<KIND>(x, P, confidence, S);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        const double pp = P[i], pv = P[4 + i], vv = P[8 + i];
-        const double l = sqrt(S[i]);                 // cho_factor of a diagonal matrix
-        const double kp = (pp / l) / l, kv = (pv / l) / l;   // cho_solve: forward, then back substitution
+        const double a = P[i], b = P[4 + i], c = P[8 + i], d = P[12 + i];
+        const double inv = 1.0 / sqrt(S[i]);         // cho_factor of a diagonal matrix; trsm inverts the diagonal
+        const double kp = (a * inv) * inv, kv = (c * inv) * inv;
         const double innov = z[i] - x[i];
         x[i] = x[i] + innov * kp;
         x[4 + i] = x[4 + i] + innov * kv;
-        // covariance - K (S K^T)   (multi_dot picks A(BC) for these shapes)
-        P[i] = pp - kp * (S[i] * kp);
-        P[4 + i] = pv - kp * (S[i] * kv);
-        P[8 + i] = vv - kv * (S[i] * kv);
+        P[i] = a - kp * (S[i] * kp);
+        P[4 + i] = b - kp * (S[i] * kv);
+        P[8 + i] = c - kv * (S[i] * kp);
+        P[12 + i] = d - kv * (S[i] * kv);
     }
 }
 
@@ -107,14 +114,14 @@ __device__ __forceinline__ double cv8_gating(const double* x, const double* P, c
     double acc = 0.0;
     for (int i = 0; i < n; i++) {
         const double d = z[i] - x[i];
-        const double q = gaussian ? d : d / sqrt(S[i]);
+        const double q = gaussian ? d : d * (1.0 / sqrt(S[i]));     // solve_triangular: reciprocal of the diagonal
         acc = i == 0 ? q * q : acc + q * q;
     }
     return acc;
 }
 
 __device__ __forceinline__ void xyah_initiate(const double* z, double* x, double* P) { cv8_initiate<CV8_XYAH>(z, x, P); }
-__device__ __forceinline__ void xyah_predict(double* x, double* P) { cv8_predict<CV8_XYAH>(x, P); }
+__device__ __forceinline__ void xyah_predict(double* x, double* P) { cv8_predict<CV8_XYAH, true>(x, P); }
 __device__ __forceinline__ void xyah_update(double* x, double* P, const double* z) { cv8_update<CV8_XYAH>(x, P, z, 0.0); }
 
 // STrack.xyxy (bytetrack.py:105-116) from the mean
@@ -129,8 +136,8 @@ __host__ __device__ inline void xyah_expand(const double* P, double* out64) {
     for (int i = 0; i < 4; i++) {
         out64[i * 8 + i] = P[i];
         out64[i * 8 + 4 + i] = P[4 + i];
-        out64[(4 + i) * 8 + i] = P[4 + i];
-        out64[(4 + i) * 8 + 4 + i] = P[8 + i];
+        out64[(4 + i) * 8 + i] = P[8 + i];
+        out64[(4 + i) * 8 + 4 + i] = P[12 + i];
     }
 }
 

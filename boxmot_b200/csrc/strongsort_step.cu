@@ -60,7 +60,7 @@ struct SsParams {
 
 struct SsState {
     int S, Tcap, Dcap, Pcap, B, M;       // M = 2 * Tcap + Dcap: bound of an assignment problem's side
-    double *mean, *covb, *tab;           // [S][Tcap][8], [S][Tcap][12], [S][Tcap][ST_FIELDS]
+    double *mean, *covb, *tab;           // [S][Tcap][8], [S][Tcap][16], [S][Tcap][ST_FIELDS]
     int *tint, *ring;                    // [S][Tcap][TI_COUNT], [S][Tcap][SS_RING]
     int *bslot, *bseq, *dslot, *dcnt;    // [S][Tcap][B] sample list entries (slot, seq); distinct slots and counts
     double* bminq;                       // [S][Tcap]
@@ -83,7 +83,7 @@ struct SsView {
     __device__ int* hdr() const { return st.hdr + (size_t)s * SH_COUNT; }
     __device__ int* order() const { return st.order + (size_t)s * st.Tcap; }
     __device__ double* mean(int t) const { return st.mean + ((size_t)s * st.Tcap + t) * 8; }
-    __device__ double* covb(int t) const { return st.covb + ((size_t)s * st.Tcap + t) * 12; }
+    __device__ double* covb(int t) const { return st.covb + ((size_t)s * st.Tcap + t) * XA_P; }
     __device__ double* tab(int t) const { return st.tab + ((size_t)s * st.Tcap + t) * ST_FIELDS; }
     __device__ int* tint(int t) const { return st.tint + ((size_t)s * st.Tcap + t) * TI_COUNT; }
     __device__ int* ring(int t) const { return st.ring + ((size_t)s * st.Tcap + t) * SS_RING; }
@@ -210,13 +210,13 @@ ss_prep_kernel(SsState st, SsParams pr, const float* __restrict__ dets, const in
             for (int c = 0; c < 6; c++) w[c] = warps ? warps[(size_t)s * 6 + c] : ident[c];
             ss_track_camera(m, a, w);
         }
-        double x[8], P[12];
+        double x[8], P[XA_P];
         double* C = v.covb(t);
         for (int c = 0; c < 8; c++) x[c] = m[c];
-        for (int c = 0; c < 12; c++) P[c] = C[c];
+        for (int c = 0; c < XA_P; c++) P[c] = C[c];
         ss_track_predict(x, P, a);
         for (int c = 0; c < 8; c++) m[c] = x[c];
-        for (int c = 0; c < 12; c++) C[c] = P[c];
+        for (int c = 0; c < XA_P; c++) C[c] = P[c];
         int* ti = v.tint(t);
         ti[TI_NUPD] = 0; ti[TI_MISS] = 0; ti[TI_FEAS] = 0;
     }
@@ -684,14 +684,14 @@ __device__ void ss_apply_update(const SsView& v, const SsParams& pr, int t, int 
         const double* d = v.dtab(k);
         double* m = v.mean(t);
         double* C = v.covb(t);
-        double x[8], P[12];
+        double x[8], P[XA_P];
         for (int c = 0; c < 8; c++) x[c] = m[c];
-        for (int c = 0; c < 12; c++) P[c] = C[c];
+        for (int c = 0; c < XA_P; c++) P[c] = C[c];
         const double d7[7] = {d[DT_XYAH], d[DT_XYAH + 1], d[DT_XYAH + 2], d[DT_XYAH + 3], d[DT_CONF], d[DT_CLS],
                               d[DT_DETIND]};
         ss_track_update(x, P, v.tab(t), d7, pr.n_init);
         for (int c = 0; c < 8; c++) m[c] = x[c];
-        for (int c = 0; c < 12; c++) C[c] = P[c];
+        for (int c = 0; c < XA_P; c++) C[c] = P[c];
     }
     __syncwarp();
 }
@@ -888,10 +888,10 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
         const double* d = v.dtab(k);
         int* ti = v.tint(t);
         if (lane == 0) {
-            double x[8], P[12];
+            double x[8], P[XA_P];
             cv8_initiate<CV8_XYAH>(d + DT_XYAH, x, P);
             for (int c = 0; c < 8; c++) v.mean(t)[c] = x[c];
-            for (int c = 0; c < 12; c++) v.covb(t)[c] = P[c];
+            for (int c = 0; c < XA_P; c++) v.covb(t)[c] = P[c];
             double* a = v.tab(t);
             for (int c = 0; c < ST_FIELDS; c++) a[c] = 0.0;
             a[SS_AGE] = 1.0; a[SS_HITS] = 1.0; a[SS_MOTION] = 1.0; a[SS_APPEAR] = 1.0;
@@ -1119,7 +1119,7 @@ int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int tra
     st.wki_stride = T * 3 + 2 * T + 2 * T + D + (2 * T + D) + D + (size_t)pr.max_age + 2 + 6 * M + 8;
     cudaError_t r = cudaGetDevice(&e->device);
     auto A = [&](auto** p, size_t n) { if (r == cudaSuccess) r = ss_alloc(e, p, n); };
-    A(&st.mean, S * T * 8); A(&st.covb, S * T * 12); A(&st.tab, S * T * bm::ST_FIELDS);
+    A(&st.mean, S * T * 8); A(&st.covb, S * T * bm::XA_P); A(&st.tab, S * T * bm::ST_FIELDS);
     A(&st.tint, S * T * bm::TI_COUNT); A(&st.ring, S * T * bm::SS_RING);
     A(&st.bslot, S * T * B); A(&st.bseq, S * T * B); A(&st.dslot, S * T * B); A(&st.dcnt, S * T * B);
     A(&st.bminq, S * T); A(&st.upd, S * T * bm::SS_MAXUPD); A(&st.order, S * T); A(&st.lost, S * 32);
@@ -1246,6 +1246,22 @@ int bm_strongsort_usage(void* handle, int* max_tracks, int* max_pool_used, int* 
     return 0;
 }
 
+int bm_strongsort_debug_copy(void* handle, int which, int stream_index, void* h_dst, size_t nbytes, void* stream) {
+    SsEngine* e = static_cast<SsEngine*>(handle);
+    if (!e || stream_index < 0 || stream_index >= e->st.S || !h_dst) return ss_fail(-1, "bm_strongsort_debug_copy: bad argument");
+    const bm::SsState& st = e->st;
+    const size_t s = stream_index;
+    const void* src = nullptr;
+    size_t avail = 0;
+    if (which == 0) { src = st.wki + s * st.wki_stride; avail = st.wki_stride * 4; }
+    else if (which == 1) { src = st.cost + s * st.Tcap * st.Dcap; avail = (size_t)st.Tcap * st.Dcap * 8; }
+    else if (which == 2) { src = st.dtab + s * st.Dcap * bm::DT_COUNT; avail = (size_t)st.Dcap * bm::DT_COUNT * 8; }
+    else return ss_fail(-1, "bm_strongsort_debug_copy: unknown buffer");
+    SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    SS_CUDA(cudaMemcpy(h_dst, src, nbytes < avail ? nbytes : avail, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int bm_strongsort_time_kernels(void* handle, int enable) {
     SsEngine* e = static_cast<SsEngine*>(handle);
     if (!e) return ss_fail(-1, "bm_strongsort_time_kernels: null handle");
@@ -1270,12 +1286,12 @@ int bm_strongsort_peek(void* handle, int stream_index, int* n_tracks, int* n_los
     const size_t s = stream_index, T = st.Tcap;
     SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
     std::vector<int> hdr(bm::SH_COUNT), order(T), tint(T * bm::TI_COUNT);
-    std::vector<double> mean(T * 8), covb(T * 12), tab(T * bm::ST_FIELDS);
+    std::vector<double> mean(T * 8), covb(T * bm::XA_P), tab(T * bm::ST_FIELDS);
     SS_CUDA(cudaMemcpy(hdr.data(), st.hdr + s * bm::SH_COUNT, hdr.size() * sizeof(int), cudaMemcpyDeviceToHost));
     SS_CUDA(cudaMemcpy(order.data(), st.order + s * T, T * sizeof(int), cudaMemcpyDeviceToHost));
     SS_CUDA(cudaMemcpy(tint.data(), st.tint + s * T * bm::TI_COUNT, tint.size() * sizeof(int), cudaMemcpyDeviceToHost));
     SS_CUDA(cudaMemcpy(mean.data(), st.mean + s * T * 8, mean.size() * sizeof(double), cudaMemcpyDeviceToHost));
-    SS_CUDA(cudaMemcpy(covb.data(), st.covb + s * T * 12, covb.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    SS_CUDA(cudaMemcpy(covb.data(), st.covb + s * T * bm::XA_P, covb.size() * sizeof(double), cudaMemcpyDeviceToHost));
     SS_CUDA(cudaMemcpy(tab.data(), st.tab + s * T * bm::ST_FIELDS, tab.size() * sizeof(double), cudaMemcpyDeviceToHost));
     const int n = hdr[bm::SH_NTRACKS];
     if (n_tracks) *n_tracks = n;
@@ -1283,7 +1299,7 @@ int bm_strongsort_peek(void* handle, int stream_index, int* n_tracks, int* n_los
     for (int p = 0; p < n; p++) {
         const int t = order[p];
         if (h_mean) for (int c = 0; c < 8; c++) h_mean[(size_t)p * 8 + c] = mean[(size_t)t * 8 + c];
-        if (h_cov) bm::xyah_expand(covb.data() + (size_t)t * 12, h_cov + (size_t)p * 64);
+        if (h_cov) bm::xyah_expand(covb.data() + (size_t)t * bm::XA_P, h_cov + (size_t)p * 64);
         if (h_tab) for (int c = 0; c < bm::ST_FIELDS; c++) h_tab[(size_t)p * bm::ST_FIELDS + c] = tab[(size_t)t * bm::ST_FIELDS + c];
         if (h_ids) h_ids[p] = tint[(size_t)t * bm::TI_COUNT + bm::TI_ID];
         if (h_nbank) h_nbank[p] = tint[(size_t)t * bm::TI_COUNT + bm::TI_NBANK];

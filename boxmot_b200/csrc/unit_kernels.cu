@@ -124,25 +124,28 @@ __global__ void xysrb_update_kernel(double* x, double* Pb, const double* z, int 
 __device__ __forceinline__ void cv8_load(const double* mean, const double* cov, int i, double* x, double* P) {
     for (int c = 0; c < 8; c++) x[c] = mean[(size_t)i * 8 + c];
     const double* C = cov + (size_t)i * 64;
-    for (int c = 0; c < 4; c++) { P[c] = C[c * 8 + c]; P[4 + c] = C[c * 8 + 4 + c]; P[8 + c] = C[(4 + c) * 8 + 4 + c]; }
+    for (int c = 0; c < 4; c++) {
+        P[c] = C[c * 8 + c]; P[4 + c] = C[c * 8 + 4 + c]; P[8 + c] = C[(4 + c) * 8 + c]; P[12 + c] = C[(4 + c) * 8 + 4 + c];
+    }
 }
 __device__ __forceinline__ void cv8_store(double* mean, double* cov, int i, const double* x, const double* P) {
     for (int c = 0; c < 8; c++) mean[(size_t)i * 8 + c] = x[c];
     xyah_expand(P, cov + (size_t)i * 64);
 }
 
-// op: 0 initiate (z -> mean, cov), 1 predict, 2 update (z, conf)
+// op: 0 initiate (z -> mean, cov), 1 predict, 2 update (z, conf), 3 multi_predict
 template <int KIND>
 __global__ void cv8_kernel(int op, double* mean, double* cov, const double* z, const double* conf, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    double x[8], P[12], zs[4];
+    double x[8], P[XA_P], zs[4];
     if (z) for (int c = 0; c < 4; c++) zs[c] = z[(size_t)i * 4 + c];
     if (op == 0) {
         cv8_initiate<KIND>(zs, x, P);
     } else {
         cv8_load(mean, cov, i, x, P);
         if (op == 1) cv8_predict<KIND>(x, P);
+        else if (op == 3) cv8_predict<KIND, true>(x, P);
         else cv8_update<KIND>(x, P, zs, conf ? conf[i] : 0.0);
     }
     cv8_store(mean, cov, i, x, P);
@@ -155,7 +158,7 @@ __global__ void cv8_gating_kernel(const double* mean, const double* cov, int nt,
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nt * nd) return;
     const int t = e / nd, d = e % nd;
-    double x[8], P[12], zs[4];
+    double x[8], P[XA_P], zs[4];
     cv8_load(mean, cov, t, x, P);
     for (int c = 0; c < 4; c++) zs[c] = meas[(size_t)d * 4 + c];
     out[e] = cv8_gating<KIND>(x, P, zs, only_position != 0, gaussian != 0);
@@ -170,7 +173,7 @@ __global__ void ss_gated_metric_kernel(double* __restrict__ cost, const double* 
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nt * nd) return;
     const int t = e / nd, d = e % nd;
-    double x[8], P[12], z[4];
+    double x[8], P[XA_P], z[4];
     cv8_load(mean, cov, t, x, P);
     for (int c = 0; c < 4; c++) z[c] = meas[(size_t)d * 4 + c];
     cost[e] = ss_gated_entry(cost[e], x, P, trk + (size_t)t * SS_FIELDS, z, mc_lambda, id_weight);
@@ -254,7 +257,7 @@ __global__ void ss_track_kernel(int op, double* __restrict__ mean, double* __res
     double* a = trk + (size_t)i * ST_FIELDS;
     if (op == 2) { ss_track_mark_missed(a, max_age); return; }
     if (op == 3) { ss_track_camera(mean + (size_t)i * 8, a, det + (size_t)i * 7); return; }
-    double x[8], P[12];
+    double x[8], P[XA_P];
     cv8_load(mean, cov, i, x, P);
     if (op == 0) ss_track_predict(x, P, a);
     else ss_track_update(x, P, a, det + (size_t)i * 7, n_init);
@@ -454,7 +457,7 @@ int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* s
 int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z, const double* d_conf, int n,
               void* stream) {
     if (n <= 0) return 0;
-    if ((kind != 0 && kind != 1) || op < 0 || op > 2 || !d_mean || !d_cov || (op != 1 && !d_z)) return -1;
+    if ((kind != 0 && kind != 1) || op < 0 || op > 3 || !d_mean || !d_cov || ((op == 0 || op == 2) && !d_z)) return -1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (kind == 0) bm::cv8_kernel<bm::CV8_XYAH><<<(n + 127) / 128, 128, 0, st>>>(op, d_mean, d_cov, d_z, d_conf, n);
     else bm::cv8_kernel<bm::CV8_XYWH><<<(n + 127) / 128, 128, 0, st>>>(op, d_mean, d_cov, d_z, d_conf, n);

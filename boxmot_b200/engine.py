@@ -115,6 +115,24 @@ class OcSortEngine(_HostStepMixin):
         self.launches += 4      # predict, assoc, update, finalize
         return out, nout
 
+    def step_frames(self, dets, ndets, out=None, nout=None):
+        """F consecutive frames in one call: dets [F,S,det_cap,6] float32, ndets [F,S] int32 -> out
+        [F,S,out_rows,8], nout [F,S].  Same results as F ``step`` calls; with stream groups the groups run
+        all their frames back to back and are joined once (bm_ocsort_step_frames)."""
+        F = int(dets.shape[0])
+        assert dets.dtype == torch.float32 and dets.is_cuda and dets.is_contiguous()
+        assert tuple(dets.shape) == (F, self.S, self.Dcap, 6) and tuple(ndets.shape) == (F, self.S)
+        assert ndets.dtype == torch.int32 and ndets.is_cuda and ndets.is_contiguous()
+        if out is None:
+            out = torch.zeros((F, self.S, self.out_rows, 8), dtype=torch.float64, device=self.device)
+            nout = torch.zeros((F, self.S), dtype=torch.int32, device=self.device)
+        assert tuple(out.shape) == (F, self.S, self.out_rows, 8) and out.is_contiguous() and nout.is_contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_ocsort_step_frames(self._h, _ptr(dets), _ptr(ndets), _ptr(out), _ptr(nout), F,
+                                                        _stream_ptr(self.device)), "bm_ocsort_step_frames")
+        self.launches += 4 * F
+        return out, nout
+
     def status(self, raise_on_error=True):
         err = ctypes.c_int(0)
         upd = ctypes.c_ulonglong(0)

@@ -48,6 +48,15 @@ int bm_ocsort_reset(void* handle, void* stream);
 int bm_ocsort_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
                    int* d_nout, void* stream);
 
+/* n_frames consecutive frames in one call: d_dets [F][S][det_cap][6], d_ndets [F][S], d_out [F][S][out_rows][8],
+ * d_nout [F][S] -- the way the reference's evaluation driver consumes a sequence whose detections are all on disk
+ * already (boxmot/engine/val.py:304-354 loops `tracker.update` over the frames of a sequence).  Results are those
+ * of n_frames bm_ocsort_step calls.  With stream groups (bm_ocsort_set_groups) every group runs all its frames
+ * back to back on its own CUDA stream and the groups are joined once at the end, so a group waiting for the
+ * slowest of its streams no longer holds the other groups back frame by frame. */
+int bm_ocsort_step_frames(void* handle, const float* d_dets, const int* d_ndets, double* d_out, int* d_nout,
+                          int n_frames, void* stream);
+
 /* Step the engine's streams as `groups` independent groups, each on a CUDA stream of its own
  * (forked from and joined back into the caller's stream inside bm_ocsort_step /
  * bm_deepocsort_step): one group's streaming kernels then run under the tail of another group's
@@ -228,6 +237,9 @@ int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4
 /* Capacity planning: over all streams, the largest number of track slots in use (tracks + lost buffer),
  * of pool slots in use and of vectors referenced by a sample list (rows of the contraction) right now. */
 int bm_strongsort_usage(void* handle, int* max_tracks, int* max_pool_used, int* max_live, void* stream);
+/* Debug: host copy of one stream's scratch (which = 0: the cascade's integer work area, 1: the cost matrix
+ * [track_cap][det_cap] float64 by list position and sorted detection, 2: the sorted detection table). */
+int bm_strongsort_debug_copy(void* handle, int which, int stream_index, void* h_dst, size_t nbytes, void* stream);
 /* Per-launch CUDA-event timing: prepare+predict, bank contraction, cost matrix, cascade, updates, finalize (ms). */
 int bm_strongsort_time_kernels(void* handle, int enable);
 int bm_strongsort_kernel_times(void* handle, float* ms6);
@@ -308,8 +320,10 @@ int bm_xysrb_update(double* d_x, double* d_Pb, const double* d_z, int n, void* s
 /* Constant-velocity box Kalman filters, batched (unit-testable form of what the ByteTrack
  * engine runs per track).  kind 0 = KalmanFilterXYAH (boxmot/motion/kalman_filters/aabb/
  * xyah_kf.py), 1 = KalmanFilterXYWH (xywh_kf.py); op 0 = initiate (base_kalman_filter.py:43-53;
- * reads d_z, writes mean/cov), 1 = predict (:62-77, multi_predict :111-127), 2 = update
- * (:129-155 with project :86-109; d_conf [n] is the NSA confidence, NULL = 0).
+ * reads d_z, writes mean/cov), 1 = predict (:62-77), 2 = update (:129-155 with project :86-109;
+ * d_conf [n] is the NSA confidence, NULL = 0), 3 = multi_predict (:111-127: the same update, but
+ * np.dot(np.dot(F, P), F^T) where predict's multi_dot evaluates F (P F^T)).  Bit-identical to the
+ * reference's numpy / scipy arithmetic (both off-diagonal entries of each block are carried).
  * d_mean [n][8], d_cov [n][8][8] dense, d_z [n][4].  Covariances must have the filter's own
  * sparsity (only (pos_i, vel_i) coupled), which initiate/predict/update preserve. */
 int bm_kf_cv8(int kind, int op, double* d_mean, double* d_cov, const double* d_z, const double* d_conf,

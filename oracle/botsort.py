@@ -21,7 +21,7 @@ from scipy.spatial.distance import cdist
 
 from oracle import assoc
 from oracle.bytetrack import LOST, NEW, REMOVED, TRACKED, _xywh_to_xyxy
-from oracle.kalman import cv8_initiate, cv8_predict, cv8_update
+from oracle.kalman import cv8_initiate, cv8_multi_predict, cv8_update
 
 
 class _STrack:
@@ -149,7 +149,8 @@ class BotSortOracle:
             m = t.mean.copy()
             if t.state != TRACKED:
                 m[6:8] = 0
-            t.mean, t.cov = cv8_predict("xywh", m, t.cov)
+            mm, cc = cv8_multi_predict("xywh", m[None], t.cov[None])      # STrack.multi_predict
+            t.mean, t.cov = mm[0], cc[0]
         warp = np.eye(2, 3) if warp is None else np.asarray(warp, dtype=float)
         self._gmc(pool, warp)
         self._gmc(unconfirmed, warp)

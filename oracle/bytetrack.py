@@ -22,7 +22,7 @@ Reference behaviours kept on purpose:
 import numpy as np
 
 from oracle import assoc
-from oracle.kalman import cv8_initiate, cv8_predict, cv8_update
+from oracle.kalman import cv8_initiate, cv8_multi_predict, cv8_update
 
 NEW, TRACKED, LOST, REMOVED = 0, 1, 2, 3
 
@@ -103,7 +103,8 @@ class ByteTrackOracle:
             m = t.mean.copy()
             if t.state != TRACKED:
                 m[7] = 0
-            t.mean, t.cov = cv8_predict("xyah", m, t.cov)
+            mm, cc = cv8_multi_predict("xyah", m[None], t.cov[None])      # STrack.multi_predict
+            t.mean, t.cov = mm[0], cc[0]
         d = assoc.iou_distance([t.xyxy for t in pool], [x.xyxy for x in high])
         d = assoc.fuse_score(d, [x.conf for x in high])
         m, u_trk, u_det = assoc.lap_thresholded(d, self.match_thresh)

@@ -177,10 +177,15 @@ def cv8_predict(kind, mean, cov):
 
 
 def cv8_multi_predict(kind, means, covs):
+    """base_kalman_filter.py:111-127: np.dot(np.dot(F, P), F^T) + Q -- NOT predict()'s multi_dot, which
+    evaluates F (P F^T): the two differ in the last bit once P is no longer bit-symmetric (update's
+    P - K (S K^T) is not)."""
     out_m = np.empty_like(means)
     out_c = np.empty_like(covs)
     for i in range(len(means)):
-        out_m[i], out_c[i] = cv8_predict(kind, means[i], covs[i])
+        q = np.diag(np.square(_stds(kind, means[i], "proc")))
+        out_m[i] = means[i] @ _MOTION.T
+        out_c[i] = np.dot(np.dot(_MOTION, covs[i]), _MOTION.T) + q
     return out_m, out_c
 
 

@@ -151,7 +151,9 @@ def test_config_shape_batch_properties_botsort_strongsort(tracker):
     dets, nd, embs = make_batch(NS, KO, FR, DC, emb_dim=E)
     dets = dets.astype(np.float32)
 
-    def run(dets, nd, embs):
+    states = {}
+
+    def run(dets, nd, embs, keep=()):
         eng = make(dets.shape[1])
         d_dets, d_nd = torch.as_tensor(np.ascontiguousarray(dets)).cuda(), torch.as_tensor(np.ascontiguousarray(nd)).cuda()
         rows = []
@@ -159,10 +161,12 @@ def test_config_shape_batch_properties_botsort_strongsort(tracker):
             out, nout = eng.step(d_dets[f], d_nd[f], torch.as_tensor(np.ascontiguousarray(embs[f])).cuda())
             rows.append((out.cpu().numpy(), nout.cpu().numpy()))
         eng.status()
+        for s in keep:
+            states[s] = eng.peek(s)
         eng.close()
         return rows
 
-    rows = run(dets, nd, embs)
+    rows = run(dets, nd, embs, keep=sample)
     oracles = {s: Oracle(**kw) for s in sample}
     for f in range(FR):
         out, nout = rows[f]
@@ -175,6 +179,13 @@ def test_config_shape_batch_properties_botsort_strongsort(tracker):
                 di = r[:, 7].astype(int)
                 assert len(set(di)) == len(di) and di.min() >= 0 and di.max() < nd[f, s]
                 assert len(set(r[:, 4])) == len(r) and r[:, 4].min() >= 1
+    # Kalman state of the sampled streams after the last frame: BIT-IDENTICAL to the oracle's numpy / scipy
+    # filter (csrc/kf_xyah.cuh carries both off-diagonal covariance entries and scipy's reciprocal solves)
+    for s in sample:
+        o = oracles[s]
+        trk = o.tracks if tracker == "strongsort" else o.active + o.lost
+        assert np.array_equal(states[s][0], np.array([t.mean for t in trk]))
+        assert np.array_equal(states[s][1], np.array([t.cov for t in trk]))
     pick = np.arange(NS)[::-5][:16]
     rows2 = run(dets[:, pick], nd[:, pick], embs[:, pick])
     for f in range(FR):

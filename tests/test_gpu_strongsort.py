@@ -82,8 +82,11 @@ def test_strongsort_engine_batched_streams_match_oracle():
                 otab = np.array([t.a for t in o.tracks])
                 otab[:, so.TS_MISSED] = tab[:, so.TS_MISSED]      # never read (a duplicated IoU row counts twice)
                 np.testing.assert_allclose(tab, otab, rtol=1e-9, atol=1e-9)
-                np.testing.assert_allclose(x, np.array([t.mean for t in o.tracks]), rtol=1e-9, atol=1e-9)
-                np.testing.assert_allclose(P, np.array([t.cov for t in o.tracks]), rtol=1e-8, atol=1e-9)
+                # with camera warps the state differs at the rounding level: camera_update's 3-term products go
+                # through a BLAS gemv whose FMA order is not reproduced (without warps the Kalman state is
+                # bit-identical: test_config_shape_batch_properties_botsort_strongsort)
+                np.testing.assert_allclose(x, np.array([t.mean for t in o.tracks]), rtol=1e-10, atol=1e-10)
+                np.testing.assert_allclose(P, np.array([t.cov for t in o.tracks]), rtol=1e-9, atol=1e-10)
                 assert np.array_equal(nb, [len(o.bank.get(t.id, [])) for t in o.tracks])
     c = eng.counters()
     assert c["track_updates"] == sum(o.n_updates for o in oracles)
@@ -132,6 +135,30 @@ def test_linear_sum_assignment_equals_scipy_including_ties():
             c = rng.uniform(0, 1, (nr, nc))
             c[c > 0.35] = 0.35 + 1e-5
         probs.append(c)
+    x = _lsa(probs)
+    for b, c in enumerate(probs):
+        rows, cols = linear_sum_assignment(c)
+        want = np.full(c.shape[0], -1)
+        want[rows] = cols
+        assert np.array_equal(x[b, : c.shape[0]], want), (b, c.shape)
+
+
+def test_linear_sum_assignment_equals_scipy_on_iou_stage_shaped_problems():
+    """The IoU stage's matrices: hundreds of candidate rows of which most are clamped constants, a few dozen
+    detection columns, and DUPLICATED candidate rows (tracker.py:257-259) -- which detection goes to the original
+    row and which to its duplicate is pure tie-breaking, and decides the order of a track's two updates."""
+    from scipy.optimize import linear_sum_assignment
+    rng = np.random.default_rng(1)
+    probs = []
+    for t in range(120):
+        nT, nD = int(rng.integers(50, 900)), int(rng.integers(2, 40))
+        c = np.full((nT, nD), 0.7 + 1e-5)
+        near = rng.choice(nT, size=min(nT, int(rng.integers(5, 60))), replace=False)
+        for p in near:
+            for d in rng.choice(nD, size=min(nD, int(rng.integers(1, 4))), replace=False):
+                c[p, d] = rng.uniform(0.1, 0.69)
+        dup = rng.choice(near, size=min(len(near), 10), replace=False)
+        probs.append(np.vstack([c, c[dup]]))
     x = _lsa(probs)
     for b, c in enumerate(probs):
         rows, cols = linear_sum_assignment(c)

@@ -233,8 +233,8 @@ def test_xysr_block_form_is_bit_identical():
 def test_cv8_kalman_kernels_match_reference_vectors(kind):
     """bm_kf_cv8 / bm_kf_cv8_gating (block-form XYAH / XYWH filters) against the reference's own
     KalmanFilterXYAH / XYWH outputs (tests/golden/ref_kf_cv8.npz): initiate, predict, update with
-    NSA confidence, gating distances (rows a1-a5).  Tolerance 1e-9 relative (the reference goes
-    through LAPACK/OpenBLAS; the block form differs at the rounding level only)."""
+    NSA confidence, multi_predict, gating distances (rows a1-a5).  BIT-IDENTICAL: the block form carries
+    both off-diagonal entries of each 2x2 block and reproduces scipy's reciprocal-of-the-diagonal solves."""
     import os
     from boxmot_b200 import _lib
     from conftest import GOLD
@@ -251,8 +251,8 @@ def test_cv8_kalman_kernels_match_reference_vectors(kind):
 
     def check():
         torch.cuda.synchronize()
-        np.testing.assert_allclose(d_mean.cpu().numpy(), means[step], rtol=1e-9, atol=1e-9)
-        np.testing.assert_allclose(d_cov.cpu().numpy(), covs[step], rtol=1e-9, atol=1e-12)
+        assert np.array_equal(d_mean.cpu().numpy(), means[step]), step      # bit for bit vs the reference's filter
+        assert np.array_equal(d_cov.cpu().numpy(), covs[step]), step
 
     check()
     for i in range(zs.shape[0]):
@@ -270,7 +270,12 @@ def test_cv8_kalman_kernels_match_reference_vectors(kind):
             _lib.check(L.bm_kf_cv8_gating(k, p(d_mean), p(d_cov), n, p(meas), meas.shape[0], op, gi, p(out), None),
                        "gating")
             torch.cuda.synchronize()
-            np.testing.assert_allclose(out.cpu().numpy(), z["%s_gate_%s_%d" % (kind, metric, op)], rtol=1e-8)
+            assert np.array_equal(out.cpu().numpy(), z["%s_gate_%s_%d" % (kind, metric, op)]), (metric, op)
+    # multi_predict of the final state (the reference's batched form sums P[i][i]'s four terms in another order)
+    _lib.check(L.bm_kf_cv8(k, 3, p(d_mean), p(d_cov), None, None, n, None), "multi_predict")
+    torch.cuda.synchronize()
+    assert np.array_equal(d_mean.cpu().numpy(), z[kind + "_mp_mean"])
+    assert np.array_equal(d_cov.cpu().numpy(), z[kind + "_mp_cov"])
 
 
 @pytest.mark.parametrize("shape", [(5, 3, 32), (128, 16, 64), (200, 77, 512), (300, 260, 96), (37, 130, 100)])
