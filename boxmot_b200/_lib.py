@@ -133,6 +133,8 @@ _SIGS = {
     "bm_strongsort_create": (c_int, [ctypes.POINTER(StrongsortConfig), c_int, c_int, c_int, c_int,
                                      ctypes.POINTER(c_void_p)]),
     "bm_strongsort_destroy": (c_int, [c_void_p]),
+    "bm_linear_sum_assignment_far_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_double,
+                                                   c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_linear_sum_assignment_batch": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                                c_void_p]),
     "bm_strongsort_reset": (c_int, [c_void_p, c_void_p]),

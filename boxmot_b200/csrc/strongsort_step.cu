@@ -410,6 +410,191 @@ __device__ int ss_min_cost_matching(const double* c, int ld, const int* rows, in
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The IoU stage's assignment (rows = a few dozen detections after scipy's transposition, columns = every
+// non-tentative track plus the duplicated ones, most of them "far": time_since_update > 1, i.e. the same
+// clamped constant for every detection) with the far columns handled IMPLICITLY.  Same result as
+// lsa_scipy_warp on the full matrix -- including which of two tied columns is taken -- because:
+//   * a far column is never scanned: its dual stays 0 and all far columns share one path cost, so it
+//     can only end a search as the sink, and scipy's tie rule (an unassigned column beats an assigned
+//     one, the LAST unassigned one in `remaining` order wins) makes an assigned far column lose against
+//     any unassigned one -- there always is one, #far >= #rows being a precondition;
+//   * `remaining` starts as C-1 .. 0 and only changes by "the last entry moves into the scanned
+//     column's place": the position of every column is C-1-j unless it is one of the few that moved in
+//     this search (kept in a small list), so the tie rule can be evaluated on the stored (near) columns
+//     plus ONE representative of the far class: the unassigned far column at the highest position.
+// Validated against scipy on random matrices of this shape (tests/test_gpu_strongsort.py).
+constexpr int SSF_NMAX = 352, SSF_RMAX = 128, SSF_MV = 32;
+constexpr int SSF_CMAX = 8192;                 // candidate columns (bit sets)
+struct FarWork {                               // carved from one per-warp shared-memory block
+    double *v, *spc, *u;                       // [N] [N] [R]
+    int *pos, *path, *row4col, *col4row, *srl, *scl, *mvc, *mvp;   // [N] [N] [N] [R] [R] [N] [MV] [MV]
+    unsigned *near_bits, *asg_bits;            // [CMAX / 32]
+};
+constexpr size_t SSF_BYTES = (size_t)(2 * SSF_NMAX + SSF_RMAX) * 8 + (size_t)(4 * SSF_NMAX + 2 * SSF_RMAX + 2 * SSF_MV) * 4 +
+                             2 * (SSF_CMAX / 32) * 4;
+__device__ __forceinline__ FarWork far_carve(unsigned char* b) {
+    FarWork w;
+    w.v = reinterpret_cast<double*>(b); w.spc = w.v + SSF_NMAX; w.u = w.spc + SSF_NMAX;
+    w.pos = reinterpret_cast<int*>(w.u + SSF_RMAX); w.path = w.pos + SSF_NMAX; w.row4col = w.path + SSF_NMAX;
+    w.scl = w.row4col + SSF_NMAX; w.col4row = w.scl + SSF_NMAX; w.srl = w.col4row + SSF_RMAX;
+    w.mvc = w.srl + SSF_RMAX; w.mvp = w.mvc + SSF_MV;
+    w.near_bits = reinterpret_cast<unsigned*>(w.mvp + SSF_MV); w.asg_bits = w.near_bits + SSF_CMAX / 32;
+    return w;
+}
+
+// cost(n, i): clamped cost of near column n (candidate index nearcol[n], ascending) and row i.
+// Returns 0 with w.row4col[n] = row of near column n or -1; 1 = needs the explicit solver (too many moves).
+template <typename CostFn>
+__device__ int lsa_far_warp(const CostFn& cost, const int* nearcol, int N, int C, int R, double cstar, const FarWork& w) {
+    const int lane = lane_id();
+    for (int k = lane; k < (C + 31) / 32; k += 32) { w.near_bits[k] = 0u; w.asg_bits[k] = 0u; }
+    __syncwarp();
+    for (int n = lane; n < N; n += 32) { atomicOr(&w.near_bits[nearcol[n] >> 5], 1u << (nearcol[n] & 31)); w.v[n] = 0.0; w.row4col[n] = -1; }
+    for (int i = lane; i < R; i += 32) { w.u[i] = 0.0; w.col4row[i] = -1; }
+    __syncwarp();
+    for (int cur = 0; cur < R; cur++) {
+        for (int n = lane; n < N; n += 32) { w.pos[n] = C - 1 - nearcol[n]; w.spc[n] = CUDART_INF; }
+        __syncwarp();
+        double min_val = 0.0, spcF = CUDART_INF;
+        int num = C, i = cur, nsr = 0, nsc = 0, nmv = 0, pathF = -1;
+        int sink_near = -1, sink_far = -1;
+        while (true) {
+            if (lane == 0) w.srl[nsr] = i;
+            nsr++;
+            const double ui = w.u[i];
+            double bv = CUDART_INF;
+            int bit = 0x7fffffff, bun = 0, bidx = -1;
+            for (int n = lane; n < N; n += 32) {
+                const int ps = w.pos[n];
+                if (ps < 0) continue;                                   // already scanned in this search
+                const double r = ((min_val + cost(n, i)) - ui) - w.v[n];
+                double sj = w.spc[n];
+                if (r < sj) { sj = r; w.spc[n] = r; w.path[n] = i; }
+                const int un = w.row4col[n] == -1;
+                bool take;
+                if (sj != bv) take = sj < bv;
+                else if (un != bun) take = un > bun;
+                else take = un ? (ps > bit) : (ps < bit);
+                if (take) { bv = sj; bit = ps; bun = un; bidx = n; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ov = shfl_xor_d(bv, o);
+                const int oit = __shfl_xor_sync(BM_FULL, bit, o), oun = __shfl_xor_sync(BM_FULL, bun, o);
+                const int oidx = __shfl_xor_sync(BM_FULL, bidx, o);
+                bool take;
+                if (oidx < 0) take = false;
+                else if (bidx < 0) take = true;
+                else if (ov != bv) take = ov < bv;
+                else if (oun != bun) take = oun > bun;
+                else take = oun ? (oit > bit) : (oit < bit);
+                if (take) { bv = ov; bit = oit; bun = oun; bidx = oidx; }
+            }
+            // the far class: one value, represented by its unassigned member at the highest position
+            const double rF = ((min_val + cstar) - ui) - 0.0;
+            if (rF < spcF) { spcF = rF; pathF = i; }
+            int pF = -1, cF = -1;
+            {
+                const int lo = C - num;                                  // unmoved columns still listed have j >= lo
+                int found = -1;
+                for (int wbase = lo >> 5; wbase < (C + 31) / 32 && found < 0; wbase += 32) {
+                    const int wi_ = wbase + lane;
+                    unsigned freeb = 0u;
+                    if (wi_ < (C + 31) / 32) {
+                        freeb = ~(w.near_bits[wi_] | w.asg_bits[wi_]);
+                        if (wi_ == (lo >> 5)) freeb &= ~0u << (lo & 31);
+                        if (wi_ == (C >> 5)) freeb &= (C & 31) ? ((1u << (C & 31)) - 1u) : 0u;
+                    }
+                    const unsigned any = __ballot_sync(BM_FULL, freeb != 0u);
+                    if (any) {
+                        const int l0 = __ffs(any) - 1;
+                        const unsigned fb = __shfl_sync(BM_FULL, freeb, l0);
+                        found = ((wbase + l0) << 5) + (__ffs(fb) - 1);
+                    }
+                }
+                if (found >= 0) { pF = C - 1 - found; cF = found; }
+                for (int k = 0; k < nmv; k++) {                          // moved far columns
+                    const int c = w.mvc[k];
+                    if (!((w.near_bits[c >> 5] >> (c & 31)) & 1u) && !((w.asg_bits[c >> 5] >> (c & 31)) & 1u) && w.mvp[k] > pF) {
+                        pF = w.mvp[k]; cF = c;
+                    }
+                }
+            }
+            bool far_wins;
+            if (bidx < 0) far_wins = true;
+            else if (spcF != bv) far_wins = spcF < bv;
+            else if (!bun) far_wins = true;                              // unassigned beats assigned
+            else far_wins = pF > bit;
+            if (far_wins) { min_val = spcF; sink_far = cF; break; }
+            min_val = bv;
+            const int n = bidx;
+            // the scanned column leaves `remaining`: the entry at the last position moves into its place
+            const int h = bit, L = num - 1;
+            __syncwarp();
+            if (h != L) {
+                int colL = C - 1 - L, k_at = -1;
+                for (int k = 0; k < nmv; k++) if (w.mvp[k] == L) { colL = w.mvc[k]; k_at = k; }
+                if (k_at < 0) {
+                    if (nmv >= SSF_MV) return 1;
+                    k_at = nmv++;
+                    if (lane == 0) w.mvc[k_at] = colL;
+                }
+                if (lane == 0) w.mvp[k_at] = h;
+                if ((w.near_bits[colL >> 5] >> (colL & 31)) & 1u) {       // a near column moved: binary search its index
+                    int a = 0, b = N - 1;
+                    while (a < b) { const int m = (a + b) >> 1; if (nearcol[m] < colL) a = m + 1; else b = m; }
+                    if (lane == 0) w.pos[a] = h;
+                }
+            }
+            __syncwarp();
+            {   // forget a list entry of the scanned column itself
+                const int cn = nearcol[n];
+                int k_rm = -1;
+                for (int k = 0; k < nmv; k++) if (w.mvc[k] == cn) k_rm = k;
+                if (k_rm >= 0) {
+                    if (lane == 0) { w.mvc[k_rm] = w.mvc[nmv - 1]; w.mvp[k_rm] = w.mvp[nmv - 1]; }
+                    nmv--;
+                }
+            }
+            num--;
+            if (lane == 0) { w.pos[n] = -1; w.scl[nsc] = n; }
+            nsc++;
+            const int rj = w.row4col[n];
+            __syncwarp();
+            if (rj == -1) { sink_near = n; break; }
+            i = rj;
+        }
+        __syncwarp();
+        // dual variables
+        for (int k = lane; k < nsr; k += 32) {
+            const int r = w.srl[k];
+            if (r == cur) w.u[r] += min_val;
+            else w.u[r] += min_val - w.spc[w.col4row[r]];
+        }
+        for (int k = lane; k < nsc; k += 32) { const int n = w.scl[k]; w.v[n] -= min_val - w.spc[n]; }
+        __syncwarp();
+        if (lane == 0) {                                                 // augment
+            int r, j;
+            if (sink_far >= 0) {
+                w.asg_bits[sink_far >> 5] |= 1u << (sink_far & 31);
+                r = pathF;
+                j = w.col4row[r]; w.col4row[r] = -2;
+            } else {
+                r = w.path[sink_near]; w.row4col[sink_near] = r;
+                j = w.col4row[r]; w.col4row[r] = sink_near;
+            }
+            while (r != cur) {
+                const int n = j;
+                r = w.path[n]; w.row4col[n] = r;
+                j = w.col4row[r]; w.col4row[r] = n;
+            }
+        }
+        __syncwarp();
+    }
+    return 0;
+}
+
 // Unit-testable form: one warp per problem on stored matrices, scipy's own transposition rule.
 struct LsaDense {
     const double* c; int ld; bool tr;
@@ -431,13 +616,54 @@ lsa_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, in
     for (int r = lane; r < nr; r += 32) x[r] = tr ? w.row4col[r] : w.col4row[r];
 }
 
+// Unit-testable form of lsa_far_warp: rows flagged in `far_rows` are constant (cstar) for every column.
+struct FarDense {
+    const double* c; int ld; const int* nearcol;
+    __device__ __forceinline__ double operator()(int n, int i) const { return c[(size_t)nearcol[n] * ld + i]; }
+};
+__global__ void __launch_bounds__(64)
+lsa_far_batch_kernel(const double* __restrict__ cost, int n_problems, int nr_max, int nc_max, const int* __restrict__ nr_,
+                     const int* __restrict__ nc_, const int* __restrict__ far_rows, double cstar, int* __restrict__ x_out,
+                     int* __restrict__ used_far, double* wd, int* wi, int M) {
+    __shared__ __align__(16) unsigned char s_far[2][SSF_BYTES];
+    const int b = blockIdx.x * 2 + (threadIdx.x >> 5), lane = lane_id();
+    if (b >= n_problems) return;
+    const int nr = nr_[b], nc = nc_[b];
+    int* x = x_out + (size_t)b * nr_max;
+    for (int i = lane; i < nr_max; i += 32) x[i] = -1;
+    if (nr <= 0 || nc <= 0) return;
+    const int* fr = far_rows + (size_t)b * nr_max;
+    int* nearcol = wi + (size_t)b * 6 * M;                      // scratch: list of near rows
+    const int N = warp_compact(nr, nearcol, 0, [&](int r) { return fr[r] == 0; }, [&](int r) { return r; });
+    const bool ok = nc < nr && N <= SSF_NMAX && nc <= SSF_RMAX && nr <= SSF_CMAX && nr - N >= nc;
+    int fell_back = 1;
+    if (ok) {
+        FarWork w = far_carve(s_far[threadIdx.x >> 5]);
+        FarDense cf{cost + (size_t)b * nr_max * nc_max, nc_max, nearcol};
+        if (lsa_far_warp(cf, nearcol, N, nr, nc, cstar, w) == 0) {
+            for (int n = lane; n < N; n += 32) x[nearcol[n]] = w.row4col[n];
+            fell_back = 0;
+        }
+        __syncwarp();
+    }
+    if (fell_back) {
+        LsaWork w = lsa_carve(wd + (size_t)b * 3 * M, wi + (size_t)b * 6 * M, M);
+        const bool tr = nc < nr;
+        LsaDense cf{cost + (size_t)b * nr_max * nc_max, nc_max, tr};
+        if (lsa_scipy_warp(cf, tr ? nc : nr, tr ? nr : nc, w)) return;
+        for (int r = lane; r < nr; r += 32) x[r] = tr ? w.row4col[r] : w.col4row[r];
+    }
+    if (lane == 0 && used_far) used_far[b] = fell_back ? 0 : 1;
+}
+
 // K4: Tracker._enhanced_match (tracker.py:183-281), one warp per stream
-constexpr int SS_MATCH_WPB = 4;
+constexpr int SS_MATCH_WPB = 2;
 constexpr int SS_LSA_SMEM_M = 160;        // assignment problems with both sides <= this run out of shared memory
 __global__ void __launch_bounds__(SS_MATCH_WPB * 32)
 ss_match_kernel(SsState st, SsParams pr) {
-    __shared__ double s_lsa_d[SS_MATCH_WPB][3 * SS_LSA_SMEM_M];
-    __shared__ int s_lsa_i[SS_MATCH_WPB][6 * SS_LSA_SMEM_M];
+    // per warp: the explicit solver's work area (3 M doubles + 6 M ints) or the implicit-far solver's (never both)
+    static_assert(SSF_BYTES >= (size_t)SS_LSA_SMEM_M * (3 * 8 + 6 * 4), "shared work area");
+    __shared__ __align__(16) unsigned char s_lsa[SS_MATCH_WPB][SSF_BYTES];
     const int s = blockIdx.x * SS_MATCH_WPB + (threadIdx.x >> 5), lane = lane_id();
     if (s >= st.S) return;
     SsView v(st, s);
@@ -456,14 +682,28 @@ ss_match_kernel(SsState st, SsParams pr) {
     int* dmatched = wi;               wi += Dc;
     int* agecnt = wi;                 wi += pr.max_age + 2;
     const LsaWork w_glob = lsa_carve(st.wkd + (size_t)s * 3 * M, wi, M);
-    const LsaWork w_smem = lsa_carve(s_lsa_d[threadIdx.x >> 5], s_lsa_i[threadIdx.x >> 5], SS_LSA_SMEM_M);
+    unsigned char* s_my = s_lsa[threadIdx.x >> 5];
+    const LsaWork w_smem = lsa_carve(reinterpret_cast<double*>(s_my),
+                                     reinterpret_cast<int*>(s_my + (size_t)SS_LSA_SMEM_M * 3 * 8), SS_LSA_SMEM_M);
     int* ulist = st.ulist + (size_t)s * Dc;
     int* unm = st.unm + (size_t)s * Dc;
     double* cost = v.cost();
 
-    for (int p = lane; p < nT; p += 32) tmatched[p] = 0;
+    // per list position, packed once: time_since_update (16 bits) | state << 16 | feasibility bits << 20 |
+    // matched-in-stage-1/2 << 24 -- the passes below read this one int instead of chasing order -> table
+    int* pinfo = tmatched;
+    for (int p = lane; p < nT; p += 32) {
+        const int t = v.order()[p];
+        const double* a = v.tab(t);
+        const int tsu = min((int)a[SS_TSU], 0xffff);
+        pinfo[p] = tsu | ((int)a[ST_STATE] << 16) | ((v.tint(t)[TI_FEAS] & 3) << 20);
+    }
     for (int k = lane; k < n; k += 32) dmatched[k] = 0;
     __syncwarp();
+#define PI_TSU(x) ((x) & 0xffff)
+#define PI_STATE(x) (((x) >> 16) & 3)
+#define PI_FEAS(x) (((x) >> 20) & 3)
+#define PI_MATCHED(x) (((x) >> 24) & 1)
     if (n == 0) {                                   // tracker.update([]): nothing matches, the IoU stage is skipped
         if (lane == 0) { hdr[SH_NUNM] = 0; hdr[SH_STAGE3] = 0; hdr[SH_NUPD] = 0; }
         return;
@@ -490,24 +730,30 @@ ss_match_kernel(SsState st, SsParams pr) {
         for (int a = lane; a <= pr.max_age + 1; a += 32) agecnt[a] = 0;
         __syncwarp();
         for (int p = lane; p < nT; p += 32) {
-            const double* a = v.tab(v.order()[p]);
-            const int age = (int)a[SS_TSU];
-            if (a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && age <= pr.max_age) atomicAdd(&agecnt[age], 1);
+            const int pi = pinfo[p], age = PI_TSU(pi);
+            if (PI_STATE(pi) == ST_CONFIRMED_STATE && !PI_MATCHED(pi) && age <= pr.max_age) atomicAdd(&agecnt[age], 1);
         }
         __syncwarp();
-        if (lane == 0) {                            // exclusive prefix; agecnt[a] becomes the write cursor of age a
+        {                                           // exclusive prefix (warp scan); agecnt[a] becomes the write cursor of age a
             int run = 0;
-            for (int a = 0; a <= pr.max_age; a++) { const int c = agecnt[a]; agecnt[a] = run; run += c; }
-            agecnt[pr.max_age + 1] = run;
+            for (int base = 0; base <= pr.max_age; base += 32) {
+                const int a = base + lane;
+                const int c = a <= pr.max_age ? agecnt[a] : 0;
+                int inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(BM_FULL, inc, o); if (lane >= o) inc += t; }
+                if (a <= pr.max_age) agecnt[a] = run + inc - c;
+                run += __shfl_sync(BM_FULL, inc, 31);
+            }
+            if (lane == 0) agecnt[pr.max_age + 1] = run;
         }
         __syncwarp();
         for (int base = 0; base < nT; base += 32) {
             const int p = base + lane;
             int age = -1;
             if (p < nT) {
-                const double* a = v.tab(v.order()[p]);
-                const int g = (int)a[SS_TSU];
-                if (a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && g <= pr.max_age) age = g;
+                const int pi = pinfo[p], g = PI_TSU(pi);
+                if (PI_STATE(pi) == ST_CONFIRMED_STATE && !PI_MATCHED(pi) && g <= pr.max_age) age = g;
             }
             const unsigned peers = __match_any_sync(BM_FULL, age);
             if (age >= 0) {
@@ -528,7 +774,7 @@ ss_match_kernel(SsState st, SsParams pr) {
             // equal (clamped) entries: scipy assigns row i to column i (transposed: column j to row j), every
             // pair is rejected, and the detections are handed on as [m, nc) followed by [0, m) when m < nc.
             int feas = 0;
-            for (int i = lane; i < m; i += 32) feas |= v.tint(v.order()[byage[start + i]])[TI_FEAS] & (1 << stage);
+            for (int i = lane; i < m; i += 32) feas |= PI_FEAS(pinfo[byage[start + i]]) & (1 << stage);
             feas = __any_sync(BM_FULL, feas != 0);
             if (!feas) {
                 if (m < nc) {
@@ -559,7 +805,7 @@ ss_match_kernel(SsState st, SsParams pr) {
             nlsa++;
             if (lane == 0)
                 for (int r = 0; r < m; r++)
-                    if (mcol[r] >= 0) { tmatched[lvl[r]] = 1; dmatched[mcol[r]] = 1; record(lvl[r], mcol[r]); }
+                    if (mcol[r] >= 0) { pinfo[lvl[r]] |= 1 << 24; dmatched[mcol[r]] = 1; record(lvl[r], mcol[r]); }
             __syncwarp();
             start = end;
         }
@@ -568,11 +814,10 @@ ss_match_kernel(SsState st, SsParams pr) {
     }
     // ---- stage 3: IoU matching.  Candidates = every non-tentative track (matched or not), then
     // AGAIN the unmatched ones with time_since_update == 1 (tracker.py:257-259: the list is a concatenation)
-    int nr3 = warp_compact(nT, rows3, 0, [&](int p) { return v.tab(v.order()[p])[ST_STATE] != (double)ST_TENTATIVE; },
-                           [&](int p) { return p; });
+    int nr3 = warp_compact(nT, rows3, 0, [&](int p) { return PI_STATE(pinfo[p]) != ST_TENTATIVE; }, [&](int p) { return p; });
     nr3 = warp_compact(nT, rows3, nr3, [&](int p) {
-        const double* a = v.tab(v.order()[p]);
-        return a[ST_STATE] == (double)ST_CONFIRMED_STATE && !tmatched[p] && a[SS_TSU] == 1.0;
+        const int pi = pinfo[p];
+        return PI_STATE(pi) == ST_CONFIRMED_STATE && !PI_MATCHED(pi) && PI_TSU(pi) == 1;
     }, [&](int p) { return p; });
     int nc3 = warp_compact(n, cols, 0, [&](int k) { return !dmatched[k] && !(v.dtab(k)[DT_CONF] < pr.conf_lo); },
                            [&](int k) { return k; });
@@ -581,27 +826,60 @@ ss_match_kernel(SsState st, SsParams pr) {
         // Rows of tracks with time_since_update > 1 are INFTY_COST times positive factors: above any
         // threshold, so the clamped entry is the same constant whatever the factors are.
         int nnear = warp_compact(nT, tmp, 0, [&](int p) {
-            const double* a = v.tab(v.order()[p]);
-            return a[ST_STATE] != (double)ST_TENTATIVE && !(a[SS_TSU] > 1.0);
+            const int pi = pinfo[p];
+            return PI_STATE(pi) != ST_TENTATIVE && PI_TSU(pi) <= 1;
         }, [&](int p) { return p; });
-        for (int e = lane; e < nnear * nc3; e += 32) {
-            const int p = tmp[e / nc3], k = cols[e % nc3];
+        for (int e = lane; e < nnear; e += 32) {          // a lane per near track: its operands stay in registers
+            const int p = tmp[e];
             const int t = v.order()[p];
             const double* a = v.tab(t);
-            const double* d = v.dtab(k);
-            cost[(size_t)p * Dc + k] = ss_enhance_entry(ss_iou_entry(v.mean(t), d + DT_TLWH), a, d[DT_QUALITY], d[DT_CONF],
-                                                        d[DT_CLS]);
+            const double* m = v.mean(t);
+            const double m4[4] = {m[0], m[1], m[2], m[3]};
+            for (int j = 0; j < nc3; j++) {
+                const int k = cols[j];
+                const double* d = v.dtab(k);
+                cost[(size_t)p * Dc + k] = ss_enhance_entry(ss_iou_entry(m4, d + DT_TLWH), a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
+            }
         }
-        for (int p = lane; p < nT; p += 32) lvl[p] = v.tab(v.order()[p])[SS_TSU] > 1.0 ? 1 : 0;
+        for (int p = lane; p < nT; p += 32) lvl[p] = PI_TSU(pinfo[p]) > 1 ? 1 : 0;
         __syncwarp();
-        bad |= ss_min_cost_matching(cost, Dc, rows3, nr3, cols, nc3, pr.max_iou_dist,
-                                    (nr3 <= SS_LSA_SMEM_M && nc3 <= SS_LSA_SMEM_M) ? w_smem : w_glob, mcol, tmp, lvl);
+        // most candidate rows are far (time_since_update > 1: one constant for every detection): solve with the
+        // far columns implicit when the shape allows it, else on the full matrix -- same result either way
+        int* nearcol = tmp;                                    // candidate indices of the near rows, ascending
+        int* nearpos = byage;                                  // their list positions (the age groups are done with)
+        const int nN = warp_compact(nr3, nearcol, 0, [&](int r) { return lvl[rows3[r]] == 0; }, [&](int r) { return r; });
+        bool solved = false;
+        if (nc3 < nr3 && nN <= SSF_NMAX && nc3 <= SSF_RMAX && nr3 <= SSF_CMAX && nr3 - nN >= nc3) {
+            for (int k = lane; k < nN; k += 32) nearpos[k] = rows3[nearcol[k]];
+            for (int r = lane; r < nr3; r += 32) mcol[r] = -1;
+            __syncwarp();
+            const double maxd = pr.max_iou_dist;
+            auto cf = [&](int nidx, int i) {
+                const double x = cost[(size_t)nearpos[nidx] * Dc + cols[i]];
+                return x > maxd ? maxd + 1e-5 : x;
+            };
+            const FarWork fw = far_carve(s_my);
+            if (lsa_far_warp(cf, nearcol, nN, nr3, nc3, maxd + 1e-5, fw) == 0) {
+                for (int k = lane; k < nN; k += 32) {
+                    const int i = fw.row4col[k];
+                    mcol[nearcol[k]] = (i >= 0 && !(cf(k, i) > maxd)) ? cols[i] : -1;
+                }
+                solved = true;
+            }
+            __syncwarp();
+        }
+        if (!solved)
+            bad |= ss_min_cost_matching(cost, Dc, rows3, nr3, cols, nc3, pr.max_iou_dist,
+                                        (nr3 <= SS_LSA_SMEM_M && nc3 <= SS_LSA_SMEM_M) ? w_smem : w_glob, mcol, tmp, lvl);
         nlsa++;
+        for (int r = lane; r < nr3; r += 32)
+            if (mcol[r] < 0) v.tint(v.order()[rows3[r]])[TI_MISS] = 1;        // unmatched_tracks_3 -> mark_missed
+        const int nm3 = warp_compact(nr3, tmp, 0, [&](int r) { return mcol[r] >= 0; }, [&](int r) { return r; });
         if (lane == 0) {
-            for (int r = 0; r < nr3; r++) {
-                const int p = rows3[r];
-                if (mcol[r] >= 0) { dmatched[mcol[r]] = 1; record(p, mcol[r]); }
-                else v.tint(v.order()[p])[TI_MISS] = 1;        // unmatched_tracks_3 -> mark_missed
+            for (int q = 0; q < nm3; q++) {                                      // matches in row order
+                const int r = tmp[q];
+                dmatched[mcol[r]] = 1;
+                record(rows3[r], mcol[r]);
             }
             hdr[SH_STAGE3] = 1;
         }
@@ -794,7 +1072,7 @@ __device__ void ss_track_release(const SsView& v, int t) {       // one thread
 }
 
 // K6: the rest of Tracker.update (tracker.py:137-181) and StrongSort._format_outputs
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, double* __restrict__ out,
                    int* __restrict__ nout, int out_rows) {
     const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
@@ -1161,6 +1439,21 @@ int bm_linear_sum_assignment_batch(const double* d_cost, int n_problems, int nr_
     return 0;
 }
 
+int bm_linear_sum_assignment_far_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                                       const int* d_nc, const int* d_far_rows, double cstar, int* d_x, int* d_used_far,
+                                       void* d_work, void* stream) {
+    if (n_problems <= 0) return 0;
+    if (!d_cost || !d_nr || !d_nc || !d_far_rows || !d_x || !d_work || nr_max <= 0 || nc_max <= 0)
+        return ss_fail(-1, "bm_linear_sum_assignment_far_batch: bad argument");
+    const int M = nr_max > nc_max ? nr_max : nc_max;
+    double* wd = static_cast<double*>(d_work);
+    int* wi = reinterpret_cast<int*>(wd + (size_t)n_problems * 3 * M);
+    bm::lsa_far_batch_kernel<<<(n_problems + 1) / 2, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_cost, n_problems, nr_max, nc_max, d_nr, d_nc, d_far_rows, cstar, d_x, d_used_far, wd, wi, M);
+    SS_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int bm_strongsort_destroy(void* handle) {
     SsEngine* e = static_cast<SsEngine*>(handle);
     if (!e) return 0;
@@ -1199,7 +1492,7 @@ int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, co
     if (tm) cudaEventRecord(e->ev[4], s);
     bm::ss_update_kernel<<<dim3((st.Dcap + 3) / 4, st.S), 128, 0, s>>>(st, pr, d_embs);
     if (tm) cudaEventRecord(e->ev[5], s);
-    bm::ss_finalize_kernel<<<st.S, 256, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
+    bm::ss_finalize_kernel<<<st.S, 512, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
     if (tm) { cudaEventRecord(e->ev[6], s); e->timed = true; }
     SS_CUDA(cudaGetLastError());
     return 0;

@@ -227,6 +227,15 @@ int bm_strongsort_destroy(void* handle);
  * d_work: caller-owned scratch of at least B * 48 * max(nr_max, nc_max) bytes. */
 int bm_linear_sum_assignment_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
                                    const int* d_nc, int* d_x, void* d_work, void* stream);
+/* The same assignment for the shape of StrongSORT's IoU stage (sort/tracker.py:257-275): many rows, few columns,
+ * and most rows "far" -- d_far_rows [B][nr_max] != 0 promises that the row equals `cstar` in every column (tracks
+ * with time_since_update > 1 after the clamp of min_cost_matching).  The far rows are then handled implicitly
+ * (never touched by the augmenting-path sweeps) with the SAME result as the full emulation, scipy's tie-breaking
+ * included; problems outside the fast path's limits are solved on the full matrix.  d_used_far [B] (may be NULL)
+ * reports which path ran.  d_work as bm_linear_sum_assignment_batch. */
+int bm_linear_sum_assignment_far_batch(const double* d_cost, int n_problems, int nr_max, int nc_max, const int* d_nr,
+                                       const int* d_nc, const int* d_far_rows, double cstar, int* d_x, int* d_used_far,
+                                       void* d_work, void* stream);
 int bm_strongsort_reset(void* handle, void* stream);
 /* One frame for all streams; buffers as bm_botsort_step, out_rows = det_cap.  Error bits (see
  * bm_strongsort_counters): 1 track_cap, 2 det_cap, 8 pool_cap exceeded, 16 assignment guard. */

@@ -165,3 +165,55 @@ def test_linear_sum_assignment_equals_scipy_on_iou_stage_shaped_problems():
         want = np.full(c.shape[0], -1)
         want[rows] = cols
         assert np.array_equal(x[b, : c.shape[0]], want), (b, c.shape)
+
+
+def test_iou_stage_assignment_with_implicit_far_rows_equals_scipy():
+    """bm_linear_sum_assignment_far_batch: the IoU stage's fast path (far rows = one constant, never swept)
+    must give scipy's assignment of every NEAR row on the full matrix -- duplicated rows, exact ties, near rows
+    used as sinks of infeasible detections and long displacement chains included."""
+    from scipy.optimize import linear_sum_assignment
+    from boxmot_b200 import _lib
+    rng = np.random.default_rng(5)
+    cstar = 0.7 + 1e-5
+    probs, fars = [], []
+    for t in range(300):
+        nT, nD = int(rng.integers(80, 700)), int(rng.integers(3, 60))
+        c = np.full((nT, nD), cstar)
+        near = np.sort(rng.choice(nT, size=int(rng.integers(5, min(nT - nD, 90))), replace=False))
+        dens = int(rng.choice([1, 3, 8, 20]))
+        for p in near:
+            k = int(rng.integers(0, dens + 1))
+            for d in rng.choice(nD, size=min(nD, k), replace=False):
+                c[p, d] = rng.choice([rng.uniform(0.1, 0.69), 0.25, 0.5])          # exact ties too
+        dup = np.sort(rng.choice(near, size=min(len(near), int(rng.integers(0, 30))), replace=False))
+        full = np.vstack([c, c[dup]])
+        far = np.ones(len(full), np.int32)
+        far[near] = 0
+        far[nT:] = 0
+        probs.append(full)
+        fars.append(far)
+    B = len(probs)
+    nr_max, nc_max = max(c.shape[0] for c in probs), max(c.shape[1] for c in probs)
+    buf = np.zeros((B, nr_max, nc_max))
+    fb = np.ones((B, nr_max), np.int32)
+    for b, c in enumerate(probs):
+        buf[b, : c.shape[0], : c.shape[1]] = c
+        fb[b, : c.shape[0]] = fars[b]
+    d_c, d_f = torch.as_tensor(buf).cuda(), torch.as_tensor(fb).cuda()
+    d_nr = torch.as_tensor(np.array([c.shape[0] for c in probs], np.int32)).cuda()
+    d_nc = torch.as_tensor(np.array([c.shape[1] for c in probs], np.int32)).cuda()
+    d_x = torch.full((B, nr_max), -7, dtype=torch.int32, device="cuda")
+    d_u = torch.zeros((B,), dtype=torch.int32, device="cuda")
+    work = torch.zeros((B * 48 * max(nr_max, nc_max) + 64,), dtype=torch.uint8, device="cuda")
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.lib().bm_linear_sum_assignment_far_batch(p(d_c), B, nr_max, nc_max, p(d_nr), p(d_nc), p(d_f), cstar,
+                                                             p(d_x), p(d_u), p(work), None), "lsa far")
+    torch.cuda.synchronize()
+    x, used = d_x.cpu().numpy(), d_u.cpu().numpy()
+    assert used.sum() > 0.8 * B                      # the fast path really ran
+    for b, c in enumerate(probs):
+        rows, cols = linear_sum_assignment(c)
+        want = np.full(c.shape[0], -1)
+        want[rows] = cols
+        near = fars[b] == 0
+        assert np.array_equal(x[b, : c.shape[0]][near], want[near]), (b, c.shape, int(used[b]))
