@@ -986,6 +986,17 @@ ss_update_kernel(SsState st, SsParams pr, const float* __restrict__ embs) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Index of `slot` in the target's distinct-slot list, or -1; all lanes converged, same result on all.
+__device__ __forceinline__ int ss_dist_find(const int* ds, int nd, int slot) {
+    const int lane = lane_id();
+    for (int base = 0; base < nd; base += 32) {
+        const int i = base + lane;
+        const unsigned b = __ballot_sync(BM_FULL, i < nd && ds[i] == slot);
+        if (b) return base + __ffs(b) - 1;
+    }
+    return -1;
+}
+
 // Sample list of one target (NearestNeighborDistanceMetric.samples[target]) as slot references.
 // Removes the worst entry = lowest quality, newest (largest seq); all lanes converged.
 __device__ void ss_bank_evict(const SsView& v, int t) {
@@ -1006,19 +1017,19 @@ __device__ void ss_bank_evict(const SsView& v, int t) {
         const int os = __shfl_xor_sync(BM_FULL, wseq, o), oi = __shfl_xor_sync(BM_FULL, wi, o);
         if (oq < wq || (oq == wq && os > wseq)) { wq = oq; wseq = os; wi = oi; }
     }
-    if (lane == 0) {
+    {
         const int slot = bs[wi];
-        bs[wi] = bs[n - 1]; bq[wi] = bq[n - 1];
-        ti[TI_NBANK] = n - 1;
         int* ds = v.dslot(t);
         int* dc = v.dcnt(t);
         const int nd = ti[TI_NDIST];
-        for (int i = 0; i < nd; i++)
-            if (ds[i] == slot) {
-                if (--dc[i] == 0) { ds[i] = ds[nd - 1]; dc[i] = dc[nd - 1]; ti[TI_NDIST] = nd - 1; }
-                break;
-            }
-        if (--v.pbank()[slot] == 0 && v.pring()[slot] == 0) ss_pool_release(v, slot);
+        const int di = ss_dist_find(ds, nd, slot);
+        __syncwarp();
+        if (lane == 0) {
+            bs[wi] = bs[n - 1]; bq[wi] = bq[n - 1];
+            ti[TI_NBANK] = n - 1;
+            if (di >= 0 && --dc[di] == 0) { ds[di] = ds[nd - 1]; dc[di] = dc[nd - 1]; ti[TI_NDIST] = nd - 1; }
+            if (--v.pbank()[slot] == 0 && v.pring()[slot] == 0) ss_pool_release(v, slot);
+        }
     }
     __syncwarp();
     // new minimum quality
@@ -1037,6 +1048,11 @@ __device__ void ss_bank_append(const SsView& v, const SsParams& pr, int t, int s
     const int n = ti[TI_NBANK];
     if (n >= pr.budget && !(q > v.bminq(t))) return;            // it would be the entry that is dropped again
     if (n >= pr.budget) ss_bank_evict(v, t);
+    int* ds = v.dslot(t);
+    int* dc = v.dcnt(t);
+    const int nd = ti[TI_NDIST];
+    const int di = ss_dist_find(ds, nd, slot);
+    __syncwarp();
     if (lane == 0) {
         const int m = ti[TI_NBANK];
         v.bslot(t)[m] = slot;
@@ -1044,31 +1060,65 @@ __device__ void ss_bank_append(const SsView& v, const SsParams& pr, int t, int s
         ti[TI_NBANK] = m + 1;
         v.bminq(t) = m == 0 ? q : fmin(v.bminq(t), q);
         v.pbank()[slot] += 1;
-        int* ds = v.dslot(t);
-        int* dc = v.dcnt(t);
-        const int nd = ti[TI_NDIST];
-        int i = 0;
-        for (; i < nd; i++) if (ds[i] == slot) { dc[i]++; break; }
-        if (i == nd) { ds[nd] = slot; dc[nd] = 1; ti[TI_NDIST] = nd + 1; }
+        if (di >= 0) dc[di]++;
+        else { ds[nd] = slot; dc[nd] = 1; ti[TI_NDIST] = nd + 1; }
     }
     __syncwarp();
 }
 
-// Everything a track holds goes back to the pool (the track left the lost buffer or never entered it)
-__device__ void ss_track_release(const SsView& v, int t) {       // one thread
+// Everything a track holds goes back to the pool (the track left the lost buffer or never entered it); one
+// warp, lanes over the ring / sample-list entries (several entries may reference one slot: atomic counts).
+__device__ void ss_track_release_warp(const SsView& v, int t) {
+    const int lane = lane_id();
     int* ti = v.tint(t);
-    for (int i = 0; i < ti[TI_NRING]; i++) {
+    const int nr = ti[TI_NRING], nb = ti[TI_NBANK];
+    for (int i = lane; i < nr; i += 32) {
         const int p = v.ring(t)[i];
         v.pring()[p] = 0;
-        if (v.pbank()[p] == 0) ss_pool_release(v, p);
     }
-    for (int i = 0; i < ti[TI_NBANK]; i++) {
+    __syncwarp();
+    for (int i = lane; i < nb; i += 32) {
         const int p = v.bslot(t)[i];
-        if (--v.pbank()[p] == 0 && v.pring()[p] == 0) ss_pool_release(v, p);
+        if (atomicSub(&v.pbank()[p], 1) == 1 && v.pring()[p] == 0) ss_pool_release(v, p);
     }
-    ti[TI_NRING] = 0; ti[TI_NBANK] = 0; ti[TI_NDIST] = 0;
-    int* hdr = v.hdr();
-    v.st.tfree[(size_t)v.s * v.st.Tcap + hdr[SH_NTFREE]++] = t;
+    __syncwarp();
+    for (int i = lane; i < nr; i += 32) {          // ring features no sample list references (any more)
+        const int p = v.ring(t)[i];
+        if (v.pbank()[p] == 0) {
+            // a slot referenced by the list was released above when its count reached 0; one that never was is released here
+            bool in_bank = false;
+            for (int k = 0; k < nb && !in_bank; k++) in_bank = v.bslot(t)[k] == p;
+            if (!in_bank) ss_pool_release(v, p);
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        ti[TI_NRING] = 0; ti[TI_NBANK] = 0; ti[TI_NDIST] = 0;
+        const int k = atomicAdd(&v.hdr()[SH_NTFREE], 1);
+        v.st.tfree[(size_t)v.s * v.st.Tcap + k] = t;
+    }
+    __syncwarp();
+}
+
+// Stable compaction by the whole CTA: calls emit(i, rank) for every i in [0, n) with pred(i), rank = number of
+// earlier i with pred.  Returns the total on all threads.  ws: shared int[33].
+template <typename Pred, typename Emit>
+__device__ int block_compact(int n, int* ws, Pred pred, Emit emit) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
+    int base_total = 0;
+    for (int base = 0; base < n; base += blockDim.x) {
+        const int i = base + tid;
+        const bool ok = i < n && pred(i);
+        const unsigned b = __ballot_sync(BM_FULL, ok);
+        __syncthreads();
+        if (lane == 0) ws[wid] = __popc(b);
+        __syncthreads();
+        int before = 0, chunk = 0;
+        for (int w = 0; w < nwarp; w++) { const int c = ws[w]; if (w < wid) before += c; chunk += c; }
+        if (ok) emit(i, base_total + before + __popc(b & ((1u << lane) - 1)));
+        base_total += chunk;
+    }
+    return base_total;
 }
 
 // K6: the rest of Tracker.update (tracker.py:137-181) and StrongSort._format_outputs
@@ -1085,6 +1135,9 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     int* born = st.ulist + (size_t)s * st.Dcap;          // reused: track slots of this frame's births
     const int E = pr.E;
     __shared__ int s_rec_l, s_rec_u, s_nb;
+    long long* stamp = reinterpret_cast<long long*>(st.wkd + (size_t)s * 3 * st.M);     // debug: phase clocks
+#define SS_STAMP(k) do { if (tid == 0) stamp[k] = clock64(); } while (0)
+    SS_STAMP(0);
     int nT = hdr[SH_NTRACKS];
     const int n = hdr[SH_NDET];
     // (a) mark_missed for the IoU stage's unmatched rows (tracker.py:141-142)
@@ -1093,25 +1146,62 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
         if (v.tint(t)[TI_MISS]) ss_track_mark_missed(v.tab(t), pr.max_age);
     }
     __syncthreads();
+    SS_STAMP(1);
     // (b) _attempt_id_recovery (tracker.py:300-351)
     const int nlost = hdr[SH_NLOST];
     int nunm = hdr[SH_NUNM];
     if (nlost > 0 && nunm > 0) {
-        for (int e = wid; e < nlost * nunm; e += nw) {
-            const int li = e / nunm, uj = e % nunm;
-            const int t = lost[li], k = unm[uj];
+        // Only "is the best similarity above 0.7, and which detection has it" is used (:325-331).  Every pair is
+        // screened in fp32 against the feature's fp32 shadow; a pair within 0.02 of the threshold -- none, for
+        // unrelated identities -- is recomputed in fp64 as the reference does, so the decision is the reference's.
+        const int ngrp = (nunm + 3) / 4;
+        for (int e = wid; e < nlost * ngrp; e += nw) {            // a warp per (lost track, 4 detections): 4 dot products in flight
+            const int li = e / ngrp, u0 = (e % ngrp) * 4;
+            const int t = lost[li];
             const int nr = v.tint(t)[TI_NRING];
-            double sim = -CUDART_INF;
+            double sim[4] = {-CUDART_INF, -CUDART_INF, -CUDART_INF, -CUDART_INF};
             if (nr > 0) {
                 const int ls = v.ring(t)[nr - 1];
-                const double* tf = v.pool(ls, E);
-                const float* f = embs + ((size_t)s * st.Dcap + v.dord()[k]) * E;
-                double acc = 0.0;
-                for (int i = lane; i < E; i += 32) acc += (double)f[i] * tf[i];
-                for (int o = 16; o > 0; o >>= 1) acc += shfl_xor_d(acc, o);
-                sim = acc / (v.dtab(k)[DT_NORM] * v.pq()[ls]);
+                const float* tf = v.pool32(ls, E);
+                const float* f[4];
+                double den[4];
+                for (int q = 0; q < 4; q++) {
+                    const int uj = min(u0 + q, nunm - 1);
+                    const int k = unm[uj];
+                    f[q] = embs + ((size_t)s * st.Dcap + v.dord()[k]) * E;
+                    den[q] = v.dtab(k)[DT_NORM] * v.pq()[ls];
+                }
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                if ((E & 3) == 0) {
+                    const float4* t4 = reinterpret_cast<const float4*>(tf);
+                    for (int i = lane; i < E / 4; i += 32) {
+                        const float4 b = t4[i];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            const float4 a = reinterpret_cast<const float4*>(f[q])[i];
+                            acc[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+                        }
+                    }
+                } else {
+                    for (int i = lane; i < E; i += 32)
+#pragma unroll
+                        for (int q = 0; q < 4; q++) acc[q] += f[q][i] * tf[i];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_xor_sync(BM_FULL, acc[q], o);
+                    acc[q] = __shfl_sync(BM_FULL, acc[q], 0);     // one value for the warp: the branch below is uniform
+                    sim[q] = (double)acc[q] / den[q];
+                    if (sim[q] > 0.68) {                          // near or above the threshold: exact
+                        const double* td = v.pool(ls, E);
+                        double ad = 0.0;
+                        for (int i = lane; i < E; i += 32) ad += (double)f[q][i] * td[i];
+                        for (int o = 16; o > 0; o >>= 1) ad += shfl_xor_d(ad, o);
+                        sim[q] = shfl_d(ad, 0) / den[q];
+                    }
+                }
             }
-            if (lane == 0) sims[li * st.Dcap + uj] = sim;
+            if (lane < 4 && u0 + lane < nunm) sims[li * st.Dcap + u0 + lane] = sim[lane];
         }
     }
     __syncthreads();
@@ -1145,6 +1235,7 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
         nunm--;
     }
     __syncthreads();
+    SS_STAMP(2);
     // (c) _initiate_track for the remaining unmatched detections, in order (tracker.py:147-150, :395-410)
     if (tid == 0) {
         int nb = 0;
@@ -1187,55 +1278,55 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     }
     __syncthreads();
     nT += nb;
+    SS_STAMP(3);
     // (d) deleted tracks -> lost buffer (tracker.py:152-163), compaction of the list
     __shared__ int s_ndel, s_w;
     int* dellist = st.wki + (size_t)s * st.wki_stride;   // the match kernel's scratch (>= Tcap ints) is free now
-    if (wid == 0) {
-        int k = 0;
-        for (int base = 0; base < nT; base += 32) {
-            const int p = base + lane;
-            const bool del = p < nT && v.tab(order[p])[ST_STATE] == (double)ST_DELETED;
-            const unsigned b = __ballot_sync(BM_FULL, del);
-            if (del) dellist[k + __popc(b & ((1u << lane) - 1))] = order[p];
-            k += __popc(b);
-        }
-        if (lane == 0) s_ndel = k;
+    __shared__ int s_ws[33];
+    {
+        const int k = block_compact(nT, s_ws, [&](int p) { return v.tab(order[p])[ST_STATE] == (double)ST_DELETED; },
+                                    [&](int p, int r) { dellist[r] = order[p]; });
+        if (tid == 0) s_ndel = k;
     }
     __syncthreads();
     const int ndel = s_ndel;
     if (ndel > 0) {
+        // the lost buffer's bookkeeping on shared-memory copies (<= 30 entries), one thread; the tracks that
+        // drop out are collected and released in parallel afterwards
+        __shared__ int s_lost[SS_LOST + 2], s_lframe[SS_LOST + 2], s_nrel;
+        int* rellist = dellist + st.Tcap;                    // second Tcap ints of the match kernel's scratch
+        const int nl0 = hdr[SH_NLOST];
+        if (tid < nl0) { s_lost[tid] = lost[tid]; s_lframe[tid] = v.tint(lost[tid])[TI_LOSTFRAME]; }
+        __syncthreads();
         if (tid == 0) {
             const int now = n > 0 ? hdr[SH_FRAME] : hdr[SH_NHIST];      // frame_id is None for tracker.update([])
-            int nl = hdr[SH_NLOST];
+            int nl = nl0, nrel = 0;
             for (int i0 = 0; i0 < ndel; i0++) {
                 const int t = dellist[i0];
                 bool kept = false;
-                if (nl < SS_LOST) { v.tint(t)[TI_LOSTFRAME] = now; lost[nl++] = t; kept = true; }
+                if (nl < SS_LOST) { s_lost[nl] = t; s_lframe[nl] = now; nl++; kept = true; v.tint(t)[TI_LOSTFRAME] = now; }
                 int k2 = 0;
                 for (int i = 0; i < nl; i++) {
-                    const int lt = lost[i];
-                    if (now - v.tint(lt)[TI_LOSTFRAME] < pr.max_age) lost[k2++] = lt;
-                    else ss_track_release(v, lt);
+                    if (now - s_lframe[i] < pr.max_age) { s_lost[k2] = s_lost[i]; s_lframe[k2] = s_lframe[i]; k2++; }
+                    else rellist[nrel++] = s_lost[i];
                 }
                 nl = k2;
-                if (!kept) ss_track_release(v, t);
+                if (!kept) rellist[nrel++] = t;
             }
+            for (int i = 0; i < nl; i++) lost[i] = s_lost[i];
             hdr[SH_NLOST] = nl;
+            s_nrel = nrel;
         }
         __syncthreads();
-        if (wid == 0) {                                  // stable compaction of the list, in place
-            int k = 0;
-            for (int base = 0; base < nT; base += 32) {
-                const int p = base + lane;
-                const int t = p < nT ? order[p] : 0;
-                const bool keep = p < nT && v.tab(t)[ST_STATE] != (double)ST_DELETED;
-                const unsigned b = __ballot_sync(BM_FULL, keep);
-                __syncwarp();
-                if (keep) order[k + __popc(b & ((1u << lane) - 1))] = t;
-                k += __popc(b);
-                __syncwarp();
-            }
-            if (lane == 0) s_w = k;
+        for (int i = wid; i < s_nrel; i += nw) ss_track_release_warp(v, rellist[i]);
+        __syncthreads();
+        {                                                // stable compaction of the list (through a scratch copy)
+            int* keep_l = dellist + 2 * (size_t)st.Tcap;     // third Tcap ints of the scratch
+            const int k = block_compact(nT, s_ws, [&](int p) { return v.tab(order[p])[ST_STATE] != (double)ST_DELETED; },
+                                        [&](int p, int r) { keep_l[r] = order[p]; });
+            __syncthreads();
+            for (int i = tid; i < k; i += blockDim.x) order[i] = keep_l[i];
+            if (tid == 0) s_w = k;
         }
         __syncthreads();
         nT = s_w;
@@ -1247,60 +1338,107 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     int anyc = 0;
     for (int p = tid; p < nT; p += blockDim.x) anyc |= v.tab(order[p])[ST_STATE] == (double)ST_CONFIRMED_STATE;
     anyc = __syncthreads_or(anyc);
+    SS_STAMP(4);
     // (e) metric.partial_fit (tracker.py:165-178, linear_assignment.py:538-593)
     if (anyc) {
         const int keep = pr.budget / 4 < 5 ? pr.budget / 4 : 5;
         const int nl = hdr[SH_NLOST];
-        for (int p = wid; p < nT + nl; p += nw) {
+        // pass 1, a thread per target: a full sample list takes a feature only if its quality beats the list's
+        // minimum -- when none of the ring's features does (the steady state) all <= 10 appends are no-ops.
+        // The targets with real work are collected for pass 2.
+        __shared__ int s_nwork;
+        int* work = st.wki + (size_t)s * st.wki_stride + 2 * (size_t)st.Tcap;     // third Tcap ints of the scratch
+        if (tid == 0) s_nwork = 0;
+        __syncthreads();
+        for (int p = tid; p < nT + nl; p += blockDim.x) {
+            const int t = p < nT ? order[p] : lost[p - nT];
+            const int* ti = v.tint(t);
+            bool todo;
+            if (p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE) {
+                const int nb0 = ti[TI_NBANK], nr = ti[TI_NRING];
+                const int* rg = v.ring(t);
+                if (nb0 + nr <= pr.budget) {
+                    // every append fits under the budget: plain appends by this thread (no other thread touches
+                    // this target; a pool slot belongs to one target)
+                    int* tw = v.tint(t);
+                    int* bs = v.bslot(t);
+                    int* bq = v.bseq(t);
+                    int* ds = v.dslot(t);
+                    int* dc = v.dcnt(t);
+                    int nb = nb0, ndl = tw[TI_NDIST], seq = tw[TI_SEQ];
+                    double mq = nb ? v.bminq(t) : CUDART_INF;
+                    for (int i = 0; i < nr; i++) {
+                        const int slot = rg[i];
+                        bs[nb] = slot; bq[nb] = seq++; nb++;
+                        mq = fmin(mq, v.pq()[slot]);
+                        v.pbank()[slot] += 1;
+                        int j = 0;
+                        for (; j < ndl; j++) if (ds[j] == slot) { dc[j]++; break; }
+                        if (j == ndl) { ds[ndl] = slot; dc[ndl] = 1; ndl++; }
+                    }
+                    tw[TI_NBANK] = nb; tw[TI_NDIST] = ndl; tw[TI_SEQ] = seq;
+                    v.bminq(t) = mq;
+                    todo = false;
+                } else {
+                    todo = nb0 < pr.budget;
+                    if (!todo) {
+                        const double mq = v.bminq(t);
+                        for (int i = 0; i < nr && !todo; i++) todo = v.pq()[rg[i]] > mq;
+                    }
+                }
+            } else {
+                todo = ti[TI_NBANK] > keep;                              // inactive target (:575-593)
+            }
+            if (todo) work[atomicAdd(&s_nwork, 1)] = p;
+        }
+        __syncthreads();
+        if (tid == 0) stamp[8] = clock64();
+        const int nwork = s_nwork;
+        if (tid == 0) stamp[9] = nwork;
+        for (int q = wid; q < nwork; q += nw) {                          // pass 2, a warp per target
+            const int p = work[q];
             const int t = p < nT ? order[p] : lost[p - nT];
             int* ti = v.tint(t);
             if (p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE) {
                 const int nr = ti[TI_NRING];
-                // a full sample list takes a feature only if its quality beats the list's minimum: when none
-                // of the ring's features does (the steady state), all <= 10 appends are no-ops
-                bool any = ti[TI_NBANK] < pr.budget;
-                if (!any) {
-                    const bool better = lane < nr && v.pq()[v.ring(t)[lane]] > v.bminq(t);
-                    any = __any_sync(BM_FULL, better);
+                // the list's minimum quality only rises while entries are replaced: a ring feature that does not
+                // beat it now cannot enter later in this loop either (while there is room, every feature enters)
+                const bool cand = lane < nr && (ti[TI_NBANK] < pr.budget || v.pq()[v.ring(t)[lane]] > v.bminq(t));
+                unsigned m = __ballot_sync(BM_FULL, cand);
+                if (ti[TI_NBANK] < pr.budget) m = nr >= 32 ? 0xffffffffu : ((1u << nr) - 1u);
+                while (m) {
+                    const int i = __ffs(m) - 1;
+                    m &= m - 1;
+                    ss_bank_append(v, pr, t, v.ring(t)[i]);
                 }
-                if (any) for (int i = 0; i < nr; i++) ss_bank_append(v, pr, t, v.ring(t)[i]);
             } else {
-                while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);        // inactive target (:575-593)
+                while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);
             }
         }
     }
     __syncthreads();
+    SS_STAMP(5);
     // (f) _format_outputs (strongsort.py:329-359): confirmed tracks updated this frame, in list order
-    if (wid == 0) {
+    {
         double* o = out + (size_t)s * out_rows * 8;
-        int k = 0;
-        for (int base = 0; base < nT; base += 32) {
-            const int p = base + lane;
-            bool ok = false;
-            int t = 0;
-            if (p < nT) {
-                t = order[p];
-                const double* a = v.tab(t);
-                ok = a[ST_STATE] == (double)ST_CONFIRMED_STATE && a[SS_TSU] < 1.0;
-            }
-            const unsigned b = __ballot_sync(BM_FULL, ok);
-            if (ok) {
-                const int r = k + __popc(b & ((1u << lane) - 1));
-                if (r < out_rows) {
-                    const double* m = v.mean(t);
-                    const double* a = v.tab(t);
-                    const double w = m[2] * m[3];
-                    const double x1 = m[0] - w / 2.0, y1 = m[1] - m[3] / 2.0;       // to_tlbr (track.py:144-171)
-                    double* row = o + (size_t)r * 8;
-                    row[0] = x1; row[1] = y1; row[2] = x1 + w; row[3] = y1 + m[3];
-                    row[4] = v.tint(t)[TI_ID]; row[5] = a[SS_CONF]; row[6] = a[SS_CLS]; row[7] = a[ST_DETIND];
-                }
-            }
-            k += __popc(b);
-        }
-        if (lane == 0) nout[s] = k < out_rows ? k : out_rows;
+        const int k = block_compact(nT, s_ws, [&](int p) {
+            const double* a = v.tab(order[p]);
+            return a[ST_STATE] == (double)ST_CONFIRMED_STATE && a[SS_TSU] < 1.0;
+        }, [&](int p, int r) {
+            if (r >= out_rows) return;
+            const int t = order[p];
+            const double* m = v.mean(t);
+            const double* a = v.tab(t);
+            const double w = m[2] * m[3];
+            const double x1 = m[0] - w / 2.0, y1 = m[1] - m[3] / 2.0;       // to_tlbr (track.py:144-171)
+            double* row = o + (size_t)r * 8;
+            row[0] = x1; row[1] = y1; row[2] = x1 + w; row[3] = y1 + m[3];
+            row[4] = v.tint(t)[TI_ID]; row[5] = a[SS_CONF]; row[6] = a[SS_CLS]; row[7] = a[ST_DETIND];
+        });
+        if (tid == 0) nout[s] = k < out_rows ? k : out_rows;
     }
     __syncthreads();
+    SS_STAMP(6);
     // (g) merge the deferred frees, rebuild the list of features some sample list references
     {
         const int nf = hdr[SH_NPFREED], np = hdr[SH_NPFREE];
@@ -1317,6 +1455,9 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
             live[k] = p;
             lnorm[k] = (float)(v.pq()[p] + 1e-8);
         }
+    __syncthreads();
+    SS_STAMP(7);
+#undef SS_STAMP
 }
 
 __global__ void ss_reset_kernel(SsState st) {
@@ -1549,6 +1690,7 @@ int bm_strongsort_debug_copy(void* handle, int which, int stream_index, void* h_
     if (which == 0) { src = st.wki + s * st.wki_stride; avail = st.wki_stride * 4; }
     else if (which == 1) { src = st.cost + s * st.Tcap * st.Dcap; avail = (size_t)st.Tcap * st.Dcap * 8; }
     else if (which == 2) { src = st.dtab + s * st.Dcap * bm::DT_COUNT; avail = (size_t)st.Dcap * bm::DT_COUNT * 8; }
+    else if (which == 3) { src = st.wkd + s * 3 * st.M; avail = (size_t)3 * st.M * 8; }
     else return ss_fail(-1, "bm_strongsort_debug_copy: unknown buffer");
     SS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
     SS_CUDA(cudaMemcpy(h_dst, src, nbytes < avail ? nbytes : avail, cudaMemcpyDeviceToHost));
