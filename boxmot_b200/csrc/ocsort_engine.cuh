@@ -146,7 +146,7 @@ __device__ __forceinline__ void store_dense(const OcsView& v, int which, int slo
     for (int c = 0; c < 49; c++) b[(size_t)c * v.Tcap] = P[c];
 }
 // Switch a track to the dense covariance (both copies), expanding the block form.
-__device__ inline void ocs_make_dense(const OcsView& v, int slot) {
+static __device__ __noinline__ void ocs_make_dense(const OcsView& v, int slot) {
     const int T = v.Tcap;
     for (int which = 0; which < 2; which++) {
         const double* src = which ? v.sxP : v.xP;
@@ -179,8 +179,49 @@ __device__ __forceinline__ bool ocs_lookback(const OcsView& v, int slot, int cur
     return true;
 }
 
+// Dense slow path (tracks with OF_DENSE), kept OUT OF LINE so that the 49-entry covariance never enters the
+// register allocation of the common block-form path.
+static __device__ __noinline__ void ocs_dense_predict(const OcsView& v, int slot, XysrConst kc, double* x_out) {
+    const int T = v.Tcap;
+    double x[7], Pd[49];
+    for (int c = 0; c < 7; c++) x[c] = v.xP[c * T + slot];
+    load_dense(v, 0, slot, Pd);
+    if (x[6] + x[2] <= 0) x[6] *= 0.0;
+    xysr_predict(x, Pd, kc);
+    for (int c = 0; c < 7; c++) { v.xP[c * T + slot] = x[c]; x_out[c] = x[c]; }
+    store_dense(v, 0, slot, Pd);
+}
+static __device__ __noinline__ void ocs_dense_update(const OcsView& v, int slot, const double* z, XysrConst kc) {
+    const int T = v.Tcap;
+    const int flags = v.I(OI_FLAGS, slot);
+    double xd[7], Pd[49];
+    if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
+        for (int c = 0; c < 7; c++) xd[c] = v.sxP[c * T + slot];
+        load_dense(v, 1, slot, Pd);
+        double z1[4];
+        for (int c = 0; c < 4; c++) z1[c] = v.lastz[c * T + slot];
+        xysr_oru_replay(xd, Pd, z1, z, v.I(OI_NNONE, slot) + 1, kc);
+    } else {
+        for (int c = 0; c < 7; c++) xd[c] = v.xP[c * T + slot];
+        load_dense(v, 0, slot, Pd);
+    }
+    xysr_update(xd, Pd, z);
+    for (int c = 0; c < 7; c++) v.xP[c * T + slot] = xd[c];
+    store_dense(v, 0, slot, Pd);
+    for (int c = 0; c < 4; c++) v.lastz[c * T + slot] = z[c];
+    v.I(OI_FLAGS, slot) = flags | OF_OBSERVED;
+    v.I(OI_NNONE, slot) = 0;
+}
+static __device__ __noinline__ void ocs_dense_freeze_copy(const OcsView& v, int slot) {
+    double P[49];
+    load_dense(v, 0, slot, P);
+    store_dense(v, 1, slot, P);
+}
+
 // KalmanBoxTracker.update(bbox, cls, det_ind) with a real detection (ocsort.py:136-169)
 // followed by KalmanFilterXYSR.update (xysr_kf.py:211-291, ORU at :249-254).
+// DENSE: compiled into the DeepOCSORT kernels only (a rotating CMC warp can switch a track to the dense covariance)
+template <bool DENSE = false>
 __device__ inline void ocs_track_update(const OcsView& v, int slot, const double* det /*x1,y1,x2,y2,conf*/,
                                         double cls, int det_ind, int delta_t, const XysrConst& kc) {
     const int T = v.Tcap;
@@ -233,26 +274,7 @@ __device__ inline void ocs_track_update(const OcsView& v, int slot, const double
     double z[4];
     xyxy_to_z(det, z);
     int flags = v.I(OI_FLAGS, slot);
-    if (flags & OF_DENSE) {                      // after a rotating CMC warp: the reference's dense arithmetic
-        double xd[7], Pd[49];
-        if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
-            for (int c = 0; c < 7; c++) xd[c] = v.sxP[c * T + slot];
-            load_dense(v, 1, slot, Pd);
-            double z1[4];
-            for (int c = 0; c < 4; c++) z1[c] = v.lastz[c * T + slot];
-            xysr_oru_replay(xd, Pd, z1, z, v.I(OI_NNONE, slot) + 1, kc);
-        } else {
-            for (int c = 0; c < 7; c++) xd[c] = v.xP[c * T + slot];
-            load_dense(v, 0, slot, Pd);
-        }
-        xysr_update(xd, Pd, z);
-        for (int c = 0; c < 7; c++) v.xP[c * T + slot] = xd[c];
-        store_dense(v, 0, slot, Pd);
-        for (int c = 0; c < 4; c++) v.lastz[c * T + slot] = z[c];
-        v.I(OI_FLAGS, slot) = flags | OF_OBSERVED;
-        v.I(OI_NNONE, slot) = 0;
-        return;
-    }
+    if (DENSE && (flags & OF_DENSE)) { ocs_dense_update(v, slot, z, kc); return; }   // after a rotating CMC warp (slow path)
     double x[7], P[13];
     if (!(flags & OF_OBSERVED) && (flags & OF_SAVED)) {
         load_xP(v.sxP, T, slot, x, P);
@@ -272,12 +294,13 @@ __device__ inline void ocs_track_update(const OcsView& v, int slot, const double
 }
 
 // KalmanBoxTracker.update(None, ...) (ocsort.py:170-171 -> xysr_kf.py:233-246)
+template <bool DENSE = false>
 __device__ inline void ocs_track_miss(const OcsView& v, int slot) {
     const int T = v.Tcap;
     int flags = v.I(OI_FLAGS, slot);
     if (flags & OF_OBSERVED) {
         for (int c = 0; c < XB_N; c++) v.sxP[c * T + slot] = v.xP[c * T + slot];
-        if (flags & OF_DENSE) { double P[49]; load_dense(v, 0, slot, P); store_dense(v, 1, slot, P); }
+        if (DENSE && (flags & OF_DENSE)) ocs_dense_freeze_copy(v, slot);
         flags |= OF_SAVED;
     }
     v.I(OI_FLAGS, slot) = flags & ~OF_OBSERVED;

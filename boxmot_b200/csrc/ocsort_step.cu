@@ -72,19 +72,14 @@ __device__ __forceinline__ void ocs_split_warp(const OcsState& st, const OcsPara
 
 // Predict of the track at list position p (ocsort.py:173-186, xysr_kf.py:137-175) and its
 // association operands.
+template <bool DENSE>
 __device__ __forceinline__ void ocs_predict_track(const OcsState& st, const OcsParams& pr, const OcsView& v, int s, int p) {
     const int Tcap = st.Tcap;
     const XysrConst kc = {pr.q_xy, pr.q_s};
     const int slot = v.order[p];
     double x[7];
-    if (v.I(OI_FLAGS, slot) & OF_DENSE) {
-        double Pd[49];
-        for (int c = 0; c < 7; c++) x[c] = v.xP[c * Tcap + slot];
-        load_dense(v, 0, slot, Pd);
-        if (x[6] + x[2] <= 0) x[6] *= 0.0;
-        xysr_predict(x, Pd, kc);
-        for (int c = 0; c < 7; c++) v.xP[c * Tcap + slot] = x[c];
-        store_dense(v, 0, slot, Pd);
+    if (DENSE && v.dP && (v.I(OI_FLAGS, slot) & OF_DENSE)) {
+        ocs_dense_predict(v, slot, kc, x);
     } else {
         double P[13];
         load_xP(v.xP, Tcap, slot, x, P);
@@ -144,6 +139,20 @@ __device__ __forceinline__ void docs_warp_block(double* P, int o, const double* 
     P[(o + 1) * 7 + o] = t10 * m00 + t11 * m01;
     P[(o + 1) * 7 + o + 1] = t10 * m10 + t11 * m11;
 }
+static __device__ __noinline__ void docs_affine_dense(const OcsView& v, int pass, int slot, const double* w6) {
+    const int T = v.Tcap;
+    double* b = pass ? v.sxP : v.xP;
+    const double x0 = b[0 * T + slot], x1 = b[1 * T + slot], x4 = b[4 * T + slot], x5 = b[5 * T + slot];
+    b[0 * T + slot] = (w6[0] * x0 + w6[1] * x1) + w6[2];
+    b[1 * T + slot] = (w6[3] * x0 + w6[4] * x1) + w6[5];
+    b[4 * T + slot] = w6[0] * x4 + w6[1] * x5;
+    b[5 * T + slot] = w6[3] * x4 + w6[4] * x5;
+    double P[49];
+    load_dense(v, pass, slot, P);
+    docs_warp_block(P, 0, w6);
+    docs_warp_block(P, 4, w6);
+    store_dense(v, pass, slot, P);
+}
 __device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, const double* w6, int delta_t) {
     const int T = v.Tcap;
     const double a = w6[0], tx = w6[2], d = w6[4], ty = w6[5];
@@ -188,19 +197,7 @@ __device__ __forceinline__ void docs_affine_track(const OcsView& v, int slot, co
     for (int pass = 0; pass < 2; pass++) {
         if (pass == 1 && !(!(flags & OF_OBSERVED) && (flags & OF_SAVED))) break;
         double* b = pass ? v.sxP : v.xP;
-        if (flags & OF_DENSE) {
-            const double x0 = b[0 * T + slot], x1 = b[1 * T + slot], x4 = b[4 * T + slot], x5 = b[5 * T + slot];
-            b[0 * T + slot] = (w6[0] * x0 + w6[1] * x1) + tx;
-            b[1 * T + slot] = (w6[3] * x0 + w6[4] * x1) + ty;
-            b[4 * T + slot] = w6[0] * x4 + w6[1] * x5;
-            b[5 * T + slot] = w6[3] * x4 + w6[4] * x5;
-            double P[49];
-            load_dense(v, pass, slot, P);
-            docs_warp_block(P, 0, w6);
-            docs_warp_block(P, 4, w6);
-            store_dense(v, pass, slot, P);
-            continue;
-        }
+        if (flags & OF_DENSE) { docs_affine_dense(v, pass, slot, w6); continue; }
         b[0 * T + slot] = a * b[0 * T + slot] + tx;
         b[1 * T + slot] = d * b[1 * T + slot] + ty;
         b[4 * T + slot] = a * b[4 * T + slot];
@@ -231,7 +228,7 @@ ocs_predict_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, co
     if (p == 0) st.n_updates[s] += (unsigned long long)nT;
     if (p < nT) {
         if (DEEP && warps) docs_affine_track(v, v.order[p], warps + (size_t)s * 6, pr.delta_t);
-        ocs_predict_track(st, pr, v, s, p);
+        ocs_predict_track<DEEP>(st, pr, v, s, p);
     }
 }
 
@@ -1419,8 +1416,9 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
 // ============================================================================ K3
 // One thread per (track, detection) pair of the frame: KalmanBoxTracker.update with a
 // real detection (ocsort.py:136-169) + KalmanFilterXYSR.update incl. ORU.
+template <bool DENSE>
 __global__ void __launch_bounds__(K3_NT)
-ocs_update_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
+ocs_update_kernel_t(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     const int chunks = (st.Dcap + K3_NT - 1) / K3_NT;
     const int s = blockIdx.x / chunks;
     const int k = (blockIdx.x % chunks) * K3_NT + threadIdx.x;
@@ -1431,7 +1429,7 @@ ocs_update_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     const float* dr = dets + ((size_t)s * st.Dcap + di) * 6;
     const double det[5] = {(double)dr[0], (double)dr[1], (double)dr[2], (double)dr[3], (double)dr[4]};
     const XysrConst kc = {pr.q_xy, pr.q_s};
-    ocs_track_update(v, slot, det, (double)dr[5], di, pr.delta_t, kc);
+    ocs_track_update<DENSE>(v, slot, det, (double)dr[5], di, pr.delta_t, kc);
 }
 
 // ============================================================================ K4
@@ -1466,8 +1464,9 @@ __device__ __forceinline__ int block_excl_scan(int val, int* total, int* ws /*[3
 
 // One CTA per stream, one thread per slot / list position (blockDim = Tcap rounded up
 // to a warp, Tcap <= 1024).
+template <bool DENSE>
 __global__ void __launch_bounds__(1024)
-ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, double* __restrict__ out,
+ocs_finalize_kernel_t(OcsState st, OcsParams pr, const float* __restrict__ dets, double* __restrict__ out,
                     int* __restrict__ nout) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     int* inuse = reinterpret_cast<int*>(smem_raw);     // [Tcap]
@@ -1489,7 +1488,7 @@ ocs_finalize_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets, d
     if (tid < nT) {
         slot = v.order[tid];
         inuse[slot] = 1;
-        if (v.I(OI_TSU, slot) != 0) ocs_track_miss(v, slot);   // update(None) (ocsort.py:388-389)
+        if (v.I(OI_TSU, slot) != 0) ocs_track_miss<DENSE>(v, slot);   // update(None) (ocsort.py:388-389)
     }
     __syncthreads();
     // births take the free slots in ascending order
@@ -1673,11 +1672,11 @@ cudaError_t ocsort_step_launch(const OcsState& st, const OcsParams& pr, const fl
     ocs_assoc_kernel<false><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel", stream)) != cudaSuccess) return e;
     BM_EV(2);
-    ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
+    ocs_update_kernel_t<false><<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_update_kernel", stream)) != cudaSuccess) return e;
     BM_EV(3);
     const int nt4 = (st.Tcap + 31) / 32 * 32;
-    ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
+    ocs_finalize_kernel_t<false><<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
     if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
     BM_EV(4);
 #undef BM_EV
@@ -1708,11 +1707,11 @@ cudaError_t deepocsort_step_launch(const OcsState& st, const OcsParams& pr, cons
     ocs_assoc_kernel<true><<<st.S, K2_NT, ocsort_step_smem(st, pr), stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_assoc_kernel<deep>", stream)) != cudaSuccess) return e;
     BM_EV(3);
-    ocs_update_kernel<<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
+    ocs_update_kernel_t<true><<<st.S * c3, K3_NT, 0, stream>>>(st, pr, dets);
     if ((e = dbg_check("ocs_update_kernel", stream)) != cudaSuccess) return e;
     BM_EV(4);
     const int nt4 = (st.Tcap + 31) / 32 * 32;
-    ocs_finalize_kernel<<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
+    ocs_finalize_kernel_t<true><<<st.S, nt4, (size_t)st.Tcap * 8, stream>>>(st, pr, dets, out, nout);
     if ((e = dbg_check("ocs_finalize_kernel", stream)) != cudaSuccess) return e;
     BM_EV(5);
     if (pr.emb_on) {
