@@ -316,7 +316,11 @@ class ClockSampler(threading.Thread):
 # every kernel, so this is an upper bound of what a live step moves):
 #   profiles/r1_launches_lane_scan_traffic.csv   predict 55.2 + assoc 19.3 + update 72.0 + finalize 39.7 MB
 #   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
-NCU_TRAFFIC = {"ocsort": 186.1e6, "bytetrack": 41.1e6}
+#   profiles/r2_launches_ocsort_traffic.csv      round 2 (commit d7eb0be5..): predict 54.8 + assoc 19.3 + update 71.7 + finalize 39.5 MB
+NCU_TRAFFIC = {"ocsort": 185.4e6, "bytetrack": 41.1e6}
+NCU_TRAFFIC_SOURCE = {"ocsort": "profiles/r2_launches_ocsort_traffic.csv (ncu, cold caches, single launch chain; the OC-SORT kernels are "
+                                "unchanged since that capture)",
+                      "bytetrack": "profiles/r1_launches_bytetrack_traffic.csv (round 1 capture)"}
 TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)",
                  "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)",
                  "deepocsort": "DeepOCSORT (deepocsort.yaml, synthetic re-ID embeddings)",
@@ -602,7 +606,7 @@ def run_gpu_arm(args):
                          "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC.get(args.tracker) if (S, args.objects, args.det_cap, args.track_cap) ==
                          (1024, 100, 128, 256) else None,
-                         "traffic_source": "ncu dram__bytes_read+write per frame step, cold caches (profiles/r1_launches_*_traffic.csv)",
+                         "traffic_source": NCU_TRAFFIC_SOURCE.get(args.tracker, "not captured for this configuration"),
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "kernel": "frame step = " + " + ".join(knames) if (deep or boost or strong) else
                                    "frame step = bot_embed + byte_step<BoT> + bot_ema" if bot else
