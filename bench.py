@@ -316,7 +316,7 @@ class ClockSampler(threading.Thread):
 # every kernel, so this is an upper bound of what a live step moves):
 #   profiles/r1_launches_lane_scan_traffic.csv   predict 55.2 + assoc 19.3 + update 72.0 + finalize 39.7 MB
 #   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
-#   profiles/r2_launches_ocsort_traffic.csv      round 2 (commit d7eb0be5..): predict 54.8 + assoc 19.3 + update 71.7 + finalize 39.5 MB
+#   profiles/r2_launches_ocsort_traffic.csv      round 2 (commit bf43990): predict 54.8 + assoc 19.3 + update 71.7 + finalize 39.5 MB
 NCU_TRAFFIC = {"ocsort": 185.4e6, "bytetrack": 41.1e6}
 NCU_TRAFFIC_SOURCE = {"ocsort": "profiles/r2_launches_ocsort_traffic.csv (ncu, cold caches, single launch chain; the OC-SORT kernels are "
                                 "unchanged since that capture)",
