@@ -34,7 +34,8 @@ constexpr int TC_M = 128, TC_KC = 32, TC_NMAX = 256, TC_NT = 256;
 constexpr uint32_t TC_TMEM_COLS = 256;
 
 __host__ __device__ inline size_t cosine_tc_smem_bytes() {
-    return 1024 /*alignment slack*/ + 2 * TC_M * 128 + 2 * TC_NMAX * 128 + 64;
+    // plain path: 96 KB of tiles; the fast path (cosine_tc_fast) needs 3 tiles of (128 + 128) rows = the same
+    return 1024 /*alignment slack*/ + 2 * TC_M * 128 + 2 * TC_NMAX * 128 + 128;
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -124,6 +125,146 @@ struct CosineProblem {
                                                                 //    neighbour over the B rows (StrongSORT's sample bank)
 };
 
+// ---------------------------------------------------------------------------------------------
+// Fast path (E a multiple of 32, 16-byte aligned rows).  The plain loop below spends its time ISSUING
+// INSTRUCTIONS (ncu: 35 % issue utilisation, ~525 warp instructions per 32-float chunk, two thirds of them
+// the round-to-nearest hi / lo split and its address arithmetic), not waiting for memory.  Here:
+//   * tcgen05 reads a tf32 operand from the upper 19 bits of an fp32 word, so the RAW fp32 tile is the `hi`
+//     operand (hi = x truncated); cp.async drops the gathered 16-byte pieces straight into the canonical
+//     K-major SWIZZLE_128B layout -- no register pass at all for hi;
+//   * lo = x - trunc(x) (exact in fp32) costs one AND and one SUB per element, computed from the landed tile;
+//   * hi tiles are double-buffered (the copy of chunk k + 1 flies during the MMAs of chunk k), one lo tile;
+//     96 KB per CTA -> two CTAs per SM, column tiles of <= 128 detections.
+// Same three products (hi.hi + hi.lo + lo.hi); the split truncates instead of rounding, which moves the
+// error from ~2^-22 to ~2^-21 relative (measured against scipy in tests/test_gpu_units.py).
+constexpr int TC3_N = 128;
+constexpr size_t TC3_TILE = (size_t)(TC_M + TC3_N) * 128;                // A rows then B rows, 128 bytes per row
+__host__ __device__ inline size_t cosine_tc3_smem_bytes() { return 1024 + 3 * TC3_TILE + 64; }
+
+__device__ __forceinline__ void tc_cp16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+
+__device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, unsigned char* sm, uint32_t tmem,
+                                               uint64_t* mbar) {
+    const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    unsigned char* hi[2] = {sm, sm + TC3_TILE};
+    unsigned char* lo = sm + 2 * TC3_TILE;
+    const uint32_t bar = smem_u32(mbar);
+    const int rows = min(TC_M, pb.nA - r0);
+    const int nk = pb.E / TC_KC;
+    constexpr int PA = TC_M * 8 / TC_NT, PB = TC3_N * 8 / TC_NT;      // 16-byte pieces per thread and chunk
+    float nn_min = CUDART_INF_F;
+    uint32_t phase = 0;
+    for (int c0 = 0; c0 < pb.nB; c0 += TC3_N) {
+        const int cols = min(TC3_N, pb.nB - c0);
+        const int npad = max(16, (cols + 15) & ~15);
+        const uint32_t idesc = tc_idesc(npad);
+        const float* src[PA + PB];                                    // this thread's pieces: global source (nullptr = padding)
+        int off[PA + PB];                                             // and swizzled byte offset in a tile (-1 = beyond npad)
+#pragma unroll
+        for (int j = 0; j < PA; j++) {
+            const int q = tid + TC_NT * j, r = q >> 3, c = q & 7;
+            src[j] = r < rows ? pb.A + (size_t)pb.ra[r0 + r] * pb.E + c * 4 : nullptr;
+            off[j] = r * 128 + ((c ^ (r & 7)) << 4);
+        }
+#pragma unroll
+        for (int j = 0; j < PB; j++) {
+            const int q = tid + TC_NT * j, r = q >> 3, c = q & 7;
+            src[PA + j] = r < cols ? pb.B + (size_t)pb.rb[c0 + r] * pb.E + c * 4 : nullptr;
+            off[PA + j] = r < npad ? TC_M * 128 + r * 128 + ((c ^ (r & 7)) << 4) : -1;
+        }
+        // padding pieces are never copied: zero them in both hi tiles once (lo follows from hi)
+#pragma unroll
+        for (int j = 0; j < PA + PB; j++)
+            if (!src[j] && off[j] >= 0) {
+                *reinterpret_cast<uint4*>(hi[0] + off[j]) = make_uint4(0, 0, 0, 0);
+                *reinterpret_cast<uint4*>(hi[1] + off[j]) = make_uint4(0, 0, 0, 0);
+            }
+        auto issue = [&](int k) {
+            unsigned char* dst = hi[k & 1];
+#pragma unroll
+            for (int j = 0; j < PA + PB; j++)
+                if (src[j]) tc_cp16(smem_u32(dst + off[j]), src[j] + (size_t)k * TC_KC);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        issue(0);
+        for (int k = 0; k < nk; k++) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");      // this thread's pieces of chunk k have landed
+            if (k > 0) { tc_mbar_wait(bar, phase); phase ^= 1u; }     // MMAs of chunk k - 1 done: lo and hi[(k+1)&1] are free
+            if (k + 1 < nk) issue(k + 1);                             // flies during the split, the MMAs and the next wait
+            const unsigned char* h = hi[k & 1];
+#pragma unroll
+            for (int j = 0; j < PA + PB; j++) {
+                if (off[j] < 0) continue;
+                const uint4 x = *reinterpret_cast<const uint4*>(h + off[j]);
+                uint4 l;
+                l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(x.x & 0xFFFFE000u));
+                l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(x.y & 0xFFFFE000u));
+                l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(x.z & 0xFFFFE000u));
+                l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(x.w & 0xFFFFE000u));
+                *reinterpret_cast<uint4*>(lo + off[j]) = l;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t dah = tc_smem_desc(smem_u32(h)), dal = tc_smem_desc(smem_u32(lo));
+                const uint64_t dbh = tc_smem_desc(smem_u32(h + TC_M * 128)), dbl = tc_smem_desc(smem_u32(lo + TC_M * 128));
+#pragma unroll
+                for (int kk = 0; kk < TC_KC / 8; kk++) {
+                    const uint64_t adv = (uint64_t)((kk * 32) >> 4);
+                    tc_mma_tf32(tmem, dah + adv, dbh + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                    tc_mma_tf32(tmem, dah + adv, dbl + adv, idesc, 1u);
+                    tc_mma_tf32(tmem, dal + adv, dbh + adv, idesc, 1u);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                             :: "r"(bar) : "memory");
+            }
+        }
+        tc_mbar_wait(bar, phase);
+        phase ^= 1u;
+        // ---- epilogue: warp w owns TMEM lanes 32 (w % 4) .. + 31 = tile rows
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int lq = wid & 3;
+        const int r = lq * 32 + lane;
+        const bool rin = r < rows;
+        const float na = (rin && pb.raw != 1) ? pb.na[r0 + r] : 1.f;
+        float* orow = (rin && pb.raw != 2) ? pb.out + (size_t)pb.ra[r0 + r] * pb.out_ld + c0 : nullptr;
+        for (int cb = 16 * (wid >> 2); cb < npad; cb += 16 * (TC_NT / 128)) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)cb;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (rin) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const int c = cb + j;
+                    if (c < cols) {
+                        if (pb.raw == 1) { orow[c] = __uint_as_float(v[j]); continue; }
+                        const double cs = (double)__uint_as_float(v[j]) / ((double)na * (double)pb.nb[c0 + c]);
+                        if (pb.raw == 2) { nn_min = fminf(nn_min, (float)(1.0 - fmin(1.0, fmax(-1.0, cs)))); continue; }
+                        orow[c] = (float)fmax(0.0, 1.0 - cs);
+                    }
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+    }
+    if (pb.raw == 2) {
+        float* part = reinterpret_cast<float*>(lo);
+        part[(wid >> 2) * TC_M + (wid & 3) * 32 + lane] = nn_min;
+        __syncthreads();
+        const int r = (wid & 3) * 32 + lane;
+        if (wid < 4 && r < rows) pb.out[pb.ra[r0 + r]] = fminf(part[r], part[TC_M + r]);
+    }
+}
+
 // grid = (row tiles of 128, problems); the caller provides problem(blockIdx.y).
 template <typename ProblemFn>
 __global__ void __launch_bounds__(TC_NT)
@@ -154,6 +295,19 @@ cosine_tc_kernel(ProblemFn problem) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
+    if ((pb.E % TC_KC) == 0 && (((uintptr_t)pb.A | (uintptr_t)pb.B) & 15) == 0) {          // uniform over the CTA
+        __syncthreads();                              // everyone has read tmem_slot: the fast path reuses that memory
+        uint64_t* mbar3 = reinterpret_cast<uint64_t*>(sm + 3 * TC3_TILE);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(mbar3)));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        cosine_tc_fast(pb, r0, sm, tmem, mbar3);
+        if (wid == 0)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(TC_TMEM_COLS) : "memory");
+        return;
+    }
     const int rows = min(TC_M, pb.nA - r0);
     uint32_t phase = 0;
     float nn_min = CUDART_INF_F;                                // raw == 2: running minimum of this thread's columns
