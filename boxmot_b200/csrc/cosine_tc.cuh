@@ -135,8 +135,8 @@ struct CosineProblem {
 //   * lo = x - trunc(x) (exact in fp32) costs one AND and one SUB per element, computed from the landed tile;
 //   * hi tiles are double-buffered (the copy of chunk k + 1 flies during the MMAs of chunk k), one lo tile;
 //     96 KB per CTA -> two CTAs per SM, column tiles of <= 128 detections.
-// Same three products (hi.hi + hi.lo + lo.hi); the split truncates instead of rounding, which moves the
-// error from ~2^-22 to ~2^-21 relative (measured against scipy in tests/test_gpu_units.py).
+// Same three products (hi.hi + hi.lo + lo.hi), hi truncated instead of rounded, lo rounded; the cross terms
+// accumulate in their own TMEM columns (see the MMA loop).  Error against scipy: tests/test_gpu_units.py.
 constexpr int TC3_N = 128;
 constexpr size_t TC3_TILE = (size_t)(TC_M + TC3_N) * 128;                // A rows then B rows, 128 bytes per row
 __host__ __device__ inline size_t cosine_tc3_smem_bytes() { return 1024 + 3 * TC3_TILE + 64; }
@@ -199,10 +199,12 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
                 if (off[j] < 0) continue;
                 const uint4 x = *reinterpret_cast<const uint4*>(h + off[j]);
                 uint4 l;
-                l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(x.x & 0xFFFFE000u));
-                l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(x.y & 0xFFFFE000u));
-                l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(x.z & 0xFFFFE000u));
-                l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(x.w & 0xFFFFE000u));
+                // + 0x1000: the tensor core drops the low 13 bits of lo as well; the half-ulp offset turns that
+                // truncation into round-to-nearest
+                l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(x.x & 0xFFFFE000u)) + 0x1000u;
+                l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(x.y & 0xFFFFE000u)) + 0x1000u;
+                l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(x.z & 0xFFFFE000u)) + 0x1000u;
+                l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(x.w & 0xFFFFE000u)) + 0x1000u;
                 *reinterpret_cast<uint4*>(lo + off[j]) = l;
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -214,9 +216,13 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
 #pragma unroll
                 for (int kk = 0; kk < TC_KC / 8; kk++) {
                     const uint64_t adv = (uint64_t)((kk * 32) >> 4);
+                    // hi.hi in columns [0, 128), the two cross terms in [128, 256): the tensor core TRUNCATES
+                    // every fp32 accumulation (measured: ~3e-8 of bias per K = 8 step on a sum near 1), so the
+                    // small terms get an accumulator of their own magnitude and the big one sees E / 8 additions
+                    // instead of 3 E / 8
                     tc_mma_tf32(tmem, dah + adv, dbh + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
-                    tc_mma_tf32(tmem, dah + adv, dbl + adv, idesc, 1u);
-                    tc_mma_tf32(tmem, dal + adv, dbh + adv, idesc, 1u);
+                    tc_mma_tf32(tmem + TC3_N, dah + adv, dbl + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                    tc_mma_tf32(tmem + TC3_N, dal + adv, dbh + adv, idesc, 1u);
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                              :: "r"(bar) : "memory");
@@ -239,7 +245,15 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                 : "r"(taddr) : "memory");
+            uint32_t w[16];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
+                  "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15])
+                : "r"(taddr + (uint32_t)TC3_N) : "memory");
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 16; j++) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
             if (rin) {
 #pragma unroll
                 for (int j = 0; j < 16; j++) {
