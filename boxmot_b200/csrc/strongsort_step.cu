@@ -244,39 +244,58 @@ struct SsBankProblem {
 };
 
 // K3: gated_metric (tracker.py:186-206) followed by _enhance_cost_matrix (linear_assignment.py:251-273,
-// the first thing min_cost_matching does to the metric's matrix) for every (confirmed track, detection)
+// the first thing min_cost_matching does to the metric's matrix) for every (confirmed track, detection).
+// A warp per track row, lanes over the detections: the projection of the Kalman state, its reciprocal square
+// roots, the adaptive lambda and the track's adjustment flags are evaluated once per row (ss_track_terms)
+// instead of once per entry; the frame's detection columns sit in shared memory as seven arrays.
 __global__ void __launch_bounds__(256)
 ss_cost_kernel(SsState st, SsParams pr) {
+    extern __shared__ double ss_cost_sm[];
     const int s = blockIdx.y;
     SsView v(st, s);
     const int nT = v.hdr()[SH_NTRACKS], n = v.hdr()[SH_NDET];
-    const int total = nT * n;
+    if (nT <= 0 || n <= 0) return;
+    const int Dc = st.Dcap;
+    double* dz = ss_cost_sm;                     // [4][Dc] xyah
+    double* dq = dz + 4 * Dc;                    // quality, conf, cls
+    double* dcf = dq + Dc;
+    double* dcl = dcf + Dc;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        const double* d = v.dtab(k);
+        dz[k] = d[DT_XYAH]; dz[Dc + k] = d[DT_XYAH + 1]; dz[2 * Dc + k] = d[DT_XYAH + 2]; dz[3 * Dc + k] = d[DT_XYAH + 3];
+        dq[k] = d[DT_QUALITY]; dcf[k] = d[DT_CONF]; dcl[k] = d[DT_CLS];
+    }
+    __syncthreads();
     const float* dist = v.dist();
     double* cost = v.cost();
-    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
-        const int p = e / n, k = e % n;
+    const int lane = lane_id(), wpb = blockDim.x >> 5;
+    for (int p = blockIdx.x * wpb + (threadIdx.x >> 5); p < nT; p += gridDim.x * wpb) {
         const int t = v.order()[p];
         const double* a = v.tab(t);
-        if (a[ST_STATE] != (double)ST_CONFIRMED_STATE) continue;
-        const int* ti = v.tint(t);
-        double app = SS_INFTY_COST;                              // metric.distance: no samples (:616-617)
-        if (ti[TI_NBANK] > 0) {
-            float mn = CUDART_INF_F;
-            const int* ds = v.dslot(t);
-            for (int i = 0; i < ti[TI_NDIST]; i++) mn = fminf(mn, dist[(size_t)ds[i] * st.Dcap + k]);
-            app = (double)mn;
+        if (a[ST_STATE] != (double)ST_CONFIRMED_STATE) continue;             // uniform over the warp
+        int* ti = v.tint(t);
+        const SsTrackTerms tt = ss_track_terms(v.mean(t), v.covb(t), a, pr.mc_lambda, pr.id_weight);
+        const int nbank = ti[TI_NBANK], ndist = ti[TI_NDIST];
+        const int* ds = v.dslot(t);
+        int bits = 0;
+        for (int k = lane; k < n; k += 32) {
+            double app = SS_INFTY_COST;                          // metric.distance: no samples (:616-617)
+            if (nbank > 0) {
+                float mn = CUDART_INF_F;
+                for (int i = 0; i < ndist; i++) mn = fminf(mn, dist[(size_t)ds[i] * Dc + k]);
+                app = (double)mn;
+            }
+            const double z[4] = {dz[k], dz[Dc + k], dz[2 * Dc + k], dz[3 * Dc + k]};
+            const double cf = dcf[k];
+            const double c = ss_pair_cost(tt, app, z, dq[k], cf, dcl[k]);
+            cost[(size_t)p * Dc + k] = c;
+            // bit 0 / 1: some high- / medium-confidence detection is within the stage's threshold of this track
+            // (the cascade skips the assignment of a level none of whose tracks has the stage's bit)
+            if (cf >= pr.conf_hi) { if (c <= pr.max_cos_dist * 0.8) bits |= 1; }
+            else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bits |= 2; }
         }
-        const double* d = v.dtab(k);
-        double c = ss_gated_entry(app, v.mean(t), v.covb(t), a, d + DT_XYAH, pr.mc_lambda, pr.id_weight);
-        c = ss_enhance_entry(c, a, d[DT_QUALITY], d[DT_CONF], d[DT_CLS]);
-        cost[(size_t)p * st.Dcap + k] = c;
-        // bit 0 / 1: some high- / medium-confidence detection is within the stage's threshold of this track
-        // (the cascade skips the assignment of a level none of whose tracks has the stage's bit)
-        const double cf = d[DT_CONF];
-        int bit = 0;
-        if (cf >= pr.conf_hi) { if (c <= pr.max_cos_dist * 0.8) bit = 1; }
-        else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bit = 2; }
-        if (bit && !(v.tint(t)[TI_FEAS] & bit)) atomicOr(&v.tint(t)[TI_FEAS], bit);
+        for (int o = 16; o > 0; o >>= 1) bits |= __shfl_xor_sync(BM_FULL, bits, o);
+        if (lane == 0 && bits) ti[TI_FEAS] |= bits;
     }
 }
 
@@ -1552,6 +1571,7 @@ int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int tra
     for (int i = 0; i < 7 && r == cudaSuccess; i++) r = cudaEventCreate(&e->ev[i]);
     if (r == cudaSuccess) r = bm::smem_optin(bm::cosine_tc_kernel<bm::SsBankProblem>);
     if (r == cudaSuccess) r = bm::smem_optin(bm::ss_prep_kernel);
+    if (r == cudaSuccess) r = bm::smem_optin(bm::ss_cost_kernel);
     if (r == cudaSuccess) {
         bm::ss_reset_kernel<<<n_streams, 256>>>(st);
         r = cudaGetLastError();
@@ -1627,7 +1647,7 @@ int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, co
     bm::cosine_tc_kernel<bm::SsBankProblem><<<dim3((st.Pcap + bm::TC_M - 1) / bm::TC_M, st.S), bm::TC_NT,
                                               bm::cosine_tc_smem_bytes(), s>>>(pb);
     if (tm) cudaEventRecord(e->ev[2], s);
-    bm::ss_cost_kernel<<<dim3(8, st.S), 256, 0, s>>>(st, pr);
+    bm::ss_cost_kernel<<<dim3(8, st.S), 256, (size_t)st.Dcap * 7 * sizeof(double), s>>>(st, pr);
     if (tm) cudaEventRecord(e->ev[3], s);
     bm::ss_match_kernel<<<(st.S + bm::SS_MATCH_WPB - 1) / bm::SS_MATCH_WPB, bm::SS_MATCH_WPB * 32, 0, s>>>(st, pr);
     if (tm) cudaEventRecord(e->ev[4], s);

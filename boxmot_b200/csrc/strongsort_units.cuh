@@ -50,6 +50,70 @@ __device__ __forceinline__ double ss_gated_entry(double c, const double* x, cons
     return c;
 }
 
+// The same entry split into its per-track part and its per-pair part for a kernel that walks one track's row:
+// every hoisted value is a subexpression of ss_gated_entry / ss_enhance_entry that depends on the track alone,
+// evaluated by the same operations (the library is compiled without FMA contraction), so the pair function
+// returns ss_enhance_entry(ss_gated_entry(...)) bit for bit.
+struct SsTrackTerms {
+    double x[4], inv[4];            // mean and 1 / sqrt(S_ii) of the projected state
+    double mfac, px, py, lam, oml, idf, quality, conf, cls;
+    bool has_vel, q95, h98, s97, s105, use_id;
+};
+__device__ __forceinline__ SsTrackTerms ss_track_terms(const double* x, const double* P, const double* a,
+                                                       double mc_lambda, double id_weight) {
+    SsTrackTerms t;
+    double S[4];
+    cv8_project<CV8_XYAH>(x, P, 0.0, S);
+#pragma unroll
+    for (int i = 0; i < 4; i++) { t.x[i] = x[i]; t.inv[i] = 1.0 / sqrt(S[i]); }
+    t.mfac = 2.0 - a[SS_MOTION];
+    t.has_vel = a[SS_HAS_VEL] != 0.0;
+    t.px = x[0] + a[SS_VX]; t.py = x[1] + a[SS_VY];
+    double lam = mc_lambda + (1.0 - mc_lambda) * fmin(a[SS_AGE] / 10.0, 1.0) * 0.1;
+    lam = lam * (0.8 + 0.4 * a[SS_MOTION]);
+    if (a[SS_APPEAR] < 0.5) lam = fmin(lam * 1.2, 0.99);
+    lam = fmin(fmax(lam, 0.1), 0.99);
+    t.lam = lam; t.oml = 1.0 - lam;
+    t.q95 = a[SS_QUALITY] > 0.8;
+    t.h98 = a[SS_HITS] > 10.0 && a[SS_TSU] == 0.0;
+    t.s97 = a[SS_HI_STREAK] > 3.0;
+    t.s105 = a[SS_LO_STREAK] > 2.0;
+    t.use_id = id_weight > 0.0;
+    t.idf = 1.0 - id_weight * fmin(a[SS_HITS] / 10.0, 1.0);
+    t.quality = a[SS_QUALITY]; t.conf = a[SS_CONF]; t.cls = a[SS_CLS];
+    return t;
+}
+// c = appearance distance of the pair, z = the detection as xyah
+__device__ __forceinline__ double ss_pair_cost(const SsTrackTerms& t, double c, const double* z, double dq, double dconf,
+                                               double dcls) {
+    double gd = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const double d = z[i] - t.x[i];
+        const double q = d * t.inv[i];
+        gd = i == 0 ? q * q : gd + q * q;
+    }
+    if (gd > SS_CHI2INV95_4) c = SS_INFTY_COST;
+    double motion = gd * t.mfac;
+    if (t.has_vel) {
+        const double dx = z[0] - t.px, dy = z[1] - t.py;
+        const double err = sqrt(dx * dx + dy * dy);
+        motion = motion * (1.0 + fmin(err / 50.0, 1.0));
+    }
+    c = t.lam * c + t.oml * motion;
+    if (t.q95) c = c * 0.95;
+    if (t.h98) c = c * 0.98;
+    if (t.s97) c = c * 0.97;
+    if (t.s105) c = c * 1.05;
+    if (t.use_id) c = c * t.idf;
+    const double q = 1.0 - ((t.quality + dq) / 2.0 - 0.5) * 0.2;
+    c = c * fmin(fmax(q, 0.8), 1.2);
+    if (t.cls == dcls) c = c * 0.9;
+    if (t.conf > 0.7 && dconf > 0.7) c = c * 0.9;
+    else if (t.conf < 0.3 || dconf < 0.3) c = c * 1.1;
+    return c;
+}
+
 // _enhance_cost_matrix (linear_assignment.py:251-273) for one entry; detection quality_score, conf, cls
 __device__ __forceinline__ double ss_enhance_entry(double c, const double* a, double dq, double dconf, double dcls) {
     const double q = 1.0 - ((a[SS_QUALITY] + dq) / 2.0 - 0.5) * 0.2;         // :355-364
