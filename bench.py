@@ -104,7 +104,7 @@ def parse():
         # runnable mode) make every low-confidence detection a track that lives max_age frames: ~12 live
         # tracks per object at steady state, hence the track / pool capacities and the long warm-up.
         for name, v in (("steps", 30), ("warmup", 90), ("objects", 100), ("det_cap", 128), ("track_cap", 2048),
-                        ("pool_cap", 8192), ("emb_dim", 768), ("streams", 256)):
+                        ("pool_cap", 8192), ("emb_dim", 768), ("streams", 512)):       # 4096 streams / 8 GPUs
             if getattr(a, name) is None or (name in ("warmup", "streams") and getattr(a, name) == ap.get_default(name)):
                 setattr(a, name, v)
     if a.emb_dim is None:
@@ -650,7 +650,7 @@ def run_gpu_arm(args):
 # attached to the headline line as "configs": device value, ms/step, roofline fraction, e2e.
 SUB_CONFIGS = [
     ("C3_botsort_1024x200_e512", ["--tracker", "botsort", "--steps", "10", "--warmup", "10"]),
-    ("C4_strongsort_256x100_e768_b50", ["--tracker", "strongsort", "--steps", "8", "--warmup", "70"]),
+    ("C4_strongsort_512x100_e768_b50", ["--tracker", "strongsort", "--steps", "8", "--warmup", "70"]),
     ("C5_deepocsort_crowd_1024x480_e512", ["--tracker", "deepocsort", "--objects", "480", "--det-cap", "512",
                                           "--track-cap", "768", "--emb-dim", "512", "--steps", "4", "--warmup", "6"]),
     ("C5_boosttrack_crowd_1024x480_e512", ["--tracker", "boosttrack", "--objects", "480", "--det-cap", "512",

@@ -1085,6 +1085,123 @@ __device__ void ss_bank_append(const SsView& v, const SsParams& pr, int t, int s
     __syncwarp();
 }
 
+// partial_fit for ONE target on a register-resident copy of its sample list (position i of the list lives in
+// lane i % 32, register i / 32; the distinct-slot list one entry per lane): the same appends and evictions, in
+// the same order and with the same tie rule as ss_bank_append / ss_bank_evict, but an eviction is a handful of
+// shuffles instead of two scans of global memory and a round trip through lane 0.  `confirmed`: append the
+// ring's features in ring order (linear_assignment.py:553-573); else trim an inactive target to `keep`
+// (:575-593).  Returns false (nothing touched) when the lists do not fit the registers; the caller then takes
+// the global-memory path.  All lanes converged.
+template <int J>
+__device__ __noinline__ bool ss_bank_pass2_regs(const SsView& v, const SsParams& pr, int t, bool confirmed, int keep) {
+    const int lane = lane_id();
+    int* ti = v.tint(t);
+    int n = ti[TI_NBANK], nd = ti[TI_NDIST];
+    const int nr = confirmed ? ti[TI_NRING] : 0;
+    if (n > 32 * J || pr.budget > 32 * J || nd + nr > 32) return false;
+    const double* pq = v.pq();
+    int* bs = v.bslot(t);
+    int* bq = v.bseq(t);
+    int slot[J], seq[J];
+    double q[J];
+    unsigned alive = 0;
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+        const int i = j * 32 + lane;
+        slot[j] = -1; seq[j] = 0; q[j] = CUDART_INF;
+        if (i < n) { slot[j] = bs[i]; seq[j] = bq[i]; q[j] = pq[slot[j]]; alive |= 1u << j; }
+    }
+    int ds = -1, dc = 0, dc0 = 0;                              // distinct slot, its count now and at load
+    if (lane < nd) { ds = v.dslot(t)[lane]; dc = dc0 = v.dcnt(t)[lane]; }
+    double minq = n ? v.bminq(t) : CUDART_INF;
+    int nseq = ti[TI_SEQ];
+
+    // removes the worst entry = lowest quality, newest (largest seq); returns its position
+    auto evict = [&]() -> int {
+        double wq = CUDART_INF;
+        int ws = -1, wp = -1, wslot = -1;
+#pragma unroll
+        for (int j = 0; j < J; j++)
+            if ((alive >> j & 1) && (q[j] < wq || (q[j] == wq && seq[j] > ws))) { wq = q[j]; ws = seq[j]; wp = j * 32 + lane; wslot = slot[j]; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double oq = shfl_xor_d(wq, o);
+            const int os = __shfl_xor_sync(BM_FULL, ws, o), op = __shfl_xor_sync(BM_FULL, wp, o),
+                      osl = __shfl_xor_sync(BM_FULL, wslot, o);
+            if (oq < wq || (oq == wq && os > ws)) { wq = oq; ws = os; wp = op; wslot = osl; }
+        }
+#pragma unroll
+        for (int j = 0; j < J; j++) if (wp == j * 32 + lane) alive &= ~(1u << j);
+        n--;
+        const unsigned b = __ballot_sync(BM_FULL, lane < nd && ds == wslot);
+        if (b) {
+            const int di = __ffs(b) - 1;
+            const int cnt = __shfl_sync(BM_FULL, dc, di) - 1;
+            if (lane == di) dc = cnt;
+            if (cnt == 0) {                                    // the slot leaves the list: the last entry takes its place
+                const int c0 = __shfl_sync(BM_FULL, dc0, di);
+                const int lds = __shfl_sync(BM_FULL, ds, nd - 1), ldc = __shfl_sync(BM_FULL, dc, nd - 1),
+                          ldc0 = __shfl_sync(BM_FULL, dc0, nd - 1);
+                if (lane == di) { ds = lds; dc = ldc; dc0 = ldc0; }
+                if (lane == nd - 1) { ds = -1; dc = 0; dc0 = 0; }
+                nd--;
+                if (lane == 0) {
+                    const int nv = v.pbank()[wslot] - c0;
+                    v.pbank()[wslot] = nv;
+                    if (nv == 0 && v.pring()[wslot] == 0) ss_pool_release(v, wslot);
+                }
+            }
+        }
+        double m = CUDART_INF;
+#pragma unroll
+        for (int j = 0; j < J; j++) if (alive >> j & 1) m = fmin(m, q[j]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmin(m, shfl_xor_d(m, o));
+        minq = m;
+        return wp;
+    };
+
+    if (confirmed) {
+        const int* rg = v.ring(t);
+        for (int i = 0; i < nr; i++) {
+            const int sl = rg[i];
+            const double qi = pq[sl];
+            if (n >= pr.budget && !(qi > minq)) continue;      // it would be the entry that is dropped again
+            const int h = n >= pr.budget ? evict() : n;        // the list has no holes here: an eviction's is refilled at once
+#pragma unroll
+            for (int j = 0; j < J; j++)
+                if (h == j * 32 + lane) { slot[j] = sl; seq[j] = nseq; q[j] = qi; alive |= 1u << j; }
+            nseq++;
+            minq = n == 0 ? qi : fmin(minq, qi);
+            n++;
+            const unsigned b = __ballot_sync(BM_FULL, lane < nd && ds == sl);
+            if (b) { if (lane == __ffs(b) - 1) dc++; }
+            else { if (lane == nd) { ds = sl; dc = 1; dc0 = 0; } nd++; }
+        }
+    } else {
+        while (n > keep) evict();
+    }
+    // write back, compacting the holes a trim leaves
+    int base = 0;
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+        const bool a = alive >> j & 1;
+        const unsigned m = __ballot_sync(BM_FULL, a);
+        if (a) {
+            const int pos = base + __popc(m & ((1u << lane) - 1u));
+            bs[pos] = slot[j]; bq[pos] = seq[j];
+        }
+        base += __popc(m);
+    }
+    if (lane < nd) {
+        v.dslot(t)[lane] = ds; v.dcnt(t)[lane] = dc;
+        if (dc != dc0) v.pbank()[ds] += dc - dc0;
+    }
+    if (lane == 0) { ti[TI_NBANK] = n; ti[TI_NDIST] = nd; ti[TI_SEQ] = nseq; v.bminq(t) = minq; }
+    __syncwarp();
+    return true;
+}
+
 // Everything a track holds goes back to the pool (the track left the lost buffer or never entered it); one
 // warp, lanes over the ring / sample-list entries (several entries may reference one slot: atomic counts).
 __device__ void ss_track_release_warp(const SsView& v, int t) {
@@ -1141,7 +1258,7 @@ __device__ int block_compact(int n, int* ws, Pred pred, Emit emit) {
 }
 
 // K6: the rest of Tracker.update (tracker.py:137-181) and StrongSort._format_outputs
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 2)
 ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, double* __restrict__ out,
                    int* __restrict__ nout, int out_rows) {
     const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
@@ -1418,7 +1535,9 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
             const int p = work[q];
             const int t = p < nT ? order[p] : lost[p - nT];
             int* ti = v.tint(t);
-            if (p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE) {
+            const bool conf = p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE;
+            if (ss_bank_pass2_regs<5>(v, pr, t, conf, keep)) continue;
+            if (conf) {
                 const int nr = ti[TI_NRING];
                 // the list's minimum quality only rises while entries are replaced: a ring feature that does not
                 // beat it now cannot enter later in this loop either (while there is room, every feature enters)
@@ -1504,7 +1623,7 @@ struct SsEngine {
     bm::SsState st;
     bm::SsParams pr;
     std::vector<void*> allocs;
-    int device = 0;
+    int device = 0, n_sm = 148;
     cudaEvent_t ev[7];
     bool timing = false, timed = false;
 };
@@ -1556,6 +1675,7 @@ int bm_strongsort_create(const bm_strongsort_config* cfg, int n_streams, int tra
     const size_t S = n_streams, T = track_cap, D = det_cap, P = pool_cap, B = st.B, M = st.M, E = pr.E;
     st.wki_stride = T * 3 + 2 * T + 2 * T + D + (2 * T + D) + D + (size_t)pr.max_age + 2 + 6 * M + 8;
     cudaError_t r = cudaGetDevice(&e->device);
+    if (r == cudaSuccess) r = cudaDeviceGetAttribute(&e->n_sm, cudaDevAttrMultiProcessorCount, e->device);
     auto A = [&](auto** p, size_t n) { if (r == cudaSuccess) r = ss_alloc(e, p, n); };
     A(&st.mean, S * T * 8); A(&st.covb, S * T * bm::XA_P); A(&st.tab, S * T * bm::ST_FIELDS);
     A(&st.tint, S * T * bm::TI_COUNT); A(&st.ring, S * T * bm::SS_RING);
@@ -1653,7 +1773,9 @@ int bm_strongsort_step(void* handle, const float* d_dets, const int* d_ndets, co
     if (tm) cudaEventRecord(e->ev[4], s);
     bm::ss_update_kernel<<<dim3((st.Dcap + 3) / 4, st.S), 128, 0, s>>>(st, pr, d_embs);
     if (tm) cudaEventRecord(e->ev[5], s);
-    bm::ss_finalize_kernel<<<st.S, 512, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
+    // one CTA per stream at 64 registers: two 512-thread CTAs per SM while every stream gets a slot at once, else
+    // four of 256 threads (the kernel is a chain of dependent global-memory phases: residency, not width, hides it)
+    bm::ss_finalize_kernel<<<st.S, st.S > 2 * e->n_sm ? 256 : 512, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
     if (tm) { cudaEventRecord(e->ev[6], s); e->timed = true; }
     SS_CUDA(cudaGetLastError());
     return 0;
