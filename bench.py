@@ -495,11 +495,16 @@ def run_gpu_arm(args):
         eng.reset()
         pipe = HostPipeline(eng)
         rows_seen = 0
-        # embeddings of a frame are staged through pinned host memory (two buffers) when the tracker takes them
+        # embeddings (when the tracker takes them): the K timed frames sit in pinned host memory before the clock
+        # starts, as the detections do -- the timed region is H2D + step + D2H, not a host-side memcpy into a
+        # staging buffer; the warm-up frames (untimed, tens of GB) go through two pinned staging buffers
         p_e = [torch.empty(embs.shape[1:], dtype=torch.float32).pin_memory() for _ in range(2)] if bot else None
+        h_embs_timed = torch.from_numpy(embs[W:W + K]).pin_memory() if bot else None
 
         def submit(f):
             if bot:
+                if f >= W:
+                    return pipe.submit(h_dets[f], h_nd[f], h_embs_timed[f - W])
                 p_e[f & 1].copy_(torch.from_numpy(embs[f]))
                 return pipe.submit(h_dets[f], h_nd[f], p_e[f & 1])
             return pipe.submit(h_dets[f], h_nd[f])

@@ -10,7 +10,7 @@ from boxmot_b200 import _lib
 ERR_BITS = {1: "track capacity exceeded", 2: "detection capacity exceeded",
             4: "cost matrix larger than scratch", 8: "non-finite costs reached the assignment solver",
             16: "a track saw more distinct classes than the class-vote history holds",
-            32: "camera-motion warp with rotation or shear (needs a dense covariance: not supported)"}
+            32: "camera-motion warp the engine could not apply (reserved: rotating warps are handled by the dense-covariance path)"}
 
 
 def _ptr(t):

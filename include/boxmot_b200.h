@@ -97,8 +97,9 @@ int bm_deepocsort_create(const bm_deepocsort_config* cfg, int n_streams, int tra
 /* One frame for all streams.  d_dets / d_ndets / d_out / d_nout as bm_ocsort_step.
  * d_embs [S][det_cap][emb_dim] float32, row-aligned with d_dets (may be NULL when
  * embedding_off).  d_warps [S][6] float64, row-major 2x3 camera-motion warp applied to every
- * track before its predict, or NULL (cmc_off / identity); a warp with rotation or shear sets
- * error bit 32 (the block-form covariance cannot hold it) and is not applied. */
+ * track before its predict, or NULL (cmc_off / identity).  Any warp is applied: without rotation or
+ * shear on the block-form covariance; from a track's first rotating warp on, that track carries a
+ * dense 7x7 covariance (apply_affine_correction, deepocsort.py:191-208 + xysr_kf.py:111-135). */
 int bm_deepocsort_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
                        const double* d_warps, double* d_out, int* d_nout, void* stream);
 /* Durations (ms) of the six launches of the last step after bm_ocsort_time_kernels(handle, 1):
@@ -173,8 +174,9 @@ int bm_bytetrack_peek(void* handle, int stream_index, int* n_active, int* n_lost
  * fuse_score / embedding_distance / linear_assignment (boxmot/utils/matching.py:184-227,
  * :488-560, :230-321, :30-108).  ReID and CMC are side inputs: d_embs [S][det_cap][emb_dim]
  * float32 rows aligned with d_dets (NULL when with_reid = 0), d_warps [S][6] float64 row-major
- * 2x3 camera-motion warps or NULL for the identity (warps with rotation / shear set error bit
- * 32: they need a dense covariance).  Other buffers as bm_bytetrack_step.  One frame = three
+ * 2x3 camera-motion warps or NULL for the identity (any warp: a track switches to a dense 8x8
+ * covariance at its first warp with rotation / shear, multi_gmc, botsort_track.py:91-104).  Other
+ * buffers as bm_bytetrack_step.  One frame = three
  * launches: embedding kernel (feature preparation + cosine-distance contraction), the step,
  * the feature EMA. */
 typedef struct bm_botsort_config {
