@@ -1417,7 +1417,7 @@ ocs_assoc_kernel(OcsState st, OcsParams pr, const float* __restrict__ dets) {
 // One thread per (track, detection) pair of the frame: KalmanBoxTracker.update with a
 // real detection (ocsort.py:136-169) + KalmanFilterXYSR.update incl. ORU.
 template <bool DENSE>
-__global__ void __launch_bounds__(K3_NT)
+__global__ void __launch_bounds__(K3_NT, DENSE ? 1 : 8)
 ocs_update_kernel_t(OcsState st, OcsParams pr, const float* __restrict__ dets) {
     const int chunks = (st.Dcap + K3_NT - 1) / K3_NT;
     const int s = blockIdx.x / chunks;
