@@ -34,8 +34,8 @@ constexpr int TC_M = 128, TC_KC = 32, TC_NMAX = 256, TC_NT = 256;
 constexpr uint32_t TC_TMEM_COLS = 256;
 
 __host__ __device__ inline size_t cosine_tc_smem_bytes() {
-    // plain path: 96 KB of tiles; the fast path (cosine_tc_fast) needs 3 tiles of (128 + 128) rows = the same
-    return 1024 /*alignment slack*/ + 2 * TC_M * 128 + 2 * TC_NMAX * 128 + 128;
+    // fast path (cosine_tc_fast): 3 A stages + 2 B stages + 2 lo tiles = 106 KB; the plain path uses the first 96 KB
+    return 1024 /*alignment slack*/ + (3 + 1) * (size_t)TC_M * 128 + (2 + 1) * (size_t)112 * 128 + 64;
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -132,87 +132,118 @@ struct CosineProblem {
 //   * tcgen05 reads a tf32 operand from the upper 19 bits of an fp32 word, so the RAW fp32 tile is the `hi`
 //     operand (hi = x truncated); cp.async drops the gathered 16-byte pieces straight into the canonical
 //     K-major SWIZZLE_128B layout -- no register pass at all for hi;
-//   * lo = x - trunc(x) (exact in fp32) costs one AND and one SUB per element, computed from the landed tile;
-//   * hi tiles are double-buffered (the copy of chunk k + 1 flies during the MMAs of chunk k), one lo tile;
-//     96 KB per CTA -> two CTAs per SM, column tiles of <= 128 detections.
+//   * lo = x - trunc(x) (exact in fp32) costs one AND, one SUB and one ADD per element, from the landed tile;
+//   * the A tile (bank rows: DRAM) has a ring of THREE stages, its copies are issued two chunks ahead; the B
+//     tile (the frame's detections: L2 hits, every row tile of the stream re-reads them) a ring of two; one lo
+//     tile each.  106 KB per CTA -> two CTAs per SM (tools/gather_bw.cu: residency beats ring depth), which is
+//     why a column tile is 112 detections, not 128.
 // Same three products (hi.hi + hi.lo + lo.hi), hi truncated instead of rounded, lo rounded; the cross terms
 // accumulate in their own TMEM columns (see the MMA loop).  Error against scipy: tests/test_gpu_units.py.
-constexpr int TC3_N = 128;
-constexpr size_t TC3_TILE = (size_t)(TC_M + TC3_N) * 128;                // A rows then B rows, 128 bytes per row
-__host__ __device__ inline size_t cosine_tc3_smem_bytes() { return 1024 + 3 * TC3_TILE + 64; }
+constexpr int TC3_N = 112;
+constexpr int TC3_RA = 3, TC3_RB = 2;
+constexpr size_t TC3_AT = (size_t)TC_M * 128, TC3_BT = (size_t)TC3_N * 128;        // bytes of an A / B stage
+constexpr size_t TC3_BYTES = TC3_RA * TC3_AT + TC3_RB * TC3_BT + TC3_AT + TC3_BT;   // + the two lo tiles
+static_assert(TC3_AT % 1024 == 0 && TC3_BT % 1024 == 0, "SWIZZLE_128B tiles are 1024-byte aligned");
 
 __device__ __forceinline__ void tc_cp16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ uint4 tc_lo4(const uint4 x) {
+    // + 0x1000: the tensor core drops the low 13 bits of lo as well; the half-ulp offset turns that truncation
+    // into round-to-nearest
+    uint4 l;
+    l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(x.x & 0xFFFFE000u)) + 0x1000u;
+    l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(x.y & 0xFFFFE000u)) + 0x1000u;
+    l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(x.z & 0xFFFFE000u)) + 0x1000u;
+    l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(x.w & 0xFFFFE000u)) + 0x1000u;
+    return l;
 }
 
 __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, unsigned char* sm, uint32_t tmem,
                                                uint64_t* mbar) {
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
-    unsigned char* hi[2] = {sm, sm + TC3_TILE};
-    unsigned char* lo = sm + 2 * TC3_TILE;
+    unsigned char* hiA = sm;
+    unsigned char* hiB = sm + TC3_RA * TC3_AT;
+    unsigned char* loA = hiB + TC3_RB * TC3_BT;
+    unsigned char* loB = loA + TC3_AT;
     const uint32_t bar = smem_u32(mbar);
     const int rows = min(TC_M, pb.nA - r0);
     const int nk = pb.E / TC_KC;
-    constexpr int PA = TC_M * 8 / TC_NT, PB = TC3_N * 8 / TC_NT;      // 16-byte pieces per thread and chunk
+    constexpr int PA = TC_M * 8 / TC_NT, PB = (TC3_N * 8 + TC_NT - 1) / TC_NT;     // 16-byte pieces per thread and chunk
     float nn_min = CUDART_INF_F;
     uint32_t phase = 0;
     for (int c0 = 0; c0 < pb.nB; c0 += TC3_N) {
         const int cols = min(TC3_N, pb.nB - c0);
         const int npad = max(16, (cols + 15) & ~15);
         const uint32_t idesc = tc_idesc(npad);
-        const float* src[PA + PB];                                    // this thread's pieces: global source (nullptr = padding)
-        int off[PA + PB];                                             // and swizzled byte offset in a tile (-1 = beyond npad)
+        const float* srcA[PA];                                        // this thread's pieces: global source (nullptr = padding)
+        const float* srcB[PB];
+        int offA[PA], offB[PB];                                       // swizzled byte offset in a stage (B: -1 = beyond npad)
 #pragma unroll
         for (int j = 0; j < PA; j++) {
             const int q = tid + TC_NT * j, r = q >> 3, c = q & 7;
-            src[j] = r < rows ? pb.A + (size_t)pb.ra[r0 + r] * pb.E + c * 4 : nullptr;
-            off[j] = r * 128 + ((c ^ (r & 7)) << 4);
+            srcA[j] = r < rows ? pb.A + (size_t)pb.ra[r0 + r] * pb.E + c * 4 : nullptr;
+            offA[j] = r * 128 + ((c ^ (r & 7)) << 4);
         }
 #pragma unroll
         for (int j = 0; j < PB; j++) {
             const int q = tid + TC_NT * j, r = q >> 3, c = q & 7;
-            src[PA + j] = r < cols ? pb.B + (size_t)pb.rb[c0 + r] * pb.E + c * 4 : nullptr;
-            off[PA + j] = r < npad ? TC_M * 128 + r * 128 + ((c ^ (r & 7)) << 4) : -1;
+            srcB[j] = r < cols ? pb.B + (size_t)pb.rb[c0 + r] * pb.E + c * 4 : nullptr;
+            offB[j] = r < npad ? r * 128 + ((c ^ (r & 7)) << 4) : -1;         // npad <= TC3_N covers q beyond the tile
         }
-        // padding pieces are never copied: zero them in both hi tiles once (lo follows from hi)
+        // padding pieces are never copied: zero them in every hi stage once (lo follows from hi)
 #pragma unroll
-        for (int j = 0; j < PA + PB; j++)
-            if (!src[j] && off[j] >= 0) {
-                *reinterpret_cast<uint4*>(hi[0] + off[j]) = make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(hi[1] + off[j]) = make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < PA; j++)
+            if (!srcA[j])
+                for (int i = 0; i < TC3_RA; i++) *reinterpret_cast<uint4*>(hiA + i * TC3_AT + offA[j]) = make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int j = 0; j < PB; j++)
+            if (!srcB[j] && offB[j] >= 0)
+                for (int i = 0; i < TC3_RB; i++) *reinterpret_cast<uint4*>(hiB + i * TC3_BT + offB[j]) = make_uint4(0, 0, 0, 0);
+        // one commit group per call, in the order ... B(k) A(k + 1) | B(k + 1) A(k + 2) ...: "all but the newest
+        // group" is then exactly "A(k) and B(k) have landed, A(k + 1) may still fly"
+        auto issueA = [&](int k, int stage) {
+            if (k < nk) {
+                unsigned char* dst = hiA + (size_t)stage * TC3_AT;
+#pragma unroll
+                for (int j = 0; j < PA; j++)
+                    if (srcA[j]) tc_cp16(smem_u32(dst + offA[j]), srcA[j] + (size_t)k * TC_KC);
             }
-        auto issue = [&](int k) {
-            unsigned char* dst = hi[k & 1];
-#pragma unroll
-            for (int j = 0; j < PA + PB; j++)
-                if (src[j]) tc_cp16(smem_u32(dst + off[j]), src[j] + (size_t)k * TC_KC);
             asm volatile("cp.async.commit_group;" ::: "memory");
         };
-        issue(0);
-        for (int k = 0; k < nk; k++) {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");      // this thread's pieces of chunk k have landed
-            if (k > 0) { tc_mbar_wait(bar, phase); phase ^= 1u; }     // MMAs of chunk k - 1 done: lo and hi[(k+1)&1] are free
-            if (k + 1 < nk) issue(k + 1);                             // flies during the split, the MMAs and the next wait
-            const unsigned char* h = hi[k & 1];
+        auto issueB = [&](int k) {
+            if (k < nk) {
+                unsigned char* dst = hiB + (size_t)(k & 1) * TC3_BT;
 #pragma unroll
-            for (int j = 0; j < PA + PB; j++) {
-                if (off[j] < 0) continue;
-                const uint4 x = *reinterpret_cast<const uint4*>(h + off[j]);
-                uint4 l;
-                // + 0x1000: the tensor core drops the low 13 bits of lo as well; the half-ulp offset turns that
-                // truncation into round-to-nearest
-                l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(x.x & 0xFFFFE000u)) + 0x1000u;
-                l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(x.y & 0xFFFFE000u)) + 0x1000u;
-                l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(x.z & 0xFFFFE000u)) + 0x1000u;
-                l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(x.w & 0xFFFFE000u)) + 0x1000u;
-                *reinterpret_cast<uint4*>(lo + off[j]) = l;
+                for (int j = 0; j < PB; j++)
+                    if (srcB[j]) tc_cp16(smem_u32(dst + offB[j]), srcB[j] + (size_t)k * TC_KC);
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        issueA(0, 0);
+        issueB(0);
+        issueA(1, 1);
+        int sa = 0;                                                   // k % TC3_RA
+        for (int k = 0; k < nk; k++) {
+            asm volatile("cp.async.wait_group 1;" ::: "memory");      // this thread's pieces of A(k) and B(k) have landed
+            if (k > 0) { tc_mbar_wait(bar, phase); phase ^= 1u; }     // MMAs of chunk k - 1 done: its stages and lo are free
+            issueB(k + 1);                                            // stage (k + 1) & 1 = that of chunk k - 1
+            issueA(k + 2, sa == 0 ? 2 : sa - 1);                      // stage (k + 2) % 3 = that of chunk k - 1
+            const unsigned char* ha = hiA + (size_t)sa * TC3_AT;
+            const unsigned char* hb = hiB + (size_t)(k & 1) * TC3_BT;
+#pragma unroll
+            for (int j = 0; j < PA; j++)
+                *reinterpret_cast<uint4*>(loA + offA[j]) = tc_lo4(*reinterpret_cast<const uint4*>(ha + offA[j]));
+#pragma unroll
+            for (int j = 0; j < PB; j++)
+                if (offB[j] >= 0)
+                    *reinterpret_cast<uint4*>(loB + offB[j]) = tc_lo4(*reinterpret_cast<const uint4*>(hb + offB[j]));
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
             if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t dah = tc_smem_desc(smem_u32(h)), dal = tc_smem_desc(smem_u32(lo));
-                const uint64_t dbh = tc_smem_desc(smem_u32(h + TC_M * 128)), dbl = tc_smem_desc(smem_u32(lo + TC_M * 128));
+                const uint64_t dah = tc_smem_desc(smem_u32(ha)), dal = tc_smem_desc(smem_u32(loA));
+                const uint64_t dbh = tc_smem_desc(smem_u32(hb)), dbl = tc_smem_desc(smem_u32(loB));
 #pragma unroll
                 for (int kk = 0; kk < TC_KC / 8; kk++) {
                     const uint64_t adv = (uint64_t)((kk * 32) >> 4);
@@ -221,12 +252,13 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
                     // small terms get an accumulator of their own magnitude and the big one sees E / 8 additions
                     // instead of 3 E / 8
                     tc_mma_tf32(tmem, dah + adv, dbh + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
-                    tc_mma_tf32(tmem + TC3_N, dah + adv, dbl + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
-                    tc_mma_tf32(tmem + TC3_N, dal + adv, dbh + adv, idesc, 1u);
+                    tc_mma_tf32(tmem + 128u, dah + adv, dbl + adv, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                    tc_mma_tf32(tmem + 128u, dal + adv, dbh + adv, idesc, 1u);
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                              :: "r"(bar) : "memory");
             }
+            sa = sa == TC3_RA - 1 ? 0 : sa + 1;
         }
         tc_mbar_wait(bar, phase);
         phase ^= 1u;
@@ -250,19 +282,32 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
                 "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
                   "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15])
-                : "r"(taddr + (uint32_t)TC3_N) : "memory");
+                : "r"(taddr + 128u) : "memory");
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
             for (int j = 0; j < 16; j++) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
             if (rin) {
+                // fp32 from here on (the dot product is fp32-accurate; an fp64 divide per entry was 37 % of the
+                // kernel's stall samples): 1 - dot / (|a| |b|), error ~1e-7 on top of the product's
+                float o[16];
 #pragma unroll
                 for (int j = 0; j < 16; j++) {
                     const int c = cb + j;
-                    if (c < cols) {
-                        if (pb.raw == 1) { orow[c] = __uint_as_float(v[j]); continue; }
-                        const double cs = (double)__uint_as_float(v[j]) / ((double)na * (double)pb.nb[c0 + c]);
-                        if (pb.raw == 2) { nn_min = fminf(nn_min, (float)(1.0 - fmin(1.0, fmax(-1.0, cs)))); continue; }
-                        orow[c] = (float)fmax(0.0, 1.0 - cs);
+                    const float dot = __uint_as_float(v[j]);
+                    if (pb.raw == 1) { o[j] = dot; continue; }
+                    const float cs = c < cols ? dot / (na * pb.nb[c0 + c]) : 0.f;
+                    if (pb.raw == 2) { if (c < cols) nn_min = fminf(nn_min, 1.f - fminf(1.f, fmaxf(-1.f, cs))); continue; }
+                    o[j] = fmaxf(0.f, 1.f - cs);
+                }
+                if (pb.raw != 2) {
+                    float* dst = orow + cb;
+                    if (cb + 16 <= cols && ((uintptr_t)dst & 15) == 0) {
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4)
+                            *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) if (cb + j < cols) dst[j] = o[j];
                     }
                 }
             }
@@ -271,7 +316,7 @@ __device__ __forceinline__ void cosine_tc_fast(const CosineProblem& pb, int r0, 
         __syncthreads();
     }
     if (pb.raw == 2) {
-        float* part = reinterpret_cast<float*>(lo);
+        float* part = reinterpret_cast<float*>(loA);
         part[(wid >> 2) * TC_M + (wid & 3) * 32 + lane] = nn_min;
         __syncthreads();
         const int r = (wid & 3) * 32 + lane;
@@ -311,7 +356,7 @@ cosine_tc_kernel(ProblemFn problem) {
     const uint32_t tmem = *tmem_slot;
     if ((pb.E % TC_KC) == 0 && (((uintptr_t)pb.A | (uintptr_t)pb.B) & 15) == 0) {          // uniform over the CTA
         __syncthreads();                              // everyone has read tmem_slot: the fast path reuses that memory
-        uint64_t* mbar3 = reinterpret_cast<uint64_t*>(sm + 3 * TC3_TILE);
+        uint64_t* mbar3 = reinterpret_cast<uint64_t*>(sm + TC3_BYTES);
         if (tid == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(mbar3)));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
