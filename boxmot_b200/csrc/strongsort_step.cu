@@ -245,10 +245,69 @@ struct SsBankProblem {
 
 // K3: gated_metric (tracker.py:186-206) followed by _enhance_cost_matrix (linear_assignment.py:251-273,
 // the first thing min_cost_matching does to the metric's matrix) for every (confirmed track, detection).
-// A warp per track row, lanes over the detections: the projection of the Kalman state, its reciprocal square
-// roots, the adaptive lambda and the track's adjustment flags are evaluated once per row (ss_track_terms)
-// instead of once per entry; the frame's detection columns sit in shared memory as seven arrays.
-__global__ void __launch_bounds__(256)
+//
+// Exact screen.  An entry is lam * app + (1 - lam) * motion, motion >= 0, times factors of which the track's
+// are known and the detection's are >= 0.8 * 0.9 * 0.9; it is only ever compared with the stage thresholds
+// (<= max_cos_dist) and clamped above them (min_cost_matching, :67).  So a pair whose appearance term alone puts
+// it beyond the threshold needs no Mahalanobis / motion arithmetic -- any value above the threshold is the same
+// entry -- and a row without a pair that survives the screen needs none of the track's Kalman state either.
+// (1 - 1e-9 covers the roundings of the real chain.)
+__device__ __forceinline__ double ss_track_screen(const double* a, double mc_lambda, double id_weight) {
+    double lam = mc_lambda + (1.0 - mc_lambda) * fmin(a[SS_AGE] / 10.0, 1.0) * 0.1;
+    lam = lam * (0.8 + 0.4 * a[SS_MOTION]);
+    if (a[SS_APPEAR] < 0.5) lam = fmin(lam * 1.2, 0.99);
+    lam = fmin(fmax(lam, 0.1), 0.99);
+    double f = lam * (0.8 * 0.9 * 0.9) * (1.0 - 1e-9);
+    if (a[SS_QUALITY] > 0.8) f *= 0.95;
+    if (a[SS_HITS] > 10.0 && a[SS_TSU] == 0.0) f *= 0.98;
+    if (a[SS_HI_STREAK] > 3.0) f *= 0.97;
+    if (a[SS_LO_STREAK] > 2.0) f *= 1.05;
+    if (id_weight > 0.0) f *= 1.0 - id_weight * fmin(a[SS_HITS] / 10.0, 1.0);
+    return f;                                                    // <= 0 (id_weight > 1): no screening
+}
+
+// One row in full: the projection of the Kalman state, its reciprocal square roots, the adaptive lambda and the
+// track's adjustment flags are evaluated once per row (ss_track_terms), lanes over the detections.  Out of line:
+// the screening loop of the kernel keeps its registers.
+__device__ __noinline__ void ss_cost_row_full(const SsState& st, const SsParams& pr, int s, int p, int t, int n,
+                                              const double* dz, double screen) {
+    SsView v(st, s);
+    const int Dc = st.Dcap, lane = lane_id();
+    const double* dq = dz + 4 * Dc;
+    const double* dcf = dq + Dc;
+    const double* dcl = dcf + Dc;
+    const float* dist = v.dist();
+    double* cost = v.cost();
+    int* ti = v.tint(t);
+    const SsTrackTerms tt = ss_track_terms(v.mean(t), v.covb(t), v.tab(t), pr.mc_lambda, pr.id_weight);
+    const int nbank = ti[TI_NBANK], ndist = ti[TI_NDIST];
+    const int* ds = v.dslot(t);
+    int bits = 0;
+    for (int k = lane; k < n; k += 32) {
+        double app = SS_INFTY_COST;                          // metric.distance: no samples (:616-617)
+        if (nbank > 0) {
+            float mn = CUDART_INF_F;
+            for (int i = 0; i < ndist; i++) mn = fminf(mn, dist[(size_t)ds[i] * Dc + k]);
+            app = (double)mn;
+        }
+        if (screen > 0.0 && app * screen > pr.max_cos_dist) { cost[(size_t)p * Dc + k] = SS_INFTY_COST; continue; }
+        const double z[4] = {dz[k], dz[Dc + k], dz[2 * Dc + k], dz[3 * Dc + k]};
+        const double cf = dcf[k];
+        const double c = ss_pair_cost(tt, app, z, dq[k], cf, dcl[k]);
+        cost[(size_t)p * Dc + k] = c;
+        // bit 0 / 1: some high- / medium-confidence detection is within the stage's threshold of this track
+        // (the cascade skips the assignment of a level none of whose tracks has the stage's bit)
+        if (cf >= pr.conf_hi) { if (c <= pr.max_cos_dist * 0.8) bits |= 1; }
+        else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bits |= 2; }
+    }
+    for (int o = 16; o > 0; o >>= 1) bits |= __shfl_xor_sync(BM_FULL, bits, o);
+    if (lane == 0 && bits) ti[TI_FEAS] |= bits;
+}
+
+// A warp takes 32 rows at a time: each lane first fetches ONE row's list slot, state, screen factor and first
+// sample slot (32 rows' dependent loads in flight at once), then the warp walks the rows with the lanes over the
+// detections; the frame's detection columns sit in shared memory as seven arrays.
+__global__ void __launch_bounds__(256, 4)
 ss_cost_kernel(SsState st, SsParams pr) {
     extern __shared__ double ss_cost_sm[];
     const int s = blockIdx.y;
@@ -256,46 +315,56 @@ ss_cost_kernel(SsState st, SsParams pr) {
     const int nT = v.hdr()[SH_NTRACKS], n = v.hdr()[SH_NDET];
     if (nT <= 0 || n <= 0) return;
     const int Dc = st.Dcap;
-    double* dz = ss_cost_sm;                     // [4][Dc] xyah
-    double* dq = dz + 4 * Dc;                    // quality, conf, cls
-    double* dcf = dq + Dc;
-    double* dcl = dcf + Dc;
+    double* dz = ss_cost_sm;                     // [4][Dc] xyah, then quality, conf, cls
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
         const double* d = v.dtab(k);
         dz[k] = d[DT_XYAH]; dz[Dc + k] = d[DT_XYAH + 1]; dz[2 * Dc + k] = d[DT_XYAH + 2]; dz[3 * Dc + k] = d[DT_XYAH + 3];
-        dq[k] = d[DT_QUALITY]; dcf[k] = d[DT_CONF]; dcl[k] = d[DT_CLS];
+        dz[4 * Dc + k] = d[DT_QUALITY]; dz[5 * Dc + k] = d[DT_CONF]; dz[6 * Dc + k] = d[DT_CLS];
     }
     __syncthreads();
     const float* dist = v.dist();
     double* cost = v.cost();
     const int lane = lane_id(), wpb = blockDim.x >> 5;
-    for (int p = blockIdx.x * wpb + (threadIdx.x >> 5); p < nT; p += gridDim.x * wpb) {
-        const int t = v.order()[p];
-        const double* a = v.tab(t);
-        if (a[ST_STATE] != (double)ST_CONFIRMED_STATE) continue;             // uniform over the warp
-        int* ti = v.tint(t);
-        const SsTrackTerms tt = ss_track_terms(v.mean(t), v.covb(t), a, pr.mc_lambda, pr.id_weight);
-        const int nbank = ti[TI_NBANK], ndist = ti[TI_NDIST];
-        const int* ds = v.dslot(t);
-        int bits = 0;
-        for (int k = lane; k < n; k += 32) {
-            double app = SS_INFTY_COST;                          // metric.distance: no samples (:616-617)
-            if (nbank > 0) {
-                float mn = CUDART_INF_F;
-                for (int i = 0; i < ndist; i++) mn = fminf(mn, dist[(size_t)ds[i] * Dc + k]);
-                app = (double)mn;
+    for (int base = (blockIdx.x * wpb + (threadIdx.x >> 5)) * 32; base < nT; base += gridDim.x * wpb * 32) {
+        const int p = base + lane;
+        int t = -1, nbank = 0, ndist = 0, ds0 = 0;
+        double screen = 0.0;
+        bool conf = false;
+        if (p < nT) {
+            t = v.order()[p];
+            const double* a = v.tab(t);
+            conf = a[ST_STATE] == (double)ST_CONFIRMED_STATE;
+            if (conf) {
+                const int* ti = v.tint(t);
+                nbank = ti[TI_NBANK]; ndist = ti[TI_NDIST];
+                if (nbank > 0 && ndist > 0) ds0 = v.dslot(t)[0];
+                screen = ss_track_screen(a, pr.mc_lambda, pr.id_weight);
             }
-            const double z[4] = {dz[k], dz[Dc + k], dz[2 * Dc + k], dz[3 * Dc + k]};
-            const double cf = dcf[k];
-            const double c = ss_pair_cost(tt, app, z, dq[k], cf, dcl[k]);
-            cost[(size_t)p * Dc + k] = c;
-            // bit 0 / 1: some high- / medium-confidence detection is within the stage's threshold of this track
-            // (the cascade skips the assignment of a level none of whose tracks has the stage's bit)
-            if (cf >= pr.conf_hi) { if (c <= pr.max_cos_dist * 0.8) bits |= 1; }
-            else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bits |= 2; }
         }
-        for (int o = 16; o > 0; o >>= 1) bits |= __shfl_xor_sync(BM_FULL, bits, o);
-        if (lane == 0 && bits) ti[TI_FEAS] |= bits;
+        unsigned cm = __ballot_sync(BM_FULL, conf);
+        while (cm) {
+            const int r = __ffs(cm) - 1;
+            cm &= cm - 1;
+            const int rt = __shfl_sync(BM_FULL, t, r), rnb = __shfl_sync(BM_FULL, nbank, r),
+                      rnd = __shfl_sync(BM_FULL, ndist, r), rds0 = __shfl_sync(BM_FULL, ds0, r);
+            const double rsc = shfl_d(screen, r);
+            const int rp = base + r;
+            bool open = !(rsc > 0.0) || (rnb > 0 && rnd <= 0);
+            if (!open) {
+                const int* ds = v.dslot(rt);
+                for (int k = lane; k < n; k += 32) {
+                    double app = SS_INFTY_COST;
+                    if (rnb > 0) {
+                        float mn = dist[(size_t)rds0 * Dc + k];
+                        for (int i = 1; i < rnd; i++) mn = fminf(mn, dist[(size_t)ds[i] * Dc + k]);
+                        app = (double)mn;
+                    }
+                    if (app * rsc > pr.max_cos_dist) cost[(size_t)rp * Dc + k] = SS_INFTY_COST;
+                    else open = true;
+                }
+            }
+            if (__any_sync(BM_FULL, open)) ss_cost_row_full(st, pr, s, rp, rt, n, dz, rsc);
+        }
     }
 }
 
