@@ -141,6 +141,7 @@ _SIGS = {
     "bm_strongsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_strongsort_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
                                        c_void_p]),
+    "bm_strongsort_set_groups": (c_int, [c_void_p, c_int]),
     "bm_strongsort_usage": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                     c_void_p]),
     "bm_strongsort_debug_copy": (c_int, [c_void_p, c_int, c_int, c_void_p, ctypes.c_size_t, c_void_p]),

@@ -750,6 +750,16 @@ class StrongSortEngine:
     def status(self, raise_on_error=True):
         return self.counters(raise_on_error)
 
+    def set_stream_groups(self, groups):
+        """Step the streams as ``groups`` independent groups on CUDA streams of their own (forked from / joined
+        into the current stream inside ``step``); returns the number in use.  Results do not depend on it."""
+        with torch.cuda.device(self.device):
+            n = _lib.lib().bm_strongsort_set_groups(self._h, int(groups))
+        if n < 0:
+            _lib.check(n, "bm_strongsort_set_groups")
+        self.groups = n
+        return n
+
     def usage(self):
         """Over all streams: (track slots in use, pool slots in use, vectors referenced by a sample list)."""
         a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)

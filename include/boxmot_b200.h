@@ -248,6 +248,9 @@ int bm_strongsort_counters(void* handle, int* err_bits, unsigned long long* out4
 /* Capacity planning: over all streams, the largest number of track slots in use (tracks + lost buffer),
  * of pool slots in use and of vectors referenced by a sample list (rows of the contraction) right now. */
 int bm_strongsort_usage(void* handle, int* max_tracks, int* max_pool_used, int* max_live, void* stream);
+/* Stream groups for the StrongSORT engine; see bm_ocsort_set_groups.  Results do not depend on it; measured at
+ * configs[3] it does not pay (one chain 6.58 ms, 2-8 groups 6.9 ms), so the default is one chain. */
+int bm_strongsort_set_groups(void* handle, int groups);
 /* Debug: host copy of one stream's scratch (which = 0: the cascade's integer work area, 1: the cost matrix
  * [track_cap][det_cap] float64 by list position and sorted detection, 2: the sorted detection table). */
 int bm_strongsort_debug_copy(void* handle, int which, int stream_index, void* h_dst, size_t nbytes, void* stream);

@@ -92,6 +92,42 @@ def test_strongsort_engine_batched_streams_match_oracle():
     assert c["track_updates"] == sum(o.n_updates for o in oracles)
 
 
+def test_strongsort_stream_groups_do_not_change_results():
+    """bm_strongsort_set_groups: the same frames stepped as 1 chain and as 3 ragged groups of streams on CUDA
+    streams of their own give identical rows, Kalman state and track tables (11 streams: groups of 3, 4, 4)."""
+    from boxmot_b200.engine import StrongSortEngine
+    from boxmot_b200.synth import make_batch
+    S, K, F, D, E = 11, 20, 30, 64, 64
+    kw = dict(STRONGSORT_YAML, nn_budget=25, max_age=12)
+    dets, nd, embs = make_batch(S, K, F, D, emb_dim=E, first_stream=2100)
+    d_dets, d_nd, d_embs = torch.as_tensor(dets.astype(np.float32)).cuda(), torch.as_tensor(nd).cuda(), torch.as_tensor(embs).cuda()
+
+    def run(groups):
+        eng = StrongSortEngine(S, track_cap=512, det_cap=D, pool_cap=2048, emb_dim=E, **kw)
+        assert eng.set_stream_groups(groups) == groups
+        rows = []
+        for f in range(F):
+            out, nout = eng.step(d_dets[f], d_nd[f], d_embs[f])
+            rows.append((out.cpu().numpy(), nout.cpu().numpy()))
+        eng.status()
+        state = [eng.peek(s) for s in (0, 3, 10)]
+        c = eng.counters()
+        eng.close()
+        return rows, state, c
+
+    base, st0, c0 = run(1)
+    rows, st1, c1 = run(3)
+    assert c0 == c1 and c0["matches"] > 100
+    for f in range(F):
+        assert np.array_equal(base[f][1], rows[f][1])
+        for s in range(S):
+            n = base[f][1][s]
+            assert np.array_equal(base[f][0][s, :n], rows[f][0][s, :n]), (f, s)
+    for a, b in zip(st0, st1):
+        for x, y in zip(a, b):
+            assert np.array_equal(np.asarray(x), np.asarray(y))
+
+
 def _lsa(cost_list):
     from boxmot_b200 import _lib
     B = len(cost_list)
