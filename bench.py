@@ -109,7 +109,7 @@ def parse():
                 setattr(a, name, v)
     if a.emb_dim is None:
         a.emb_dim = 512
-    for name, dflt, dbot in (("steps", 290, 40), ("objects", 100, 200), ("det_cap", 128, 256), ("track_cap", 256, 512)):
+    for name, dflt, dbot in (("steps", 290, 40), ("objects", 100, 200), ("det_cap", 128, 256), ("track_cap", 256, 384)):     # BoT-SORT: pool ~ 160 tracks at 200 objects/frame; 384 slots = 4 step CTAs per SM (512: 3)
         if getattr(a, name) is None:
             setattr(a, name, dbot if bot else (40 if (emb and name == "steps") else dflt))
     if not emb:
