@@ -141,6 +141,8 @@ _SIGS = {
     "bm_strongsort_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bm_strongsort_counters": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_ulonglong * 4),
                                        c_void_p]),
+    "bm_bytetrack_select_class": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
+    "bm_boosttrack_hold_frame": (c_int, [c_void_p, c_int, c_void_p]),
     "bm_strongsort_set_groups": (c_int, [c_void_p, c_int]),
     "bm_strongsort_usage": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                     c_void_p]),

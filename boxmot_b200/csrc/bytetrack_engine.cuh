@@ -51,6 +51,12 @@ struct ByteState {
     float* etn;        // [S][Tcap] |smooth_feat| by row position
     float* edn;        // [S][Dcap] |detection feature| by column position
     int tensor_cores;  // 1: tcgen05 contraction (csrc/cosine_tc.cuh), 0: fp32 FFMA tiles in bot_embed_kernel
+    // per_class mode (bm_bytetrack_select_class): the active lists of the classes that are not the current one; their
+    // slots are in use although they are in neither st.act nor st.lost
+    int* pc_act = nullptr;    // [S][pc_C][Tcap]
+    int* pc_n = nullptr;      // [S][pc_C]
+    int* pc_meta = nullptr;   // [S][2] current class (-1: none), frame counter at the frame's start
+    int pc_C = 0;
 };
 
 // Streams [s0, s0 + n) as an engine of their own (every array is stream-major); see ocs_substate.
@@ -58,6 +64,7 @@ inline ByteState byte_substate(const ByteState& st, int s0, int n, int E) {
     ByteState g = st;
     const size_t o = (size_t)s0, T = st.Tcap, D = st.Dcap;
     g.S = n;
+    if (g.pc_act) { g.pc_act += o * st.pc_C * T; g.pc_n += o * st.pc_C; g.pc_meta += o * 2; }
     g.xP += o * XA_N * T;  g.confcls += o * 2 * T;  g.tbox += o * 4 * T;  g.ints += o * BI_COUNT * T;
     g.act += o * T;  g.lost += o * T;  g.hdr += o * BH_COUNT;  g.n_updates += o;  g.scratch += o * T * D;
     if (st.chist) g.chist += o * 2 * BOT_HIST * T;

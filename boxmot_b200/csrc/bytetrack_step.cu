@@ -431,6 +431,15 @@ byte_step_kernel(ByteState st, ByteParams pr, const float* __restrict__ dets, co
         v.set_box(slot, mean_to_xyxy<KIND>(x));
         sm.tflag[slot] |= TF_USED;
     }
+    if (st.pc_act) {      // per_class: the other classes' active tracks keep their slots
+        const int cur = st.pc_meta[(size_t)s * 2];
+        for (int c = 0; c < st.pc_C; c++) {
+            if (c == cur) continue;
+            const int m = st.pc_n[(size_t)s * st.pc_C + c];
+            const int* l = st.pc_act + ((size_t)s * st.pc_C + c) * Tcap;
+            for (int i = tid; i < m; i += BT_NT) sm.tflag[l[i]] |= TF_USED;
+        }
+    }
     for (int p = tid; p < nU; p += BT_NT) {          // unconfirmed tracks are not predicted, only warped
         const int slot = sm.unc[p];
         sm.tflag[slot] |= TF_USED;

@@ -93,7 +93,42 @@ struct BoostEngine {
     cudaEvent_t ev[7];
     bool timing = false, timed = false;
     StreamGroups grp;
+    int* pc_frame = nullptr;   // [S] frame counter at the frame's start (bm_boosttrack_hold_frame)
 };
+
+// per_class_decorator (boxmot/trackers/basetracker.py:154-201) for the BYTE family: before class `cls` is updated
+// the decorator makes per_class_active_tracks[cls] the tracker's active_tracks and resets frame_count to the
+// frame's starting value; lost_stracks / removed_stracks are NOT swapped (one list for all classes).
+__global__ void byte_select_class_kernel(bm::ByteState st, int* pc_act, int* pc_n, int* pc_meta, int C, int cls,
+                                         int new_frame) {
+    const int s = blockIdx.x, tid = threadIdx.x;
+    int* hdr = st.hdr + (size_t)s * bm::BH_COUNT;
+    int* act = st.act + (size_t)s * st.Tcap;
+    int* meta = pc_meta + (size_t)s * 2;
+    const int cur = meta[0], n = hdr[bm::BH_NACT];
+    if (cur >= 0) {
+        int* dst = pc_act + ((size_t)s * C + cur) * st.Tcap;
+        for (int i = tid; i < n; i += blockDim.x) dst[i] = act[i];
+        if (tid == 0) pc_n[(size_t)s * C + cur] = n;
+    }
+    __syncthreads();
+    const int m = pc_n[(size_t)s * C + cls];
+    const int* src = pc_act + ((size_t)s * C + cls) * st.Tcap;
+    for (int i = tid; i < m; i += blockDim.x) act[i] = src[i];
+    __syncthreads();
+    if (tid == 0) {
+        hdr[bm::BH_NACT] = m;
+        if (new_frame) meta[1] = hdr[bm::BH_FRAME]; else hdr[bm::BH_FRAME] = meta[1];
+        meta[0] = cls;
+    }
+}
+
+__global__ void boost_hold_frame_kernel(bm::BoostState st, int* pc_frame, int new_frame) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= st.S) return;
+    int* hdr = st.hdr + (size_t)s * bm::BTH_COUNT;
+    if (new_frame) pc_frame[s] = hdr[bm::BTH_FRAME]; else hdr[bm::BTH_FRAME] = pc_frame[s];
+}
 
 template <typename E, typename T>
 cudaError_t dev_alloc(E* e, T** p, size_t n) {
@@ -578,6 +613,19 @@ int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, co
     return 0;
 }
 
+int bm_boosttrack_hold_frame(void* handle, int new_frame, void* stream) {
+    BoostEngine* e = static_cast<BoostEngine*>(handle);
+    if (!e) return fail(-1, "bm_boosttrack_hold_frame: null handle");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!e->pc_frame) {
+        BM_CUDA(dev_alloc(e, &e->pc_frame, (size_t)e->st.S));
+        BM_CUDA(cudaMemsetAsync(e->pc_frame, 0, (size_t)e->st.S * sizeof(int), s));
+    }
+    boost_hold_frame_kernel<<<(e->st.S + 127) / 128, 128, 0, s>>>(e->st, e->pc_frame, new_frame);
+    BM_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int bm_boosttrack_set_groups(void* handle, int groups) {
     BoostEngine* e = static_cast<BoostEngine*>(handle);
     if (!e) return fail(-1, "null handle");
@@ -807,6 +855,31 @@ int bm_bytetrack_reset(void* handle, void* stream) {
     BM_CUDA(cudaMemsetAsync(st.lost, 0, S * T * sizeof(int), s));
     BM_CUDA(cudaMemsetAsync(st.xP, 0, S * bm::XA_N * T * sizeof(double), s));
     BM_CUDA(cudaMemsetAsync(st.tbox, 0, S * 4 * T * sizeof(double), s));
+    if (st.pc_act) {
+        BM_CUDA(cudaMemsetAsync(st.pc_n, 0, S * st.pc_C * sizeof(int), s));
+        BM_CUDA(cudaMemsetAsync(st.pc_meta, 0xFF, S * 2 * sizeof(int), s));
+    }
+    return 0;
+}
+
+int bm_bytetrack_select_class(void* handle, int n_classes, int cls, int new_frame, void* stream) {
+    ByteEngine* e = static_cast<ByteEngine*>(handle);
+    if (!e || n_classes < 1 || cls < 0 || cls >= n_classes) return fail(-1, "bm_bytetrack_select_class: bad argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    bm::ByteState& st = e->st;
+    if (!st.pc_act) {
+        const size_t S = st.S;
+        int *a = nullptr, *n = nullptr, *m = nullptr;
+        BM_CUDA(dev_alloc(e, &a, S * n_classes * st.Tcap));
+        BM_CUDA(dev_alloc(e, &n, S * n_classes));
+        BM_CUDA(dev_alloc(e, &m, S * 2));
+        BM_CUDA(cudaMemsetAsync(n, 0, S * n_classes * sizeof(int), s));
+        BM_CUDA(cudaMemsetAsync(m, 0xFF, S * 2 * sizeof(int), s));
+        st.pc_act = a; st.pc_n = n; st.pc_meta = m; st.pc_C = n_classes;
+    }
+    if (n_classes != st.pc_C) return fail(-1, "bm_bytetrack_select_class: the number of classes is fixed by the first call");
+    byte_select_class_kernel<<<st.S, 128, 0, s>>>(st, st.pc_act, st.pc_n, st.pc_meta, st.pc_C, cls, new_frame);
+    BM_CUDA(cudaGetLastError());
     return 0;
 }
 

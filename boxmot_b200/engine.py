@@ -51,6 +51,51 @@ class _HostStepMixin:
         return [ho[s, : hn2[s]].copy() for s in range(self.S)]
 
 
+def _step_classes_host(eng, class_dets, class_embs=None, class_warps=None):
+    """per_class stepping of a ONE-stream engine whose lost / removed lists (ByteTrack, BoT-SORT) or whole track
+    pool (BoostTrack) are shared by the classes: ``class_dets[c]`` (N_c, 6) are the detections of class id c.
+    All classes are uploaded at once; per class ``eng.select_class`` then ``eng.step`` on that class's slice are
+    enqueued without a host synchronisation; one download.  Returns the list of (M_c, 8) row arrays."""
+    assert eng.S == 1, "per_class stepping drives a single-stream engine"
+    C = len(class_dets)
+    E = getattr(eng, "E", 0) if getattr(eng, "with_reid", False) else 0
+    key = "_pc_bufs"
+    if getattr(eng, key, None) is None or eng._pc_bufs[0] != C:
+        h = dict(dets=torch.zeros((C, eng.Dcap, 6), dtype=torch.float32).pin_memory(),
+                 nd=torch.zeros((C,), dtype=torch.int32).pin_memory(),
+                 embs=torch.zeros((C, eng.Dcap, max(E, 1)), dtype=torch.float32).pin_memory(),
+                 warps=torch.zeros((C, 2, 3), dtype=torch.float64).pin_memory(),
+                 out=torch.zeros((C, eng.out_rows, 8), dtype=torch.float64).pin_memory(),
+                 nout=torch.zeros((C,), dtype=torch.int32).pin_memory())
+        d = {k: torch.zeros_like(v, device=eng.device) for k, v in h.items()}
+        eng._pc_bufs = (C, h, d)
+    _, h, d = eng._pc_bufs
+    hd, hn, he, hw = h["dets"].numpy(), h["nd"].numpy(), h["embs"].numpy(), h["warps"].numpy()
+    for c, x in enumerate(class_dets):
+        n = 0 if x is None else len(x)
+        if n > eng.Dcap:
+            raise RuntimeError("class %d: %d detections exceed det_cap=%d" % (c, n, eng.Dcap))
+        if n:
+            hd[c, :n] = x
+            if E:
+                he[c, :n] = class_embs[c]
+        hn[c] = n
+        hw[c] = np.eye(2, 3) if class_warps is None else class_warps[c]
+    for k in ("dets", "nd") + (("embs",) if E else ()) + (("warps",) if class_warps is not None else ()):
+        d[k].copy_(h[k], non_blocking=True)
+    for c in range(C):
+        eng.select_class(C, c, c == 0)
+        args = [d["dets"][c:c + 1], d["nd"][c:c + 1]]
+        if hasattr(eng, "with_reid"):
+            args += [d["embs"][c:c + 1] if E else None, d["warps"][c:c + 1] if class_warps is not None else None]
+        eng.step(*args, out=d["out"][c:c + 1], nout=d["nout"][c:c + 1])
+    h["out"].copy_(d["out"], non_blocking=True)
+    h["nout"].copy_(d["nout"], non_blocking=True)
+    torch.cuda.current_stream(eng.device).synchronize()
+    ho, hn2 = h["out"].numpy(), h["nout"].numpy()
+    return [ho[c, : hn2[c]].copy() for c in range(C)]
+
+
 class OcSortEngine(_HostStepMixin):
     """S independent OC-SORT trackers advanced by one kernel launch per frame.
 
@@ -363,6 +408,16 @@ class BoostTrackEngine:
         self.launches += 7 if self.with_reid else 5
         return out, nout
 
+    def select_class(self, n_classes, cls, new_frame):
+        """per_class mode (bm_boosttrack_hold_frame): the reference's decorator does not swap BoostTrack's track
+        pool, so a class call only rewinds the frame counter.  Asynchronous."""
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_boosttrack_hold_frame(self._h, int(bool(new_frame)), _stream_ptr(self.device)),
+                       "bm_boosttrack_hold_frame")
+
+    def step_classes_host(self, class_dets, class_embs=None, class_warps=None):
+        return _step_classes_host(self, class_dets, class_embs, class_warps)
+
     def counters(self, raise_on_error=True):
         err = ctypes.c_int(0)
         buf = (ctypes.c_ulonglong * 4)()
@@ -543,6 +598,16 @@ class ByteTrackEngine(_HostStepMixin):
                                                     _stream_ptr(self.device)), "bm_bytetrack_step")
         self.launches += 1
         return out, nout
+
+    def select_class(self, n_classes, cls, new_frame):
+        """per_class mode (bm_bytetrack_select_class): make class ``cls``'s active list the engine's; lost / removed
+        tracks stay shared, as in the reference's decorator.  Asynchronous."""
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bm_bytetrack_select_class(self._h, int(n_classes), int(cls), int(bool(new_frame)),
+                                                            _stream_ptr(self.device)), "bm_bytetrack_select_class")
+
+    def step_classes_host(self, class_dets, class_embs=None, class_warps=None):
+        return _step_classes_host(self, class_dets, class_embs, class_warps)
 
     def counters(self, raise_on_error=True):
         """Cumulative {track_updates, lap_solves, matches, births}; raises on device error bits."""

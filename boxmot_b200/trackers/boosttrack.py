@@ -38,8 +38,6 @@ class BoostTrack(BaseTracker):
     def update(self, dets, img=None, embs=None, warp=None):
         dets = self._prepare(dets, img)
         self.check_inputs(dets, img, embs)
-        if self.per_class:
-            raise NotImplementedError("per_class BoostTrack is not wired to the engine")
         if self.with_reid and embs is None and len(dets):
             raise RuntimeError("with_reid=True needs `embs`: the ReID backend is outside the association path")
         if self._engine is None:
@@ -53,6 +51,22 @@ class BoostTrack(BaseTracker):
             for _ in range(self._skipped):     # empty frames seen before: advance the frame counter
                 self._engine.step_host([np.empty((0, 6))], [np.empty((0, max(e, 1)))])
         self.frame_count += 1
+        if self.per_class:
+            # per_class_decorator (basetracker.py:154-201) over a tracker whose tracks live in self.trackers
+            # (boosttrack.py:185), which the decorator does not swap: every class call predicts, matches and ages the
+            # ONE pool with that class's detections at the same frame_count -- a track survives a frame only if fewer
+            # than max_age class calls miss it.  Reproduced as nr_classes steps of the one stream.
+            C = self.nr_classes
+            sel = [(dets[:, 5] == c) if dets.size else np.zeros((0,), bool) for c in range(C)]
+            warps = None
+            if warp is not None:
+                w = np.asarray(warp, dtype=np.float64)
+                warps = w if w.ndim == 3 else np.concatenate([w[None], np.tile(np.eye(2, 3), (C - 1, 1, 1))])
+            rows = self._engine.step_classes_host([dets[m] for m in sel],
+                                                  [embs[m] for m in sel] if self.with_reid else None, warps)
+            rows = [r for r in rows if len(r)]
+            self._engine.status()
+            return np.vstack(rows) if rows else np.empty((0, 8))
         rows = self._engine.step_host([dets], [embs] if self.with_reid else None,
                                       None if warp is None else [np.asarray(warp, dtype=np.float64)])[0]
         self._engine.status()

@@ -39,8 +39,6 @@ class BotSort(BaseTracker):
     def update(self, dets, img=None, embs=None, warp=None):
         dets = self._prepare(dets, img)
         self.check_inputs(dets, img, embs)
-        if self.per_class:
-            raise NotImplementedError("per_class BoT-SORT is not wired to the engine")
         if self.with_reid and embs is None and len(dets):
             raise RuntimeError("with_reid=True needs `embs`: the ReID backend is outside the association path")
         if self._engine is None:
@@ -54,10 +52,30 @@ class BotSort(BaseTracker):
             for _ in range(getattr(self, "_skipped", 0)):     # empty frames seen before: advance the frame counter
                 self._engine.step_host([np.empty((0, 6))], [np.empty((0, max(e, 1)))])
         self.frame_count += 1
+        if self.per_class:
+            return self._update_per_class(dets, embs, warp)
         rows = self._engine.step_host([dets], [embs] if self.with_reid else None,
                                       None if warp is None else [np.asarray(warp, dtype=np.float64)])[0]
         self._engine.status()
         return rows if len(rows) else np.asarray([])
+
+    def _update_per_class(self, dets, embs, warp):
+        """per_class_decorator (basetracker.py:154-201): one update per class id on that class's active_tracks with
+        the lost / removed lists shared by all classes (botsort.py:70-71).  ``warp``: None, an array [nr_classes, 2, 3]
+        (what ``self.cmc.apply`` returned in each class call), or one 2x3 matrix, which is then the FIRST class call's
+        warp and the identity afterwards -- what the reference's stateful CMC yields when asked nr_classes times about
+        the same image."""
+        C = self.nr_classes
+        sel = [(dets[:, 5] == c) if dets.size else np.zeros((0,), bool) for c in range(C)]
+        per_cls = [dets[m] for m in sel]
+        per_emb = [embs[m] for m in sel] if self.with_reid else None
+        warps = None
+        if warp is not None:
+            w = np.asarray(warp, dtype=np.float64)
+            warps = w if w.ndim == 3 else np.concatenate([w[None], np.tile(np.eye(2, 3), (C - 1, 1, 1))])
+        rows = [r for r in self._engine.step_classes_host(per_cls, per_emb, warps) if len(r)]
+        self._engine.status()
+        return np.vstack(rows) if rows else np.empty((0, 8))
 
     def reset(self):
         if self._engine is not None:

@@ -28,8 +28,6 @@ class ByteTrack(BaseTracker):
         self._engine = None
 
     def _make_engine(self):
-        if self.per_class:
-            raise NotImplementedError("per_class ByteTrack is not wired to the engine yet")
         self._engine = ByteTrackEngine(
             1, track_cap=self._caps[0], det_cap=self._caps[1], device=self._device,
             min_conf=self.min_conf, track_thresh=self.track_thresh, match_thresh=self.match_thresh,
@@ -41,6 +39,15 @@ class ByteTrack(BaseTracker):
         if self._engine is None:
             self._make_engine()
         self.frame_count += 1
+        if self.per_class:
+            # per_class_decorator (basetracker.py:154-201): update once per class id with that class's active_tracks;
+            # lost_stracks / removed_stracks are ONE list for all classes (bytetrack.py:126-127), so every class call
+            # also predicts, re-finds and ages the lost tracks of the others -- reproduced on the device
+            # (bm_bytetrack_select_class).  det_ind is the index within the class subset.
+            per_cls = [dets[dets[:, 5] == c] if dets.size else dets[:0] for c in range(self.nr_classes)]
+            rows = [r for r in self._engine.step_classes_host(per_cls) if len(r)]
+            self._engine.status()
+            return np.vstack(rows) if rows else np.empty((0, 8))
         rows = self._engine.step_host([dets])[0]
         self._engine.status()
         # np.asarray(outputs) of an empty list (bytetrack.py:301)

@@ -129,6 +129,11 @@ int bm_boosttrack_reset(void* handle, void* stream);
  * order (tracker list order); the reported confidence is the BOOSTED detection confidence. */
 int bm_boosttrack_step(void* handle, const float* d_dets, const int* d_ndets, const float* d_embs,
                        const double* d_warps, double* d_out, int* d_nout, void* stream);
+/* per_class mode of BoostTrack: the decorator calls update once per class id, but BoostTrack keeps its tracks in
+ * self.trackers (boosttrack.py:185), which the decorator does not swap -- every class call predicts, matches and ages
+ * the ONE pool with that class's detections, at the same frame_count.  new_frame = 1 records the frame counter before
+ * the frame's first class call, new_frame = 0 rewinds it before each of the others. */
+int bm_boosttrack_hold_frame(void* handle, int new_frame, void* stream);
 /* Stream groups for the BoostTrack engine; see bm_ocsort_set_groups. */
 int bm_boosttrack_set_groups(void* handle, int groups);
 /* Synchronises `stream`: OR of the per-stream error bits and cumulative {track_updates,
@@ -159,6 +164,14 @@ int bm_bytetrack_destroy(void* handle);
 int bm_bytetrack_reset(void* handle, void* stream);
 int bm_bytetrack_step(void* handle, const float* d_dets, const int* d_ndets, double* d_out,
                       int* d_nout, void* stream);
+/* per_class mode of the BYTE family (also for BoT-SORT handles): the reference's per_class_decorator
+ * (boxmot/trackers/basetracker.py:154-201) calls update once per class id 0 .. nr_classes-1 per frame, each time with
+ * per_class_active_tracks[cls] as the tracker's active_tracks and frame_count reset to the frame's starting value;
+ * lost_stracks / removed_stracks stay ONE list for all classes (bytetrack.py:126-127, botsort.py:70-71), which
+ * couples the classes.  This call makes class `cls`'s active list the engine's (saving the current one) and, unless
+ * new_frame, rewinds the frame counter; the caller then steps the class's detections (det_ind relative to them).
+ * new_frame = 1 on the frame's first class.  n_classes is fixed by the first call.  Asynchronous on `stream`. */
+int bm_bytetrack_select_class(void* handle, int n_classes, int cls, int new_frame, void* stream);
 /* out4 = {pool tracks predicted, assignments solved, matches, births}, summed over streams;
  * err_bits = OR of the per-stream error bits.  Synchronises the stream. */
 int bm_bytetrack_counters(void* handle, int* err_bits, unsigned long long* out4, void* stream);

@@ -105,6 +105,30 @@ def main_deepocsort_per_class():
     print("deepocsort per_class", out.shape, "ids", int(out[:, 5].max()))
 
 
+def main_per_class_shared():
+    """per_class=True for the trackers whose classes are COUPLED by the decorator (basetracker.py:154-201):
+    ByteTrack / BoT-SORT share lost_stracks and removed_stracks across the class calls, BoostTrack's self.trackers
+    is not swapped at all.  The CMC stand-in is asked nr_classes times per frame: identity every time."""
+    out = run_ref("bytetrack", per_class_frames(), per_class=True)
+    np.savez_compressed(os.path.join(GOLD, "ref_bytetrack_synth_k40_perclass.npz"), rows=out,
+                        kw=np.array(repr({"per_class": True})))
+    print("bytetrack per_class", out.shape, "ids", int(out[:, 5].max()))
+    fr, em = per_class_emb_frames()
+    for name, case, kw in (("botsort", "synth_k40_e32_perclass", {}),
+                           ("boosttrack", "synth_k40_perclass", {}),
+                           ("boosttrack", "synth_k40_perclass_age200", {"max_age": 200, "with_reid": True})):
+        trk = ref_shim.make_tracker(name, per_class=True, **kw)
+        rows = []
+        for i, d in enumerate(fr):
+            r = np.asarray(trk.update(d.copy(), IMG, em[i].copy()), dtype=float)
+            r = r.reshape(-1, r.shape[-1])[:, :8] if r.size else np.empty((0, 8))
+            rows.append(np.c_[np.full(len(r), i), r])
+        out = np.vstack(rows)
+        np.savez_compressed(os.path.join(GOLD, "ref_%s_%s.npz" % (name, case)), rows=out,
+                            kw=np.array(repr(dict(kw, per_class=True))))
+        print(name, case, out.shape, "ids", int(out[:, 5].max()) if len(out) else None)
+
+
 def main_kf():
     """Known-answer vectors of the reference's KalmanFilterXYAH / XYWH (rows a1-a5): a chain
     initiate -> (predict -> update(conf))* on random boxes, and gating distances."""
@@ -686,6 +710,8 @@ if __name__ == "__main__":
         main_per_class()
     elif "--deepocsort-per-class" in sys.argv:
         main_deepocsort_per_class()
+    elif "--per-class-shared" in sys.argv:
+        main_per_class_shared()
     elif "--kf" in sys.argv:
         main_kf()
     elif "--botsort-rot" in sys.argv:
