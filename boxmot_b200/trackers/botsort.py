@@ -61,7 +61,7 @@ class BotSort(BaseTracker):
 
     def _update_per_class(self, dets, embs, warp):
         """per_class_decorator (basetracker.py:154-201): one update per class id on that class's active_tracks with
-        the lost / removed lists shared by all classes (botsort.py:70-71).  ``warp``: None, an array [nr_classes, 2, 3]
+        the lost / removed lists shared by all classes (botsort.py:68-69).  ``warp``: None, an array [nr_classes, 2, 3]
         (what ``self.cmc.apply`` returned in each class call), or one 2x3 matrix, which is then the FIRST class call's
         warp and the identity afterwards -- what the reference's stateful CMC yields when asked nr_classes times about
         the same image."""

@@ -41,7 +41,7 @@ class ByteTrack(BaseTracker):
         self.frame_count += 1
         if self.per_class:
             # per_class_decorator (basetracker.py:154-201): update once per class id with that class's active_tracks;
-            # lost_stracks / removed_stracks are ONE list for all classes (bytetrack.py:126-127), so every class call
+            # lost_stracks / removed_stracks are ONE list for all classes (bytetrack.py:143-144), so every class call
             # also predicts, re-finds and ages the lost tracks of the others -- reproduced on the device
             # (bm_bytetrack_select_class).  det_ind is the index within the class subset.
             per_cls = [dets[dets[:, 5] == c] if dets.size else dets[:0] for c in range(self.nr_classes)]

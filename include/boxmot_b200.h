@@ -167,7 +167,7 @@ int bm_bytetrack_step(void* handle, const float* d_dets, const int* d_ndets, dou
 /* per_class mode of the BYTE family (also for BoT-SORT handles): the reference's per_class_decorator
  * (boxmot/trackers/basetracker.py:154-201) calls update once per class id 0 .. nr_classes-1 per frame, each time with
  * per_class_active_tracks[cls] as the tracker's active_tracks and frame_count reset to the frame's starting value;
- * lost_stracks / removed_stracks stay ONE list for all classes (bytetrack.py:126-127, botsort.py:70-71), which
+ * lost_stracks / removed_stracks stay ONE list for all classes (bytetrack.py:143-144, botsort.py:68-69), which
  * couples the classes.  This call makes class `cls`'s active list the engine's (saving the current one) and, unless
  * new_frame, rewinds the frame counter; the caller then steps the class's detections (det_ind relative to them).
  * new_frame = 1 on the frame's first class.  n_classes is fixed by the first call.  Asynchronous on `stream`. */
