@@ -363,3 +363,48 @@ def test_iou_family_oracle_equals_reference_functions():
         ref = AssociationFunction(w=1920, h=1080, asso_mode=name).asso_func(a, b)
         mine = assoc.asso_func(name, 1920, 1080)(a, b)
         assert np.array_equal(np.asarray(ref), np.asarray(mine)), name
+
+
+# ---- per_class for the trackers whose classes the decorator couples (row a25)
+def _per_class_frames(with_embs):
+    from boxmot_b200.synth import make_stream
+    if with_embs:
+        from conftest import deepocsort_per_class_case
+        fr, em, _, _ = deepocsort_per_class_case()
+    else:
+        fr, em = make_stream(5, 40, 60), None
+    out = []
+    for d in fr:
+        d = d.copy()
+        d[:, 5] = np.floor((d[:, 0] + d[:, 2]) / 2.0 / 640.0).clip(0, 2)
+        out.append(d.astype(np.float32).astype(np.float64))
+    return out, em
+
+
+@pytest.mark.parametrize("tracker,case", [("bytetrack", "synth_k40_perclass"), ("botsort", "synth_k40_e32_perclass"),
+                                          ("boosttrack", "synth_k40_perclass"),
+                                          ("boosttrack", "synth_k40_perclass_age200")])
+def test_per_class_oracles_match_reference_golden(tracker, case):
+    """oracle/per_class.py (the decorator's loop over the numpy oracles: active list swapped, lost list / BoostTrack
+    pool shared, frame counter rewound) against the reference's own per_class=True output."""
+    from conftest import BOOSTTRACK_YAML, BOTSORT_YAML, BYTETRACK_YAML, assert_rows_match, golden_rows, split_by_frame
+    from oracle.per_class import per_class_update
+    want, kw = golden_rows(tracker, case)
+    kw = {k: v for k, v in kw.items() if k != "per_class"}
+    frames, embs = _per_class_frames(tracker != "bytetrack")
+    if tracker == "bytetrack":
+        from oracle.bytetrack import ByteTrackOracle
+        o = ByteTrackOracle(**BYTETRACK_YAML)
+    elif tracker == "botsort":
+        from oracle.botsort import BotSortOracle
+        o = BotSortOracle(**BOTSORT_YAML)
+    else:
+        from oracle.boosttrack import BoostTrackOracle
+        o = BoostTrackOracle(**dict(BOOSTTRACK_YAML, **kw))
+    wf = split_by_frame(want, len(frames))
+    n = 0
+    for f, d in enumerate(frames):
+        got = per_class_update(o, d, None if embs is None else embs[f].astype(np.float64), swap=tracker != "boosttrack")
+        assert_rows_match(got, wf[f], f, conf_rtol=1e-9 if tracker == "boosttrack" else 0.0)
+        n += len(got)
+    assert n == len(want)
