@@ -303,12 +303,13 @@ __device__ __noinline__ void ss_cost_row_full(const SsState& st, const SsParams&
         else if (cf >= pr.conf_lo) { if (c <= pr.max_cos_dist) bits |= 2; }
     }
     for (int o = 16; o > 0; o >>= 1) bits |= __shfl_xor_sync(BM_FULL, bits, o);
-    if (lane == 0 && bits) ti[TI_FEAS] |= bits;
+    if (lane == 0) ti[TI_FEAS] |= bits | 4;                      // bit 2: this row of the matrix is stored
 }
 
 // A warp takes 32 rows at a time: each lane first fetches ONE row's list slot, state, screen factor and first
 // sample slot (32 rows' dependent loads in flight at once), then the warp walks the rows with the lanes over the
-// detections; the frame's detection columns sit in shared memory as seven arrays.
+// detections; the frame's detection columns sit in shared memory as seven arrays.  A row without a surviving pair
+// is not written at all: the cascade reads it as the clamp constant (TI_FEAS bit 2 clear, SsClampCost::stored).
 __global__ void __launch_bounds__(256, 4)
 ss_cost_kernel(SsState st, SsParams pr) {
     extern __shared__ double ss_cost_sm[];
@@ -325,7 +326,6 @@ ss_cost_kernel(SsState st, SsParams pr) {
     }
     __syncthreads();
     const float* dist = v.dist();
-    double* cost = v.cost();
     const int lane = lane_id(), wpb = blockDim.x >> 5;
     for (int base = (blockIdx.x * wpb + (threadIdx.x >> 5)) * 32; base < nT; base += gridDim.x * wpb * 32) {
         const int p = base + lane;
@@ -361,8 +361,7 @@ ss_cost_kernel(SsState st, SsParams pr) {
                         for (int i = 1; i < rnd; i++) mn = fminf(mn, dist[(size_t)ds[i] * Dc + k]);
                         app = (double)mn;
                     }
-                    if (app * rsc > pr.max_cos_dist) cost[(size_t)rp * Dc + k] = SS_INFTY_COST;
-                    else open = true;
+                    if (!(app * rsc > pr.max_cos_dist)) open = true;
                 }
             }
             if (__any_sync(BM_FULL, open)) ss_cost_row_full(st, pr, s, rp, rt, n, dz, rsc);
@@ -466,9 +465,11 @@ __device__ int lsa_scipy_warp(const CostFn& cost, int nr, int nc, const LsaWork&
 struct SsClampCost {
     const double* c; int ld; const int* rows; const int* cols; double maxd; bool tr;
     const int* far;      // optional, by list position: the whole row is above max_distance (never stored)
+    const int* stored;   // optional, pinfo by list position: bit 22 clear = the cost kernel screened the whole row out
     __device__ __forceinline__ double at(int r, int cpos) const {
         const int p = rows[r];
         if (far && far[p]) return maxd + 1e-5;
+        if (stored && !((stored[p] >> 22) & 1)) return maxd + 1e-5;
         const double x = c[(size_t)p * ld + cols[cpos]];
         return x > maxd ? maxd + 1e-5 : x;
     }
@@ -476,10 +477,11 @@ struct SsClampCost {
 };
 
 __device__ int ss_min_cost_matching(const double* c, int ld, const int* rows, int nr, int* cols, int& nc, double maxd,
-                                    const LsaWork& w, int* match_col, int* tmp, const int* far = nullptr) {
+                                    const LsaWork& w, int* match_col, int* tmp, const int* far = nullptr,
+                                    const int* stored = nullptr) {
     const int lane = lane_id();
     const bool tr = nc < nr;
-    SsClampCost cf{c, ld, rows, cols, maxd, tr, far};
+    SsClampCost cf{c, ld, rows, cols, maxd, tr, far, stored};
     if (lsa_scipy_warp(cf, tr ? nc : nr, tr ? nr : nc, w)) return 1;
     // row -> column of the original orientation, into match_col (w.srl is free after the solve)
     for (int r = lane; r < nr; r += 32) match_col[r] = tr ? w.row4col[r] : w.col4row[r];
@@ -787,7 +789,7 @@ ss_match_kernel(SsState st, SsParams pr) {
         const int t = v.order()[p];
         const double* a = v.tab(t);
         const int tsu = min((int)a[SS_TSU], 0xffff);
-        pinfo[p] = tsu | ((int)a[ST_STATE] << 16) | ((v.tint(t)[TI_FEAS] & 3) << 20);
+        pinfo[p] = tsu | ((int)a[ST_STATE] << 16) | ((v.tint(t)[TI_FEAS] & 7) << 20);      // bit 22: cost row stored
     }
     for (int k = lane; k < n; k += 32) dmatched[k] = 0;
     __syncwarp();
@@ -892,7 +894,7 @@ ss_match_kernel(SsState st, SsParams pr) {
             }
             __syncwarp();
             bad |= ss_min_cost_matching(cost, Dc, lvl, m, cols, nc, thr, (m <= SS_LSA_SMEM_M && nc <= SS_LSA_SMEM_M) ? w_smem : w_glob,
-                                        mcol, tmp);
+                                        mcol, tmp, nullptr, pinfo);
             nlsa++;
             if (lane == 0)
                 for (int r = 0; r < m; r++)
