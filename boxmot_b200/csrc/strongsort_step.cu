@@ -1067,8 +1067,10 @@ __device__ void ss_apply_update(const SsView& v, const SsParams& pr, int t, int 
     __syncwarp();
 }
 
-// K5: Track.update for every matched track, in match order (a track matched twice is updated twice)
-__global__ void __launch_bounds__(128)
+// K5: Track.update for every matched track, in match order (a track matched twice is updated twice).  Held to 64
+// registers: a chain of dependent loads per warp (update list -> track -> ring -> pool vector), so eight CTAs per
+// SM beat the 250 bytes of spills (0.75 -> 0.50 ms at 512 streams; 80 registers: 0.57)
+__global__ void __launch_bounds__(128, 8)
 ss_update_kernel(SsState st, SsParams pr, const float* __restrict__ embs) {
     const int s = st.s0 + blockIdx.y, u = blockIdx.x * 4 + (threadIdx.x >> 5);
     SsView v(st, s);
