@@ -270,7 +270,8 @@ __device__ __forceinline__ double ss_track_screen(const double* a, double mc_lam
 
 // One row in full: the projection of the Kalman state, its reciprocal square roots, the adaptive lambda and the
 // track's adjustment flags are evaluated once per row (ss_track_terms), lanes over the detections.  Out of line:
-// the screening loop of the kernel keeps its registers.
+// the kernel is held to 40 registers for six CTAs per SM (screened workload 0.66 -> 0.54 ms; a workload whose rows
+// are all open pays 4 % for this function's spills: 1.36 -> 1.42 ms).
 __device__ __noinline__ void ss_cost_row_full(const SsState& st, const SsParams& pr, int s, int p, int t, int n,
                                               const double* dz, double screen) {
     SsView v(st, s);
@@ -310,7 +311,7 @@ __device__ __noinline__ void ss_cost_row_full(const SsState& st, const SsParams&
 // sample slot (32 rows' dependent loads in flight at once), then the warp walks the rows with the lanes over the
 // detections; the frame's detection columns sit in shared memory as seven arrays.  A row without a surviving pair
 // is not written at all: the cascade reads it as the clamp constant (TI_FEAS bit 2 clear, SsClampCost::stored).
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, 6)
 ss_cost_kernel(SsState st, SsParams pr) {
     extern __shared__ double ss_cost_sm[];
     const int s = st.s0 + blockIdx.y;
