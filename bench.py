@@ -403,7 +403,7 @@ def run_gpu_arm(args):
     # OC-SORT batches of more than 1536 streams run the first-round screen as a fifth launch (capi.cu ocs_create)
     prescreen = (not (deep or boost or bot or byte)) and (
         os.environ.get("BM_PRESCREEN", "1" if S > 1536 else "0")[:1] == "1")
-    n_kernels = 6 if strong else 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5 if prescreen else 4
+    n_kernels = 8 if strong else 7 if deep else 7 if boost else 3 if bot else 1 if byte else 5 if prescreen else 4
     groups = 1
     if hasattr(eng, "set_stream_groups"):
         groups = eng.set_stream_groups(args.groups if args.groups is not None else DEFAULT_GROUPS.get(args.tracker, 1))

@@ -44,7 +44,7 @@ namespace bm {
 void set_last_error(const char* msg);
 
 enum { SH_NTRACKS = 0, SH_NLOST, SH_NTFREE, SH_NPFREE, SH_NPFREED, SH_NEXT_ID, SH_FRAME, SH_ERR, SH_NHIST, SH_NLIVE,
-       SH_NDET, SH_NUPD, SH_STAGE3, SH_NUNM, SH_LSA, SH_MATCH, SH_BIRTHS, SH_HADDETS, SH_COUNT = 20 };
+       SH_NDET, SH_NUPD, SH_STAGE3, SH_NUNM, SH_LSA, SH_MATCH, SH_BIRTHS, SH_HADDETS, SH_NWORK, SH_COUNT = 20 };
 enum { TI_ID = 0, TI_NRING, TI_NBANK, TI_NDIST, TI_LOSTFRAME, TI_SEQ, TI_NUPD, TI_MISS, TI_FEAS, TI_COUNT };
 // sorted detection table
 enum { DT_TLWH = 0, DT_XYAH = 4, DT_CONF = 8, DT_CLS, DT_DETIND, DT_QUALITY, DT_NORM, DT_COUNT };
@@ -1239,10 +1239,14 @@ __device__ __noinline__ bool ss_bank_pass2_regs(const SsView& v, const SsParams&
     };
 
     if (confirmed) {
+        // the ring's slots and their qualities, one per lane, fetched ONCE (a load pair per loop iteration was a
+        // serial chain of 2 nr memory round trips: most of this pass's time)
         const int* rg = v.ring(t);
+        const int rsl = lane < nr ? rg[lane] : 0;
+        const double rqi = lane < nr ? pq[rsl] : 0.0;
         for (int i = 0; i < nr; i++) {
-            const int sl = rg[i];
-            const double qi = pq[sl];
+            const int sl = __shfl_sync(BM_FULL, rsl, i);
+            const double qi = shfl_d(rqi, i);
             if (n >= pr.budget && !(qi > minq)) continue;      // it would be the entry that is dropped again
             const int h = n >= pr.budget ? evict() : n;        // the list has no holes here: an eviction's is refilled at once
 #pragma unroll
@@ -1255,8 +1259,63 @@ __device__ __noinline__ bool ss_bank_pass2_regs(const SsView& v, const SsParams&
             if (b) { if (lane == __ffs(b) - 1) dc++; }
             else { if (lane == nd) { ds = sl; dc = 1; dc0 = 0; } nd++; }
         }
-    } else {
-        while (n > keep) evict();
+    } else if (n > keep) {
+        // Trim of an inactive target (:575-593): n - keep evictions of the worst entry leave the `keep` BEST entries
+        // under the same order (quality, then older first) -- select those directly (a dying zombie's list is 50
+        // copies of one vector: 45 evictions of ~500 cycles each were most of this pass)
+        unsigned sel = 0;
+        for (int it = 0; it < keep; it++) {
+            double bq2 = -CUDART_INF;
+            int bs2 = 0x7fffffff, bp = -1;
+#pragma unroll
+            for (int j = 0; j < J; j++)
+                if ((alive >> j & 1) && !(sel >> j & 1) && (q[j] > bq2 || (q[j] == bq2 && seq[j] < bs2))) { bq2 = q[j]; bs2 = seq[j]; bp = j * 32 + lane; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double oq = shfl_xor_d(bq2, o);
+                const int os = __shfl_xor_sync(BM_FULL, bs2, o), op = __shfl_xor_sync(BM_FULL, bp, o);
+                if (op >= 0 && (bp < 0 || oq > bq2 || (oq == bq2 && os < bs2))) { bq2 = oq; bs2 = os; bp = op; }
+            }
+#pragma unroll
+            for (int j = 0; j < J; j++) if (bp == j * 32 + lane) sel |= 1u << j;
+        }
+        alive = sel;
+        n = keep;
+        // distinct list: the count of each old slot among the survivors; a slot without one leaves (and goes back to
+        // the pool when the ring does not hold it either)
+        int dcn = 0;
+#pragma unroll
+        for (int j = 0; j < J; j++) {
+            unsigned m = __ballot_sync(BM_FULL, alive >> j & 1);
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1;
+                const int sl = __shfl_sync(BM_FULL, slot[j], src);
+                if (lane < nd && ds == sl) dcn++;
+            }
+        }
+        const bool gone = lane < nd && dcn == 0;
+        if (gone) {
+            const int nv = v.pbank()[ds] - dc0;
+            v.pbank()[ds] = nv;
+            if (nv == 0 && v.pring()[ds] == 0) ss_pool_release(v, ds);
+        }
+        // the kept entries move to the front: lane i takes the i-th kept lane's (slot, new count, count at load); the
+        // write-back below applies pbank[slot] += new - old
+        const unsigned km = __ballot_sync(BM_FULL, lane < nd && dcn > 0);
+        const int nd2 = __popc(km);
+        const unsigned srcl = __fns(km, 0, lane + 1);
+        const int from = srcl < 32u ? (int)srcl : 0;
+        const int nds = __shfl_sync(BM_FULL, ds, from), ndc = __shfl_sync(BM_FULL, dcn, from),
+                  ndc0 = __shfl_sync(BM_FULL, dc0, from);
+        if (lane < nd2) { ds = nds; dc = ndc; dc0 = ndc0; } else { ds = -1; dc = 0; dc0 = 0; }
+        nd = nd2;
+        double m2 = CUDART_INF;
+#pragma unroll
+        for (int j = 0; j < J; j++) if (alive >> j & 1) m2 = fmin(m2, q[j]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m2 = fmin(m2, shfl_xor_d(m2, o));
+        minq = m2;
     }
     // write back, compacting the holes a trim leaves
     int base = 0;
@@ -1605,32 +1664,8 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
             if (todo) work[atomicAdd(&s_nwork, 1)] = p;
         }
         __syncthreads();
-        if (tid == 0) stamp[8] = clock64();
-        const int nwork = s_nwork;
-        if (tid == 0) stamp[9] = nwork;
-        for (int q = wid; q < nwork; q += nw) {                          // pass 2, a warp per target
-            const int p = work[q];
-            const int t = p < nT ? order[p] : lost[p - nT];
-            int* ti = v.tint(t);
-            const bool conf = p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE;
-            if (ss_bank_pass2_regs<5>(v, pr, t, conf, keep)) continue;
-            if (conf) {
-                const int nr = ti[TI_NRING];
-                // the list's minimum quality only rises while entries are replaced: a ring feature that does not
-                // beat it now cannot enter later in this loop either (while there is room, every feature enters)
-                const bool cand = lane < nr && (ti[TI_NBANK] < pr.budget || v.pq()[v.ring(t)[lane]] > v.bminq(t));
-                unsigned m = __ballot_sync(BM_FULL, cand);
-                if (ti[TI_NBANK] < pr.budget) m = nr >= 32 ? 0xffffffffu : ((1u << nr) - 1u);
-                while (m) {
-                    const int i = __ffs(m) - 1;
-                    m &= m - 1;
-                    ss_bank_append(v, pr, t, v.ring(t)[i]);
-                }
-            } else {
-                while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);
-            }
-        }
-    }
+        if (tid == 0) { stamp[8] = clock64(); stamp[9] = s_nwork; hdr[SH_NWORK] = s_nwork; }   // pass 2: ss_bank_kernel
+    } else if (tid == 0) hdr[SH_NWORK] = 0;
     __syncthreads();
     SS_STAMP(5);
     // (f) _format_outputs (strongsort.py:329-359): confirmed tracks updated this frame, in list order
@@ -1654,7 +1689,57 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
     }
     __syncthreads();
     SS_STAMP(6);
-    // (g) merge the deferred frees, rebuild the list of features some sample list references
+#undef SS_STAMP
+}
+
+// K6b: partial_fit's second pass, a warp per target with real appends / trims (the work list of K6), spread over
+// several CTAs per stream: in K6 it was 43 % of the CTA's time at eight warps per stream
+__global__ void __launch_bounds__(256, 5)
+ss_bank_kernel(SsState st, SsParams pr) {
+    const int s = st.s0 + blockIdx.y, lane = threadIdx.x & 31;
+    SsView v(st, s);
+    const int* hdr = v.hdr();
+    const int nwork = hdr[SH_NWORK];
+    if (nwork <= 0) return;
+    const int nT = hdr[SH_NTRACKS];
+    const int* order = v.order();
+    const int* lost = st.lost + (size_t)s * 32;
+    const int* work = st.wki + (size_t)s * st.wki_stride + 2 * (size_t)st.Tcap;
+    const int keep = pr.budget / 4 < 5 ? pr.budget / 4 : 5;
+    const int nw = (blockDim.x >> 5) * gridDim.x;
+    for (int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < nwork; q += nw) {
+        const int p = work[q];
+        const int t = p < nT ? order[p] : lost[p - nT];
+        int* ti = v.tint(t);
+        const bool conf = p < nT && v.tab(t)[ST_STATE] == (double)ST_CONFIRMED_STATE;
+        // the list lives in J registers per lane: the smallest J that holds the budget (the pass is instruction-bound,
+        // ~200 warp instructions per append at J = 5)
+        if (pr.budget <= 64 ? ss_bank_pass2_regs<2>(v, pr, t, conf, keep) : ss_bank_pass2_regs<5>(v, pr, t, conf, keep)) continue;
+        if (conf) {
+            const int nr = ti[TI_NRING];
+            // the list's minimum quality only rises while entries are replaced: a ring feature that does not
+            // beat it now cannot enter later in this loop either (while there is room, every feature enters)
+            const bool cand = lane < nr && (ti[TI_NBANK] < pr.budget || v.pq()[v.ring(t)[lane]] > v.bminq(t));
+            unsigned m = __ballot_sync(BM_FULL, cand);
+            if (ti[TI_NBANK] < pr.budget) m = nr >= 32 ? 0xffffffffu : ((1u << nr) - 1u);
+            while (m) {
+                const int i = __ffs(m) - 1;
+                m &= m - 1;
+                ss_bank_append(v, pr, t, v.ring(t)[i]);
+            }
+        } else {
+            while (ti[TI_NBANK] > keep) ss_bank_evict(v, t);
+        }
+    }
+}
+
+// K6c: merge the deferred frees, rebuild the list of features some sample list references (the rows of the next
+// frame's contraction)
+__global__ void __launch_bounds__(256)
+ss_live_kernel(SsState st) {
+    const int s = st.s0 + blockIdx.x, tid = threadIdx.x;
+    SsView v(st, s);
+    int* hdr = v.hdr();
     {
         const int nf = hdr[SH_NPFREED], np = hdr[SH_NPFREE];
         for (int i = tid; i < nf; i += blockDim.x) v.pfree()[np + i] = v.pfreed()[i];
@@ -1670,9 +1755,6 @@ ss_finalize_kernel(SsState st, SsParams pr, const float* __restrict__ embs, doub
             live[k] = p;
             lnorm[k] = (float)(v.pq()[p] + 1e-8);
         }
-    __syncthreads();
-    SS_STAMP(7);
-#undef SS_STAMP
 }
 
 __global__ void ss_reset_kernel(SsState st) {
@@ -1857,6 +1939,8 @@ static cudaError_t ss_launch_chain(SsEngine* e, const bm::SsState& st, const flo
     // one CTA per stream at 64 registers: two 512-thread CTAs per SM while every stream gets a slot at once, else
     // four of 256 threads (the kernel is a chain of dependent global-memory phases: residency, not width, hides it)
     bm::ss_finalize_kernel<<<st.S, e->st.S > 2 * e->n_sm ? 256 : 512, 0, s>>>(st, pr, d_embs, d_out, d_nout, st.Dcap);
+    bm::ss_bank_kernel<<<dim3(4, st.S), 256, 0, s>>>(st, pr);
+    bm::ss_live_kernel<<<st.S, 256, 0, s>>>(st);
     if (tm) { cudaEventRecord(e->ev[6], s); e->timed = true; }
     return cudaGetLastError();
 }

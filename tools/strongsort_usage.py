@@ -24,6 +24,6 @@ for s_ in range(0, S, max(1, S // 16)):
     st = np.zeros(10, np.int64)
     _lib.check(_lib.lib().bm_strongsort_debug_copy(eng._h, 3, s_, st.ctypes.data, st.nbytes, None), "dbg")
     acc += np.diff(st[:8])
-    print("  stream", s_, "partial_fit pass 1 cycles", st[8] - st[4], "pass 2 cycles", st[5] - st[8], "targets with work", st[9])
-print("finalize phases (cycles, mean of sampled streams): mark_missed, id recovery, births, deletions, partial_fit, outputs, live list:",
-      (acc / len(range(0, S, max(1, S // 16)))).astype(int))
+    print("  stream", s_, "partial_fit pass 1 cycles", st[8] - st[4], "targets with work (ss_bank_kernel)", st[9])
+print("finalize phases (cycles, mean of sampled streams): mark_missed, id recovery, births, deletions, partial_fit pass 1, outputs:",
+      (acc / len(range(0, S, max(1, S // 16)))).astype(int)[:6])
