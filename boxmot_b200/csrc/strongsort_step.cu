@@ -17,7 +17,9 @@
 //                         step-for-step emulation of scipy's rectangular linear_sum_assignment
 //   K5 ss_update_kernel   warp per updated track: adaptive feature EMA + NSA Kalman update + scores
 //   K6 ss_finalize_kernel CTA per stream: mark_missed, id recovery, births, lost buffer,
-//                         partial_fit, output rows, list of live bank features for the next frame
+//                         partial_fit's first pass (which targets have real appends), output rows
+//   K6b ss_bank_kernel    warp per listed target: partial_fit's appends / evictions on a register-resident list
+//   K6c ss_live_kernel    CTA per stream: list of live bank features for the next frame
 //
 // Feature storage.  The reference re-adds all (<= 10) features of every confirmed track to the
 // target's sample list EVERY frame, so a sample list of `budget` entries holds ~budget/10 distinct

@@ -267,7 +267,8 @@ int bm_strongsort_set_groups(void* handle, int groups);
 /* Debug: host copy of one stream's scratch (which = 0: the cascade's integer work area, 1: the cost matrix
  * [track_cap][det_cap] float64 by list position and sorted detection, 2: the sorted detection table). */
 int bm_strongsort_debug_copy(void* handle, int which, int stream_index, void* h_dst, size_t nbytes, void* stream);
-/* Per-launch CUDA-event timing: prepare+predict, bank contraction, cost matrix, cascade, updates, finalize (ms). */
+/* Per-launch CUDA-event timing: prepare+predict, bank contraction, cost matrix, cascade, updates, finalize (the
+ * finalize, sample-list and live-list launches together) (ms). */
 int bm_strongsort_time_kernels(void* handle, int enable);
 int bm_strongsort_kernel_times(void* handle, float* ms6);
 /* Test hook: tracks of one stream in list order: means [n][8], covariances [n][64], table rows
