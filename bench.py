@@ -317,9 +317,11 @@ class ClockSampler(threading.Thread):
 #   profiles/r1_launches_lane_scan_traffic.csv   predict 55.2 + assoc 19.3 + update 72.0 + finalize 39.7 MB
 #   profiles/r1_launches_bytetrack_traffic.csv   byte_step_kernel 25.3 MB read + 15.8 MB written
 #   profiles/r2_launches_ocsort_traffic.csv      round 2 (commit bf43990): predict 54.8 + assoc 19.3 + update 71.7 + finalize 39.5 MB
-NCU_TRAFFIC = {"ocsort": 185.4e6, "bytetrack": 41.1e6}
-NCU_TRAFFIC_SOURCE = {"ocsort": "profiles/r2_launches_ocsort_traffic.csv (ncu, cold caches, single launch chain; the OC-SORT kernels are "
-                                "unchanged since that capture)",
+#   profiles/r2_launches_ocsort_traffic_final.csv  final kernels of round 2 (update at 128, finalize at 32 registers):
+#                                                predict 53.1 + assoc 19.2 + update 72.3 + finalize 42.5 MB = 187.1 MB
+NCU_TRAFFIC = {"ocsort": 187.1e6, "bytetrack": 41.1e6}
+NCU_TRAFFIC_SOURCE = {"ocsort": "profiles/r2_launches_ocsort_traffic_final.csv (ncu dram__bytes_read+write of the four kernels of one "
+                                "frame step, cold caches, single launch chain; captured with the final kernels of round 2)",
                       "bytetrack": "profiles/r1_launches_bytetrack_traffic.csv (round 1 capture)"}
 TRACKER_NAMES = {"ocsort": "OC-SORT (ocsort.yaml)", "bytetrack": "ByteTrack (bytetrack.yaml)",
                  "botsort": "BoT-SORT (botsort.yaml, synthetic re-ID embeddings)",
