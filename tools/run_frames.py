@@ -1,5 +1,5 @@
 """Advance S synthetic streams by F frames through an engine (driver for ncu captures).
-usage: run_frames.py [S=1024] [F=45] [K=100] [tracker=ocsort|bytetrack|botsort|deepocsort|boosttrack] [E=512]"""
+usage: run_frames.py [S=1024] [F=45] [K=100] [tracker=ocsort|bytetrack|botsort|strongsort|deepocsort|boosttrack] [E=512]"""
 import os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -17,6 +17,12 @@ if tracker == "botsort":
     eng = BotSortEngine(S, track_cap=512, det_cap=256, emb_dim=E, track_high_thresh=0.6, track_low_thresh=0.1,
                         new_track_thresh=0.7, track_buffer=30, match_thresh=0.8, proximity_thresh=0.5,
                         appearance_thresh=0.25, frame_rate=30, fuse_first_associate=False, with_reid=True)
+elif tracker == "strongsort":
+    import bench
+    from boxmot_b200.engine import StrongSortEngine
+    E = int(sys.argv[5]) if len(sys.argv) > 5 else 768
+    dets, nd, embs = make_batch(S, K, F, 128, emb_dim=E)
+    eng = StrongSortEngine(S, track_cap=2048, det_cap=128, pool_cap=8192, emb_dim=E, **bench.STRONGSORT_ARGS)
 elif tracker in ("deepocsort", "boosttrack"):
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import bench
@@ -29,7 +35,7 @@ elif tracker in ("deepocsort", "boosttrack"):
         eng = BoostTrackEngine(S, track_cap=256, det_cap=128, emb_dim=E, **bench.BOOSTTRACK_YAML)
 else:
     dets, nd = make_batch(S, K, F, 128)
-if tracker in ("botsort", "deepocsort", "boosttrack"):
+if tracker in ("botsort", "deepocsort", "boosttrack", "strongsort"):
     pass
 elif tracker == "bytetrack":
     eng = ByteTrackEngine(S, track_cap=256, det_cap=128, min_conf=0.1, track_thresh=0.6, match_thresh=0.9,
